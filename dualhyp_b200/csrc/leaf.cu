@@ -1,0 +1,451 @@
+// Bandwidth-bound leaf kernels of the decoder path: RMSNorm fwd/bwd, embedding gather, RoPE (standalone
+// API and in-place on the interleaved QKV row), cross-entropy over bf16 logits with in-place gradient,
+// loss reduction, arg-max, casts, fused AdamW, KV-cache scatter.  All are one pass over their operands
+// with 16-byte vector accesses; grids are sized by rows so every SM streams.
+#include <math.h>
+
+#include "common.cuh"
+#include "../../include/dualhyp.h"
+
+namespace dh {
+
+// block-wide sum; every thread gets the result.  blockDim.x <= 1024, multiple of 32.
+__device__ __forceinline__ float block_sum(float v, float* red) {
+  v = warp_sum(v);
+  const int w = threadIdx.x >> 5, l = threadIdx.x & 31, nw = blockDim.x >> 5;
+  __syncthreads();
+  if (l == 0) red[w] = v;
+  __syncthreads();
+  float t = (l < nw) ? red[l] : 0.f;
+  return warp_sum(t);
+}
+__device__ __forceinline__ float block_max(float v, float* red) {
+  v = warp_max(v);
+  const int w = threadIdx.x >> 5, l = threadIdx.x & 31, nw = blockDim.x >> 5;
+  __syncthreads();
+  if (l == 0) red[w] = v;
+  __syncthreads();
+  float t = (l < nw) ? red[l] : -INFINITY;
+  return warp_max(t);
+}
+
+__device__ __forceinline__ void load8(const float* p, float (&f)[8]) {
+  float4 a = reinterpret_cast<const float4*>(p)[0], b = reinterpret_cast<const float4*>(p)[1];
+  f[0] = a.x; f[1] = a.y; f[2] = a.z; f[3] = a.w; f[4] = b.x; f[5] = b.y; f[6] = b.z; f[7] = b.w;
+}
+__device__ __forceinline__ void load8(const bf16* p, float (&f)[8]) {
+  uint4 u = *reinterpret_cast<const uint4*>(p);
+  float2 a = unpack_bf16x2(u.x), b = unpack_bf16x2(u.y), c = unpack_bf16x2(u.z), d = unpack_bf16x2(u.w);
+  f[0] = a.x; f[1] = a.y; f[2] = b.x; f[3] = b.y; f[4] = c.x; f[5] = c.y; f[6] = d.x; f[7] = d.y;
+}
+__device__ __forceinline__ void store8(float* p, const float (&f)[8]) {
+  reinterpret_cast<float4*>(p)[0] = make_float4(f[0], f[1], f[2], f[3]);
+  reinterpret_cast<float4*>(p)[1] = make_float4(f[4], f[5], f[6], f[7]);
+}
+__device__ __forceinline__ void store8(bf16* p, const float (&f)[8]) {
+  uint4 u;
+  u.x = pack_bf16x2(f[0], f[1]); u.y = pack_bf16x2(f[2], f[3]);
+  u.z = pack_bf16x2(f[4], f[5]); u.w = pack_bf16x2(f[6], f[7]);
+  *reinterpret_cast<uint4*>(p) = u;
+}
+
+// ---------------------------------------------------------------------------------------------
+// RMSNorm (ger/rmsnorm.py:17-21).  One block per row, 8 elements per thread (blockDim = C/8).
+// ---------------------------------------------------------------------------------------------
+template <typename XT>
+__global__ void rmsnorm_fwd_kernel(const XT* __restrict__ x, const float* __restrict__ w, bf16* __restrict__ y,
+                                   float* __restrict__ rstd, int C, float eps) {
+  __shared__ float red[32];
+  const long long row = blockIdx.x;
+  const int c0 = threadIdx.x * 8;
+  float v[8], g[8];
+  load8(x + row * C + c0, v);
+  load8(w + c0, g);
+  float ss = 0.f;
+#pragma unroll
+  for (int i = 0; i < 8; ++i) ss += v[i] * v[i];
+  ss = block_sum(ss, red);
+  const float r = rsqrtf(ss / (float)C + eps);
+#pragma unroll
+  for (int i = 0; i < 8; ++i) v[i] = g[i] * (v[i] * r);
+  store8(y + row * C + c0, v);
+  if (rstd && threadIdx.x == 0) rstd[row] = r;
+}
+
+// dx = dres + rstd * (w*dy - xhat * mean(w*dy*xhat)),  xhat = x*rstd
+template <typename XT>
+__global__ void rmsnorm_bwd_kernel(const XT* __restrict__ x, const float* __restrict__ w, const float* __restrict__ rstd,
+                                   const bf16* __restrict__ dy, const float* dres, float* dx_out, bf16* dx_bf16, int C) {
+  __shared__ float red[32];
+  const long long row = blockIdx.x;
+  const int c0 = threadIdx.x * 8;
+  float xv[8], g[8], d[8];
+  load8(x + row * C + c0, xv);
+  load8(w + c0, g);
+  load8(dy + row * C + c0, d);
+  const float r = rstd[row];
+  float dot = 0.f;
+#pragma unroll
+  for (int i = 0; i < 8; ++i) {
+    xv[i] *= r;          // xhat
+    d[i] *= g[i];        // w*dy
+    dot += d[i] * xv[i];
+  }
+  dot = block_sum(dot, red) / (float)C;
+  float o[8];
+  if (dres) load8(dres + row * C + c0, o);
+  else {
+#pragma unroll
+    for (int i = 0; i < 8; ++i) o[i] = 0.f;
+  }
+#pragma unroll
+  for (int i = 0; i < 8; ++i) o[i] += r * (d[i] - xv[i] * dot);
+  store8(dx_out + row * C + c0, o);
+  if (dx_bf16) store8(dx_bf16 + row * C + c0, o);
+}
+
+// ---------------------------------------------------------------------------------------------
+// embedding gather (ger/lora.py:537)
+// ---------------------------------------------------------------------------------------------
+template <typename WT, typename OT>
+__global__ void embedding_kernel(const long long* __restrict__ idx, const WT* __restrict__ wte, OT* __restrict__ out, int C,
+                                 int vocab_rows) {
+  const long long row = blockIdx.x;
+  long long id = idx[row];
+  if (id < 0 || id >= vocab_rows) __trap();   // nn.Embedding raises on out-of-range ids
+  for (int c0 = threadIdx.x * 8; c0 < C; c0 += blockDim.x * 8) {
+    float v[8];
+    load8(wte + id * C + c0, v);
+    store8(out + row * C + c0, v);
+  }
+}
+
+// ---------------------------------------------------------------------------------------------
+// RoPE
+// ---------------------------------------------------------------------------------------------
+// apply_rotary_emb_func (ger/fused_rotary_embedding.py:10-90): x (B,T,H,D), cos/sin [T, rot/2].
+template <typename CT>
+__global__ void rope_apply_kernel(const bf16* __restrict__ x, bf16* out, const CT* __restrict__ cs, const CT* __restrict__ sn,
+                                  long long total_pairs, int T, int H, int D, int rot, int interleaved, int conj) {
+  const int half = rot / 2;
+  for (long long i = blockIdx.x * (long long)blockDim.x + threadIdx.x; i < total_pairs; i += (long long)gridDim.x * blockDim.x) {
+    const int p = (int)(i % half);
+    const long long bth = i / half;
+    const int t = (int)((bth / H) % T);
+    const long long base = bth * D;
+    const int i1 = interleaved ? 2 * p : p, i2 = interleaved ? 2 * p + 1 : p + half;
+    const float c = (float)cs[(long long)t * half + p];
+    float s = (float)sn[(long long)t * half + p];
+    if (conj) s = -s;
+    const float x1 = __bfloat162float(x[base + i1]), x2 = __bfloat162float(x[base + i2]);
+    out[base + i1] = __float2bfloat16_rn(x1 * c - x2 * s);
+    out[base + i2] = __float2bfloat16_rn(x1 * s + x2 * c);
+  }
+}
+__global__ void copy_tail_kernel(const bf16* __restrict__ x, bf16* out, long long n_heads, int D, int rot) {
+  const int tail = D - rot;
+  for (long long i = blockIdx.x * (long long)blockDim.x + threadIdx.x; i < n_heads * tail; i += (long long)gridDim.x * blockDim.x) {
+    const long long h = i / tail;
+    const int d = rot + (int)(i % tail);
+    out[h * D + d] = x[h * D + d];
+  }
+}
+
+// In-place NeoX rotation of the q and k slots of group-interleaved rows; tables bf16 [block, 64].
+__global__ void rope_qkv_inplace_kernel(bf16* qkv, const bf16* __restrict__ cs, const bf16* __restrict__ sn,
+                                        const int* __restrict__ positions, int M, int seq_len, int n_groups, int qpk, int conj) {
+  const int slots = n_groups * (qpk + 2);
+  const long long total = (long long)M * slots * 4;   // 4 threads per 64-wide head, 8 pairs each
+  for (long long i = blockIdx.x * (long long)blockDim.x + threadIdx.x; i < total; i += (long long)gridDim.x * blockDim.x) {
+    const int part = (int)(i & 3);
+    const long long rs = i >> 2;
+    const int slot = (int)(rs % slots);
+    const long long row = rs / slots;
+    if ((slot % (qpk + 2)) == qpk + 1) continue;   // v slot
+    const int pos = positions ? positions[row] : (int)(row % seq_len);
+    bf16* h = qkv + (row * slots + slot) * 64;
+    float a[8], b[8], c[8], s[8];
+    load8(h + part * 8, a);
+    load8(h + 32 + part * 8, b);
+    load8(cs + (long long)pos * 64 + part * 8, c);
+    load8(sn + (long long)pos * 64 + part * 8, s);
+    float o1[8], o2[8];
+#pragma unroll
+    for (int j = 0; j < 8; ++j) {
+      const float sj = conj ? -s[j] : s[j];
+      o1[j] = a[j] * c[j] - b[j] * sj;
+      o2[j] = b[j] * c[j] + a[j] * sj;
+    }
+    store8(h + part * 8, o1);
+    store8(h + 32 + part * 8, o2);
+  }
+}
+
+// ---------------------------------------------------------------------------------------------
+// cross entropy over one bf16 logits row held in shared memory; gradient written in place
+// ---------------------------------------------------------------------------------------------
+__global__ void __launch_bounds__(256) cross_entropy_kernel(bf16* logits, long long ldl, const long long* __restrict__ targets,
+                                                            float* __restrict__ row_loss, int V, float grad_scale, int write_grad) {
+  extern __shared__ uint4 srow[];   // V/8 uint4
+  __shared__ float red[32];
+  const long long row = blockIdx.x;
+  const long long tg = targets[row];
+  bf16* lrow = logits + row * ldl;
+  const int nv = V / 8;
+  if (tg < 0) {   // ignore_index = -1: no loss, zero gradient
+    if (threadIdx.x == 0) row_loss[row] = 0.f;
+    if (write_grad) {
+      const uint4 z = make_uint4(0, 0, 0, 0);
+      for (int i = threadIdx.x; i < nv; i += blockDim.x) reinterpret_cast<uint4*>(lrow)[i] = z;
+    }
+    return;
+  }
+  if (tg >= V) __trap();
+  float mx = -INFINITY;
+  for (int i = threadIdx.x; i < nv; i += blockDim.x) {
+    uint4 u = reinterpret_cast<const uint4*>(lrow)[i];
+    srow[i] = u;
+    float2 a = unpack_bf16x2(u.x), b = unpack_bf16x2(u.y), c = unpack_bf16x2(u.z), d = unpack_bf16x2(u.w);
+    mx = fmaxf(mx, fmaxf(fmaxf(fmaxf(a.x, a.y), fmaxf(b.x, b.y)), fmaxf(fmaxf(c.x, c.y), fmaxf(d.x, d.y))));
+  }
+  mx = block_max(mx, red);
+  const float L2E = 1.4426950408889634f;
+  float sum = 0.f;
+  for (int i = threadIdx.x; i < nv; i += blockDim.x) {
+    uint4 u = srow[i];
+    float2 a = unpack_bf16x2(u.x), b = unpack_bf16x2(u.y), c = unpack_bf16x2(u.z), d = unpack_bf16x2(u.w);
+    sum += exp2f((a.x - mx) * L2E) + exp2f((a.y - mx) * L2E) + exp2f((b.x - mx) * L2E) + exp2f((b.y - mx) * L2E) +
+           exp2f((c.x - mx) * L2E) + exp2f((c.y - mx) * L2E) + exp2f((d.x - mx) * L2E) + exp2f((d.y - mx) * L2E);
+  }
+  sum = block_sum(sum, red);
+  const float lse = mx + logf(sum);
+  const bf16* s16 = reinterpret_cast<const bf16*>(srow);
+  if (threadIdx.x == 0) row_loss[row] = lse - __bfloat162float(s16[tg]);
+  if (write_grad) {
+    const float inv = grad_scale / sum;
+    for (int i = threadIdx.x; i < nv; i += blockDim.x) {
+      uint4 u = srow[i];
+      float f[8];
+      float2 a = unpack_bf16x2(u.x), b = unpack_bf16x2(u.y), c = unpack_bf16x2(u.z), d = unpack_bf16x2(u.w);
+      f[0] = a.x; f[1] = a.y; f[2] = b.x; f[3] = b.y; f[4] = c.x; f[5] = c.y; f[6] = d.x; f[7] = d.y;
+#pragma unroll
+      for (int j = 0; j < 8; ++j) {
+        f[j] = exp2f((f[j] - mx) * L2E) * inv;
+        if ((long long)i * 8 + j == tg) f[j] -= grad_scale;
+      }
+      store8(lrow + (long long)i * 8, f);
+    }
+  }
+}
+
+__global__ void loss_reduce_kernel(const float* __restrict__ row_loss, const long long* __restrict__ targets, float* out2, int M) {
+  __shared__ float red[32];
+  float s = 0.f, n = 0.f;
+  for (int i = threadIdx.x; i < M; i += blockDim.x) {
+    s += row_loss[i];
+    n += targets[i] >= 0 ? 1.f : 0.f;
+  }
+  s = block_sum(s, red);
+  n = block_sum(n, red);
+  if (threadIdx.x == 0) { out2[0] = s; out2[1] = n; }
+}
+
+__global__ void __launch_bounds__(256) argmax_kernel(const bf16* __restrict__ logits, long long ldl, long long* __restrict__ ids, int V) {
+  __shared__ float sv[8];
+  __shared__ int si[8];
+  const long long row = blockIdx.x;
+  const bf16* l = logits + row * ldl;
+  float best = -INFINITY;
+  int bi = 0x7fffffff;
+  for (int i = threadIdx.x; i < V; i += blockDim.x) {
+    float v = __bfloat162float(l[i]);
+    if (v > best) { best = v; bi = i; }   // strided scan keeps the lowest index per thread
+  }
+#pragma unroll
+  for (int o = 16; o > 0; o >>= 1) {
+    float ov = __shfl_xor_sync(0xffffffffu, best, o);
+    int oi = __shfl_xor_sync(0xffffffffu, bi, o);
+    if (ov > best || (ov == best && oi < bi)) { best = ov; bi = oi; }
+  }
+  if ((threadIdx.x & 31) == 0) { sv[threadIdx.x >> 5] = best; si[threadIdx.x >> 5] = bi; }
+  __syncthreads();
+  if (threadIdx.x == 0) {
+    for (int w = 1; w < (int)(blockDim.x >> 5); ++w)
+      if (sv[w] > best || (sv[w] == best && si[w] < bi)) { best = sv[w]; bi = si[w]; }
+    ids[row] = bi;
+  }
+}
+
+__global__ void cast_f32_bf16_kernel(const float* __restrict__ src, long long lds, bf16* __restrict__ dst, long long ldd,
+                                     long long rows, long long cols) {
+  const long long cv = cols / 8;
+  for (long long i = blockIdx.x * (long long)blockDim.x + threadIdx.x; i < rows * cv; i += (long long)gridDim.x * blockDim.x) {
+    const long long r = i / cv, c = (i % cv) * 8;
+    float v[8];
+    load8(src + r * lds + c, v);
+    store8(dst + r * ldd + c, v);
+  }
+}
+
+// torch.optim.AdamW (decoupled weight decay, bias-corrected), one flat bucket
+__global__ void adamw_kernel(float* p, const float* __restrict__ g, float* m, float* v, long long n, float lr, float b1, float b2,
+                             float eps, float wd, float bc1, float bc2_sqrt, float gscale) {
+  for (long long i = blockIdx.x * (long long)blockDim.x + threadIdx.x; i < n; i += (long long)gridDim.x * blockDim.x) {
+    const float gi = g[i] * gscale;
+    float pi = p[i] * (1.f - lr * wd);
+    const float mi = b1 * m[i] + (1.f - b1) * gi;
+    const float vi = b2 * v[i] + (1.f - b2) * gi * gi;
+    m[i] = mi;
+    v[i] = vi;
+    const float denom = sqrtf(vi) / bc2_sqrt + eps;
+    p[i] = pi - (lr / bc1) * (mi / denom);
+  }
+}
+
+// scatter k and v slots of interleaved qkv rows into [nseq, n_groups, max_len, 64] caches
+__global__ void kv_cache_write_kernel(const bf16* __restrict__ qkv, bf16* ck, bf16* cv, const int* __restrict__ seq,
+                                      const int* __restrict__ pos, int M, int max_len, int n_groups, int qpk) {
+  const long long total = (long long)M * n_groups * 2 * 8;   // 8 uint4 per 64-wide head
+  const int slots = n_groups * (qpk + 2);
+  for (long long i = blockIdx.x * (long long)blockDim.x + threadIdx.x; i < total; i += (long long)gridDim.x * blockDim.x) {
+    const int part = (int)(i & 7);
+    long long r = i >> 3;
+    const int is_v = (int)(r & 1); r >>= 1;
+    const int g = (int)(r % n_groups);
+    const long long row = r / n_groups;
+    const uint4 u = *reinterpret_cast<const uint4*>(qkv + (row * slots + g * (qpk + 2) + qpk + is_v) * 64 + part * 8);
+    bf16* dst = (is_v ? cv : ck) + (((long long)seq[row] * n_groups + g) * max_len + pos[row]) * 64 + part * 8;
+    *reinterpret_cast<uint4*>(dst) = u;
+  }
+}
+
+static inline int grid_for(long long work, int block) {
+  long long g = (work + block - 1) / block;
+  long long cap = (long long)sm_count() * 16;
+  return (int)(g < 1 ? 1 : (g > cap ? cap : g));
+}
+
+}  // namespace dh
+
+using namespace dh;
+
+extern "C" int dh_rmsnorm_fwd(const void* x, int x_dtype, const float* weight, void* y, float* rstd, int M, int C, float eps,
+                              void* stream) {
+  DH_CHECK(x && weight && y && M > 0, "dh_rmsnorm_fwd: null argument");
+  DH_CHECK(C % 256 == 0 && C <= 8192, "dh_rmsnorm_fwd: C=%d must be a multiple of 256 and <= 8192", C);
+  cudaStream_t s = (cudaStream_t)stream;
+  if (x_dtype == 0) rmsnorm_fwd_kernel<float><<<M, C / 8, 0, s>>>((const float*)x, weight, (bf16*)y, rstd, C, eps);
+  else rmsnorm_fwd_kernel<bf16><<<M, C / 8, 0, s>>>((const bf16*)x, weight, (bf16*)y, rstd, C, eps);
+  DH_CUDA(cudaGetLastError());
+  return 0;
+}
+
+extern "C" int dh_rmsnorm_bwd(const void* x, int x_dtype, const float* weight, const float* rstd, const void* dy,
+                              const float* dres, float* dx_out, void* dx_bf16, int M, int C, void* stream) {
+  DH_CHECK(x && weight && rstd && dy && dx_out && M > 0, "dh_rmsnorm_bwd: null argument");
+  DH_CHECK(C % 256 == 0 && C <= 8192, "dh_rmsnorm_bwd: C=%d must be a multiple of 256 and <= 8192", C);
+  cudaStream_t s = (cudaStream_t)stream;
+  if (x_dtype == 0)
+    rmsnorm_bwd_kernel<float><<<M, C / 8, 0, s>>>((const float*)x, weight, rstd, (const bf16*)dy, dres, dx_out, (bf16*)dx_bf16, C);
+  else
+    rmsnorm_bwd_kernel<bf16><<<M, C / 8, 0, s>>>((const bf16*)x, weight, rstd, (const bf16*)dy, dres, dx_out, (bf16*)dx_bf16, C);
+  DH_CUDA(cudaGetLastError());
+  return 0;
+}
+
+extern "C" int dh_embedding_fwd(const int64_t* idx, const void* wte, int wte_dtype, void* out, int out_dtype, int M, int C,
+                                int vocab_rows, void* stream) {
+  DH_CHECK(idx && wte && out && M > 0 && C % 8 == 0, "dh_embedding_fwd: bad argument");
+  cudaStream_t s = (cudaStream_t)stream;
+  const int block = C / 8 < 256 ? ((C / 8 + 31) / 32) * 32 : 256;
+  const long long* ix = (const long long*)idx;
+  if (wte_dtype == 0 && out_dtype == 0) embedding_kernel<float, float><<<M, block, 0, s>>>(ix, (const float*)wte, (float*)out, C, vocab_rows);
+  else if (wte_dtype == 0 && out_dtype == 1) embedding_kernel<float, bf16><<<M, block, 0, s>>>(ix, (const float*)wte, (bf16*)out, C, vocab_rows);
+  else if (wte_dtype == 1 && out_dtype == 0) embedding_kernel<bf16, float><<<M, block, 0, s>>>(ix, (const bf16*)wte, (float*)out, C, vocab_rows);
+  else embedding_kernel<bf16, bf16><<<M, block, 0, s>>>(ix, (const bf16*)wte, (bf16*)out, C, vocab_rows);
+  DH_CUDA(cudaGetLastError());
+  return 0;
+}
+
+extern "C" int dh_rope_apply(const void* x, void* out, const void* cos, const void* sin, int cs_dtype, int B, int T, int H, int D,
+                             int rot, int interleaved, int conj, void* stream) {
+  DH_CHECK(x && out && cos && sin, "dh_rope_apply: null argument");
+  DH_CHECK(rot % 2 == 0 && rot <= D && rot > 0, "dh_rope_apply: rotary_dim %d must be even and <= headdim %d", rot, D);
+  cudaStream_t s = (cudaStream_t)stream;
+  const long long heads = (long long)B * T * H;
+  const long long pairs = heads * (rot / 2);
+  if (cs_dtype == 0)
+    rope_apply_kernel<float><<<grid_for(pairs, 256), 256, 0, s>>>((const bf16*)x, (bf16*)out, (const float*)cos, (const float*)sin, pairs, T, H, D, rot, interleaved, conj);
+  else
+    rope_apply_kernel<bf16><<<grid_for(pairs, 256), 256, 0, s>>>((const bf16*)x, (bf16*)out, (const bf16*)cos, (const bf16*)sin, pairs, T, H, D, rot, interleaved, conj);
+  if (out != x && rot < D) copy_tail_kernel<<<grid_for(heads * (D - rot), 256), 256, 0, s>>>((const bf16*)x, (bf16*)out, heads, D, rot);
+  DH_CUDA(cudaGetLastError());
+  return 0;
+}
+
+extern "C" int dh_rope_qkv_inplace(void* qkv, const void* cos, const void* sin, const int32_t* positions, int M, int seq_len,
+                                   int n_groups, int q_per_kv, int conj, void* stream) {
+  DH_CHECK(qkv && cos && sin && M > 0 && seq_len > 0, "dh_rope_qkv_inplace: bad argument");
+  const long long total = (long long)M * n_groups * (q_per_kv + 2) * 4;
+  rope_qkv_inplace_kernel<<<grid_for(total, 256), 256, 0, (cudaStream_t)stream>>>((bf16*)qkv, (const bf16*)cos, (const bf16*)sin,
+                                                                                   positions, M, seq_len, n_groups, q_per_kv, conj);
+  DH_CUDA(cudaGetLastError());
+  return 0;
+}
+
+extern "C" int dh_cross_entropy(void* logits, int64_t ldl, const int64_t* targets, float* row_loss, int M, int V, float grad_scale,
+                                int write_grad, void* stream) {
+  DH_CHECK(logits && targets && row_loss && M > 0, "dh_cross_entropy: null argument");
+  DH_CHECK(V % 8 == 0 && ldl % 8 == 0 && V * 2 <= 200 * 1024, "dh_cross_entropy: V=%d must be a multiple of 8 and fit shared memory", V);
+  static bool attr = false;
+  if (!attr) {
+    DH_CUDA(cudaFuncSetAttribute(cross_entropy_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, 200 * 1024));
+    attr = true;
+  }
+  cross_entropy_kernel<<<M, 256, (size_t)V * 2, (cudaStream_t)stream>>>((bf16*)logits, ldl, (const long long*)targets, row_loss, V,
+                                                                        grad_scale, write_grad);
+  DH_CUDA(cudaGetLastError());
+  return 0;
+}
+
+extern "C" int dh_loss_reduce(const float* row_loss, const int64_t* targets, float* out2, int M, void* stream) {
+  DH_CHECK(row_loss && targets && out2 && M > 0, "dh_loss_reduce: null argument");
+  loss_reduce_kernel<<<1, 1024, 0, (cudaStream_t)stream>>>(row_loss, (const long long*)targets, out2, M);
+  DH_CUDA(cudaGetLastError());
+  return 0;
+}
+
+extern "C" int dh_argmax(const void* logits, int64_t ldl, int64_t* ids, int M, int V, void* stream) {
+  DH_CHECK(logits && ids && M > 0 && V > 0, "dh_argmax: bad argument");
+  argmax_kernel<<<M, 256, 0, (cudaStream_t)stream>>>((const bf16*)logits, ldl, (long long*)ids, V);
+  DH_CUDA(cudaGetLastError());
+  return 0;
+}
+
+extern "C" int dh_cast_f32_to_bf16(const float* src, int64_t lds, void* dst, int64_t ldd, int64_t rows, int64_t cols, void* stream) {
+  DH_CHECK(src && dst && rows > 0 && cols > 0 && cols % 8 == 0 && lds % 4 == 0 && ldd % 8 == 0, "dh_cast_f32_to_bf16: bad argument");
+  cast_f32_bf16_kernel<<<grid_for(rows * cols / 8, 256), 256, 0, (cudaStream_t)stream>>>(src, lds, (bf16*)dst, ldd, rows, cols);
+  DH_CUDA(cudaGetLastError());
+  return 0;
+}
+
+extern "C" int dh_adamw_step(float* param, const float* grad, float* exp_avg, float* exp_avg_sq, int64_t n, float lr, float beta1,
+                             float beta2, float eps, float weight_decay, int step, float grad_scale, void* stream) {
+  DH_CHECK(param && grad && exp_avg && exp_avg_sq && n > 0 && step > 0, "dh_adamw_step: bad argument");
+  const float bc1 = 1.f - powf(beta1, (float)step);
+  const float bc2s = sqrtf(1.f - powf(beta2, (float)step));
+  adamw_kernel<<<grid_for(n, 256), 256, 0, (cudaStream_t)stream>>>(param, grad, exp_avg, exp_avg_sq, n, lr, beta1, beta2, eps,
+                                                                    weight_decay, bc1, bc2s, grad_scale);
+  DH_CUDA(cudaGetLastError());
+  return 0;
+}
+
+extern "C" int dh_kv_cache_write(const void* qkv, void* cache_k, void* cache_v, const int32_t* seq, const int32_t* pos, int M,
+                                 int max_len, int n_groups, int q_per_kv, void* stream) {
+  DH_CHECK(qkv && cache_k && cache_v && seq && pos && M > 0, "dh_kv_cache_write: null argument");
+  const long long total = (long long)M * n_groups * 16;
+  kv_cache_write_kernel<<<grid_for(total, 256), 256, 0, (cudaStream_t)stream>>>((const bf16*)qkv, (bf16*)cache_k, (bf16*)cache_v, seq,
+                                                                                 pos, M, max_len, n_groups, q_per_kv);
+  DH_CUDA(cudaGetLastError());
+  return 0;
+}

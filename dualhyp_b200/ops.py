@@ -1,0 +1,255 @@
+"""Tensor-level wrappers over the C ABI (include/dualhyp.h).  PyTorch is used for device memory and the
+current stream only; every function here enqueues hand-written sm_100a kernels and nothing else."""
+from __future__ import annotations
+
+import ctypes as C
+from typing import Optional
+
+import torch
+
+from . import _lib
+from ._lib import (EPI_BF16, EPI_F32, EPI_QKV_ROPE, EPI_RESID_BF16, EPI_RESID_F32, EPI_SWIGLU, EPI_SWIGLU_BWD,
+                   GemmArgs, check)
+
+Tensor = torch.Tensor
+_launches = 0           # kernels launched through this module (bench.py reports it as gpu_launches)
+
+
+def launches() -> int:
+    return _launches
+
+
+def _count(n: int = 1) -> None:
+    global _launches
+    _launches += n
+
+
+def _stream() -> int:
+    return torch.cuda.current_stream().cuda_stream
+
+
+def _ptr(t: Optional[Tensor]) -> Optional[int]:
+    return None if t is None else t.data_ptr()
+
+
+def _dev(t: Tensor) -> None:
+    if not t.is_cuda:
+        raise _lib.DualHypError("dualhyp_b200 ops need CUDA tensors (there is no CPU fallback)")
+    _lib.init(t.device.index or 0)
+
+
+def _rowmajor(t: Tensor, what: str) -> int:
+    """Leading dimension of a 2-D row-major view (last stride 1)."""
+    if t.dim() != 2 or t.stride(1) != 1:
+        raise _lib.DualHypError(f"{what}: expected a 2-D row-major tensor, got shape {tuple(t.shape)} strides {t.stride()}")
+    return t.stride(0)
+
+
+def gemm(A: Tensor, B: Tensor, out: Optional[Tensor], *, epilogue: int = EPI_BF16, b_layout: int = 0, a_layout: int = 0,
+         A2: Optional[Tensor] = None, B2: Optional[Tensor] = None, a2_layout: int = 0, b2_layout: int = 0,
+         out2: Optional[Tensor] = None, aux: Optional[Tensor] = None, alpha: float = 1.0, accumulate: bool = False,
+         col_scale: Optional[Tensor] = None, col_bias: Optional[Tensor] = None, rope_cos: Optional[Tensor] = None,
+         rope_sin: Optional[Tensor] = None, positions: Optional[Tensor] = None, seq_len: int = 0, q_per_kv: int = 0) -> None:
+    """D = A op(B) (+ A2 op(B2)) with a fused epilogue; see `dh_gemm` in include/dualhyp.h."""
+    _dev(A)
+    assert A.dtype == torch.bfloat16 and B.dtype == torch.bfloat16
+    a = GemmArgs()
+    a.A, a.lda = A.data_ptr(), _rowmajor(A, "A")
+    a.B, a.ldb = B.data_ptr(), _rowmajor(B, "B")
+    if a_layout == 0:
+        M, K = A.shape
+    else:
+        K, M = A.shape
+    if b_layout == 0:
+        N, Kb = B.shape
+    else:
+        Kb, N = B.shape
+    assert K == Kb, f"K mismatch: A gives {K}, B gives {Kb}"
+    a.M, a.N, a.K1, a.K2 = M, N, K, 0
+    a.a_layout, a.b_layout = a_layout, b_layout
+    if A2 is not None:
+        assert B2 is not None and A2.dtype == torch.bfloat16 and B2.dtype == torch.bfloat16
+        a.A2, a.lda2 = A2.data_ptr(), _rowmajor(A2, "A2")
+        a.B2, a.ldb2 = B2.data_ptr(), _rowmajor(B2, "B2")
+        a.K2 = A2.shape[1] if a2_layout == 0 else A2.shape[0]
+        a.a2_layout, a.b2_layout = a2_layout, b2_layout
+    a.epilogue, a.accumulate, a.alpha = epilogue, int(accumulate), alpha
+    a.seq_len, a.q_per_kv = seq_len, q_per_kv
+    if out is not None:
+        a.out, a.ldo = out.data_ptr(), _rowmajor(out, "out")
+    if out2 is not None:
+        a.out2, a.ldo2 = out2.data_ptr(), _rowmajor(out2, "out2")
+    if aux is not None:
+        a.aux, a.ldaux = aux.data_ptr(), _rowmajor(aux, "aux")
+    a.col_scale, a.col_bias = _ptr(col_scale), _ptr(col_bias)
+    a.rope_cos, a.rope_sin, a.positions = _ptr(rope_cos), _ptr(rope_sin), _ptr(positions)
+    check(_lib.load().dh_gemm(C.byref(a), _stream()), "dh_gemm")
+    _count()
+
+
+def rmsnorm_fwd(x: Tensor, weight: Tensor, y: Tensor, rstd: Optional[Tensor], eps: float) -> None:
+    _dev(x)
+    M, Cdim = x.shape
+    assert x.is_contiguous() and y.is_contiguous() and weight.dtype == torch.float32 and y.dtype == torch.bfloat16
+    xd = 0 if x.dtype == torch.float32 else 1
+    check(_lib.load().dh_rmsnorm_fwd(x.data_ptr(), xd, weight.data_ptr(), y.data_ptr(), _ptr(rstd), M, Cdim, eps, _stream()),
+          "dh_rmsnorm_fwd")
+    _count()
+
+
+def rmsnorm_bwd(x: Tensor, weight: Tensor, rstd: Tensor, dy: Tensor, dres: Optional[Tensor], dx_out: Tensor,
+                dx_bf16: Optional[Tensor]) -> None:
+    _dev(x)
+    M, Cdim = x.shape
+    assert x.is_contiguous() and dy.is_contiguous() and dx_out.is_contiguous() and dy.dtype == torch.bfloat16
+    xd = 0 if x.dtype == torch.float32 else 1
+    check(_lib.load().dh_rmsnorm_bwd(x.data_ptr(), xd, weight.data_ptr(), rstd.data_ptr(), dy.data_ptr(), _ptr(dres),
+                                     dx_out.data_ptr(), _ptr(dx_bf16), M, Cdim, _stream()), "dh_rmsnorm_bwd")
+    _count()
+
+
+def embedding_fwd(idx: Tensor, wte: Tensor, out: Tensor) -> None:
+    _dev(wte)
+    assert idx.dtype == torch.int64 and idx.is_contiguous() and wte.is_contiguous() and out.is_contiguous()
+    M = idx.numel()
+    dt = {torch.float32: 0, torch.bfloat16: 1}
+    check(_lib.load().dh_embedding_fwd(idx.data_ptr(), wte.data_ptr(), dt[wte.dtype], out.data_ptr(), dt[out.dtype], M,
+                                       wte.shape[1], wte.shape[0], _stream()), "dh_embedding_fwd")
+    _count()
+
+
+def rope_apply(x: Tensor, cos: Tensor, sin: Tensor, out: Tensor, interleaved: bool = False, conj: bool = False) -> None:
+    """x (B,T,H,D) bf16, cos/sin (T, rot/2) f32|bf16 -- ger/fused_rotary_embedding.py:10-90."""
+    _dev(x)
+    B, T, H, D = x.shape
+    assert x.is_contiguous() and out.is_contiguous() and x.dtype == torch.bfloat16 and cos.is_contiguous() and sin.is_contiguous()
+    assert cos.shape[0] >= T and cos.shape == sin.shape and cos.dtype == sin.dtype
+    csd = 0 if cos.dtype == torch.float32 else 1
+    check(_lib.load().dh_rope_apply(x.data_ptr(), out.data_ptr(), cos.data_ptr(), sin.data_ptr(), csd, B, T, H, D,
+                                    2 * cos.shape[1], int(interleaved), int(conj), _stream()), "dh_rope_apply")
+    _count(2 if (out.data_ptr() != x.data_ptr() and 2 * cos.shape[1] < D) else 1)
+
+
+def rope_qkv_inplace(qkv: Tensor, cos: Tensor, sin: Tensor, seq_len: int, n_groups: int, q_per_kv: int, conj: bool,
+                     positions: Optional[Tensor] = None) -> None:
+    _dev(qkv)
+    assert qkv.is_contiguous() and qkv.dtype == torch.bfloat16 and cos.dtype == torch.bfloat16
+    check(_lib.load().dh_rope_qkv_inplace(qkv.data_ptr(), cos.data_ptr(), sin.data_ptr(), _ptr(positions), qkv.shape[0], seq_len,
+                                          n_groups, q_per_kv, int(conj), _stream()), "dh_rope_qkv_inplace")
+    _count()
+
+
+def attention_fwd(qkv: Tensor, out: Tensor, lse: Tensor, B: int, T: int, n_groups: int, q_per_kv: int,
+                  prefix_kv: Optional[Tensor] = None, gate: Optional[Tensor] = None, prefix_len: int = 0) -> None:
+    _dev(qkv)
+    assert qkv.is_contiguous() and out.is_contiguous() and lse.is_contiguous() and qkv.dtype == torch.bfloat16
+    assert qkv.shape == (B * T, n_groups * (q_per_kv + 2) * 64) and out.shape == (B * T, n_groups * q_per_kv * 64)
+    if prefix_kv is not None:
+        assert prefix_kv.is_contiguous() and prefix_kv.shape[1] == qkv.shape[1] and gate.dtype == torch.float32
+    check(_lib.load().dh_attention_fwd(qkv.data_ptr(), out.data_ptr(), lse.data_ptr(), _ptr(prefix_kv), _ptr(gate), B, T, n_groups,
+                                       q_per_kv, prefix_len, _stream()), "dh_attention_fwd")
+    _count()
+
+
+def attention_bwd_workspace(B: int, T: int, n_groups: int, q_per_kv: int) -> int:
+    return int(_lib.load().dh_attention_bwd_workspace(B, T, n_groups, q_per_kv))
+
+
+def attention_bwd(qkv: Tensor, out: Tensor, dout: Tensor, lse: Tensor, dqkv: Optional[Tensor], workspace: Tensor, B: int, T: int,
+                  n_groups: int, q_per_kv: int, prefix_kv: Optional[Tensor] = None, gate: Optional[Tensor] = None,
+                  d_prefix_kv: Optional[Tensor] = None, d_gate: Optional[Tensor] = None, prefix_len: int = 0,
+                  need_dqkv: bool = True, rope_cos: Optional[Tensor] = None, rope_sin: Optional[Tensor] = None) -> None:
+    _dev(qkv)
+    assert qkv.is_contiguous() and out.is_contiguous() and dout.is_contiguous() and dout.dtype == torch.bfloat16
+    if d_prefix_kv is not None:
+        assert d_prefix_kv.dtype == torch.float32 and d_prefix_kv.is_contiguous() and d_gate.dtype == torch.float32
+    check(_lib.load().dh_attention_bwd(qkv.data_ptr(), out.data_ptr(), dout.data_ptr(), lse.data_ptr(), _ptr(prefix_kv), _ptr(gate),
+                                       _ptr(dqkv), _ptr(d_prefix_kv), _ptr(d_gate), int(need_dqkv), _ptr(rope_cos), _ptr(rope_sin),
+                                       B, T, n_groups, q_per_kv, prefix_len, workspace.data_ptr(),
+                                       workspace.numel() * workspace.element_size(), _stream()), "dh_attention_bwd")
+    _count(3 if need_dqkv else 1)
+
+
+def attention_decode(qkv: Tensor, cache_k: Tensor, cache_v: Tensor, lens: Tensor, out: Tensor, n_groups: int, q_per_kv: int,
+                     prefix_kv: Optional[Tensor] = None, gate: Optional[Tensor] = None, prefix_len: int = 0) -> None:
+    _dev(qkv)
+    nseq, max_len = cache_k.shape[0], cache_k.shape[2]
+    assert cache_k.is_contiguous() and cache_v.is_contiguous() and lens.dtype == torch.int32 and qkv.is_contiguous()
+    check(_lib.load().dh_attention_decode(qkv.data_ptr(), cache_k.data_ptr(), cache_v.data_ptr(), lens.data_ptr(), out.data_ptr(),
+                                          _ptr(prefix_kv), _ptr(gate), nseq, max_len, n_groups, q_per_kv, prefix_len, _stream()),
+          "dh_attention_decode")
+    _count()
+
+
+def kv_cache_write(qkv: Tensor, cache_k: Tensor, cache_v: Tensor, seq: Tensor, pos: Tensor, n_groups: int, q_per_kv: int) -> None:
+    _dev(qkv)
+    assert seq.dtype == torch.int32 and pos.dtype == torch.int32 and qkv.is_contiguous()
+    check(_lib.load().dh_kv_cache_write(qkv.data_ptr(), cache_k.data_ptr(), cache_v.data_ptr(), seq.data_ptr(), pos.data_ptr(),
+                                        qkv.shape[0], cache_k.shape[2], n_groups, q_per_kv, _stream()), "dh_kv_cache_write")
+    _count()
+
+
+def cross_entropy(logits: Tensor, targets: Tensor, row_loss: Tensor, grad_scale: float, write_grad: bool) -> None:
+    _dev(logits)
+    assert logits.dtype == torch.bfloat16 and targets.dtype == torch.int64 and targets.is_contiguous()
+    M, V = logits.shape
+    check(_lib.load().dh_cross_entropy(logits.data_ptr(), _rowmajor(logits, "logits"), targets.data_ptr(), row_loss.data_ptr(), M, V,
+                                       grad_scale, int(write_grad), _stream()), "dh_cross_entropy")
+    _count()
+
+
+def loss_reduce(row_loss: Tensor, targets: Tensor, out2: Tensor) -> None:
+    _dev(row_loss)
+    check(_lib.load().dh_loss_reduce(row_loss.data_ptr(), targets.data_ptr(), out2.data_ptr(), row_loss.numel(), _stream()),
+          "dh_loss_reduce")
+    _count()
+
+
+def argmax(logits: Tensor, ids: Tensor) -> None:
+    _dev(logits)
+    M, V = logits.shape
+    assert logits.dtype == torch.bfloat16 and ids.dtype == torch.int64
+    check(_lib.load().dh_argmax(logits.data_ptr(), _rowmajor(logits, "logits"), ids.data_ptr(), M, V, _stream()), "dh_argmax")
+    _count()
+
+
+def cast_f32_to_bf16(src: Tensor, dst: Tensor) -> None:
+    _dev(src)
+    assert src.dtype == torch.float32 and dst.dtype == torch.bfloat16 and src.shape == dst.shape
+    check(_lib.load().dh_cast_f32_to_bf16(src.data_ptr(), _rowmajor(src, "src"), dst.data_ptr(), _rowmajor(dst, "dst"), src.shape[0],
+                                          src.shape[1], _stream()), "dh_cast_f32_to_bf16")
+    _count()
+
+
+def adamw_step(param: Tensor, grad: Tensor, exp_avg: Tensor, exp_avg_sq: Tensor, lr: float, beta1: float, beta2: float, eps: float,
+               weight_decay: float, step: int, grad_scale: float = 1.0) -> None:
+    _dev(param)
+    for t in (param, grad, exp_avg, exp_avg_sq):
+        assert t.dtype == torch.float32 and t.is_contiguous()
+    check(_lib.load().dh_adamw_step(param.data_ptr(), grad.data_ptr(), exp_avg.data_ptr(), exp_avg_sq.data_ptr(), param.numel(), lr,
+                                    beta1, beta2, eps, weight_decay, step, grad_scale, _stream()), "dh_adamw_step")
+    _count()
+
+
+def relpred_fwd(x: Tensor, w1, b1, w2, b2, wc, bc, h1: Tensor, h2: Tensor, pooled: Tensor, logits: Tensor, pool: int) -> None:
+    _dev(x)
+    B, T, Cd = x.shape
+    for t in (x, w1, b1, w2, b2, wc, bc, h1, h2, pooled, logits):
+        assert t.dtype == torch.float32 and t.is_contiguous()
+    check(_lib.load().dh_relpred_fwd(x.data_ptr(), w1.data_ptr(), b1.data_ptr(), w2.data_ptr(), b2.data_ptr(), wc.data_ptr(),
+                                     bc.data_ptr(), h1.data_ptr(), h2.data_ptr(), pooled.data_ptr(), logits.data_ptr(), B, T, Cd,
+                                     pool, _stream()), "dh_relpred_fwd")
+    _count(4)
+
+
+def relpred_bwd(x, w1, w2, wc, h1, h2, pooled, d_logits, dw1, db1, dw2, db2, dwc, dbc, scratch, pool: int) -> None:
+    _dev(x)
+    B, T, Cd = x.shape
+    for t in (x, w1, w2, wc, h1, h2, pooled, d_logits, dw1, db1, dw2, db2, dwc, dbc, scratch):
+        assert t.dtype == torch.float32 and t.is_contiguous()
+    assert scratch.numel() >= 2 * B * T * 256
+    check(_lib.load().dh_relpred_bwd(x.data_ptr(), w1.data_ptr(), w2.data_ptr(), wc.data_ptr(), h1.data_ptr(), h2.data_ptr(),
+                                     pooled.data_ptr(), d_logits.data_ptr(), dw1.data_ptr(), db1.data_ptr(), dw2.data_ptr(),
+                                     db2.data_ptr(), dwc.data_ptr(), dbc.data_ptr(), scratch.data_ptr(), B, T, Cd, pool, _stream()),
+          "dh_relpred_bwd")
+    _count(7)

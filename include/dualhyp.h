@@ -1,0 +1,176 @@
+/*
+ * dualhyp.h -- C ABI of libdualhyp.so: the B200 (sm_100a) device path of the DualHyp decoder hot path.
+ *
+ * The reference (sungnyun/dualhyp) is pure Python over PyTorch; its hot path has no FFI of its own
+ * (SURVEY.md section 8b).  These entry points are what the reference-side binding -- a ctypes stub inside
+ * the `ger` package, shown in INTEGRATION.md and shipped as dualhyp_b200/_lib.py -- binds in place of the
+ * ATen / cuBLAS / flash-attn calls the reference makes.  Each entry cites the reference site it replaces.
+ *
+ * Conventions: plain pointers and sizes only; every pointer is a DEVICE pointer unless stated; the library
+ * never allocates or frees caller-visible memory and keeps no mutable global state except a per-device
+ * TMA-descriptor cache and the last-error string; all work is enqueued on `stream` (a cudaStream_t) and is
+ * stream-ordered; functions return 0 on success, negative on error (dh_last_error() tells why).
+ * bf16 = 2-byte bfloat16.  Row-major everywhere; `ld*` are leading dimensions in ELEMENTS.
+ */
+#ifndef DUALHYP_H
+#define DUALHYP_H
+
+#include <stddef.h>
+#include <stdint.h>
+
+#ifdef __cplusplus
+extern "C" {
+#endif
+
+#define DH_ABI_VERSION 1
+
+int dh_abi_version(void);
+const char* dh_last_error(void);
+/* Idempotent per-device initialisation (function attributes, SM count). Fails when no sm_100 device. */
+int dh_init(int device);
+int dh_sm_count(void);
+
+/* ---------------------------------------------------------------------------------------------------
+ * GEMM core (tcgen05.mma + TMEM accumulators + TMA operand staging), replaces every nn.Linear on the path:
+ * ger/model.py:213,266,313-316 ; ger/lora.py:162-166,388-402 ; ger/lora.py:70-71 (lm_head).
+ *   D[M,N] = A[M,K1] * op(B) (+ A2[M,K2] * op(B2)),   bf16 operands, fp32 accumulation in TMEM.
+ * a_layout/b_layout 0 = K-major  (A is [M,K] row-major; B is [N,K] row-major, i.e. y = x W^T with W as stored)
+ *                   1 = MN-major (A is [K,M] row-major; B is [K,N] row-major)            -- dgrad / wgrad forms
+ * The second source pair folds a LoRA low-rank delta into the same accumulator (K extension).
+ * Constraints: N % 64 == 0, K1 % 64 == 0, K2 % 64 == 0, 16-byte aligned rows.  M is arbitrary (tail rows are
+ * zero-filled by TMA on load and masked on store).
+ * ------------------------------------------------------------------------------------------------- */
+enum dh_epilogue {
+  DH_EPI_BF16 = 0,        /* out[bf16] = (acc*alpha [+col_bias]) [*col_scale]                                  */
+  DH_EPI_F32 = 1,         /* out[f32]  = acc*alpha (+ out if accumulate)                                       */
+  DH_EPI_RESID_F32 = 2,   /* out[f32]  = aux[f32] + bf16(acc)        residual add, fp32 stream (ger/model.py:185-186) */
+  DH_EPI_RESID_BF16 = 3,  /* out[bf16] = bf16(aux[bf16] + bf16(acc)) residual add, bf16 stream (bf16-true inference)  */
+  DH_EPI_QKV_ROPE = 4,    /* out[bf16] = NeoX RoPE on the q and k head slots of the group-interleaved QKV row,
+                             v copied (ger/model.py:216-246,349-355); positions[row] or row % seq_len           */
+  DH_EPI_SWIGLU = 5,      /* columns are [fc_1 x32 | fc_2 x32] interleaved blocks: out[bf16, ld N] = raw h12 (may be
+                             NULL), out2[bf16, ld N/2] = silu(h1)*h2  (ger/model.py:313-316)                   */
+  DH_EPI_SWIGLU_BWD = 6,  /* acc = d(act) [M, N]; aux = h12 [M, 2N] interleaved; out[bf16, 2N] = d(h12)          */
+  DH_EPI_ROPE_BWD_QKV = 7 /* reserved */
+};
+
+typedef struct dh_gemm_args {
+  const void* A;  int64_t lda;
+  const void* B;  int64_t ldb;
+  const void* A2; int64_t lda2;      /* optional (K2 == 0 -> unused) */
+  const void* B2; int64_t ldb2;
+  int32_t M, N, K1, K2;
+  int32_t a_layout, b_layout, a2_layout, b2_layout;
+  int32_t epilogue;
+  int32_t accumulate;                /* DH_EPI_F32 only */
+  float alpha;
+  int32_t seq_len;                   /* DH_EPI_QKV_ROPE: row -> position = row % seq_len when positions == NULL */
+  int32_t q_per_kv;                  /* DH_EPI_QKV_ROPE: q heads per kv head (group = q_per_kv + 2 slots of 64)   */
+  int32_t reserved0;
+  void* out;  int64_t ldo;
+  void* out2; int64_t ldo2;
+  const void* aux; int64_t ldaux;
+  const float* col_scale;            /* optional [N]  (AdapterV2Linear.adapter_scale, ger/lora.py:70-71) */
+  const float* col_bias;             /* optional [N]  (AdapterV2Linear.adapter_bias) */
+  const void* rope_cos;              /* bf16 [block_size, 64] as built by ger/model.py:319-346 */
+  const void* rope_sin;
+  const int32_t* positions;          /* optional [M] */
+} dh_gemm_args;
+
+int dh_gemm(const dh_gemm_args* args, void* stream);
+
+/* ---------------------------------------------------------------------------------------------------
+ * Bandwidth-bound leaf ops
+ * ------------------------------------------------------------------------------------------------- */
+/* ger/rmsnorm.py:17-21.  x [M,C] (x_dtype 0 = f32, 1 = bf16), weight f32 [C]; y bf16 [M,C]; rstd f32 [M]
+ * (may be NULL).  C % 8 == 0, C <= 8192. */
+int dh_rmsnorm_fwd(const void* x, int x_dtype, const float* weight, void* y, float* rstd, int M, int C, float eps,
+                   void* stream);
+/* Backward of the above w.r.t. x (weights are frozen on this path).  dy bf16 [M,C].
+ * dx_out f32 [M,C] = (dres ? dres : 0) + d(rmsnorm)/dx ; dx_bf16 (optional) = bf16(dx_out).
+ * dres may alias dx_out. */
+int dh_rmsnorm_bwd(const void* x, int x_dtype, const float* weight, const float* rstd, const void* dy,
+                   const float* dres, float* dx_out, void* dx_bf16, int M, int C, void* stream);
+/* nn.Embedding gather (ger/lora.py:537): out (dtype 0 = f32, 1 = bf16) [M,C] = wte[idx[m]] ; wte dtype likewise. */
+int dh_embedding_fwd(const int64_t* idx, const void* wte, int wte_dtype, void* out, int out_dtype, int M, int C,
+                     int vocab_rows, void* stream);
+/* ger/fused_rotary_embedding.py:10-90 (apply_rotary_emb_func): x bf16 (B, T, H, D) contiguous, cos/sin f32 or bf16
+ * [T, rot/2]; rotates the first `rot` dims of every head, NeoX halves (interleaved=0) or GPT-J pairs (1);
+ * conj=1 is the backward rotation.  out may alias x (inplace). */
+int dh_rope_apply(const void* x, void* out, const void* cos, const void* sin, int cs_dtype, int B, int T, int H, int D,
+                  int rot, int interleaved, int conj, void* stream);
+/* In-place NeoX RoPE (conj = backward) on the q and k slots of a group-interleaved [M, n_groups*(qpk+2)*64] bf16
+ * buffer -- the backward of DH_EPI_QKV_ROPE. */
+int dh_rope_qkv_inplace(void* qkv, const void* cos, const void* sin, const int32_t* positions, int M, int seq_len,
+                        int n_groups, int q_per_kv, int conj, void* stream);
+
+/* ---------------------------------------------------------------------------------------------------
+ * Attention (ger/model.py:270-290 causal SDPA with native GQA; ger/adapter.py:116-146 gated prefix)
+ * qkv: bf16 [B*T, n_groups*(qpk+2)*64] group-interleaved, RoPE already applied.  out: bf16 [B*T, n_head*64].
+ * lse: f32 [B, n_head, T] (log-sum-exp of the scaled scores, natural log).  head_size is 64.
+ * Prefix (optional, prefix_kv != NULL): prefix_kv bf16 [aT, n_groups*(qpk+2)*64] (the qkv linear applied to
+ * adapter_wte; only its k and v slots are read, no RoPE), gate f32 [n_head]:
+ *     out = softmax_causal(q k^T / 8) v + gate[h] * softmax(q ak^T / 8) av
+ * ------------------------------------------------------------------------------------------------- */
+int dh_attention_fwd(const void* qkv, void* out, float* lse, const void* prefix_kv, const float* gate, int B, int T,
+                     int n_groups, int q_per_kv, int prefix_len, void* stream);
+/* Backward.  dout bf16 [B*T, n_head*64].  dqkv bf16 (same layout as qkv; every slot is written).
+ * d_prefix_kv f32 [aT, n_groups*(qpk+2)*64] and d_gate f32 [n_head] are ACCUMULATED into (caller zeroes).
+ * need_dqkv = 0 computes only the prefix/gate gradients (first adapter layer). workspace: dh_attention_bwd_workspace.
+ * rope_cos/rope_sin (bf16 [block_size, 64], or both NULL): when given, the conjugate RoPE rotation -- the backward of
+ * DH_EPI_QKV_ROPE -- is fused into the dq and dk stores, so dqkv is the gradient w.r.t. the PRE-rotation QKV row
+ * (position of row m is m % T). */
+size_t dh_attention_bwd_workspace(int B, int T, int n_groups, int q_per_kv);
+int dh_attention_bwd(const void* qkv, const void* out, const void* dout, const float* lse, const void* prefix_kv,
+                     const float* gate, void* dqkv, float* d_prefix_kv, float* d_gate, int need_dqkv,
+                     const void* rope_cos, const void* rope_sin, int B, int T, int n_groups, int q_per_kv, int prefix_len,
+                     void* workspace, size_t workspace_bytes, void* stream);
+/* Single-query attention over a KV cache (ger/model.py:248-261 decode step).  q bf16 [nseq, n_head*64] taken from
+ * the q slots of qkv rows; cache_k/v bf16 [nseq, n_groups, max_len, 64]; lens int32 [nseq] = number of valid keys
+ * INCLUDING the token being decoded.  out bf16 [nseq, n_head*64]. */
+int dh_attention_decode(const void* qkv, const void* cache_k, const void* cache_v, const int32_t* lens, void* out,
+                        const void* prefix_kv, const float* gate, int nseq, int max_len, int n_groups, int q_per_kv,
+                        int prefix_len, void* stream);
+/* Scatter the k and v slots of qkv rows into the cache at (seq[m], pos[m]). */
+int dh_kv_cache_write(const void* qkv, void* cache_k, void* cache_v, const int32_t* seq, const int32_t* pos, int M,
+                      int max_len, int n_groups, int q_per_kv, void* stream);
+
+/* ---------------------------------------------------------------------------------------------------
+ * Loss (ger/utils.py:424-463 over lm_head logits, ger/lora.py:546-549)
+ * logits bf16 [M, V] (ld = ldl).  targets int64 [M], -1 = ignore.  Writes per-row loss f32 [M] (0 where ignored)
+ * and, when write_grad, overwrites logits IN PLACE with d(loss)/d(logits) * grad_scale
+ *   = (softmax - onehot) * grad_scale   for valid rows, 0 for ignored rows.
+ * The caller owns the reduction: train = sum(row_loss)/M (quirk Q2), val = sum/valid.
+ * ------------------------------------------------------------------------------------------------- */
+int dh_cross_entropy(void* logits, int64_t ldl, const int64_t* targets, float* row_loss, int M, int V,
+                     float grad_scale, int write_grad, void* stream);
+/* out[0] = sum(row_loss[0..M)), out[1] = number of targets != -1 */
+int dh_loss_reduce(const float* row_loss, const int64_t* targets, float* out2, int M, void* stream);
+/* argmax over bf16 logits rows (generate/base.py:62-70 with top_k=1): ids int64 [M]; ties -> lowest index */
+int dh_argmax(const void* logits, int64_t ldl, int64_t* ids, int M, int V, void* stream);
+
+/* ---------------------------------------------------------------------------------------------------
+ * RelPrompt reliability predictor (ger/relprompt.py:126-147): Conv1d(k3,p1)+ReLU -> Conv1d(k3,p1)+ReLU ->
+ * AvgPool1d(pool, ceil_mode) -> Linear(256->3).  x f32 [B, T, C]; conv weights f32 in PyTorch layout
+ * [256, Cin, 3]; logits f32 [B, ceil(T/pool), 3].  h1/h2 f32 [B, T, 256] are scratch that the backward reads.
+ * ------------------------------------------------------------------------------------------------- */
+int dh_relpred_fwd(const float* x, const float* w1, const float* b1, const float* w2, const float* b2,
+                   const float* wc, const float* bc, float* h1, float* h2, float* pooled, float* logits, int B, int T,
+                   int C, int pool, void* stream);
+/* d_logits f32 [B, n_out, 3] -> gradients of all six parameter tensors (ACCUMULATED; caller zeroes). */
+int dh_relpred_bwd(const float* x, const float* w1, const float* w2, const float* wc, const float* h1, const float* h2,
+                   const float* pooled, const float* d_logits, float* dw1, float* db1, float* dw2, float* db2,
+                   float* dwc, float* dbc, float* scratch, int B, int T, int C, int pool, void* stream);
+
+/* ---------------------------------------------------------------------------------------------------
+ * Small utilities
+ * ------------------------------------------------------------------------------------------------- */
+/* dst bf16 [rows, cols] = src f32 [rows, cols] (ld in elements) */
+int dh_cast_f32_to_bf16(const float* src, int64_t lds, void* dst, int64_t ldd, int64_t rows, int64_t cols, void* stream);
+/* fused AdamW over one flat fp32 bucket (torch.optim.AdamW semantics, finetune/ger.py:132) */
+int dh_adamw_step(float* param, const float* grad, float* exp_avg, float* exp_avg_sq, int64_t n, float lr, float beta1,
+                  float beta2, float eps, float weight_decay, int step, float grad_scale, void* stream);
+
+#ifdef __cplusplus
+}
+#endif
+#endif /* DUALHYP_H */

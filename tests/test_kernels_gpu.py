@@ -1,0 +1,368 @@
+"""GPU parity tests of the individual sm_100a kernels, called through the C ABI (dualhyp_b200.ops ->
+ctypes -> libdualhyp.so).  The checker is fp32 torch arithmetic on the same bf16-rounded inputs (the same
+formulas `oracle/oracle.py` restates); tolerances are stated per test and are bf16-output tolerances:
+one bf16 ulp is 2^-8 relative, so `rel_err` (Frobenius) < 1e-2 means "within a few bf16 ulps"."""
+import math
+
+import pytest
+import torch
+import torch.nn.functional as F
+
+from dualhyp_b200 import ops, synthetic
+from oracle import oracle as O
+
+pytestmark = pytest.mark.gpu
+DEV = "cuda"
+
+
+def rnd(shape, stream, bound=1.0, dtype=torch.bfloat16, seed=11):
+    return synthetic.hash_uniform(shape, seed, stream, bound, device=DEV).to(dtype)
+
+
+def rel(a, b):
+    a, b = a.double().flatten(), b.double().flatten()
+    return float((a - b).norm() / b.norm().clamp_min(1e-30))
+
+
+def report(name, got, ref):
+    got, ref = got.float(), ref.float()
+    err = (got - ref).abs()
+    i = int(err.argmax())
+    return (f"{name}: rel {rel(got, ref):.3e} max_abs {float(err.max()):.3e} at flat {i} "
+            f"got {float(got.flatten()[i]):.5f} ref {float(ref.flatten()[i]):.5f} "
+            f"nan {int(torch.isnan(got).sum())}")
+
+
+# ----------------------------------------------------------------------------------------------
+# GEMM
+# ----------------------------------------------------------------------------------------------
+@pytest.mark.parametrize("M,N,K", [(128, 64, 64), (128, 128, 64), (256, 256, 128), (1000, 512, 256), (77, 320, 192),
+                                   (4096, 2560, 2048)])
+def test_gemm_kmajor(M, N, K):
+    A, B = rnd((M, K), 1), rnd((N, K), 2)
+    out = torch.full((M, N), float("nan"), device=DEV, dtype=torch.bfloat16)
+    ops.gemm(A, B, out)
+    torch.cuda.synchronize()
+    ref = A.float() @ B.float().t()
+    assert rel(out, ref) < 4e-3, report("gemm", out, ref)
+
+
+@pytest.mark.parametrize("M,N,K", [(128, 64, 64), (256, 256, 128), (300, 512, 320), (2048, 2048, 2560)])
+def test_gemm_b_mn_major(M, N, K):
+    """dgrad form: D = A @ B with B stored [K, N] (the forward weight as stored)."""
+    A, B = rnd((M, K), 3), rnd((K, N), 4)
+    out = torch.full((M, N), float("nan"), device=DEV, dtype=torch.bfloat16)
+    ops.gemm(A, B, out, b_layout=1)
+    torch.cuda.synchronize()
+    ref = A.float() @ B.float()
+    assert rel(out, ref) < 4e-3, report("gemm b_mn", out, ref)
+
+
+@pytest.mark.parametrize("M,N,K", [(128, 64, 64), (64, 256, 1024), (24, 2048, 4096)])
+def test_gemm_wgrad_form(M, N, K):
+    """wgrad form: D[M,N] = A^T B with A stored [K, M], B stored [K, N]; fp32 output, accumulate."""
+    A, B = rnd((K, M), 5), rnd((K, N), 6)
+    out = torch.ones((M, N), device=DEV, dtype=torch.float32)
+    ops.gemm(A, B, out, a_layout=1, b_layout=1, epilogue=ops.EPI_F32, alpha=0.5, accumulate=True)
+    torch.cuda.synchronize()
+    ref = 1.0 + 0.5 * (A.float().t() @ B.float())
+    assert rel(out, ref) < 1e-4, report("gemm wgrad", out, ref)
+
+
+def test_gemm_dual_source_lora():
+    """pretrained + LoRA delta folded in as a K extension (ger/lora.py:388-402)."""
+    M, N, K, K2 = 512, 640, 256, 64
+    A, B, A2, B2 = rnd((M, K), 7), rnd((N, K), 8), rnd((M, K2), 9), rnd((N, K2), 10)
+    out = torch.empty((M, N), device=DEV, dtype=torch.bfloat16)
+    ops.gemm(A, B, out, A2=A2, B2=B2)
+    torch.cuda.synchronize()
+    ref = A.float() @ B.float().t() + A2.float() @ B2.float().t()
+    assert rel(out, ref) < 4e-3, report("gemm dual", out, ref)
+
+
+def test_gemm_residual_and_colscale():
+    M, N, K = 384, 256, 128
+    A, B = rnd((M, K), 11), rnd((N, K), 12)
+    res = rnd((M, N), 13, dtype=torch.float32)
+    out = torch.empty((M, N), device=DEV, dtype=torch.float32)
+    ops.gemm(A, B, out, epilogue=ops.EPI_RESID_F32, aux=res)
+    torch.cuda.synchronize()
+    ref = res + (A.float() @ B.float().t()).bfloat16().float()
+    assert rel(out, ref) < 1e-3, report("resid", out, ref)
+    scale, bias = rnd((N,), 14, dtype=torch.float32) + 1.5, rnd((N,), 15, dtype=torch.float32)
+    o2 = torch.empty((M, N), device=DEV, dtype=torch.bfloat16)
+    ops.gemm(A, B, o2, col_scale=scale, col_bias=bias)
+    torch.cuda.synchronize()
+    ref2 = scale * ((A.float() @ B.float().t()) + bias)
+    assert rel(o2, ref2) < 6e-3, report("adapter_v2 head", o2, ref2)
+
+
+def test_gemm_qkv_rope_epilogue():
+    """QKV linear + RoPE on the group-interleaved row (ger/model.py:213-246) against the oracle's split + apply_rope."""
+    B_, T, G, qpk, C = 2, 96, 2, 2, 256
+    cfg = O.OracleConfig(n_head=G * qpk, n_query_groups=G, n_embd=C, block_size=128)
+    x, W = rnd((B_ * T, C), 16), rnd((cfg.qkv_out, C), 17, bound=1 / 16)
+    cos, sin = O.build_rope_cache(128, 64)
+    out = torch.empty((B_ * T, cfg.qkv_out), device=DEV, dtype=torch.bfloat16)
+    ops.gemm(x, W, out, epilogue=ops.EPI_QKV_ROPE, rope_cos=cos.to(DEV), rope_sin=sin.to(DEV), seq_len=T, q_per_kv=qpk)
+    torch.cuda.synchronize()
+    qkv = (x.float() @ W.float().t()).cpu().view(B_, T, -1)
+    q, k, v = O.split_qkv(qkv, cfg)
+    q, k = O.apply_rope(q, cos[:T], sin[:T]), O.apply_rope(k, cos[:T], sin[:T])
+    got = out.float().cpu().view(B_, T, G, qpk + 2, 64)
+    gq = got[:, :, :, :qpk].permute(0, 2, 3, 1, 4).reshape(B_, G * qpk, T, 64)
+    gk = got[:, :, :, qpk].permute(0, 2, 1, 3)
+    gv = got[:, :, :, qpk + 1].permute(0, 2, 1, 3)
+    assert rel(gq, q) < 6e-3, report("rope q", gq, q)
+    assert rel(gk, k[:, ::qpk]) < 6e-3, report("rope k", gk, k[:, ::qpk])
+    assert rel(gv, v[:, ::qpk]) < 6e-3, report("v", gv, v[:, ::qpk])
+
+
+def _interleave(w1, w2):
+    I = w1.shape[0]
+    return torch.stack((w1.view(I // 32, 32, -1), w2.view(I // 32, 32, -1)), dim=1).reshape(2 * I, -1)
+
+
+def test_gemm_swiglu_fwd_bwd():
+    M, C, I = 256, 128, 256
+    x, W1, W2 = rnd((M, C), 18), rnd((I, C), 19, bound=0.2), rnd((I, C), 20, bound=0.2)
+    W12 = _interleave(W1, W2).contiguous()
+    h12 = torch.empty((M, 2 * I), device=DEV, dtype=torch.bfloat16)
+    act = torch.empty((M, I), device=DEV, dtype=torch.bfloat16)
+    ops.gemm(x, W12, h12, epilogue=ops.EPI_SWIGLU, out2=act)
+    torch.cuda.synchronize()
+    h1, h2 = x.float() @ W1.float().t(), x.float() @ W2.float().t()
+    ref = F.silu(h1) * h2
+    assert rel(act, ref) < 8e-3, report("swiglu act", act, ref)
+    h12v = h12.float().view(M, I // 32, 2, 32)
+    assert rel(h12v[:, :, 0].reshape(M, I), h1) < 4e-3 and rel(h12v[:, :, 1].reshape(M, I), h2) < 4e-3
+    # backward epilogue: d(act) = dy @ Wp with Wp [Cout, I] stored as the forward weight (MN-major B)
+    Cout = 128
+    dy, Wp = rnd((M, Cout), 21), rnd((Cout, I), 22, bound=0.2)
+    dh12 = torch.empty((M, 2 * I), device=DEV, dtype=torch.bfloat16)
+    ops.gemm(dy, Wp, dh12, b_layout=1, epilogue=ops.EPI_SWIGLU_BWD, aux=h12)
+    torch.cuda.synchronize()
+    h1b, h2b = h12v[:, :, 0].reshape(M, I), h12v[:, :, 1].reshape(M, I)
+    dact = (dy.float() @ Wp.float()).bfloat16().float()
+    sig = torch.sigmoid(h1b)
+    rdh1 = dact * h2b * (sig * (1 + h1b * (1 - sig)))
+    rdh2 = dact * (h1b * sig)
+    g = dh12.float().view(M, I // 32, 2, 32)
+    assert rel(g[:, :, 0].reshape(M, I), rdh1) < 8e-3, report("dh1", g[:, :, 0].reshape(M, I), rdh1)
+    assert rel(g[:, :, 1].reshape(M, I), rdh2) < 8e-3, report("dh2", g[:, :, 1].reshape(M, I), rdh2)
+
+
+# ----------------------------------------------------------------------------------------------
+# leaf ops
+# ----------------------------------------------------------------------------------------------
+def test_rmsnorm_fwd_bwd():
+    M, C = 300, 2048
+    x = rnd((M, C), 30, 2.0, torch.float32)
+    w = rnd((C,), 31, 0.5, torch.float32) + 1.0
+    y = torch.empty((M, C), device=DEV, dtype=torch.bfloat16)
+    rstd = torch.empty(M, device=DEV)
+    ops.rmsnorm_fwd(x, w, y, rstd, 1e-5)
+    ref = O.rmsnorm(x, w, 1e-5)
+    assert rel(y, ref) < 4e-3, report("rmsnorm", y, ref)
+    dy = rnd((M, C), 32)
+    dres = rnd((M, C), 33, dtype=torch.float32)
+    xr = x.clone().requires_grad_(True)
+    O.rmsnorm(xr, w, 1e-5).backward(dy.float())
+    dx = torch.empty_like(x)
+    dxb = torch.empty((M, C), device=DEV, dtype=torch.bfloat16)
+    ops.rmsnorm_bwd(x, w, rstd, dy, dres, dx, dxb)
+    torch.cuda.synchronize()
+    assert rel(dx, dres + xr.grad) < 1e-5, report("rmsnorm bwd", dx, dres + xr.grad)
+    assert rel(dxb, dres + xr.grad) < 4e-3
+
+
+def test_embedding_and_rope_apply():
+    V, C = 1000, 256
+    wte = rnd((V, C), 34, dtype=torch.float32)
+    idx = synthetic.hash_ints((4, 50), 3, 35, 0, V).to(DEV)
+    out = torch.empty((200, C), device=DEV)
+    ops.embedding_fwd(idx, wte, out)
+    assert torch.equal(out, wte[idx.flatten()])
+    # apply_rotary_emb_func semantics (ger/fused_rotary_embedding.py): (B,T,H,D), cos/sin (T, rot/2)
+    B_, T, H, D, rot = 2, 40, 3, 64, 32
+    x = rnd((B_, T, H, D), 36)
+    ang = torch.outer(torch.arange(T, dtype=torch.float32), 1.0 / (10000 ** (torch.arange(0, rot, 2).float() / rot))).to(DEV)
+    cos, sin = ang.cos(), ang.sin()
+    o = torch.empty_like(x)
+    ops.rope_apply(x, cos, sin, o)
+    xf = x.float()
+    x1, x2 = xf[..., : rot // 2], xf[..., rot // 2: rot]
+    c, s = cos[None, :, None, :], sin[None, :, None, :]
+    ref = torch.cat((x1 * c - x2 * s, x1 * s + x2 * c, xf[..., rot:]), dim=-1)
+    assert rel(o, ref) < 4e-3, report("rope_apply", o, ref)
+    back = torch.empty_like(x)
+    ops.rope_apply(o, cos, sin, back, conj=True)          # backward rotation undoes the forward one
+    assert rel(back[..., :rot], x[..., :rot]) < 1e-2
+
+
+def test_cross_entropy_and_argmax():
+    M, V = 257, 32000
+    logits = rnd((M, V), 40, 6.0)
+    tg = synthetic.hash_ints((M,), 5, 41, -1, V).to(DEV)
+    tg[::7] = -1
+    ref_rows = F.cross_entropy(logits.float(), tg, ignore_index=-1, reduction="none")
+    lf = logits.float().requires_grad_(True)
+    (F.cross_entropy(lf, tg, ignore_index=-1, reduction="none").sum() * 0.37).backward()
+    ids = torch.empty(M, dtype=torch.int64, device=DEV)
+    ops.argmax(logits, ids)
+    assert torch.equal(ids, logits.float().argmax(dim=-1))
+    row = torch.empty(M, device=DEV)
+    ops.cross_entropy(logits, tg, row, 0.37, True)
+    out2 = torch.empty(2, device=DEV)
+    ops.loss_reduce(row, tg, out2)
+    torch.cuda.synchronize()
+    assert rel(row, ref_rows) < 1e-5, report("ce rows", row, ref_rows)
+    assert abs(float(out2[0]) - float(ref_rows.sum())) < 1e-2 and int(out2[1]) == int((tg >= 0).sum())
+    assert rel(logits, lf.grad) < 8e-3, report("ce grad", logits, lf.grad)
+    assert float(logits[::7].abs().max()) == 0.0
+
+
+def test_adamw_matches_torch():
+    n = 10000
+    p0, g = rnd((n,), 50, dtype=torch.float32), rnd((n,), 51, dtype=torch.float32)
+    p = p0.clone()
+    m, v = torch.zeros_like(p), torch.zeros_like(p)
+    tp = torch.nn.Parameter(p0.clone())
+    opt = torch.optim.AdamW([tp], lr=1e-3, betas=(0.9, 0.999), eps=1e-8, weight_decay=0.02)
+    for step in range(1, 4):
+        tp.grad = g * step
+        opt.step()
+        ops.adamw_step(p, g * step, m, v, 1e-3, 0.9, 0.999, 1e-8, 0.02, step)
+    torch.cuda.synchronize()
+    assert rel(p, tp.data) < 1e-6, report("adamw", p, tp.data)
+
+
+# ----------------------------------------------------------------------------------------------
+# attention
+# ----------------------------------------------------------------------------------------------
+def _attn_ref(qkv, B_, T, G, qpk, prefix_kv=None, gate=None):
+    """fp32 reference through the oracle's split/sdpa (+ prefix) on an already-roped interleaved row."""
+    cfg = O.OracleConfig(n_head=G * qpk, n_query_groups=G)
+    v5 = qkv.view(B_, T, G, qpk + 2, 64).permute(0, 2, 3, 1, 4)
+    q, k, v = v5.split((qpk, 1, 1), dim=2)
+    k = k.expand(B_, G, qpk, T, 64).reshape(B_, -1, T, 64)
+    v = v.expand(B_, G, qpk, T, 64).reshape(B_, -1, T, 64)
+    q = q.reshape(B_, -1, T, 64)
+    y = O.sdpa(q, k, v, None, 0.125)
+    if prefix_kv is not None:
+        aT = prefix_kv.shape[0]
+        a5 = prefix_kv.view(1, aT, G, qpk + 2, 64).permute(0, 2, 3, 1, 4)
+        _, ak, av = a5.split((qpk, 1, 1), dim=2)
+        ak = ak.repeat_interleave(qpk, dim=2).reshape(1, -1, aT, 64)
+        av = av.repeat_interleave(qpk, dim=2).reshape(1, -1, aT, 64)
+        ay = O.sdpa(q, ak, av, torch.ones(T, aT, dtype=torch.bool), 0.125)
+        y = y + gate.view(1, 1, -1, 1) * ay
+    return y.reshape(B_, T, -1)
+
+
+@pytest.mark.parametrize("B_,T,G,qpk,prefix", [(1, 128, 1, 1, 0), (2, 256, 2, 2, 0), (2, 160, 2, 2, 10), (1, 512, 4, 8, 10),
+                                               (3, 77, 1, 4, 0)])
+def test_attention_fwd(B_, T, G, qpk, prefix):
+    N = G * (qpk + 2) * 64
+    qkv = rnd((B_ * T, N), 60, 2.0)
+    pk = rnd((prefix, N), 61, 2.0) if prefix else None
+    gate = rnd((G * qpk,), 62, 1.0, torch.float32) if prefix else None
+    out = torch.full((B_ * T, G * qpk * 64), float("nan"), device=DEV, dtype=torch.bfloat16)
+    lse = torch.empty((B_, G * qpk, T), device=DEV)
+    ops.attention_fwd(qkv, out, lse, B_, T, G, qpk, pk, gate, prefix)
+    torch.cuda.synchronize()
+    ref = _attn_ref(qkv.float().cpu(), B_, T, G, qpk, None if pk is None else pk.float().cpu(),
+                    None if gate is None else gate.cpu())
+    got = out.float().cpu().view(B_, T, -1)
+    assert rel(got, ref) < 1e-2, report("attn fwd", got, ref)
+
+
+@pytest.mark.parametrize("B_,T,G,qpk,prefix,rope", [(1, 128, 1, 1, 0, False), (2, 256, 2, 2, 0, False), (2, 160, 2, 2, 10, False),
+                                                    (1, 384, 2, 4, 10, True)])
+def test_attention_bwd(B_, T, G, qpk, prefix, rope):
+    N = G * (qpk + 2) * 64
+    H = G * qpk
+    qkv = rnd((B_ * T, N), 63, 2.0)
+    pk = rnd((prefix, N), 64, 2.0) if prefix else None
+    gate = rnd((H,), 65, 1.0, torch.float32) if prefix else None
+    dout = rnd((B_ * T, H * 64), 66, 1.0)
+    out = torch.empty((B_ * T, H * 64), device=DEV, dtype=torch.bfloat16)
+    lse = torch.empty((B_, H, T), device=DEV)
+    ops.attention_fwd(qkv, out, lse, B_, T, G, qpk, pk, gate, prefix)
+    dqkv = torch.full((B_ * T, N), float("nan"), device=DEV, dtype=torch.bfloat16)
+    ws = torch.empty(ops.attention_bwd_workspace(B_, T, G, qpk), dtype=torch.uint8, device=DEV)
+    dpk = torch.zeros((prefix, N), device=DEV) if prefix else None
+    dg = torch.zeros(H, device=DEV) if prefix else None
+    cos, sin = O.build_rope_cache(512, 64)
+    ops.attention_bwd(qkv, out, dout, lse, dqkv, ws, B_, T, G, qpk, pk, gate, dpk, dg, prefix,
+                      rope_cos=cos.to(DEV) if rope else None, rope_sin=sin.to(DEV) if rope else None)
+    torch.cuda.synchronize()
+    # reference by autograd.  With rope=True the kernel returns the gradient w.r.t. the PRE-rotation row, so the
+    # reference treats `qkv` as the rotated value of a leaf `pre` (rotation is orthogonal: pre = R^-1 qkv).
+    x = qkv.float().cpu().requires_grad_(True)
+    pkr = pk.float().cpu().requires_grad_(True) if prefix else None
+    gr = gate.cpu().clone().requires_grad_(True) if prefix else None
+    y = _attn_ref(x, B_, T, G, qpk, pkr, gr)
+    y.backward(dout.float().cpu().view(B_, T, -1))
+    ref = x.grad.view(B_, T, G, qpk + 2, 64).clone()
+    if rope:
+        c, s = cos[:T].float()[None, :, None, None, :], sin[:T].float()[None, :, None, None, :]
+        qk = ref[:, :, :, : qpk + 1]
+        rot = torch.cat((qk[..., 32:], -qk[..., :32]), dim=-1)      # conjugate rotation
+        ref[:, :, :, : qpk + 1] = qk * c + rot * s
+    got = dqkv.float().cpu().view(B_, T, G, qpk + 2, 64)
+    assert rel(got[:, :, :, qpk + 1], ref[:, :, :, qpk + 1]) < 1.5e-2, report("dv", got[:, :, :, qpk + 1], ref[:, :, :, qpk + 1])
+    assert rel(got[:, :, :, qpk], ref[:, :, :, qpk]) < 1.5e-2, report("dk", got[:, :, :, qpk], ref[:, :, :, qpk])
+    assert rel(got[:, :, :, :qpk], ref[:, :, :, :qpk]) < 1.5e-2, report("dq", got[:, :, :, :qpk], ref[:, :, :, :qpk])
+    if prefix:
+        assert rel(dg.cpu(), gr.grad) < 1e-2, report("dgate", dg.cpu(), gr.grad)
+        assert rel(dpk.cpu(), pkr.grad) < 1e-2, report("dprefix", dpk.cpu(), pkr.grad)
+
+
+def test_attention_decode_matches_prefill():
+    B_, T, G, qpk, prefix = 3, 200, 2, 4, 10
+    N, H = G * (qpk + 2) * 64, G * qpk
+    qkv = rnd((B_ * T, N), 67, 2.0)
+    pk, gate = rnd((prefix, N), 68, 2.0), rnd((H,), 69, 1.0, torch.float32)
+    out = torch.empty((B_ * T, H * 64), device=DEV, dtype=torch.bfloat16)
+    lse = torch.empty((B_, H, T), device=DEV)
+    ops.attention_fwd(qkv, out, lse, B_, T, G, qpk, pk, gate, prefix)
+    max_len = 256
+    ck = torch.zeros((B_, G, max_len, 64), device=DEV, dtype=torch.bfloat16)
+    cv = torch.zeros_like(ck)
+    seq = torch.arange(B_, device=DEV, dtype=torch.int32).repeat_interleave(T)
+    pos = torch.arange(T, device=DEV, dtype=torch.int32).repeat(B_)
+    ops.kv_cache_write(qkv, ck, cv, seq, pos, G, qpk)
+    lens = torch.tensor([T, T - 37, 1], device=DEV, dtype=torch.int32)
+    rows = torch.stack([qkv[b * T + int(lens[b]) - 1] for b in range(B_)]).contiguous()
+    dec = torch.empty((B_, H * 64), device=DEV, dtype=torch.bfloat16)
+    ops.attention_decode(rows, ck, cv, lens, dec, G, qpk, pk, gate, prefix)
+    torch.cuda.synchronize()
+    ref = torch.stack([out[b * T + int(lens[b]) - 1] for b in range(B_)])
+    assert rel(dec, ref) < 1e-2, report("decode attn", dec, ref)
+
+
+def test_relpred_fwd_bwd():
+    B_, T, C, pool = 3, 103, 96, 10
+    x = synthetic.synth_features(B_, T, C, 3, 70, DEV)
+    p = "audio_noise_classifier."
+    shapes = {"conv1.weight": (256, C, 3), "conv1.bias": (256,), "conv2.weight": (256, 256, 3), "conv2.bias": (256,),
+              "classifier.weight": (3, 256), "classifier.bias": (3,)}
+    names = list(shapes)
+    sd = {p + n: synthetic.hash_uniform(shapes[n], 5, 80 + i, 0.08, DEV, bf16_exact=False) for i, n in enumerate(names)}
+    n_out = -(-T // pool)
+    h1, h2 = torch.empty((B_, T, 256), device=DEV), torch.empty((B_, T, 256), device=DEV)
+    pooled, logits = torch.empty((B_, n_out, 256), device=DEV), torch.empty((B_, n_out, 3), device=DEV)
+    args = [sd[p + n] for n in names]
+    ops.relpred_fwd(x, *args, h1, h2, pooled, logits, pool)
+    work = {k: v.clone().requires_grad_(True) for k, v in sd.items()}
+    ref = O.noise_mask_classifier(x, work, p, pool)
+    assert rel(logits, ref) < 1e-4, report("relpred fwd", logits, ref)
+    dl = rnd((B_, n_out, 3), 71, dtype=torch.float32)
+    ref.backward(dl)
+    grads = [torch.zeros_like(a) for a in args]
+    scratch = torch.empty(2 * B_ * T * 256, device=DEV)
+    ops.relpred_bwd(x, args[0], args[2], args[4], h1, h2, pooled, dl, *grads, scratch, pool)
+    torch.cuda.synchronize()
+    for n, g in zip(names, grads):
+        assert rel(g, work[p + n].grad) < 1e-4, report("relpred " + n, g, work[p + n].grad)
