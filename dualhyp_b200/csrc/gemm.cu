@@ -186,8 +186,8 @@ gemm_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant__ CUt
   const int warp = threadIdx.x >> 5;
   const int lane = threadIdx.x & 31;
   const int num_tiles = p.tiles_m * p.tiles_n;
-  const int nkb1 = p.K1 / BK;
-  const int nkb = nkb1 + p.K2 / BK;
+  const int nkb1 = (p.K1 + BK - 1) / BK;   // a ragged K tail is zero-filled by TMA
+  const int nkb = nkb1 + (p.K2 + BK - 1) / BK;
 
   if (warp == 0 && lane == 0) {
     tma_prefetch_desc(&tmA);
@@ -378,9 +378,9 @@ extern "C" int dh_gemm(const dh_gemm_args* a, void* stream_) {
   cudaStream_t stream = reinterpret_cast<cudaStream_t>(stream_);
   DH_CHECK(a != nullptr, "dh_gemm: null args");
   DH_CHECK(a->M > 0 && a->N > 0 && a->K1 > 0, "dh_gemm: bad shape M=%d N=%d K1=%d", a->M, a->N, a->K1);
-  DH_CHECK(a->N % 64 == 0 && a->K1 % 64 == 0 && a->K2 % 64 == 0, "dh_gemm: N, K1, K2 must be multiples of 64 (N=%d K1=%d K2=%d)",
+  DH_CHECK(a->N % 64 == 0 && a->K1 % 8 == 0 && a->K2 % 8 == 0, "dh_gemm: N %% 64, K1 %% 8, K2 %% 8 must be 0 (N=%d K1=%d K2=%d)",
            a->N, a->K1, a->K2);
-  DH_CHECK(a->A && a->B && a->out || a->epilogue == DH_EPI_SWIGLU, "dh_gemm: null operand");
+  DH_CHECK(a->A && a->B && (a->out || a->epilogue == DH_EPI_SWIGLU), "dh_gemm: null operand");
   DH_CHECK((a->lda % 8) == 0 && (a->ldb % 8) == 0, "dh_gemm: leading dimensions must be multiples of 8 elements");
   DH_CHECK(((uintptr_t)a->A & 15) == 0 && ((uintptr_t)a->B & 15) == 0, "dh_gemm: operands must be 16-byte aligned");
   if (a->K2 > 0) DH_CHECK(a->A2 && a->B2 && (a->lda2 % 8) == 0 && (a->ldb2 % 8) == 0, "dh_gemm: bad second source");

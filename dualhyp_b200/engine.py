@@ -1,0 +1,444 @@
+"""DecoderEngine: the B200 execution of the lit-gpt-style decoder the DualHyp modules run
+(reference ger/model.py:65-114,163-268,312-316; ger/lora.py:504-549; ger/adapter.py:116-146).
+
+The engine owns bf16 copies of the frozen weights in the layouts the kernels want, the RoPE tables, the
+activation buffers that the backward reads, and the KV caches; it sequences hand-written sm_100a kernels
+through the C ABI (dualhyp_b200.ops).  PyTorch supplies device memory and the stream, nothing else.
+
+Per layer, forward (M = B*T token rows):
+    rmsnorm -> [LoRA a = n A^T] -> QKV GEMM (+LoRA K-extension, RoPE epilogue, interleaved row kept as is)
+    -> [prefix K/V GEMM] -> flash attention (+gated prefix) -> proj GEMM (+LoRA, residual epilogue, fp32 stream)
+    -> rmsnorm -> fc_1|fc_2 GEMM (SwiGLU epilogue) -> proj GEMM (residual epilogue)
+Backward is dgrad only for the frozen weights (the forward weight, as stored, is the MN-major B operand:
+no transposed copies), plus the small LoRA / adapter wgrads.
+"""
+from __future__ import annotations
+
+import math
+from dataclasses import dataclass
+from typing import Dict, List, Optional
+
+import torch
+
+from . import ops
+
+Tensor = torch.Tensor
+LORA_PAD = 64          # LoRA rank (x3 for QKV) padded to one 64-wide K block
+
+
+@dataclass
+class EngineSpec:
+    n_layer: int
+    n_head: int
+    n_query_groups: int
+    n_embd: int
+    intermediate_size: int
+    vocab: int
+    block_size: int
+    norm_eps: float
+    variant: str = "base"              # base | lora | adapter
+    r: int = 0
+    alpha: float = 1.0
+    lora_qkv: bool = False
+    lora_proj: bool = False
+    lora_start_layer: int = 0
+    adapter_prompt_length: int = 0
+    adapter_start_layer: int = 0
+
+    @property
+    def qpk(self) -> int:
+        return self.n_head // self.n_query_groups
+
+    @property
+    def qkv_out(self) -> int:
+        return (self.n_head + 2 * self.n_query_groups) * 64
+
+    @property
+    def kv_embd(self) -> int:
+        return self.n_embd // self.qpk
+
+    def has_lora(self, layer: int) -> bool:
+        return self.variant == "lora" and self.r > 0 and layer >= self.lora_start_layer and (self.lora_qkv or self.lora_proj)
+
+    def has_adapter(self, layer: int) -> bool:
+        return self.variant == "adapter" and layer >= self.adapter_start_layer
+
+    @property
+    def first_trainable_layer(self) -> int:
+        if self.variant == "adapter":
+            return self.adapter_start_layer
+        if self.variant == "lora" and self.r > 0 and (self.lora_qkv or self.lora_proj):
+            return self.lora_start_layer
+        return self.n_layer
+
+
+def build_rope_tables(block_size: int, device) -> tuple:
+    """ger/model.py:319-346 with the call site's dtype=bfloat16 (:120-126): fp32 math, tables rounded to bf16,
+    halves repeated (`repeat(1, 2)`).  Built on the host so they are bit-identical to the CPU oracle's."""
+    theta = 1.0 / (10000 ** (torch.arange(0, 64, 2) / 64))
+    idx_theta = torch.outer(torch.arange(block_size) / 1, theta).repeat(1, 2)
+    return torch.cos(idx_theta).bfloat16().to(device).contiguous(), torch.sin(idx_theta).bfloat16().to(device).contiguous()
+
+
+def interleave_fc(w1: Tensor, w2: Tensor) -> Tensor:
+    """[fc_1 rows 0..31 | fc_2 rows 0..31 | fc_1 rows 32..63 | ...]: the SwiGLU epilogue needs both halves of a
+    column pair inside one 64-wide accumulator chunk."""
+    inter = w1.shape[0]
+    return torch.stack((w1.view(inter // 32, 32, -1), w2.view(inter // 32, 32, -1)), dim=1).reshape(2 * inter, -1).contiguous()
+
+
+class DecoderEngine:
+    def __init__(self, spec: EngineSpec, device: torch.device):
+        assert spec.n_embd % 256 == 0 and spec.intermediate_size % 64 == 0 and spec.vocab % 64 == 0
+        assert spec.adapter_prompt_length <= 16
+        if spec.variant == "lora" and spec.r > 0:
+            assert 3 * spec.r <= LORA_PAD, "LoRA rank too large for the single-block K extension (3r <= 64)"
+        self.spec = spec
+        self.device = device
+        self.cos, self.sin = build_rope_tables(spec.block_size, device)
+        self.layers: List[Dict[str, Tensor]] = []
+        self.wte: Optional[Tensor] = None
+        self.ln_f: Optional[Tensor] = None
+        self.lm_w: Optional[Tensor] = None
+        self.lm_scale: Optional[Tensor] = None
+        self.lm_bias: Optional[Tensor] = None
+        self._bufs: Dict = {}
+        self._saved: Optional[Dict] = None
+        self.step_id = 0
+        # KV cache
+        self.cache_k: List[Tensor] = []
+        self.cache_v: List[Tensor] = []
+        self.cache_max_len = 0
+
+    # ------------------------------------------------------------------------------------------
+    # weights
+    # ------------------------------------------------------------------------------------------
+    def load_frozen(self, sd: Dict[str, Tensor]) -> None:
+        """Pack the frozen decoder weights from a (reference-keyed) state dict: bf16, fc_1/fc_2 interleaved."""
+        s, dev = self.spec, self.device
+        lk = ".linear.weight" if any(k.endswith("attn.attn.linear.weight") for k in sd) else ".weight"
+
+        def bf(k):
+            return sd[k].detach().to(dev, torch.bfloat16).contiguous()
+
+        def f32(k):
+            return sd[k].detach().to(dev, torch.float32).contiguous()
+
+        self.layers = []
+        for i in range(s.n_layer):
+            p = f"transformer.h.{i}."
+            self.layers.append(dict(
+                norm1=f32(p + "norm_1.weight"), norm2=f32(p + "norm_2.weight"),
+                wqkv=bf(p + "attn.attn" + lk), wproj=bf(p + "attn.proj" + lk),
+                w12=interleave_fc(bf(p + "mlp.fc_1" + lk), bf(p + "mlp.fc_2" + lk)), wmlp=bf(p + "mlp.proj" + lk)))
+        self.wte = sd["transformer.wte.weight"].detach().to(dev).contiguous()
+        if self.wte.dtype not in (torch.float32, torch.bfloat16):
+            self.wte = self.wte.float()
+        self.ln_f = f32("transformer.ln_f.weight")
+        if "lm_head.linear.weight" in sd:
+            self.lm_w = bf("lm_head.linear.weight")
+            scale, bias = f32("lm_head.adapter_scale"), f32("lm_head.adapter_bias")
+            # AdapterV2Linear is frozen at scale=1, bias=0 (ger/lora.py:67-68); skip the epilogue work when trivial
+            self.lm_scale = None if bool((scale == 1).all()) else scale
+            self.lm_bias = None if bool((bias == 0).all()) else bias
+        else:
+            self.lm_w = bf("lm_head.weight")
+            self.lm_scale = self.lm_bias = None
+
+    def pack_trainable(self, tr: Dict[str, Tensor]) -> Dict[int, Dict[str, Tensor]]:
+        """Per-step bf16 forms of the small trainable tensors (reference-keyed, fp32 masters)."""
+        s, dev = self.spec, self.device
+        packed: Dict[int, Dict[str, Tensor]] = {}
+        scaling = (s.alpha / s.r) if s.r > 0 else 0.0
+        for i in range(s.n_layer):
+            p = f"transformer.h.{i}.attn."
+            d: Dict[str, Tensor] = {}
+            if s.has_adapter(i):
+                d["prefix"] = tr[p + "adapter_wte.weight"].detach().to(dev, torch.bfloat16).contiguous()
+                d["gate"] = tr[p + "gating_factor"].detach().to(dev, torch.float32).reshape(-1).contiguous()
+            if s.has_lora(i):
+                C, r = s.n_embd, s.r
+                if s.lora_qkv:
+                    A, Bm = tr[p + "attn.lora_A"].detach().to(dev), tr[p + "attn.lora_B"].detach().to(dev)
+                    a_pad = torch.zeros((LORA_PAD, C), device=dev, dtype=torch.bfloat16)
+                    a_pad[: 3 * r] = (A.float() * scaling).to(torch.bfloat16)
+                    b_ext = torch.zeros((s.qkv_out, LORA_PAD), device=dev, dtype=torch.bfloat16)
+                    kv = s.kv_embd
+                    b_ext[:C, 0:r] = Bm[:C].to(torch.bfloat16)                      # q rows use after_A[:, 0:r]
+                    b_ext[C:C + kv, r:2 * r] = Bm[C:C + kv].to(torch.bfloat16)      # k rows use [:, r:2r]
+                    b_ext[C + kv:, 2 * r:3 * r] = Bm[C + kv:].to(torch.bfloat16)    # v rows use [:, 2r:3r]
+                    d["qkv_a"], d["qkv_b"] = a_pad, b_ext
+                if s.lora_proj:
+                    A, Bm = tr[p + "proj.lora_A"].detach().to(dev), tr[p + "proj.lora_B"].detach().to(dev)
+                    a_pad = torch.zeros((LORA_PAD, C), device=dev, dtype=torch.bfloat16)
+                    a_pad[:r] = (A.float() * scaling).to(torch.bfloat16)
+                    b_ext = torch.zeros((C, LORA_PAD), device=dev, dtype=torch.bfloat16)
+                    b_ext[:, :r] = Bm.to(torch.bfloat16)
+                    d["proj_a"], d["proj_b"] = a_pad, b_ext
+            if d:
+                packed[i] = d
+        return packed
+
+    # ------------------------------------------------------------------------------------------
+    # buffers
+    # ------------------------------------------------------------------------------------------
+    def _buf(self, name: str, shape, dtype) -> Tensor:
+        key = (name, tuple(shape), dtype)
+        t = self._bufs.get(key)
+        if t is None:
+            t = torch.empty(shape, device=self.device, dtype=dtype)
+            self._bufs[key] = t
+        return t
+
+    def release_buffers(self) -> None:
+        self._bufs.clear()
+        self._saved = None
+
+    # ------------------------------------------------------------------------------------------
+    # forward over full sequences (training / evaluation / prefill)
+    # ------------------------------------------------------------------------------------------
+    def forward_hidden(self, idx: Tensor, packed: Dict[int, Dict[str, Tensor]], save: bool, write_cache: bool = False) -> Tensor:
+        """idx int64 [B, T] -> ln_f output bf16 [B*T, C].  save=True keeps what backward() needs."""
+        s = self.spec
+        B, T = idx.shape
+        assert T <= s.block_size, f"Cannot forward sequence of length {T}, block size is only {s.block_size}"
+        M, C, I, G, qpk = B * T, s.n_embd, s.intermediate_size, s.n_query_groups, s.qpk
+        L = s.n_layer
+        bf, f32 = torch.bfloat16, torch.float32
+        idx = idx.contiguous()
+        per = (lambda name, i: f"{name}{i}") if save else (lambda name, i: name)
+        # the residual stream alternates between two buffers unless the backward needs every stage
+        x = self._buf(per("x", 0), (M, C), f32)
+        ops.embedding_fwd(idx.view(-1), self.wte, x)
+        n = self._buf("n", (M, C), bf)
+        act = self._buf("act", (M, I), bf)
+        saved = dict(B=B, T=T, layers=[], packed=packed) if save else None
+        for i, lw in enumerate(self.layers):
+            pk = packed.get(i, {})
+            rstd1 = self._buf(per("rstd1_", i), (M,), f32)
+            n_i = self._buf(per("n1_", i), (M, C), bf) if (save and "qkv_a" in pk) else n
+            ops.rmsnorm_fwd(x, lw["norm1"], n_i, rstd1, s.norm_eps)
+            qkv = self._buf(per("qkv", i), (M, s.qkv_out), bf)
+            a_s = None
+            if "qkv_a" in pk:
+                a_s = self._buf(per("qkv_as", i), (M, LORA_PAD), bf)
+                ops.gemm(n_i, pk["qkv_a"], a_s)
+                ops.gemm(n_i, lw["wqkv"], qkv, A2=a_s, B2=pk["qkv_b"], epilogue=ops.EPI_QKV_ROPE, rope_cos=self.cos, rope_sin=self.sin,
+                         seq_len=T, q_per_kv=qpk)
+            else:
+                ops.gemm(n_i, lw["wqkv"], qkv, epilogue=ops.EPI_QKV_ROPE, rope_cos=self.cos, rope_sin=self.sin, seq_len=T, q_per_kv=qpk)
+            prefix_kv = gate = None
+            if "prefix" in pk:
+                prefix_kv = self._buf(per("pkv", i), (s.adapter_prompt_length, s.qkv_out), bf)
+                ops.gemm(pk["prefix"], lw["wqkv"], prefix_kv)
+                gate = pk["gate"]
+            if write_cache:
+                self._write_prefill_cache(i, qkv, B, T)
+            y = self._buf(per("y", i), (M, C), bf)
+            lse = self._buf(per("lse", i), (B, s.n_head, T), f32)
+            ops.attention_fwd(qkv, y, lse, B, T, G, qpk, prefix_kv, gate, s.adapter_prompt_length if prefix_kv is not None else 0)
+            xmid = self._buf(per("xmid", i), (M, C), f32)
+            ap_s = None
+            if "proj_a" in pk:
+                ap_s = self._buf(per("proj_as", i), (M, LORA_PAD), bf)
+                ops.gemm(y, pk["proj_a"], ap_s)
+                ops.gemm(y, lw["wproj"], xmid, A2=ap_s, B2=pk["proj_b"], epilogue=ops.EPI_RESID_F32, aux=x)
+            else:
+                ops.gemm(y, lw["wproj"], xmid, epilogue=ops.EPI_RESID_F32, aux=x)
+            rstd2 = self._buf(per("rstd2_", i), (M,), f32)
+            ops.rmsnorm_fwd(xmid, lw["norm2"], n, rstd2, s.norm_eps)
+            h12 = self._buf(per("h12_", i), (M, 2 * I), bf) if save else None
+            ops.gemm(n, lw["w12"], h12, epilogue=ops.EPI_SWIGLU, out2=act)
+            x_next = self._buf(per("x", i + 1), (M, C), f32) if save else self._buf("x_alt" if (i % 2 == 0) else "x", (M, C), f32)
+            ops.gemm(act, lw["wmlp"], x_next, epilogue=ops.EPI_RESID_F32, aux=xmid)
+            if save:
+                saved["layers"].append(dict(x=x, xmid=xmid, rstd1=rstd1, rstd2=rstd2, qkv=qkv, y=y, lse=lse, h12=h12, n1=n_i,
+                                            a_s=a_s, ap_s=ap_s, prefix_kv=prefix_kv, gate=gate))
+            x = x_next
+        hidden = self._buf("hidden", (M, C), bf)
+        rstd_f = self._buf("rstd_f", (M,), f32)
+        ops.rmsnorm_fwd(x, self.ln_f, hidden, rstd_f, s.norm_eps)
+        if save:
+            saved["x_final"], saved["rstd_f"] = x, rstd_f
+            self.step_id += 1
+            saved["step_id"] = self.step_id
+            self._saved = saved
+        return hidden
+
+    def lm_head(self, hidden: Tensor, out: Optional[Tensor] = None) -> Tensor:
+        """bf16 logits [M, V] = adapter_scale * (hidden W^T + adapter_bias)  (ger/lora.py:70-71)."""
+        M = hidden.shape[0]
+        logits = out if out is not None else self._buf("logits", (M, self.spec.vocab), torch.bfloat16)
+        ops.gemm(hidden, self.lm_w, logits, col_scale=self.lm_scale, col_bias=self.lm_bias)
+        return logits
+
+    # ------------------------------------------------------------------------------------------
+    # backward: d(hidden) -> gradients of the trainable tensors (reference-keyed, fp32)
+    # ------------------------------------------------------------------------------------------
+    def lm_head_backward(self, dlogits: Tensor) -> Tensor:
+        """d(hidden) bf16 [M, C] = dlogits [M, V] @ W [V, C]   (W as stored is the MN-major B operand)."""
+        M = dlogits.shape[0]
+        d_hidden = self._buf("d_hidden", (M, self.spec.n_embd), torch.bfloat16)
+        if self.lm_scale is not None:
+            raise NotImplementedError("training through a non-trivial adapter_scale is not supported (it is frozen at 1)")
+        ops.gemm(dlogits, self.lm_w, d_hidden, b_layout=1)
+        return d_hidden
+
+    def backward(self, d_hidden: Tensor, step_id: Optional[int] = None) -> Dict[str, Tensor]:
+        s = self.spec
+        sv = self._saved
+        if sv is None:
+            raise RuntimeError("backward() without a saved forward")
+        if step_id is not None and step_id != sv["step_id"]:
+            raise RuntimeError("the engine's saved activations belong to a later forward; call backward before the next forward")
+        B, T = sv["B"], sv["T"]
+        M, C, I, G, qpk = B * T, s.n_embd, s.intermediate_size, s.n_query_groups, s.qpk
+        bf, f32 = torch.bfloat16, torch.float32
+        packed = sv["packed"]
+        grads: Dict[str, Tensor] = {}
+        first = s.first_trainable_layer
+        if first >= s.n_layer:
+            return grads
+        dx = self._buf("dx", (M, C), f32)
+        dxb = self._buf("dxb", (M, C), bf)
+        ops.rmsnorm_bwd(sv["x_final"], self.ln_f, sv["rstd_f"], d_hidden.contiguous(), None, dx, dxb)
+        dh12 = self._buf("dh12", (M, 2 * I), bf)
+        dn = self._buf("dn", (M, C), bf)
+        dy = self._buf("dy", (M, C), bf)
+        dqkv = self._buf("dqkv", (M, s.qkv_out), bf)
+        ws = self._buf("attn_ws", (ops.attention_bwd_workspace(B, T, G, qpk),), torch.uint8)
+        scaling = (s.alpha / s.r) if s.r > 0 else 0.0
+        for i in range(s.n_layer - 1, first - 1, -1):
+            lw, a, pk = self.layers[i], sv["layers"][i], packed.get(i, {})
+            p = f"transformer.h.{i}.attn."
+            # ---- MLP: d(act) = dx Wp ; SwiGLU backward in the epilogue ; d(n2) = d(h12) W12 ----
+            ops.gemm(dxb, lw["wmlp"], dh12, b_layout=1, epilogue=ops.EPI_SWIGLU_BWD, aux=a["h12"])
+            ops.gemm(dh12, lw["w12"], dn, b_layout=1)
+            ops.rmsnorm_bwd(a["xmid"], lw["norm2"], a["rstd2"], dn, dx, dx, dxb)
+            # ---- attention output projection ----
+            if "proj_a" in pk:
+                dap = self._buf("dap", (M, LORA_PAD), bf)
+                ops.gemm(dxb, pk["proj_b"], dap, b_layout=1)
+                db = torch.empty((C, LORA_PAD), device=self.device, dtype=f32)
+                ops.gemm(dxb, a["ap_s"], db, a_layout=1, b_layout=1, epilogue=ops.EPI_F32)
+                da = torch.empty((LORA_PAD, C), device=self.device, dtype=f32)
+                ops.gemm(dap, a["y"], da, a_layout=1, b_layout=1, epilogue=ops.EPI_F32, alpha=scaling)
+                grads[p + "proj.lora_A"] = da[: s.r]
+                grads[p + "proj.lora_B"] = db[:, : s.r]
+                ops.gemm(dxb, lw["wproj"], dy, b_layout=1, A2=dap, B2=pk["proj_a"], b2_layout=1)
+            else:
+                ops.gemm(dxb, lw["wproj"], dy, b_layout=1)
+            # ---- attention ----
+            need_dqkv = not (s.variant == "adapter" and i == first)
+            d_pkv = d_gate = None
+            if a["prefix_kv"] is not None:
+                d_pkv = torch.zeros((s.adapter_prompt_length, s.qkv_out), device=self.device, dtype=f32)
+                d_gate = torch.zeros((s.n_head,), device=self.device, dtype=f32)
+            ops.attention_bwd(a["qkv"], a["y"], dy, a["lse"], dqkv if need_dqkv else None, ws, B, T, G, qpk, a["prefix_kv"], a["gate"],
+                              d_pkv, d_gate, s.adapter_prompt_length if a["prefix_kv"] is not None else 0, need_dqkv,
+                              rope_cos=self.cos, rope_sin=self.sin)
+            if d_pkv is not None:
+                d_pkv_b = self._buf("d_pkv_b", (s.adapter_prompt_length, s.qkv_out), bf)
+                ops.cast_f32_to_bf16(d_pkv, d_pkv_b)
+                d_wte = torch.empty((s.adapter_prompt_length, C), device=self.device, dtype=f32)
+                ops.gemm(d_pkv_b, lw["wqkv"], d_wte, b_layout=1, epilogue=ops.EPI_F32)
+                grads[p + "adapter_wte.weight"] = d_wte
+                grads[p + "gating_factor"] = d_gate.view(1, 1, s.n_head, 1)
+            if not need_dqkv:
+                continue
+            # ---- QKV projection ----
+            if "qkv_a" in pk:
+                da_s = self._buf("da_s", (M, LORA_PAD), bf)
+                ops.gemm(dqkv, pk["qkv_b"], da_s, b_layout=1)
+                db = torch.empty((s.qkv_out, LORA_PAD), device=self.device, dtype=f32)
+                ops.gemm(dqkv, a["a_s"], db, a_layout=1, b_layout=1, epilogue=ops.EPI_F32)
+                da = torch.empty((LORA_PAD, C), device=self.device, dtype=f32)
+                ops.gemm(da_s, a["n1"], da, a_layout=1, b_layout=1, epilogue=ops.EPI_F32, alpha=scaling)
+                r, kv = s.r, s.kv_embd
+                grads[p + "attn.lora_A"] = da[: 3 * r]
+                grads[p + "attn.lora_B"] = torch.cat((db[:C, 0:r], db[C:C + kv, r:2 * r], db[C + kv:, 2 * r:3 * r]), dim=0)
+                if i > first:
+                    ops.gemm(dqkv, lw["wqkv"], dn, b_layout=1, A2=da_s, B2=pk["qkv_a"], b2_layout=1)
+            elif i > first:
+                ops.gemm(dqkv, lw["wqkv"], dn, b_layout=1)
+            if i > first:
+                ops.rmsnorm_bwd(a["x"], lw["norm1"], a["rstd1"], dn, dx, dx, dxb)
+        return grads
+
+    # ------------------------------------------------------------------------------------------
+    # KV-cache decode (ger/model.py:132-151,248-261; generate/base.py:19-82)
+    # ------------------------------------------------------------------------------------------
+    def alloc_cache(self, nseq: int, max_len: int) -> None:
+        s = self.spec
+        if self.cache_k and self.cache_k[0].shape[0] == nseq and self.cache_max_len == max_len:
+            return
+        shape = (nseq, s.n_query_groups, max_len, 64)       # native GQA: 4 kv heads, not 32 expanded ones (quirk Q4)
+        self.cache_k = [torch.zeros(shape, device=self.device, dtype=torch.bfloat16) for _ in range(s.n_layer)]
+        self.cache_v = [torch.zeros(shape, device=self.device, dtype=torch.bfloat16) for _ in range(s.n_layer)]
+        self.cache_max_len = max_len
+
+    def drop_cache(self) -> None:
+        self.cache_k, self.cache_v, self.cache_max_len = [], [], 0
+
+    def _write_prefill_cache(self, layer: int, qkv: Tensor, B: int, T: int) -> None:
+        seq = self._buf("pf_seq", (B * T,), torch.int32)
+        pos = self._buf("pf_pos", (B * T,), torch.int32)
+        if layer == 0:
+            seq.copy_(torch.arange(B, device=self.device, dtype=torch.int32).repeat_interleave(T))
+            pos.copy_(torch.arange(T, device=self.device, dtype=torch.int32).repeat(B))
+        ops.kv_cache_write(qkv, self.cache_k[layer], self.cache_v[layer], seq, pos, self.spec.n_query_groups, self.spec.qpk)
+
+    def prefill(self, idx: Tensor, packed: Dict[int, Dict[str, Tensor]]) -> Tensor:
+        """Full causal forward over right-padded prompts [B, T]; K/V of every position go to the cache."""
+        assert self.cache_k and self.cache_k[0].shape[0] >= idx.shape[0] and self.cache_max_len >= idx.shape[1]
+        return self.forward_hidden(idx, packed, save=False, write_cache=True)
+
+    def decode_step(self, tokens: Tensor, positions: Tensor, packed: Dict[int, Dict[str, Tensor]]) -> Tensor:
+        """One new token per sequence: tokens int64 [n], positions int32 [n] (0-based position of that token).
+        Returns ln_f output bf16 [n, C]."""
+        s = self.spec
+        n_seq = tokens.shape[0]
+        C, I, G, qpk = s.n_embd, s.intermediate_size, s.n_query_groups, s.qpk
+        bf, f32 = torch.bfloat16, torch.float32
+        x = self._buf("dec_x", (n_seq, C), f32)
+        x2 = self._buf("dec_x2", (n_seq, C), f32)
+        n = self._buf("dec_n", (n_seq, C), bf)
+        qkv = self._buf("dec_qkv", (n_seq, s.qkv_out), bf)
+        y = self._buf("dec_y", (n_seq, C), bf)
+        act = self._buf("dec_act", (n_seq, I), bf)
+        seq_ids = self._buf("dec_seq", (n_seq,), torch.int32)
+        lens = self._buf("dec_lens", (n_seq,), torch.int32)
+        seq_ids.copy_(torch.arange(n_seq, device=self.device, dtype=torch.int32))
+        torch.add(positions, 1, out=lens)
+        ops.embedding_fwd(tokens.contiguous(), self.wte, x)
+        for i, lw in enumerate(self.layers):
+            pk = packed.get(i, {})
+            ops.rmsnorm_fwd(x, lw["norm1"], n, None, s.norm_eps)
+            if "qkv_a" in pk:
+                a_s = self._buf("dec_as", (n_seq, LORA_PAD), bf)
+                ops.gemm(n, pk["qkv_a"], a_s)
+                ops.gemm(n, lw["wqkv"], qkv, A2=a_s, B2=pk["qkv_b"], epilogue=ops.EPI_QKV_ROPE, rope_cos=self.cos, rope_sin=self.sin,
+                         positions=positions, seq_len=1, q_per_kv=qpk)
+            else:
+                ops.gemm(n, lw["wqkv"], qkv, epilogue=ops.EPI_QKV_ROPE, rope_cos=self.cos, rope_sin=self.sin, positions=positions,
+                         seq_len=1, q_per_kv=qpk)
+            ops.kv_cache_write(qkv, self.cache_k[i], self.cache_v[i], seq_ids, positions, G, qpk)
+            prefix_kv = gate = None
+            if "prefix" in pk:
+                prefix_kv = self._buf(f"dec_pkv{i}", (s.adapter_prompt_length, s.qkv_out), bf)
+                ops.gemm(pk["prefix"], lw["wqkv"], prefix_kv)
+                gate = pk["gate"]
+            ops.attention_decode(qkv, self.cache_k[i], self.cache_v[i], lens, y, G, qpk, prefix_kv, gate,
+                                 s.adapter_prompt_length if prefix_kv is not None else 0)
+            if "proj_a" in pk:
+                ap_s = self._buf("dec_aps", (n_seq, LORA_PAD), bf)
+                ops.gemm(y, pk["proj_a"], ap_s)
+                ops.gemm(y, lw["wproj"], x2, A2=ap_s, B2=pk["proj_b"], epilogue=ops.EPI_RESID_F32, aux=x)
+            else:
+                ops.gemm(y, lw["wproj"], x2, epilogue=ops.EPI_RESID_F32, aux=x)
+            ops.rmsnorm_fwd(x2, lw["norm2"], n, None, s.norm_eps)
+            ops.gemm(n, lw["w12"], None, epilogue=ops.EPI_SWIGLU, out2=act)
+            ops.gemm(act, lw["wmlp"], x, epilogue=ops.EPI_RESID_F32, aux=x2)
+        hidden = self._buf("dec_hidden", (n_seq, C), bf)
+        ops.rmsnorm_fwd(x, self.ln_f, hidden, None, s.norm_eps)
+        return hidden

@@ -37,8 +37,8 @@ int dh_sm_count(void);
  * a_layout/b_layout 0 = K-major  (A is [M,K] row-major; B is [N,K] row-major, i.e. y = x W^T with W as stored)
  *                   1 = MN-major (A is [K,M] row-major; B is [K,N] row-major)            -- dgrad / wgrad forms
  * The second source pair folds a LoRA low-rank delta into the same accumulator (K extension).
- * Constraints: N % 64 == 0, K1 % 64 == 0, K2 % 64 == 0, 16-byte aligned rows.  M is arbitrary (tail rows are
- * zero-filled by TMA on load and masked on store).
+ * Constraints: N % 64 == 0, K1 % 8 == 0, K2 % 8 == 0, 16-byte aligned rows.  M is arbitrary and K may be ragged (tails
+ * are zero-filled by TMA on load; tail rows are masked on store).
  * ------------------------------------------------------------------------------------------------- */
 enum dh_epilogue {
   DH_EPI_BF16 = 0,        /* out[bf16] = (acc*alpha [+col_bias]) [*col_scale]                                  */

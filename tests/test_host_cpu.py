@@ -1,0 +1,102 @@
+"""CPU: host-side logic of the `ger` mirror -- config registry, module trees / state-dict keys against the
+reference's (live where mounted, and by the golden key lists), checkpoint key remapping, LazyLogits slicing,
+synthetic-input determinism, flop accounting."""
+import pytest
+import torch
+
+from dualhyp_b200 import flops, synthetic
+from dualhyp_b200.ger import adapter, lora, relprompt
+from dualhyp_b200.ger.config import Config
+from dualhyp_b200.ger.model import LazyLogits
+from oracle import refshim
+from tests.helpers import load_golden
+
+LORA = dict(r=8, alpha=16, to_query=True, to_key=True, to_value=True, to_projection=True)
+
+
+def test_tinyllama_config_resolves_by_hf_name():
+    c = Config.from_name("TinyLlama-1.1B-Chat-v1.0")
+    assert (c.n_layer, c.n_head, c.n_query_groups, c.n_embd, c.intermediate_size, c.padded_vocab_size, c.head_size) == \
+        (22, 32, 4, 2048, 5632, 32000, 64)
+    c.check_engine_supported()
+    with pytest.raises(ValueError):
+        Config.from_name("no-such-model")
+
+
+def test_parameter_counts_match_survey():
+    m = torch.device("meta")
+    with m:
+        lo = lora.GPT(lora.Config.from_name("tiny-llama-1.1b", **{**LORA, "r": 16}))
+        ad = adapter.GPT(adapter.Config.from_name("tiny-llama-1.1b"))
+    lora.mark_only_lora_as_trainable(lo)
+    adapter.mark_only_adapter_as_trainable(ad)
+    assert sum(p.numel() for p in lo.parameters() if p.requires_grad) == 4_505_600
+    assert sum(p.numel() for p in ad.parameters() if p.requires_grad) == 410_240
+    assert sum(p.numel() for p in lo.parameters()) == 1_104_617_984 + 0
+
+
+def test_state_dict_keys_match_golden_gradient_keys():
+    for variant, mod, extra in (("lora", lora, LORA), ("adapter", adapter, {"adapter_start_layer": 1})):
+        g = load_golden(f"tiny_{variant}.npz")
+        model = mod.GPT(mod.Config.from_name("tiny-llama-test", **extra))
+        names = {n for n, _ in model.named_parameters()}
+        for k in g:
+            if k.startswith("grad."):
+                assert k[5:] in names, k
+
+
+@pytest.mark.skipif(not refshim.available(), reason="reference checkout not mounted")
+def test_state_dict_keys_equal_live_reference():
+    refshim.install()
+    import ger.lora as RL
+    rcfg = RL.Config(name="t", block_size=256, vocab_size=512, padded_vocab_size=512, n_layer=3, n_head=4, n_embd=256,
+                     rotary_percentage=1.0, parallel_residual=False, bias=False, _norm_class="RMSNorm", norm_eps=1e-5,
+                     _mlp_class="LLaMAMLP", intermediate_size=512, n_query_groups=2, **LORA)
+    ref = RL.GPT(rcfg).state_dict()
+    mine = lora.GPT(lora.Config.from_name("tiny-llama-test", **LORA)).state_dict()
+    assert list(ref.keys()) == list(mine.keys())
+    assert all(ref[k].shape == mine[k].shape for k in ref)
+
+
+def test_base_checkpoint_keys_are_remapped():
+    cfg = lora.Config.from_name("tiny-llama-test", **LORA)
+    m = lora.GPT(cfg)
+    res = m.load_state_dict(synthetic.synth_state_dict(cfg, "base", 3), strict=False)
+    assert not res.unexpected_keys
+    assert all("lora_" in k or "adapter_" in k for k in res.missing_keys)
+
+
+def test_lazy_logits_slicing_stays_lazy():
+    class Fake:
+        class config:
+            padded_vocab_size = 11
+    h = torch.zeros(2, 10, 4)
+    chunks = [LazyLogits(Fake, h[:, a:a + 4], h, a, min(10, a + 4)) for a in range(0, 10, 4)]
+    assert [tuple(c.shape) for c in chunks] == [(2, 4, 11), (2, 4, 11), (2, 2, 11)]
+    last = chunks[-1][..., :-1, :]
+    assert isinstance(last, LazyLogits) and (last.t0, last.t1) == (8, 9) and last.base is h
+    row = LazyLogits(Fake, h)[0, -1]
+    assert isinstance(row, LazyLogits) and tuple(row.shape) == (11,)
+
+
+def test_synthetic_inputs_are_deterministic_and_structured():
+    a = synthetic.synth_batch(4, 512, 32000, 1337)
+    b = synthetic.synth_batch(4, 512, 32000, 1337)
+    assert torch.equal(a[0], b[0]) and torch.equal(a[1], b[1])
+    ids, labels = a
+    for r in range(4):
+        valid = (labels[r] >= 0).nonzero().flatten()
+        assert 8 <= valid.numel() <= 24 and 330 <= int(valid[0]) <= 480
+        assert torch.equal(labels[r][valid], ids[r][valid])
+        assert (ids[r][int(valid[-1]) + 1:] == 0).all()          # right padding with id 0, label -1
+    w = synthetic.hash_uniform((64, 64), 1, 2, 0.1)
+    assert torch.equal(w, w.bfloat16().float())                   # bf16-exact weights
+
+
+def test_flop_accounting_matches_survey_figures():
+    c = Config.from_name("tiny-llama-1.1b")
+    assert abs(flops.forward_flops_per_token(c, 512) / 1e9 - 2.115) < 0.01
+    c.lora_start_layer = 0
+    assert abs((flops.forward_flops_per_token(c, 512) + flops.backward_flops_per_token(c, "lora", 512)) / 1e9 - 4.29) < 0.02
+    c.adapter_start_layer = 2
+    assert abs((flops.forward_flops_per_token(c, 512) + flops.backward_flops_per_token(c, "adapter", 512)) / 1e9 - 4.10) < 0.03
