@@ -41,6 +41,13 @@ static int resolve_encode() {
 int make_tensor_map(CUtensorMap* map, const void* base, CUtensorMapDataType dtype, int rank, const uint64_t* dims,
                     const uint64_t* strides_bytes, const uint32_t* box, CUtensorMapSwizzle swizzle) {
   if (resolve_encode()) return -1;
+  // The encoder is a driver-API call and needs a current context.  PyTorch's autograd worker threads (where
+  // backward kernels are launched from) may never have bound the primary context: bind it once per thread.
+  static thread_local bool ctx_bound = false;
+  if (!ctx_bound) {
+    cudaFree(0);
+    ctx_bound = true;
+  }
   cuuint64_t gdim[5], gstr[4];
   cuuint32_t gbox[5], estr[5];
   for (int i = 0; i < rank; ++i) {
