@@ -19,6 +19,47 @@ def launches() -> int:
     return _launches
 
 
+# ---- optional per-launch timing (bench.py's roofline pass): CUDA events on the launching stream ----
+_prof = None
+
+
+class profile:
+    """`with ops.profile() as recs:` records (name, meta, start_event, end_event) for every op launched inside."""
+
+    def __enter__(self):
+        global _prof
+        _prof = []
+        return _prof
+
+    def __exit__(self, *exc):
+        global _prof
+        _prof = None
+        return False
+
+
+def _profiled(name, meta_fn=None):
+    def deco(fn):
+        def wrapper(*args, **kwargs):
+            if _prof is None:
+                return fn(*args, **kwargs)
+            e0, e1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+            e0.record()
+            out = fn(*args, **kwargs)
+            e1.record()
+            _prof.append((name, meta_fn(*args, **kwargs) if meta_fn else None, e0, e1))
+            return out
+        wrapper.__name__, wrapper.__doc__ = fn.__name__, fn.__doc__
+        return wrapper
+    return deco
+
+
+def _gemm_meta(A, B, out, *, epilogue=EPI_BF16, b_layout=0, a_layout=0, A2=None, **kw):
+    M, K = (A.shape if a_layout == 0 else (A.shape[1], A.shape[0]))
+    N = B.shape[0] if b_layout == 0 else B.shape[1]
+    K2 = 0 if A2 is None else (A2.shape[1] if kw.get("a2_layout", 0) == 0 else A2.shape[0])
+    return (int(M), int(N), int(K), int(K2), int(epilogue), int(a_layout), int(b_layout))
+
+
 def _count(n: int = 1) -> None:
     global _launches
     _launches += n
@@ -45,6 +86,7 @@ def _rowmajor(t: Tensor, what: str) -> int:
     return t.stride(0)
 
 
+@_profiled("gemm", _gemm_meta)
 def gemm(A: Tensor, B: Tensor, out: Optional[Tensor], *, epilogue: int = EPI_BF16, b_layout: int = 0, a_layout: int = 0,
          A2: Optional[Tensor] = None, B2: Optional[Tensor] = None, a2_layout: int = 0, b2_layout: int = 0,
          out2: Optional[Tensor] = None, aux: Optional[Tensor] = None, alpha: float = 1.0, accumulate: bool = False,
@@ -87,6 +129,7 @@ def gemm(A: Tensor, B: Tensor, out: Optional[Tensor], *, epilogue: int = EPI_BF1
     _count()
 
 
+@_profiled("rmsnorm_fwd")
 def rmsnorm_fwd(x: Tensor, weight: Tensor, y: Tensor, rstd: Optional[Tensor], eps: float) -> None:
     _dev(x)
     M, Cdim = x.shape
@@ -97,6 +140,7 @@ def rmsnorm_fwd(x: Tensor, weight: Tensor, y: Tensor, rstd: Optional[Tensor], ep
     _count()
 
 
+@_profiled("rmsnorm_bwd")
 def rmsnorm_bwd(x: Tensor, weight: Tensor, rstd: Tensor, dy: Tensor, dres: Optional[Tensor], dx_out: Tensor,
                 dx_bf16: Optional[Tensor]) -> None:
     _dev(x)
@@ -108,6 +152,7 @@ def rmsnorm_bwd(x: Tensor, weight: Tensor, rstd: Tensor, dy: Tensor, dres: Optio
     _count()
 
 
+@_profiled("embedding_fwd")
 def embedding_fwd(idx: Tensor, wte: Tensor, out: Tensor) -> None:
     _dev(wte)
     assert idx.dtype == torch.int64 and idx.is_contiguous() and wte.is_contiguous() and out.is_contiguous()
@@ -139,6 +184,7 @@ def rope_qkv_inplace(qkv: Tensor, cos: Tensor, sin: Tensor, seq_len: int, n_grou
     _count()
 
 
+@_profiled("attention_fwd")
 def attention_fwd(qkv: Tensor, out: Tensor, lse: Tensor, B: int, T: int, n_groups: int, q_per_kv: int,
                   prefix_kv: Optional[Tensor] = None, gate: Optional[Tensor] = None, prefix_len: int = 0) -> None:
     _dev(qkv)
@@ -155,6 +201,7 @@ def attention_bwd_workspace(B: int, T: int, n_groups: int, q_per_kv: int) -> int
     return int(_lib.load().dh_attention_bwd_workspace(B, T, n_groups, q_per_kv))
 
 
+@_profiled("attention_bwd")
 def attention_bwd(qkv: Tensor, out: Tensor, dout: Tensor, lse: Tensor, dqkv: Optional[Tensor], workspace: Tensor, B: int, T: int,
                   n_groups: int, q_per_kv: int, prefix_kv: Optional[Tensor] = None, gate: Optional[Tensor] = None,
                   d_prefix_kv: Optional[Tensor] = None, d_gate: Optional[Tensor] = None, prefix_len: int = 0,
@@ -170,6 +217,7 @@ def attention_bwd(qkv: Tensor, out: Tensor, dout: Tensor, lse: Tensor, dqkv: Opt
     _count(3 if need_dqkv else 1)
 
 
+@_profiled("attention_decode")
 def attention_decode(qkv: Tensor, cache_k: Tensor, cache_v: Tensor, lens: Tensor, out: Tensor, n_groups: int, q_per_kv: int,
                      prefix_kv: Optional[Tensor] = None, gate: Optional[Tensor] = None, prefix_len: int = 0) -> None:
     _dev(qkv)
@@ -181,6 +229,7 @@ def attention_decode(qkv: Tensor, cache_k: Tensor, cache_v: Tensor, lens: Tensor
     _count()
 
 
+@_profiled("kv_cache_write")
 def kv_cache_write(qkv: Tensor, cache_k: Tensor, cache_v: Tensor, seq: Tensor, pos: Tensor, n_groups: int, q_per_kv: int) -> None:
     _dev(qkv)
     assert seq.dtype == torch.int32 and pos.dtype == torch.int32 and qkv.is_contiguous()
@@ -189,6 +238,7 @@ def kv_cache_write(qkv: Tensor, cache_k: Tensor, cache_v: Tensor, seq: Tensor, p
     _count()
 
 
+@_profiled("cross_entropy")
 def cross_entropy(logits: Tensor, targets: Tensor, row_loss: Tensor, grad_scale: float, write_grad: bool) -> None:
     _dev(logits)
     assert logits.dtype == torch.bfloat16 and targets.dtype == torch.int64 and targets.is_contiguous()
@@ -198,6 +248,7 @@ def cross_entropy(logits: Tensor, targets: Tensor, row_loss: Tensor, grad_scale:
     _count()
 
 
+@_profiled("loss_reduce")
 def loss_reduce(row_loss: Tensor, targets: Tensor, out2: Tensor) -> None:
     _dev(row_loss)
     check(_lib.load().dh_loss_reduce(row_loss.data_ptr(), targets.data_ptr(), out2.data_ptr(), row_loss.numel(), _stream()),
@@ -205,6 +256,7 @@ def loss_reduce(row_loss: Tensor, targets: Tensor, out2: Tensor) -> None:
     _count()
 
 
+@_profiled("argmax")
 def argmax(logits: Tensor, ids: Tensor) -> None:
     _dev(logits)
     M, V = logits.shape
@@ -213,6 +265,7 @@ def argmax(logits: Tensor, ids: Tensor) -> None:
     _count()
 
 
+@_profiled("cast_f32_to_bf16")
 def cast_f32_to_bf16(src: Tensor, dst: Tensor) -> None:
     _dev(src)
     assert src.dtype == torch.float32 and dst.dtype == torch.bfloat16 and src.shape == dst.shape
@@ -221,6 +274,7 @@ def cast_f32_to_bf16(src: Tensor, dst: Tensor) -> None:
     _count()
 
 
+@_profiled("adamw_step")
 def adamw_step(param: Tensor, grad: Tensor, exp_avg: Tensor, exp_avg_sq: Tensor, lr: float, beta1: float, beta2: float, eps: float,
                weight_decay: float, step: int, grad_scale: float = 1.0) -> None:
     _dev(param)
