@@ -6,6 +6,8 @@
 //
 // Roles (256 threads, 1 CTA / SM): warp 0 = TMA producer, warp 1 = MMA issuer, warp 2 = TMEM allocator,
 // warps 4-7 = epilogue (warp w owns TMEM lanes 32*(w%4) .. +31, one accumulator row per thread).
+#include <stdlib.h>
+
 #include "common.cuh"
 #include "../../include/dualhyp.h"
 
@@ -305,6 +307,144 @@ gemm_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant__ CUt
 }
 
 // ------------------------------------------------------------------------------------------------
+// CTA-pair kernel (cluster of 2, tcgen05 cta_group::2): one 256 x 256 output tile per pair.  CTA r of the
+// pair stages A rows [128 r, 128 r + 128) and B rows (= output columns) [128 r, 128 r + 128) of the tile
+// and owns accumulator rows [128 r, +128) x 256 columns in its own TMEM; the leader's MMA thread drives
+// both tensor cores, so every B byte is fetched into shared memory once per pair instead of once per SM.
+// K-major operands only (dgrads use pre-transposed frozen weights).
+// ------------------------------------------------------------------------------------------------
+struct PairCfg {
+  static constexpr int BN = 256;
+  static constexpr int A_BYTES = 128 * BK * 2;
+  static constexpr int B_BYTES = 128 * BK * 2;
+  static constexpr int STAGE_BYTES = A_BYTES + B_BYTES;
+  static constexpr int STAGES = 6;
+  static constexpr int SMEM_BYTES = STAGES * STAGE_BYTES + 1024 + 256;
+};
+
+template <int EPI>
+__global__ void __cluster_dims__(2, 1, 1) __launch_bounds__(GEMM_THREADS, 1)
+gemm_pair_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant__ CUtensorMap tmB,
+                 const __grid_constant__ CUtensorMap tmA2, const __grid_constant__ CUtensorMap tmB2, const GemmParams p) {
+  using Cfg = PairCfg;
+  constexpr int STAGES = Cfg::STAGES;
+  constexpr int BN = Cfg::BN;
+  extern __shared__ uint8_t smem_raw[];
+  uint8_t* smem = reinterpret_cast<uint8_t*>((reinterpret_cast<uintptr_t>(smem_raw) + 1023) & ~uintptr_t(1023));
+  uint64_t* bars = reinterpret_cast<uint64_t*>(smem + STAGES * Cfg::STAGE_BYTES);
+  uint64_t* full_bar = bars;                     // [STAGES]  TMA (both CTAs) -> MMA       (leader's copy is used)
+  uint64_t* empty_bar = bars + STAGES;           // [STAGES]  MMA -> TMA                   (multicast to both)
+  uint64_t* tfull_bar = bars + 2 * STAGES;       // [2]       MMA -> epilogue              (multicast to both)
+  uint64_t* tempty_bar = bars + 2 * STAGES + 2;  // [2]       epilogue (both CTAs) -> MMA  (leader's copy is used)
+  uint32_t* tmem_slot = reinterpret_cast<uint32_t*>(bars + 2 * STAGES + 4);
+
+  const int warp = threadIdx.x >> 5;
+  const int lane = threadIdx.x & 31;
+  const uint32_t rank = cluster_ctarank();
+  const int pair = blockIdx.x >> 1;
+  const int npairs = gridDim.x >> 1;
+  const int num_tiles = p.tiles_m * p.tiles_n;
+  const int nkb1 = (p.K1 + BK - 1) / BK;
+  const int nkb = nkb1 + (p.K2 + BK - 1) / BK;
+
+  if (warp == 0 && lane == 0) {
+    tma_prefetch_desc(&tmA);
+    tma_prefetch_desc(&tmB);
+    if (p.K2 > 0) { tma_prefetch_desc(&tmA2); tma_prefetch_desc(&tmB2); }
+  }
+  if (warp == 1 && lane == 0) {
+    for (int i = 0; i < STAGES; ++i) { mbar_init(&full_bar[i], 1); mbar_init(&empty_bar[i], 1); }
+    for (int i = 0; i < 2; ++i) { mbar_init(&tfull_bar[i], 1); mbar_init(&tempty_bar[i], 8); }
+    fence_barrier_init();
+  }
+  if (warp == 2) {
+    tmem_alloc2(tmem_slot, 512);
+    tmem_relinquish2();
+  }
+  tc_fence_before();
+  cluster_sync_all();
+  tc_fence_after();
+  const uint32_t tmem_base = *tmem_slot;
+
+  if (warp == 0 && lane == 0) {
+    // ===================== TMA producer (each CTA loads its own halves) =====================
+    uint32_t it = 0;
+    for (int tile = pair; tile < num_tiles; tile += npairs) {
+      const int m0 = (tile % p.tiles_m) * 256 + (int)rank * 128;
+      const int n0 = (tile / p.tiles_m) * BN + (int)rank * 128;
+      for (int kb = 0; kb < nkb; ++kb, ++it) {
+        const int s = it % STAGES;
+        mbar_wait(&empty_bar[s], ((it / STAGES) & 1) ^ 1);
+        uint8_t* sa = smem + s * Cfg::STAGE_BYTES;
+        uint8_t* sb = sa + Cfg::A_BYTES;
+        if (rank == 0) mbar_expect_tx(&full_bar[s], 2 * Cfg::STAGE_BYTES);
+        const uint32_t bar = mapa_shared(smem_u32(&full_bar[s]), 0);
+        const bool second = kb >= nkb1;
+        const int k0 = (second ? kb - nkb1 : kb) * BK;
+        tma_load_2d_pair(sa, second ? &tmA2 : &tmA, k0, m0, bar);
+        tma_load_2d_pair(sb, second ? &tmB2 : &tmB, k0, n0, bar);
+      }
+    }
+  } else if (warp == 1 && lane == 0 && rank == 0) {
+    // ===================== MMA issuer (leader CTA only) =====================
+    constexpr uint32_t idesc = umma_idesc_bf16(256, BN, 0, 0);
+    uint32_t it = 0, tcount = 0;
+    for (int tile = pair; tile < num_tiles; tile += npairs, ++tcount) {
+      const int acc = tcount & 1;
+      mbar_wait(&tempty_bar[acc], ((tcount >> 1) & 1) ^ 1);
+      tc_fence_after();
+      const uint32_t d_tmem = tmem_base + acc * BN;
+      for (int kb = 0; kb < nkb; ++kb, ++it) {
+        const int s = it % STAGES;
+        mbar_wait(&full_bar[s], (it / STAGES) & 1);
+        tc_fence_after();
+        const uint32_t sa = smem_u32(smem + s * Cfg::STAGE_BYTES);
+        const uint32_t sb = sa + Cfg::A_BYTES;
+#pragma unroll
+        for (int k = 0; k < BK / 16; ++k)
+          tc_mma_ss_pair(d_tmem, umma_desc_sw128(sa + k * 32, 16, 1024), umma_desc_sw128(sb + k * 32, 16, 1024), idesc, (kb | k) != 0);
+        tc_commit_pair(&empty_bar[s], 3);
+      }
+      tc_commit_pair(&tfull_bar[acc], 3);
+    }
+  } else if (warp >= 4) {
+    // ===================== epilogue (each CTA drains its own 128 accumulator rows) =====================
+    const int q = warp & 3;
+    uint32_t tcount = 0;
+    for (int tile = pair; tile < num_tiles; tile += npairs, ++tcount) {
+      const int acc = tcount & 1;
+      const int m0 = (tile % p.tiles_m) * 256 + (int)rank * 128;
+      const int n0 = (tile / p.tiles_m) * BN;
+      mbar_wait(&tfull_bar[acc], (tcount >> 1) & 1);
+      tc_fence_after();
+      const int row = m0 + q * 32 + lane;
+      const uint32_t taddr = tmem_base + ((uint32_t)(q * 32) << 16) + acc * BN;
+#pragma unroll 1
+      for (int c = 0; c < BN / 64; ++c) {
+        uint32_t r0[32], r1[32];
+        tmem_ld32(taddr + c * 64, r0);
+        tmem_ld32(taddr + c * 64 + 32, r1);
+        tmem_wait_ld();
+        float v[64];
+#pragma unroll
+        for (int j = 0; j < 32; ++j) { v[j] = __uint_as_float(r0[j]); v[j + 32] = __uint_as_float(r1[j]); }
+        if (row < p.M) epilogue_chunk<EPI>(p, row, n0 + c * 64, v);
+      }
+      tc_fence_before();
+      __syncwarp();
+      if (lane == 0) mbar_arrive_cluster(mapa_shared(smem_u32(&tempty_bar[acc]), 0));
+    }
+  }
+
+  tc_fence_before();
+  cluster_sync_all();
+  if (warp == 2) {
+    tc_fence_after();
+    tmem_dealloc2(tmem_base, 512);
+  }
+}
+
+// ------------------------------------------------------------------------------------------------
 // host
 // ------------------------------------------------------------------------------------------------
 static int make_operand_map(CUtensorMap* map, const void* base, long long ld, int mn_extent, int k_extent, int mn_major,
@@ -319,6 +459,25 @@ static int make_operand_map(CUtensorMap* map, const void* base, long long ld, in
   uint64_t strides[1] = {(uint64_t)ld * 2};
   uint32_t box[2] = {64, 64};
   return make_tensor_map(map, base, CU_TENSOR_MAP_DATA_TYPE_BFLOAT16, 2, dims, strides, box, CU_TENSOR_MAP_SWIZZLE_128B);
+}
+
+static GemmParams make_params(const dh_gemm_args* a) {
+  GemmParams p;
+  p.M = a->M; p.N = a->N; p.K1 = a->K1; p.K2 = a->K2;
+  p.tiles_m = p.tiles_n = 0;
+  p.a_mn = a->a_layout; p.b_mn = a->b_layout; p.a2_mn = a->a2_layout; p.b2_mn = a->b2_layout;
+  p.accumulate = a->accumulate;
+  p.alpha = a->alpha;
+  p.seq_len = a->seq_len > 0 ? a->seq_len : 1;
+  p.q_per_kv = a->q_per_kv;
+  p.out = a->out; p.ldo = a->ldo;
+  p.out2 = a->out2; p.ldo2 = a->ldo2;
+  p.aux = a->aux; p.ldaux = a->ldaux;
+  p.col_scale = a->col_scale; p.col_bias = a->col_bias;
+  p.rope_cos = reinterpret_cast<const bf16*>(a->rope_cos);
+  p.rope_sin = reinterpret_cast<const bf16*>(a->rope_sin);
+  p.positions = a->positions;
+  return p;
 }
 
 template <int BN, int EPI>
@@ -339,22 +498,9 @@ static int launch_gemm(const dh_gemm_args* a, cudaStream_t stream) {
     tmA2 = tmA;
     tmB2 = tmB;
   }
-  GemmParams p;
-  p.M = a->M; p.N = a->N; p.K1 = a->K1; p.K2 = a->K2;
+  GemmParams p = make_params(a);
   p.tiles_m = (a->M + BM - 1) / BM;
   p.tiles_n = a->N / BN;
-  p.a_mn = a->a_layout; p.b_mn = a->b_layout; p.a2_mn = a->a2_layout; p.b2_mn = a->b2_layout;
-  p.accumulate = a->accumulate;
-  p.alpha = a->alpha;
-  p.seq_len = a->seq_len > 0 ? a->seq_len : 1;
-  p.q_per_kv = a->q_per_kv;
-  p.out = a->out; p.ldo = a->ldo;
-  p.out2 = a->out2; p.ldo2 = a->ldo2;
-  p.aux = a->aux; p.ldaux = a->ldaux;
-  p.col_scale = a->col_scale; p.col_bias = a->col_bias;
-  p.rope_cos = reinterpret_cast<const bf16*>(a->rope_cos);
-  p.rope_sin = reinterpret_cast<const bf16*>(a->rope_sin);
-  p.positions = a->positions;
   const int tiles = p.tiles_m * p.tiles_n;
   const int grid = tiles < sm_count() ? tiles : sm_count();
   gemm_kernel<BN, EPI><<<grid, GEMM_THREADS, Cfg::SMEM_BYTES, stream>>>(tmA, tmB, tmA2, tmB2, p);
@@ -363,7 +509,46 @@ static int launch_gemm(const dh_gemm_args* a, cudaStream_t stream) {
 }
 
 template <int EPI>
+static int launch_gemm_pair(const dh_gemm_args* a, cudaStream_t stream) {
+  using Cfg = PairCfg;
+  static bool attr_set = false;
+  if (!attr_set) {
+    DH_CUDA(cudaFuncSetAttribute(gemm_pair_kernel<EPI>, cudaFuncAttributeMaxDynamicSharedMemorySize, Cfg::SMEM_BYTES));
+    attr_set = true;
+  }
+  CUtensorMap tmA, tmB, tmA2, tmB2;
+  if (make_operand_map(&tmA, a->A, a->lda, a->M, a->K1, 0, 128)) return -3;
+  if (make_operand_map(&tmB, a->B, a->ldb, a->N, a->K1, 0, 128)) return -3;
+  if (a->K2 > 0) {
+    if (make_operand_map(&tmA2, a->A2, a->lda2, a->M, a->K2, 0, 128)) return -3;
+    if (make_operand_map(&tmB2, a->B2, a->ldb2, a->N, a->K2, 0, 128)) return -3;
+  } else {
+    tmA2 = tmA;
+    tmB2 = tmB;
+  }
+  GemmParams p = make_params(a);
+  p.tiles_m = (a->M + 255) / 256;
+  p.tiles_n = a->N / Cfg::BN;
+  const int tiles = p.tiles_m * p.tiles_n;
+  const int pairs = sm_count() / 2;
+  const int grid = 2 * (tiles < pairs ? tiles : pairs);
+  gemm_pair_kernel<EPI><<<grid, GEMM_THREADS, Cfg::SMEM_BYTES, stream>>>(tmA, tmB, tmA2, tmB2, p);
+  DH_CUDA(cudaGetLastError());
+  return 0;
+}
+
+static int g_force_single = -1;   // DH_GEMM_SINGLE=1 forces the 1-CTA kernel (A/B testing)
+
+template <int EPI>
 static int dispatch_bn(const dh_gemm_args* a, cudaStream_t stream) {
+  if (g_force_single < 0) {
+    const char* e = getenv("DH_GEMM_SINGLE");
+    g_force_single = (e && e[0] == '1') ? 1 : 0;
+  }
+  // CTA pairs for the big K-major GEMMs of the decoder; the 1-CTA kernel covers small M, MN-major operands, odd N.
+  if (!g_force_single && a->a_layout == 0 && a->b_layout == 0 && (a->K2 == 0 || (a->a2_layout == 0 && a->b2_layout == 0)) &&
+      a->N % 256 == 0 && a->M >= 1024)
+    return launch_gemm_pair<EPI>(a, stream);
   // Tile width: 256 when it divides N and leaves enough tiles to fill the machine, else 128, else 64.
   const long long tiles_m = (a->M + BM - 1) / BM;
   if (a->N % 256 == 0 && tiles_m * (a->N / 256) >= sm_count()) return launch_gemm<256, EPI>(a, stream);

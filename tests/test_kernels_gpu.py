@@ -37,7 +37,7 @@ def report(name, got, ref):
 # GEMM
 # ----------------------------------------------------------------------------------------------
 @pytest.mark.parametrize("M,N,K", [(128, 64, 64), (128, 128, 64), (256, 256, 128), (1000, 512, 256), (77, 320, 192),
-                                   (4096, 2560, 2048)])
+                                   (4096, 2560, 2048), (1024, 256, 64), (1100, 768, 320), (2048, 512, 264), (8192, 2048, 2048)])
 def test_gemm_kmajor(M, N, K):
     A, B = rnd((M, K), 1), rnd((N, K), 2)
     out = torch.full((M, N), float("nan"), device=DEV, dtype=torch.bfloat16)
