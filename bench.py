@@ -291,7 +291,11 @@ def run_native(args):
                             "avg_ms": round(dms / dcount, 4), "share_of_step": round(dms / total_ms, 4),
                             "all_gemms": {"tflops": round(gemm_fl / (gemm_ms / 1e3) / 1e12, 1), "share_of_step": round(gemm_ms / total_ms, 4)},
                             "by_op_ms_per_step": {n: round(sum(v[1] for k, v in agg.items() if k[0] == n) / 2, 3)
-                                                  for n in sorted({k[0] for k in agg})}}
+                                                  for n in sorted({k[0] for k in agg})},
+                            "gemm_by_shape": [{"M": k[1][0], "N": k[1][1], "K": k[1][2] + k[1][3], "epi": gemm_epi_name(k[1][4]),
+                                               "n": v[0] // 2, "avg_ms": round(v[1] / v[0], 4),
+                                               "tflops": round(2.0 * k[1][0] * k[1][1] * (k[1][2] + k[1][3]) / (v[1] / v[0] / 1e3) / 1e12, 1)}
+                                              for k, v in sorted(agg.items(), key=lambda kv: -kv[1][1]) if k[0] == "gemm"][:12]}
     if rank == 0 and world == 1 and not args.no_cpu_baseline:
         tps, ms, cores, sample = cpu_step_tokens_per_s(args.workload, T, 2, 1)
         line["cpu_baseline"] = {"value": round(tps, 2), "unit": UNIT, "cores": cores, "kind": "port", "sample": sample}

@@ -69,6 +69,16 @@ __device__ __forceinline__ void load_bf16x32(const bf16* src, float (&f)[32]) {
   }
 }
 
+__device__ __forceinline__ void unpack_bf16x8(const uint4& u, float (&f)[8]) {
+  float2 a = unpack_bf16x2(u.x), b = unpack_bf16x2(u.y), c = unpack_bf16x2(u.z), d = unpack_bf16x2(u.w);
+  f[0] = a.x; f[1] = a.y; f[2] = b.x; f[3] = b.y; f[4] = c.x; f[5] = c.y; f[6] = d.x; f[7] = d.y;
+}
+__device__ __forceinline__ uint4 pack_bf16x8(const float (&f)[8]) {
+  uint4 u;
+  u.x = pack_bf16x2(f[0], f[1]); u.y = pack_bf16x2(f[2], f[3]); u.z = pack_bf16x2(f[4], f[5]); u.w = pack_bf16x2(f[6], f[7]);
+  return u;
+}
+
 template <int EPI>
 __device__ __forceinline__ void epilogue_chunk(const GemmParams& p, int row, int col0, float (&v)[64]) {
   if constexpr (EPI == DH_EPI_BF16) {
@@ -307,6 +317,197 @@ gemm_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant__ CUt
 }
 
 // ------------------------------------------------------------------------------------------------
+// Transposing epilogue of the CTA-pair kernel.  A warp owns 32 accumulator rows (TMEM lanes) and handles 64
+// accumulator columns per unit: row-wise math in registers (one thread = one row: RoPE / SwiGLU pairs live in
+// the same thread), the result staged in a warp-private swizzled shared-memory slab, read back transposed so
+// that every global load/store instruction of the warp touches whole 128-byte lines (4 rows x 128 B or
+// 2 rows x 256 B) instead of 32 different rows.  Element-wise work against another [M, N] tensor (residual
+// add, accumulate, SwiGLU backward against h12) happens on the transposed side with coalesced reads.
+// ------------------------------------------------------------------------------------------------
+constexpr int STG_BYTES = 8192;   // per epilogue warp: 32 rows x 256 B
+
+// 16-byte chunk c of row r in a slab with 128-byte rows (8 chunks) / 256-byte rows (16 chunks): XOR swizzle inside each
+// 128-byte segment keeps both the row-per-lane writes and the transposed reads bank-conflict free.
+__device__ __forceinline__ uint32_t stg_off128(int r, int c) { return (uint32_t)(r * 128 + (((c ^ r) & 7) << 4)); }
+__device__ __forceinline__ uint32_t stg_off256(int r, int c) { return (uint32_t)(r * 256 + ((c & 8) << 4) + (((c ^ r) & 7) << 4)); }
+// 64-byte rows (4 chunks): two rows share a 128-byte bank row
+__device__ __forceinline__ uint32_t stg_off64(int r, int c) { return (uint32_t)(r * 64 + (((c ^ (r >> 1)) & 3) << 4)); }
+
+__device__ __forceinline__ void stage_bf16x64(uint8_t* stg, int lane, const float (&f)[64]) {
+#pragma unroll
+  for (int c = 0; c < 8; ++c) {
+    uint4 u;
+    u.x = pack_bf16x2(f[8 * c + 0], f[8 * c + 1]); u.y = pack_bf16x2(f[8 * c + 2], f[8 * c + 3]);
+    u.z = pack_bf16x2(f[8 * c + 4], f[8 * c + 5]); u.w = pack_bf16x2(f[8 * c + 6], f[8 * c + 7]);
+    *reinterpret_cast<uint4*>(stg + stg_off128(lane, c)) = u;
+  }
+}
+// transposed copy-out of a staged [32 x 64] bf16 slab: 4 rows x 128 B per instruction
+__device__ __forceinline__ void copy_out_bf16x64(const uint8_t* stg, int lane, bf16* out, long long ld, int row0, int col0, int M) {
+  const int rr = lane >> 3, c = lane & 7;
+#pragma unroll
+  for (int i = 0; i < 8; ++i) {
+    const int r = 4 * i + rr;
+    const uint4 u = *reinterpret_cast<const uint4*>(stg + stg_off128(r, c));
+    if (row0 + r < M) *reinterpret_cast<uint4*>(out + (long long)(row0 + r) * ld + col0 + 8 * c) = u;
+  }
+}
+
+struct RopeRegs { uint4 c[4], s[4]; };   // cos/sin[pos][0..32) as packed bf16 (table halves are identical)
+
+template <int EPI>
+__device__ __forceinline__ void epi_unit(const GemmParams& p, uint8_t* stg, int lane, int row0, int col0, float (&v)[64],
+                                         const RopeRegs& rope) {
+  const int M = p.M;
+  if constexpr (EPI == DH_EPI_BF16) {
+#pragma unroll
+    for (int j = 0; j < 64; ++j) v[j] *= p.alpha;
+    if (p.col_bias) {
+#pragma unroll
+      for (int j = 0; j < 64; ++j) v[j] = bf16_round(v[j]) + __ldg(p.col_bias + col0 + j);
+    }
+    if (p.col_scale) {
+#pragma unroll
+      for (int j = 0; j < 64; ++j) v[j] *= __ldg(p.col_scale + col0 + j);
+    }
+    stage_bf16x64(stg, lane, v);
+    __syncwarp();
+    copy_out_bf16x64(stg, lane, reinterpret_cast<bf16*>(p.out), p.ldo, row0, col0, M);
+  } else if constexpr (EPI == DH_EPI_F32) {
+#pragma unroll
+    for (int c = 0; c < 16; ++c)
+      *reinterpret_cast<float4*>(stg + stg_off256(lane, c)) =
+          make_float4(v[4 * c] * p.alpha, v[4 * c + 1] * p.alpha, v[4 * c + 2] * p.alpha, v[4 * c + 3] * p.alpha);
+    __syncwarp();
+    const int rr = lane >> 4, c = lane & 15;
+#pragma unroll
+    for (int i = 0; i < 16; ++i) {
+      const int r = 2 * i + rr;
+      float4 a = *reinterpret_cast<const float4*>(stg + stg_off256(r, c));
+      if (row0 + r < M) {
+        float4* o = reinterpret_cast<float4*>(reinterpret_cast<float*>(p.out) + (long long)(row0 + r) * p.ldo + col0 + 4 * c);
+        if (p.accumulate) {
+          const float4 old = *o;
+          a.x += old.x; a.y += old.y; a.z += old.z; a.w += old.w;
+        }
+        *o = a;
+      }
+    }
+  } else if constexpr (EPI == DH_EPI_RESID_F32) {
+    stage_bf16x64(stg, lane, v);   // bf16(acc) is what the reference adds to the fp32 stream
+    __syncwarp();
+    const int rr = lane >> 4, c = lane & 15;   // output chunk c = 4 floats = 8 staged bytes
+#pragma unroll
+    for (int i = 0; i < 16; ++i) {
+      const int r = 2 * i + rr;
+      const uint2 u = *reinterpret_cast<const uint2*>(stg + stg_off128(r, c >> 1) + ((c & 1) << 3));
+      if (row0 + r < M) {
+        const long long off = (long long)(row0 + r);
+        float4 a = *reinterpret_cast<const float4*>(reinterpret_cast<const float*>(p.aux) + off * p.ldaux + col0 + 4 * c);
+        const float2 lo = unpack_bf16x2(u.x), hi = unpack_bf16x2(u.y);
+        a.x += lo.x; a.y += lo.y; a.z += hi.x; a.w += hi.y;
+        *reinterpret_cast<float4*>(reinterpret_cast<float*>(p.out) + off * p.ldo + col0 + 4 * c) = a;
+      }
+    }
+  } else if constexpr (EPI == DH_EPI_RESID_BF16) {
+    stage_bf16x64(stg, lane, v);
+    __syncwarp();
+    const int rr = lane >> 3, c = lane & 7;
+#pragma unroll
+    for (int i = 0; i < 8; ++i) {
+      const int r = 4 * i + rr;
+      const uint4 u = *reinterpret_cast<const uint4*>(stg + stg_off128(r, c));
+      if (row0 + r < M) {
+        const long long off = (long long)(row0 + r);
+        const uint4 x = *reinterpret_cast<const uint4*>(reinterpret_cast<const bf16*>(p.aux) + off * p.ldaux + col0 + 8 * c);
+        const float2 a0 = unpack_bf16x2(u.x), a1 = unpack_bf16x2(u.y), a2 = unpack_bf16x2(u.z), a3 = unpack_bf16x2(u.w);
+        const float2 x0 = unpack_bf16x2(x.x), x1 = unpack_bf16x2(x.y), x2 = unpack_bf16x2(x.z), x3 = unpack_bf16x2(x.w);
+        uint4 o;
+        o.x = pack_bf16x2(x0.x + a0.x, x0.y + a0.y); o.y = pack_bf16x2(x1.x + a1.x, x1.y + a1.y);
+        o.z = pack_bf16x2(x2.x + a2.x, x2.y + a2.y); o.w = pack_bf16x2(x3.x + a3.x, x3.y + a3.y);
+        *reinterpret_cast<uint4*>(reinterpret_cast<bf16*>(p.out) + off * p.ldo + col0 + 8 * c) = o;
+      }
+    }
+  } else if constexpr (EPI == DH_EPI_QKV_ROPE) {
+    const int slot = (col0 >> 6) % (p.q_per_kv + 2);
+    if (slot <= p.q_per_kv) {   // q heads and the k head rotate; v passes through
+#pragma unroll
+      for (int i = 0; i < 4; ++i) {
+        const uint32_t cw[4] = {rope.c[i].x, rope.c[i].y, rope.c[i].z, rope.c[i].w};
+        const uint32_t sw[4] = {rope.s[i].x, rope.s[i].y, rope.s[i].z, rope.s[i].w};
+#pragma unroll
+        for (int k = 0; k < 4; ++k) {
+          const float2 cc = unpack_bf16x2(cw[k]), ss = unpack_bf16x2(sw[k]);
+          const int j = 8 * i + 2 * k;
+          const float a0 = bf16_round(v[j]), b0 = bf16_round(v[j + 32]);
+          const float a1 = bf16_round(v[j + 1]), b1 = bf16_round(v[j + 33]);
+          v[j] = a0 * cc.x - b0 * ss.x;      v[j + 32] = b0 * cc.x + a0 * ss.x;
+          v[j + 1] = a1 * cc.y - b1 * ss.y;  v[j + 33] = b1 * cc.y + a1 * ss.y;
+        }
+      }
+    }
+    stage_bf16x64(stg, lane, v);
+    __syncwarp();
+    copy_out_bf16x64(stg, lane, reinterpret_cast<bf16*>(p.out), p.ldo, row0, col0, M);
+  } else if constexpr (EPI == DH_EPI_SWIGLU) {
+    // raw h12 (64 cols) in the first 4 KB of the slab, act = silu(h1) * h2 (32 cols, 64-byte rows) in the next 2 KB
+    uint8_t* stg2 = stg + 4096;
+    if (p.out) stage_bf16x64(stg, lane, v);
+#pragma unroll
+    for (int c = 0; c < 4; ++c) {
+      float a[8];
+#pragma unroll
+      for (int k = 0; k < 8; ++k) {
+        const float h1 = bf16_round(v[8 * c + k]), h2 = bf16_round(v[8 * c + k + 32]);
+        a[k] = (h1 / (1.f + __expf(-h1))) * h2;
+      }
+      uint4 u;
+      u.x = pack_bf16x2(a[0], a[1]); u.y = pack_bf16x2(a[2], a[3]); u.z = pack_bf16x2(a[4], a[5]); u.w = pack_bf16x2(a[6], a[7]);
+      *reinterpret_cast<uint4*>(stg2 + stg_off64(lane, c)) = u;
+    }
+    __syncwarp();
+    if (p.out) copy_out_bf16x64(stg, lane, reinterpret_cast<bf16*>(p.out), p.ldo, row0, col0, M);
+    const int rr = lane >> 2, c = lane & 3;
+#pragma unroll
+    for (int i = 0; i < 4; ++i) {
+      const int r = 8 * i + rr;
+      const uint4 u = *reinterpret_cast<const uint4*>(stg2 + stg_off64(r, c));
+      if (row0 + r < M) *reinterpret_cast<uint4*>(reinterpret_cast<bf16*>(p.out2) + (long long)(row0 + r) * p.ldo2 + (col0 >> 1) + 8 * c) = u;
+    }
+  } else if constexpr (EPI == DH_EPI_SWIGLU_BWD) {
+    // acc = d(act) columns col0..col0+63; h12 / d(h12) columns 2*col0 .. 2*col0+127 as two [h1 x32 | h2 x32] blocks
+    stage_bf16x64(stg, lane, v);
+    __syncwarp();
+    const int rr = lane >> 3, t = lane & 7, g = t >> 2, cc = t & 3;
+#pragma unroll
+    for (int i = 0; i < 8; ++i) {
+      const int r = 4 * i + rr;
+      const uint4 du = *reinterpret_cast<const uint4*>(stg + stg_off128(r, g * 4 + cc));
+      if (row0 + r < M) {
+        const long long off = (long long)(row0 + r);
+        const bf16* h = reinterpret_cast<const bf16*>(p.aux) + off * p.ldaux + 2 * col0 + 64 * g + 8 * cc;
+        bf16* o = reinterpret_cast<bf16*>(p.out) + off * p.ldo + 2 * col0 + 64 * g + 8 * cc;
+        const uint4 h1u = *reinterpret_cast<const uint4*>(h);
+        const uint4 h2u = *reinterpret_cast<const uint4*>(h + 32);
+        float da[8], h1[8], h2[8], d1[8], d2[8];
+        unpack_bf16x8(du, da);
+        unpack_bf16x8(h1u, h1);
+        unpack_bf16x8(h2u, h2);
+#pragma unroll
+        for (int k = 0; k < 8; ++k) {
+          const float sig = 1.f / (1.f + __expf(-h1[k]));
+          d1[k] = da[k] * h2[k] * (sig * (1.f + h1[k] * (1.f - sig)));
+          d2[k] = da[k] * (h1[k] * sig);
+        }
+        *reinterpret_cast<uint4*>(o) = pack_bf16x8(d1);
+        *reinterpret_cast<uint4*>(o + 32) = pack_bf16x8(d2);
+      }
+    }
+  }
+  __syncwarp();   // the slab is rewritten by the next unit
+}
+
+// ------------------------------------------------------------------------------------------------
 // CTA-pair kernel (cluster of 2, tcgen05 cta_group::2): one 256 x 256 output tile per pair.  CTA r of the
 // pair stages A rows [128 r, 128 r + 128) and B rows (= output columns) [128 r, 128 r + 128) of the tile
 // and owns accumulator rows [128 r, +128) x 256 columns in its own TMEM; the leader's MMA thread drives
@@ -319,7 +520,7 @@ struct PairCfg {
   static constexpr int B_BYTES = 128 * BK * 2;
   static constexpr int STAGE_BYTES = A_BYTES + B_BYTES;
   static constexpr int STAGES = 6;
-  static constexpr int SMEM_BYTES = STAGES * STAGE_BYTES + 1024 + 256;
+  static constexpr int SMEM_BYTES = STAGES * STAGE_BYTES + 4 * STG_BYTES + 1024 + 256;
 };
 
 template <int EPI>
@@ -331,7 +532,8 @@ gemm_pair_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant_
   constexpr int BN = Cfg::BN;
   extern __shared__ uint8_t smem_raw[];
   uint8_t* smem = reinterpret_cast<uint8_t*>((reinterpret_cast<uintptr_t>(smem_raw) + 1023) & ~uintptr_t(1023));
-  uint64_t* bars = reinterpret_cast<uint64_t*>(smem + STAGES * Cfg::STAGE_BYTES);
+  uint8_t* stg_base = smem + STAGES * Cfg::STAGE_BYTES;   // 4 epilogue warps x 8 KB
+  uint64_t* bars = reinterpret_cast<uint64_t*>(stg_base + 4 * STG_BYTES);
   uint64_t* full_bar = bars;                     // [STAGES]  TMA (both CTAs) -> MMA       (leader's copy is used)
   uint64_t* empty_bar = bars + STAGES;           // [STAGES]  MMA -> TMA                   (multicast to both)
   uint64_t* tfull_bar = bars + 2 * STAGES;       // [2]       MMA -> epilogue              (multicast to both)
@@ -417,22 +619,33 @@ gemm_pair_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant_
       const int n0 = (tile / p.tiles_m) * BN;
       mbar_wait(&tfull_bar[acc], (tcount >> 1) & 1);
       tc_fence_after();
-      const int row = m0 + q * 32 + lane;
+      const int row0 = m0 + q * 32;
       const uint32_t taddr = tmem_base + ((uint32_t)(q * 32) << 16) + acc * BN;
+      RopeRegs rope;
+      if constexpr (EPI == DH_EPI_QKV_ROPE) {
+        const int row = row0 + lane < p.M ? row0 + lane : p.M - 1;
+        const int pos = p.positions ? __ldg(p.positions + row) : (row % p.seq_len);
+        const uint4* c4 = reinterpret_cast<const uint4*>(p.rope_cos + (long long)pos * 64);
+        const uint4* s4 = reinterpret_cast<const uint4*>(p.rope_sin + (long long)pos * 64);
+#pragma unroll
+        for (int i = 0; i < 4; ++i) { rope.c[i] = __ldg(c4 + i); rope.s[i] = __ldg(s4 + i); }
+      }
 #pragma unroll 1
       for (int c = 0; c < BN / 64; ++c) {
         uint32_t r0[32], r1[32];
         tmem_ld32(taddr + c * 64, r0);
         tmem_ld32(taddr + c * 64 + 32, r1);
         tmem_wait_ld();
+        if (c == BN / 64 - 1) {   // accumulator fully read: hand the TMEM buffer back before the last unit's stores
+          tc_fence_before();
+          __syncwarp();
+          if (lane == 0) mbar_arrive_cluster(mapa_shared(smem_u32(&tempty_bar[acc]), 0));
+        }
         float v[64];
 #pragma unroll
         for (int j = 0; j < 32; ++j) { v[j] = __uint_as_float(r0[j]); v[j + 32] = __uint_as_float(r1[j]); }
-        if (row < p.M) epilogue_chunk<EPI>(p, row, n0 + c * 64, v);
+        epi_unit<EPI>(p, stg_base + q * STG_BYTES, lane, row0, n0 + c * 64, v, rope);
       }
-      tc_fence_before();
-      __syncwarp();
-      if (lane == 0) mbar_arrive_cluster(mapa_shared(smem_u32(&tempty_bar[acc]), 0));
     }
   }
 

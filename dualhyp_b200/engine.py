@@ -9,8 +9,10 @@ Per layer, forward (M = B*T token rows):
     rmsnorm -> [LoRA a = n A^T] -> QKV GEMM (+LoRA K-extension, RoPE epilogue, interleaved row kept as is)
     -> [prefix K/V GEMM] -> flash attention (+gated prefix) -> proj GEMM (+LoRA, residual epilogue, fp32 stream)
     -> rmsnorm -> fc_1|fc_2 GEMM (SwiGLU epilogue) -> proj GEMM (residual epilogue)
-Backward is dgrad only for the frozen weights (the forward weight, as stored, is the MN-major B operand:
-no transposed copies), plus the small LoRA / adapter wgrads.
+Backward is dgrad only for the frozen weights, plus the small LoRA / adapter wgrads.  Every frozen weight is
+kept twice in HBM, as stored ([out, in]: the K-major B operand of the forward GEMM) and transposed ([in, out]:
+the K-major B operand of its dgrad), so that both directions run on the CTA-pair tcgen05 kernel; the extra
+2.1 GB is nothing against 180 GB and the copies are made once at load time.
 """
 from __future__ import annotations
 
@@ -100,6 +102,7 @@ class DecoderEngine:
         self.wte: Optional[Tensor] = None
         self.ln_f: Optional[Tensor] = None
         self.lm_w: Optional[Tensor] = None
+        self.lm_w_t: Optional[Tensor] = None
         self.lm_scale: Optional[Tensor] = None
         self.lm_bias: Optional[Tensor] = None
         self._bufs: Dict = {}
@@ -127,10 +130,14 @@ class DecoderEngine:
         self.layers = []
         for i in range(s.n_layer):
             p = f"transformer.h.{i}."
-            self.layers.append(dict(
+            lw = dict(
                 norm1=f32(p + "norm_1.weight"), norm2=f32(p + "norm_2.weight"),
                 wqkv=bf(p + "attn.attn" + lk), wproj=bf(p + "attn.proj" + lk),
-                w12=interleave_fc(bf(p + "mlp.fc_1" + lk), bf(p + "mlp.fc_2" + lk)), wmlp=bf(p + "mlp.proj" + lk)))
+                w12=interleave_fc(bf(p + "mlp.fc_1" + lk), bf(p + "mlp.fc_2" + lk)), wmlp=bf(p + "mlp.proj" + lk))
+            if i >= s.first_trainable_layer:      # dgrad operands ([in, out] row-major)
+                for k in ("wqkv", "wproj", "w12", "wmlp"):
+                    lw[k + "_t"] = lw[k].t().contiguous()
+            self.layers.append(lw)
         self.wte = sd["transformer.wte.weight"].detach().to(dev).contiguous()
         if self.wte.dtype not in (torch.float32, torch.bfloat16):
             self.wte = self.wte.float()
@@ -144,6 +151,7 @@ class DecoderEngine:
         else:
             self.lm_w = bf("lm_head.weight")
             self.lm_scale = self.lm_bias = None
+        self.lm_w_t = self.lm_w.t().contiguous() if s.first_trainable_layer < s.n_layer else None
 
     def pack_trainable(self, tr: Dict[str, Tensor]) -> Dict[int, Dict[str, Tensor]]:
         """Per-step bf16 forms of the small trainable tensors (reference-keyed, fp32 masters)."""
@@ -168,6 +176,7 @@ class DecoderEngine:
                     b_ext[C:C + kv, r:2 * r] = Bm[C:C + kv].to(torch.bfloat16)      # k rows use [:, r:2r]
                     b_ext[C + kv:, 2 * r:3 * r] = Bm[C + kv:].to(torch.bfloat16)    # v rows use [:, 2r:3r]
                     d["qkv_a"], d["qkv_b"] = a_pad, b_ext
+                    d["qkv_a_t"], d["qkv_b_t"] = a_pad.t().contiguous(), b_ext.t().contiguous()
                 if s.lora_proj:
                     A, Bm = tr[p + "proj.lora_A"].detach().to(dev), tr[p + "proj.lora_B"].detach().to(dev)
                     a_pad = torch.zeros((LORA_PAD, C), device=dev, dtype=torch.bfloat16)
@@ -175,6 +184,7 @@ class DecoderEngine:
                     b_ext = torch.zeros((C, LORA_PAD), device=dev, dtype=torch.bfloat16)
                     b_ext[:, :r] = Bm.to(torch.bfloat16)
                     d["proj_a"], d["proj_b"] = a_pad, b_ext
+                    d["proj_a_t"], d["proj_b_t"] = a_pad.t().contiguous(), b_ext.t().contiguous()
             if d:
                 packed[i] = d
         return packed
@@ -276,12 +286,12 @@ class DecoderEngine:
     # backward: d(hidden) -> gradients of the trainable tensors (reference-keyed, fp32)
     # ------------------------------------------------------------------------------------------
     def lm_head_backward(self, dlogits: Tensor) -> Tensor:
-        """d(hidden) bf16 [M, C] = dlogits [M, V] @ W [V, C]   (W as stored is the MN-major B operand)."""
+        """d(hidden) bf16 [M, C] = dlogits [M, V] @ W [V, C]   (W^T [C, V] is the K-major B operand)."""
         M = dlogits.shape[0]
         d_hidden = self._buf("d_hidden", (M, self.spec.n_embd), torch.bfloat16)
         if self.lm_scale is not None:
             raise NotImplementedError("training through a non-trivial adapter_scale is not supported (it is frozen at 1)")
-        ops.gemm(dlogits, self.lm_w, d_hidden, b_layout=1)
+        ops.gemm(dlogits, self.lm_w_t, d_hidden)
         return d_hidden
 
     def backward(self, d_hidden: Tensor, step_id: Optional[int] = None) -> Dict[str, Tensor]:
@@ -312,22 +322,22 @@ class DecoderEngine:
             lw, a, pk = self.layers[i], sv["layers"][i], packed.get(i, {})
             p = f"transformer.h.{i}.attn."
             # ---- MLP: d(act) = dx Wp ; SwiGLU backward in the epilogue ; d(n2) = d(h12) W12 ----
-            ops.gemm(dxb, lw["wmlp"], dh12, b_layout=1, epilogue=ops.EPI_SWIGLU_BWD, aux=a["h12"])
-            ops.gemm(dh12, lw["w12"], dn, b_layout=1)
+            ops.gemm(dxb, lw["wmlp_t"], dh12, epilogue=ops.EPI_SWIGLU_BWD, aux=a["h12"])
+            ops.gemm(dh12, lw["w12_t"], dn)
             ops.rmsnorm_bwd(a["xmid"], lw["norm2"], a["rstd2"], dn, dx, dx, dxb)
             # ---- attention output projection ----
             if "proj_a" in pk:
                 dap = self._buf("dap", (M, LORA_PAD), bf)
-                ops.gemm(dxb, pk["proj_b"], dap, b_layout=1)
+                ops.gemm(dxb, pk["proj_b_t"], dap)
                 db = torch.empty((C, LORA_PAD), device=self.device, dtype=f32)
                 ops.gemm(dxb, a["ap_s"], db, a_layout=1, b_layout=1, epilogue=ops.EPI_F32)
                 da = torch.empty((LORA_PAD, C), device=self.device, dtype=f32)
                 ops.gemm(dap, a["y"], da, a_layout=1, b_layout=1, epilogue=ops.EPI_F32, alpha=scaling)
                 grads[p + "proj.lora_A"] = da[: s.r]
                 grads[p + "proj.lora_B"] = db[:, : s.r]
-                ops.gemm(dxb, lw["wproj"], dy, b_layout=1, A2=dap, B2=pk["proj_a"], b2_layout=1)
+                ops.gemm(dxb, lw["wproj_t"], dy, A2=dap, B2=pk["proj_a_t"])
             else:
-                ops.gemm(dxb, lw["wproj"], dy, b_layout=1)
+                ops.gemm(dxb, lw["wproj_t"], dy)
             # ---- attention ----
             need_dqkv = not (s.variant == "adapter" and i == first)
             d_pkv = d_gate = None
@@ -349,7 +359,7 @@ class DecoderEngine:
             # ---- QKV projection ----
             if "qkv_a" in pk:
                 da_s = self._buf("da_s", (M, LORA_PAD), bf)
-                ops.gemm(dqkv, pk["qkv_b"], da_s, b_layout=1)
+                ops.gemm(dqkv, pk["qkv_b_t"], da_s)
                 db = torch.empty((s.qkv_out, LORA_PAD), device=self.device, dtype=f32)
                 ops.gemm(dqkv, a["a_s"], db, a_layout=1, b_layout=1, epilogue=ops.EPI_F32)
                 da = torch.empty((LORA_PAD, C), device=self.device, dtype=f32)
@@ -358,9 +368,9 @@ class DecoderEngine:
                 grads[p + "attn.lora_A"] = da[: 3 * r]
                 grads[p + "attn.lora_B"] = torch.cat((db[:C, 0:r], db[C:C + kv, r:2 * r], db[C + kv:, 2 * r:3 * r]), dim=0)
                 if i > first:
-                    ops.gemm(dqkv, lw["wqkv"], dn, b_layout=1, A2=da_s, B2=pk["qkv_a"], b2_layout=1)
+                    ops.gemm(dqkv, lw["wqkv_t"], dn, A2=da_s, B2=pk["qkv_a_t"])
             elif i > first:
-                ops.gemm(dqkv, lw["wqkv"], dn, b_layout=1)
+                ops.gemm(dqkv, lw["wqkv_t"], dn)
             if i > first:
                 ops.rmsnorm_bwd(a["x"], lw["norm1"], a["rstd1"], dn, dx, dx, dxb)
         return grads

@@ -41,6 +41,40 @@ def gemm_case(M, N, K, b_layout=0, name=""):
                       "tflops": round(fl / t / 1e9, 1), "cublas_ms": round(tc, 4), "cublas_tflops": round(fl / tc / 1e9, 1)}), flush=True)
 
 
+def gemm_epilogue_cases(M, C=2048, I=5632, G=4, qpk=8):
+    """The decoder's GEMMs with their real fused epilogues (what the training step launches)."""
+    bf = torch.bfloat16
+    n = torch.randn(M, C, device=DEV, dtype=bf)
+    x32 = torch.randn(M, C, device=DEV)
+    out32 = torch.empty(M, C, device=DEV)
+    cos = torch.randn(2048, 64, device=DEV, dtype=bf)
+    NQ = G * (qpk + 2) * 64
+    wqkv = torch.randn(NQ, C, device=DEV, dtype=bf) * 0.02
+    qkv = torch.empty(M, NQ, device=DEV, dtype=bf)
+    w12 = torch.randn(2 * I, C, device=DEV, dtype=bf) * 0.02
+    h12 = torch.empty(M, 2 * I, device=DEV, dtype=bf)
+    act = torch.empty(M, I, device=DEV, dtype=bf)
+    wmlp = torch.randn(C, I, device=DEV, dtype=bf) * 0.02
+    wmlp_t = wmlp.t().contiguous()
+    w12_t = w12.t().contiguous()
+    wproj = torch.randn(C, C, device=DEV, dtype=bf) * 0.02
+    dh12 = torch.empty(M, 2 * I, device=DEV, dtype=bf)
+    dn = torch.empty(M, C, device=DEV, dtype=bf)
+    cases = [
+        ("qkv+rope", NQ, C, lambda: ops.gemm(n, wqkv, qkv, epilogue=ops.EPI_QKV_ROPE, rope_cos=cos, rope_sin=cos, seq_len=512, q_per_kv=qpk)),
+        ("proj+resid_f32", C, C, lambda: ops.gemm(n, wproj, out32, epilogue=ops.EPI_RESID_F32, aux=x32)),
+        ("fc12+swiglu", 2 * I, C, lambda: ops.gemm(n, w12, h12, epilogue=ops.EPI_SWIGLU, out2=act)),
+        ("fc12+swiglu(no h12)", 2 * I, C, lambda: ops.gemm(n, w12, None, epilogue=ops.EPI_SWIGLU, out2=act)),
+        ("mlp_proj+resid_f32", C, I, lambda: ops.gemm(act, wmlp, out32, epilogue=ops.EPI_RESID_F32, aux=x32)),
+        ("d_act+swiglu_bwd", I, C, lambda: ops.gemm(n, wmlp_t, dh12, epilogue=ops.EPI_SWIGLU_BWD, aux=h12)),
+        ("d_n2", C, 2 * I, lambda: ops.gemm(dh12, w12_t, dn)),
+    ]
+    for name, N, K, fn in cases:
+        t = timeit(fn)
+        fl = 2.0 * M * N * K
+        print(json.dumps({"kernel": "gemm+epi", "name": name, "M": M, "N": N, "K": K, "ms": round(t, 4), "tflops": round(fl / t / 1e9, 1)}), flush=True)
+
+
 def attn_case(B, T, G=4, qpk=8):
     N, H = G * (qpk + 2) * 64, G * qpk
     qkv = torch.randn(B * T, N, device=DEV, dtype=torch.bfloat16)
@@ -96,5 +130,6 @@ if __name__ == "__main__":
                            ("lm_head", 32000, 2048, 0), ("d_act", 5632, 2048, 1), ("d_n2", 2048, 11264, 1), ("d_n1", 2048, 2560, 1),
                            ("d_hidden", 2048, 32000, 1)]:
         gemm_case(M, N, K, bl, name)
+    gemm_epilogue_cases(M)
     attn_case(M // 512, 512)
     leaf_cases(M)

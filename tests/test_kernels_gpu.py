@@ -152,6 +152,86 @@ def test_gemm_swiglu_fwd_bwd():
     assert rel(g[:, :, 1].reshape(M, I), rdh2) < 8e-3, report("dh2", g[:, :, 1].reshape(M, I), rdh2)
 
 
+@pytest.mark.parametrize("M", [1024, 1100, 2304])
+def test_gemm_pair_kernel_epilogues(M):
+    """Every fused epilogue at shapes that dispatch to the CTA-pair kernel (M >= 1024, N % 256 == 0, K-major operands),
+    including a ragged last row tile; same references as the small-shape tests above."""
+    N, K = 512, 320
+    A, B = rnd((M, K), 40), rnd((N, K), 41, bound=0.25)
+    acc = A.float() @ B.float().t()
+    # bf16 out with column bias / scale (AdapterV2Linear form)
+    scale, bias = rnd((N,), 42, dtype=torch.float32) + 1.5, rnd((N,), 43, dtype=torch.float32)
+    o = torch.full((M, N), float("nan"), device=DEV, dtype=torch.bfloat16)
+    ops.gemm(A, B, o, col_scale=scale, col_bias=bias)
+    assert rel(o, scale * (acc + bias)) < 6e-3, report("pair bf16+colscale", o, scale * (acc + bias))
+    # fp32 out, accumulate
+    o32 = torch.ones((M, N), device=DEV, dtype=torch.float32)
+    ops.gemm(A, B, o32, epilogue=ops.EPI_F32, alpha=0.5, accumulate=True)
+    assert rel(o32, 1.0 + 0.5 * acc) < 1e-4, report("pair f32 acc", o32, 1.0 + 0.5 * acc)
+    # residual add into the fp32 stream / bf16 stream
+    res = rnd((M, N), 44, dtype=torch.float32)
+    ops.gemm(A, B, o32, epilogue=ops.EPI_RESID_F32, aux=res)
+    assert rel(o32, res + acc.bfloat16().float()) < 1e-3, report("pair resid f32", o32, res + acc.bfloat16().float())
+    resb = res.bfloat16()
+    ops.gemm(A, B, o, epilogue=ops.EPI_RESID_BF16, aux=resb)
+    assert rel(o, resb.float() + acc.bfloat16().float()) < 6e-3, report("pair resid bf16", o, resb.float() + acc)
+    # dual source (LoRA K extension)
+    A2, B2 = rnd((M, 64), 45), rnd((N, 64), 46)
+    ops.gemm(A, B, o, A2=A2, B2=B2)
+    assert rel(o, acc + A2.float() @ B2.float().t()) < 4e-3, report("pair dual", o, acc + A2.float() @ B2.float().t())
+    torch.cuda.synchronize()
+
+
+def test_gemm_pair_kernel_rope_and_swiglu():
+    B_, T, G, qpk, C = 3, 400, 2, 2, 256          # M = 1200 (ragged), N = 512
+    cfg = O.OracleConfig(n_head=G * qpk, n_query_groups=G, n_embd=C, block_size=512)
+    M = B_ * T
+    x, W = rnd((M, C), 47), rnd((cfg.qkv_out, C), 48, bound=1 / 16)
+    assert cfg.qkv_out % 256 == 0
+    cos, sin = O.build_rope_cache(512, 64)
+    out = torch.full((M, cfg.qkv_out), float("nan"), device=DEV, dtype=torch.bfloat16)
+    ops.gemm(x, W, out, epilogue=ops.EPI_QKV_ROPE, rope_cos=cos.to(DEV), rope_sin=sin.to(DEV), seq_len=T, q_per_kv=qpk)
+    torch.cuda.synchronize()
+    qkv = (x.float() @ W.float().t()).cpu().view(B_, T, -1)
+    q, k, v = O.split_qkv(qkv, cfg)
+    q, k = O.apply_rope(q, cos[:T], sin[:T]), O.apply_rope(k, cos[:T], sin[:T])
+    got = out.float().cpu().view(B_, T, G, qpk + 2, 64)
+    gq = got[:, :, :, :qpk].permute(0, 2, 3, 1, 4).reshape(B_, G * qpk, T, 64)
+    assert rel(gq, q) < 6e-3, report("pair rope q", gq, q)
+    assert rel(got[:, :, :, qpk].permute(0, 2, 1, 3), k[:, ::qpk]) < 6e-3
+    assert rel(got[:, :, :, qpk + 1].permute(0, 2, 1, 3), v[:, ::qpk]) < 6e-3
+    # explicit positions (decode form) give the same rotation
+    out2 = torch.empty_like(out)
+    pos = torch.arange(T, device=DEV, dtype=torch.int32).repeat(B_)
+    ops.gemm(x, W, out2, epilogue=ops.EPI_QKV_ROPE, rope_cos=cos.to(DEV), rope_sin=sin.to(DEV), positions=pos, seq_len=1, q_per_kv=qpk)
+    assert torch.equal(out, out2)
+    # SwiGLU forward + backward epilogues
+    I = 256
+    W1, W2 = rnd((I, C), 49, bound=0.2), rnd((I, C), 50, bound=0.2)
+    W12 = _interleave(W1, W2).contiguous()
+    h12 = torch.empty((M, 2 * I), device=DEV, dtype=torch.bfloat16)
+    act = torch.empty((M, I), device=DEV, dtype=torch.bfloat16)
+    ops.gemm(x, W12, h12, epilogue=ops.EPI_SWIGLU, out2=act)
+    h1, h2 = x.float() @ W1.float().t(), x.float() @ W2.float().t()
+    assert rel(act, F.silu(h1) * h2) < 8e-3, report("pair swiglu act", act, F.silu(h1) * h2)
+    act2 = torch.empty_like(act)
+    ops.gemm(x, W12, None, epilogue=ops.EPI_SWIGLU, out2=act2)      # inference form: h12 not kept
+    assert torch.equal(act, act2)
+    h12v = h12.float().view(M, I // 32, 2, 32)
+    h1b, h2b = h12v[:, :, 0].reshape(M, I), h12v[:, :, 1].reshape(M, I)
+    assert rel(h1b, h1) < 4e-3 and rel(h2b, h2) < 4e-3
+    Cout = 128
+    dy, WpT = rnd((M, Cout), 51), rnd((I, Cout), 52, bound=0.2)      # transposed proj weight: K-major B of the dgrad
+    dh12 = torch.empty((M, 2 * I), device=DEV, dtype=torch.bfloat16)
+    ops.gemm(dy, WpT, dh12, epilogue=ops.EPI_SWIGLU_BWD, aux=h12)
+    torch.cuda.synchronize()
+    dact = (dy.float() @ WpT.float().t()).bfloat16().float()
+    sig = torch.sigmoid(h1b)
+    g = dh12.float().view(M, I // 32, 2, 32)
+    assert rel(g[:, :, 0].reshape(M, I), dact * h2b * (sig * (1 + h1b * (1 - sig)))) < 8e-3
+    assert rel(g[:, :, 1].reshape(M, I), dact * (h1b * sig)) < 8e-3
+
+
 # ----------------------------------------------------------------------------------------------
 # leaf ops
 # ----------------------------------------------------------------------------------------------
