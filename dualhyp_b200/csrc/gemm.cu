@@ -317,48 +317,109 @@ gemm_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant__ CUt
 }
 
 // ------------------------------------------------------------------------------------------------
-// Transposing epilogue of the CTA-pair kernel.  A warp owns 32 accumulator rows (TMEM lanes) and handles 64
-// accumulator columns per unit: row-wise math in registers (one thread = one row: RoPE / SwiGLU pairs live in
-// the same thread), the result staged in a warp-private swizzled shared-memory slab, read back transposed so
-// that every global load/store instruction of the warp touches whole 128-byte lines (4 rows x 128 B or
-// 2 rows x 256 B) instead of 32 different rows.  Element-wise work against another [M, N] tensor (residual
-// add, accumulate, SwiGLU backward against h12) happens on the transposed side with coalesced reads.
+// Epilogue of the CTA-pair kernel: all global traffic is TMA.  An epilogue warp owns 32 accumulator rows (TMEM
+// lanes; thread = row) and works in units of 64 accumulator columns.  Per unit it has an 8 KB shared-memory
+// tile pair laid out exactly as the tensor maps' boxes (128-byte rows, 128B swizzle => row-per-lane accesses
+// are bank-conflict free): tensors that are read (residual stream, h12 for the SwiGLU backward, the fp32
+// output when accumulating) are prefetched one unit ahead by cp.async.bulk.tensor loads, combined with the
+// accumulator row in place, and written back by a bulk tensor store.  No thread issues a global ld/st, ragged
+// M is clipped by the tensor map, and the tile buffers are double buffered so loads, math and stores overlap.
 // ------------------------------------------------------------------------------------------------
-constexpr int STG_BYTES = 8192;   // per epilogue warp: 32 rows x 256 B
+constexpr int EPI_BOX_BYTES = 4096;                // one box: 32 rows x 128 B
+constexpr int EPI_WARP_BYTES = 2 * EPI_BOX_BYTES;  // two boxes per epilogue warp
+constexpr int PAIR_EPI_WARPS = 8;                  // two warps per TMEM lane quadrant
+constexpr int PAIR_THREADS = 128 + 32 * PAIR_EPI_WARPS;
 
-// 16-byte chunk c of row r in a slab with 128-byte rows (8 chunks) / 256-byte rows (16 chunks): XOR swizzle inside each
-// 128-byte segment keeps both the row-per-lane writes and the transposed reads bank-conflict free.
-__device__ __forceinline__ uint32_t stg_off128(int r, int c) { return (uint32_t)(r * 128 + (((c ^ r) & 7) << 4)); }
-__device__ __forceinline__ uint32_t stg_off256(int r, int c) { return (uint32_t)(r * 256 + ((c & 8) << 4) + (((c ^ r) & 7) << 4)); }
-// 64-byte rows (4 chunks): two rows share a 128-byte bank row
-__device__ __forceinline__ uint32_t stg_off64(int r, int c) { return (uint32_t)(r * 64 + (((c ^ (r >> 1)) & 3) << 4)); }
+__device__ __forceinline__ void tma_store_2d(const CUtensorMap* m, uint32_t src_smem, int c0, int c1) {
+  asm volatile("cp.async.bulk.tensor.2d.global.shared::cta.bulk_group [%0, {%2, %3}], [%1];" ::"l"(m), "r"(src_smem), "r"(c0),
+               "r"(c1)
+               : "memory");
+}
+__device__ __forceinline__ void tma_load_2d_s(uint32_t dst_smem, const CUtensorMap* m, int c0, int c1, uint64_t* bar) {
+  asm volatile("cp.async.bulk.tensor.2d.shared::cluster.global.mbarrier::complete_tx::bytes [%0], [%1, {%3, %4}], [%2];" ::"r"(dst_smem),
+               "l"(m), "r"(smem_u32(bar)), "r"(c0), "r"(c1)
+               : "memory");
+}
+__device__ __forceinline__ void tma_store_commit() { asm volatile("cp.async.bulk.commit_group;" ::: "memory"); }
+template <int N> __device__ __forceinline__ void tma_store_wait_read() {
+  asm volatile("cp.async.bulk.wait_group.read %0;" ::"n"(N) : "memory");
+}
+__device__ __forceinline__ void tma_store_wait_all() { asm volatile("cp.async.bulk.wait_group 0;" ::: "memory"); }
 
-__device__ __forceinline__ void stage_bf16x64(uint8_t* stg, int lane, const float (&f)[64]) {
+__device__ __forceinline__ uint4 lds128(uint32_t addr) {
+  uint4 u;
+  asm volatile("ld.shared.v4.b32 {%0, %1, %2, %3}, [%4];" : "=r"(u.x), "=r"(u.y), "=r"(u.z), "=r"(u.w) : "r"(addr) : "memory");
+  return u;
+}
+__device__ __forceinline__ void sts128(uint32_t addr, const uint4& u) {
+  asm volatile("st.shared.v4.b32 [%0], {%1, %2, %3, %4};" ::"r"(addr), "r"(u.x), "r"(u.y), "r"(u.z), "r"(u.w) : "memory");
+}
+
+// byte offset of 16-byte chunk c of row r in a box with 128-byte rows (SWIZZLE_128B) / 64-byte rows (SWIZZLE_64B)
+__device__ __forceinline__ uint32_t box_off128(int r, int c) { return (uint32_t)(r * 128 + (((c ^ r) & 7) << 4)); }
+__device__ __forceinline__ uint32_t box_off64(int r, int c) { return (uint32_t)(r * 64 + (((c ^ (r >> 1)) & 3) << 4)); }
+
+// round two fp32 values to bf16 and back with one packed convert (ALU pipe) instead of two F2F (XU pipe)
+__device__ __forceinline__ void bf16_round2(float& a, float& b) {
+  const uint32_t u = pack_bf16x2(a, b);
+  a = __uint_as_float(u << 16);
+  b = __uint_as_float(u & 0xffff0000u);
+}
+__device__ __forceinline__ float fast_sigmoid(float x) {
+  float r;
+  asm("rcp.approx.ftz.f32 %0, %1;" : "=f"(r) : "f"(1.f + __expf(-x)));
+  return r;
+}
+
+// accumulator columns per epilogue unit: every unit moves 4 KB boxes
+template <int EPI> __host__ __device__ constexpr int epi_unit_cols() {
+  return (EPI == DH_EPI_F32 || EPI == DH_EPI_RESID_F32 || EPI == DH_EPI_SWIGLU_BWD) ? 32 : 64;
+}
+template <int EPI> __device__ __forceinline__ bool epi_loads(const GemmParams& p) {
+  if constexpr (EPI == DH_EPI_RESID_F32 || EPI == DH_EPI_RESID_BF16 || EPI == DH_EPI_SWIGLU_BWD) return true;
+  if constexpr (EPI == DH_EPI_F32) return p.accumulate != 0;
+  return false;
+}
+
+// lane 0: prefetch the box one unit reads
+template <int EPI>
+__device__ __forceinline__ void epi_issue_load(const CUtensorMap* tmAux, uint32_t buf, uint64_t* bar, int row0, int col0) {
+  mbar_expect_tx(bar, EPI_BOX_BYTES);
+  tma_load_2d_s(buf, tmAux, EPI == DH_EPI_SWIGLU_BWD ? 2 * col0 : col0, row0, bar);
+}
+
+// lane 0: write the unit's box(es) back
+template <int EPI>
+__device__ __forceinline__ void epi_issue_store(const GemmParams& p, const CUtensorMap* tmOut, const CUtensorMap* tmOut2, uint32_t buf,
+                                                uint32_t buf2, int row0, int col0) {
+  if constexpr (EPI == DH_EPI_SWIGLU) {
+    if (p.out) tma_store_2d(tmOut, buf, col0, row0);
+    tma_store_2d(tmOut2, buf2, col0 >> 1, row0);
+  } else if constexpr (EPI == DH_EPI_SWIGLU_BWD) {
+    tma_store_2d(tmOut, buf, 2 * col0, row0);
+  } else {
+    tma_store_2d(tmOut, buf, col0, row0);
+  }
+  tma_store_commit();
+}
+
+template <int NCOL>
+__device__ __forceinline__ void box_put_bf16(uint32_t box, int lane, const float (&f)[NCOL]) {
 #pragma unroll
-  for (int c = 0; c < 8; ++c) {
+  for (int c = 0; c < NCOL / 8; ++c) {
     uint4 u;
     u.x = pack_bf16x2(f[8 * c + 0], f[8 * c + 1]); u.y = pack_bf16x2(f[8 * c + 2], f[8 * c + 3]);
     u.z = pack_bf16x2(f[8 * c + 4], f[8 * c + 5]); u.w = pack_bf16x2(f[8 * c + 6], f[8 * c + 7]);
-    *reinterpret_cast<uint4*>(stg + stg_off128(lane, c)) = u;
-  }
-}
-// transposed copy-out of a staged [32 x 64] bf16 slab: 4 rows x 128 B per instruction
-__device__ __forceinline__ void copy_out_bf16x64(const uint8_t* stg, int lane, bf16* out, long long ld, int row0, int col0, int M) {
-  const int rr = lane >> 3, c = lane & 7;
-#pragma unroll
-  for (int i = 0; i < 8; ++i) {
-    const int r = 4 * i + rr;
-    const uint4 u = *reinterpret_cast<const uint4*>(stg + stg_off128(r, c));
-    if (row0 + r < M) *reinterpret_cast<uint4*>(out + (long long)(row0 + r) * ld + col0 + 8 * c) = u;
+    sts128(box + box_off128(lane, c), u);
   }
 }
 
 struct RopeRegs { uint4 c[4], s[4]; };   // cos/sin[pos][0..32) as packed bf16 (table halves are identical)
 
-template <int EPI>
-__device__ __forceinline__ void epi_unit(const GemmParams& p, uint8_t* stg, int lane, int row0, int col0, float (&v)[64],
-                                         const RopeRegs& rope) {
-  const int M = p.M;
+// thread = accumulator row `lane` of the unit, v = its epi_unit_cols() columns starting at col0; boxes are updated in place
+template <int EPI, int NCOL>
+__device__ __forceinline__ void epi_compute(const GemmParams& p, uint32_t buf, uint32_t buf2, int lane, int col0, float (&v)[NCOL],
+                                            const RopeRegs& rope) {
   if constexpr (EPI == DH_EPI_BF16) {
 #pragma unroll
     for (int j = 0; j < 64; ++j) v[j] *= p.alpha;
@@ -370,63 +431,42 @@ __device__ __forceinline__ void epi_unit(const GemmParams& p, uint8_t* stg, int 
 #pragma unroll
       for (int j = 0; j < 64; ++j) v[j] *= __ldg(p.col_scale + col0 + j);
     }
-    stage_bf16x64(stg, lane, v);
-    __syncwarp();
-    copy_out_bf16x64(stg, lane, reinterpret_cast<bf16*>(p.out), p.ldo, row0, col0, M);
+    box_put_bf16<64>(buf, lane, v);
   } else if constexpr (EPI == DH_EPI_F32) {
 #pragma unroll
-    for (int c = 0; c < 16; ++c)
-      *reinterpret_cast<float4*>(stg + stg_off256(lane, c)) =
-          make_float4(v[4 * c] * p.alpha, v[4 * c + 1] * p.alpha, v[4 * c + 2] * p.alpha, v[4 * c + 3] * p.alpha);
-    __syncwarp();
-    const int rr = lane >> 4, c = lane & 15;
-#pragma unroll
-    for (int i = 0; i < 16; ++i) {
-      const int r = 2 * i + rr;
-      float4 a = *reinterpret_cast<const float4*>(stg + stg_off256(r, c));
-      if (row0 + r < M) {
-        float4* o = reinterpret_cast<float4*>(reinterpret_cast<float*>(p.out) + (long long)(row0 + r) * p.ldo + col0 + 4 * c);
-        if (p.accumulate) {
-          const float4 old = *o;
-          a.x += old.x; a.y += old.y; a.z += old.z; a.w += old.w;
-        }
-        *o = a;
+    for (int c = 0; c < 8; ++c) {
+      const uint32_t slot = buf + box_off128(lane, c);
+      float4 a = make_float4(v[4 * c] * p.alpha, v[4 * c + 1] * p.alpha, v[4 * c + 2] * p.alpha, v[4 * c + 3] * p.alpha);
+      if (p.accumulate) {
+        const uint4 old = lds128(slot);
+        a.x += __uint_as_float(old.x); a.y += __uint_as_float(old.y); a.z += __uint_as_float(old.z); a.w += __uint_as_float(old.w);
       }
+      sts128(slot, make_uint4(__float_as_uint(a.x), __float_as_uint(a.y), __float_as_uint(a.z), __float_as_uint(a.w)));
     }
   } else if constexpr (EPI == DH_EPI_RESID_F32) {
-    stage_bf16x64(stg, lane, v);   // bf16(acc) is what the reference adds to the fp32 stream
-    __syncwarp();
-    const int rr = lane >> 4, c = lane & 15;   // output chunk c = 4 floats = 8 staged bytes
 #pragma unroll
-    for (int i = 0; i < 16; ++i) {
-      const int r = 2 * i + rr;
-      const uint2 u = *reinterpret_cast<const uint2*>(stg + stg_off128(r, c >> 1) + ((c & 1) << 3));
-      if (row0 + r < M) {
-        const long long off = (long long)(row0 + r);
-        float4 a = *reinterpret_cast<const float4*>(reinterpret_cast<const float*>(p.aux) + off * p.ldaux + col0 + 4 * c);
-        const float2 lo = unpack_bf16x2(u.x), hi = unpack_bf16x2(u.y);
-        a.x += lo.x; a.y += lo.y; a.z += hi.x; a.w += hi.y;
-        *reinterpret_cast<float4*>(reinterpret_cast<float*>(p.out) + off * p.ldo + col0 + 4 * c) = a;
-      }
+    for (int c = 0; c < 8; ++c) {
+      const uint32_t slot = buf + box_off128(lane, c);
+      const uint4 x = lds128(slot);
+      float a0 = v[4 * c], a1 = v[4 * c + 1], a2 = v[4 * c + 2], a3 = v[4 * c + 3];
+      bf16_round2(a0, a1);   // bf16(acc) is what the reference adds to the fp32 stream
+      bf16_round2(a2, a3);
+      sts128(slot, make_uint4(__float_as_uint(__uint_as_float(x.x) + a0), __float_as_uint(__uint_as_float(x.y) + a1),
+                              __float_as_uint(__uint_as_float(x.z) + a2), __float_as_uint(__uint_as_float(x.w) + a3)));
     }
   } else if constexpr (EPI == DH_EPI_RESID_BF16) {
-    stage_bf16x64(stg, lane, v);
-    __syncwarp();
-    const int rr = lane >> 3, c = lane & 7;
 #pragma unroll
-    for (int i = 0; i < 8; ++i) {
-      const int r = 4 * i + rr;
-      const uint4 u = *reinterpret_cast<const uint4*>(stg + stg_off128(r, c));
-      if (row0 + r < M) {
-        const long long off = (long long)(row0 + r);
-        const uint4 x = *reinterpret_cast<const uint4*>(reinterpret_cast<const bf16*>(p.aux) + off * p.ldaux + col0 + 8 * c);
-        const float2 a0 = unpack_bf16x2(u.x), a1 = unpack_bf16x2(u.y), a2 = unpack_bf16x2(u.z), a3 = unpack_bf16x2(u.w);
-        const float2 x0 = unpack_bf16x2(x.x), x1 = unpack_bf16x2(x.y), x2 = unpack_bf16x2(x.z), x3 = unpack_bf16x2(x.w);
-        uint4 o;
-        o.x = pack_bf16x2(x0.x + a0.x, x0.y + a0.y); o.y = pack_bf16x2(x1.x + a1.x, x1.y + a1.y);
-        o.z = pack_bf16x2(x2.x + a2.x, x2.y + a2.y); o.w = pack_bf16x2(x3.x + a3.x, x3.y + a3.y);
-        *reinterpret_cast<uint4*>(reinterpret_cast<bf16*>(p.out) + off * p.ldo + col0 + 8 * c) = o;
+    for (int c = 0; c < 8; ++c) {
+      const uint32_t slot = buf + box_off128(lane, c);
+      float x[8];
+      unpack_bf16x8(lds128(slot), x);
+#pragma unroll
+      for (int k = 0; k < 8; k += 2) {
+        float a0 = v[8 * c + k], a1 = v[8 * c + k + 1];
+        bf16_round2(a0, a1);
+        x[k] += a0; x[k + 1] += a1;
       }
+      sts128(slot, pack_bf16x8(x));
     }
   } else if constexpr (EPI == DH_EPI_QKV_ROPE) {
     const int slot = (col0 >> 6) % (p.q_per_kv + 2);
@@ -439,72 +479,53 @@ __device__ __forceinline__ void epi_unit(const GemmParams& p, uint8_t* stg, int 
         for (int k = 0; k < 4; ++k) {
           const float2 cc = unpack_bf16x2(cw[k]), ss = unpack_bf16x2(sw[k]);
           const int j = 8 * i + 2 * k;
-          const float a0 = bf16_round(v[j]), b0 = bf16_round(v[j + 32]);
-          const float a1 = bf16_round(v[j + 1]), b1 = bf16_round(v[j + 33]);
+          float a0 = v[j], a1 = v[j + 1], b0 = v[j + 32], b1 = v[j + 33];
+          bf16_round2(a0, a1);
+          bf16_round2(b0, b1);
           v[j] = a0 * cc.x - b0 * ss.x;      v[j + 32] = b0 * cc.x + a0 * ss.x;
           v[j + 1] = a1 * cc.y - b1 * ss.y;  v[j + 33] = b1 * cc.y + a1 * ss.y;
         }
       }
     }
-    stage_bf16x64(stg, lane, v);
-    __syncwarp();
-    copy_out_bf16x64(stg, lane, reinterpret_cast<bf16*>(p.out), p.ldo, row0, col0, M);
+    box_put_bf16<64>(buf, lane, v);
   } else if constexpr (EPI == DH_EPI_SWIGLU) {
-    // raw h12 (64 cols) in the first 4 KB of the slab, act = silu(h1) * h2 (32 cols, 64-byte rows) in the next 2 KB
-    uint8_t* stg2 = stg + 4096;
-    if (p.out) stage_bf16x64(stg, lane, v);
+    // raw h12 (64 cols) in the first box, act = silu(h1) * h2 (32 cols, 64-byte rows, SWIZZLE_64B) in the second
+    if (p.out) box_put_bf16<64>(buf, lane, v);
 #pragma unroll
     for (int c = 0; c < 4; ++c) {
       float a[8];
 #pragma unroll
-      for (int k = 0; k < 8; ++k) {
-        const float h1 = bf16_round(v[8 * c + k]), h2 = bf16_round(v[8 * c + k + 32]);
-        a[k] = (h1 / (1.f + __expf(-h1))) * h2;
+      for (int k = 0; k < 8; k += 2) {
+        float h1a = v[8 * c + k], h1b = v[8 * c + k + 1], h2a = v[8 * c + k + 32], h2b = v[8 * c + k + 33];
+        bf16_round2(h1a, h1b);
+        bf16_round2(h2a, h2b);
+        a[k] = h1a * fast_sigmoid(h1a) * h2a;
+        a[k + 1] = h1b * fast_sigmoid(h1b) * h2b;
       }
-      uint4 u;
-      u.x = pack_bf16x2(a[0], a[1]); u.y = pack_bf16x2(a[2], a[3]); u.z = pack_bf16x2(a[4], a[5]); u.w = pack_bf16x2(a[6], a[7]);
-      *reinterpret_cast<uint4*>(stg2 + stg_off64(lane, c)) = u;
-    }
-    __syncwarp();
-    if (p.out) copy_out_bf16x64(stg, lane, reinterpret_cast<bf16*>(p.out), p.ldo, row0, col0, M);
-    const int rr = lane >> 2, c = lane & 3;
-#pragma unroll
-    for (int i = 0; i < 4; ++i) {
-      const int r = 8 * i + rr;
-      const uint4 u = *reinterpret_cast<const uint4*>(stg2 + stg_off64(r, c));
-      if (row0 + r < M) *reinterpret_cast<uint4*>(reinterpret_cast<bf16*>(p.out2) + (long long)(row0 + r) * p.ldo2 + (col0 >> 1) + 8 * c) = u;
+      sts128(buf2 + box_off64(lane, c), pack_bf16x8(a));
     }
   } else if constexpr (EPI == DH_EPI_SWIGLU_BWD) {
-    // acc = d(act) columns col0..col0+63; h12 / d(h12) columns 2*col0 .. 2*col0+127 as two [h1 x32 | h2 x32] blocks
-    stage_bf16x64(stg, lane, v);
-    __syncwarp();
-    const int rr = lane >> 3, t = lane & 7, g = t >> 2, cc = t & 3;
+    // acc = d(act) columns col0..col0+31; the box holds h12 columns 2*col0 .. 2*col0+63 = [h1 x32 | h2 x32]
 #pragma unroll
-    for (int i = 0; i < 8; ++i) {
-      const int r = 4 * i + rr;
-      const uint4 du = *reinterpret_cast<const uint4*>(stg + stg_off128(r, g * 4 + cc));
-      if (row0 + r < M) {
-        const long long off = (long long)(row0 + r);
-        const bf16* h = reinterpret_cast<const bf16*>(p.aux) + off * p.ldaux + 2 * col0 + 64 * g + 8 * cc;
-        bf16* o = reinterpret_cast<bf16*>(p.out) + off * p.ldo + 2 * col0 + 64 * g + 8 * cc;
-        const uint4 h1u = *reinterpret_cast<const uint4*>(h);
-        const uint4 h2u = *reinterpret_cast<const uint4*>(h + 32);
-        float da[8], h1[8], h2[8], d1[8], d2[8];
-        unpack_bf16x8(du, da);
-        unpack_bf16x8(h1u, h1);
-        unpack_bf16x8(h2u, h2);
+    for (int c = 0; c < 4; ++c) {
+      const uint32_t s1 = buf + box_off128(lane, c), s2 = buf + box_off128(lane, c + 4);
+      float h1[8], h2[8], d1[8], d2[8];
+      unpack_bf16x8(lds128(s1), h1);
+      unpack_bf16x8(lds128(s2), h2);
 #pragma unroll
-        for (int k = 0; k < 8; ++k) {
-          const float sig = 1.f / (1.f + __expf(-h1[k]));
-          d1[k] = da[k] * h2[k] * (sig * (1.f + h1[k] * (1.f - sig)));
-          d2[k] = da[k] * (h1[k] * sig);
-        }
-        *reinterpret_cast<uint4*>(o) = pack_bf16x8(d1);
-        *reinterpret_cast<uint4*>(o + 32) = pack_bf16x8(d2);
+      for (int k = 0; k < 8; k += 2) {
+        float da0 = v[8 * c + k], da1 = v[8 * c + k + 1];
+        bf16_round2(da0, da1);
+        const float sg0 = fast_sigmoid(h1[k]), sg1 = fast_sigmoid(h1[k + 1]);
+        d1[k] = da0 * h2[k] * (sg0 * (1.f + h1[k] * (1.f - sg0)));
+        d2[k] = da0 * (h1[k] * sg0);
+        d1[k + 1] = da1 * h2[k + 1] * (sg1 * (1.f + h1[k + 1] * (1.f - sg1)));
+        d2[k + 1] = da1 * (h1[k + 1] * sg1);
       }
+      sts128(s1, pack_bf16x8(d1));
+      sts128(s2, pack_bf16x8(d2));
     }
   }
-  __syncwarp();   // the slab is rewritten by the next unit
 }
 
 // ------------------------------------------------------------------------------------------------
@@ -513,32 +534,38 @@ __device__ __forceinline__ void epi_unit(const GemmParams& p, uint8_t* stg, int 
 // and owns accumulator rows [128 r, +128) x 256 columns in its own TMEM; the leader's MMA thread drives
 // both tensor cores, so every B byte is fetched into shared memory once per pair instead of once per SM.
 // K-major operands only (dgrads use pre-transposed frozen weights).
+// Roles (384 threads): warp 0 = TMA producer, warp 1 = MMA issuer, warp 2 = TMEM allocator, warps 4-11 = epilogue
+// (warp w owns TMEM lanes 32*(w%4).., and the units of a tile alternate between the two warps of a quadrant).
 // ------------------------------------------------------------------------------------------------
 struct PairCfg {
   static constexpr int BN = 256;
   static constexpr int A_BYTES = 128 * BK * 2;
   static constexpr int B_BYTES = 128 * BK * 2;
   static constexpr int STAGE_BYTES = A_BYTES + B_BYTES;
-  static constexpr int STAGES = 6;
-  static constexpr int SMEM_BYTES = STAGES * STAGE_BYTES + 4 * STG_BYTES + 1024 + 256;
+  static constexpr int STAGES = 5;
+  static constexpr int SMEM_BYTES = STAGES * STAGE_BYTES + PAIR_EPI_WARPS * EPI_WARP_BYTES + 1024 + 512;
+};
+
+struct PairMaps {
+  CUtensorMap A, B, A2, B2, out, out2, aux;
 };
 
 template <int EPI>
-__global__ void __cluster_dims__(2, 1, 1) __launch_bounds__(GEMM_THREADS, 1)
-gemm_pair_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant__ CUtensorMap tmB,
-                 const __grid_constant__ CUtensorMap tmA2, const __grid_constant__ CUtensorMap tmB2, const GemmParams p) {
+__global__ void __cluster_dims__(2, 1, 1) __launch_bounds__(PAIR_THREADS, 1)
+gemm_pair_kernel(const __grid_constant__ PairMaps tm, const GemmParams p) {
   using Cfg = PairCfg;
   constexpr int STAGES = Cfg::STAGES;
   constexpr int BN = Cfg::BN;
   extern __shared__ uint8_t smem_raw[];
   uint8_t* smem = reinterpret_cast<uint8_t*>((reinterpret_cast<uintptr_t>(smem_raw) + 1023) & ~uintptr_t(1023));
-  uint8_t* stg_base = smem + STAGES * Cfg::STAGE_BYTES;   // 4 epilogue warps x 8 KB
-  uint64_t* bars = reinterpret_cast<uint64_t*>(stg_base + 4 * STG_BYTES);
+  uint8_t* epi_base = smem + STAGES * Cfg::STAGE_BYTES;   // 8 epilogue warps x 2 x 4 KB
+  uint64_t* bars = reinterpret_cast<uint64_t*>(epi_base + PAIR_EPI_WARPS * EPI_WARP_BYTES);
   uint64_t* full_bar = bars;                     // [STAGES]  TMA (both CTAs) -> MMA       (leader's copy is used)
   uint64_t* empty_bar = bars + STAGES;           // [STAGES]  MMA -> TMA                   (multicast to both)
   uint64_t* tfull_bar = bars + 2 * STAGES;       // [2]       MMA -> epilogue              (multicast to both)
   uint64_t* tempty_bar = bars + 2 * STAGES + 2;  // [2]       epilogue (both CTAs) -> MMA  (leader's copy is used)
-  uint32_t* tmem_slot = reinterpret_cast<uint32_t*>(bars + 2 * STAGES + 4);
+  uint64_t* eload_bar = bars + 2 * STAGES + 4;   // [8][2]    epilogue box prefetch, per warp and buffer
+  uint32_t* tmem_slot = reinterpret_cast<uint32_t*>(bars + 2 * STAGES + 4 + 2 * PAIR_EPI_WARPS);
 
   const int warp = threadIdx.x >> 5;
   const int lane = threadIdx.x & 31;
@@ -550,13 +577,19 @@ gemm_pair_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant_
   const int nkb = nkb1 + (p.K2 + BK - 1) / BK;
 
   if (warp == 0 && lane == 0) {
-    tma_prefetch_desc(&tmA);
-    tma_prefetch_desc(&tmB);
-    if (p.K2 > 0) { tma_prefetch_desc(&tmA2); tma_prefetch_desc(&tmB2); }
+    tma_prefetch_desc(&tm.A);
+    tma_prefetch_desc(&tm.B);
+    if (p.K2 > 0) { tma_prefetch_desc(&tm.A2); tma_prefetch_desc(&tm.B2); }
+  }
+  if (warp == 3 && lane == 0) {
+    if (p.out || EPI != DH_EPI_SWIGLU) tma_prefetch_desc(&tm.out);
+    if constexpr (EPI == DH_EPI_SWIGLU) tma_prefetch_desc(&tm.out2);
+    if (epi_loads<EPI>(p)) tma_prefetch_desc(&tm.aux);
   }
   if (warp == 1 && lane == 0) {
     for (int i = 0; i < STAGES; ++i) { mbar_init(&full_bar[i], 1); mbar_init(&empty_bar[i], 1); }
-    for (int i = 0; i < 2; ++i) { mbar_init(&tfull_bar[i], 1); mbar_init(&tempty_bar[i], 8); }
+    for (int i = 0; i < 2; ++i) { mbar_init(&tfull_bar[i], 1); mbar_init(&tempty_bar[i], 2 * PAIR_EPI_WARPS); }
+    for (int i = 0; i < 2 * PAIR_EPI_WARPS; ++i) mbar_init(&eload_bar[i], 1);
     fence_barrier_init();
   }
   if (warp == 2) {
@@ -583,8 +616,8 @@ gemm_pair_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant_
         const uint32_t bar = mapa_shared(smem_u32(&full_bar[s]), 0);
         const bool second = kb >= nkb1;
         const int k0 = (second ? kb - nkb1 : kb) * BK;
-        tma_load_2d_pair(sa, second ? &tmA2 : &tmA, k0, m0, bar);
-        tma_load_2d_pair(sb, second ? &tmB2 : &tmB, k0, n0, bar);
+        tma_load_2d_pair(sa, second ? &tm.A2 : &tm.A, k0, m0, bar);
+        tma_load_2d_pair(sb, second ? &tm.B2 : &tm.B, k0, n0, bar);
       }
     }
   } else if (warp == 1 && lane == 0 && rank == 0) {
@@ -611,42 +644,74 @@ gemm_pair_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant_
     }
   } else if (warp >= 4) {
     // ===================== epilogue (each CTA drains its own 128 accumulator rows) =====================
-    const int q = warp & 3;
-    uint32_t tcount = 0;
-    for (int tile = pair; tile < num_tiles; tile += npairs, ++tcount) {
-      const int acc = tcount & 1;
-      const int m0 = (tile % p.tiles_m) * 256 + (int)rank * 128;
-      const int n0 = (tile / p.tiles_m) * BN;
-      mbar_wait(&tfull_bar[acc], (tcount >> 1) & 1);
-      tc_fence_after();
-      const int row0 = m0 + q * 32;
-      const uint32_t taddr = tmem_base + ((uint32_t)(q * 32) << 16) + acc * BN;
-      RopeRegs rope;
-      if constexpr (EPI == DH_EPI_QKV_ROPE) {
-        const int row = row0 + lane < p.M ? row0 + lane : p.M - 1;
-        const int pos = p.positions ? __ldg(p.positions + row) : (row % p.seq_len);
-        const uint4* c4 = reinterpret_cast<const uint4*>(p.rope_cos + (long long)pos * 64);
-        const uint4* s4 = reinterpret_cast<const uint4*>(p.rope_sin + (long long)pos * 64);
+    constexpr int UC = epi_unit_cols<EPI>();     // accumulator columns per unit
+    constexpr int UPW = BN / UC / 2;             // units per warp per tile
+    constexpr bool SINGLE_BUF = (EPI == DH_EPI_SWIGLU);   // uses both boxes for one unit
+    const int q = warp & 3, half = (warp - 4) >> 2;
+    const uint32_t ebuf = smem_u32(epi_base + (warp - 4) * EPI_WARP_BYTES);
+    uint64_t* lbar = eload_bar + 2 * (warp - 4);
+    const bool loads = epi_loads<EPI>(p);
+    const int my_tiles = pair < num_tiles ? (num_tiles - pair + npairs - 1) / npairs : 0;
+    const int n_units = my_tiles * UPW;
+    // unit u of this warp = column slice 2 * (u % UPW) + half of this pair's (u / UPW)-th tile
+    auto unit_row0 = [&](int u) { return ((pair + (u / UPW) * npairs) % p.tiles_m) * 256 + (int)rank * 128 + q * 32; };
+    auto unit_col0 = [&](int u) { return ((pair + (u / UPW) * npairs) / p.tiles_m) * BN + (2 * (u % UPW) + half) * UC; };
+    if (loads && lane == 0 && n_units > 0) epi_issue_load<EPI>(&tm.aux, ebuf, &lbar[0], unit_row0(0), unit_col0(0));
+    RopeRegs rope;
+    for (int u = 0; u < n_units; ++u) {
+      const int tcount = u / UPW, acc = tcount & 1, c = 2 * (u % UPW) + half;
+      const int row0 = unit_row0(u), col0 = unit_col0(u);
+      const uint32_t buf = SINGLE_BUF ? ebuf : ebuf + (u & 1) * EPI_BOX_BYTES;
+      if (u % UPW == 0) {
+        mbar_wait(&tfull_bar[acc], (tcount >> 1) & 1);
+        tc_fence_after();
+        if constexpr (EPI == DH_EPI_QKV_ROPE) {
+          const int row = row0 + lane < p.M ? row0 + lane : p.M - 1;
+          const int pos = p.positions ? __ldg(p.positions + row) : (row % p.seq_len);
+          const uint4* c4 = reinterpret_cast<const uint4*>(p.rope_cos + (long long)pos * 64);
+          const uint4* s4 = reinterpret_cast<const uint4*>(p.rope_sin + (long long)pos * 64);
 #pragma unroll
-        for (int i = 0; i < 4; ++i) { rope.c[i] = __ldg(c4 + i); rope.s[i] = __ldg(s4 + i); }
-      }
-#pragma unroll 1
-      for (int c = 0; c < BN / 64; ++c) {
-        uint32_t r0[32], r1[32];
-        tmem_ld32(taddr + c * 64, r0);
-        tmem_ld32(taddr + c * 64 + 32, r1);
-        tmem_wait_ld();
-        if (c == BN / 64 - 1) {   // accumulator fully read: hand the TMEM buffer back before the last unit's stores
-          tc_fence_before();
-          __syncwarp();
-          if (lane == 0) mbar_arrive_cluster(mapa_shared(smem_u32(&tempty_bar[acc]), 0));
+          for (int i = 0; i < 4; ++i) { rope.c[i] = __ldg(c4 + i); rope.s[i] = __ldg(s4 + i); }
         }
-        float v[64];
-#pragma unroll
-        for (int j = 0; j < 32; ++j) { v[j] = __uint_as_float(r0[j]); v[j + 32] = __uint_as_float(r1[j]); }
-        epi_unit<EPI>(p, stg_base + q * STG_BYTES, lane, row0, n0 + c * 64, v, rope);
       }
+      const uint32_t taddr = tmem_base + ((uint32_t)(q * 32) << 16) + acc * BN + c * UC;
+      float v[UC];
+      {
+        uint32_t r0[32];
+        tmem_ld32(taddr, r0);
+        if constexpr (UC == 64) {
+          uint32_t r1[32];
+          tmem_ld32(taddr + 32, r1);
+          tmem_wait_ld();
+#pragma unroll
+          for (int j = 0; j < 32; ++j) v[j + 32 * (UC == 64)] = __uint_as_float(r1[j]);
+        } else {
+          tmem_wait_ld();
+        }
+#pragma unroll
+        for (int j = 0; j < 32; ++j) v[j] = __uint_as_float(r0[j]);
+      }
+      if (lane == 0) {
+        if (loads) {
+          tma_store_wait_read<0>();   // the other box's store (unit u-1) has left shared memory: refill it
+          if (u + 1 < n_units)
+            epi_issue_load<EPI>(&tm.aux, ebuf + ((u + 1) & 1) * EPI_BOX_BYTES, &lbar[(u + 1) & 1], unit_row0(u + 1), unit_col0(u + 1));
+        } else if (SINGLE_BUF) {
+          tma_store_wait_read<0>();
+        } else {
+          tma_store_wait_read<1>();   // this box's previous store (unit u-2) has left shared memory
+        }
+      }
+      if (u % UPW == UPW - 1) tc_fence_before();   // this warp has read its share of the accumulator: hand it back
+      __syncwarp();
+      if (u % UPW == UPW - 1 && lane == 0) mbar_arrive_cluster(mapa_shared(smem_u32(&tempty_bar[acc]), 0));
+      if (loads) mbar_wait(&lbar[u & 1], (u >> 1) & 1);
+      epi_compute<EPI, UC>(p, buf, ebuf + EPI_BOX_BYTES, lane, col0, v, rope);
+      fence_proxy_async_smem();
+      __syncwarp();
+      if (lane == 0) epi_issue_store<EPI>(p, &tm.out, &tm.out2, buf, ebuf + EPI_BOX_BYTES, row0, col0);
     }
+    if (lane == 0) tma_store_wait_all();
   }
 
   tc_fence_before();
@@ -721,6 +786,30 @@ static int launch_gemm(const dh_gemm_args* a, cudaStream_t stream) {
   return 0;
 }
 
+// [rows, cols] row-major tensor of `esize`-byte elements, box = {box_cols, 32 rows}
+static int make_epi_map(CUtensorMap* map, const void* base, long long ld, long long rows, long long cols, int esize, int box_cols) {
+  uint64_t dims[2] = {(uint64_t)cols, (uint64_t)rows};
+  uint64_t strides[1] = {(uint64_t)ld * esize};
+  uint32_t box[2] = {(uint32_t)box_cols, 32};
+  const int row_bytes = box_cols * esize;
+  return make_tensor_map(map, base, esize == 2 ? CU_TENSOR_MAP_DATA_TYPE_BFLOAT16 : CU_TENSOR_MAP_DATA_TYPE_FLOAT32, 2, dims, strides, box,
+                         row_bytes == 128 ? CU_TENSOR_MAP_SWIZZLE_128B : CU_TENSOR_MAP_SWIZZLE_64B);
+}
+
+// can the epilogue tensors of this call be described by tensor maps (16-byte aligned bases and row pitches)?
+static bool pair_epilogue_ok(const dh_gemm_args* a) {
+  auto ok = [](const void* ptr, long long ld, int esize) { return ((uintptr_t)ptr & 15) == 0 && (ld * esize) % 16 == 0; };
+  switch (a->epilogue) {
+    case DH_EPI_BF16: case DH_EPI_QKV_ROPE: return ok(a->out, a->ldo, 2);
+    case DH_EPI_F32: return ok(a->out, a->ldo, 4);
+    case DH_EPI_RESID_F32: return ok(a->out, a->ldo, 4) && ok(a->aux, a->ldaux, 4);
+    case DH_EPI_RESID_BF16: return ok(a->out, a->ldo, 2) && ok(a->aux, a->ldaux, 2);
+    case DH_EPI_SWIGLU: return (!a->out || ok(a->out, a->ldo, 2)) && ok(a->out2, a->ldo2, 2);
+    case DH_EPI_SWIGLU_BWD: return ok(a->out, a->ldo, 2) && ok(a->aux, a->ldaux, 2);
+    default: return false;
+  }
+}
+
 template <int EPI>
 static int launch_gemm_pair(const dh_gemm_args* a, cudaStream_t stream) {
   using Cfg = PairCfg;
@@ -729,15 +818,35 @@ static int launch_gemm_pair(const dh_gemm_args* a, cudaStream_t stream) {
     DH_CUDA(cudaFuncSetAttribute(gemm_pair_kernel<EPI>, cudaFuncAttributeMaxDynamicSharedMemorySize, Cfg::SMEM_BYTES));
     attr_set = true;
   }
-  CUtensorMap tmA, tmB, tmA2, tmB2;
-  if (make_operand_map(&tmA, a->A, a->lda, a->M, a->K1, 0, 128)) return -3;
-  if (make_operand_map(&tmB, a->B, a->ldb, a->N, a->K1, 0, 128)) return -3;
+  PairMaps tm;
+  if (make_operand_map(&tm.A, a->A, a->lda, a->M, a->K1, 0, 128)) return -3;
+  if (make_operand_map(&tm.B, a->B, a->ldb, a->N, a->K1, 0, 128)) return -3;
   if (a->K2 > 0) {
-    if (make_operand_map(&tmA2, a->A2, a->lda2, a->M, a->K2, 0, 128)) return -3;
-    if (make_operand_map(&tmB2, a->B2, a->ldb2, a->N, a->K2, 0, 128)) return -3;
+    if (make_operand_map(&tm.A2, a->A2, a->lda2, a->M, a->K2, 0, 128)) return -3;
+    if (make_operand_map(&tm.B2, a->B2, a->ldb2, a->N, a->K2, 0, 128)) return -3;
   } else {
-    tmA2 = tmA;
-    tmB2 = tmB;
+    tm.A2 = tm.A;
+    tm.B2 = tm.B;
+  }
+  const long long M = a->M, N = a->N;
+  tm.out = tm.out2 = tm.aux = tm.A;   // placeholders for the maps this epilogue never touches
+  if constexpr (EPI == DH_EPI_BF16 || EPI == DH_EPI_QKV_ROPE) {
+    if (make_epi_map(&tm.out, a->out, a->ldo, M, N, 2, 64)) return -3;
+  } else if constexpr (EPI == DH_EPI_F32) {
+    if (make_epi_map(&tm.out, a->out, a->ldo, M, N, 4, 32)) return -3;
+    tm.aux = tm.out;   // accumulate reads what it overwrites
+  } else if constexpr (EPI == DH_EPI_RESID_F32) {
+    if (make_epi_map(&tm.out, a->out, a->ldo, M, N, 4, 32)) return -3;
+    if (make_epi_map(&tm.aux, a->aux, a->ldaux, M, N, 4, 32)) return -3;
+  } else if constexpr (EPI == DH_EPI_RESID_BF16) {
+    if (make_epi_map(&tm.out, a->out, a->ldo, M, N, 2, 64)) return -3;
+    if (make_epi_map(&tm.aux, a->aux, a->ldaux, M, N, 2, 64)) return -3;
+  } else if constexpr (EPI == DH_EPI_SWIGLU) {
+    if (a->out && make_epi_map(&tm.out, a->out, a->ldo, M, N, 2, 64)) return -3;
+    if (make_epi_map(&tm.out2, a->out2, a->ldo2, M, N / 2, 2, 32)) return -3;
+  } else if constexpr (EPI == DH_EPI_SWIGLU_BWD) {
+    if (make_epi_map(&tm.out, a->out, a->ldo, M, 2 * N, 2, 64)) return -3;
+    if (make_epi_map(&tm.aux, a->aux, a->ldaux, M, 2 * N, 2, 64)) return -3;
   }
   GemmParams p = make_params(a);
   p.tiles_m = (a->M + 255) / 256;
@@ -745,7 +854,7 @@ static int launch_gemm_pair(const dh_gemm_args* a, cudaStream_t stream) {
   const int tiles = p.tiles_m * p.tiles_n;
   const int pairs = sm_count() / 2;
   const int grid = 2 * (tiles < pairs ? tiles : pairs);
-  gemm_pair_kernel<EPI><<<grid, GEMM_THREADS, Cfg::SMEM_BYTES, stream>>>(tmA, tmB, tmA2, tmB2, p);
+  gemm_pair_kernel<EPI><<<grid, PAIR_THREADS, Cfg::SMEM_BYTES, stream>>>(tm, p);
   DH_CUDA(cudaGetLastError());
   return 0;
 }
@@ -760,7 +869,7 @@ static int dispatch_bn(const dh_gemm_args* a, cudaStream_t stream) {
   }
   // CTA pairs for the big K-major GEMMs of the decoder; the 1-CTA kernel covers small M, MN-major operands, odd N.
   if (!g_force_single && a->a_layout == 0 && a->b_layout == 0 && (a->K2 == 0 || (a->a2_layout == 0 && a->b2_layout == 0)) &&
-      a->N % 256 == 0 && a->M >= 1024)
+      a->N % 256 == 0 && a->M >= 1024 && pair_epilogue_ok(a))
     return launch_gemm_pair<EPI>(a, stream);
   // Tile width: 256 when it divides N and leaves enough tiles to fill the machine, else 128, else 64.
   const long long tiles_m = (a->M + BM - 1) / BM;
