@@ -11,7 +11,7 @@ import os
 from typing import Optional
 
 _HERE = os.path.dirname(os.path.abspath(__file__))
-LIB_PATH = os.path.join(_HERE, "libdualhyp.so")
+LIB_PATH = os.path.join(_HERE, os.environ.get("DUALHYP_LIB", "libdualhyp.so"))   # DUALHYP_LIB: developer override (trace builds)
 
 EPI_BF16, EPI_F32, EPI_RESID_F32, EPI_RESID_BF16, EPI_QKV_ROPE, EPI_SWIGLU, EPI_SWIGLU_BWD = range(7)
 

@@ -18,6 +18,16 @@
 
 namespace dh {
 
+#ifdef DH_ATTN_TRACE
+#define TRC_DECL long long trc_t[48]; int trc_n = 0; const bool trc_on = (blockIdx.x == 0 && blockIdx.y == 5 && blockIdx.z == 3);
+#define TRC(tag) do { if (trc_on && trc_n < 48) { trc_t[trc_n++] = clock64(); } } while (0)
+#define TRC_DUMP(who) do { if (trc_on && lane == 0) { for (int i_ = 1; i_ < trc_n; ++i_) printf("%s w%d ev%d +%lld (abs %lld)\n", who, warp, i_, trc_t[i_] - trc_t[i_ - 1], trc_t[i_] - trc_t[0]); } } while (0)
+#else
+#define TRC_DECL
+#define TRC(tag)
+#define TRC_DUMP(who)
+#endif
+
 constexpr int ATT_BQ = 128;
 constexpr int ATT_BK = 128;
 constexpr int HD = 64;
@@ -117,209 +127,360 @@ __device__ __forceinline__ void rope_conj_halves(float (&lo)[32], float (&hi)[32
 }
 
 // =================================================================================================
-// forward
+// forward.  CTA = (q tile pair {nq-1-x, x}, head, batch): every CTA does nq+1 key tiles, so the grid is
+// balanced whatever the causal triangle looks like; two CTAs share an SM (256 TMEM columns each) and
+// fill each other's bubbles.  Per key tile:
+//   MMA warp   : S = Q K^T (tcgen05, fp32 in TMEM)            -> s_full
+//   softmax    : 8 warps; two threads per query row, 64 score columns each, straight into registers
+//                (-> s_free: the MMA warp issues the NEXT tile's S while this one is exponentiated);
+//                the row max is exchanged through shared memory; lazy rescaling of O (only when the
+//                max grew by more than 2^8); P = 2^(s - m) packed to bf16 and written back to TMEM -> p_full
+//   MMA warp   : O += P V with P as the TMEM A operand, V the MN-major smem B operand  -> o_done
+// K and V tiles are double buffered.  The adapter prefix (ger/adapter.py:129-146) rides the same
+// pipes: S_a = Q AK^T is a 16-column MMA issued before the first key tile, its softmax weights stay
+// in registers and, once the causal row sum l is known, gate * l * softmax(S_a) is the A operand of
+// one last K=16 MMA into O, so (O + l gate P_a AV) / l = causal + gate * prefix.
 // =================================================================================================
-constexpr int FWD_THREADS = 192;
-constexpr int FWD_SMEM = 5 * TILE_BYTES + 2 * MAX_PREFIX * HD * 4 + 1024 + 128;
+constexpr int FWD_SM_WARPS = 8;                       // softmax warps
+constexpr int FWD_THREADS = (FWD_SM_WARPS + 2) * 32;  // + TMA warp + MMA warp
+constexpr int FWD_OFF_K = 2 * TILE_BYTES, FWD_OFF_V = 4 * TILE_BYTES, FWD_OFF_AK = 6 * TILE_BYTES, FWD_OFF_AV = FWD_OFF_AK + 2048,
+              FWD_OFF_X = FWD_OFF_AV + 2048 /* float [2 parity][2 halves][128] */, FWD_OFF_PW = FWD_OFF_X + 2048 /* float [16][128] */,
+              FWD_OFF_BAR = FWD_OFF_PW + MAX_PREFIX * 128 * 4;
+constexpr int FWD_SMEM = FWD_OFF_BAR + 256 + 1024;
+constexpr float RESCALE_THRESHOLD = 8.f;   // log2 units
 
-__global__ void __launch_bounds__(FWD_THREADS, 2) attn_fwd_kernel(const __grid_constant__ CUtensorMap tmQKV, const AttnParams p) {
+// O[128 x 64] (+)= P[128 x 16*ksteps] (TMEM, bf16 pairs per column) * V[16*ksteps keys x 64] (smem, MN-major)
+__device__ __forceinline__ void mma_pv_ts(uint32_t d_tmem, uint32_t p_tmem, uint32_t v_smem, int ksteps, bool accumulate) {
+  constexpr uint32_t idesc = umma_idesc_bf16(128, 64, 0, 1);
+  for (int k = 0; k < ksteps; ++k)
+    tc_mma_ts(d_tmem, p_tmem + k * 8, umma_desc_sw128(v_smem + k * 2048, 8192, 1024), idesc, accumulate || k != 0);
+}
+
+// max over one 32-column chunk of a score row; TRI: only columns <= lane are visible (diagonal chunk)
+template <bool TRI>
+__device__ __forceinline__ void chunk_max(const uint32_t (&s)[32], int lane, float& m0, float& m1) {
+#pragma unroll
+  for (int i = 0; i < 32; i += 2) {
+    float a = __uint_as_float(s[i]), c = __uint_as_float(s[i + 1]);
+    if (TRI) { a = (i <= lane) ? a : -INFINITY; c = (i + 1 <= lane) ? c : -INFINITY; }
+    m0 = fmaxf(m0, a);
+    m1 = fmaxf(m1, c);
+  }
+}
+// P = 2^(s * scale_log2 - m) for one chunk -> 16 packed bf16 pairs; the row sum is taken before rounding
+template <bool TRI>
+__device__ __forceinline__ void chunk_exp(const uint32_t (&s)[32], int lane, float scale_log2, float neg_m, float& sum0, float& sum1,
+                                          uint32_t (&out)[16]) {
+#pragma unroll
+  for (int i = 0; i < 32; i += 2) {
+    float a = fast_exp2(fmaf(__uint_as_float(s[i]), scale_log2, neg_m));
+    float c = fast_exp2(fmaf(__uint_as_float(s[i + 1]), scale_log2, neg_m));
+    if (TRI) { a = (i <= lane) ? a : 0.f; c = (i + 1 <= lane) ? c : 0.f; }
+    sum0 += a;
+    sum1 += c;
+    out[i >> 1] = pack_bf16x2(a, c);
+  }
+}
+// mode: 0 = chunk fully visible, 1 = triangular (diagonal chunk), 2 = fully masked
+__device__ __forceinline__ void chunk_max_mode(int mode, const uint32_t (&s)[32], int lane, float& m0, float& m1) {
+  if (mode == 0) chunk_max<false>(s, lane, m0, m1);
+  else if (mode == 1) chunk_max<true>(s, lane, m0, m1);
+}
+__device__ __forceinline__ void chunk_exp_mode(int mode, const uint32_t (&s)[32], int lane, float scale_log2, float neg_m, float& sum0,
+                                               float& sum1, uint32_t (&out)[16]) {
+  if (mode == 0) chunk_exp<false>(s, lane, scale_log2, neg_m, sum0, sum1, out);
+  else if (mode == 1) chunk_exp<true>(s, lane, scale_log2, neg_m, sum0, sum1, out);
+  else {
+#pragma unroll
+    for (int i = 0; i < 16; ++i) out[i] = 0u;
+  }
+}
+__device__ __forceinline__ void named_bar_sync(int id, int nthreads) {
+  asm volatile("bar.sync %0, %1;" ::"r"(id), "r"(nthreads) : "memory");
+}
+
+__global__ void __launch_bounds__(FWD_THREADS, 2) attn_fwd_kernel(const __grid_constant__ CUtensorMap tmQKV,
+                                                                  const __grid_constant__ CUtensorMap tmPFX, const AttnParams p) {
   extern __shared__ uint8_t smem_raw[];
   uint8_t* smem = reinterpret_cast<uint8_t*>((reinterpret_cast<uintptr_t>(smem_raw) + 1023) & ~uintptr_t(1023));
-  uint8_t* sQ = smem;
-  uint8_t* sK = smem + TILE_BYTES;
-  uint8_t* sV = smem + 2 * TILE_BYTES;
-  uint8_t* sP = smem + 3 * TILE_BYTES;   // two tiles
-  float* sak = reinterpret_cast<float*>(smem + 5 * TILE_BYTES);
-  float* sav = sak + MAX_PREFIX * HD;
-  uint64_t* bars = reinterpret_cast<uint64_t*>(sav + MAX_PREFIX * HD);
-  uint64_t *q_full = bars, *k_full = bars + 1, *v_full = bars + 2, *s_full = bars + 3, *p_full = bars + 4, *o_done = bars + 5;
-  uint32_t* tmem_slot = reinterpret_cast<uint32_t*>(bars + 6);
+  uint8_t* sQ = smem;                    // [2 items]
+  uint8_t* sK = smem + FWD_OFF_K;        // [2 stages]
+  uint8_t* sV = smem + FWD_OFF_V;        // [2 stages]
+  uint8_t* sAK = smem + FWD_OFF_AK;      // [16 x 64] prefix keys (rows >= prefix_len are zero)
+  uint8_t* sAV = smem + FWD_OFF_AV;
+  float* sX = reinterpret_cast<float*>(smem + FWD_OFF_X);   // row max / row sum exchange between the two halves of a row
+  float* sPW = reinterpret_cast<float*>(smem + FWD_OFF_PW);  // gate * softmax over the prefix keys, [a][row]
+  uint64_t* bars = reinterpret_cast<uint64_t*>(smem + FWD_OFF_BAR);
+  uint64_t *q_full = bars /*[2]*/, *k_full = bars + 2 /*[2]*/, *k_free = bars + 4 /*[2]*/, *v_full = bars + 6 /*[2]*/,
+           *v_free = bars + 8 /*[2]*/, *s_full = bars + 10, *s_free = bars + 11, *p_full = bars + 12, *o_done = bars + 13,
+           *pfx_full = bars + 14;
+  uint32_t* tmem_slot = reinterpret_cast<uint32_t*>(bars + 16);
 
   const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
+  TRC_DECL
+  TRC(0);
   const int nq = (p.T + ATT_BQ - 1) / ATT_BQ;
-  const int qi = nq - 1 - blockIdx.x;   // heavy tiles first
   const int h = blockIdx.y, b = blockIdx.z;
   const int g = h / p.qpk;
   const int q_slot = g * (p.qpk + 2) + (h % p.qpk), k_slot = g * (p.qpk + 2) + p.qpk, v_slot = k_slot + 1;
   const int row_base = b * p.T;
-  const int q0 = qi * ATT_BQ;
-  const int nkv = qi + 1;
+  const int qi_first = nq - 1 - (int)blockIdx.x, qi_second = (int)blockIdx.x;
+  const int n_items = (qi_first == qi_second) ? 1 : 2;
+  const bool has_prefix = p.prefix_len > 0;
 
-  if (threadIdx.x == 0) {
-    mbar_init(q_full, 1); mbar_init(k_full, 1); mbar_init(v_full, 1);
-    mbar_init(s_full, 1); mbar_init(p_full, 128); mbar_init(o_done, 1);
+  if (warp == FWD_SM_WARPS && lane == 0) {
+    // the producer thread initialises the barriers and starts the first loads before the CTA-wide sync
+    for (int i = 0; i < 2; ++i) {
+      mbar_init(&q_full[i], 1); mbar_init(&k_full[i], 1); mbar_init(&k_free[i], 1); mbar_init(&v_full[i], 1); mbar_init(&v_free[i], 1);
+    }
+    mbar_init(s_full, 1); mbar_init(s_free, FWD_SM_WARPS * 32); mbar_init(p_full, FWD_SM_WARPS * 32); mbar_init(o_done, 1);
+    mbar_init(pfx_full, 1);
     fence_barrier_init();
-    tma_prefetch_desc(&tmQKV);
+    mbar_expect_tx(&q_full[0], TILE_BYTES);
+    tma_load_3d(sQ, &tmQKV, 0, q_slot, row_base + qi_first * ATT_BQ, &q_full[0]);
+    if (has_prefix) {
+      mbar_expect_tx(pfx_full, 4096);
+      tma_load_3d(sAK, &tmPFX, 0, k_slot, 0, pfx_full);
+      tma_load_3d(sAV, &tmPFX, 0, v_slot, 0, pfx_full);
+    }
+    mbar_expect_tx(&k_full[0], TILE_BYTES);
+    tma_load_3d(sK, &tmQKV, 0, k_slot, row_base, &k_full[0]);
+    mbar_expect_tx(&v_full[0], TILE_BYTES);
+    tma_load_3d(sV, &tmQKV, 0, v_slot, row_base, &v_full[0]);
   }
-  if (warp == 5) { tmem_alloc(tmem_slot, 256); tmem_relinquish(); }
-  if (p.prefix_len > 0) load_prefix_to_smem(p, g, sak, sav);
+  if (warp == FWD_SM_WARPS + 1) { tmem_alloc(tmem_slot, 256); tmem_relinquish(); }
   tc_fence_before();
   __syncthreads();
   tc_fence_after();
   const uint32_t tmem = *tmem_slot;
-  const uint32_t tS = tmem, tO = tmem + 128;
+  const uint32_t tS = tmem, tO = tmem + 128, tP = tmem + 192;
 
-  if (warp == 4) {
+  if (warp == FWD_SM_WARPS) {
+    // ---------------- TMA producer (tile 0 of item 0 and Q of item 0 are already in flight) ----------------
     if (lane == 0) {
-      mbar_expect_tx(q_full, TILE_BYTES);
-      tma_load_3d(sQ, &tmQKV, 0, q_slot, row_base + q0, q_full);
-      for (int j = 0; j < nkv; ++j) {
-        if (j > 0) mbar_wait(s_full, (j - 1) & 1);       // K(j-1) consumed by S(j-1)
-        mbar_expect_tx(k_full, TILE_BYTES);
-        tma_load_3d(sK, &tmQKV, 0, k_slot, row_base + j * ATT_BK, k_full);
-        if (j > 0) mbar_wait(o_done, (j - 1) & 1);       // V(j-1) consumed by PV(j-1)
-        mbar_expect_tx(v_full, TILE_BYTES);
-        tma_load_3d(sV, &tmQKV, 0, v_slot, row_base + j * ATT_BK, v_full);
+      if (n_items == 2) {
+        mbar_expect_tx(&q_full[1], TILE_BYTES);
+        tma_load_3d(sQ + TILE_BYTES, &tmQKV, 0, q_slot, row_base + qi_second * ATT_BQ, &q_full[1]);
+      }
+      int n = 0;
+      for (int it = 0; it < n_items; ++it) {
+        const int qi = it ? qi_second : qi_first;
+        for (int j = 0; j <= qi; ++j, ++n) {
+          if (n == 0) continue;
+          const int st = n & 1;
+          if (n >= 2) mbar_wait(&k_free[st], ((n >> 1) - 1) & 1);
+          mbar_expect_tx(&k_full[st], TILE_BYTES);
+          tma_load_3d(sK + st * TILE_BYTES, &tmQKV, 0, k_slot, row_base + j * ATT_BK, &k_full[st]);
+          if (n >= 2) mbar_wait(&v_free[st], ((n >> 1) - 1) & 1);
+          mbar_expect_tx(&v_full[st], TILE_BYTES);
+          tma_load_3d(sV + st * TILE_BYTES, &tmQKV, 0, v_slot, row_base + j * ATT_BK, &v_full[st]);
+        }
       }
     }
-  } else if (warp == 5) {
+  } else if (warp == FWD_SM_WARPS + 1) {
+    // ---------------- MMA issuer ----------------
     if (lane == 0) {
-      mbar_wait(q_full, 0);
-      for (int j = 0; j < nkv; ++j) {
-        mbar_wait(k_full, j & 1);
+      int n = 0, es = 0, ep = 0;
+      if (has_prefix) mbar_wait(pfx_full, 0);
+      for (int it = 0; it < n_items; ++it) {
+        const int nkv = (it ? qi_second : qi_first) + 1;
+        const uint32_t q_addr = smem_u32(sQ + it * TILE_BYTES);
+        mbar_wait(&q_full[it], 0);
         tc_fence_after();
-        mma_qk(tS, smem_u32(sQ), smem_u32(sK));
+        if (has_prefix) {
+          constexpr uint32_t idesc16 = umma_idesc_bf16(128, 16, 0, 0);
+#pragma unroll
+          for (int k = 0; k < 4; ++k)
+            tc_mma_ss(tS, umma_desc_sw128(q_addr + k * 32, 16, 1024), umma_desc_sw128(smem_u32(sAK) + k * 32, 16, 1024), idesc16, k != 0);
+          tc_commit(s_full);
+          mbar_wait(s_free, es & 1); ++es;
+          tc_fence_after();
+        }
+        mbar_wait(&k_full[n & 1], (n >> 1) & 1);
+        tc_fence_after();
+        mma_qk(tS, q_addr, smem_u32(sK + (n & 1) * TILE_BYTES));
+        tc_commit(&k_free[n & 1]);
         tc_commit(s_full);
-        mbar_wait(p_full, j & 1);
-        mbar_wait(v_full, j & 1);
-        tc_fence_after();
-        mma_pv(tO, smem_u32(sP), smem_u32(sV), j > 0);
-        tc_commit(o_done);
+        for (int j = 0; j < nkv; ++j, ++n) {
+          mbar_wait(s_free, es & 1); ++es;           // S(j) is in registers
+          tc_fence_after();
+          if (j + 1 < nkv) {
+            const int n1 = n + 1;
+            mbar_wait(&k_full[n1 & 1], (n1 >> 1) & 1);
+            tc_fence_after();
+            mma_qk(tS, q_addr, smem_u32(sK + (n1 & 1) * TILE_BYTES));
+            tc_commit(&k_free[n1 & 1]);
+            tc_commit(s_full);
+          }
+          mbar_wait(p_full, ep & 1); ++ep;           // P(j) is in TMEM, O rescaled if needed
+          mbar_wait(&v_full[n & 1], (n >> 1) & 1);
+          tc_fence_after();
+          mma_pv_ts(tO, tP, smem_u32(sV + (n & 1) * TILE_BYTES), 8, j > 0);
+          tc_commit(&v_free[n & 1]);
+          tc_commit(o_done);
+        }
+        if (has_prefix) {
+          mbar_wait(p_full, ep & 1); ++ep;
+          tc_fence_after();
+          mma_pv_ts(tO, tP, smem_u32(sAV), 1, true);
+          tc_commit(o_done);
+        }
       }
     }
   } else {
-    // ---- softmax / epilogue: thread = query row ----
-    const int r = warp * 32 + lane;
-    const int tq = q0 + r;
-    const uint32_t lane_off = (uint32_t)(warp * 32) << 16;
-    float m2 = -INFINITY, l = 0.f;
-    for (int j = 0; j < nkv; ++j) {
-      mbar_wait(s_full, j & 1);
-      tc_fence_after();
-      const int kv0 = j * ATT_BK;
-      const bool diag = (j == qi);
-      float mx = -INFINITY;
-#pragma unroll 1
-      for (int c = 0; c < 4; ++c) {
-        uint32_t v[32];
-        tmem_ld32(tS + lane_off + c * 32, v);
-        tmem_wait_ld();
-#pragma unroll
-        for (int i = 0; i < 32; ++i) {
-          float s = __uint_as_float(v[i]);
-          if (diag && kv0 + c * 32 + i > tq) s = -INFINITY;
-          mx = fmaxf(mx, s);
-        }
-      }
-      const float m_new = fmaxf(m2, mx * p.scale_log2);
-      const float alpha = exp2f(m2 - m_new);
-      if (j > 0) {
-        mbar_wait(o_done, (j - 1) & 1);   // PV(j-1) done: O may be rescaled, P may be overwritten
-        tc_fence_after();
-#pragma unroll 1
-        for (int c = 0; c < 2; ++c) {
-          uint32_t v[32];
-          tmem_ld32(tO + lane_off + c * 32, v);
-          tmem_wait_ld();
-#pragma unroll
-          for (int i = 0; i < 32; ++i) v[i] = __float_as_uint(__uint_as_float(v[i]) * alpha);
-          tmem_st32(tO + lane_off + c * 32, v);
-        }
-        tmem_wait_st();
-      }
-      float rowsum = 0.f;
-#pragma unroll 1
-      for (int c = 0; c < 4; ++c) {
-        uint32_t v[32];
-        tmem_ld32(tS + lane_off + c * 32, v);
-        tmem_wait_ld();
-        float f[32];
-#pragma unroll
-        for (int i = 0; i < 32; ++i) {
-          float e = exp2f(__uint_as_float(v[i]) * p.scale_log2 - m_new);
-          if (diag && kv0 + c * 32 + i > tq) e = 0.f;
-          f[i] = e;
-          rowsum += e;
-        }
-        store_a_chunk(sP, r, c, f);
-      }
-      l = l * alpha + rowsum;
-      m2 = m_new;
-      fence_proxy_async_smem();
-      tc_fence_before();
-      mbar_arrive(p_full);
-    }
-    mbar_wait(o_done, (nkv - 1) & 1);
-    tc_fence_after();
-    const float inv_l = 1.f / l;
-    // gated prefix: its own softmax over the aT prefix keys (no RoPE on them), then gate[h] * (p_a @ av)
-    float pw[MAX_PREFIX];
+    // ---------------- softmax / epilogue: two threads per query row, 64 score columns each ----------------
+    const int quad = warp & 3, hf = warp >> 2;
+    const int r = quad * 32 + lane;
+    const uint32_t lane_off = (uint32_t)(quad * 32) << 16;
     const int aT = p.prefix_len;
-    if (aT > 0) {
-      float sp[MAX_PREFIX];
+    const float sl2 = p.scale_log2;
+    int fs = 0;       // s_full events consumed
+    int np = 0;       // p_full arrivals made (one o_done event follows each)
+    int wo = 0;       // o_done events waited for
+    int xc = 0;       // exchanges through sX (parity selects the buffer)
+    for (int it = 0; it < n_items; ++it) {
+      const int qi = it ? qi_second : qi_first;
+      const int nkv = qi + 1;
+      const int tq = qi * ATT_BQ + r;
+      if (has_prefix) {
+        mbar_wait(s_full, fs & 1); ++fs;
+        tc_fence_after();
+        uint32_t v[16];
+        tmem_ld16(tS + lane_off, v);
+        tmem_wait_ld();
+        tc_fence_before();
+        mbar_arrive(s_free);
+        if (hf == 0) {
+          float mx = -INFINITY;
 #pragma unroll
-      for (int a = 0; a < MAX_PREFIX; ++a) sp[a] = 0.f;
-#pragma unroll 1
-      for (int c8 = 0; c8 < 8; ++c8) {
-        float qv[8];
-        unpack8(*reinterpret_cast<const uint4*>(sQ + r * 128 + ((c8 ^ (r & 7)) << 4)), qv);
+          for (int a = 0; a < MAX_PREFIX; ++a) if (a < aT) mx = fmaxf(mx, __uint_as_float(v[a]));
+          float sum = 0.f;
 #pragma unroll
-        for (int a = 0; a < MAX_PREFIX; ++a) {
-          if (a < aT) {
-#pragma unroll
-            for (int i = 0; i < 8; ++i) sp[a] += qv[i] * sak[a * HD + c8 * 8 + i];
+          for (int a = 0; a < MAX_PREFIX; ++a) {
+            const float e = (a < aT) ? fast_exp2((__uint_as_float(v[a]) - mx) * sl2) : 0.f;
+            v[a] = __float_as_uint(e);
+            sum += e;
           }
+          const float gs = p.gate[h] / sum;
+#pragma unroll
+          for (int a = 0; a < MAX_PREFIX; ++a) sPW[a * 128 + r] = __uint_as_float(v[a]) * gs;   // read back by this thread only
         }
       }
-      float mxp = -INFINITY;
+      float m_ref = -INFINITY, l = 0.f;
+      for (int j = 0; j < nkv; ++j) {
+        mbar_wait(s_full, fs & 1); ++fs;
+        TRC(1);
+        tc_fence_after();
+        uint32_t s0[32], s1[32];
+        tmem_ld32(tS + lane_off + 64 * hf, s0);
+        tmem_ld32(tS + lane_off + 64 * hf + 32, s1);
+        tmem_wait_ld();
+        TRC(2);
+        tc_fence_before();
+        mbar_arrive(s_free);
+        // diagonal tile: rows of quad w see 32-column chunks c < w unmasked, chunk w triangular, chunks c > w masked
+        int mode0 = 0, mode1 = 0;
+        if (j == qi) {
+          const int c0 = 2 * hf, c1 = 2 * hf + 1;
+          mode0 = c0 < quad ? 0 : (c0 == quad ? 1 : 2);
+          mode1 = c1 < quad ? 0 : (c1 == quad ? 1 : 2);
+        }
+        float mx0 = -INFINITY, mx1 = -INFINITY;
+        chunk_max_mode(mode0, s0, lane, mx0, mx1);
+        chunk_max_mode(mode1, s1, lane, mx0, mx1);
+        float* xb = sX + (xc & 1) * 256; ++xc;
+        xb[hf * 128 + r] = fmaxf(mx0, mx1);
+        named_bar_sync(1, FWD_SM_WARPS * 32);
+        const float m_new = fmaxf(m_ref, fmaxf(fmaxf(mx0, mx1), xb[(hf ^ 1) * 128 + r]) * sl2);
+        TRC(3);
+        // lazy rescaling: keep the stale reference max while the true max is within 2^8 of it
+        if (__any_sync(0xffffffffu, m_new - m_ref > RESCALE_THRESHOLD)) {
+          const float alpha = fast_exp2(m_ref - m_new);     // 0 on the first tile (m_ref = -inf)
+          l *= alpha;
+          m_ref = m_new;
+          if (j > 0) {
+            while (wo < np) { mbar_wait(o_done, wo & 1); ++wo; }
+            tc_fence_after();
 #pragma unroll
-      for (int a = 0; a < MAX_PREFIX; ++a) if (a < aT) mxp = fmaxf(mxp, sp[a]);
-      float sum = 0.f;
+            for (int c = 0; c < 2; ++c) {
+              uint32_t o[16];
+              tmem_ld16(tO + lane_off + 32 * hf + c * 16, o);
+              tmem_wait_ld();
 #pragma unroll
-      for (int a = 0; a < MAX_PREFIX; ++a) {
-        pw[a] = (a < aT) ? exp2f((sp[a] - mxp) * p.scale_log2) : 0.f;
-        sum += pw[a];
+              for (int i = 0; i < 16; ++i) o[i] = __float_as_uint(__uint_as_float(o[i]) * alpha);
+              tmem_st16(tO + lane_off + 32 * hf + c * 16, o);
+            }
+          }
+        }
+        while (wo < np) { mbar_wait(o_done, wo & 1); ++wo; }   // P V(j-1) has read the previous P
+        TRC(4);
+        tc_fence_after();
+        const float neg_m = -m_ref;
+        float sum0 = 0.f, sum1 = 0.f;
+        uint32_t pk[16];
+        chunk_exp_mode(mode0, s0, lane, sl2, neg_m, sum0, sum1, pk);
+        tmem_st16(tP + lane_off + 32 * hf, pk);
+        chunk_exp_mode(mode1, s1, lane, sl2, neg_m, sum0, sum1, pk);
+        tmem_st16(tP + lane_off + 32 * hf + 16, pk);
+        l += sum0 + sum1;
+        TRC(5);
+        tmem_wait_st();
+        TRC(6);
+        tc_fence_before();
+        mbar_arrive(p_full); ++np;
       }
-      const float gs = p.gate[h] / sum;
+      // total row sum: exchange the two halves
+      {
+        float* xb = sX + (xc & 1) * 256; ++xc;
+        xb[hf * 128 + r] = l;
+        named_bar_sync(1, FWD_SM_WARPS * 32);
+        l += xb[(hf ^ 1) * 128 + r];
+      }
+      if (has_prefix) {
+        // A operand of the last MMA: l * gate * softmax_a, so that the common 1/l below leaves gate * prefix
+        while (wo < np) { mbar_wait(o_done, wo & 1); ++wo; }
+        tc_fence_after();
+        if (hf == 0) {
+          uint32_t pk[8];
 #pragma unroll
-      for (int a = 0; a < MAX_PREFIX; ++a) pw[a] *= gs;
-    }
-    // TMEM loads are .sync.aligned: every lane issues them; only the global stores are predicated.
-    const bool valid = tq < p.T;
-    bf16* orow = p.out + (long long)(row_base + (valid ? tq : 0)) * (p.H * HD) + h * HD;
-#pragma unroll 1
-    for (int c = 0; c < 2; ++c) {
-      uint32_t v[32];
-      tmem_ld32(tO + lane_off + c * 32, v);
+          for (int a = 0; a < 8; ++a) pk[a] = pack_bf16x2(sPW[(2 * a) * 128 + r] * l, sPW[(2 * a + 1) * 128 + r] * l);
+          tmem_st8(tP + lane_off, pk);
+          tmem_wait_st();
+        }
+        tc_fence_before();
+        mbar_arrive(p_full); ++np;
+      }
+      while (wo < np) { mbar_wait(o_done, wo & 1); ++wo; }
+      TRC(7);
+      tc_fence_after();
+      const float inv_l = 1.f / l;
+      // TMEM loads are .sync.aligned: every lane issues them; only the global stores are predicated.
+      const bool valid = tq < p.T;
+      bf16* orow = p.out + (long long)(row_base + (valid ? tq : 0)) * (p.H * HD) + h * HD + 32 * hf;
+      uint32_t o[32];
+      tmem_ld32(tO + lane_off + 32 * hf, o);
       tmem_wait_ld();
-      float f[32];
-#pragma unroll
-      for (int i = 0; i < 32; ++i) f[i] = __uint_as_float(v[i]) * inv_l;
-      if (aT > 0) {
-#pragma unroll
-        for (int a = 0; a < MAX_PREFIX; ++a) {
-          if (a < aT) {
-#pragma unroll
-            for (int i = 0; i < 32; ++i) f[i] += pw[a] * sav[a * HD + c * 32 + i];
-          }
-        }
-      }
+      tc_fence_before();
       if (valid) {
-        uint4* o4 = reinterpret_cast<uint4*>(orow + c * 32);
+        uint4* o4 = reinterpret_cast<uint4*>(orow);
 #pragma unroll
         for (int i = 0; i < 4; ++i) {
-          float t8[8];
-#pragma unroll
-          for (int k = 0; k < 8; ++k) t8[k] = f[8 * i + k];
-          o4[i] = pack8(t8);
+          uint4 u;
+          u.x = pack_bf16x2(__uint_as_float(o[8 * i + 0]) * inv_l, __uint_as_float(o[8 * i + 1]) * inv_l);
+          u.y = pack_bf16x2(__uint_as_float(o[8 * i + 2]) * inv_l, __uint_as_float(o[8 * i + 3]) * inv_l);
+          u.z = pack_bf16x2(__uint_as_float(o[8 * i + 4]) * inv_l, __uint_as_float(o[8 * i + 5]) * inv_l);
+          u.w = pack_bf16x2(__uint_as_float(o[8 * i + 6]) * inv_l, __uint_as_float(o[8 * i + 7]) * inv_l);
+          o4[i] = u;
         }
+        if (hf == 0) p.lse[((long long)b * p.H + h) * p.T + tq] = (m_ref + log2f(l)) * LN2;
       }
+      TRC(8);
     }
-    if (valid) p.lse[((long long)b * p.H + h) * p.T + tq] = (m2 + log2f(l)) * LN2;
   }
+  if (warp == 0) TRC_DUMP("sm");
   tc_fence_before();
   __syncthreads();
-  if (warp == 5) { tc_fence_after(); tmem_dealloc(tmem, 256); }
+  if (warp == FWD_SM_WARPS + 1) { tc_fence_after(); tmem_dealloc(tmem, 256); }
 }
 
 // =================================================================================================
@@ -607,171 +768,278 @@ __global__ void __launch_bounds__(BWD_THREADS, 1) attn_bwd_dq_kernel(const __gri
 }
 
 // =================================================================================================
-// backward dK/dV: CTA = (k tile j, kv head g, batch); loops over the q heads of the group and q tiles
-// i >= j.  Thread = key row.  S^T = K Q^T, dP^T = V dO^T -> P^T, dS^T (smem) -> dV += P^T dO, dK += dS^T Q.
-// Q/dO (+ their lse/delta) are double buffered.
+// backward dK/dV.  CTA = (k tile pair {nq-1-x, x}, kv group, batch), one CTA per SM, flat loop over the
+// qpk heads of the group and the q tiles i >= j of each key tile j (every CTA does qpk*(nq+1) iterations).
+// The key row is the TMEM lane: S^T = K Q^T and dP^T = V dO^T (SS MMAs) land in TMEM, eight softmax warps
+// (two threads per key row, 64 query columns each) pull them into registers (-> st_free: the MMA warp issues
+// the NEXT iteration's S^T / dP^T right away), form P^T = 2^(s - lse) and dS^T = P^T (dP^T - delta), and
+// write both back to TMEM as bf16 A operands of dV += P^T dO and dK += dS^T Q (TS MMAs).  dV / dK stay in
+// TMEM over all heads of the group (the GQA reduction is free).  Q / dO tiles (+ their lse / delta rows) are
+// double buffered; the K/V tiles of the two key tiles of the pair have a buffer each.
 // =================================================================================================
-constexpr int DKV_SMEM = 10 * TILE_BYTES + 4 * 128 * 4 + 1024 + 128;
+constexpr int DKV_SM_WARPS = 8;
+constexpr int DKV_THREADS = (DKV_SM_WARPS + 2) * 32;
+constexpr int DKV_OFF_QDO = 4 * TILE_BYTES, DKV_OFF_STAT = 8 * TILE_BYTES, DKV_OFF_BAR = DKV_OFF_STAT + 2 * 256 * 4;
+constexpr int DKV_SMEM = DKV_OFF_BAR + 256 + 1024;
 
-__global__ void __launch_bounds__(BWD_THREADS, 1) attn_bwd_dkv_kernel(const __grid_constant__ CUtensorMap tmQKV,
+// D[128 x 64] (+)= A[128 x 128] (TMEM, bf16 pairs per column) * B[128 x 64] (smem tile [k rows][64], MN-major)
+__device__ __forceinline__ void mma_ts_k128(uint32_t d_tmem, uint32_t a_tmem, uint32_t b_smem, bool accumulate) {
+  constexpr uint32_t idesc = umma_idesc_bf16(128, 64, 0, 1);
+#pragma unroll
+  for (int k = 0; k < 8; ++k)
+    tc_mma_ts(d_tmem, a_tmem + k * 8, umma_desc_sw128(b_smem + k * 2048, 8192, 1024), idesc, accumulate || k != 0);
+}
+
+// One 32-column chunk of the backward elementwise step.  MODE 0: all visible, 1: columns <= lane visible,
+// 2: columns >= lane visible, 3: nothing visible.  lse2 / delta come per column (COLSTAT, from smem) or per row.
+template <int MODE, bool COLSTAT, bool WANT_P>
+__device__ __forceinline__ void bwd_chunk(const uint32_t (&s)[32], const uint32_t (&dp)[32], int lane, float sl2, const float* lse2c,
+                                          const float* deltac, float lse2r, float deltar, uint32_t (&pp)[16], uint32_t (&ds)[16]) {
+  if (MODE == 3) {
+#pragma unroll
+    for (int i = 0; i < 16; ++i) { if (WANT_P) pp[i] = 0u; ds[i] = 0u; }
+    return;
+  }
+#pragma unroll
+  for (int i4 = 0; i4 < 8; ++i4) {
+    float l4[4], d4[4];
+    if (COLSTAT) {
+      const float4 a = *reinterpret_cast<const float4*>(lse2c + 4 * i4);
+      const float4 c = *reinterpret_cast<const float4*>(deltac + 4 * i4);
+      l4[0] = a.x; l4[1] = a.y; l4[2] = a.z; l4[3] = a.w;
+      d4[0] = c.x; d4[1] = c.y; d4[2] = c.z; d4[3] = c.w;
+    } else {
+#pragma unroll
+      for (int k = 0; k < 4; ++k) { l4[k] = lse2r; d4[k] = deltar; }
+    }
+    float pr[4], dv[4];
+#pragma unroll
+    for (int k = 0; k < 4; ++k) {
+      const int i = 4 * i4 + k;
+      float e = fast_exp2(fmaf(__uint_as_float(s[i]), sl2, -l4[k]));
+      if (MODE == 1) e = (i <= lane) ? e : 0.f;
+      if (MODE == 2) e = (i >= lane) ? e : 0.f;
+      pr[k] = e;
+      dv[k] = e * (__uint_as_float(dp[i]) - d4[k]);
+    }
+    if (WANT_P) { pp[2 * i4] = pack_bf16x2(pr[0], pr[1]); pp[2 * i4 + 1] = pack_bf16x2(pr[2], pr[3]); }
+    ds[2 * i4] = pack_bf16x2(dv[0], dv[1]);
+    ds[2 * i4 + 1] = pack_bf16x2(dv[2], dv[3]);
+  }
+}
+template <bool COLSTAT, bool WANT_P>
+__device__ __forceinline__ void bwd_chunk_mode(int mode, const uint32_t (&s)[32], const uint32_t (&dp)[32], int lane, float sl2,
+                                               const float* lse2c, const float* deltac, float lse2r, float deltar, uint32_t (&pp)[16],
+                                               uint32_t (&ds)[16]) {
+  if (mode == 0) bwd_chunk<0, COLSTAT, WANT_P>(s, dp, lane, sl2, lse2c, deltac, lse2r, deltar, pp, ds);
+  else if (mode == 1) bwd_chunk<1, COLSTAT, WANT_P>(s, dp, lane, sl2, lse2c, deltac, lse2r, deltar, pp, ds);
+  else if (mode == 2) bwd_chunk<2, COLSTAT, WANT_P>(s, dp, lane, sl2, lse2c, deltac, lse2r, deltar, pp, ds);
+  else bwd_chunk<3, COLSTAT, WANT_P>(s, dp, lane, sl2, lse2c, deltac, lse2r, deltar, pp, ds);
+}
+
+// 16 + 16 accumulator columns (d in [16hf, 16hf+16) and the matching d + 32) -> bf16 row segments in global memory,
+// optionally through the conjugate RoPE rotation at position `pos`.
+__device__ __forceinline__ void store_rot_pairs(bf16* row, int hf, uint32_t (&lo)[16], uint32_t (&hi)[16], float scale, const bf16* cs,
+                                                const bf16* sn, int pos) {
+  float a[16], c[16];
+#pragma unroll
+  for (int i = 0; i < 16; ++i) { a[i] = __uint_as_float(lo[i]) * scale; c[i] = __uint_as_float(hi[i]) * scale; }
+  if (cs) {
+    const uint4* c4 = reinterpret_cast<const uint4*>(cs + (long long)pos * 64 + 16 * hf);
+    const uint4* s4 = reinterpret_cast<const uint4*>(sn + (long long)pos * 64 + 16 * hf);
+#pragma unroll
+    for (int i = 0; i < 2; ++i) {
+      float cc[8], ss[8];
+      unpack8(c4[i], cc);
+      unpack8(s4[i], ss);
+#pragma unroll
+      for (int j = 0; j < 8; ++j) {
+        const float x = a[8 * i + j], y = c[8 * i + j];
+        a[8 * i + j] = x * cc[j] + y * ss[j];
+        c[8 * i + j] = y * cc[j] - x * ss[j];
+      }
+    }
+  }
+  uint4* plo = reinterpret_cast<uint4*>(row + 16 * hf);
+  uint4* phi = reinterpret_cast<uint4*>(row + 32 + 16 * hf);
+#pragma unroll
+  for (int i = 0; i < 2; ++i) {
+    float t8[8], u8[8];
+#pragma unroll
+    for (int j = 0; j < 8; ++j) { t8[j] = a[8 * i + j]; u8[j] = c[8 * i + j]; }
+    plo[i] = pack8(t8);
+    phi[i] = pack8(u8);
+  }
+}
+
+__global__ void __launch_bounds__(DKV_THREADS, 1) attn_bwd_dkv_kernel(const __grid_constant__ CUtensorMap tmQKV,
                                                                        const __grid_constant__ CUtensorMap tmDO, const AttnParams p) {
   extern __shared__ uint8_t smem_raw[];
   uint8_t* smem = reinterpret_cast<uint8_t*>((reinterpret_cast<uintptr_t>(smem_raw) + 1023) & ~uintptr_t(1023));
-  uint8_t* sK = smem;
-  uint8_t* sV = smem + TILE_BYTES;
-  uint8_t* sQ = smem + 2 * TILE_BYTES;     // [2 stages]
-  uint8_t* sdO = smem + 4 * TILE_BYTES;    // [2 stages]
-  uint8_t* sPT = smem + 6 * TILE_BYTES;    // two tiles
-  uint8_t* sdST = smem + 8 * TILE_BYTES;   // two tiles
-  float* s_lse = reinterpret_cast<float*>(smem + 10 * TILE_BYTES);   // [2][128]
-  float* s_delta = s_lse + 256;                                       // [2][128]
-  uint64_t* bars = reinterpret_cast<uint64_t*>(s_delta + 256);
-  uint64_t *kv_full = bars, *qdo_full = bars + 1 /*[2]*/, *qdo_free = bars + 3 /*[2]*/, *st_full = bars + 5, *pds_full = bars + 6,
-           *acc_done = bars + 7;
-  uint32_t* tmem_slot = reinterpret_cast<uint32_t*>(bars + 8);
+  uint8_t* sKV = smem;                       // [2 items][K | V]
+  uint8_t* sQdO = smem + DKV_OFF_QDO;        // [2 stages][Q | dO]
+  float* sStat = reinterpret_cast<float*>(smem + DKV_OFF_STAT);   // [2 stages][lse*log2e 128 | delta 128]
+  uint64_t* bars = reinterpret_cast<uint64_t*>(smem + DKV_OFF_BAR);
+  uint64_t *kv_full = bars /*[2]*/, *qdo_full = bars + 2 /*[2]*/, *qdo_free = bars + 4 /*[2]*/, *st_full = bars + 6, *st_free = bars + 7,
+           *pds_full = bars + 8, *acc_done = bars + 9;
+  uint32_t* tmem_slot = reinterpret_cast<uint32_t*>(bars + 10);
 
   const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
   const int nq = (p.T + ATT_BQ - 1) / ATT_BQ;
-  const int j = blockIdx.x;               // k tile
   const int g = blockIdx.y, b = blockIdx.z;
   const int k_slot = g * (p.qpk + 2) + p.qpk, v_slot = k_slot + 1;
   const int row_base = b * p.T;
-  const int kv0 = j * ATT_BK;
-  const int n_qt = nq - j;                // q tiles j..nq-1
-  const int nit = p.qpk * n_qt;
+  const int j_first = nq - 1 - (int)blockIdx.x, j_second = (int)blockIdx.x;
+  const int n_items = (j_first == j_second) ? 1 : 2;
 
-  if (threadIdx.x == 0) {
-    mbar_init(kv_full, 1);
-    for (int s = 0; s < 2; ++s) { mbar_init(&qdo_full[s], 1); mbar_init(&qdo_free[s], 1); }
-    mbar_init(st_full, 1); mbar_init(pds_full, 128); mbar_init(acc_done, 1);
+  if (warp == DKV_SM_WARPS && lane == 0) {
+    for (int i = 0; i < 2; ++i) { mbar_init(&kv_full[i], 1); mbar_init(&qdo_full[i], 33); mbar_init(&qdo_free[i], 1); }
+    mbar_init(st_full, 1); mbar_init(st_free, DKV_SM_WARPS * 32); mbar_init(pds_full, DKV_SM_WARPS * 32); mbar_init(acc_done, 1);
     fence_barrier_init();
+    for (int it = 0; it < n_items; ++it) {
+      const int j = it ? j_second : j_first;
+      mbar_expect_tx(&kv_full[it], 2 * TILE_BYTES);
+      tma_load_3d(sKV + it * 2 * TILE_BYTES, &tmQKV, 0, k_slot, row_base + j * ATT_BK, &kv_full[it]);
+      tma_load_3d(sKV + it * 2 * TILE_BYTES + TILE_BYTES, &tmQKV, 0, v_slot, row_base + j * ATT_BK, &kv_full[it]);
+    }
   }
-  if (warp == 5) { tmem_alloc(tmem_slot, 512); tmem_relinquish(); }
+  if (warp == DKV_SM_WARPS + 1) { tmem_alloc(tmem_slot, 512); tmem_relinquish(); }
   tc_fence_before();
   __syncthreads();
   tc_fence_after();
   const uint32_t tmem = *tmem_slot;
-  const uint32_t tST = tmem, tdPT = tmem + 128, tdV = tmem + 256, tdK = tmem + 320;
+  const uint32_t tST = tmem, tdPT = tmem + 128, tPT = tmem + 256, tdST = tmem + 320, tdV = tmem + 384, tdK = tmem + 448;
 
-  if (warp == 4) {
-    if (lane == 0) {
-      mbar_expect_tx(kv_full, 2 * TILE_BYTES);
-      tma_load_3d(sK, &tmQKV, 0, k_slot, row_base + kv0, kv_full);
-      tma_load_3d(sV, &tmQKV, 0, v_slot, row_base + kv0, kv_full);
-      for (int it = 0; it < nit; ++it) {
-        const int s = it & 1;
-        const int hh = it / n_qt, i = j + it % n_qt;
+  if (warp == DKV_SM_WARPS) {
+    // ---------------- producer: Q / dO tiles by TMA, their lse / delta rows by the 32 lanes ----------------
+    int n = 0;
+    for (int item = 0; item < n_items; ++item) {
+      const int j = item ? j_second : j_first;
+      for (int hh = 0; hh < p.qpk; ++hh) {
         const int h = g * p.qpk + hh;
-        if (it >= 2) mbar_wait(&qdo_free[s], ((it >> 1) - 1) & 1);
-        mbar_expect_tx(&qdo_full[s], 2 * TILE_BYTES);
-        tma_load_3d(sQ + s * TILE_BYTES, &tmQKV, 0, g * (p.qpk + 2) + hh, row_base + i * ATT_BQ, &qdo_full[s]);
-        tma_load_3d(sdO + s * TILE_BYTES, &tmDO, 0, h, row_base + i * ATT_BQ, &qdo_full[s]);
+        for (int i = j; i < nq; ++i, ++n) {
+          const int s = n & 1;
+          if (n >= 2) mbar_wait(&qdo_free[s], ((n >> 1) - 1) & 1);
+          if (lane == 0) {
+            mbar_expect_tx(&qdo_full[s], 2 * TILE_BYTES);
+            tma_load_3d(sQdO + s * 2 * TILE_BYTES, &tmQKV, 0, g * (p.qpk + 2) + hh, row_base + i * ATT_BQ, &qdo_full[s]);
+            tma_load_3d(sQdO + s * 2 * TILE_BYTES + TILE_BYTES, &tmDO, 0, h, row_base + i * ATT_BQ, &qdo_full[s]);
+          }
+          const long long sbase = ((long long)b * p.H + h) * p.T;
+#pragma unroll
+          for (int k = 0; k < 4; ++k) {
+            const int c = lane + 32 * k, tq = i * ATT_BQ + c;
+            const bool ok = tq < p.T;
+            sStat[s * 256 + c] = ok ? p.lse[sbase + tq] * LOG2E : INFINITY;   // +inf => p = 0 for padded query rows
+            sStat[s * 256 + 128 + c] = ok ? p.delta[sbase + tq] : 0.f;
+          }
+          mbar_arrive(&qdo_full[s]);
+        }
       }
     }
-  } else if (warp == 5) {
+  } else if (warp == DKV_SM_WARPS + 1) {
+    // ---------------- MMA issuer ----------------
     if (lane == 0) {
-      mbar_wait(kv_full, 0);
-      for (int it = 0; it < nit; ++it) {
-        const int s = it & 1;
-        mbar_wait(&qdo_full[s], (it >> 1) & 1);
-        if (it > 0) mbar_wait(pds_full, (it - 1) & 1);   // S^T/dP^T of the previous iteration consumed
+      int n = 0, nfree = 0, npds = 0;
+      for (int item = 0; item < n_items; ++item) {
+        const int j = item ? j_second : j_first;
+        const int nit = p.qpk * (nq - j);
+        const uint32_t k_addr = smem_u32(sKV + item * 2 * TILE_BYTES), v_addr = k_addr + TILE_BYTES;
+        mbar_wait(&kv_full[item], 0);
+        mbar_wait(&qdo_full[n & 1], (n >> 1) & 1);
+        if (n > 0) { mbar_wait(st_free, nfree & 1); ++nfree; }
         tc_fence_after();
-        mma_qk(tST, smem_u32(sK), smem_u32(sQ + s * TILE_BYTES));
-        mma_qk(tdPT, smem_u32(sV), smem_u32(sdO + s * TILE_BYTES));
+        mma_qk(tST, k_addr, smem_u32(sQdO + (n & 1) * 2 * TILE_BYTES));
+        mma_qk(tdPT, v_addr, smem_u32(sQdO + (n & 1) * 2 * TILE_BYTES + TILE_BYTES));
         tc_commit(st_full);
-        mbar_wait(pds_full, it & 1);
-        tc_fence_after();
-        mma_pv(tdV, smem_u32(sPT), smem_u32(sdO + s * TILE_BYTES), it > 0);
-        mma_pv(tdK, smem_u32(sdST), smem_u32(sQ + s * TILE_BYTES), it > 0);
-        tc_commit(&qdo_free[s]);
-        tc_commit(acc_done);
+        for (int it = 0; it < nit; ++it, ++n) {
+          if (it + 1 < nit) {
+            const int n1 = n + 1;
+            mbar_wait(&qdo_full[n1 & 1], (n1 >> 1) & 1);
+            mbar_wait(st_free, nfree & 1); ++nfree;       // S^T / dP^T of iteration n are in registers
+            tc_fence_after();
+            mma_qk(tST, k_addr, smem_u32(sQdO + (n1 & 1) * 2 * TILE_BYTES));
+            mma_qk(tdPT, v_addr, smem_u32(sQdO + (n1 & 1) * 2 * TILE_BYTES + TILE_BYTES));
+            tc_commit(st_full);
+          }
+          mbar_wait(pds_full, npds & 1); ++npds;          // P^T / dS^T of iteration n are in TMEM
+          tc_fence_after();
+          const uint32_t q_addr = smem_u32(sQdO + (n & 1) * 2 * TILE_BYTES);
+          mma_ts_k128(tdV, tPT, q_addr + TILE_BYTES, it > 0);
+          mma_ts_k128(tdK, tdST, q_addr, it > 0);
+          tc_commit(&qdo_free[n & 1]);
+          tc_commit(acc_done);
+        }
       }
     }
   } else {
-    const int r = warp * 32 + lane;
-    const int tk = kv0 + r;
-    const uint32_t lane_off = (uint32_t)(warp * 32) << 16;
-    for (int it = 0; it < nit; ++it) {
-      const int s = it & 1;
-      const int hh = it / n_qt, i = j + it % n_qt;
-      const int h = g * p.qpk + hh;
-      const int q0 = i * ATT_BQ;
-      // stage lse / delta of this q tile (128 values each) for broadcast reads
-      {
-        const int tq = q0 + r;
-        const bool ok = tq < p.T;
-        const long long si = ((long long)b * p.H + h) * p.T + (ok ? tq : 0);
-        s_lse[s * 128 + r] = ok ? p.lse[si] * LOG2E : INFINITY;   // +inf => p = 0 for padded query rows
-        s_delta[s * 128 + r] = ok ? p.delta[si] : 0.f;
-      }
-      asm volatile("bar.sync 1, 128;" ::: "memory");
-      mbar_wait(st_full, it & 1);
-      tc_fence_after();
-      if (it > 0) mbar_wait(acc_done, (it - 1) & 1);   // P^T / dS^T buffers free
-      const bool diag = (i == j);
-#pragma unroll 1
-      for (int c = 0; c < 4; ++c) {
-        uint32_t sv[32], dv[32];
-        tmem_ld32(tST + lane_off + c * 32, sv);
-        tmem_ld32(tdPT + lane_off + c * 32, dv);
+    // ---------------- softmax-backward warps: two threads per key row, 64 query columns each ----------------
+    const int quad = warp & 3, hf = warp >> 2;
+    const int r = quad * 32 + lane;
+    const uint32_t lane_off = (uint32_t)(quad * 32) << 16;
+    const float sl2 = p.scale_log2;
+    int n = 0, npds = 0, nacc = 0;
+    for (int item = 0; item < n_items; ++item) {
+      const int j = item ? j_second : j_first;
+      const int n_qt = nq - j;
+      const int nit = p.qpk * n_qt;
+      for (int it = 0; it < nit; ++it, ++n) {
+        const int s = n & 1;
+        const int i = j + it % n_qt;
+        mbar_wait(&qdo_full[s], (n >> 1) & 1);      // lse / delta rows of this q tile are in smem
+        mbar_wait(st_full, n & 1);
+        tc_fence_after();
+        uint32_t s0[32], s1[32], d0[32], d1[32];
+        tmem_ld32(tST + lane_off + 64 * hf, s0);
+        tmem_ld32(tST + lane_off + 64 * hf + 32, s1);
+        tmem_ld32(tdPT + lane_off + 64 * hf, d0);
+        tmem_ld32(tdPT + lane_off + 64 * hf + 32, d1);
         tmem_wait_ld();
-        float pt[32], ds[32];
-#pragma unroll
-        for (int ii = 0; ii < 32; ++ii) {
-          const int col = c * 32 + ii;
-          float pr = exp2f(__uint_as_float(sv[ii]) * p.scale_log2 - s_lse[s * 128 + col]);
-          if (diag && tk > q0 + col) pr = 0.f;
-          pt[ii] = pr;
-          ds[ii] = pr * (__uint_as_float(dv[ii]) - s_delta[s * 128 + col]);
+        tc_fence_before();
+        mbar_arrive(st_free);
+        // diagonal tile (i == j): key row r sees query column c iff c >= r; per 32-column chunk cg vs quad
+        int mode0 = 0, mode1 = 0;
+        if (i == j) {
+          const int c0 = 2 * hf, c1 = 2 * hf + 1;
+          mode0 = c0 > quad ? 0 : (c0 == quad ? 2 : 3);
+          mode1 = c1 > quad ? 0 : (c1 == quad ? 2 : 3);
         }
-        store_a_chunk(sPT, r, c, pt);
-        store_a_chunk(sdST, r, c, ds);
+        const float* lse2c = sStat + s * 256 + 64 * hf;
+        const float* deltac = lse2c + 128;
+        uint32_t pp0[16], ds0[16], pp1[16], ds1[16];
+        bwd_chunk_mode<true, true>(mode0, s0, d0, lane, sl2, lse2c, deltac, 0.f, 0.f, pp0, ds0);
+        while (nacc < npds) { mbar_wait(acc_done, nacc & 1); ++nacc; }   // dV / dK MMAs of the previous iteration have read P^T / dS^T
+        tc_fence_after();
+        tmem_st16(tPT + lane_off + 32 * hf, pp0);
+        tmem_st16(tdST + lane_off + 32 * hf, ds0);
+        bwd_chunk_mode<true, true>(mode1, s1, d1, lane, sl2, lse2c + 32, deltac + 32, 0.f, 0.f, pp1, ds1);
+        tmem_st16(tPT + lane_off + 32 * hf + 16, pp1);
+        tmem_st16(tdST + lane_off + 32 * hf + 16, ds1);
+        tmem_wait_st();
+        tc_fence_before();
+        mbar_arrive(pds_full); ++npds;
       }
-      fence_proxy_async_smem();
+      // ---- epilogue of this key tile: dV and dK (scaled, conjugate RoPE) rows to dqkv ----
+      while (nacc < npds) { mbar_wait(acc_done, nacc & 1); ++nacc; }
+      tc_fence_after();
+      const int tk = j * ATT_BK + r;
+      const bool valid = tk < p.T;
+      bf16* rowp = p.dqkv + (long long)(row_base + (valid ? tk : 0)) * p.ld_qkv;
+      uint32_t lo[16], hi[16];
+      tmem_ld16(tdV + lane_off + 16 * hf, lo);
+      tmem_ld16(tdV + lane_off + 32 + 16 * hf, hi);
+      tmem_wait_ld();
+      if (valid) store_rot_pairs(rowp + v_slot * HD, hf, lo, hi, 1.f, nullptr, nullptr, 0);
+      tmem_ld16(tdK + lane_off + 16 * hf, lo);
+      tmem_ld16(tdK + lane_off + 32 + 16 * hf, hi);
+      tmem_wait_ld();
       tc_fence_before();
-      mbar_arrive(pds_full);
-    }
-    mbar_wait(acc_done, (nit - 1) & 1);
-    tc_fence_after();
-    uint32_t a0[32], a1[32];
-    // dV
-    tmem_ld32(tdV + lane_off, a0);
-    tmem_ld32(tdV + lane_off + 32, a1);
-    tmem_wait_ld();
-    if (tk < p.T) {
-      bf16* dv = p.dqkv + (long long)(row_base + tk) * p.ld_qkv + v_slot * HD;
-#pragma unroll
-      for (int i4 = 0; i4 < 4; ++i4) {
-        float x[8], y[8];
-#pragma unroll
-        for (int k = 0; k < 8; ++k) { x[k] = __uint_as_float(a0[8 * i4 + k]); y[k] = __uint_as_float(a1[8 * i4 + k]); }
-        reinterpret_cast<uint4*>(dv)[i4] = pack8(x);
-        reinterpret_cast<uint4*>(dv + 32)[i4] = pack8(y);
-      }
-    }
-    // dK
-    tmem_ld32(tdK + lane_off, a0);
-    tmem_ld32(tdK + lane_off + 32, a1);
-    tmem_wait_ld();
-    if (tk < p.T) {
-      float lo[32], hi[32];
-#pragma unroll
-      for (int i2 = 0; i2 < 32; ++i2) { lo[i2] = __uint_as_float(a0[i2]) * p.scale; hi[i2] = __uint_as_float(a1[i2]) * p.scale; }
-      if (p.rope_cos) rope_conj_halves(lo, hi, p.rope_cos, p.rope_sin, tk);
-      bf16* dk = p.dqkv + (long long)(row_base + tk) * p.ld_qkv + k_slot * HD;
-#pragma unroll
-      for (int i4 = 0; i4 < 4; ++i4) {
-        float x[8], y[8];
-#pragma unroll
-        for (int k = 0; k < 8; ++k) { x[k] = lo[8 * i4 + k]; y[k] = hi[8 * i4 + k]; }
-        reinterpret_cast<uint4*>(dk)[i4] = pack8(x);
-        reinterpret_cast<uint4*>(dk + 32)[i4] = pack8(y);
-      }
+      if (valid) store_rot_pairs(rowp + k_slot * HD, hf, lo, hi, p.scale, p.rope_cos, p.rope_sin, tk);
     }
   }
   tc_fence_before();
   __syncthreads();
-  if (warp == 5) { tc_fence_after(); tmem_dealloc(tmem, 512); }
+  if (warp == DKV_SM_WARPS + 1) { tc_fence_after(); tmem_dealloc(tmem, 512); }
 }
 
 // =================================================================================================
@@ -861,10 +1129,10 @@ __global__ void __launch_bounds__(256) attn_decode_kernel(const bf16* __restrict
 // ---------------------------------------------------------------------------------------------
 // host
 // ---------------------------------------------------------------------------------------------
-static int make_head_map(CUtensorMap* map, const void* base, int slots, long long rows, long long ld) {
+static int make_head_map(CUtensorMap* map, const void* base, int slots, long long rows, long long ld, int box_rows = 128) {
   uint64_t dims[3] = {64, (uint64_t)slots, (uint64_t)rows};
   uint64_t strides[2] = {128, (uint64_t)ld * 2};
-  uint32_t box[3] = {64, 1, 128};
+  uint32_t box[3] = {64, 1, (uint32_t)box_rows};
   return make_tensor_map(map, base, CU_TENSOR_MAP_DATA_TYPE_BFLOAT16, 3, dims, strides, box, CU_TENSOR_MAP_SWIZZLE_128B);
 }
 
@@ -889,15 +1157,18 @@ extern "C" int dh_attention_fwd(const void* qkv, void* out, float* lse, const vo
   fill_common(p, B, T, n_groups, q_per_kv, prefix_kv ? prefix_len : 0);
   p.qkv = (const bf16*)qkv; p.out = (bf16*)out; p.lse = lse;
   p.prefix_kv = (const bf16*)prefix_kv; p.gate = gate;
-  CUtensorMap tm;
+  CUtensorMap tm, tmp;
   if (make_head_map(&tm, qkv, p.slots, (long long)B * T, p.ld_qkv)) return -3;
+  // prefix rows: a 16-row box over the prefix_len rows that exist, rows beyond are zero-filled by TMA
+  if (make_head_map(&tmp, p.prefix_len > 0 ? prefix_kv : qkv, p.slots, p.prefix_len > 0 ? p.prefix_len : 1, p.ld_qkv, 16)) return -3;
   static bool attr = false;
   if (!attr) {
     DH_CUDA(cudaFuncSetAttribute(attn_fwd_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, FWD_SMEM));
     attr = true;
   }
-  dim3 grid((T + ATT_BQ - 1) / ATT_BQ, p.H, B);
-  attn_fwd_kernel<<<grid, FWD_THREADS, FWD_SMEM, (cudaStream_t)stream>>>(tm, p);
+  const int nq = (T + ATT_BQ - 1) / ATT_BQ;
+  dim3 grid((nq + 1) / 2, p.H, B);
+  attn_fwd_kernel<<<grid, FWD_THREADS, FWD_SMEM, (cudaStream_t)stream>>>(tm, tmp, p);
   DH_CUDA(cudaGetLastError());
   return 0;
 }
@@ -943,7 +1214,7 @@ extern "C" int dh_attention_bwd(const void* qkv, const void* out, const void* do
     attr = true;
   }
   const int nq = (T + ATT_BQ - 1) / ATT_BQ;
-  attn_bwd_dkv_kernel<<<dim3(nq, n_groups, B), BWD_THREADS, DKV_SMEM, s>>>(tmQKV, tmDO, p);
+  attn_bwd_dkv_kernel<<<dim3((nq + 1) / 2, n_groups, B), DKV_THREADS, DKV_SMEM, s>>>(tmQKV, tmDO, p);
   DH_CUDA(cudaGetLastError());
   attn_bwd_dq_kernel<<<dim3(nq, p.H, B), BWD_THREADS, DQ_SMEM, s>>>(tmQKV, tmDO, p);
   DH_CUDA(cudaGetLastError());
