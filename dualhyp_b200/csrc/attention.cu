@@ -19,7 +19,7 @@
 namespace dh {
 
 #ifdef DH_ATTN_TRACE
-#define TRC_DECL long long trc_t[48]; int trc_n = 0; const bool trc_on = (blockIdx.x == 0 && blockIdx.y == 5 && blockIdx.z == 3);
+#define TRC_DECL long long trc_t[48]; int trc_n = 0; const bool trc_on = (blockIdx.x == 0 && blockIdx.y == 1 && blockIdx.z == 3);
 #define TRC(tag) do { if (trc_on && trc_n < 48) { trc_t[trc_n++] = clock64(); } } while (0)
 #define TRC_DUMP(who) do { if (trc_on && lane == 0) { for (int i_ = 1; i_ < trc_n; ++i_) printf("%s w%d ev%d +%lld (abs %lld)\n", who, warp, i_, trc_t[i_] - trc_t[i_ - 1], trc_t[i_] - trc_t[0]); } } while (0)
 #else
@@ -626,160 +626,19 @@ __global__ void __launch_bounds__(128) attn_bwd_prep_kernel(const AttnParams p) 
 }
 
 // =================================================================================================
-// backward dQ: CTA = (q tile, head, batch); loop over k tiles j <= qi.
-//   S = Q K^T, dP = dO V^T  ->  dS = P * (dP - delta)  ->  dQ += dS K
-// =================================================================================================
-constexpr int BWD_THREADS = 192;
-constexpr int DQ_SMEM = 6 * TILE_BYTES + 1024 + 128;
-
-__global__ void __launch_bounds__(BWD_THREADS, 1) attn_bwd_dq_kernel(const __grid_constant__ CUtensorMap tmQKV,
-                                                                      const __grid_constant__ CUtensorMap tmDO, const AttnParams p) {
-  extern __shared__ uint8_t smem_raw[];
-  uint8_t* smem = reinterpret_cast<uint8_t*>((reinterpret_cast<uintptr_t>(smem_raw) + 1023) & ~uintptr_t(1023));
-  uint8_t* sQ = smem;
-  uint8_t* sdO = smem + TILE_BYTES;
-  uint8_t* sK = smem + 2 * TILE_BYTES;
-  uint8_t* sV = smem + 3 * TILE_BYTES;
-  uint8_t* sdS = smem + 4 * TILE_BYTES;   // two tiles
-  uint64_t* bars = reinterpret_cast<uint64_t*>(smem + 6 * TILE_BYTES);
-  uint64_t *q_full = bars, *k_full = bars + 1, *v_full = bars + 2, *sp_full = bars + 3, *ds_full = bars + 4, *dq_done = bars + 5;
-  uint32_t* tmem_slot = reinterpret_cast<uint32_t*>(bars + 6);
-
-  const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
-  const int nq = (p.T + ATT_BQ - 1) / ATT_BQ;
-  const int qi = nq - 1 - blockIdx.x;
-  const int h = blockIdx.y, b = blockIdx.z;
-  const int g = h / p.qpk;
-  const int q_slot = g * (p.qpk + 2) + (h % p.qpk), k_slot = g * (p.qpk + 2) + p.qpk, v_slot = k_slot + 1;
-  const int row_base = b * p.T;
-  const int q0 = qi * ATT_BQ;
-  const int nkv = qi + 1;
-
-  if (threadIdx.x == 0) {
-    mbar_init(q_full, 1); mbar_init(k_full, 1); mbar_init(v_full, 1);
-    mbar_init(sp_full, 1); mbar_init(ds_full, 128); mbar_init(dq_done, 1);
-    fence_barrier_init();
-  }
-  if (warp == 5) { tmem_alloc(tmem_slot, 512); tmem_relinquish(); }
-  tc_fence_before();
-  __syncthreads();
-  tc_fence_after();
-  const uint32_t tmem = *tmem_slot;
-  const uint32_t tS = tmem, tdP = tmem + 128, tdQ = tmem + 256;
-
-  if (warp == 4) {
-    if (lane == 0) {
-      mbar_expect_tx(q_full, 2 * TILE_BYTES);
-      tma_load_3d(sQ, &tmQKV, 0, q_slot, row_base + q0, q_full);
-      tma_load_3d(sdO, &tmDO, 0, h, row_base + q0, q_full);
-      for (int j = 0; j < nkv; ++j) {
-        if (j > 0) mbar_wait(dq_done, (j - 1) & 1);      // K(j-1) consumed by dQ(j-1)
-        mbar_expect_tx(k_full, TILE_BYTES);
-        tma_load_3d(sK, &tmQKV, 0, k_slot, row_base + j * ATT_BK, k_full);
-        if (j > 0) mbar_wait(sp_full, (j - 1) & 1);      // V(j-1) consumed by dP(j-1) (already true after dq_done)
-        mbar_expect_tx(v_full, TILE_BYTES);
-        tma_load_3d(sV, &tmQKV, 0, v_slot, row_base + j * ATT_BK, v_full);
-      }
-    }
-  } else if (warp == 5) {
-    if (lane == 0) {
-      mbar_wait(q_full, 0);
-      for (int j = 0; j < nkv; ++j) {
-        mbar_wait(k_full, j & 1);
-        mbar_wait(v_full, j & 1);
-        tc_fence_after();
-        mma_qk(tS, smem_u32(sQ), smem_u32(sK));
-        mma_qk(tdP, smem_u32(sdO), smem_u32(sV));
-        tc_commit(sp_full);
-        mbar_wait(ds_full, j & 1);
-        tc_fence_after();
-        mma_pv(tdQ, smem_u32(sdS), smem_u32(sK), j > 0);
-        tc_commit(dq_done);
-      }
-    }
-  } else {
-    const int r = warp * 32 + lane;
-    const int tq = q0 + r;
-    const bool valid = tq < p.T;
-    const uint32_t lane_off = (uint32_t)(warp * 32) << 16;
-    const long long stat_idx = ((long long)b * p.H + h) * p.T + (valid ? tq : 0);
-    const float lse2 = p.lse[stat_idx] * LOG2E;
-    const float delta = p.delta[stat_idx];
-    for (int j = 0; j < nkv; ++j) {
-      mbar_wait(sp_full, j & 1);
-      tc_fence_after();
-      if (j > 0) mbar_wait(dq_done, (j - 1) & 1);   // dS buffer free
-      const int kv0 = j * ATT_BK;
-      const bool diag = (j == qi);
-#pragma unroll 1
-      for (int c = 0; c < 4; ++c) {
-        uint32_t s[32], d[32];
-        tmem_ld32(tS + lane_off + c * 32, s);
-        tmem_ld32(tdP + lane_off + c * 32, d);
-        tmem_wait_ld();
-        float f[32];
-#pragma unroll
-        for (int i = 0; i < 32; ++i) {
-          float pr = exp2f(__uint_as_float(s[i]) * p.scale_log2 - lse2);
-          if ((diag && kv0 + c * 32 + i > tq) || !valid) pr = 0.f;
-          f[i] = pr * (__uint_as_float(d[i]) - delta);
-        }
-        store_a_chunk(sdS, r, c, f);
-      }
-      fence_proxy_async_smem();
-      tc_fence_before();
-      mbar_arrive(ds_full);
-    }
-    mbar_wait(dq_done, (nkv - 1) & 1);
-    tc_fence_after();
-    uint32_t v0[32], v1[32];
-    tmem_ld32(tdQ + lane_off, v0);
-    tmem_ld32(tdQ + lane_off + 32, v1);
-    tmem_wait_ld();
-    if (valid) {
-      float lo[32], hi[32];
-#pragma unroll
-      for (int i = 0; i < 32; ++i) { lo[i] = __uint_as_float(v0[i]) * p.scale; hi[i] = __uint_as_float(v1[i]) * p.scale; }
-      bf16* dq = p.dqkv + (long long)(row_base + tq) * p.ld_qkv + q_slot * HD;
-      if (p.prefix_len > 0) {   // prefix contribution written by the prep kernel
-#pragma unroll
-        for (int i = 0; i < 4; ++i) {
-          float a[8], c[8];
-          unpack8(reinterpret_cast<const uint4*>(dq)[i], a);
-          unpack8(reinterpret_cast<const uint4*>(dq + 32)[i], c);
-#pragma unroll
-          for (int k = 0; k < 8; ++k) { lo[8 * i + k] += a[k]; hi[8 * i + k] += c[k]; }
-        }
-      }
-      if (p.rope_cos) rope_conj_halves(lo, hi, p.rope_cos, p.rope_sin, tq);
-#pragma unroll
-      for (int i = 0; i < 4; ++i) {
-        float a[8], c[8];
-#pragma unroll
-        for (int k = 0; k < 8; ++k) { a[k] = lo[8 * i + k]; c[k] = hi[8 * i + k]; }
-        reinterpret_cast<uint4*>(dq)[i] = pack8(a);
-        reinterpret_cast<uint4*>(dq + 32)[i] = pack8(c);
-      }
-    }
-  }
-  tc_fence_before();
-  __syncthreads();
-  if (warp == 5) { tc_fence_after(); tmem_dealloc(tmem, 512); }
-}
-
-// =================================================================================================
 // backward dK/dV.  CTA = (k tile pair {nq-1-x, x}, kv group, batch), one CTA per SM, flat loop over the
 // qpk heads of the group and the q tiles i >= j of each key tile j (every CTA does qpk*(nq+1) iterations).
 // The key row is the TMEM lane: S^T = K Q^T and dP^T = V dO^T (SS MMAs) land in TMEM, eight softmax warps
-// (two threads per key row, 64 query columns each) pull them into registers (-> st_free: the MMA warp issues
+// (four threads per key row, 32 query columns each) pull them into registers (-> st_free: the MMA warp issues
 // the NEXT iteration's S^T / dP^T right away), form P^T = 2^(s - lse) and dS^T = P^T (dP^T - delta), and
 // write both back to TMEM as bf16 A operands of dV += P^T dO and dK += dS^T Q (TS MMAs).  dV / dK stay in
 // TMEM over all heads of the group (the GQA reduction is free).  Q / dO tiles (+ their lse / delta rows) are
 // double buffered; the K/V tiles of the two key tiles of the pair have a buffer each.
 // =================================================================================================
-constexpr int DKV_SM_WARPS = 8;
+constexpr int DKV_SM_WARPS = 16;
+constexpr int DKV_STAGES = 3;     // Q / dO ring
 constexpr int DKV_THREADS = (DKV_SM_WARPS + 2) * 32;
-constexpr int DKV_OFF_QDO = 4 * TILE_BYTES, DKV_OFF_STAT = 8 * TILE_BYTES, DKV_OFF_BAR = DKV_OFF_STAT + 2 * 256 * 4;
+constexpr int DKV_OFF_QDO = 4 * TILE_BYTES, DKV_OFF_STAT = (4 + 2 * DKV_STAGES) * TILE_BYTES, DKV_OFF_BAR = DKV_OFF_STAT + DKV_STAGES * 256 * 4;
 constexpr int DKV_SMEM = DKV_OFF_BAR + 256 + 1024;
 
 // D[128 x 64] (+)= A[128 x 128] (TMEM, bf16 pairs per column) * B[128 x 64] (smem tile [k rows][64], MN-major)
@@ -790,22 +649,29 @@ __device__ __forceinline__ void mma_ts_k128(uint32_t d_tmem, uint32_t a_tmem, ui
     tc_mma_ts(d_tmem, a_tmem + k * 8, umma_desc_sw128(b_smem + k * 2048, 8192, 1024), idesc, accumulate || k != 0);
 }
 
-// One 32-column chunk of the backward elementwise step.  MODE 0: all visible, 1: columns <= lane visible,
-// 2: columns >= lane visible, 3: nothing visible.  lse2 / delta come per column (COLSTAT, from smem) or per row.
+__device__ __forceinline__ float4 lds128(uint32_t addr) {
+  float4 v;
+  asm volatile("ld.shared.v4.f32 {%0, %1, %2, %3}, [%4];" : "=f"(v.x), "=f"(v.y), "=f"(v.z), "=f"(v.w) : "r"(addr));
+  return v;
+}
+// 16 columns [c0, c0+16) of the backward elementwise step: P = 2^(s*sl2 - lse2), dS = P (dP - delta), packed bf16 pairs.
+// MODE 0: all visible, 1: columns <= lane visible, 2: columns >= lane visible, 3: nothing visible (c = column index
+// inside the 32-column chunk).  lse2 / delta come per column (COLSTAT: shared-memory address of the 16 floats of this
+// piece, delta 512 bytes further) or per row.
 template <int MODE, bool COLSTAT, bool WANT_P>
-__device__ __forceinline__ void bwd_chunk(const uint32_t (&s)[32], const uint32_t (&dp)[32], int lane, float sl2, const float* lse2c,
-                                          const float* deltac, float lse2r, float deltar, uint32_t (&pp)[16], uint32_t (&ds)[16]) {
+__device__ __forceinline__ void bwd_piece(const uint32_t* s, const uint32_t* dp, int c0, int lane, float sl2, uint32_t stat_addr, float lse2r,
+                                          float deltar, uint32_t (&pp)[8], uint32_t (&ds)[8]) {
   if (MODE == 3) {
 #pragma unroll
-    for (int i = 0; i < 16; ++i) { if (WANT_P) pp[i] = 0u; ds[i] = 0u; }
+    for (int i = 0; i < 8; ++i) { if (WANT_P) pp[i] = 0u; ds[i] = 0u; }
     return;
   }
 #pragma unroll
-  for (int i4 = 0; i4 < 8; ++i4) {
+  for (int i4 = 0; i4 < 4; ++i4) {
     float l4[4], d4[4];
     if (COLSTAT) {
-      const float4 a = *reinterpret_cast<const float4*>(lse2c + 4 * i4);
-      const float4 c = *reinterpret_cast<const float4*>(deltac + 4 * i4);
+      const float4 a = lds128(stat_addr + 16 * i4);
+      const float4 c = lds128(stat_addr + 512 + 16 * i4);
       l4[0] = a.x; l4[1] = a.y; l4[2] = a.z; l4[3] = a.w;
       d4[0] = c.x; d4[1] = c.y; d4[2] = c.z; d4[3] = c.w;
     } else {
@@ -817,8 +683,8 @@ __device__ __forceinline__ void bwd_chunk(const uint32_t (&s)[32], const uint32_
     for (int k = 0; k < 4; ++k) {
       const int i = 4 * i4 + k;
       float e = fast_exp2(fmaf(__uint_as_float(s[i]), sl2, -l4[k]));
-      if (MODE == 1) e = (i <= lane) ? e : 0.f;
-      if (MODE == 2) e = (i >= lane) ? e : 0.f;
+      if (MODE == 1) e = (c0 + i <= lane) ? e : 0.f;
+      if (MODE == 2) e = (c0 + i >= lane) ? e : 0.f;
       pr[k] = e;
       dv[k] = e * (__uint_as_float(dp[i]) - d4[k]);
     }
@@ -828,48 +694,34 @@ __device__ __forceinline__ void bwd_chunk(const uint32_t (&s)[32], const uint32_
   }
 }
 template <bool COLSTAT, bool WANT_P>
-__device__ __forceinline__ void bwd_chunk_mode(int mode, const uint32_t (&s)[32], const uint32_t (&dp)[32], int lane, float sl2,
-                                               const float* lse2c, const float* deltac, float lse2r, float deltar, uint32_t (&pp)[16],
-                                               uint32_t (&ds)[16]) {
-  if (mode == 0) bwd_chunk<0, COLSTAT, WANT_P>(s, dp, lane, sl2, lse2c, deltac, lse2r, deltar, pp, ds);
-  else if (mode == 1) bwd_chunk<1, COLSTAT, WANT_P>(s, dp, lane, sl2, lse2c, deltac, lse2r, deltar, pp, ds);
-  else if (mode == 2) bwd_chunk<2, COLSTAT, WANT_P>(s, dp, lane, sl2, lse2c, deltac, lse2r, deltar, pp, ds);
-  else bwd_chunk<3, COLSTAT, WANT_P>(s, dp, lane, sl2, lse2c, deltac, lse2r, deltar, pp, ds);
+__device__ __forceinline__ void bwd_piece_mode(int mode, const uint32_t* s, const uint32_t* dp, int c0, int lane, float sl2,
+                                               uint32_t stat_addr, float lse2r, float deltar, uint32_t (&pp)[8], uint32_t (&ds)[8]) {
+  if (mode == 0) bwd_piece<0, COLSTAT, WANT_P>(s, dp, c0, lane, sl2, stat_addr, lse2r, deltar, pp, ds);
+  else if (mode == 1) bwd_piece<1, COLSTAT, WANT_P>(s, dp, c0, lane, sl2, stat_addr, lse2r, deltar, pp, ds);
+  else if (mode == 2) bwd_piece<2, COLSTAT, WANT_P>(s, dp, c0, lane, sl2, stat_addr, lse2r, deltar, pp, ds);
+  else bwd_piece<3, COLSTAT, WANT_P>(s, dp, c0, lane, sl2, stat_addr, lse2r, deltar, pp, ds);
 }
 
-// 16 + 16 accumulator columns (d in [16hf, 16hf+16) and the matching d + 32) -> bf16 row segments in global memory,
+// 8 + 8 accumulator columns (d in [8qt, 8qt+8) and the matching d + 32) -> bf16 row segments in global memory,
 // optionally through the conjugate RoPE rotation at position `pos`.
-__device__ __forceinline__ void store_rot_pairs(bf16* row, int hf, uint32_t (&lo)[16], uint32_t (&hi)[16], float scale, const bf16* cs,
+__device__ __forceinline__ void store_rot_pairs(bf16* row, int qt, uint32_t (&lo)[8], uint32_t (&hi)[8], float scale, const bf16* cs,
                                                 const bf16* sn, int pos) {
-  float a[16], c[16];
+  float a[8], c[8];
 #pragma unroll
-  for (int i = 0; i < 16; ++i) { a[i] = __uint_as_float(lo[i]) * scale; c[i] = __uint_as_float(hi[i]) * scale; }
+  for (int i = 0; i < 8; ++i) { a[i] = __uint_as_float(lo[i]) * scale; c[i] = __uint_as_float(hi[i]) * scale; }
   if (cs) {
-    const uint4* c4 = reinterpret_cast<const uint4*>(cs + (long long)pos * 64 + 16 * hf);
-    const uint4* s4 = reinterpret_cast<const uint4*>(sn + (long long)pos * 64 + 16 * hf);
+    float cc[8], ss[8];
+    unpack8(*reinterpret_cast<const uint4*>(cs + (long long)pos * 64 + 8 * qt), cc);
+    unpack8(*reinterpret_cast<const uint4*>(sn + (long long)pos * 64 + 8 * qt), ss);
 #pragma unroll
-    for (int i = 0; i < 2; ++i) {
-      float cc[8], ss[8];
-      unpack8(c4[i], cc);
-      unpack8(s4[i], ss);
-#pragma unroll
-      for (int j = 0; j < 8; ++j) {
-        const float x = a[8 * i + j], y = c[8 * i + j];
-        a[8 * i + j] = x * cc[j] + y * ss[j];
-        c[8 * i + j] = y * cc[j] - x * ss[j];
-      }
+    for (int j = 0; j < 8; ++j) {
+      const float x = a[j], y = c[j];
+      a[j] = x * cc[j] + y * ss[j];
+      c[j] = y * cc[j] - x * ss[j];
     }
   }
-  uint4* plo = reinterpret_cast<uint4*>(row + 16 * hf);
-  uint4* phi = reinterpret_cast<uint4*>(row + 32 + 16 * hf);
-#pragma unroll
-  for (int i = 0; i < 2; ++i) {
-    float t8[8], u8[8];
-#pragma unroll
-    for (int j = 0; j < 8; ++j) { t8[j] = a[8 * i + j]; u8[j] = c[8 * i + j]; }
-    plo[i] = pack8(t8);
-    phi[i] = pack8(u8);
-  }
+  *reinterpret_cast<uint4*>(row + 8 * qt) = pack8(a);
+  *reinterpret_cast<uint4*>(row + 32 + 8 * qt) = pack8(c);
 }
 
 __global__ void __launch_bounds__(DKV_THREADS, 1) attn_bwd_dkv_kernel(const __grid_constant__ CUtensorMap tmQKV,
@@ -877,14 +729,16 @@ __global__ void __launch_bounds__(DKV_THREADS, 1) attn_bwd_dkv_kernel(const __gr
   extern __shared__ uint8_t smem_raw[];
   uint8_t* smem = reinterpret_cast<uint8_t*>((reinterpret_cast<uintptr_t>(smem_raw) + 1023) & ~uintptr_t(1023));
   uint8_t* sKV = smem;                       // [2 items][K | V]
-  uint8_t* sQdO = smem + DKV_OFF_QDO;        // [2 stages][Q | dO]
-  float* sStat = reinterpret_cast<float*>(smem + DKV_OFF_STAT);   // [2 stages][lse*log2e 128 | delta 128]
+  uint8_t* sQdO = smem + DKV_OFF_QDO;        // [DKV_STAGES][Q | dO]
+  float* sStat = reinterpret_cast<float*>(smem + DKV_OFF_STAT);   // [DKV_STAGES][lse*log2e 128 | delta 128]
   uint64_t* bars = reinterpret_cast<uint64_t*>(smem + DKV_OFF_BAR);
-  uint64_t *kv_full = bars /*[2]*/, *qdo_full = bars + 2 /*[2]*/, *qdo_free = bars + 4 /*[2]*/, *st_full = bars + 6, *st_free = bars + 7,
-           *pds_full = bars + 8, *acc_done = bars + 9;
-  uint32_t* tmem_slot = reinterpret_cast<uint32_t*>(bars + 10);
+  uint64_t *kv_full = bars /*[2]*/, *qdo_full = bars + 2 /*[STAGES]*/, *qdo_free = bars + 2 + DKV_STAGES /*[STAGES]*/,
+           *st_full = bars + 2 + 2 * DKV_STAGES, *st_free = st_full + 1, *pds_full = st_full + 2, *acc_done = st_full + 3;
+  uint32_t* tmem_slot = reinterpret_cast<uint32_t*>(st_full + 4);
 
-  const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
+  const int warp = __shfl_sync(0xffffffffu, threadIdx.x >> 5, 0), lane = threadIdx.x & 31;   // shfl: the compiler sees a warp-uniform value
+  TRC_DECL
+  TRC(0);
   const int nq = (p.T + ATT_BQ - 1) / ATT_BQ;
   const int g = blockIdx.y, b = blockIdx.z;
   const int k_slot = g * (p.qpk + 2) + p.qpk, v_slot = k_slot + 1;
@@ -893,7 +747,8 @@ __global__ void __launch_bounds__(DKV_THREADS, 1) attn_bwd_dkv_kernel(const __gr
   const int n_items = (j_first == j_second) ? 1 : 2;
 
   if (warp == DKV_SM_WARPS && lane == 0) {
-    for (int i = 0; i < 2; ++i) { mbar_init(&kv_full[i], 1); mbar_init(&qdo_full[i], 33); mbar_init(&qdo_free[i], 1); }
+    for (int i = 0; i < 2; ++i) mbar_init(&kv_full[i], 1);
+    for (int i = 0; i < DKV_STAGES; ++i) { mbar_init(&qdo_full[i], 33); mbar_init(&qdo_free[i], 1); }
     mbar_init(st_full, 1); mbar_init(st_free, DKV_SM_WARPS * 32); mbar_init(pds_full, DKV_SM_WARPS * 32); mbar_init(acc_done, 1);
     fence_barrier_init();
     for (int it = 0; it < n_items; ++it) {
@@ -907,7 +762,7 @@ __global__ void __launch_bounds__(DKV_THREADS, 1) attn_bwd_dkv_kernel(const __gr
   tc_fence_before();
   __syncthreads();
   tc_fence_after();
-  const uint32_t tmem = *tmem_slot;
+  const uint32_t tmem = __shfl_sync(0xffffffffu, *tmem_slot, 0);
   const uint32_t tST = tmem, tdPT = tmem + 128, tPT = tmem + 256, tdST = tmem + 320, tdV = tmem + 384, tdK = tmem + 448;
 
   if (warp == DKV_SM_WARPS) {
@@ -918,63 +773,89 @@ __global__ void __launch_bounds__(DKV_THREADS, 1) attn_bwd_dkv_kernel(const __gr
       for (int hh = 0; hh < p.qpk; ++hh) {
         const int h = g * p.qpk + hh;
         for (int i = j; i < nq; ++i, ++n) {
-          const int s = n & 1;
-          if (n >= 2) mbar_wait(&qdo_free[s], ((n >> 1) - 1) & 1);
+          const int s = n % DKV_STAGES;
+          // the statistics go to registers first (independent loads, in flight across the wait for the stage)
+          const long long sbase = ((long long)b * p.H + h) * p.T;
+          float lv[4], dv[4];
+#pragma unroll
+          for (int k = 0; k < 4; ++k) {
+            const int tq = i * ATT_BQ + lane + 32 * k;
+            const bool ok = tq < p.T;
+            lv[k] = ok ? __ldg(p.lse + sbase + tq) * LOG2E : INFINITY;   // +inf => p = 0 for padded query rows
+            dv[k] = ok ? __ldg(p.delta + sbase + tq) : 0.f;
+          }
+          if (n >= DKV_STAGES) mbar_wait(&qdo_free[s], ((n / DKV_STAGES) - 1) & 1);
           if (lane == 0) {
             mbar_expect_tx(&qdo_full[s], 2 * TILE_BYTES);
             tma_load_3d(sQdO + s * 2 * TILE_BYTES, &tmQKV, 0, g * (p.qpk + 2) + hh, row_base + i * ATT_BQ, &qdo_full[s]);
             tma_load_3d(sQdO + s * 2 * TILE_BYTES + TILE_BYTES, &tmDO, 0, h, row_base + i * ATT_BQ, &qdo_full[s]);
           }
-          const long long sbase = ((long long)b * p.H + h) * p.T;
 #pragma unroll
           for (int k = 0; k < 4; ++k) {
-            const int c = lane + 32 * k, tq = i * ATT_BQ + c;
-            const bool ok = tq < p.T;
-            sStat[s * 256 + c] = ok ? p.lse[sbase + tq] * LOG2E : INFINITY;   // +inf => p = 0 for padded query rows
-            sStat[s * 256 + 128 + c] = ok ? p.delta[sbase + tq] : 0.f;
+            sStat[s * 256 + lane + 32 * k] = lv[k];
+            sStat[s * 256 + 128 + lane + 32 * k] = dv[k];
           }
           mbar_arrive(&qdo_full[s]);
         }
       }
     }
   } else if (warp == DKV_SM_WARPS + 1) {
-    // ---------------- MMA issuer ----------------
-    if (lane == 0) {
-      int n = 0, nfree = 0, npds = 0;
-      for (int item = 0; item < n_items; ++item) {
-        const int j = item ? j_second : j_first;
-        const int nit = p.qpk * (nq - j);
-        const uint32_t k_addr = smem_u32(sKV + item * 2 * TILE_BYTES), v_addr = k_addr + TILE_BYTES;
-        mbar_wait(&kv_full[item], 0);
-        mbar_wait(&qdo_full[n & 1], (n >> 1) & 1);
-        if (n > 0) { mbar_wait(st_free, nfree & 1); ++nfree; }
-        tc_fence_after();
-        mma_qk(tST, k_addr, smem_u32(sQdO + (n & 1) * 2 * TILE_BYTES));
-        mma_qk(tdPT, v_addr, smem_u32(sQdO + (n & 1) * 2 * TILE_BYTES + TILE_BYTES));
-        tc_commit(st_full);
-        for (int it = 0; it < nit; ++it, ++n) {
-          if (it + 1 < nit) {
-            const int n1 = n + 1;
-            mbar_wait(&qdo_full[n1 & 1], (n1 >> 1) & 1);
-            mbar_wait(st_free, nfree & 1); ++nfree;       // S^T / dP^T of iteration n are in registers
-            tc_fence_after();
-            mma_qk(tST, k_addr, smem_u32(sQdO + (n1 & 1) * 2 * TILE_BYTES));
-            mma_qk(tdPT, v_addr, smem_u32(sQdO + (n1 & 1) * 2 * TILE_BYTES + TILE_BYTES));
+    // ---------------- MMA issuer: the whole warp walks the loop (uniform control flow and operands), one elected
+    // lane issues -- a `lane == 0` region would make every descriptor a per-lane value and cost ~20 instructions per MMA
+    int n = 0, nfree = 0, npds = 0;
+    for (int item = 0; item < n_items; ++item) {
+      const int j = item ? j_second : j_first;
+      const int nit = p.qpk * (nq - j);
+      const uint32_t k_addr = smem_u32(sKV + item * 2 * TILE_BYTES), v_addr = k_addr + TILE_BYTES;
+      mbar_wait(&kv_full[item], 0);
+      mbar_wait(&qdo_full[n % DKV_STAGES], (n / DKV_STAGES) & 1);
+      if (n > 0) { mbar_wait(st_free, nfree & 1); ++nfree; }
+      tc_fence_after();
+      {
+        const uint32_t q_addr = smem_u32(sQdO + (n % DKV_STAGES) * 2 * TILE_BYTES);
+        if (elect_one()) {
+          mma_qk(tST, k_addr, q_addr);
+          mma_qk(tdPT, v_addr, q_addr + TILE_BYTES);
+          tc_commit(st_full);
+        }
+        __syncwarp();
+      }
+      for (int it = 0; it < nit; ++it, ++n) {
+        if (it + 1 < nit) {
+          const int n1 = n + 1;
+          TRC(20);
+          mbar_wait(&qdo_full[n1 % DKV_STAGES], (n1 / DKV_STAGES) & 1);
+          TRC(21);
+          mbar_wait(st_free, nfree & 1); ++nfree;       // S^T / dP^T of iteration n are in registers
+          TRC(22);
+          tc_fence_after();
+          const uint32_t q1_addr = smem_u32(sQdO + (n1 % DKV_STAGES) * 2 * TILE_BYTES);
+          if (elect_one()) {
+            mma_qk(tST, k_addr, q1_addr);
+            mma_qk(tdPT, v_addr, q1_addr + TILE_BYTES);
             tc_commit(st_full);
           }
-          mbar_wait(pds_full, npds & 1); ++npds;          // P^T / dS^T of iteration n are in TMEM
-          tc_fence_after();
-          const uint32_t q_addr = smem_u32(sQdO + (n & 1) * 2 * TILE_BYTES);
-          mma_ts_k128(tdV, tPT, q_addr + TILE_BYTES, it > 0);
-          mma_ts_k128(tdK, tdST, q_addr, it > 0);
-          tc_commit(&qdo_free[n & 1]);
+          __syncwarp();
+        }
+        TRC(23);
+        mbar_wait(pds_full, npds & 1); ++npds;          // P^T / dS^T of iteration n are in TMEM
+        TRC(24);
+        tc_fence_after();
+        const uint32_t q_addr = smem_u32(sQdO + (n % DKV_STAGES) * 2 * TILE_BYTES);
+        const bool acc = it > 0;
+        if (elect_one()) {
+          mma_ts_k128(tdV, tPT, q_addr + TILE_BYTES, acc);
+          mma_ts_k128(tdK, tdST, q_addr, acc);
+          tc_commit(&qdo_free[n % DKV_STAGES]);
           tc_commit(acc_done);
         }
+        __syncwarp();
+        TRC(25);
       }
     }
   } else {
-    // ---------------- softmax-backward warps: two threads per key row, 64 query columns each ----------------
-    const int quad = warp & 3, hf = warp >> 2;
+    // ---------------- softmax-backward warps: four threads per key row, 32 query columns each ----------------
+    const int quad = warp & 3, qt = warp >> 2;
     const int r = quad * 32 + lane;
     const uint32_t lane_off = (uint32_t)(quad * 32) << 16;
     const float sl2 = p.scale_log2;
@@ -984,38 +865,35 @@ __global__ void __launch_bounds__(DKV_THREADS, 1) attn_bwd_dkv_kernel(const __gr
       const int n_qt = nq - j;
       const int nit = p.qpk * n_qt;
       for (int it = 0; it < nit; ++it, ++n) {
-        const int s = n & 1;
+        const int s = n % DKV_STAGES;
         const int i = j + it % n_qt;
-        mbar_wait(&qdo_full[s], (n >> 1) & 1);      // lse / delta rows of this q tile are in smem
+        mbar_wait(&qdo_full[s], (n / DKV_STAGES) & 1);      // lse / delta rows of this q tile are in smem
         mbar_wait(st_full, n & 1);
+        TRC(1);
         tc_fence_after();
-        uint32_t s0[32], s1[32], d0[32], d1[32];
-        tmem_ld32(tST + lane_off + 64 * hf, s0);
-        tmem_ld32(tST + lane_off + 64 * hf + 32, s1);
-        tmem_ld32(tdPT + lane_off + 64 * hf, d0);
-        tmem_ld32(tdPT + lane_off + 64 * hf + 32, d1);
+        uint32_t sv[32], dv[32];
+        tmem_ld32(tST + lane_off + 32 * qt, sv);
+        tmem_ld32(tdPT + lane_off + 32 * qt, dv);
         tmem_wait_ld();
+        TRC(2);
         tc_fence_before();
         mbar_arrive(st_free);
-        // diagonal tile (i == j): key row r sees query column c iff c >= r; per 32-column chunk cg vs quad
-        int mode0 = 0, mode1 = 0;
-        if (i == j) {
-          const int c0 = 2 * hf, c1 = 2 * hf + 1;
-          mode0 = c0 > quad ? 0 : (c0 == quad ? 2 : 3);
-          mode1 = c1 > quad ? 0 : (c1 == quad ? 2 : 3);
-        }
-        const float* lse2c = sStat + s * 256 + 64 * hf;
-        const float* deltac = lse2c + 128;
-        uint32_t pp0[16], ds0[16], pp1[16], ds1[16];
-        bwd_chunk_mode<true, true>(mode0, s0, d0, lane, sl2, lse2c, deltac, 0.f, 0.f, pp0, ds0);
+        // diagonal tile (i == j): key row r sees query column c iff c >= r; per 32-column chunk qt vs quad
+        const int mode = (i == j) ? (qt > quad ? 0 : (qt == quad ? 2 : 3)) : 0;
+        const uint32_t stat_addr = smem_u32(sStat + s * 256 + 32 * qt);
         while (nacc < npds) { mbar_wait(acc_done, nacc & 1); ++nacc; }   // dV / dK MMAs of the previous iteration have read P^T / dS^T
+        TRC(3);
         tc_fence_after();
-        tmem_st16(tPT + lane_off + 32 * hf, pp0);
-        tmem_st16(tdST + lane_off + 32 * hf, ds0);
-        bwd_chunk_mode<true, true>(mode1, s1, d1, lane, sl2, lse2c + 32, deltac + 32, 0.f, 0.f, pp1, ds1);
-        tmem_st16(tPT + lane_off + 32 * hf + 16, pp1);
-        tmem_st16(tdST + lane_off + 32 * hf + 16, ds1);
+#pragma unroll
+        for (int hp = 0; hp < 2; ++hp) {
+          uint32_t pp[8], ds[8];
+          bwd_piece_mode<true, true>(mode, sv + 16 * hp, dv + 16 * hp, 16 * hp, lane, sl2, stat_addr + 64 * hp, 0.f, 0.f, pp, ds);
+          tmem_st8(tPT + lane_off + 16 * qt + 8 * hp, pp);
+          tmem_st8(tdST + lane_off + 16 * qt + 8 * hp, ds);
+        }
+        TRC(4);
         tmem_wait_st();
+        TRC(5);
         tc_fence_before();
         mbar_arrive(pds_full); ++npds;
       }
@@ -1025,21 +903,219 @@ __global__ void __launch_bounds__(DKV_THREADS, 1) attn_bwd_dkv_kernel(const __gr
       const int tk = j * ATT_BK + r;
       const bool valid = tk < p.T;
       bf16* rowp = p.dqkv + (long long)(row_base + (valid ? tk : 0)) * p.ld_qkv;
-      uint32_t lo[16], hi[16];
-      tmem_ld16(tdV + lane_off + 16 * hf, lo);
-      tmem_ld16(tdV + lane_off + 32 + 16 * hf, hi);
+      uint32_t lo[8], hi[8];
+      tmem_ld8(tdV + lane_off + 8 * qt, lo);
+      tmem_ld8(tdV + lane_off + 32 + 8 * qt, hi);
       tmem_wait_ld();
-      if (valid) store_rot_pairs(rowp + v_slot * HD, hf, lo, hi, 1.f, nullptr, nullptr, 0);
-      tmem_ld16(tdK + lane_off + 16 * hf, lo);
-      tmem_ld16(tdK + lane_off + 32 + 16 * hf, hi);
+      if (valid) store_rot_pairs(rowp + v_slot * HD, qt, lo, hi, 1.f, nullptr, nullptr, 0);
+      tmem_ld8(tdK + lane_off + 8 * qt, lo);
+      tmem_ld8(tdK + lane_off + 32 + 8 * qt, hi);
       tmem_wait_ld();
       tc_fence_before();
-      if (valid) store_rot_pairs(rowp + k_slot * HD, hf, lo, hi, p.scale, p.rope_cos, p.rope_sin, tk);
+      if (valid) store_rot_pairs(rowp + k_slot * HD, qt, lo, hi, p.scale, p.rope_cos, p.rope_sin, tk);
     }
   }
+  if (warp == 0 || warp >= DKV_SM_WARPS - 1) TRC_DUMP("dkv");
   tc_fence_before();
   __syncthreads();
   if (warp == DKV_SM_WARPS + 1) { tc_fence_after(); tmem_dealloc(tmem, 512); }
+}
+
+// =================================================================================================
+// backward dQ.  CTA = (q tile pair {nq-1-x, x}, kv group, batch), one CTA per SM, flat loop over the qpk heads
+// of the group and the key tiles j <= i of each query tile i (qpk*(nq+1) iterations per CTA, like dK/dV).
+// The query row is the TMEM lane: S = Q K^T and dP = dO V^T (SS MMAs) -> sixteen softmax warps (four threads
+// per row, 32 key columns each) -> dS = 2^(s - lse) (dP - delta) as bf16 back into TMEM -> dQ += dS K (TS MMA,
+// K as the MN-major B operand).  K/V tiles run through a 3-deep ring, Q/dO tiles are double buffered over heads,
+// and so is the dQ accumulator, so that the rows of head h (scaled, + the prefix part the prep kernel left in
+// dqkv, conjugate RoPE) are written out while head h+1 is already being accumulated.
+// =================================================================================================
+constexpr int DQ_SM_WARPS = 16;
+constexpr int DQ_THREADS = (DQ_SM_WARPS + 2) * 32;
+constexpr int DQ_KV_STAGES = 3;
+constexpr int DQ_OFF_KV = 4 * TILE_BYTES, DQ_OFF_BAR = (4 + 2 * DQ_KV_STAGES) * TILE_BYTES;
+constexpr int DQ_SMEM = DQ_OFF_BAR + 256 + 1024;
+
+__global__ void __launch_bounds__(DQ_THREADS, 1) attn_bwd_dq_kernel(const __grid_constant__ CUtensorMap tmQKV,
+                                                                     const __grid_constant__ CUtensorMap tmDO, const AttnParams p) {
+  extern __shared__ uint8_t smem_raw[];
+  uint8_t* smem = reinterpret_cast<uint8_t*>((reinterpret_cast<uintptr_t>(smem_raw) + 1023) & ~uintptr_t(1023));
+  uint8_t* sQdO = smem;                     // [2 heads in flight][Q | dO]
+  uint8_t* sKV = smem + DQ_OFF_KV;          // [DQ_KV_STAGES][K | V]
+  uint64_t* bars = reinterpret_cast<uint64_t*>(smem + DQ_OFF_BAR);
+  uint64_t *qdo_full = bars /*[2]*/, *qdo_free = bars + 2 /*[2]*/, *kv_full = bars + 4 /*[STAGES]*/, *kv_free = bars + 4 + DQ_KV_STAGES,
+           *sp_full = bars + 4 + 2 * DQ_KV_STAGES, *sp_free = sp_full + 1, *ds_full = sp_full + 2, *dsq_done = sp_full + 3,
+           *dq_done = sp_full + 4 /*[2]*/;
+  uint32_t* tmem_slot = reinterpret_cast<uint32_t*>(sp_full + 6);
+
+  const int warp = __shfl_sync(0xffffffffu, threadIdx.x >> 5, 0), lane = threadIdx.x & 31;
+  const int nq = (p.T + ATT_BQ - 1) / ATT_BQ;
+  const int g = blockIdx.y, b = blockIdx.z;
+  const int k_slot = g * (p.qpk + 2) + p.qpk, v_slot = k_slot + 1;
+  const int row_base = b * p.T;
+  const int i_first = nq - 1 - (int)blockIdx.x, i_second = (int)blockIdx.x;
+  const int n_items = (i_first == i_second) ? 1 : 2;
+
+  if (warp == DQ_SM_WARPS && lane == 0) {
+    for (int i = 0; i < 2; ++i) { mbar_init(&qdo_full[i], 1); mbar_init(&qdo_free[i], 1); mbar_init(&dq_done[i], 1); }
+    for (int i = 0; i < DQ_KV_STAGES; ++i) { mbar_init(&kv_full[i], 1); mbar_init(&kv_free[i], 1); }
+    mbar_init(sp_full, 1); mbar_init(sp_free, DQ_SM_WARPS * 32); mbar_init(ds_full, DQ_SM_WARPS * 32); mbar_init(dsq_done, 1);
+    fence_barrier_init();
+  }
+  if (warp == DQ_SM_WARPS + 1) { tmem_alloc(tmem_slot, 512); tmem_relinquish(); }
+  tc_fence_before();
+  __syncthreads();
+  tc_fence_after();
+  const uint32_t tmem = __shfl_sync(0xffffffffu, *tmem_slot, 0);
+  const uint32_t tS = tmem, tdP = tmem + 128, tdS = tmem + 256, tdQ = tmem + 320 /* [2] x 64 */;
+
+  if (warp == DQ_SM_WARPS) {
+    // ---------------- TMA producer ----------------
+    if (lane == 0) {
+      int n = 0, hc = 0;
+      for (int item = 0; item < n_items; ++item) {
+        const int i = item ? i_second : i_first;
+        for (int hh = 0; hh < p.qpk; ++hh, ++hc) {
+          const int qs = hc & 1;
+          if (hc >= 2) mbar_wait(&qdo_free[qs], ((hc >> 1) - 1) & 1);
+          mbar_expect_tx(&qdo_full[qs], 2 * TILE_BYTES);
+          tma_load_3d(sQdO + qs * 2 * TILE_BYTES, &tmQKV, 0, g * (p.qpk + 2) + hh, row_base + i * ATT_BQ, &qdo_full[qs]);
+          tma_load_3d(sQdO + qs * 2 * TILE_BYTES + TILE_BYTES, &tmDO, 0, g * p.qpk + hh, row_base + i * ATT_BQ, &qdo_full[qs]);
+          for (int j = 0; j <= i; ++j, ++n) {
+            const int s = n % DQ_KV_STAGES;
+            if (n >= DQ_KV_STAGES) mbar_wait(&kv_free[s], ((n / DQ_KV_STAGES) - 1) & 1);
+            mbar_expect_tx(&kv_full[s], 2 * TILE_BYTES);
+            tma_load_3d(sKV + s * 2 * TILE_BYTES, &tmQKV, 0, k_slot, row_base + j * ATT_BK, &kv_full[s]);
+            tma_load_3d(sKV + s * 2 * TILE_BYTES + TILE_BYTES, &tmQKV, 0, v_slot, row_base + j * ATT_BK, &kv_full[s]);
+          }
+        }
+      }
+    }
+  } else if (warp == DQ_SM_WARPS + 1) {
+    // ---------------- MMA issuer (whole warp walks the loop, one elected lane issues) ----------------
+    // iteration n = (item, head counter hc, key tile j); the S / dP MMAs of iteration n+1 go out as soon as the
+    // softmax warps hold iteration n in registers, the dQ MMA of iteration n once its dS is in TMEM
+    int n = 0, hc = 0;
+    int item_nx = 0, hh_nx = 0, j_nx = 0, hc_nx = 0;          // the iteration whose S / dP is issued next
+    auto issue_sdp = [&](int n_it) {
+      const int i_nx = item_nx ? i_second : i_first;
+      const int qs = hc_nx & 1, s = n_it % DQ_KV_STAGES;
+      if (j_nx == 0) mbar_wait(&qdo_full[qs], (hc_nx >> 1) & 1);
+      mbar_wait(&kv_full[s], (n_it / DQ_KV_STAGES) & 1);
+      if (n_it > 0) mbar_wait(sp_free, (n_it - 1) & 1);      // S / dP of iteration n_it-1 are in registers
+      tc_fence_after();
+      const uint32_t q_addr = smem_u32(sQdO + qs * 2 * TILE_BYTES), kv_addr = smem_u32(sKV + s * 2 * TILE_BYTES);
+      if (elect_one()) {
+        mma_qk(tS, q_addr, kv_addr);
+        mma_qk(tdP, q_addr + TILE_BYTES, kv_addr + TILE_BYTES);
+        tc_commit(sp_full);
+      }
+      __syncwarp();
+      // advance the look-ahead iterator
+      if (++j_nx > i_nx) { j_nx = 0; ++hc_nx; if (++hh_nx == p.qpk) { hh_nx = 0; ++item_nx; } }
+    };
+    issue_sdp(0);
+    for (int item = 0; item < n_items; ++item) {
+      const int i = item ? i_second : i_first;
+      for (int hh = 0; hh < p.qpk; ++hh, ++hc) {
+        for (int j = 0; j <= i; ++j, ++n) {
+          if (item_nx < n_items) issue_sdp(n + 1);
+          mbar_wait(ds_full, n & 1);                          // dS of iteration n is in TMEM
+          tc_fence_after();
+          const int s = n % DQ_KV_STAGES;
+          const uint32_t k_addr = smem_u32(sKV + s * 2 * TILE_BYTES);
+          const bool acc = j > 0, last = (j == i);
+          const uint32_t d_tmem = tdQ + 64 * (hc & 1);
+          if (elect_one()) {
+            mma_ts_k128(d_tmem, tdS, k_addr, acc);
+            tc_commit(&kv_free[s]);
+            tc_commit(dsq_done);
+            if (last) { tc_commit(&dq_done[hc & 1]); tc_commit(&qdo_free[hc & 1]); }
+          }
+          __syncwarp();
+        }
+      }
+    }
+  } else {
+    // ---------------- softmax-backward warps: four threads per query row, 32 key columns each ----------------
+    const int quad = warp & 3, qt = warp >> 2;
+    const int r = quad * 32 + lane;
+    const uint32_t lane_off = (uint32_t)(quad * 32) << 16;
+    const float sl2 = p.scale_log2;
+    int n = 0, hc = 0;
+    int nds = 0, ndsq = 0;          // ds_full arrivals made / dsq_done events waited for
+    int pend_hc = -1, pend_tq = 0, pend_h = 0;   // head whose dQ rows still have to be written out
+
+    auto write_dq = [&](int hcw, int tq, int h) {
+      // rows of head h: dQ * scale (+ prefix part left in dqkv by the prep kernel), conjugate RoPE, bf16
+      mbar_wait(&dq_done[hcw & 1], (hcw >> 1) & 1);
+      tc_fence_after();
+      uint32_t lo[8], hi[8];
+      tmem_ld8(tdQ + 64 * (hcw & 1) + lane_off + 8 * qt, lo);
+      tmem_ld8(tdQ + 64 * (hcw & 1) + lane_off + 32 + 8 * qt, hi);
+      tmem_wait_ld();
+      tc_fence_before();
+      if (tq < p.T) {
+        bf16* row = p.dqkv + (long long)(row_base + tq) * p.ld_qkv + (g * (p.qpk + 2) + (h - g * p.qpk)) * HD;
+        if (p.prefix_len > 0) {
+          float a[8], c[8];
+          unpack8(*reinterpret_cast<const uint4*>(row + 8 * qt), a);
+          unpack8(*reinterpret_cast<const uint4*>(row + 32 + 8 * qt), c);
+          const float inv = 1.f / p.scale;
+#pragma unroll
+          for (int k = 0; k < 8; ++k) {
+            lo[k] = __float_as_uint(__uint_as_float(lo[k]) + a[k] * inv);
+            hi[k] = __float_as_uint(__uint_as_float(hi[k]) + c[k] * inv);
+          }
+        }
+        store_rot_pairs(row, qt, lo, hi, p.scale, p.rope_cos, p.rope_sin, tq);
+      }
+    };
+
+    for (int item = 0; item < n_items; ++item) {
+      const int i = item ? i_second : i_first;
+      const int tq = i * ATT_BQ + r;
+      const bool valid = tq < p.T;
+      for (int hh = 0; hh < p.qpk; ++hh, ++hc) {
+        const int h = g * p.qpk + hh;
+        const long long stat_idx = ((long long)b * p.H + h) * p.T + (valid ? tq : 0);
+        const float lse2 = valid ? __ldg(p.lse + stat_idx) * LOG2E : INFINITY;    // +inf => p = 0 on padded rows
+        const float delta = valid ? __ldg(p.delta + stat_idx) : 0.f;
+        for (int j = 0; j <= i; ++j, ++n) {
+          mbar_wait(sp_full, n & 1);
+          tc_fence_after();
+          uint32_t sv[32], dv[32];
+          tmem_ld32(tS + lane_off + 32 * qt, sv);
+          tmem_ld32(tdP + lane_off + 32 * qt, dv);
+          tmem_wait_ld();
+          tc_fence_before();
+          mbar_arrive(sp_free);
+          // diagonal tile (j == i): query row r sees key column c iff c <= r; per 32-column chunk qt vs quad
+          const int mode = (j == i) ? (qt < quad ? 0 : (qt == quad ? 1 : 3)) : 0;
+          while (ndsq < nds) { mbar_wait(dsq_done, ndsq & 1); ++ndsq; }   // the dQ MMA of the previous iteration has read dS
+          tc_fence_after();
+#pragma unroll
+          for (int hp = 0; hp < 2; ++hp) {
+            uint32_t pp[8], ds[8];
+            bwd_piece_mode<false, false>(mode, sv + 16 * hp, dv + 16 * hp, 16 * hp, lane, sl2, 0u, lse2, delta, pp, ds);
+            tmem_st8(tdS + lane_off + 16 * qt + 8 * hp, ds);
+          }
+          tmem_wait_st();
+          tc_fence_before();
+          mbar_arrive(ds_full); ++nds;
+          if (pend_hc >= 0 && pend_hc < hc) { write_dq(pend_hc, pend_tq, pend_h); pend_hc = -1; }
+          if (j == i) {
+            if (pend_hc >= 0) write_dq(pend_hc, pend_tq, pend_h);      // single-iteration heads: flush the older one first
+            pend_hc = hc; pend_tq = tq; pend_h = h;
+          }
+        }
+      }
+    }
+    if (pend_hc >= 0) write_dq(pend_hc, pend_tq, pend_h);
+  }
+  tc_fence_before();
+  __syncthreads();
+  if (warp == DQ_SM_WARPS + 1) { tc_fence_after(); tmem_dealloc(tmem, 512); }
 }
 
 // =================================================================================================
@@ -1216,7 +1292,7 @@ extern "C" int dh_attention_bwd(const void* qkv, const void* out, const void* do
   const int nq = (T + ATT_BQ - 1) / ATT_BQ;
   attn_bwd_dkv_kernel<<<dim3((nq + 1) / 2, n_groups, B), DKV_THREADS, DKV_SMEM, s>>>(tmQKV, tmDO, p);
   DH_CUDA(cudaGetLastError());
-  attn_bwd_dq_kernel<<<dim3(nq, p.H, B), BWD_THREADS, DQ_SMEM, s>>>(tmQKV, tmDO, p);
+  attn_bwd_dq_kernel<<<dim3((nq + 1) / 2, n_groups, B), DQ_THREADS, DQ_SMEM, s>>>(tmQKV, tmDO, p);
   DH_CUDA(cudaGetLastError());
   return 0;
 }
