@@ -484,148 +484,6 @@ __global__ void __launch_bounds__(FWD_THREADS, 2) attn_fwd_kernel(const __grid_c
 }
 
 // =================================================================================================
-// backward, step 0: delta = rowsum(dO * y_causal) and the prefix / gate gradients.  CUDA cores.
-// out = y + gate*ay  =>  rowsum(dO*y) = rowsum(dO*out) - gate*rowsum(dO*ay).
-// block = 128 threads, thread = one token row of head blockIdx.y; blocks stride over row tiles.
-// =================================================================================================
-__global__ void __launch_bounds__(128) attn_bwd_prep_kernel(const AttnParams p) {
-  __shared__ float sak[MAX_PREFIX * HD], sav[MAX_PREFIX * HD];
-  __shared__ float sPA[4][32][MAX_PREFIX];   // gate * p[a]            (for d_av)
-  __shared__ float sDS[4][32][MAX_PREFIX];   // scale * ds[a]          (for d_ak and dq)
-  __shared__ float sgate[4];
-  const int h = blockIdx.y;
-  const int g = h / p.qpk;
-  const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
-  const int aT = p.prefix_len;
-  const long long M = (long long)p.B * p.T;
-  const int q_slot = g * (p.qpk + 2) + (h % p.qpk), k_slot = g * (p.qpk + 2) + p.qpk;
-  if (aT > 0) load_prefix_to_smem(p, g, sak, sav);
-  __syncthreads();
-  const float gate = aT > 0 ? p.gate[h] : 0.f;
-  float acc_v[MAX_PREFIX][2], acc_k[MAX_PREFIX][2];
-#pragma unroll
-  for (int a = 0; a < MAX_PREFIX; ++a) { acc_v[a][0] = acc_v[a][1] = acc_k[a][0] = acc_k[a][1] = 0.f; }
-  float dgate_acc = 0.f;
-
-  for (long long m0 = (long long)blockIdx.x * 128; m0 < M; m0 += (long long)gridDim.x * 128) {
-    const long long m = m0 + threadIdx.x;
-    const bool valid = m < M;
-    float dot_out = 0.f;
-    float sp[MAX_PREFIX], dpv[MAX_PREFIX];
-#pragma unroll
-    for (int a = 0; a < MAX_PREFIX; ++a) { sp[a] = 0.f; dpv[a] = 0.f; }
-    if (valid) {
-      const uint4* o4 = reinterpret_cast<const uint4*>(p.o + m * (p.H * HD) + h * HD);
-      const uint4* d4 = reinterpret_cast<const uint4*>(p.dout + m * (p.H * HD) + h * HD);
-      const uint4* q4 = reinterpret_cast<const uint4*>(p.qkv + m * p.ld_qkv + q_slot * HD);
-#pragma unroll 1
-      for (int c8 = 0; c8 < 8; ++c8) {
-        float ov[8], dv[8];
-        unpack8(o4[c8], ov);
-        unpack8(d4[c8], dv);
-#pragma unroll
-        for (int i = 0; i < 8; ++i) dot_out += ov[i] * dv[i];
-        if (aT > 0) {
-          float qv[8];
-          unpack8(q4[c8], qv);
-#pragma unroll
-          for (int a = 0; a < MAX_PREFIX; ++a) {
-            if (a < aT) {
-#pragma unroll
-              for (int i = 0; i < 8; ++i) {
-                sp[a] += qv[i] * sak[a * HD + c8 * 8 + i];
-                dpv[a] += dv[i] * sav[a * HD + c8 * 8 + i];
-              }
-            }
-          }
-        }
-      }
-    }
-    float delta = dot_out;
-    if (aT > 0) {
-      float mx = -INFINITY, sum = 0.f, doay = 0.f;
-#pragma unroll
-      for (int a = 0; a < MAX_PREFIX; ++a) if (a < aT) mx = fmaxf(mx, sp[a]);
-#pragma unroll
-      for (int a = 0; a < MAX_PREFIX; ++a) {
-        sp[a] = (a < aT) ? exp2f((sp[a] - mx) * p.scale_log2) : 0.f;
-        sum += sp[a];
-      }
-      const float inv = 1.f / sum;
-#pragma unroll
-      for (int a = 0; a < MAX_PREFIX; ++a) { sp[a] *= inv; doay += sp[a] * dpv[a]; }
-      delta = dot_out - gate * doay;
-      if (valid) dgate_acc += doay;
-      float ds[MAX_PREFIX];
-#pragma unroll
-      for (int a = 0; a < MAX_PREFIX; ++a) {
-        ds[a] = valid ? sp[a] * gate * (dpv[a] - doay) * p.scale : 0.f;
-        sPA[warp][lane][a] = valid ? gate * sp[a] : 0.f;
-        sDS[warp][lane][a] = ds[a];
-      }
-      if (valid && p.need_dqkv) {   // dq_prefix = scale * sum_a ds[a] * ak[a]  (pre-rotation; the dQ kernel adds its part)
-        uint4* dq4 = reinterpret_cast<uint4*>(p.dqkv + m * p.ld_qkv + q_slot * HD);
-#pragma unroll 1
-        for (int c8 = 0; c8 < 8; ++c8) {
-          float f[8];
-#pragma unroll
-          for (int i = 0; i < 8; ++i) f[i] = 0.f;
-#pragma unroll
-          for (int a = 0; a < MAX_PREFIX; ++a) {
-            if (a < aT) {
-#pragma unroll
-              for (int i = 0; i < 8; ++i) f[i] += ds[a] * sak[a * HD + c8 * 8 + i];
-            }
-          }
-          dq4[c8] = pack8(f);
-        }
-      }
-      __syncwarp();
-      // phase 2: lane owns head dims {lane, lane+32}; accumulate d_av += (gate p)^T dO, d_ak += (scale ds)^T q
-      const long long mw = m0 + warp * 32;
-#pragma unroll 1
-      for (int rr = 0; rr < 32; ++rr) {
-        const long long mr = mw + rr;
-        if (mr >= M) break;
-        const bf16* dr = p.dout + mr * (p.H * HD) + h * HD;
-        const bf16* qr = p.qkv + mr * p.ld_qkv + q_slot * HD;
-        const float d0 = __bfloat162float(dr[lane]), d1 = __bfloat162float(dr[lane + 32]);
-        const float x0 = __bfloat162float(qr[lane]), x1 = __bfloat162float(qr[lane + 32]);
-#pragma unroll
-        for (int a = 0; a < MAX_PREFIX; ++a) {
-          if (a < aT) {
-            const float pa = sPA[warp][rr][a], da = sDS[warp][rr][a];
-            acc_v[a][0] += pa * d0; acc_v[a][1] += pa * d1;
-            acc_k[a][0] += da * x0; acc_k[a][1] += da * x1;
-          }
-        }
-      }
-      __syncwarp();
-    }
-    if (valid) {
-      const int b = (int)(m / p.T), t = (int)(m % p.T);
-      p.delta[((long long)b * p.H + h) * p.T + t] = delta;
-    }
-  }
-  if (aT > 0) {
-    float* dk = p.d_prefix_kv + (long long)k_slot * HD;
-#pragma unroll
-    for (int a = 0; a < MAX_PREFIX; ++a) {
-      if (a < aT) {
-        atomicAdd(dk + (long long)a * p.ld_qkv + lane, acc_k[a][0]);
-        atomicAdd(dk + (long long)a * p.ld_qkv + lane + 32, acc_k[a][1]);
-        atomicAdd(dk + (long long)a * p.ld_qkv + HD + lane, acc_v[a][0]);
-        atomicAdd(dk + (long long)a * p.ld_qkv + HD + lane + 32, acc_v[a][1]);
-      }
-    }
-    dgate_acc = warp_sum(dgate_acc);
-    if (lane == 0) sgate[warp] = dgate_acc;
-    __syncthreads();
-    if (threadIdx.x == 0) atomicAdd(p.d_gate + h, sgate[0] + sgate[1] + sgate[2] + sgate[3]);
-  }
-}
-
-// =================================================================================================
 // backward dK/dV.  CTA = (k tile pair {nq-1-x, x}, kv group, batch), one CTA per SM, flat loop over the
 // qpk heads of the group and the q tiles i >= j of each key tile j (every CTA does qpk*(nq+1) iterations).
 // The key row is the TMEM lane: S^T = K Q^T and dP^T = V dO^T (SS MMAs) land in TMEM, eight softmax warps
@@ -1119,6 +977,251 @@ __global__ void __launch_bounds__(DQ_THREADS, 1) attn_bwd_dq_kernel(const __grid
 }
 
 // =================================================================================================
+// backward, step 0.  delta = rowsum(dO * y_causal) for the dQ and dK/dV kernels, and the whole backward of the
+// gated prefix term (ger/adapter.py:129-146).  out = y + gate * ay  =>  delta = rowsum(dO*out) - gate*rowsum(dO*ay).
+//
+// attn_bwd_delta_kernel  (no prefix): pure streaming, 8 lanes per (row, head).
+// attn_bwd_prefix_kernel (prefix):    CTA = (row tiles strided, head), tensor cores for every contraction:
+//     S_a  = Q AK^T, dPV = dO AV^T          two N=16 MMAs -> TMEM; thread = row: softmax over the aT prefix keys,
+//     delta, d_gate, dS_a = scale p gate (dPV - <p,dPV>), gP = gate p
+//     dQ_a = dS_a AK                         dS_a as the TMEM A operand (K = 16) -> bf16 rows into dqkv (the dQ
+//                                            kernel adds them before the RoPE rotation)
+//     [dAK^T ; dAV^T] += [Q^T ; dO^T] [dS_a | gP]   one M=128 (two stacked MN-major tiles), N=32, K=128 MMA chain,
+//                                            accumulated in TMEM over all row tiles of the CTA, then atomics.
+// =================================================================================================
+__global__ void __launch_bounds__(256) attn_bwd_delta_kernel(const AttnParams p) {
+  const long long M = (long long)p.B * p.T;
+  const int sub = threadIdx.x & 7;                      // 8 lanes x 16 bytes = one head of one row
+  const long long pairs = M * p.H;
+  for (long long pr = (long long)blockIdx.x * 32 + (threadIdx.x >> 3); pr < pairs; pr += (long long)gridDim.x * 32) {
+    const long long m = pr / p.H;
+    const int h = (int)(pr % p.H);
+    float ov[8], dv[8];
+    unpack8(*reinterpret_cast<const uint4*>(p.o + m * (p.H * HD) + h * HD + sub * 8), ov);
+    unpack8(*reinterpret_cast<const uint4*>(p.dout + m * (p.H * HD) + h * HD + sub * 8), dv);
+    float acc = 0.f;
+#pragma unroll
+    for (int i = 0; i < 8; ++i) acc += ov[i] * dv[i];
+    acc += __shfl_xor_sync(0xffffffffu, acc, 1);
+    acc += __shfl_xor_sync(0xffffffffu, acc, 2);
+    acc += __shfl_xor_sync(0xffffffffu, acc, 4);
+    if (sub == 0) p.delta[((long long)(m / p.T) * p.H + h) * p.T + (m % p.T)] = acc;
+  }
+}
+
+constexpr int PFX_THREADS = 192;
+constexpr int PFX_STAGE = 3 * TILE_BYTES;                 // Q | dO | O
+constexpr int PFX_OFF_AK = 2 * PFX_STAGE, PFX_OFF_AV = PFX_OFF_AK + 2048, PFX_OFF_B2 = PFX_OFF_AV + 2048, PFX_OFF_BAR = PFX_OFF_B2 + 8192;
+constexpr int PFX_SMEM = PFX_OFF_BAR + 256 + 1024;
+
+__global__ void __launch_bounds__(PFX_THREADS, 2) attn_bwd_prefix_kernel(const __grid_constant__ CUtensorMap tmQKV,
+                                                                          const __grid_constant__ CUtensorMap tmDO,
+                                                                          const __grid_constant__ CUtensorMap tmO,
+                                                                          const __grid_constant__ CUtensorMap tmPFX, const AttnParams p) {
+  extern __shared__ uint8_t smem_raw[];
+  uint8_t* smem = reinterpret_cast<uint8_t*>((reinterpret_cast<uintptr_t>(smem_raw) + 1023) & ~uintptr_t(1023));
+  uint8_t* sAK = smem + PFX_OFF_AK;
+  uint8_t* sAV = smem + PFX_OFF_AV;
+  uint8_t* sB2 = smem + PFX_OFF_B2;                        // [32 n][128 rows] bf16, K-major: n < 16 dS_a, n >= 16 gP
+  uint64_t* bars = reinterpret_cast<uint64_t*>(smem + PFX_OFF_BAR);
+  uint64_t *full = bars /*[2]*/, *stage_free = bars + 2 /*[2]*/, *pfx_full = bars + 4, *sp_full = bars + 5, *dsp_full = bars + 6,
+           *dq_full = bars + 7, *acc_done = bars + 8;
+  uint32_t* tmem_slot = reinterpret_cast<uint32_t*>(bars + 10);
+  __shared__ float s_gate_part[4];
+
+  const int warp = __shfl_sync(0xffffffffu, threadIdx.x >> 5, 0), lane = threadIdx.x & 31;
+  const int h = blockIdx.y;
+  const int g = h / p.qpk;
+  const int q_slot = g * (p.qpk + 2) + (h % p.qpk), k_slot = g * (p.qpk + 2) + p.qpk, v_slot = k_slot + 1;
+  const long long M = (long long)p.B * p.T;
+  const int ntiles = (int)((M + 127) / 128);
+  const int my_tiles = ((int)blockIdx.x < ntiles) ? (ntiles - 1 - (int)blockIdx.x) / (int)gridDim.x + 1 : 0;
+
+  if (warp == 4 && lane == 0) {
+    for (int i = 0; i < 2; ++i) { mbar_init(&full[i], 1); mbar_init(&stage_free[i], 1); }
+    mbar_init(pfx_full, 1); mbar_init(sp_full, 1); mbar_init(dsp_full, 128); mbar_init(dq_full, 1); mbar_init(acc_done, 1);
+    fence_barrier_init();
+    mbar_expect_tx(pfx_full, 4096);
+    tma_load_3d(sAK, &tmPFX, 0, k_slot, 0, pfx_full);
+    tma_load_3d(sAV, &tmPFX, 0, v_slot, 0, pfx_full);
+  }
+  if (warp == 5) { tmem_alloc(tmem_slot, 256); tmem_relinquish(); }
+  tc_fence_before();
+  __syncthreads();
+  tc_fence_after();
+  const uint32_t tmem = __shfl_sync(0xffffffffu, *tmem_slot, 0);
+  const uint32_t tSp = tmem, tdPV = tmem + 16, tdSp = tmem + 32, tdq = tmem + 64, tacc = tmem + 128;
+
+  if (warp == 4) {
+    // ---------------- TMA producer ----------------
+    if (lane == 0) {
+      for (int n = 0; n < my_tiles; ++n) {
+        const int s = n & 1;
+        const int row0 = ((int)blockIdx.x + n * (int)gridDim.x) * 128;
+        if (n >= 2) mbar_wait(&stage_free[s], ((n >> 1) - 1) & 1);
+        mbar_expect_tx(&full[s], 3 * TILE_BYTES);
+        tma_load_3d(smem + s * PFX_STAGE, &tmQKV, 0, q_slot, row0, &full[s]);
+        tma_load_3d(smem + s * PFX_STAGE + TILE_BYTES, &tmDO, 0, h, row0, &full[s]);
+        tma_load_3d(smem + s * PFX_STAGE + 2 * TILE_BYTES, &tmO, 0, h, row0, &full[s]);
+      }
+    }
+  } else if (warp == 5) {
+    // ---------------- MMA issuer (uniform control flow, one elected lane issues) ----------------
+    mbar_wait(pfx_full, 0);
+    for (int n = 0; n < my_tiles; ++n) {
+      const int s = n & 1;
+      const uint32_t q_addr = smem_u32(smem + s * PFX_STAGE), do_addr = q_addr + TILE_BYTES;
+      const uint32_t ak_addr = smem_u32(sAK), av_addr = smem_u32(sAV), b2_addr = smem_u32(sB2);
+      mbar_wait(&full[s], (n >> 1) & 1);
+      tc_fence_after();
+      if (elect_one()) {
+        constexpr uint32_t idesc16 = umma_idesc_bf16(128, 16, 0, 0);
+#pragma unroll
+        for (int k = 0; k < 4; ++k) {
+          tc_mma_ss(tSp, umma_desc_sw128(q_addr + k * 32, 16, 1024), umma_desc_sw128(ak_addr + k * 32, 16, 1024), idesc16, k != 0);
+          tc_mma_ss(tdPV, umma_desc_sw128(do_addr + k * 32, 16, 1024), umma_desc_sw128(av_addr + k * 32, 16, 1024), idesc16, k != 0);
+        }
+        tc_commit(sp_full);
+      }
+      __syncwarp();
+      mbar_wait(dsp_full, n & 1);              // dS_a in TMEM, [dS_a | gP] in smem
+      tc_fence_after();
+      const bool acc = n > 0;
+      if (elect_one()) {
+        if (p.need_dqkv) {
+          tc_mma_ts(tdq, tdSp, umma_desc_sw128(ak_addr, 8192, 1024), umma_idesc_bf16(128, 64, 0, 1), 0);
+          tc_commit(dq_full);
+        }
+        constexpr uint32_t idesc_t = umma_idesc_bf16(128, 32, 1, 0);
+#pragma unroll
+        for (int k = 0; k < 8; ++k)     // A: 16 rows (K) x [64 d of Q | 64 d of dO] (M), MN-major; B: [32 n][16 rows], K-major
+          tc_mma_ss(tacc, umma_desc_sw128(q_addr + k * 2048, TILE_BYTES, 1024),
+                    umma_desc_sw128(b2_addr + (k >> 2) * 4096 + (k & 3) * 32, 16, 1024), idesc_t, acc || k != 0);
+        tc_commit(&stage_free[s]);
+        tc_commit(acc_done);
+      }
+      __syncwarp();
+    }
+  } else {
+    // ---------------- row threads: thread = one token row of the 128-row tile ----------------
+    const int r = warp * 32 + lane;
+    const uint32_t lane_off = (uint32_t)(warp * 32) << 16;
+    const int aT = p.prefix_len;
+    const float gate = p.gate[h];
+    float dgate_acc = 0.f;
+    for (int n = 0; n < my_tiles; ++n) {
+      const int s = n & 1;
+      const long long m = (long long)((int)blockIdx.x + n * (int)gridDim.x) * 128 + r;
+      const bool valid = m < M;
+      mbar_wait(&full[s], (n >> 1) & 1);
+      // rowsum(dO * out) from the staged tiles (128B-swizzled rows)
+      float dot_out = 0.f;
+      {
+        const uint8_t* sdO = smem + s * PFX_STAGE + TILE_BYTES + r * 128;
+        const uint8_t* sO = sdO + TILE_BYTES;
+#pragma unroll
+        for (int c8 = 0; c8 < 8; ++c8) {
+          float ov[8], dv[8];
+          unpack8(*reinterpret_cast<const uint4*>(sO + ((c8 ^ (r & 7)) << 4)), ov);
+          unpack8(*reinterpret_cast<const uint4*>(sdO + ((c8 ^ (r & 7)) << 4)), dv);
+#pragma unroll
+          for (int i = 0; i < 8; ++i) dot_out += ov[i] * dv[i];
+        }
+      }
+      mbar_wait(sp_full, n & 1);
+      tc_fence_after();
+      uint32_t sv[16], dv[16];
+      tmem_ld16(tSp + lane_off, sv);
+      tmem_ld16(tdPV + lane_off, dv);
+      tmem_wait_ld();
+      float mx = -INFINITY;
+#pragma unroll
+      for (int a = 0; a < MAX_PREFIX; ++a) if (a < aT) mx = fmaxf(mx, __uint_as_float(sv[a]));
+      float pa[MAX_PREFIX], sum = 0.f;
+#pragma unroll
+      for (int a = 0; a < MAX_PREFIX; ++a) {
+        pa[a] = (a < aT) ? fast_exp2((__uint_as_float(sv[a]) - mx) * p.scale_log2) : 0.f;
+        sum += pa[a];
+      }
+      const float inv = 1.f / sum;
+      float doay = 0.f;
+#pragma unroll
+      for (int a = 0; a < MAX_PREFIX; ++a) { pa[a] *= inv; doay += pa[a] * __uint_as_float(dv[a]); }
+      if (valid) {
+        p.delta[((long long)(m / p.T) * p.H + h) * p.T + (m % p.T)] = dot_out - gate * doay;
+        dgate_acc += doay;
+      }
+      // dS_a (scaled) and gP, bf16: A operand of dQ_a (TMEM) and B operand of the dAK / dAV accumulation (smem)
+      uint32_t dsp[8];
+      float dsf[MAX_PREFIX], gpf[MAX_PREFIX];
+#pragma unroll
+      for (int a = 0; a < MAX_PREFIX; ++a) {
+        dsf[a] = valid ? pa[a] * gate * (__uint_as_float(dv[a]) - doay) * p.scale : 0.f;
+        gpf[a] = valid ? gate * pa[a] : 0.f;
+      }
+#pragma unroll
+      for (int a = 0; a < 8; ++a) dsp[a] = pack_bf16x2(dsf[2 * a], dsf[2 * a + 1]);
+      tmem_st8(tdSp + lane_off, dsp);
+      if (n > 0) mbar_wait(acc_done, (n - 1) & 1);      // the previous tile's accumulation has read sB2
+      {
+        uint8_t* b2 = sB2 + (r >> 6) * 4096;
+        const int col = r & 63;
+#pragma unroll
+        for (int a = 0; a < MAX_PREFIX; ++a) {
+          *reinterpret_cast<bf16*>(b2 + sw128_offset(a, col)) = __float2bfloat16_rn(dsf[a]);
+          *reinterpret_cast<bf16*>(b2 + sw128_offset(16 + a, col)) = __float2bfloat16_rn(gpf[a]);
+        }
+      }
+      fence_proxy_async_smem();
+      tmem_wait_st();
+      tc_fence_before();
+      mbar_arrive(dsp_full);
+      if (p.need_dqkv) {
+        mbar_wait(dq_full, n & 1);
+        tc_fence_after();
+        uint32_t q0[32], q1[32];
+        tmem_ld32(tdq + lane_off, q0);
+        tmem_ld32(tdq + lane_off + 32, q1);
+        tmem_wait_ld();
+        tc_fence_before();
+        if (valid) {
+          uint4* dq4 = reinterpret_cast<uint4*>(p.dqkv + m * p.ld_qkv + q_slot * HD);
+#pragma unroll
+          for (int i = 0; i < 4; ++i) {
+            float t8[8], u8[8];
+#pragma unroll
+            for (int k = 0; k < 8; ++k) { t8[k] = __uint_as_float(q0[8 * i + k]); u8[k] = __uint_as_float(q1[8 * i + k]); }
+            dq4[i] = pack8(t8);
+            dq4[4 + i] = pack8(u8);
+          }
+        }
+      }
+    }
+    // ---- d(prefix k / v) and d(gate): one atomic per element and CTA ----
+    if (my_tiles > 0) {
+      mbar_wait(acc_done, (my_tiles - 1) & 1);
+      tc_fence_after();
+      uint32_t acc[16];
+      // lanes 0..63 hold dAK^T rows (d = r) in columns 0..15, lanes 64..127 dAV^T rows (d = r - 64) in columns 16..31
+      tmem_ld16(tacc + lane_off + (r < 64 ? 0 : 16), acc);
+      tmem_wait_ld();
+      tc_fence_before();
+      float* dst = p.d_prefix_kv + (long long)(r < 64 ? k_slot : v_slot) * HD + (r & 63);
+#pragma unroll
+      for (int a = 0; a < MAX_PREFIX; ++a)
+        if (a < aT) atomicAdd(dst + (long long)a * p.ld_qkv, __uint_as_float(acc[a]));
+    }
+    dgate_acc = warp_sum(dgate_acc);
+    if (lane == 0) s_gate_part[warp] = dgate_acc;
+    named_bar_sync(1, 128);
+    if (threadIdx.x == 0) atomicAdd(p.d_gate + h, s_gate_part[0] + s_gate_part[1] + s_gate_part[2] + s_gate_part[3]);
+  }
+  tc_fence_before();
+  __syncthreads();
+  if (warp == 5) { tc_fence_after(); tmem_dealloc(tmem, 256); }
+}
+
+// =================================================================================================
 // decode: one query per (sequence, head) against the KV cache.  Block = (sequence, kv group); warp = one
 // q head of the group; keys strided over lanes for the scores, head dims over lanes for P V.
 // =================================================================================================
@@ -1273,10 +1376,28 @@ extern "C" int dh_attention_bwd(const void* qkv, const void* out, const void* do
   p.need_dqkv = need_dqkv;
   p.rope_cos = (const bf16*)rope_cos; p.rope_sin = (const bf16*)rope_sin;
   const long long M = (long long)B * T;
-  {
-    int gx = (int)((M + 127) / 128);
-    if (gx > 64) gx = 64;
-    attn_bwd_prep_kernel<<<dim3(gx, p.H), 128, 0, s>>>(p);
+  if (!has_prefix) {
+    const long long pairs = M * p.H;
+    long long gx = (pairs + 31) / 32;
+    if (gx > 148 * 16) gx = 148 * 16;
+    attn_bwd_delta_kernel<<<(unsigned)gx, 256, 0, s>>>(p);
+    DH_CUDA(cudaGetLastError());
+  } else {
+    CUtensorMap tQ, tDO, tO, tP;
+    if (make_head_map(&tQ, qkv, p.slots, M, p.ld_qkv)) return -3;
+    if (make_head_map(&tDO, dout, p.H, M, (long long)p.H * HD)) return -3;
+    if (make_head_map(&tO, out, p.H, M, (long long)p.H * HD)) return -3;
+    if (make_head_map(&tP, prefix_kv, p.slots, p.prefix_len, p.ld_qkv, 16)) return -3;
+    static bool pattr = false;
+    if (!pattr) {
+      DH_CUDA(cudaFuncSetAttribute(attn_bwd_prefix_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, PFX_SMEM));
+      pattr = true;
+    }
+    const int ntiles = (int)((M + 127) / 128);
+    int gx = (2 * sm_count() + p.H - 1) / p.H;
+    if (gx > ntiles) gx = ntiles;
+    if (gx < 1) gx = 1;
+    attn_bwd_prefix_kernel<<<dim3(gx, p.H), PFX_THREADS, PFX_SMEM, s>>>(tQ, tDO, tO, tP, p);
     DH_CUDA(cudaGetLastError());
   }
   if (!need_dqkv) return 0;
