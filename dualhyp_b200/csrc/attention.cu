@@ -149,11 +149,12 @@ constexpr int FWD_OFF_K = 2 * TILE_BYTES, FWD_OFF_V = 4 * TILE_BYTES, FWD_OFF_AK
 constexpr int FWD_SMEM = FWD_OFF_BAR + 256 + 1024;
 constexpr float RESCALE_THRESHOLD = 8.f;   // log2 units
 
-// O[128 x 64] (+)= P[128 x 16*ksteps] (TMEM, bf16 pairs per column) * V[16*ksteps keys x 64] (smem, MN-major)
-__device__ __forceinline__ void mma_pv_ts(uint32_t d_tmem, uint32_t p_tmem, uint32_t v_smem, int ksteps, bool accumulate) {
+// D[128 x 64] (+)= A[128 x 128] (TMEM, bf16 pairs per column) * B[128 x 64] (smem tile [k rows][64], MN-major)
+__device__ __forceinline__ void mma_ts_k128(uint32_t d_tmem, uint32_t a_tmem, uint32_t b_smem, bool accumulate) {
   constexpr uint32_t idesc = umma_idesc_bf16(128, 64, 0, 1);
-  for (int k = 0; k < ksteps; ++k)
-    tc_mma_ts(d_tmem, p_tmem + k * 8, umma_desc_sw128(v_smem + k * 2048, 8192, 1024), idesc, accumulate || k != 0);
+#pragma unroll
+  for (int k = 0; k < 8; ++k)
+    tc_mma_ts(d_tmem, a_tmem + k * 8, umma_desc_sw128(b_smem + k * 2048, 8192, 1024), idesc, accumulate || k != 0);
 }
 
 // max over one 32-column chunk of a score row; TRI: only columns <= lane are visible (diagonal chunk)
@@ -216,7 +217,7 @@ __global__ void __launch_bounds__(FWD_THREADS, 2) attn_fwd_kernel(const __grid_c
            *pfx_full = bars + 14;
   uint32_t* tmem_slot = reinterpret_cast<uint32_t*>(bars + 16);
 
-  const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
+  const int warp = __shfl_sync(0xffffffffu, threadIdx.x >> 5, 0), lane = threadIdx.x & 31;   // shfl: warp-uniform for the compiler
   TRC_DECL
   TRC(0);
   const int nq = (p.T + ATT_BQ - 1) / ATT_BQ;
@@ -252,7 +253,7 @@ __global__ void __launch_bounds__(FWD_THREADS, 2) attn_fwd_kernel(const __grid_c
   tc_fence_before();
   __syncthreads();
   tc_fence_after();
-  const uint32_t tmem = *tmem_slot;
+  const uint32_t tmem = __shfl_sync(0xffffffffu, *tmem_slot, 0);
   const uint32_t tS = tmem, tO = tmem + 128, tP = tmem + 192;
 
   if (warp == FWD_SM_WARPS) {
@@ -278,53 +279,74 @@ __global__ void __launch_bounds__(FWD_THREADS, 2) attn_fwd_kernel(const __grid_c
       }
     }
   } else if (warp == FWD_SM_WARPS + 1) {
-    // ---------------- MMA issuer ----------------
-    if (lane == 0) {
-      int n = 0, es = 0, ep = 0;
-      if (has_prefix) mbar_wait(pfx_full, 0);
-      for (int it = 0; it < n_items; ++it) {
-        const int nkv = (it ? qi_second : qi_first) + 1;
-        const uint32_t q_addr = smem_u32(sQ + it * TILE_BYTES);
-        mbar_wait(&q_full[it], 0);
-        tc_fence_after();
-        if (has_prefix) {
+    // ---------------- MMA issuer: the whole warp walks the loop (uniform operands), one elected lane issues ----------------
+    int n = 0, es = 0, ep = 0;
+    if (has_prefix) mbar_wait(pfx_full, 0);
+    for (int it = 0; it < n_items; ++it) {
+      const int nkv = (it ? qi_second : qi_first) + 1;
+      const uint32_t q_addr = smem_u32(sQ + it * TILE_BYTES);
+      mbar_wait(&q_full[it], 0);
+      tc_fence_after();
+      if (has_prefix) {
+        const uint32_t ak_addr = smem_u32(sAK);
+        if (elect_one()) {
           constexpr uint32_t idesc16 = umma_idesc_bf16(128, 16, 0, 0);
 #pragma unroll
           for (int k = 0; k < 4; ++k)
-            tc_mma_ss(tS, umma_desc_sw128(q_addr + k * 32, 16, 1024), umma_desc_sw128(smem_u32(sAK) + k * 32, 16, 1024), idesc16, k != 0);
+            tc_mma_ss(tS, umma_desc_sw128(q_addr + k * 32, 16, 1024), umma_desc_sw128(ak_addr + k * 32, 16, 1024), idesc16, k != 0);
           tc_commit(s_full);
-          mbar_wait(s_free, es & 1); ++es;
-          tc_fence_after();
         }
-        mbar_wait(&k_full[n & 1], (n >> 1) & 1);
+        __syncwarp();
+        mbar_wait(s_free, es & 1); ++es;
         tc_fence_after();
-        mma_qk(tS, q_addr, smem_u32(sK + (n & 1) * TILE_BYTES));
-        tc_commit(&k_free[n & 1]);
-        tc_commit(s_full);
-        for (int j = 0; j < nkv; ++j, ++n) {
-          mbar_wait(s_free, es & 1); ++es;           // S(j) is in registers
+      }
+      mbar_wait(&k_full[n & 1], (n >> 1) & 1);
+      tc_fence_after();
+      {
+        const uint32_t k_addr = smem_u32(sK + (n & 1) * TILE_BYTES);
+        if (elect_one()) {
+          mma_qk(tS, q_addr, k_addr);
+          tc_commit(&k_free[n & 1]);
+          tc_commit(s_full);
+        }
+        __syncwarp();
+      }
+      for (int j = 0; j < nkv; ++j, ++n) {
+        mbar_wait(s_free, es & 1); ++es;           // S(j) is in registers
+        tc_fence_after();
+        if (j + 1 < nkv) {
+          const int n1 = n + 1;
+          mbar_wait(&k_full[n1 & 1], (n1 >> 1) & 1);
           tc_fence_after();
-          if (j + 1 < nkv) {
-            const int n1 = n + 1;
-            mbar_wait(&k_full[n1 & 1], (n1 >> 1) & 1);
-            tc_fence_after();
-            mma_qk(tS, q_addr, smem_u32(sK + (n1 & 1) * TILE_BYTES));
+          const uint32_t k_addr = smem_u32(sK + (n1 & 1) * TILE_BYTES);
+          if (elect_one()) {
+            mma_qk(tS, q_addr, k_addr);
             tc_commit(&k_free[n1 & 1]);
             tc_commit(s_full);
           }
-          mbar_wait(p_full, ep & 1); ++ep;           // P(j) is in TMEM, O rescaled if needed
-          mbar_wait(&v_full[n & 1], (n >> 1) & 1);
-          tc_fence_after();
-          mma_pv_ts(tO, tP, smem_u32(sV + (n & 1) * TILE_BYTES), 8, j > 0);
+          __syncwarp();
+        }
+        mbar_wait(p_full, ep & 1); ++ep;           // P(j) is in TMEM, O rescaled if needed
+        mbar_wait(&v_full[n & 1], (n >> 1) & 1);
+        tc_fence_after();
+        const uint32_t v_addr = smem_u32(sV + (n & 1) * TILE_BYTES);
+        const bool acc = j > 0;
+        if (elect_one()) {
+          mma_ts_k128(tO, tP, v_addr, acc);
           tc_commit(&v_free[n & 1]);
           tc_commit(o_done);
         }
-        if (has_prefix) {
-          mbar_wait(p_full, ep & 1); ++ep;
-          tc_fence_after();
-          mma_pv_ts(tO, tP, smem_u32(sAV), 1, true);
+        __syncwarp();
+      }
+      if (has_prefix) {
+        mbar_wait(p_full, ep & 1); ++ep;
+        tc_fence_after();
+        const uint32_t av_addr = smem_u32(sAV);
+        if (elect_one()) {
+          tc_mma_ts(tO, tP, umma_desc_sw128(av_addr, 8192, 1024), umma_idesc_bf16(128, 64, 0, 1), 1);
           tc_commit(o_done);
         }
+        __syncwarp();
       }
     }
   } else {
@@ -498,14 +520,6 @@ constexpr int DKV_STAGES = 3;     // Q / dO ring
 constexpr int DKV_THREADS = (DKV_SM_WARPS + 2) * 32;
 constexpr int DKV_OFF_QDO = 4 * TILE_BYTES, DKV_OFF_STAT = (4 + 2 * DKV_STAGES) * TILE_BYTES, DKV_OFF_BAR = DKV_OFF_STAT + DKV_STAGES * 256 * 4;
 constexpr int DKV_SMEM = DKV_OFF_BAR + 256 + 1024;
-
-// D[128 x 64] (+)= A[128 x 128] (TMEM, bf16 pairs per column) * B[128 x 64] (smem tile [k rows][64], MN-major)
-__device__ __forceinline__ void mma_ts_k128(uint32_t d_tmem, uint32_t a_tmem, uint32_t b_smem, bool accumulate) {
-  constexpr uint32_t idesc = umma_idesc_bf16(128, 64, 0, 1);
-#pragma unroll
-  for (int k = 0; k < 8; ++k)
-    tc_mma_ts(d_tmem, a_tmem + k * 8, umma_desc_sw128(b_smem + k * 2048, 8192, 1024), idesc, accumulate || k != 0);
-}
 
 __device__ __forceinline__ float4 lds128(uint32_t addr) {
   float4 v;

@@ -195,7 +195,7 @@ gemm_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant__ CUt
   uint64_t* tempty_bar = bars + 2 * STAGES + 2;  // [2]   epilogue -> MMA
   uint32_t* tmem_slot = reinterpret_cast<uint32_t*>(bars + 2 * STAGES + 4);
 
-  const int warp = threadIdx.x >> 5;
+  const int warp = __shfl_sync(0xffffffffu, threadIdx.x >> 5, 0);   // shfl: a warp-uniform value for the compiler
   const int lane = threadIdx.x & 31;
   const int num_tiles = p.tiles_m * p.tiles_n;
   const int nkb1 = (p.K1 + BK - 1) / BK;   // a ragged K tail is zero-filled by TMA
@@ -218,7 +218,7 @@ gemm_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant__ CUt
   tc_fence_before();
   __syncthreads();
   tc_fence_after();
-  const uint32_t tmem_base = *tmem_slot;
+  const uint32_t tmem_base = __shfl_sync(0xffffffffu, *tmem_slot, 0);
 
   if (warp == 0 && lane == 0) {
     // ===================== TMA producer =====================
@@ -250,8 +250,8 @@ gemm_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant__ CUt
         }
       }
     }
-  } else if (warp == 1 && lane == 0) {
-    // ===================== MMA issuer =====================
+  } else if (warp == 1) {
+    // ===================== MMA issuer: the whole warp walks the loop (uniform operands), one elected lane issues =====================
     uint32_t it = 0, tcount = 0;
     for (int tile = blockIdx.x; tile < num_tiles; tile += gridDim.x, ++tcount) {
       const int acc = tcount & 1;
@@ -268,17 +268,20 @@ gemm_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant__ CUt
         const uint32_t idesc = umma_idesc_bf16(BM, BN, a_mn, b_mn);
         const uint32_t sa = smem_u32(smem + s * Cfg::STAGE_BYTES);
         const uint32_t sb = sa + Cfg::A_BYTES;
+        if (elect_one()) {
 #pragma unroll
-        for (int k = 0; k < BK / 16; ++k) {
-          // K-major: 16 k-elements = 32 bytes inside the 128B swizzle row.  MN-major: 16 k-rows = two
-          // 8-row atoms of 1024 B; 64-wide MN groups are 8 KB apart (LBO), 8-row atoms 1 KB apart (SBO).
-          const uint64_t da = a_mn ? umma_desc_sw128(sa + k * 2048, 8192, 1024) : umma_desc_sw128(sa + k * 32, 16, 1024);
-          const uint64_t db = b_mn ? umma_desc_sw128(sb + k * 2048, 8192, 1024) : umma_desc_sw128(sb + k * 32, 16, 1024);
-          tc_mma_ss(d_tmem, da, db, idesc, (kb | k) != 0);
+          for (int k = 0; k < BK / 16; ++k) {
+            // K-major: 16 k-elements = 32 bytes inside the 128B swizzle row.  MN-major: 16 k-rows = two
+            // 8-row atoms of 1024 B; 64-wide MN groups are 8 KB apart (LBO), 8-row atoms 1 KB apart (SBO).
+            const uint64_t da = a_mn ? umma_desc_sw128(sa + k * 2048, 8192, 1024) : umma_desc_sw128(sa + k * 32, 16, 1024);
+            const uint64_t db = b_mn ? umma_desc_sw128(sb + k * 2048, 8192, 1024) : umma_desc_sw128(sb + k * 32, 16, 1024);
+            tc_mma_ss(d_tmem, da, db, idesc, (kb | k) != 0);
+          }
+          tc_commit(&empty_bar[s]);   // frees the smem slot when these MMAs have drained
+          if (kb == nkb - 1) tc_commit(&tfull_bar[acc]);   // accumulator complete
         }
-        tc_commit(&empty_bar[s]);   // frees the smem slot when these MMAs have drained
+        __syncwarp();
       }
-      tc_commit(&tfull_bar[acc]);   // accumulator complete
     }
   } else if (warp >= 4) {
     // ===================== epilogue =====================
@@ -567,7 +570,7 @@ gemm_pair_kernel(const __grid_constant__ PairMaps tm, const GemmParams p) {
   uint64_t* eload_bar = bars + 2 * STAGES + 4;   // [8][2]    epilogue box prefetch, per warp and buffer
   uint32_t* tmem_slot = reinterpret_cast<uint32_t*>(bars + 2 * STAGES + 4 + 2 * PAIR_EPI_WARPS);
 
-  const int warp = threadIdx.x >> 5;
+  const int warp = __shfl_sync(0xffffffffu, threadIdx.x >> 5, 0);   // shfl: a warp-uniform value for the compiler
   const int lane = threadIdx.x & 31;
   const uint32_t rank = cluster_ctarank();
   const int pair = blockIdx.x >> 1;
@@ -599,7 +602,7 @@ gemm_pair_kernel(const __grid_constant__ PairMaps tm, const GemmParams p) {
   tc_fence_before();
   cluster_sync_all();
   tc_fence_after();
-  const uint32_t tmem_base = *tmem_slot;
+  const uint32_t tmem_base = __shfl_sync(0xffffffffu, *tmem_slot, 0);
 
   if (warp == 0 && lane == 0) {
     // ===================== TMA producer (each CTA loads its own halves) =====================
@@ -620,7 +623,7 @@ gemm_pair_kernel(const __grid_constant__ PairMaps tm, const GemmParams p) {
         tma_load_2d_pair(sb, second ? &tm.B2 : &tm.B, k0, n0, bar);
       }
     }
-  } else if (warp == 1 && lane == 0 && rank == 0) {
+  } else if (warp == 1 && rank == 0) {
     // ===================== MMA issuer (leader CTA only) =====================
     constexpr uint32_t idesc = umma_idesc_bf16(256, BN, 0, 0);
     uint32_t it = 0, tcount = 0;
@@ -635,12 +638,15 @@ gemm_pair_kernel(const __grid_constant__ PairMaps tm, const GemmParams p) {
         tc_fence_after();
         const uint32_t sa = smem_u32(smem + s * Cfg::STAGE_BYTES);
         const uint32_t sb = sa + Cfg::A_BYTES;
+        if (elect_one()) {
 #pragma unroll
-        for (int k = 0; k < BK / 16; ++k)
-          tc_mma_ss_pair(d_tmem, umma_desc_sw128(sa + k * 32, 16, 1024), umma_desc_sw128(sb + k * 32, 16, 1024), idesc, (kb | k) != 0);
-        tc_commit_pair(&empty_bar[s], 3);
+          for (int k = 0; k < BK / 16; ++k)
+            tc_mma_ss_pair(d_tmem, umma_desc_sw128(sa + k * 32, 16, 1024), umma_desc_sw128(sb + k * 32, 16, 1024), idesc, (kb | k) != 0);
+          tc_commit_pair(&empty_bar[s], 3);
+          if (kb == nkb - 1) tc_commit_pair(&tfull_bar[acc], 3);
+        }
+        __syncwarp();
       }
-      tc_commit_pair(&tfull_bar[acc], 3);
     }
   } else if (warp >= 4) {
     // ===================== epilogue (each CTA drains its own 128 accumulator rows) =====================
