@@ -59,6 +59,8 @@ SIGNATURES = {
     "dh_attention_bwd_workspace": (_Z, [_I, _I, _I, _I]),
     "dh_attention_bwd": (_I, [_P, _P, _P, _P, _P, _P, _P, _P, _P, _I, _P, _P, _I, _I, _I, _I, _I, _P, _Z, _P]),
     "dh_attention_decode": (_I, [_P, _P, _P, _P, _P, _P, _P, _I, _I, _I, _I, _I, _P]),
+    "dh_prefix_project_fwd": (_I, [_P, _P, _P, _I, _I, _I, _I, _I, _P]),
+    "dh_prefix_project_bwd": (_I, [_P, _P, _P, _I, _I, _I, _I, _I, _P]),
     "dh_kv_cache_write": (_I, [_P, _P, _P, _P, _P, _I, _I, _I, _I, _P]),
     "dh_cross_entropy": (_I, [_P, _L, _P, _P, _I, _I, _F, _I, _P]),
     "dh_loss_reduce": (_I, [_P, _P, _P, _I, _P]),

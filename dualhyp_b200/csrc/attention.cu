@@ -50,16 +50,6 @@ __device__ __forceinline__ void store_a_chunk(uint8_t* base, int r, int c, const
   }
 }
 
-__device__ __forceinline__ void unpack8(const uint4& u, float (&f)[8]) {
-  float2 a = unpack_bf16x2(u.x), b = unpack_bf16x2(u.y), c = unpack_bf16x2(u.z), d = unpack_bf16x2(u.w);
-  f[0] = a.x; f[1] = a.y; f[2] = b.x; f[3] = b.y; f[4] = c.x; f[5] = c.y; f[6] = d.x; f[7] = d.y;
-}
-__device__ __forceinline__ uint4 pack8(const float (&f)[8]) {
-  uint4 u;
-  u.x = pack_bf16x2(f[0], f[1]); u.y = pack_bf16x2(f[2], f[3]); u.z = pack_bf16x2(f[4], f[5]); u.w = pack_bf16x2(f[6], f[7]);
-  return u;
-}
-
 // S/dP style MMA: D[128 x 128] = A[128 x 64] * B[128 x 64]^T, both K-major tiles.
 __device__ __forceinline__ void mma_qk(uint32_t d_tmem, uint32_t a_smem, uint32_t b_smem) {
   constexpr uint32_t idesc = umma_idesc_bf16(128, 128, 0, 0);

@@ -325,6 +325,89 @@ static inline int grid_for(long long work, int block) {
   return (int)(g < 1 ? 1 : (g > cap ? cap : g));
 }
 
+// -------------------------------------------------------------------------------------------------
+// Adapter prefix K/V projection for ALL adapter layers in one launch (ger/adapter.py:129-137: `self.attn(prefix)`
+// then only the k and v slots are used).  wkv [L, G*128, C] holds the k and v rows of every layer's QKV weight
+// (row r of group g: k rows 0..63, v rows 64..127).  HBM-bound on the weights: one warp per weight row, the aT
+// prefix rows of the layer staged in shared memory.
+// -------------------------------------------------------------------------------------------------
+constexpr int PFX_MAX = 16;
+
+__global__ void __launch_bounds__(256) prefix_project_fwd_kernel(const bf16* __restrict__ prefix, const bf16* __restrict__ wkv,
+                                                                 bf16* __restrict__ out, int aT, int C, int R, int G, int qpk,
+                                                                 long long ld_out, int rows_per_block) {
+  extern __shared__ uint4 spfx4[];                    // [aT][C] bf16
+  const int l = blockIdx.y;
+  const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
+  const uint4* src = reinterpret_cast<const uint4*>(prefix + (long long)l * aT * C);
+  for (int i = threadIdx.x; i < aT * C / 8; i += blockDim.x) spfx4[i] = src[i];
+  __syncthreads();
+  const int r0 = blockIdx.x * rows_per_block;
+  for (int r = r0 + warp; r < r0 + rows_per_block && r < R; r += 8) {
+    const uint4* wrow = reinterpret_cast<const uint4*>(wkv + ((long long)l * R + r) * C);
+    float acc[PFX_MAX];
+#pragma unroll
+    for (int a = 0; a < PFX_MAX; ++a) acc[a] = 0.f;
+    for (int c8 = lane; c8 < C / 8; c8 += 32) {
+      float w[8];
+      unpack8(__ldg(wrow + c8), w);
+#pragma unroll
+      for (int a = 0; a < PFX_MAX; ++a) {
+        if (a < aT) {
+          float x[8];
+          unpack8(spfx4[a * (C / 8) + c8], x);
+#pragma unroll
+          for (int i = 0; i < 8; ++i) acc[a] += w[i] * x[i];
+        }
+      }
+    }
+    const int g = r / 128, rr = r % 128;
+    const long long col = (long long)(g * (qpk + 2) + qpk) * 64 + rr;
+#pragma unroll
+    for (int a = 0; a < PFX_MAX; ++a) {
+      if (a < aT) {
+        const float v = warp_sum(acc[a]);
+        if (lane == 0) out[((long long)l * aT + a) * ld_out + col] = __float2bfloat16_rn(v);
+      }
+    }
+  }
+}
+
+// d(prefix)[l, a, c] = sum_r d(prefix_kv)[l, a, col(r)] * wkv[l, r, c]   (fp32 out; thread = 2 columns c)
+__global__ void __launch_bounds__(128) prefix_project_bwd_kernel(const float* __restrict__ dpkv, const bf16* __restrict__ wkv,
+                                                                 float* __restrict__ dprefix, int aT, int C, int R, int G, int qpk,
+                                                                 long long ld) {
+  extern __shared__ float sd[];                       // [aT][R]
+  const int l = blockIdx.y;
+  for (int i = threadIdx.x; i < aT * R; i += blockDim.x) {
+    const int a = i / R, r = i % R;
+    const int g = r / 128, rr = r % 128;
+    sd[i] = dpkv[((long long)l * aT + a) * ld + (long long)(g * (qpk + 2) + qpk) * 64 + rr];
+  }
+  __syncthreads();
+  const int c = (blockIdx.x * 128 + threadIdx.x) * 2;
+  if (c >= C) return;
+  float a0[PFX_MAX], a1[PFX_MAX];
+#pragma unroll
+  for (int a = 0; a < PFX_MAX; ++a) { a0[a] = 0.f; a1[a] = 0.f; }
+  const bf16* wl = wkv + (long long)l * R * C + c;
+#pragma unroll 4
+  for (int r = 0; r < R; ++r) {
+    const float2 w = unpack_bf16x2(__ldg(reinterpret_cast<const uint32_t*>(wl + (long long)r * C)));
+#pragma unroll
+    for (int a = 0; a < PFX_MAX; ++a) {
+      if (a < aT) {
+        const float d = sd[a * R + r];
+        a0[a] += d * w.x;
+        a1[a] += d * w.y;
+      }
+    }
+  }
+#pragma unroll
+  for (int a = 0; a < PFX_MAX; ++a)
+    if (a < aT) *reinterpret_cast<float2*>(dprefix + ((long long)l * aT + a) * C + c) = make_float2(a0[a], a1[a]);
+}
+
 }  // namespace dh
 
 using namespace dh;
@@ -446,6 +529,38 @@ extern "C" int dh_kv_cache_write(const void* qkv, void* cache_k, void* cache_v, 
   const long long total = (long long)M * n_groups * 16;
   kv_cache_write_kernel<<<grid_for(total, 256), 256, 0, (cudaStream_t)stream>>>((const bf16*)qkv, (bf16*)cache_k, (bf16*)cache_v, seq,
                                                                                  pos, M, max_len, n_groups, q_per_kv);
+  DH_CUDA(cudaGetLastError());
+  return 0;
+}
+
+extern "C" int dh_prefix_project_fwd(const void* prefix, const void* wkv, void* prefix_kv, int L, int aT, int C, int n_groups,
+                                     int q_per_kv, void* stream) {
+  DH_CHECK(prefix && wkv && prefix_kv && L > 0 && aT > 0 && aT <= PFX_MAX && C % 256 == 0, "dh_prefix_project_fwd: bad argument");
+  const int R = n_groups * 128;
+  const size_t smem = (size_t)aT * C * 2;
+  DH_CHECK(smem <= 96 * 1024, "dh_prefix_project_fwd: prefix rows do not fit in shared memory");
+  static bool attr = false;
+  if (!attr) {
+    DH_CUDA(cudaFuncSetAttribute(prefix_project_fwd_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, 96 * 1024));
+    attr = true;
+  }
+  const int rows_per_block = 32;
+  const long long ld_out = (long long)n_groups * (q_per_kv + 2) * 64;
+  prefix_project_fwd_kernel<<<dim3((R + rows_per_block - 1) / rows_per_block, L), 256, smem, (cudaStream_t)stream>>>(
+      (const bf16*)prefix, (const bf16*)wkv, (bf16*)prefix_kv, aT, C, R, n_groups, q_per_kv, ld_out, rows_per_block);
+  DH_CUDA(cudaGetLastError());
+  return 0;
+}
+
+extern "C" int dh_prefix_project_bwd(const float* d_prefix_kv, const void* wkv, float* d_prefix, int L, int aT, int C, int n_groups,
+                                     int q_per_kv, void* stream) {
+  DH_CHECK(d_prefix_kv && wkv && d_prefix && L > 0 && aT > 0 && aT <= PFX_MAX && C % 256 == 0, "dh_prefix_project_bwd: bad argument");
+  const int R = n_groups * 128;
+  const size_t smem = (size_t)aT * R * 4;
+  DH_CHECK(smem <= 48 * 1024, "dh_prefix_project_bwd: too many kv rows");
+  const long long ld = (long long)n_groups * (q_per_kv + 2) * 64;
+  prefix_project_bwd_kernel<<<dim3(C / 256, L), 128, smem, (cudaStream_t)stream>>>(d_prefix_kv, (const bf16*)wkv, d_prefix, aT, C, R,
+                                                                                   n_groups, q_per_kv, ld);
   DH_CUDA(cudaGetLastError());
   return 0;
 }

@@ -138,6 +138,12 @@ class DecoderEngine:
                 for k in ("wqkv", "wproj", "w12", "wmlp"):
                     lw[k + "_t"] = lw[k].t().contiguous()
             self.layers.append(lw)
+        self.wkv_all = None
+        if s.variant == "adapter" and s.adapter_start_layer < s.n_layer:
+            # k rows then v rows of every group, for all adapter layers: the operand of the batched prefix projection
+            G, qpk = s.n_query_groups, s.qpk
+            rows = torch.cat([torch.arange((g * (qpk + 2) + qpk) * 64, (g * (qpk + 2) + qpk + 2) * 64) for g in range(G)]).to(dev)
+            self.wkv_all = torch.stack([self.layers[i]["wqkv"].index_select(0, rows) for i in range(s.adapter_start_layer, s.n_layer)]).contiguous()
         self.wte = sd["transformer.wte.weight"].detach().to(dev).contiguous()
         if self.wte.dtype not in (torch.float32, torch.bfloat16):
             self.wte = self.wte.float()
@@ -187,6 +193,8 @@ class DecoderEngine:
                     d["proj_a_t"], d["proj_b_t"] = a_pad.t().contiguous(), b_ext.t().contiguous()
             if d:
                 packed[i] = d
+        if s.variant == "adapter" and s.adapter_start_layer < s.n_layer:
+            packed[-1] = {"prefix_all": torch.stack([packed[i]["prefix"] for i in range(s.adapter_start_layer, s.n_layer)]).contiguous()}
         return packed
 
     # ------------------------------------------------------------------------------------------
@@ -223,6 +231,7 @@ class DecoderEngine:
         n = self._buf("n", (M, C), bf)
         act = self._buf("act", (M, I), bf)
         saved = dict(B=B, T=T, layers=[], packed=packed) if save else None
+        pkv_all = self._project_prefixes(packed, "pkv_all")
         for i, lw in enumerate(self.layers):
             pk = packed.get(i, {})
             rstd1 = self._buf(per("rstd1_", i), (M,), f32)
@@ -239,8 +248,7 @@ class DecoderEngine:
                 ops.gemm(n_i, lw["wqkv"], qkv, epilogue=ops.EPI_QKV_ROPE, rope_cos=self.cos, rope_sin=self.sin, seq_len=T, q_per_kv=qpk)
             prefix_kv = gate = None
             if "prefix" in pk:
-                prefix_kv = self._buf(per("pkv", i), (s.adapter_prompt_length, s.qkv_out), bf)
-                ops.gemm(pk["prefix"], lw["wqkv"], prefix_kv)
+                prefix_kv = pkv_all[i - s.adapter_start_layer]
                 gate = pk["gate"]
             if write_cache:
                 self._write_prefill_cache(i, qkv, B, T)
@@ -274,6 +282,20 @@ class DecoderEngine:
             saved["step_id"] = self.step_id
             self._saved = saved
         return hidden
+
+    def _project_prefixes(self, packed: Dict[int, Dict[str, Tensor]], name: str) -> Optional[Tensor]:
+        """k / v slots of `attn(adapter_wte)` for every adapter layer, one launch (ger/adapter.py:129-137)."""
+        s = self.spec
+        if -1 not in packed:
+            return None
+        La = s.n_layer - s.adapter_start_layer
+        key = (name, (La, s.adapter_prompt_length, s.qkv_out), torch.bfloat16)
+        fresh = key not in self._bufs
+        pkv_all = self._buf(name, (La, s.adapter_prompt_length, s.qkv_out), torch.bfloat16)
+        if fresh:
+            pkv_all.zero_()          # the q slots are never written nor read
+        ops.prefix_project_fwd(packed[-1]["prefix_all"], self.wkv_all, pkv_all, s.n_query_groups, s.qpk)
+        return pkv_all
 
     def lm_head(self, hidden: Tensor, out: Optional[Tensor] = None) -> Tensor:
         """bf16 logits [M, V] = adapter_scale * (hidden W^T + adapter_bias)  (ger/lora.py:70-71)."""
@@ -318,6 +340,11 @@ class DecoderEngine:
         dqkv = self._buf("dqkv", (M, s.qkv_out), bf)
         ws = self._buf("attn_ws", (ops.attention_bwd_workspace(B, T, G, qpk),), torch.uint8)
         scaling = (s.alpha / s.r) if s.r > 0 else 0.0
+        d_pkv_all = d_gate_all = None
+        if s.variant == "adapter":
+            La = s.n_layer - s.adapter_start_layer
+            d_pkv_all = torch.zeros((La, s.adapter_prompt_length, s.qkv_out), device=self.device, dtype=f32)
+            d_gate_all = torch.zeros((La, s.n_head), device=self.device, dtype=f32)
         for i in range(s.n_layer - 1, first - 1, -1):
             lw, a, pk = self.layers[i], sv["layers"][i], packed.get(i, {})
             p = f"transformer.h.{i}.attn."
@@ -342,17 +369,11 @@ class DecoderEngine:
             need_dqkv = not (s.variant == "adapter" and i == first)
             d_pkv = d_gate = None
             if a["prefix_kv"] is not None:
-                d_pkv = torch.zeros((s.adapter_prompt_length, s.qkv_out), device=self.device, dtype=f32)
-                d_gate = torch.zeros((s.n_head,), device=self.device, dtype=f32)
+                d_pkv, d_gate = d_pkv_all[i - s.adapter_start_layer], d_gate_all[i - s.adapter_start_layer]
             ops.attention_bwd(a["qkv"], a["y"], dy, a["lse"], dqkv if need_dqkv else None, ws, B, T, G, qpk, a["prefix_kv"], a["gate"],
                               d_pkv, d_gate, s.adapter_prompt_length if a["prefix_kv"] is not None else 0, need_dqkv,
                               rope_cos=self.cos, rope_sin=self.sin)
             if d_pkv is not None:
-                d_pkv_b = self._buf("d_pkv_b", (s.adapter_prompt_length, s.qkv_out), bf)
-                ops.cast_f32_to_bf16(d_pkv, d_pkv_b)
-                d_wte = torch.empty((s.adapter_prompt_length, C), device=self.device, dtype=f32)
-                ops.gemm(d_pkv_b, lw["wqkv"], d_wte, b_layout=1, epilogue=ops.EPI_F32)
-                grads[p + "adapter_wte.weight"] = d_wte
                 grads[p + "gating_factor"] = d_gate.view(1, 1, s.n_head, 1)
             if not need_dqkv:
                 continue
@@ -373,6 +394,11 @@ class DecoderEngine:
                 ops.gemm(dqkv, lw["wqkv_t"], dn)
             if i > first:
                 ops.rmsnorm_bwd(a["x"], lw["norm1"], a["rstd1"], dn, dx, dx, dxb)
+        if d_pkv_all is not None:      # d(adapter_wte) of all layers in one launch: d(prefix k/v) through the k / v weight rows
+            d_wte_all = torch.empty((d_pkv_all.shape[0], s.adapter_prompt_length, C), device=self.device, dtype=f32)
+            ops.prefix_project_bwd(d_pkv_all, self.wkv_all, d_wte_all, G, qpk)
+            for i in range(s.adapter_start_layer, s.n_layer):
+                grads[f"transformer.h.{i}.attn.adapter_wte.weight"] = d_wte_all[i - s.adapter_start_layer]
         return grads
 
     # ------------------------------------------------------------------------------------------
@@ -421,6 +447,7 @@ class DecoderEngine:
         seq_ids.copy_(torch.arange(n_seq, device=self.device, dtype=torch.int32))
         torch.add(positions, 1, out=lens)
         ops.embedding_fwd(tokens.contiguous(), self.wte, x)
+        pkv_all = self._project_prefixes(packed, "dec_pkv_all")
         for i, lw in enumerate(self.layers):
             pk = packed.get(i, {})
             ops.rmsnorm_fwd(x, lw["norm1"], n, None, s.norm_eps)
@@ -435,8 +462,7 @@ class DecoderEngine:
             ops.kv_cache_write(qkv, self.cache_k[i], self.cache_v[i], seq_ids, positions, G, qpk)
             prefix_kv = gate = None
             if "prefix" in pk:
-                prefix_kv = self._buf(f"dec_pkv{i}", (s.adapter_prompt_length, s.qkv_out), bf)
-                ops.gemm(pk["prefix"], lw["wqkv"], prefix_kv)
+                prefix_kv = pkv_all[i - s.adapter_start_layer]
                 gate = pk["gate"]
             ops.attention_decode(qkv, self.cache_k[i], self.cache_v[i], lens, y, G, qpk, prefix_kv, gate,
                                  s.adapter_prompt_length if prefix_kv is not None else 0)

@@ -307,3 +307,28 @@ def relpred_bwd(x, w1, w2, wc, h1, h2, pooled, d_logits, dw1, db1, dw2, db2, dwc
                                      db2.data_ptr(), dwc.data_ptr(), dbc.data_ptr(), scratch.data_ptr(), B, T, Cd, pool, _stream()),
           "dh_relpred_bwd")
     _count(7)
+
+
+@_profiled("prefix_project_fwd")
+def prefix_project_fwd(prefix: Tensor, wkv: Tensor, prefix_kv: Tensor, n_groups: int, q_per_kv: int) -> None:
+    """prefix bf16 [L, aT, C], wkv bf16 [L, n_groups*128, C] -> k / v slots of prefix_kv bf16 [L, aT, n_groups*(qpk+2)*64]."""
+    _dev(prefix)
+    L, aT, C = prefix.shape
+    assert prefix.is_contiguous() and wkv.is_contiguous() and prefix_kv.is_contiguous()
+    assert wkv.shape == (L, n_groups * 128, C) and prefix_kv.shape == (L, aT, n_groups * (q_per_kv + 2) * 64)
+    assert prefix.dtype == wkv.dtype == prefix_kv.dtype == torch.bfloat16
+    check(_lib.load().dh_prefix_project_fwd(prefix.data_ptr(), wkv.data_ptr(), prefix_kv.data_ptr(), L, aT, C, n_groups, q_per_kv,
+                                            _stream()), "dh_prefix_project_fwd")
+    _count()
+
+
+@_profiled("prefix_project_bwd")
+def prefix_project_bwd(d_prefix_kv: Tensor, wkv: Tensor, d_prefix: Tensor, n_groups: int, q_per_kv: int) -> None:
+    _dev(d_prefix_kv)
+    L, aT, C = d_prefix.shape
+    assert d_prefix_kv.is_contiguous() and wkv.is_contiguous() and d_prefix.is_contiguous()
+    assert d_prefix_kv.dtype == torch.float32 and d_prefix.dtype == torch.float32 and wkv.dtype == torch.bfloat16
+    assert d_prefix_kv.shape == (L, aT, n_groups * (q_per_kv + 2) * 64) and wkv.shape == (L, n_groups * 128, C)
+    check(_lib.load().dh_prefix_project_bwd(d_prefix_kv.data_ptr(), wkv.data_ptr(), d_prefix.data_ptr(), L, aT, C, n_groups, q_per_kv,
+                                            _stream()), "dh_prefix_project_bwd")
+    _count()

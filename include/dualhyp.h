@@ -124,6 +124,14 @@ int dh_attention_bwd(const void* qkv, const void* out, const void* dout, const f
                      const float* gate, void* dqkv, float* d_prefix_kv, float* d_gate, int need_dqkv,
                      const void* rope_cos, const void* rope_sin, int B, int T, int n_groups, int q_per_kv, int prefix_len,
                      void* workspace, size_t workspace_bytes, void* stream);
+/* Adapter prefix K/V for ALL adapter layers in one launch (ger/adapter.py:129-137, `self.attn(prefix)` of which only the k
+ * and v slots are used).  prefix bf16 [L, aT, C]; wkv bf16 [L, n_groups*128, C] = the k rows (64) then the v rows (64) of
+ * every group of each layer's QKV weight; prefix_kv bf16 [L, aT, n_groups*(qpk+2)*64]: only the k and v slots are written.
+ * The backward takes d(prefix_kv) f32 in that same layout (what dh_attention_bwd accumulates) -> d_prefix f32 [L, aT, C]. */
+int dh_prefix_project_fwd(const void* prefix, const void* wkv, void* prefix_kv, int L, int aT, int C, int n_groups, int q_per_kv,
+                          void* stream);
+int dh_prefix_project_bwd(const float* d_prefix_kv, const void* wkv, float* d_prefix, int L, int aT, int C, int n_groups,
+                          int q_per_kv, void* stream);
 /* Single-query attention over a KV cache (ger/model.py:248-261 decode step).  q bf16 [nseq, n_head*64] taken from
  * the q slots of qkv rows; cache_k/v bf16 [nseq, n_groups, max_len, 64]; lens int32 [nseq] = number of valid keys
  * INCLUDING the token being decoded.  out bf16 [nseq, n_head*64]. */

@@ -447,3 +447,27 @@ def test_relpred_fwd_bwd():
     torch.cuda.synchronize()
     for n, g in zip(names, grads):
         assert rel(g.cpu(), work[p + n].grad) < 1e-4, report("relpred " + n, g.cpu(), work[p + n].grad)
+
+
+def test_prefix_project_fwd_bwd():
+    """Batched adapter prefix K/V projection (ger/adapter.py:129-137) and its backward, all layers in one launch."""
+    L, aT, C, G, qpk = 3, 10, 512, 2, 4
+    N = G * (qpk + 2) * 64
+    prefix = rnd((L, aT, C), 90, 1.0)
+    w = rnd((L, N, C), 91, 0.05)
+    rows = torch.cat([torch.arange((g * (qpk + 2) + qpk) * 64, (g * (qpk + 2) + qpk + 2) * 64) for g in range(G)]).to(DEV)
+    wkv = w.index_select(1, rows).contiguous()
+    out = torch.zeros((L, aT, N), device=DEV, dtype=torch.bfloat16)
+    ops.prefix_project_fwd(prefix, wkv, out, G, qpk)
+    ref = torch.einsum("lac,lnc->lan", prefix.float(), w.float())
+    got = out.float().index_select(2, rows)
+    assert rel(got, ref.index_select(2, rows)) < 1e-2, report("prefix fwd", got, ref.index_select(2, rows))
+    qcols = torch.ones(N, dtype=torch.bool, device=DEV)
+    qcols[rows] = False
+    assert float(out[:, :, qcols].abs().max()) == 0.0          # q slots untouched
+    d_pkv = torch.zeros((L, aT, N), device=DEV)
+    d_pkv[:, :, rows] = rnd((L, aT, rows.numel()), 92, 1.0, torch.float32)
+    d_prefix = torch.empty((L, aT, C), device=DEV)
+    ops.prefix_project_bwd(d_pkv, wkv, d_prefix, G, qpk)
+    refb = torch.einsum("lan,lnc->lac", d_pkv, w.float())
+    assert rel(d_prefix, refb) < 1e-3, report("prefix bwd", d_prefix, refb)
