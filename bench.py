@@ -258,7 +258,10 @@ def run_native(args):
             "e2e": {"value": round(e2e_value, 1), "unit": UNIT, "h2d_bytes_per_step": 2 * B * T * 8, "d2h_bytes_per_step": 4,
                     "ms_per_step": round(ms_e2e / args.steps, 3)},
             "gpu_launches": n_launch, "clocks": clocks}
-    step_fl = flops.step_flops(model.config, args.workload, B, T, training=True)
+    # the vocabulary projection only runs on rows with a target (valid-row compaction): credit only those flops
+    rho = float((labels_h[..., 1:] != -1).sum()) / float(B * T)
+    line["config"]["lm_head_row_fraction"] = round(rho, 4)
+    step_fl = flops.step_flops(model.config, args.workload, B, T, training=True, rho=rho)
     line["step_tflops_per_gpu"] = round(step_fl / (ms_total / args.steps / 1e3) / 1e12, 1)
 
     # ---- roofline of the dominant kernel: per-launch CUDA events in a dedicated instrumented pass ----

@@ -38,6 +38,7 @@ class GemmArgs(C.Structure):
         ("col_scale", C.c_void_p), ("col_bias", C.c_void_p),
         ("rope_cos", C.c_void_p), ("rope_sin", C.c_void_p),
         ("positions", C.c_void_p),
+        ("m_limit", C.c_void_p),
     ]
 
 
@@ -63,6 +64,9 @@ SIGNATURES = {
     "dh_prefix_project_bwd": (_I, [_P, _P, _P, _I, _I, _I, _I, _I, _P]),
     "dh_kv_cache_write": (_I, [_P, _P, _P, _P, _P, _I, _I, _I, _I, _P]),
     "dh_cross_entropy": (_I, [_P, _L, _P, _P, _I, _I, _F, _I, _P]),
+    "dh_compact_targets": (_I, [_P, _I, _P, _P, _P, _P]),
+    "dh_gather_rows": (_I, [_P, _P, _P, _P, _I, _I, _P]),
+    "dh_scatter_rows": (_I, [_P, _P, _P, _P, _I, _I, _P]),
     "dh_loss_reduce": (_I, [_P, _P, _P, _I, _P]),
     "dh_argmax": (_I, [_P, _L, _P, _I, _I, _P]),
     "dh_relpred_fwd": (_I, [_P] * 11 + [_I, _I, _I, _I, _P]),

@@ -32,6 +32,7 @@ struct GemmParams {
   const bf16* rope_cos;
   const bf16* rope_sin;
   const int* positions;
+  const int* m_limit;      // optional device-side row count: tiles at or beyond it are skipped
 };
 
 template <int BN> struct GemmCfg {
@@ -197,7 +198,9 @@ gemm_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant__ CUt
 
   const int warp = __shfl_sync(0xffffffffu, threadIdx.x >> 5, 0);   // shfl: a warp-uniform value for the compiler
   const int lane = threadIdx.x & 31;
-  const int num_tiles = p.tiles_m * p.tiles_n;
+  int tiles_m = p.tiles_m;
+  if (p.m_limit) { const int t = (__ldg(p.m_limit) + BM - 1) / BM; tiles_m = t < tiles_m ? t : tiles_m; }
+  const int num_tiles = tiles_m * p.tiles_n;
   const int nkb1 = (p.K1 + BK - 1) / BK;   // a ragged K tail is zero-filled by TMA
   const int nkb = nkb1 + (p.K2 + BK - 1) / BK;
 
@@ -224,8 +227,8 @@ gemm_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant__ CUt
     // ===================== TMA producer =====================
     uint32_t it = 0;
     for (int tile = blockIdx.x; tile < num_tiles; tile += gridDim.x) {
-      const int m0 = (tile % p.tiles_m) * BM;
-      const int n0 = (tile / p.tiles_m) * BN;
+      const int m0 = (tile % tiles_m) * BM;
+      const int n0 = (tile / tiles_m) * BN;
       for (int kb = 0; kb < nkb; ++kb, ++it) {
         const int s = it % STAGES;
         mbar_wait(&empty_bar[s], ((it / STAGES) & 1) ^ 1);
@@ -289,8 +292,8 @@ gemm_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant__ CUt
     uint32_t tcount = 0;
     for (int tile = blockIdx.x; tile < num_tiles; tile += gridDim.x, ++tcount) {
       const int acc = tcount & 1;
-      const int m0 = (tile % p.tiles_m) * BM;
-      const int n0 = (tile / p.tiles_m) * BN;
+      const int m0 = (tile % tiles_m) * BM;
+      const int n0 = (tile / tiles_m) * BN;
       mbar_wait(&tfull_bar[acc], (tcount >> 1) & 1);
       tc_fence_after();
       const int row = m0 + q * 32 + lane;
@@ -575,7 +578,9 @@ gemm_pair_kernel(const __grid_constant__ PairMaps tm, const GemmParams p) {
   const uint32_t rank = cluster_ctarank();
   const int pair = blockIdx.x >> 1;
   const int npairs = gridDim.x >> 1;
-  const int num_tiles = p.tiles_m * p.tiles_n;
+  int tiles_m = p.tiles_m;
+  if (p.m_limit) { const int t = (__ldg(p.m_limit) + 255) / 256; tiles_m = t < tiles_m ? t : tiles_m; }
+  const int num_tiles = tiles_m * p.tiles_n;
   const int nkb1 = (p.K1 + BK - 1) / BK;
   const int nkb = nkb1 + (p.K2 + BK - 1) / BK;
 
@@ -608,8 +613,8 @@ gemm_pair_kernel(const __grid_constant__ PairMaps tm, const GemmParams p) {
     // ===================== TMA producer (each CTA loads its own halves) =====================
     uint32_t it = 0;
     for (int tile = pair; tile < num_tiles; tile += npairs) {
-      const int m0 = (tile % p.tiles_m) * 256 + (int)rank * 128;
-      const int n0 = (tile / p.tiles_m) * BN + (int)rank * 128;
+      const int m0 = (tile % tiles_m) * 256 + (int)rank * 128;
+      const int n0 = (tile / tiles_m) * BN + (int)rank * 128;
       for (int kb = 0; kb < nkb; ++kb, ++it) {
         const int s = it % STAGES;
         mbar_wait(&empty_bar[s], ((it / STAGES) & 1) ^ 1);
@@ -660,8 +665,8 @@ gemm_pair_kernel(const __grid_constant__ PairMaps tm, const GemmParams p) {
     const int my_tiles = pair < num_tiles ? (num_tiles - pair + npairs - 1) / npairs : 0;
     const int n_units = my_tiles * UPW;
     // unit u of this warp = column slice 2 * (u % UPW) + half of this pair's (u / UPW)-th tile
-    auto unit_row0 = [&](int u) { return ((pair + (u / UPW) * npairs) % p.tiles_m) * 256 + (int)rank * 128 + q * 32; };
-    auto unit_col0 = [&](int u) { return ((pair + (u / UPW) * npairs) / p.tiles_m) * BN + (2 * (u % UPW) + half) * UC; };
+    auto unit_row0 = [&](int u) { return ((pair + (u / UPW) * npairs) % tiles_m) * 256 + (int)rank * 128 + q * 32; };
+    auto unit_col0 = [&](int u) { return ((pair + (u / UPW) * npairs) / tiles_m) * BN + (2 * (u % UPW) + half) * UC; };
     if (loads && lane == 0 && n_units > 0) epi_issue_load<EPI>(&tm.aux, ebuf, &lbar[0], unit_row0(0), unit_col0(0));
     RopeRegs rope;
     for (int u = 0; u < n_units; ++u) {
@@ -761,6 +766,7 @@ static GemmParams make_params(const dh_gemm_args* a) {
   p.rope_cos = reinterpret_cast<const bf16*>(a->rope_cos);
   p.rope_sin = reinterpret_cast<const bf16*>(a->rope_sin);
   p.positions = a->positions;
+  p.m_limit = a->m_limit;
   return p;
 }
 

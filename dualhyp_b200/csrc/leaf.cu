@@ -194,7 +194,7 @@ __global__ void __launch_bounds__(256) cross_entropy_kernel(bf16* logits, long l
   const int nv = V / 8;
   if (tg < 0) {   // ignore_index = -1: no loss, zero gradient
     if (threadIdx.x == 0) row_loss[row] = 0.f;
-    if (write_grad) {
+    if (write_grad == 1) {
       const uint4 z = make_uint4(0, 0, 0, 0);
       for (int i = threadIdx.x; i < nv; i += blockDim.x) reinterpret_cast<uint4*>(lrow)[i] = z;
     }
@@ -408,6 +408,68 @@ __global__ void __launch_bounds__(128) prefix_project_bwd_kernel(const float* __
     if (a < aT) *reinterpret_cast<float2*>(dprefix + ((long long)l * aT + a) * C + c) = make_float2(a0[a], a1[a]);
 }
 
+// -------------------------------------------------------------------------------------------------
+// Valid-row compaction for the fused lm_head + loss: only rows whose target is not -1 contribute to the loss or to
+// d(hidden), so only those are sent through the vocabulary projection.  One block: ordered compaction of the row
+// indices (rows[i] = original row of the i-th valid target, -1 beyond the count), the gathered targets and the count.
+// -------------------------------------------------------------------------------------------------
+__global__ void __launch_bounds__(1024) compact_targets_kernel(const long long* __restrict__ targets, int M, int* __restrict__ count,
+                                                              int* __restrict__ rows, long long* __restrict__ tg_c) {
+  __shared__ int warp_tot[32];
+  __shared__ int base;
+  const int lane = threadIdx.x & 31, warp = threadIdx.x >> 5;
+  if (threadIdx.x == 0) base = 0;
+  __syncthreads();
+  for (int m0 = 0; m0 < M; m0 += 1024) {
+    const int m = m0 + threadIdx.x;
+    const long long tg = m < M ? targets[m] : -1;
+    const bool ok = tg >= 0;
+    const unsigned bal = __ballot_sync(0xffffffffu, ok);
+    if (lane == 0) warp_tot[warp] = __popc(bal);
+    __syncthreads();
+    int off = base;
+    for (int w = 0; w < warp; ++w) off += warp_tot[w];
+    if (ok) {
+      const int pos = off + __popc(bal & ((1u << lane) - 1));
+      rows[pos] = m;
+      tg_c[pos] = tg;
+    }
+    __syncthreads();
+    if (threadIdx.x == 0) { int t = 0; for (int w = 0; w < 32; ++w) t += warp_tot[w]; base += t; }
+    __syncthreads();
+  }
+  const int n = base;
+  if (threadIdx.x == 0) *count = n;
+  for (int i = n + threadIdx.x; i < M; i += 1024) { rows[i] = -1; tg_c[i] = -1; }
+}
+
+// dst[i, :] = src[rows[i], :] for i < *count  (bf16 rows of C elements, C % 8 == 0)
+__global__ void __launch_bounds__(256) gather_rows_kernel(const bf16* __restrict__ src, const int* __restrict__ rows,
+                                                          const int* __restrict__ count, bf16* __restrict__ dst, int C) {
+  const int n = *count;
+  for (int i = blockIdx.x; i < n; i += gridDim.x) {
+    const uint4* s4 = reinterpret_cast<const uint4*>(src + (long long)rows[i] * C);
+    uint4* d4 = reinterpret_cast<uint4*>(dst + (long long)i * C);
+    for (int c = threadIdx.x; c < C / 8; c += blockDim.x) d4[c] = s4[c];
+  }
+}
+
+// dst [M, C] = 0, then dst[rows[i], :] = src[i, :] for i < *count.  Block = one destination row; the inverse map is
+// found by binary search in the (ascending) rows list.
+__global__ void __launch_bounds__(256) scatter_rows_kernel(const bf16* __restrict__ src, const int* __restrict__ rows,
+                                                           const int* __restrict__ count, bf16* __restrict__ dst, int M, int C) {
+  const int n = *count;
+  for (int m = blockIdx.x; m < M; m += gridDim.x) {
+    int lo = 0, hi = n;
+    while (lo < hi) { const int mid = (lo + hi) >> 1; if (rows[mid] < m) lo = mid + 1; else hi = mid; }
+    const bool hit = lo < n && rows[lo] == m;
+    uint4* d4 = reinterpret_cast<uint4*>(dst + (long long)m * C);
+    const uint4* s4 = reinterpret_cast<const uint4*>(src + (long long)lo * C);
+    const uint4 z = make_uint4(0, 0, 0, 0);
+    for (int c = threadIdx.x; c < C / 8; c += blockDim.x) d4[c] = hit ? s4[c] : z;
+  }
+}
+
 }  // namespace dh
 
 using namespace dh;
@@ -561,6 +623,27 @@ extern "C" int dh_prefix_project_bwd(const float* d_prefix_kv, const void* wkv, 
   const long long ld = (long long)n_groups * (q_per_kv + 2) * 64;
   prefix_project_bwd_kernel<<<dim3(C / 256, L), 128, smem, (cudaStream_t)stream>>>(d_prefix_kv, (const bf16*)wkv, d_prefix, aT, C, R,
                                                                                    n_groups, q_per_kv, ld);
+  DH_CUDA(cudaGetLastError());
+  return 0;
+}
+
+extern "C" int dh_compact_targets(const int64_t* targets, int M, int32_t* count, int32_t* rows, int64_t* targets_c, void* stream) {
+  DH_CHECK(targets && count && rows && targets_c && M > 0, "dh_compact_targets: bad argument");
+  compact_targets_kernel<<<1, 1024, 0, (cudaStream_t)stream>>>((const long long*)targets, M, count, rows, (long long*)targets_c);
+  DH_CUDA(cudaGetLastError());
+  return 0;
+}
+
+extern "C" int dh_gather_rows(const void* src, const int32_t* rows, const int32_t* count, void* dst, int M, int C, void* stream) {
+  DH_CHECK(src && rows && count && dst && M > 0 && C > 0 && C % 8 == 0, "dh_gather_rows: bad argument");
+  gather_rows_kernel<<<M < 1184 ? M : 1184, 256, 0, (cudaStream_t)stream>>>((const bf16*)src, rows, count, (bf16*)dst, C);
+  DH_CUDA(cudaGetLastError());
+  return 0;
+}
+
+extern "C" int dh_scatter_rows(const void* src, const int32_t* rows, const int32_t* count, void* dst, int M, int C, void* stream) {
+  DH_CHECK(src && rows && count && dst && M > 0 && C > 0 && C % 8 == 0, "dh_scatter_rows: bad argument");
+  scatter_rows_kernel<<<M < 2368 ? M : 2368, 256, 0, (cudaStream_t)stream>>>((const bf16*)src, rows, count, (bf16*)dst, M, C);
   DH_CUDA(cudaGetLastError());
   return 0;
 }

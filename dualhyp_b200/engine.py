@@ -297,23 +297,24 @@ class DecoderEngine:
         ops.prefix_project_fwd(packed[-1]["prefix_all"], self.wkv_all, pkv_all, s.n_query_groups, s.qpk)
         return pkv_all
 
-    def lm_head(self, hidden: Tensor, out: Optional[Tensor] = None) -> Tensor:
-        """bf16 logits [M, V] = adapter_scale * (hidden W^T + adapter_bias)  (ger/lora.py:70-71)."""
+    def lm_head(self, hidden: Tensor, out: Optional[Tensor] = None, m_limit: Optional[Tensor] = None) -> Tensor:
+        """bf16 logits [M, V] = adapter_scale * (hidden W^T + adapter_bias)  (ger/lora.py:70-71).  m_limit (device int32):
+        only the first *m_limit rows are needed (valid-row compaction of the fused loss)."""
         M = hidden.shape[0]
         logits = out if out is not None else self._buf("logits", (M, self.spec.vocab), torch.bfloat16)
-        ops.gemm(hidden, self.lm_w, logits, col_scale=self.lm_scale, col_bias=self.lm_bias)
+        ops.gemm(hidden, self.lm_w, logits, col_scale=self.lm_scale, col_bias=self.lm_bias, m_limit=m_limit)
         return logits
 
     # ------------------------------------------------------------------------------------------
     # backward: d(hidden) -> gradients of the trainable tensors (reference-keyed, fp32)
     # ------------------------------------------------------------------------------------------
-    def lm_head_backward(self, dlogits: Tensor) -> Tensor:
+    def lm_head_backward(self, dlogits: Tensor, m_limit: Optional[Tensor] = None, name: str = "d_hidden") -> Tensor:
         """d(hidden) bf16 [M, C] = dlogits [M, V] @ W [V, C]   (W^T [C, V] is the K-major B operand)."""
         M = dlogits.shape[0]
-        d_hidden = self._buf("d_hidden", (M, self.spec.n_embd), torch.bfloat16)
+        d_hidden = self._buf(name, (M, self.spec.n_embd), torch.bfloat16)
         if self.lm_scale is not None:
             raise NotImplementedError("training through a non-trivial adapter_scale is not supported (it is frozen at 1)")
-        ops.gemm(dlogits, self.lm_w_t, d_hidden)
+        ops.gemm(dlogits, self.lm_w_t, d_hidden, m_limit=m_limit)
         return d_hidden
 
     def backward(self, d_hidden: Tensor, step_id: Optional[int] = None) -> Dict[str, Tensor]:

@@ -84,24 +84,37 @@ class _LMHeadCEFn(torch.autograd.Function):
     def forward(ctx, model: "GPT", hidden: Tensor, targets: Tensor, denom: float):
         eng = model._engine_ready()
         h2 = hidden.reshape(-1, hidden.shape[-1]).to(torch.bfloat16).contiguous()
-        M = h2.shape[0]
+        M, C = h2.shape
         need_grad = bool(ctx.needs_input_grad[1])
-        logits = eng.lm_head(h2)
+        tg = targets.reshape(-1).contiguous()
+        # Only rows with a target != -1 carry loss or gradient (the response span: a few percent of the prompt), so only
+        # they go through the vocabulary projection: ordered compaction on the device, GEMMs bounded by the device-side
+        # count -- the host never learns it, there is no sync.
+        count = eng._buf("ce_count", (1,), torch.int32)
+        rows = eng._buf("ce_row_idx", (M,), torch.int32)
+        tg_c = eng._buf("ce_targets_c", (M,), torch.int64)
+        h_c = eng._buf("ce_hidden_c", (M, C), torch.bfloat16)
+        ops.compact_targets(tg, count, rows, tg_c)
+        ops.gather_rows(h2, rows, count, h_c)
+        logits = eng.lm_head(h_c, m_limit=count)
         row = eng._buf("ce_rows", (M,), torch.float32)
         out2 = torch.empty(2, device=h2.device, dtype=torch.float32)
-        tg = targets.reshape(-1).contiguous()
-        ops.cross_entropy(logits, tg, row, (1.0 / denom) if denom > 0 else 1.0, need_grad)
-        ops.loss_reduce(row, tg, out2)
+        ops.cross_entropy(logits, tg_c, row, (1.0 / denom) if denom > 0 else 1.0, 2 if need_grad else 0)
+        ops.loss_reduce(row, tg_c, out2)
         ctx.model, ctx.shape, ctx.denom = model, hidden.shape, denom
         ctx.save_for_backward(out2)
         ctx.logits = logits if need_grad else None
+        ctx.compact = (rows, count)
         return out2[0] / denom if denom > 0 else out2[0] / out2[1]
 
     @staticmethod
     def backward(ctx, d_loss: Tensor):
         model = ctx.model
         eng = model._engine
-        d_hidden = eng.lm_head_backward(ctx.logits)
+        rows, count = ctx.compact
+        d_hidden_c = eng.lm_head_backward(ctx.logits, m_limit=count, name="d_hidden_c")
+        d_hidden = eng._buf("d_hidden", tuple(d_hidden_c.shape), torch.bfloat16)
+        ops.scatter_rows(d_hidden_c, rows, count, d_hidden)
         (out2,) = ctx.saved_tensors
         scale = d_loss.float() if ctx.denom > 0 else d_loss.float() / out2[1]
         # the scalar is applied to the (small) final gradients by _DecoderFn.backward, in fp32

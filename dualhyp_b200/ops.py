@@ -57,6 +57,8 @@ def _gemm_meta(A, B, out, *, epilogue=EPI_BF16, b_layout=0, a_layout=0, A2=None,
     M, K = (A.shape if a_layout == 0 else (A.shape[1], A.shape[0]))
     N = B.shape[0] if b_layout == 0 else B.shape[1]
     K2 = 0 if A2 is None else (A2.shape[1] if kw.get("a2_layout", 0) == 0 else A2.shape[0])
+    if kw.get("m_limit") is not None:
+        M = 0          # row count only known on the device: no flops are credited to bounded GEMMs in the profile
     return (int(M), int(N), int(K), int(K2), int(epilogue), int(a_layout), int(b_layout))
 
 
@@ -91,7 +93,8 @@ def gemm(A: Tensor, B: Tensor, out: Optional[Tensor], *, epilogue: int = EPI_BF1
          A2: Optional[Tensor] = None, B2: Optional[Tensor] = None, a2_layout: int = 0, b2_layout: int = 0,
          out2: Optional[Tensor] = None, aux: Optional[Tensor] = None, alpha: float = 1.0, accumulate: bool = False,
          col_scale: Optional[Tensor] = None, col_bias: Optional[Tensor] = None, rope_cos: Optional[Tensor] = None,
-         rope_sin: Optional[Tensor] = None, positions: Optional[Tensor] = None, seq_len: int = 0, q_per_kv: int = 0) -> None:
+         rope_sin: Optional[Tensor] = None, positions: Optional[Tensor] = None, seq_len: int = 0, q_per_kv: int = 0,
+         m_limit: Optional[Tensor] = None) -> None:
     """D = A op(B) (+ A2 op(B2)) with a fused epilogue; see `dh_gemm` in include/dualhyp.h."""
     _dev(A)
     assert A.dtype == torch.bfloat16 and B.dtype == torch.bfloat16
@@ -125,6 +128,7 @@ def gemm(A: Tensor, B: Tensor, out: Optional[Tensor], *, epilogue: int = EPI_BF1
         a.aux, a.ldaux = aux.data_ptr(), _rowmajor(aux, "aux")
     a.col_scale, a.col_bias = _ptr(col_scale), _ptr(col_bias)
     a.rope_cos, a.rope_sin, a.positions = _ptr(rope_cos), _ptr(rope_sin), _ptr(positions)
+    a.m_limit = _ptr(m_limit)
     check(_lib.load().dh_gemm(C.byref(a), _stream()), "dh_gemm")
     _count()
 
@@ -331,4 +335,34 @@ def prefix_project_bwd(d_prefix_kv: Tensor, wkv: Tensor, d_prefix: Tensor, n_gro
     assert d_prefix_kv.shape == (L, aT, n_groups * (q_per_kv + 2) * 64) and wkv.shape == (L, n_groups * 128, C)
     check(_lib.load().dh_prefix_project_bwd(d_prefix_kv.data_ptr(), wkv.data_ptr(), d_prefix.data_ptr(), L, aT, C, n_groups, q_per_kv,
                                             _stream()), "dh_prefix_project_bwd")
+    _count()
+
+
+@_profiled("compact_targets")
+def compact_targets(targets: Tensor, count: Tensor, rows: Tensor, targets_c: Tensor) -> None:
+    """targets int64 [M] (-1 = ignore) -> count int32 [1], rows int32 [M] (ascending valid rows, -1 beyond), targets_c int64 [M]."""
+    _dev(targets)
+    M = targets.numel()
+    assert targets.dtype == torch.int64 and targets_c.dtype == torch.int64 and rows.dtype == torch.int32 and count.dtype == torch.int32
+    assert targets.is_contiguous() and rows.numel() == M and targets_c.numel() == M
+    check(_lib.load().dh_compact_targets(targets.data_ptr(), M, count.data_ptr(), rows.data_ptr(), targets_c.data_ptr(), _stream()),
+          "dh_compact_targets")
+    _count()
+
+
+@_profiled("gather_rows")
+def gather_rows(src: Tensor, rows: Tensor, count: Tensor, dst: Tensor) -> None:
+    _dev(src)
+    assert src.dtype == torch.bfloat16 and dst.dtype == torch.bfloat16 and src.is_contiguous() and dst.is_contiguous()
+    check(_lib.load().dh_gather_rows(src.data_ptr(), rows.data_ptr(), count.data_ptr(), dst.data_ptr(), src.shape[0], src.shape[1],
+                                     _stream()), "dh_gather_rows")
+    _count()
+
+
+@_profiled("scatter_rows")
+def scatter_rows(src: Tensor, rows: Tensor, count: Tensor, dst: Tensor) -> None:
+    _dev(src)
+    assert src.dtype == torch.bfloat16 and dst.dtype == torch.bfloat16 and src.is_contiguous() and dst.is_contiguous()
+    check(_lib.load().dh_scatter_rows(src.data_ptr(), rows.data_ptr(), count.data_ptr(), dst.data_ptr(), dst.shape[0], dst.shape[1],
+                                      _stream()), "dh_scatter_rows")
     _count()

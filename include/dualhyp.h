@@ -22,7 +22,7 @@
 extern "C" {
 #endif
 
-#define DH_ABI_VERSION 1
+#define DH_ABI_VERSION 2
 
 int dh_abi_version(void);
 const char* dh_last_error(void);
@@ -74,6 +74,8 @@ typedef struct dh_gemm_args {
   const void* rope_cos;              /* bf16 [block_size, 64] as built by ger/model.py:319-346 */
   const void* rope_sin;
   const int32_t* positions;          /* optional [M] */
+  const int32_t* m_limit;            /* optional device int: only rows [0, *m_limit) are needed; whole tiles beyond are skipped
+                                        (rows of a partly needed tile are still computed).  ABI v2. */
 } dh_gemm_args;
 
 int dh_gemm(const dh_gemm_args* args, void* stream);
@@ -146,11 +148,20 @@ int dh_kv_cache_write(const void* qkv, void* cache_k, void* cache_v, const int32
  * Loss (ger/utils.py:424-463 over lm_head logits, ger/lora.py:546-549)
  * logits bf16 [M, V] (ld = ldl).  targets int64 [M], -1 = ignore.  Writes per-row loss f32 [M] (0 where ignored)
  * and, when write_grad, overwrites logits IN PLACE with d(loss)/d(logits) * grad_scale
- *   = (softmax - onehot) * grad_scale   for valid rows, 0 for ignored rows.
+ *   = (softmax - onehot) * grad_scale   for valid rows, 0 for ignored rows (write_grad = 2: ignored rows are left untouched).
  * The caller owns the reduction: train = sum(row_loss)/M (quirk Q2), val = sum/valid.
  * ------------------------------------------------------------------------------------------------- */
 int dh_cross_entropy(void* logits, int64_t ldl, const int64_t* targets, float* row_loss, int M, int V,
                      float grad_scale, int write_grad, void* stream);
+/* Valid-row compaction for the fused lm_head + loss (only rows with a target != -1 carry loss or gradient, so only they
+ * are projected onto the vocabulary).  count int32[1] = number of valid targets; rows int32[M]: rows[i] = row of the i-th
+ * valid target (ascending), -1 for i >= count; targets_c int64[M] = the gathered targets, -1 beyond count.
+ * dh_gather_rows: dst[i] = src[rows[i]] for i < *count (bf16 [., C]).  dh_scatter_rows: dst [M, C] = 0 except
+ * dst[rows[i]] = src[i].  With dh_gemm's m_limit = count and dh_cross_entropy's write_grad = 2 nothing beyond the
+ * valid rows (rounded up to one GEMM tile) is computed, without the host ever learning the count. */
+int dh_compact_targets(const int64_t* targets, int M, int32_t* count, int32_t* rows, int64_t* targets_c, void* stream);
+int dh_gather_rows(const void* src, const int32_t* rows, const int32_t* count, void* dst, int M, int C, void* stream);
+int dh_scatter_rows(const void* src, const int32_t* rows, const int32_t* count, void* dst, int M, int C, void* stream);
 /* out[0] = sum(row_loss[0..M)), out[1] = number of targets != -1 */
 int dh_loss_reduce(const float* row_loss, const int64_t* targets, float* out2, int M, void* stream);
 /* argmax over bf16 logits rows (generate/base.py:62-70 with top_k=1): ids int64 [M]; ties -> lowest index */

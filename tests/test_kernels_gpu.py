@@ -471,3 +471,42 @@ def test_prefix_project_fwd_bwd():
     ops.prefix_project_bwd(d_pkv, wkv, d_prefix, G, qpk)
     refb = torch.einsum("lan,lnc->lac", d_pkv, w.float())
     assert rel(d_prefix, refb) < 1e-3, report("prefix bwd", d_prefix, refb)
+
+
+def test_valid_row_compaction_and_bounded_gemm():
+    """dh_compact_targets / dh_gather_rows / dh_scatter_rows and dh_gemm's device-side m_limit (fused loss path)."""
+    M, C, N = 1500, 256, 512
+    g = torch.Generator().manual_seed(5)
+    tg = torch.full((M,), -1, dtype=torch.int64)
+    valid = torch.randperm(M, generator=g)[:300].sort().values
+    tg[valid] = torch.randint(0, N, (300,), generator=g)
+    tg = tg.to(DEV)
+    count = torch.zeros(1, dtype=torch.int32, device=DEV)
+    rows = torch.empty(M, dtype=torch.int32, device=DEV)
+    tg_c = torch.empty(M, dtype=torch.int64, device=DEV)
+    ops.compact_targets(tg, count, rows, tg_c)
+    assert int(count) == 300
+    assert torch.equal(rows[:300].cpu().long(), valid) and bool((rows[300:] == -1).all())
+    assert torch.equal(tg_c[:300], tg[valid.to(DEV)]) and bool((tg_c[300:] == -1).all())
+    h = rnd((M, C), 95, 1.0)
+    h_c = torch.zeros((M, C), device=DEV, dtype=torch.bfloat16)
+    ops.gather_rows(h, rows, count, h_c)
+    assert torch.equal(h_c[:300], h[valid.to(DEV)]) and float(h_c[300:].abs().max()) == 0.0
+    w = rnd((N, C), 96, 0.1)
+    out = torch.full((M, N), 7.0, device=DEV, dtype=torch.bfloat16)
+    ops.gemm(h_c, w, out, m_limit=count)
+    torch.cuda.synchronize()
+    ref = h_c[:300].float() @ w.float().t()
+    assert rel(out[:300], ref) < 1e-2, report("bounded gemm", out[:300], ref)
+    assert bool((out[1280:] == 7.0).all())                 # tiles beyond the limit are never touched
+    back = torch.full((M, C), 3.0, device=DEV, dtype=torch.bfloat16)
+    ops.scatter_rows(h_c, rows, count, back)
+    exp = torch.zeros_like(h)
+    exp[valid.to(DEV)] = h[valid.to(DEV)]
+    assert torch.equal(back, exp)
+    # all targets ignored: count 0, nothing runs, nothing hangs
+    tg0 = torch.full((M,), -1, dtype=torch.int64, device=DEV)
+    ops.compact_targets(tg0, count, rows, tg_c)
+    ops.gemm(h_c, w, out, m_limit=count)
+    torch.cuda.synchronize()
+    assert int(count) == 0
