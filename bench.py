@@ -10,6 +10,9 @@ forward + train-reduction loss + backward (PEFT gradients) + gradient all-reduce
 `value` = tokens/s over all ranks with inputs resident in HBM; `e2e` = the same step through the public
 `ger` API starting from pinned HOST token ids / labels and ending with the loss read back on the host.
 `--workload lora` switches to configs[2] (LoRA r=8; global batch 64 split over the ranks).
+`--workload decode` measures the second half of BASELINE.json's metric (configs[4]): greedy KV-cache generation,
+64 synthetic DualHyp prompts per GPU (the 512-utterance test set sharded 8 ways), 64 new tokens each, in utt/s;
+the default run appends a short sample of it as `"infer"` to the training line.
 """
 from __future__ import annotations
 
@@ -30,6 +33,8 @@ METRIC = "DualHyp train tokens/s (adapter fine-tune step, TinyLlama-1.1B, 5+5 N-
 UNIT = "tokens/s"
 SEQ_LEN = 512
 PER_GPU_BATCH = 16
+DECODE_METRIC = "DualHyp infer utterances/s (greedy KV-cache decode, adapter TinyLlama-1.1B, 5+5 N-best prompts, 64 new tokens)"
+DECODE_UTTS, DECODE_NEW = 64, 64
 LORA = dict(r=8, alpha=16, dropout=0.0, to_query=True, to_key=True, to_value=True, to_projection=True)
 # DRAM bytes per launch of the dominant GEMMs from one `ncu --set full` capture of this command (profiles/r01g_ncu_full_summary.txt);
 # key = (M, N, K, epilogue).  Algorithmic bytes of the SwiGLU GEMM: A 33.6 MB + B 46.1 MB + h12 184.5 MB + act 92.3 MB = 356.5 MB.
@@ -42,15 +47,21 @@ def parse_args():
     ap.add_argument("--steps", type=int, default=10)
     ap.add_argument("--warmup", type=int, default=3)
     ap.add_argument("--impl", default="native", choices=["native", "reference"])
-    ap.add_argument("--workload", default="adapter", choices=["adapter", "lora"])
+    ap.add_argument("--workload", default="adapter", choices=["adapter", "lora", "decode"])
     ap.add_argument("--batch", type=int, default=0, help="prompts per GPU (default 16; lora: 64 / gpus)")
     ap.add_argument("--seq", type=int, default=SEQ_LEN)
     ap.add_argument("--no-cpu-baseline", action="store_true")
     ap.add_argument("--no-roofline", action="store_true")
+    ap.add_argument("--no-infer", action="store_true", help="skip the decode sample appended to the training line")
+    ap.add_argument("--utts", type=int, default=DECODE_UTTS, help="decode workload: utterances per GPU per step")
+    ap.add_argument("--new-tokens", type=int, default=DECODE_NEW)
     return ap.parse_args()
 
 
 def workload_name(args) -> str:
+    if args.workload == "decode":
+        return ("DualHyp greedy generation with KV cache, TinyLlama-1.1B adapter random-init, synthetic prompts U[330,480] tokens, "
+                f"{args.new_tokens} new tokens, bf16, utterances sharded across GPUs")
     if args.workload == "adapter":
         return "DualHyp adapter fine-tune step, TinyLlama-1.1B random-init, 5 ASR + 5 VSR synthetic hyps per prompt, seq 512, bf16"
     return "DualHyp LoRA (r=8) fine-tune step, TinyLlama-1.1B random-init, global batch 64 x seq 512, bf16, data parallel"
@@ -139,9 +150,149 @@ def cpu_step_tokens_per_s(workload: str, seq: int, steps: int, warmup: int):
     return seq * len(times) / total, 1e3 * total / len(times), cores, sample
 
 
+def cpu_decode_utt_per_s(new_tokens: int):
+    """Bounded sample of the reference decode loop (generate/base.py:19-82 as restated by the oracle) for ONE utterance
+    of 405 prompt tokens: a run with 1 new token (prefill + first token) and a run with 5 give the per-token cost;
+    utt time = prefill run + (new_tokens - 1) x per-token cost.  Returns (utt/s, ms per utterance, cores, sample)."""
+    import torch
+    from dualhyp_b200 import synthetic
+    from oracle import oracle as O
+    cores = os.cpu_count() or 1
+    torch.set_num_threads(cores)
+    cfg = O.OracleConfig(variant="adapter")
+    sd = synthetic.synth_state_dict(cfg, "adapter", 1337)
+    prompt = synthetic.synth_prompts(1, 32000, 1337, prompt_range=(405, 405))[0]
+    O.generate_greedy(sd, cfg, prompt[:64], 65)                     # warm the thread pool / allocator
+    t0 = time.perf_counter()
+    O.generate_greedy(sd, cfg, prompt, prompt.numel() + 1)
+    t1 = time.perf_counter()
+    O.generate_greedy(sd, cfg, prompt, prompt.numel() + 5)
+    t2 = time.perf_counter()
+    per_tok = max(((t2 - t1) - (t1 - t0)) / 4.0, 0.0)
+    utt = (t1 - t0) + (new_tokens - 1) * per_tok
+    sample = (f"oracle (CPU restatement of generate/base.py + ger.adapter) fp32, 1 utterance, 405-token prompt: prefill+1 token "
+              f"{t1 - t0:.2f} s, {per_tok * 1e3:.0f} ms per further token (4 timed), extrapolated to {new_tokens} new tokens")
+    return 1.0 / utt, 1e3 * utt, cores, sample
+
+
+def decode_measure(model, dev, world: int, rank: int, utts: int, new_tokens: int, steps: int, warmup: int, timed_fn):
+    """utt/s of generate_batch over `utts` prompts per GPU: HBM-resident prompts (`value`) and host prompts -> host ids
+    (`e2e`); per-token graph replays timed separately for the HBM roofline of the decode step."""
+    import torch
+    from dualhyp_b200 import ops, synthetic
+    from dualhyp_b200.generate import generate_batch
+    prompts_h = synthetic.synth_prompts(utts, 32000, 4242 + rank)
+    prompts_d = [p.to(dev) for p in prompts_h]
+    for _ in range(max(warmup, 3)):
+        generate_batch(model, prompts_d, new_tokens, return_device=True)
+    l0 = ops.launches()
+    ms_dev = timed_fn(lambda: generate_batch(model, prompts_d, new_tokens, return_device=True), steps)
+    launches_eager_equiv = ops.launches() - l0
+    ms_e2e = timed_fn(lambda: generate_batch(model, prompts_h, new_tokens), steps)
+    # the token loop alone (graph replays): the HBM-bound part
+    eng = model._engine
+    loop = eng._bufs["decode_loops"][utts]
+    lens = torch.tensor([p.numel() for p in prompts_h], dtype=torch.int32, device=dev)
+    e0, e1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+    with torch.inference_mode():
+        loop.pos.copy_(lens)
+        loop.step.zero_()
+        torch.cuda.synchronize()
+        e0.record()
+        for _ in range(new_tokens):
+            loop.graph.replay()
+        e1.record()
+        torch.cuda.synchronize()
+    tok_ms = e0.elapsed_time(e1) / new_tokens
+    s = eng.spec
+    w_bytes = 2.0 * (s.n_layer * (s.qkv_out * s.n_embd + s.n_embd * s.n_embd + 3 * s.n_embd * s.intermediate_size) + s.vocab * s.n_embd)
+    kv_bytes = 2.0 * s.n_layer * 2 * s.n_query_groups * 64 * float(lens.sum() + utts * new_tokens / 2)
+    return dict(ms_dev=ms_dev, ms_e2e=ms_e2e, tok_ms=tok_ms, step_bytes=w_bytes + kv_bytes, launches=launches_eager_equiv,
+                h2d=int(sum(p.numel() for p in prompts_h) * 8), d2h=utts * new_tokens * 8,
+                prompt_tokens=int(lens.sum()), kernels_per_token=loop.kernels_per_token)
+
+
+def run_decode(args):
+    import torch
+    import torch.distributed as dist
+    world = int(os.environ.get("WORLD_SIZE", "1"))
+    rank = int(os.environ.get("RANK", "0"))
+    local = int(os.environ.get("LOCAL_RANK", "0"))
+    torch.cuda.set_device(local)
+    dev = torch.device("cuda", local)
+    if world > 1:
+        dist.init_process_group("nccl", device_id=dev)
+    model = build_model("adapter", dev)
+
+    def barrier():
+        if world > 1:
+            dist.barrier()
+        torch.cuda.synchronize()
+
+    def timed(fn, k):
+        barrier()
+        e0, e1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+        e0.record()
+        for _ in range(k):
+            fn()
+        e1.record()
+        barrier()
+        ms = torch.tensor([e0.elapsed_time(e1)], device=dev)
+        if world > 1:
+            dist.all_reduce(ms, op=dist.ReduceOp.MAX)
+        return float(ms)
+
+    sampler = ClockSampler(local) if rank == 0 else None
+    r = decode_measure(model, dev, world, rank, args.utts, args.new_tokens, args.steps, args.warmup, timed)
+    clocks = sampler.stop() if sampler else None
+    utts = world * args.utts * args.steps
+    line = decode_line(args, r, world, utts, clocks)
+    if rank == 0 and world == 1 and not args.no_cpu_baseline:
+        ups, ms, cores, sample = cpu_decode_utt_per_s(args.new_tokens)
+        line["cpu_baseline"] = {"value": round(ups, 5), "unit": "utt/s", "cores": cores, "kind": "port", "sample": sample}
+    if rank == 0:
+        print(json.dumps(line), flush=True)
+    if world > 1:
+        dist.destroy_process_group()
+
+
+def decode_line(args, r, world, utts, clocks):
+    peaks = {}
+    try:
+        peaks = json.load(open(os.path.join(ROOT, "MEASURED_PEAKS.json")))
+    except Exception:  # noqa: BLE001
+        pass
+    peak = float(peaks.get("hbm_gbs", 6500.0))
+    ach = r["step_bytes"] / (r["tok_ms"] / 1e3) / 1e9
+    return {"metric": DECODE_METRIC, "value": round(utts / (r["ms_dev"] / 1e3), 2), "unit": "utt/s", "n_gpus": world, "steps": args.steps,
+            "warmup": max(args.warmup, 3), "ms_per_step": round(r["ms_dev"] / args.steps, 3), "higher_is_better": True, "scaling": "weak",
+            "vs_baseline": None, "dtype": "bf16", "data": "synthetic",
+            "config": {"workload": workload_name(args), "model": "TinyLlama-1.1B (random init)", "utterances_per_gpu": args.utts,
+                       "new_tokens": args.new_tokens, "prompt_tokens_per_gpu": r["prompt_tokens"], "parallelism": f"dp{world} (utterance sharding, no collective)",
+                       "l2": "each token step streams 2.2 GB of weights >> 126 MB L2; no explicit flush", "eos": "disabled for timing (fixed token count)"},
+            "e2e": {"value": round(utts / (r["ms_e2e"] / 1e3), 2), "unit": "utt/s", "h2d_bytes_per_step": r["h2d"], "d2h_bytes_per_step": r["d2h"],
+                    "ms_per_step": round(r["ms_e2e"] / args.steps, 3)},
+            "gpu_launches": r["launches"], "clocks": clocks,
+            "roofline": {"bound": "hbm", "achieved": round(ach, 1), "peak": peak, "unit": "GB/s", "frac": round(ach / peak, 4), "traffic": None,
+                         "peak_source": "measured copy bandwidth (MEASURED_PEAKS.json)" if peaks else "fallback 6.5 TB/s",
+                         "kernel": "one decode token step (CUDA graph of %d kernels: lm_head, arg-max, 22 layers over the KV cache)" % r["kernels_per_token"],
+                         "algorithmic_bytes_per_launch": round(r["step_bytes"]), "avg_ms": round(r["tok_ms"], 4),
+                         "share_of_step": round(r["tok_ms"] * args.new_tokens * args.steps / r["ms_dev"], 4),
+                         "prefill_ms_per_step": round(r["ms_dev"] / args.steps - r["tok_ms"] * args.new_tokens, 3)}}
+
+
 def run_reference_arm(args):
     rank = int(os.environ.get("RANK", "0"))
     if rank != 0:
+        return
+    if args.workload == "decode":
+        ups, ms, cores, sample = cpu_decode_utt_per_s(args.new_tokens)
+        line = {"impl": "reference", "metric": DECODE_METRIC, "value": round(ups, 5), "unit": "utt/s", "n_gpus": args.gpus, "steps": args.steps,
+                "warmup": args.warmup, "ms_per_step": round(ms, 1), "higher_is_better": True, "scaling": "weak", "vs_baseline": None,
+                "dtype": "f32", "data": "synthetic", "config": {"workload": workload_name(args), "utterances_per_step": 1},
+                "cpu_baseline": {"value": round(ups, 5), "unit": "utt/s", "cores": cores, "kind": "port", "sample": sample},
+                "e2e": {"value": round(ups, 5), "unit": "utt/s", "h2d_bytes_per_step": 0, "d2h_bytes_per_step": 0}, "gpu_launches": 0}
+        print(json.dumps(line), flush=True)
         return
     tps, ms, cores, sample = cpu_step_tokens_per_s(args.workload, args.seq, args.steps, args.warmup)
     line = {"impl": "reference", "metric": METRIC, "value": round(tps, 2), "unit": UNIT, "n_gpus": args.gpus, "steps": args.steps,
@@ -177,6 +328,8 @@ def gemm_epi_name(e: int) -> str:
 
 
 def run_native(args):
+    if args.workload == "decode":
+        return run_decode(args)
     import torch
     import torch.distributed as dist
     from dualhyp_b200 import flops, ops, synthetic
@@ -303,6 +456,15 @@ def run_native(args):
                                                "n": v[0] // 2, "avg_ms": round(v[1] / v[0], 4),
                                                "tflops": round(2.0 * k[1][0] * k[1][1] * (k[1][2] + k[1][3]) / (v[1] / v[0] / 1e3) / 1e12, 1)}
                                               for k, v in sorted(agg.items(), key=lambda kv: -kv[1][1]) if k[0] == "gemm"][:12]}
+    # ---- the metric's second half: a short sample of the greedy decode workload on the same model (full run: --workload decode) ----
+    if args.workload == "adapter" and not args.no_infer:
+        bucket.zero_grad()
+        model._engine.release_buffers()
+        r = decode_measure(model, dev, world, rank, args.utts, args.new_tokens, 2, 3, timed)
+        if rank == 0:
+            d = decode_line(args, r, world, world * args.utts * 2, None)
+            line["infer"] = {"metric": DECODE_METRIC, "value": d["value"], "unit": "utt/s", "e2e": d["e2e"], "ms_per_batch": d["ms_per_step"],
+                             "utterances_per_gpu": args.utts, "new_tokens": args.new_tokens, "roofline": d["roofline"]}
     if rank == 0 and world == 1 and not args.no_cpu_baseline:
         tps, ms, cores, sample = cpu_step_tokens_per_s(args.workload, T, 2, 1)
         line["cpu_baseline"] = {"value": round(tps, 2), "unit": UNIT, "cores": cores, "kind": "port", "sample": sample}

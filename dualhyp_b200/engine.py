@@ -430,9 +430,12 @@ class DecoderEngine:
         assert self.cache_k and self.cache_k[0].shape[0] >= idx.shape[0] and self.cache_max_len >= idx.shape[1]
         return self.forward_hidden(idx, packed, save=False, write_cache=True)
 
-    def decode_step(self, tokens: Tensor, positions: Tensor, packed: Dict[int, Dict[str, Tensor]]) -> Tensor:
+    def decode_step(self, tokens: Tensor, positions: Tensor, packed: Dict[int, Dict[str, Tensor]],
+                    pkv_all: Optional[Tensor] = None) -> Tensor:
         """One new token per sequence: tokens int64 [n], positions int32 [n] (0-based position of that token).
-        Returns ln_f output bf16 [n, C]."""
+        Returns ln_f output bf16 [n, C].  Allocation-free after the first call of a given n (all buffers come from
+        `_buf`), so a whole step can be captured into a CUDA graph (generate.DecodeLoop); `pkv_all` = the adapter
+        prefix K/V of `project_prefixes()` when the caller hoisted it out of the token loop."""
         s = self.spec
         n_seq = tokens.shape[0]
         C, I, G, qpk = s.n_embd, s.intermediate_size, s.n_query_groups, s.qpk
@@ -445,10 +448,13 @@ class DecoderEngine:
         act = self._buf("dec_act", (n_seq, I), bf)
         seq_ids = self._buf("dec_seq", (n_seq,), torch.int32)
         lens = self._buf("dec_lens", (n_seq,), torch.int32)
-        seq_ids.copy_(torch.arange(n_seq, device=self.device, dtype=torch.int32))
+        if self._bufs.get("dec_seq_n") != n_seq:
+            seq_ids.copy_(torch.arange(n_seq, device=self.device, dtype=torch.int32))
+            self._bufs["dec_seq_n"] = n_seq
         torch.add(positions, 1, out=lens)
         ops.embedding_fwd(tokens.contiguous(), self.wte, x)
-        pkv_all = self._project_prefixes(packed, "dec_pkv_all")
+        if pkv_all is None:
+            pkv_all = self._project_prefixes(packed, "dec_pkv_all")
         for i, lw in enumerate(self.layers):
             pk = packed.get(i, {})
             ops.rmsnorm_fwd(x, lw["norm1"], n, None, s.norm_eps)

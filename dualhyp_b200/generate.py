@@ -6,16 +6,117 @@ reference's `top_k=1` setting the sampling step keeps a single candidate, so the
 by `dh_argmax` with no per-token host sync unless an `eos_id` has to be polled.
 
 `generate_batch()` is the batched form: right-padded prompts prefilled together,
-one decode step per new token for all live sequences, per-sequence lengths on the device."""
+one decode step per new token for all live sequences, per-sequence lengths and the EOS flags on the device.
+The per-token work (lm_head -> arg-max -> record -> 22 decoder layers over the KV cache -> position bump) is
+captured ONCE into a CUDA graph (`DecodeLoop`) and replayed per token: the reference's loop costs ~400 kernel
+launches and a host sync per token (generate/base.py:57-80); here a token is one `cudaGraphLaunch`."""
 from __future__ import annotations
 
-from typing import List, Optional, Sequence
+from typing import Dict, List, Optional, Sequence
 
 import torch
 
 from . import ops
 
 Tensor = torch.Tensor
+
+
+class DecodeLoop:
+    """Device-resident state of a batched greedy decode plus the captured graph of one token step.
+
+    State (all on the device, fixed addresses so that the graph can be replayed and re-used across calls):
+    `last` = ln_f hidden state of each sequence's newest token, `pos` = position the next token will take,
+    `out_ids[:, step]` = generated ids, `done` = EOS seen, `step` = tokens generated so far, `eos` = the id to
+    stop at (-1: none).  One `body()` = one new token for every sequence."""
+
+    def __init__(self, eng, packed: Dict[int, Dict[str, Tensor]], n: int, max_new: int):
+        dev = eng.device
+        self.eng, self.n, self.max_new = eng, n, max_new
+        self.packed = packed
+        self.pkv_all = eng._project_prefixes(packed, "dec_pkv_all")
+        self.last = eng._buf("dec_hidden", (n, eng.spec.n_embd), torch.bfloat16)      # decode_step writes its result here
+        self.logits = torch.empty((n, eng.spec.vocab), dtype=torch.bfloat16, device=dev)
+        self.nxt = torch.zeros(n, dtype=torch.int64, device=dev)
+        self.pos = torch.zeros(n, dtype=torch.int32, device=dev)
+        self.out_ids = torch.zeros((n, max_new), dtype=torch.int64, device=dev)
+        self.done = torch.zeros(n, dtype=torch.bool, device=dev)
+        self.step = torch.zeros(1, dtype=torch.int64, device=dev)
+        self.eos = torch.full((1,), -1, dtype=torch.int64, device=dev)
+        self.eos_id: Optional[int] = None
+        self.kernels_per_token = 0
+        self.graph: Optional[torch.cuda.CUDAGraph] = None
+        self.cache_sig = None
+
+    def refresh(self, packed: Dict[int, Dict[str, Tensor]]) -> None:
+        """New values of the trainable tensors into the buffers the captured graph reads."""
+        for i, d in packed.items():
+            for k, t in d.items():
+                self.packed[i][k].copy_(t)
+        self.pkv_all = self.eng._project_prefixes(self.packed, "dec_pkv_all")
+
+    def reset(self, last: Tensor, lens: Tensor, eos_id: Optional[int]) -> None:
+        self.last.copy_(last)
+        self.pos.copy_(lens)
+        self.out_ids.zero_()
+        self.done.zero_()
+        self.step.zero_()
+        self.eos_id = eos_id
+        self.eos.fill_(-1 if eos_id is None else int(eos_id))
+
+    def body(self) -> None:
+        eng = self.eng
+        l0 = ops.launches()
+        eng.lm_head(self.last, out=self.logits)
+        ops.argmax(self.logits, self.nxt)
+        self.out_ids.index_copy_(1, self.step, self.nxt.unsqueeze(1))
+        self.done.logical_or_(self.nxt == self.eos)
+        hidden = eng.decode_step(self.nxt, self.pos, self.packed, self.pkv_all)
+        assert hidden.data_ptr() == self.last.data_ptr()
+        self.pos.add_(1)
+        self.step.add_(1)
+        self.kernels_per_token = ops.launches() - l0          # this library's kernels in one token step
+
+    def capture(self) -> None:
+        """Record one body() into a graph.  Must follow at least one eager body() of the same shape (first-use
+        initialisation inside the C ABI -- function attributes, the device query -- is not capturable)."""
+        sig = tuple(t.data_ptr() for t in self.eng.cache_k)
+        if self.graph is not None and sig == self.cache_sig:
+            return
+        torch.cuda.synchronize()
+        g = torch.cuda.CUDAGraph()
+        l0 = ops.launches()
+        with torch.cuda.graph(g):
+            self.body()
+        ops._count(l0 - ops.launches())                        # capturing launches nothing
+        self.graph, self.cache_sig = g, sig
+
+    def run(self, n_tokens: int, use_graph: bool, poll_every: int) -> int:
+        """Generate up to n_tokens; returns how many steps ran.  The first token of a fresh loop runs eagerly."""
+        polling = self.eos_id is not None and poll_every > 0
+        steps = 0
+        while steps < n_tokens:
+            if use_graph and (self.graph is not None or steps > 0):
+                self.capture()
+                self.graph.replay()
+                ops._count(self.kernels_per_token)             # keep ops.launches() truthful under replay
+            else:
+                self.body()
+            steps += 1
+            if polling and steps % poll_every == 0 and bool(self.done.all()):
+                break
+        return steps
+
+
+def _decode_loop(eng, packed, n: int, max_new: int) -> DecodeLoop:
+    """One loop (and one captured graph) per batch size; `out_ids` has room for at least 256 new tokens so that
+    calls with different `max_new_tokens` (generate/base.py is called once per utterance) share it."""
+    loops = eng._bufs.setdefault("decode_loops", {})
+    loop = loops.get(n)
+    if loop is None or loop.max_new < max_new:
+        loop = loops[n] = DecodeLoop(eng, packed, n, max(256, max_new))
+    else:
+        loop.refresh(packed)
+    return loop
 
 
 @torch.inference_mode()
@@ -33,9 +134,10 @@ def generate(model, idx: Tensor, max_returned_tokens: int, *, temperature: float
 
 @torch.inference_mode()
 def generate_batch(model, prompts: Sequence[Tensor], max_new_tokens: int, eos_id: Optional[int] = None,
-                   poll_every: int = 8) -> List[Tensor]:
-    """Greedy-decode every prompt (1-D int64 tensors).  Returns prompt + generated ids per sequence, cut after
-    the first `eos_id` (inclusive) when given."""
+                   poll_every: int = 8, use_graph: bool = True, return_device: bool = False):
+    """Greedy-decode every prompt (1-D int64 tensors, host or device).  Returns prompt + generated ids per sequence,
+    cut after the first `eos_id` (inclusive) when given.  `return_device=True` returns the raw device tensor
+    `[n, steps]` of generated ids instead (no device-to-host copy; used by bench.py's HBM-resident leg)."""
     eng = model._engine_ready()
     dev = eng.device
     names, tensors = model._trainables()
@@ -45,33 +147,23 @@ def generate_batch(model, prompts: Sequence[Tensor], max_new_tokens: int, eos_id
     Tmax = int(lens.max())
     total = Tmax + max_new_tokens
     assert total - 1 <= model.max_seq_length, "prompt + new tokens exceed max_seq_length"
-    ids = torch.zeros((n, Tmax), dtype=torch.int64)
-    for i, p in enumerate(prompts):
-        ids[i, : p.numel()] = p.cpu()
-    ids = ids.to(dev)
+    if all(p.is_cuda for p in prompts):
+        ids = torch.nn.utils.rnn.pad_sequence(list(prompts), batch_first=True, padding_value=0)
+    else:
+        ids = torch.zeros((n, Tmax), dtype=torch.int64).pin_memory()
+        for i, p in enumerate(prompts):
+            ids[i, : p.numel()] = p.cpu()
+        ids = ids.to(dev, non_blocking=True)
     lens_d = lens.to(dev)
     eng.alloc_cache(n, max(model.max_seq_length, total))
-    hidden = eng.prefill(ids, packed).view(n, Tmax, -1)
-    last = hidden[torch.arange(n, device=dev), (lens_d - 1).long()].contiguous()       # ln_f state of each prompt's last token
-    out_ids = torch.zeros((n, max_new_tokens), dtype=torch.int64, device=dev)
-    nxt = torch.empty(n, dtype=torch.int64, device=dev)
-    logits = torch.empty((n, eng.spec.vocab), dtype=torch.bfloat16, device=dev)
-    pos = lens_d.clone()                                                               # position of the token being generated
-    done = torch.zeros(n, dtype=torch.bool, device=dev)
-    steps = 0
-    for step in range(max_new_tokens):
-        eng.lm_head(last, out=logits)
-        ops.argmax(logits, nxt)
-        out_ids[:, step] = nxt
-        steps = step + 1
-        if eos_id is not None:
-            done |= nxt == eos_id
-            if (step + 1) % poll_every == 0 and bool(done.all()):
-                break
-        if step + 1 < max_new_tokens:
-            last = eng.decode_step(nxt, pos, packed)
-            pos = pos + 1
-    out_ids = out_ids[:, :steps].cpu()
+    loop = _decode_loop(eng, packed, n, max_new_tokens)
+    hidden = eng.prefill(ids, loop.packed).view(n, Tmax, -1)
+    last = hidden[torch.arange(n, device=dev), (lens_d - 1).long()]                    # ln_f state of each prompt's last token
+    loop.reset(last, lens_d, eos_id)
+    steps = loop.run(max_new_tokens, use_graph, poll_every)
+    if return_device:
+        return loop.out_ids[:, :steps]
+    out_ids = loop.out_ids[:, :steps].cpu()
     result = []
     for i, p in enumerate(prompts):
         gen = out_ids[i]

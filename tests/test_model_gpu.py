@@ -174,6 +174,42 @@ def test_batched_decode_equals_single_and_uncached():
     m.reset_cache()
 
 
+def test_graph_decode_equals_eager_and_is_reusable():
+    """The captured per-token CUDA graph (generate.DecodeLoop) produces the same ids as the eager launch sequence,
+    is re-used by later calls with other prompts / token budgets / trainable values, and honours `eos_id` (the cut
+    is inclusive, generate/base.py:72-74)."""
+    m, _ = build("adapter", adapter_start_layer=1)
+    pa = [p.to(DEV) for p in synthetic.synth_prompts(4, 512, SEED + 1, prompt_range=(20, 60))]
+    pb = [p.to(DEV) for p in synthetic.synth_prompts(4, 512, SEED + 2, prompt_range=(10, 90))]
+    eager_a = generate_batch(m, pa, 12, use_graph=False)
+    graph_a = generate_batch(m, pa, 12, use_graph=True)           # first token eager, then capture + replay
+    loop = m._engine._bufs["decode_loops"][4]
+    g0 = loop.graph
+    assert g0 is not None
+    graph_b = generate_batch(m, pb, 9, use_graph=True)            # pure replay of the same graph
+    eager_b = generate_batch(m, pb, 9, use_graph=False)
+    assert m._engine._bufs["decode_loops"][4].graph is g0
+    for e, g in zip(eager_a + eager_b, graph_a + graph_b):
+        assert e.tolist() == g.tolist()
+    # a changed trainable tensor must reach the replayed graph (DecodeLoop.refresh)
+    with torch.no_grad():
+        for n_, p_ in m.named_parameters():
+            if "gating_factor" in n_:
+                p_.mul_(-3.0)
+    eager_c = generate_batch(m, pa, 12, use_graph=False)
+    graph_c = generate_batch(m, pa, 12, use_graph=True)
+    assert [x.tolist() for x in eager_c] == [x.tolist() for x in graph_c]
+    assert [x.tolist() for x in eager_c] != [x.tolist() for x in eager_a], "the gate change did not alter the decode"
+    # EOS: stop id = the 3rd generated token of sequence 0
+    eos = int(graph_c[0][pa[0].numel() + 2])
+    cut = generate_batch(m, pa, 12, eos_id=eos, poll_every=4)
+    for full, c in zip(graph_c, cut):
+        gen = full[len(full) - 12:].tolist()
+        want = full.tolist() if eos not in gen else full[: len(full) - 12 + gen.index(eos) + 1].tolist()
+        assert c.tolist() == want
+    m.reset_cache()
+
+
 def test_reference_generate_loop_runs_on_the_model():
     """generate/base.py's loop restated verbatim: model(x, input_pos) -> logits[0, -1] / temperature -> topk(1) ->
     where(< v) -> softmax -> multinomial, one token at a time through the KV cache.  bf16 logits can tie exactly at
