@@ -1226,55 +1226,163 @@ __global__ void __launch_bounds__(PFX_THREADS, 2) attn_bwd_prefix_kernel(const _
 }
 
 // =================================================================================================
-// decode: one query per (sequence, head) against the KV cache.  Block = (sequence, kv group); warp = one
-// q head of the group; keys strided over lanes for the scores, head dims over lanes for P V.
+// decode: one query per (sequence, head) against the KV cache -- HBM-bound (the cache is read once per token).
+// Block = (sequence, kv group): the group's q heads (<= 8) share every K / V row, so a row is loaded ONCE and
+// used by all of them (native GQA).  Thread = (dg, ks): dg = tid % 8 owns head dims [8 dg, 8 dg + 8) (one 16-byte
+// load per row), ks = tid / 8 walks keys ks, ks + 32, ...  => a warp reads 4 whole 128-byte rows per load
+// instruction, 4 loads in flight per thread.  Scores go through shared memory (fp32), the softmax is one warp per
+// head, P V accumulates 8 heads x 8 dims per thread and is reduced over the 32 key slices at the end.
 // =================================================================================================
 constexpr int DEC_MAX_QPK = 8;
+constexpr int DEC_THREADS = 256;
+constexpr int DEC_FIXED_FLOATS = DEC_MAX_QPK * HD /*q*/ + 8 * 8 * HD /*per-warp partial outputs*/ + DEC_MAX_QPK * HD /*out*/ + 2 * DEC_MAX_QPK;
 
-__global__ void __launch_bounds__(256) attn_decode_kernel(const bf16* __restrict__ qkv, const bf16* __restrict__ ck,
-                                                          const bf16* __restrict__ cv, const int* __restrict__ lens, bf16* out,
-                                                          const bf16* __restrict__ prefix_kv, const float* __restrict__ gate, int max_len,
-                                                          int G, int qpk, int prefix_len, long long ld_qkv, float scale) {
-  extern __shared__ float sdec[];   // [qpk][max_len + MAX_PREFIX] scores
+__global__ void __launch_bounds__(DEC_THREADS) attn_decode_kernel(const bf16* __restrict__ qkv, const bf16* __restrict__ ck,
+                                                                  const bf16* __restrict__ cv, const int* __restrict__ lens, bf16* out,
+                                                                  const bf16* __restrict__ prefix_kv, const float* __restrict__ gate,
+                                                                  int max_len, int G, int qpk, int prefix_len, long long ld_qkv, float scale) {
+  extern __shared__ float sdec[];
+  float* sq = sdec;                                   // [8][64]   scaled queries
+  float* spart = sq + DEC_MAX_QPK * HD;               // [8 warps][8 heads][64]
+  float* sout = spart + 8 * 8 * HD;                   // [8][64]
+  float* sinv = sout + DEC_MAX_QPK * HD;              // [8] 1 / sum, [8] spare
+  float* sc = sinv + 2 * DEC_MAX_QPK;                 // [qpk][stride] scores / probabilities
+  const int stride = max_len + 1;                     // odd stride: the 8 heads of one key land in different banks
   const int seq = blockIdx.x, g = blockIdx.y;
-  const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
-  if (warp >= qpk) return;
-  const int h = g * qpk + warp;
+  const int tid = threadIdx.x, warp = tid >> 5, lane = tid & 31;
+  const int dg = tid & 7, ks = tid >> 3;
   const int H = G * qpk;
   const int len = lens[seq];
-  float* sc = sdec + warp * (max_len + MAX_PREFIX);
-  const bf16* q = qkv + (long long)seq * ld_qkv + (g * (qpk + 2) + warp) * HD;
-  const float q0 = __bfloat162float(q[lane]) * scale, q1 = __bfloat162float(q[lane + 32]) * scale;
-  const bf16* kbase = ck + ((long long)seq * G + g) * max_len * HD;
-  const bf16* vbase = cv + ((long long)seq * G + g) * max_len * HD;
-  // scores: each key needs a 64-dim dot; lanes hold dims {lane, lane+32}, reduce across the warp
-  float mx = -INFINITY;
-  for (int k = 0; k < len; ++k) {
-    const bf16* kr = kbase + (long long)k * HD;
-    float s = q0 * __bfloat162float(kr[lane]) + q1 * __bfloat162float(kr[lane + 32]);
-    s = warp_sum(s);
-    if (lane == 0) sc[k] = s;
-    mx = fmaxf(mx, s);
+  for (int i = tid; i < DEC_MAX_QPK * HD; i += DEC_THREADS) {
+    const int h = i >> 6;
+    sq[i] = h < qpk ? __bfloat162float(qkv[(long long)seq * ld_qkv + (g * (qpk + 2) + h) * HD + (i & 63)]) * scale : 0.f;
   }
-  __syncwarp();
-  float sum = 0.f;
-  for (int k = lane; k < len; k += 32) {
-    const float e = __expf(sc[k] - mx);
-    sc[k] = e;
-    sum += e;
+  __syncthreads();
+  const uint4* kbase = reinterpret_cast<const uint4*>(ck + ((long long)seq * G + g) * max_len * HD) + dg;   // row k: kbase[8 k]
+  const uint4* vbase = reinterpret_cast<const uint4*>(cv + ((long long)seq * G + g) * max_len * HD) + dg;
+
+  // ---- scores ----
+  {
+    float qr[DEC_MAX_QPK][8];
+#pragma unroll
+    for (int h = 0; h < DEC_MAX_QPK; ++h)
+#pragma unroll
+      for (int j = 0; j < 8; ++j) qr[h][j] = sq[h * HD + dg * 8 + j];
+    for (int kb = 0; kb < len; kb += 128) {      // block-uniform trip count: the shuffles below need whole warps
+      const int k0 = kb + ks;
+      uint4 kv[4];
+#pragma unroll
+      for (int u = 0; u < 4; ++u) {
+        const int k = k0 + 32 * u;
+        kv[u] = k < len ? __ldg(kbase + 8 * (long long)k) : make_uint4(0, 0, 0, 0);
+      }
+#pragma unroll
+      for (int u = 0; u < 4; ++u) {
+        const int k = k0 + 32 * u;
+        float kf[8];
+        unpack8(kv[u], kf);
+        float part[DEC_MAX_QPK];
+#pragma unroll
+        for (int h = 0; h < DEC_MAX_QPK; ++h) {
+          float a = 0.f;
+#pragma unroll
+          for (int j = 0; j < 8; ++j) a = fmaf(kf[j], qr[h][j], a);
+          part[h] = a;
+        }
+        // sum over the 8 dim groups (lanes dg = 0..7 of this key); lane dg keeps head dg
+#pragma unroll
+        for (int h = 0; h < DEC_MAX_QPK; ++h) {
+          float a = part[h];
+          a += __shfl_xor_sync(0xffffffffu, a, 1);
+          a += __shfl_xor_sync(0xffffffffu, a, 2);
+          a += __shfl_xor_sync(0xffffffffu, a, 4);
+          part[h] = a;
+        }
+        float mine = part[0];
+#pragma unroll
+        for (int h = 1; h < DEC_MAX_QPK; ++h) mine = dg == h ? part[h] : mine;
+        if (k < len && dg < qpk) sc[dg * stride + k] = mine;
+      }
+    }
   }
-  sum = warp_sum(sum);
-  __syncwarp();
-  float o0 = 0.f, o1 = 0.f;
-  for (int k = 0; k < len; ++k) {
-    const float pk = sc[k];
-    const bf16* vr = vbase + (long long)k * HD;
-    o0 += pk * __bfloat162float(vr[lane]);
-    o1 += pk * __bfloat162float(vr[lane + 32]);
+  __syncthreads();
+  // ---- softmax: warp h owns head h ----
+  if (warp < qpk) {
+    float* row = sc + warp * stride;
+    float mx = -INFINITY;
+    for (int k = lane; k < len; k += 32) mx = fmaxf(mx, row[k]);
+    mx = warp_max(mx);
+    float sum = 0.f;
+    for (int k = lane; k < len; k += 32) {
+      const float e = __expf(row[k] - mx);
+      row[k] = e;
+      sum += e;
+    }
+    sum = warp_sum(sum);
+    if (lane == 0) sinv[warp] = 1.f / sum;
   }
-  const float inv = 1.f / sum;
-  o0 *= inv; o1 *= inv;
+  __syncthreads();
+  // ---- P V ----
+  {
+    float acc[DEC_MAX_QPK][8];
+#pragma unroll
+    for (int h = 0; h < DEC_MAX_QPK; ++h)
+#pragma unroll
+      for (int j = 0; j < 8; ++j) acc[h][j] = 0.f;
+    for (int kb = 0; kb < len; kb += 128) {
+      const int k0 = kb + ks;
+      uint4 vv[4];
+#pragma unroll
+      for (int u = 0; u < 4; ++u) {
+        const int k = k0 + 32 * u;
+        vv[u] = k < len ? __ldg(vbase + 8 * (long long)k) : make_uint4(0, 0, 0, 0);
+      }
+#pragma unroll
+      for (int u = 0; u < 4; ++u) {
+        const int k = k0 + 32 * u;
+        if (k < len) {
+          float vf[8];
+          unpack8(vv[u], vf);
+#pragma unroll
+          for (int h = 0; h < DEC_MAX_QPK; ++h) {
+            const float pk = h < qpk ? sc[h * stride + k] : 0.f;
+#pragma unroll
+            for (int j = 0; j < 8; ++j) acc[h][j] = fmaf(pk, vf[j], acc[h][j]);
+          }
+        }
+      }
+    }
+    // reduce over the 4 key slices of this warp (lane bits 3, 4), then over the 8 warps through shared memory
+#pragma unroll
+    for (int h = 0; h < DEC_MAX_QPK; ++h)
+#pragma unroll
+      for (int j = 0; j < 8; ++j) {
+        float a = acc[h][j];
+        a += __shfl_xor_sync(0xffffffffu, a, 8);
+        a += __shfl_xor_sync(0xffffffffu, a, 16);
+        acc[h][j] = a;
+      }
+    if (lane < 8) {
+#pragma unroll
+      for (int h = 0; h < DEC_MAX_QPK; ++h)
+#pragma unroll
+        for (int j = 0; j < 8; ++j) spart[(warp * 8 + h) * HD + dg * 8 + j] = acc[h][j];
+    }
+  }
+  __syncthreads();
+  for (int i = tid; i < DEC_MAX_QPK * HD; i += DEC_THREADS) {
+    float a = 0.f;
+#pragma unroll
+    for (int w = 0; w < 8; ++w) a += spart[w * 8 * HD + i];
+    sout[i] = a * sinv[i >> 6];
+  }
+  __syncthreads();
+  if (warp >= qpk) return;
+  // ---- warp h finishes head h: + gate * softmax(q . prefix_k) prefix_v (its own softmax, ger/adapter.py:139-146) ----
+  const int h = g * qpk + warp;
+  float o0 = sout[warp * HD + lane], o1 = sout[warp * HD + lane + 32];
   if (prefix_len > 0) {
+    const float q0 = sq[warp * HD + lane], q1 = sq[warp * HD + lane + 32];
     const long long koff = (long long)(g * (qpk + 2) + qpk) * HD;
     float ps[MAX_PREFIX];
     float pm = -INFINITY;
@@ -1428,7 +1536,7 @@ extern "C" int dh_attention_decode(const void* qkv, const void* cache_k, const v
   DH_CHECK(qkv && cache_k && cache_v && lens && out && nseq > 0, "dh_attention_decode: bad argument");
   DH_CHECK(q_per_kv <= DEC_MAX_QPK, "dh_attention_decode: q_per_kv %d > %d", q_per_kv, DEC_MAX_QPK);
   DH_CHECK(prefix_len >= 0 && prefix_len <= MAX_PREFIX, "dh_attention_decode: prefix_len too large");
-  const size_t smem = (size_t)q_per_kv * (max_len + MAX_PREFIX) * sizeof(float);
+  const size_t smem = ((size_t)DEC_FIXED_FLOATS + (size_t)q_per_kv * (max_len + 1)) * sizeof(float);
   DH_CHECK(smem <= 200 * 1024, "dh_attention_decode: max_len %d too large for the score buffer", max_len);
   static bool attr = false;
   if (!attr) {
@@ -1436,7 +1544,7 @@ extern "C" int dh_attention_decode(const void* qkv, const void* cache_k, const v
     attr = true;
   }
   const long long ld = (long long)n_groups * (q_per_kv + 2) * HD;
-  attn_decode_kernel<<<dim3(nseq, n_groups), 256, smem, (cudaStream_t)stream>>>(
+  attn_decode_kernel<<<dim3(nseq, n_groups), DEC_THREADS, smem, (cudaStream_t)stream>>>(
       (const bf16*)qkv, (const bf16*)cache_k, (const bf16*)cache_v, lens, (bf16*)out, (const bf16*)(prefix_len > 0 ? prefix_kv : nullptr),
       gate, max_len, n_groups, q_per_kv, prefix_kv ? prefix_len : 0, ld, 1.0f / sqrtf((float)HD));
   DH_CUDA(cudaGetLastError());

@@ -33,6 +33,7 @@ struct GemmParams {
   const bf16* rope_sin;
   const int* positions;
   const int* m_limit;      // optional device-side row count: tiles at or beyond it are skipped
+  int sk_stages;           // skinny kernel: depth of the TMA ring
 };
 
 template <int BN> struct GemmCfg {
@@ -319,6 +320,195 @@ gemm_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant__ CUt
   if (warp == 2) {
     tc_fence_after();
     tmem_dealloc(tmem_base, Cfg::TMEM_COLS);
+  }
+}
+
+// ------------------------------------------------------------------------------------------------
+// Skinny GEMM (M <= 128: the decode step, one token per sequence) -- weight streaming, HBM-bound.
+// A 128 x 128 output tile per CTA leaves only N / 128 tiles (16 when N = 2048), so K is split over a thread-block
+// CLUSTER of S <= 4 CTAs per tile: each CTA streams its K range through an 8-stage TMA ring into tcgen05.mma,
+// parks its fp32 partial tile in its own shared memory, and after one cluster barrier the tile's (row, 64-column)
+// units are dealt round-robin to the S CTAs, each summing the S partials over DISTRIBUTED SHARED MEMORY in rank
+// order (deterministic) and running the fused epilogue.  No global workspace, no atomics.
+// M <= 64 loads only a 64-row A box: the accumulator rows 64..127 are then garbage computed from whatever the
+// B tile behind it holds (MMA rows are independent) and are never read, so a stage is 8 KB of A + 16 KB of W.
+// Roles as gemm_kernel: warp 0 TMA, warp 1 MMA, warp 2 TMEM, warps 4-7 epilogue.
+// ------------------------------------------------------------------------------------------------
+constexpr int SK_BN = 128;
+constexpr int SK_B_BYTES = SK_BN * BK * 2;
+constexpr int SK_PAD = SK_BN + 4;               // fp32 partial row pitch (floats): 16-byte aligned, conflict-free rows
+constexpr int SK_RING_BYTES = 192 * 1024;
+constexpr int SK_MAX_STAGES = 8;
+
+// cluster barrier without .aligned: the role branches above leave warp 0 / 1 possibly un-converged
+__device__ __forceinline__ void cluster_sync_any() {
+  asm volatile("barrier.cluster.arrive.release;\n\tbarrier.cluster.wait.acquire;" ::: "memory");
+}
+__device__ __forceinline__ float4 ld_dsmem_f4(uint32_t cluster_addr) {
+  float4 v;
+  asm("ld.shared::cluster.v4.f32 {%0, %1, %2, %3}, [%4];" : "=f"(v.x), "=f"(v.y), "=f"(v.z), "=f"(v.w) : "r"(cluster_addr));
+  return v;
+}
+
+template <int EPI>
+__global__ void __launch_bounds__(GEMM_THREADS, 1)
+gemm_skinny_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant__ CUtensorMap tmB,
+                   const __grid_constant__ CUtensorMap tmA2, const __grid_constant__ CUtensorMap tmB2, const GemmParams p) {
+  extern __shared__ uint8_t smem_raw[];
+  uint8_t* smem = reinterpret_cast<uint8_t*>((reinterpret_cast<uintptr_t>(smem_raw) + 1023) & ~uintptr_t(1023));
+  const int a_bytes = p.M <= 64 ? 64 * BK * 2 : BM * BK * 2;
+  const int stage_bytes = a_bytes + SK_B_BYTES;
+  const int stages = p.sk_stages;
+  uint64_t* bars = reinterpret_cast<uint64_t*>(smem + stages * stage_bytes);
+  uint64_t* full_bar = bars;                       // [stages]
+  uint64_t* empty_bar = bars + SK_MAX_STAGES;      // [stages]
+  uint64_t* tfull_bar = bars + 2 * SK_MAX_STAGES;  // [1]
+  uint32_t* tmem_slot = reinterpret_cast<uint32_t*>(bars + 2 * SK_MAX_STAGES + 1);
+
+  const int warp = __shfl_sync(0xffffffffu, threadIdx.x >> 5, 0);
+  const int lane = threadIdx.x & 31;
+  const int S = gridDim.x, split = blockIdx.x, tile = blockIdx.y;      // the cluster spans x: rank == split
+  const int n0 = tile * SK_BN;
+  const int nkb1 = (p.K1 + BK - 1) / BK;
+  const int nkb = nkb1 + (p.K2 + BK - 1) / BK;
+  const int kb_begin = (int)((long long)nkb * split / S), kb_end = (int)((long long)nkb * (split + 1) / S);
+
+  if (warp == 0 && lane == 0) {
+    tma_prefetch_desc(&tmA);
+    tma_prefetch_desc(&tmB);
+    if (p.K2 > 0) { tma_prefetch_desc(&tmA2); tma_prefetch_desc(&tmB2); }
+  }
+  if (warp == 1 && lane == 0) {
+    for (int i = 0; i < stages; ++i) { mbar_init(&full_bar[i], 1); mbar_init(&empty_bar[i], 1); }
+    mbar_init(tfull_bar, 1);
+    fence_barrier_init();
+  }
+  if (warp == 2) {
+    tmem_alloc(tmem_slot, SK_BN);
+    tmem_relinquish();
+  }
+  tc_fence_before();
+  __syncthreads();
+  tc_fence_after();
+  const uint32_t tmem_base = __shfl_sync(0xffffffffu, *tmem_slot, 0);
+
+  if (warp == 0 && lane == 0) {
+    uint32_t it = 0;
+    for (int kb = kb_begin; kb < kb_end; ++kb, ++it) {
+      const int s = it % stages;
+      mbar_wait(&empty_bar[s], ((it / stages) & 1) ^ 1);
+      uint8_t* sa = smem + s * stage_bytes;
+      uint8_t* sb = sa + a_bytes;
+      mbar_expect_tx(&full_bar[s], stage_bytes);
+      const bool second = kb >= nkb1;
+      const int k0 = (second ? kb - nkb1 : kb) * BK;
+      tma_load_2d(sa, second ? &tmA2 : &tmA, k0, 0, &full_bar[s]);
+      tma_load_2d(sb, second ? &tmB2 : &tmB, k0, n0, &full_bar[s]);
+    }
+  } else if (warp == 1) {
+    const uint32_t idesc = umma_idesc_bf16(BM, SK_BN, 0, 0);
+    uint32_t it = 0;
+    for (int kb = kb_begin; kb < kb_end; ++kb, ++it) {
+      const int s = it % stages;
+      mbar_wait(&full_bar[s], (it / stages) & 1);
+      tc_fence_after();
+      const uint32_t sa = smem_u32(smem + s * stage_bytes);
+      const uint32_t sb = sa + a_bytes;
+      if (elect_one()) {
+#pragma unroll
+        for (int k = 0; k < BK / 16; ++k)
+          tc_mma_ss(tmem_base, umma_desc_sw128(sa + k * 32, 16, 1024), umma_desc_sw128(sb + k * 32, 16, 1024), idesc, (it | k) != 0);
+        tc_commit(&empty_bar[s]);
+        if (kb == kb_end - 1) tc_commit(tfull_bar);
+      }
+      __syncwarp();
+    }
+  } else if (warp >= 4 && S > 1) {
+    // park this CTA's partial rows in shared memory (the ring is idle once the last MMA has completed)
+    const int q = warp & 3;
+    const int r = q * 32 + lane;
+    mbar_wait(tfull_bar, 0);
+    tc_fence_after();
+    float* prow = reinterpret_cast<float*>(smem) + (size_t)r * SK_PAD;
+#pragma unroll 1
+    for (int c = 0; c < SK_BN / 32; ++c) {
+      uint32_t r0[32];
+      tmem_ld32(tmem_base + ((uint32_t)(q * 32) << 16) + c * 32, r0);
+      tmem_wait_ld();
+      if (r < p.M) {
+#pragma unroll
+        for (int i = 0; i < 8; ++i)
+          *reinterpret_cast<float4*>(prow + c * 32 + 4 * i) =
+              make_float4(__uint_as_float(r0[4 * i]), __uint_as_float(r0[4 * i + 1]), __uint_as_float(r0[4 * i + 2]), __uint_as_float(r0[4 * i + 3]));
+      }
+    }
+  }
+  if (S > 1) {
+    tc_fence_before();
+    __syncthreads();
+    cluster_sync_any();
+  }
+  if (warp >= 4) {
+    const int t = threadIdx.x - 128;
+    if (S == 1) {
+      const int q = warp & 3;
+      const int row = q * 32 + lane;
+      mbar_wait(tfull_bar, 0);
+      tc_fence_after();
+#pragma unroll 1
+      for (int c = 0; c < SK_BN / 64; ++c) {
+        uint32_t r0[32], r1[32];
+        const uint32_t taddr = tmem_base + ((uint32_t)(q * 32) << 16) + c * 64;
+        tmem_ld32(taddr, r0);
+        tmem_ld32(taddr + 32, r1);
+        tmem_wait_ld();
+        float v[64];
+#pragma unroll
+        for (int j = 0; j < 32; ++j) { v[j] = __uint_as_float(r0[j]); v[j + 32] = __uint_as_float(r1[j]); }
+        if (row < p.M) epilogue_chunk<EPI>(p, row, n0 + c * 64, v);
+      }
+    } else {
+      // This CTA finishes the (row, 64-column) units u = split, split + S, ... of the tile.  Phase 1: all 128 epilogue
+      // threads sum the S partials of those units over distributed shared memory, one float4 column group at a time
+      // (S independent remote loads in flight per thread, ranks in fixed order => deterministic).  Phase 2: one thread
+      // per unit runs the fused epilogue on the reduced 64 values.
+      const int units = p.M * (SK_BN / 64);
+      const int my_units = units > split ? (units - split + S - 1) / S : 0;
+      float* red = reinterpret_cast<float*>(smem) + (size_t)p.M * SK_PAD;      // [my_units][64] behind the partial tile
+      const uint32_t base = smem_u32(smem);
+      for (int e = t; e < my_units * 16; e += 128) {
+        const int j = e >> 4, i = e & 15;
+        const int u = split + S * j;
+        const uint32_t local = base + (uint32_t)(((u >> 1) * SK_PAD + (u & 1) * 64 + 4 * i) * 4);
+        float4 x[8];
+#pragma unroll
+        for (int s2 = 0; s2 < 8; ++s2)
+          if (s2 < S) x[s2] = ld_dsmem_f4(mapa_shared(local, (uint32_t)s2));
+        float4 a = x[0];
+#pragma unroll
+        for (int s2 = 1; s2 < 8; ++s2)
+          if (s2 < S) { a.x += x[s2].x; a.y += x[s2].y; a.z += x[s2].z; a.w += x[s2].w; }
+        *reinterpret_cast<float4*>(red + j * 64 + 4 * i) = a;
+      }
+      asm volatile("bar.sync 1, 128;" ::: "memory");
+      for (int j = t; j < my_units; j += 128) {
+        const int u = split + S * j;
+        float v[64];
+#pragma unroll
+        for (int i = 0; i < 16; ++i) {
+          const float4 a = *reinterpret_cast<const float4*>(red + j * 64 + 4 * i);
+          v[4 * i] = a.x; v[4 * i + 1] = a.y; v[4 * i + 2] = a.z; v[4 * i + 3] = a.w;
+        }
+        epilogue_chunk<EPI>(p, u >> 1, n0 + (u & 1) * 64, v);
+      }
+    }
+  }
+  tc_fence_before();
+  __syncthreads();
+  if (S > 1) cluster_sync_any();       // nobody leaves while a peer may still read its partial tile
+  if (warp == 2) {
+    tc_fence_after();
+    tmem_dealloc(tmem_base, SK_BN);
   }
 }
 
@@ -767,6 +957,7 @@ static GemmParams make_params(const dh_gemm_args* a) {
   p.rope_sin = reinterpret_cast<const bf16*>(a->rope_sin);
   p.positions = a->positions;
   p.m_limit = a->m_limit;
+  p.sk_stages = 0;
   return p;
 }
 
@@ -871,6 +1062,65 @@ static int launch_gemm_pair(const dh_gemm_args* a, cudaStream_t stream) {
   return 0;
 }
 
+template <int EPI>
+static int launch_gemm_skinny(const dh_gemm_args* a, cudaStream_t stream) {
+  static bool attr_set = false;
+  if (!attr_set) {
+    DH_CUDA(cudaFuncSetAttribute(gemm_skinny_kernel<EPI>, cudaFuncAttributeMaxDynamicSharedMemorySize, SK_RING_BYTES + 1024 + 256));
+    attr_set = true;
+  }
+  const int box_m = a->M <= 64 ? 64 : BM;
+  CUtensorMap tmA, tmB, tmA2, tmB2;
+  if (make_operand_map(&tmA, a->A, a->lda, a->M, a->K1, 0, box_m)) return -3;
+  if (make_operand_map(&tmB, a->B, a->ldb, a->N, a->K1, 0, SK_BN)) return -3;
+  if (a->K2 > 0) {
+    if (make_operand_map(&tmA2, a->A2, a->lda2, a->M, a->K2, 0, box_m)) return -3;
+    if (make_operand_map(&tmB2, a->B2, a->ldb2, a->N, a->K2, 0, SK_BN)) return -3;
+  } else {
+    tmA2 = tmA;
+    tmB2 = tmB;
+  }
+  GemmParams p = make_params(a);
+  p.tiles_m = 1;
+  p.tiles_n = a->N / SK_BN;
+  const int tiles = p.tiles_n;
+  const int nkb = (a->K1 + BK - 1) / BK + (a->K2 + BK - 1) / BK;
+  // cluster size: a power of two <= 4 that keeps every CTA resident at once (one wave) with >= 2 k-blocks each.
+  // Measured on B200 (scripts/skinny_probe.py): a CTA streams one k-block per ~0.4 us whatever the ring depth (the
+  // SM's cap on bytes in flight), a cluster adds ~4 us, and 16 clusters of EIGHT 192 KB CTAs do not all fit at once
+  // (two per GPC would need 16 free SMs in every GPC), which doubles the time -- hence the cap of 4.
+  int S = 1;
+  while (S < 4 && tiles * (2 * S) <= sm_count() && nkb / (2 * S) >= 2) S *= 2;
+  const int stage_bytes = box_m * BK * 2 + SK_B_BYTES;
+  int stages = SK_RING_BYTES / stage_bytes;
+  if (stages > SK_MAX_STAGES) stages = SK_MAX_STAGES;
+  const int per_cta = (nkb + S - 1) / S;
+  if (stages > per_cta) stages = per_cta;
+  static int env_s = -2, env_stages = -2;      // developer knobs for A/B runs: DH_SKINNY_S, DH_SKINNY_STAGES
+  if (env_s == -2) { const char* e = getenv("DH_SKINNY_S"); env_s = e ? atoi(e) : -1; }
+  if (env_stages == -2) { const char* e = getenv("DH_SKINNY_STAGES"); env_stages = e ? atoi(e) : -1; }
+  if (env_s > 0 && nkb / env_s >= 1) S = env_s;
+  if (env_stages > 0 && env_stages <= SK_MAX_STAGES && env_stages * stage_bytes <= SK_RING_BYTES) stages = env_stages;
+  // the fp32 partial tile and this CTA's reduced units (S > 1) re-use the ring
+  const size_t park = (size_t)a->M * SK_PAD * sizeof(float) + (size_t)((a->M * 2 + S - 1) / S) * 64 * sizeof(float);
+  while (S > 1 && (size_t)stages * stage_bytes < park) ++stages;
+  p.sk_stages = stages;
+  cudaLaunchConfig_t cfg = {};
+  cfg.gridDim = dim3(S, tiles);
+  cfg.blockDim = dim3(GEMM_THREADS);
+  cfg.dynamicSmemBytes = (size_t)stages * stage_bytes + 1024 + 256;
+  cfg.stream = stream;
+  cudaLaunchAttribute attr[1];
+  attr[0].id = cudaLaunchAttributeClusterDimension;
+  attr[0].val.clusterDim.x = S;
+  attr[0].val.clusterDim.y = 1;
+  attr[0].val.clusterDim.z = 1;
+  cfg.attrs = attr;
+  cfg.numAttrs = 1;
+  DH_CUDA(cudaLaunchKernelEx(&cfg, gemm_skinny_kernel<EPI>, tmA, tmB, tmA2, tmB2, p));
+  return 0;
+}
+
 static int g_force_single = -1;   // DH_GEMM_SINGLE=1 forces the 1-CTA kernel (A/B testing)
 
 template <int EPI>
@@ -883,6 +1133,10 @@ static int dispatch_bn(const dh_gemm_args* a, cudaStream_t stream) {
   if (!g_force_single && a->a_layout == 0 && a->b_layout == 0 && (a->K2 == 0 || (a->a2_layout == 0 && a->b2_layout == 0)) &&
       a->N % 256 == 0 && a->M >= 1024 && pair_epilogue_ok(a))
     return launch_gemm_pair<EPI>(a, stream);
+  // one token per sequence (decode): weight streaming with K split over a cluster
+  if (a->M <= BM && a->N % SK_BN == 0 && a->a_layout == 0 && a->b_layout == 0 && (a->K2 == 0 || (a->a2_layout == 0 && a->b2_layout == 0)) &&
+      !a->m_limit && EPI != DH_EPI_SWIGLU_BWD && (EPI != DH_EPI_F32 || !a->accumulate))
+    return launch_gemm_skinny<EPI>(a, stream);
   // Tile width: 256 when it divides N and leaves enough tiles to fill the machine, else 128, else 64.
   const long long tiles_m = (a->M + BM - 1) / BM;
   if (a->N % 256 == 0 && tiles_m * (a->N / 256) >= sm_count()) return launch_gemm<256, EPI>(a, stream);

@@ -118,6 +118,57 @@ def test_gemm_qkv_rope_epilogue():
     assert rel(gv, v[:, ::qpk]) < 6e-3, report("v", gv, v[:, ::qpk])
 
 
+@pytest.mark.parametrize("M", [1, 5, 64, 100, 128])
+def test_gemm_skinny_decode_shapes(M):
+    """M <= 128 (decode: one token per sequence) takes the cluster split-K weight-streaming kernel: every epilogue the decode
+    step uses, at the TinyLlama shapes (split counts 1, 2, 8, 9, with and without the LoRA second source), is checked
+    against fp32 math and must be bit-identical run to run (partials are summed in split order, not arrival order)."""
+    C, I, G, qpk = 2048, 5632, 4, 8
+    x = rnd((M, C), 301)
+    # plain bf16 + column scale / bias (lm_head shape class, many tiles => no split) and a 2048-wide one (8 splits)
+    for N in (4096, 2048):
+        W = rnd((N, C), 302, bound=1 / 32)
+        o1 = torch.full((M, N), float("nan"), device=DEV, dtype=torch.bfloat16)
+        ops.gemm(x, W, o1)
+        o2 = torch.full((M, N), float("nan"), device=DEV, dtype=torch.bfloat16)
+        ops.gemm(x, W, o2)
+        torch.cuda.synchronize()
+        ref = x.float() @ W.float().t()
+        assert rel(o1, ref) < 4e-3, report(f"splitk bf16 N={N}", o1, ref)
+        assert torch.equal(o1, o2), "split-K result differs between two runs"
+    # residual epilogue, K = 5632 (9 splits) + LoRA K-extension
+    a = rnd((M, I), 303)
+    Wp = rnd((C, I), 304, bound=1 / 64)
+    a2, b2 = rnd((M, 64), 305, bound=0.1), rnd((C, 64), 306, bound=0.1)
+    res = rnd((M, C), 307, dtype=torch.float32)
+    out = torch.full((M, C), float("nan"), device=DEV, dtype=torch.float32)
+    ops.gemm(a, Wp, out, A2=a2, B2=b2, epilogue=ops.EPI_RESID_F32, aux=res)
+    torch.cuda.synchronize()
+    ref = res + (a.float() @ Wp.float().t() + a2.float() @ b2.float().t()).bfloat16().float()
+    assert rel(out, ref) < 1e-3, report("splitk resid", out, ref)
+    # SwiGLU (2 splits at N = 11264)
+    W1, W2 = rnd((I, C), 308, bound=1 / 32), rnd((I, C), 309, bound=1 / 32)
+    act = torch.full((M, I), float("nan"), device=DEV, dtype=torch.bfloat16)
+    ops.gemm(x, _interleave(W1, W2).contiguous(), None, epilogue=ops.EPI_SWIGLU, out2=act)
+    torch.cuda.synchronize()
+    ref = F.silu(x.float() @ W1.float().t()) * (x.float() @ W2.float().t())
+    assert rel(act, ref) < 8e-3, report("splitk swiglu", act, ref)
+    # QKV + RoPE with explicit positions (decode)
+    cfg = O.OracleConfig(n_head=G * qpk, n_query_groups=G, n_embd=C, block_size=2048)
+    Wq = rnd((cfg.qkv_out, C), 310, bound=1 / 32)
+    cos, sin = O.build_rope_cache(2048, 64)
+    pos = synthetic.hash_ints((M,), 5, 311, 0, 2048).to(torch.int32)
+    qkv = torch.full((M, cfg.qkv_out), float("nan"), device=DEV, dtype=torch.bfloat16)
+    ops.gemm(x, Wq, qkv, epilogue=ops.EPI_QKV_ROPE, rope_cos=cos.to(DEV), rope_sin=sin.to(DEV), positions=pos.to(DEV), seq_len=1, q_per_kv=qpk)
+    torch.cuda.synchronize()
+    raw = (x.float() @ Wq.float().t()).bfloat16().float().cpu().view(M, G, qpk + 2, 64)
+    c, s_ = cos.float()[pos.long()][:, None, None, :], sin.float()[pos.long()][:, None, None, :]
+    rot = torch.cat((-raw[..., 32:], raw[..., :32]), dim=-1)
+    want = raw.clone()
+    want[:, :, : qpk + 1] = (raw * c + rot * s_)[:, :, : qpk + 1]
+    assert rel(qkv.cpu().view(M, G, qpk + 2, 64), want) < 6e-3, report("splitk rope", qkv.cpu().view(M, G, qpk + 2, 64), want)
+
+
 def _interleave(w1, w2):
     I = w1.shape[0]
     return torch.stack((w1.view(I // 32, 32, -1), w2.view(I // 32, 32, -1)), dim=1).reshape(2 * I, -1)
@@ -420,6 +471,35 @@ def test_attention_decode_matches_prefill():
     torch.cuda.synchronize()
     ref = torch.stack([out[b * T + int(lens[b]) - 1] for b in range(B_)])
     assert rel(dec, ref) < 1e-2, report("decode attn", dec, ref)
+
+
+@pytest.mark.parametrize("nseq,G,qpk,prefix", [(5, 4, 8, 10), (3, 2, 2, 0), (2, 1, 1, 16)])
+def test_attention_decode_against_fp32(nseq, G, qpk, prefix):
+    """The decode kernel against fp32 softmax attention over the valid cache slots (lengths from 1 to several hundred,
+    not multiples of the 32-key slice width), with and without the gated prefix."""
+    H, max_len = G * qpk, 640
+    N = G * (qpk + 2) * 64
+    lens = synthetic.hash_ints((nseq,), 3, 401, 1, max_len + 1).to(torch.int32)
+    lens[0], lens[-1] = 1, max_len
+    ck, cv = rnd((nseq, G, max_len, 64), 402, 2.0), rnd((nseq, G, max_len, 64), 403, 2.0)
+    row = rnd((nseq, N), 404, 2.0)
+    pk = rnd((max(prefix, 1), N), 405, 2.0)
+    gate = rnd((H,), 406, 1.0, torch.float32)
+    out = torch.full((nseq, H * 64), float("nan"), device=DEV, dtype=torch.bfloat16)
+    ops.attention_decode(row, ck, cv, lens.to(DEV), out, G, qpk, pk if prefix else None, gate if prefix else None, prefix)
+    torch.cuda.synchronize()
+    r = row.float().view(nseq, G, qpk + 2, 64)
+    ref = torch.zeros((nseq, G, qpk, 64), device=DEV)
+    for b in range(nseq):
+        L = int(lens[b])
+        q = r[b, :, :qpk]                                                  # [G, qpk, 64]
+        sc = torch.einsum("gqd,gkd->gqk", q, ck[b, :, :L].float()) / 8.0
+        ref[b] = torch.einsum("gqk,gkd->gqd", sc.softmax(-1), cv[b, :, :L].float())
+        if prefix:
+            pkv = pk.float().view(-1, G, qpk + 2, 64)[:prefix]
+            sa = torch.einsum("gqd,agd->gqa", q, pkv[:, :, qpk]) / 8.0
+            ref[b] += gate.view(G, qpk, 1) * torch.einsum("gqa,agd->gqd", sa.softmax(-1), pkv[:, :, qpk + 1])
+    assert rel(out, ref.reshape(nseq, -1)) < 6e-3, report("decode attn fp32", out, ref.reshape(nseq, -1))
 
 
 def test_relpred_fwd_bwd():
