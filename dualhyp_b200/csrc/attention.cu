@@ -1289,18 +1289,22 @@ __global__ void __launch_bounds__(DEC_THREADS) attn_decode_kernel(const bf16* __
           for (int j = 0; j < 8; ++j) a = fmaf(kf[j], qr[h][j], a);
           part[h] = a;
         }
-        // sum over the 8 dim groups (lanes dg = 0..7 of this key); lane dg keeps head dg
+        // transposing butterfly over the 8 dim-group lanes of this key: 4 + 2 + 1 shuffles leave head dg's full
+        // dot product in lane dg (each step halves the heads a lane still carries)
+        const bool b2 = dg & 4, b1 = dg & 2, b0 = dg & 1;
+        float k4[4], k2[2];
 #pragma unroll
-        for (int h = 0; h < DEC_MAX_QPK; ++h) {
-          float a = part[h];
-          a += __shfl_xor_sync(0xffffffffu, a, 1);
-          a += __shfl_xor_sync(0xffffffffu, a, 2);
-          a += __shfl_xor_sync(0xffffffffu, a, 4);
-          part[h] = a;
+        for (int i = 0; i < 4; ++i) {
+          const float recv = __shfl_xor_sync(0xffffffffu, b2 ? part[i] : part[i + 4], 4);
+          k4[i] = (b2 ? part[i + 4] : part[i]) + recv;
         }
-        float mine = part[0];
 #pragma unroll
-        for (int h = 1; h < DEC_MAX_QPK; ++h) mine = dg == h ? part[h] : mine;
+        for (int i = 0; i < 2; ++i) {
+          const float recv = __shfl_xor_sync(0xffffffffu, b1 ? k4[i] : k4[i + 2], 2);
+          k2[i] = (b1 ? k4[i + 2] : k4[i]) + recv;
+        }
+        const float recv = __shfl_xor_sync(0xffffffffu, b0 ? k2[0] : k2[1], 1);
+        const float mine = (b0 ? k2[1] : k2[0]) + recv;
         if (k < len && dg < qpk) sc[dg * stride + k] = mine;
       }
     }
