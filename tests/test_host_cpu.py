@@ -100,3 +100,44 @@ def test_flop_accounting_matches_survey_figures():
     assert abs((flops.forward_flops_per_token(c, 512) + flops.backward_flops_per_token(c, "lora", 512)) / 1e9 - 4.29) < 0.02
     c.adapter_start_layer = 2
     assert abs((flops.forward_flops_per_token(c, 512) + flops.backward_flops_per_token(c, "adapter", 512)) / 1e9 - 4.10) < 0.03
+
+
+def test_trainable_only_checkpoint_roundtrip(tmp_path):
+    """only the PEFT tensors are written (reference-keyed, loadable with strict=False on top of the
+    frozen base), the load checks names / shapes / completeness, and the frozen weights are left untouched."""
+    from dualhyp_b200 import checkpoint
+    cfg = lora.Config.from_name("tiny-llama-test", **LORA)
+    a, b = lora.GPT(cfg), lora.GPT(cfg)
+    lora.mark_only_lora_as_trainable(a)
+    lora.mark_only_lora_as_trainable(b)
+    with torch.no_grad():
+        for n, p in a.named_parameters():
+            if p.requires_grad:
+                p.normal_(0, 0.1)
+    path = tmp_path / "iter-000010.pth"
+    nbytes = checkpoint.save_trainable(a, path)
+    n_train = sum(p.numel() for p in a.parameters() if p.requires_grad)
+    assert nbytes == 4 * n_train and path.stat().st_size < nbytes + 64 * 1024
+    stored = torch.load(str(path), weights_only=False)
+    assert stored["format"] == checkpoint.FORMAT and all("lora_" in k for k in stored["model"])
+    assert set(stored["model"]) == {n for n, p in a.named_parameters() if p.requires_grad}
+    frozen_before = {n: p.clone() for n, p in b.named_parameters() if not p.requires_grad}
+    loaded = checkpoint.load_trainable(b, path)
+    assert len(loaded) == len(stored["model"])
+    for (n, pa), (_, pb) in zip(a.named_parameters(), b.named_parameters()):
+        if pa.requires_grad:
+            assert torch.equal(pa, pb), n
+        else:
+            assert torch.equal(pb, frozen_before[n]), n
+    # the reference's own filter selects the same tensors
+    assert checkpoint.trainable_state(a, lora.lora_filter).keys() == stored["model"].keys()
+    # a checkpoint of another variant is rejected, an incomplete one too
+    ad = adapter.GPT(adapter.Config.from_name("tiny-llama-test", adapter_start_layer=1))
+    adapter.mark_only_adapter_as_trainable(ad)
+    with pytest.raises(KeyError):
+        checkpoint.load_trainable(ad, path)
+    partial = {"model": {k: v for i, (k, v) in enumerate(stored["model"].items()) if i % 2 == 0}}
+    torch.save(partial, str(tmp_path / "partial.pth"))
+    with pytest.raises(KeyError):
+        checkpoint.load_trainable(b, tmp_path / "partial.pth")
+    checkpoint.load_trainable(b, tmp_path / "partial.pth", require_all=False)
