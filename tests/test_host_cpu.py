@@ -141,3 +141,35 @@ def test_trainable_only_checkpoint_roundtrip(tmp_path):
     with pytest.raises(KeyError):
         checkpoint.load_trainable(b, tmp_path / "partial.pth")
     checkpoint.load_trainable(b, tmp_path / "partial.pth", require_all=False)
+
+
+def test_relprompt_mask_token_splice_equals_text_substitution():
+    """splicing mask-token ids == the reference's text replace + re-tokenise (inference/relprompt.py:145-157)
+    for a tokenizer in which every mask token is one id (what add_special_tokens + resize_token_embeddings(3) gives)."""
+    from dualhyp_b200 import relprompt_infer as R
+    vocab = {"<<C>>": 500, "<<M>>": 501, "<<N>>": 502, R.ASR_PLACEHOLDER: 7, R.VSR_PLACEHOLDER: 7}
+    words = "revise asr hyps : x y z ### Audio Mask: {} ### VSR : u v ### Video Mask: {} end".split()
+
+    def encode(text):       # whitespace tokenizer with single-id special tokens
+        out = []
+        for w in text.split():
+            while w:
+                for tok, i in vocab.items():
+                    if w.startswith(tok):
+                        out.append(i)
+                        w = w[len(tok):]
+                        break
+                else:
+                    out.append(10 + (sum(map(ord, w)) % 400))
+                    w = ""
+        return torch.tensor(out)
+
+    template = " ".join(words).format(R.ASR_PLACEHOLDER, R.VSR_PLACEHOLDER)
+    a_pred, v_pred = torch.tensor([0, 2, 2, 1, 0]), torch.tensor([1, 1, 0])
+    assert R.mask_strings(a_pred) == "<<C>><<N>><<N>><<M>><<C>>"
+    via_text = encode(R.fill_prompt_text(template, a_pred, v_pred))
+    ids = encode(template)
+    slots = [i for i, t in enumerate(ids.tolist()) if t == 7]
+    via_ids = R.fill_mask_tokens(ids, a_pred, v_pred, slots[0], slots[1], first_mask_id=500)
+    assert via_ids.tolist() == via_text.tolist()
+    assert via_ids.numel() == ids.numel() - 2 + 5 + 3

@@ -210,6 +210,41 @@ def test_graph_decode_equals_eager_and_is_reusable():
     m.reset_cache()
 
 
+def test_relprompt_inference_glue():
+    """inference/relprompt.py:102-173 on tensors: classifier arg-max (checked against the oracle's classifier), mask
+    tokens spliced into the prompts, batched decode == the same prompts decoded one by one through generate()."""
+    from dualhyp_b200 import relprompt_infer as R
+    m, sd = build("relprompt", whisper_dim=48, raven_dim=32, pool_size=5)
+    m.eval()
+    cfg = tiny_cfg("relprompt")
+    Bn = 3
+    af = synthetic.synth_features(Bn, 93, cfg.whisper_dim, SEED, 71, DEV)
+    vf = synthetic.synth_features(Bn, 47, cfg.raven_dim, SEED, 72, DEV)
+    a_pred, v_pred = R.predict_masks(m, af, vf, audio_frames=[93, 80, 41], visual_frames=[47, 40, 21])
+    ref_a = O.noise_mask_classifier(af.cpu(), sd, "audio_noise_classifier.", 2 * cfg.pool_size)
+    ref_v = O.noise_mask_classifier(vf.cpu(), sd, "visual_noise_classifier.", cfg.pool_size)
+    assert [p.numel() for p in a_pred] == [10, 8, 5] and [p.numel() for p in v_pred] == [10, 8, 5]
+    for b in range(Bn):
+        ra, rv = ref_a[b, : a_pred[b].numel()], ref_v[b, : v_pred[b].numel()]
+        clear_a = (ra.topk(2).values[:, 0] - ra.topk(2).values[:, 1]) > 1e-3
+        clear_v = (rv.topk(2).values[:, 0] - rv.topk(2).values[:, 1]) > 1e-3
+        assert torch.equal(a_pred[b].cpu()[clear_a], ra.argmax(-1)[clear_a])
+        assert torch.equal(v_pred[b].cpu()[clear_v], rv.argmax(-1)[clear_v])
+    prompts = [p.to(DEV) for p in synthetic.synth_prompts(Bn, 500, SEED + 5, prompt_range=(24, 40))]
+    slots = [(5, 17), (3, 20), (8, 9)]
+    first = m.transformer.wte.weight.shape[0] - 3
+    outs, _, _ = R.relprompt_generate(m, prompts, slots, af, vf, max_new_tokens=6, audio_frames=[93, 80, 41],
+                                      visual_frames=[47, 40, 21], first_mask_id=first)
+    filled = [R.fill_mask_tokens(prompts[b], a_pred[b], v_pred[b], slots[b][0], slots[b][1], first) for b in range(Bn)]
+    direct = generate_batch(m, filled, 6)                                     # the same decode, prompts spliced by hand
+    for b in range(Bn):
+        assert filled[b].numel() == prompts[b].numel() - 2 + a_pred[b].numel() + v_pred[b].numel()
+        assert int(filled[b].max()) >= first                                  # mask-token rows of the resized wte are used
+        assert outs[b][: filled[b].numel()].tolist() == filled[b].tolist()
+        assert outs[b].tolist() == direct[b].tolist()
+    m.reset_cache()
+
+
 def test_reference_generate_loop_runs_on_the_model():
     """generate/base.py's loop restated verbatim: model(x, input_pos) -> logits[0, -1] / temperature -> topk(1) ->
     where(< v) -> softmax -> multinomial, one token at a time through the KV cache.  bf16 logits can tie exactly at
