@@ -31,7 +31,7 @@ class GemmArgs(C.Structure):
         ("a_layout", C.c_int32), ("b_layout", C.c_int32), ("a2_layout", C.c_int32), ("b2_layout", C.c_int32),
         ("epilogue", C.c_int32), ("accumulate", C.c_int32),
         ("alpha", C.c_float),
-        ("seq_len", C.c_int32), ("q_per_kv", C.c_int32), ("reserved0", C.c_int32),
+        ("seq_len", C.c_int32), ("q_per_kv", C.c_int32), ("split_k", C.c_int32),
         ("out", C.c_void_p), ("ldo", C.c_int64),
         ("out2", C.c_void_p), ("ldo2", C.c_int64),
         ("aux", C.c_void_p), ("ldaux", C.c_int64),
@@ -52,6 +52,7 @@ SIGNATURES = {
     "dh_sm_count": (_I, []),
     "dh_gemm": (_I, [C.POINTER(GemmArgs), _P]),
     "dh_rmsnorm_fwd": (_I, [_P, _I, _P, _P, _P, _I, _I, _F, _P]),
+    "dh_splitk_resid_rmsnorm": (_I, [_P, _I, _L, _P, _P, _P, _P, _I, _I, _F, _P]),
     "dh_rmsnorm_bwd": (_I, [_P, _I, _P, _P, _P, _P, _P, _P, _I, _I, _P]),
     "dh_embedding_fwd": (_I, [_P, _P, _I, _P, _I, _I, _I, _I, _P]),
     "dh_rope_apply": (_I, [_P, _P, _P, _P, _I, _I, _I, _I, _I, _I, _I, _I, _P]),

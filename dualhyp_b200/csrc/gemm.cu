@@ -34,6 +34,7 @@ struct GemmParams {
   const int* positions;
   const int* m_limit;      // optional device-side row count: tiles at or beyond it are skipped
   int sk_stages;           // skinny kernel: depth of the TMA ring
+  int sk_partial;          // skinny kernel: gridDim.x CTAs per tile each store their K range's product to slice blockIdx.x of out
 };
 
 template <int BN> struct GemmCfg {
@@ -367,11 +368,12 @@ gemm_skinny_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constan
 
   const int warp = __shfl_sync(0xffffffffu, threadIdx.x >> 5, 0);
   const int lane = threadIdx.x & 31;
-  const int S = gridDim.x, split = blockIdx.x, tile = blockIdx.y;      // the cluster spans x: rank == split
+  const int KS = gridDim.x, split = blockIdx.x, tile = blockIdx.y;     // the cluster spans x: rank == split
+  const int S = p.sk_partial ? 1 : KS;          // CTAs whose partial tiles are reduced here (partial mode: none, the consumer sums)
   const int n0 = tile * SK_BN;
   const int nkb1 = (p.K1 + BK - 1) / BK;
   const int nkb = nkb1 + (p.K2 + BK - 1) / BK;
-  const int kb_begin = (int)((long long)nkb * split / S), kb_end = (int)((long long)nkb * (split + 1) / S);
+  const int kb_begin = (int)((long long)nkb * split / KS), kb_end = (int)((long long)nkb * (split + 1) / KS);
 
   if (warp == 0 && lane == 0) {
     tma_prefetch_desc(&tmA);
@@ -465,7 +467,15 @@ gemm_skinny_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constan
         float v[64];
 #pragma unroll
         for (int j = 0; j < 32; ++j) { v[j] = __uint_as_float(r0[j]); v[j + 32] = __uint_as_float(r1[j]); }
-        if (row < p.M) epilogue_chunk<EPI>(p, row, n0 + c * 64, v);
+        if (row < p.M) {
+          if (EPI == DH_EPI_F32 && p.sk_partial) {          // slice `split` of the [KS][M][ldo] partial products
+            GemmParams ps = p;
+            ps.out = reinterpret_cast<float*>(p.out) + (long long)split * p.M * p.ldo;
+            epilogue_chunk<EPI>(ps, row, n0 + c * 64, v);
+          } else {
+            epilogue_chunk<EPI>(p, row, n0 + c * 64, v);
+          }
+        }
       }
     } else {
       // This CTA finishes the (row, 64-column) units u = split, split + S, ... of the tile.  Phase 1: all 128 epilogue
@@ -957,7 +967,7 @@ static GemmParams make_params(const dh_gemm_args* a) {
   p.rope_sin = reinterpret_cast<const bf16*>(a->rope_sin);
   p.positions = a->positions;
   p.m_limit = a->m_limit;
-  p.sk_stages = 0;
+  p.sk_stages = 0; p.sk_partial = 0;
   return p;
 }
 
@@ -1096,14 +1106,22 @@ static int launch_gemm_skinny(const dh_gemm_args* a, cudaStream_t stream) {
   if (stages > SK_MAX_STAGES) stages = SK_MAX_STAGES;
   const int per_cta = (nkb + S - 1) / S;
   if (stages > per_cta) stages = per_cta;
+  if (a->split_k > 1) {       // partial products for a consumer that sums them: no cluster, any split count with >= 1 k-block each
+    S = a->split_k < nkb ? a->split_k : nkb;
+    p.sk_partial = 1;
+    stages = SK_RING_BYTES / stage_bytes;
+    if (stages > SK_MAX_STAGES) stages = SK_MAX_STAGES;
+    const int pc = (nkb + S - 1) / S;
+    if (stages > pc) stages = pc;
+  }
   static int env_s = -2, env_stages = -2;      // developer knobs for A/B runs: DH_SKINNY_S, DH_SKINNY_STAGES
   if (env_s == -2) { const char* e = getenv("DH_SKINNY_S"); env_s = e ? atoi(e) : -1; }
   if (env_stages == -2) { const char* e = getenv("DH_SKINNY_STAGES"); env_stages = e ? atoi(e) : -1; }
-  if (env_s > 0 && nkb / env_s >= 1) S = env_s;
+  if (env_s > 0 && nkb / env_s >= 1 && !p.sk_partial) S = env_s;
   if (env_stages > 0 && env_stages <= SK_MAX_STAGES && env_stages * stage_bytes <= SK_RING_BYTES) stages = env_stages;
   // the fp32 partial tile and this CTA's reduced units (S > 1) re-use the ring
   const size_t park = (size_t)a->M * SK_PAD * sizeof(float) + (size_t)((a->M * 2 + S - 1) / S) * 64 * sizeof(float);
-  while (S > 1 && (size_t)stages * stage_bytes < park) ++stages;
+  while (S > 1 && !p.sk_partial && (size_t)stages * stage_bytes < park) ++stages;
   p.sk_stages = stages;
   cudaLaunchConfig_t cfg = {};
   cfg.gridDim = dim3(S, tiles);
@@ -1112,7 +1130,7 @@ static int launch_gemm_skinny(const dh_gemm_args* a, cudaStream_t stream) {
   cfg.stream = stream;
   cudaLaunchAttribute attr[1];
   attr[0].id = cudaLaunchAttributeClusterDimension;
-  attr[0].val.clusterDim.x = S;
+  attr[0].val.clusterDim.x = p.sk_partial ? 1 : S;
   attr[0].val.clusterDim.y = 1;
   attr[0].val.clusterDim.z = 1;
   cfg.attrs = attr;
@@ -1157,6 +1175,10 @@ extern "C" int dh_gemm(const dh_gemm_args* a, void* stream_) {
   DH_CHECK((a->lda % 8) == 0 && (a->ldb % 8) == 0, "dh_gemm: leading dimensions must be multiples of 8 elements");
   DH_CHECK(((uintptr_t)a->A & 15) == 0 && ((uintptr_t)a->B & 15) == 0, "dh_gemm: operands must be 16-byte aligned");
   if (a->K2 > 0) DH_CHECK(a->A2 && a->B2 && (a->lda2 % 8) == 0 && (a->ldb2 % 8) == 0, "dh_gemm: bad second source");
+  if (a->split_k > 1)
+    DH_CHECK(a->M <= BM && a->N % 128 == 0 && a->a_layout == 0 && a->b_layout == 0 && (a->K2 == 0 || (a->a2_layout == 0 && a->b2_layout == 0)) &&
+                 a->epilogue == DH_EPI_F32 && !a->accumulate && !a->m_limit,
+             "dh_gemm: split_k needs M <= 128, N %% 128 == 0, K-major operands and the plain DH_EPI_F32 epilogue");
   switch (a->epilogue) {
     case DH_EPI_BF16: return dispatch_bn<DH_EPI_BF16>(a, stream);
     case DH_EPI_F32: return dispatch_bn<DH_EPI_F32>(a, stream);

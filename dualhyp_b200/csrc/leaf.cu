@@ -72,6 +72,52 @@ __global__ void rmsnorm_fwd_kernel(const XT* __restrict__ x, const float* __rest
   if (rstd && threadIdx.x == 0) rstd[row] = r;
 }
 
+// Decode: consumer of a split-K GEMM (dh_gemm with split_k > 1 leaves `splits` fp32 partial products [splits][M][C]):
+//   x_out = resid + bf16(sum_s partial[s])      (the residual epilogue of the GEMM, ger/model.py:185-186)
+//   y     = rmsnorm(x_out) * w  in bf16         (the next norm, ger/rmsnorm.py:17-21)
+// One row per block; the partials are summed in split order (deterministic).
+__global__ void splitk_resid_rmsnorm_kernel(const float* __restrict__ partial, int splits, long long split_stride,
+                                            const float* __restrict__ resid, const float* __restrict__ w, float* __restrict__ x_out,
+                                            bf16* __restrict__ y, int C, float eps) {
+  __shared__ float red[32];
+  const long long row = blockIdx.x;
+  const int c0 = threadIdx.x * 8;
+  float acc[8], v[8], g[8];
+#pragma unroll
+  for (int i = 0; i < 8; ++i) acc[i] = 0.f;
+  const float* prow = partial + row * C + c0;
+  for (int s0 = 0; s0 < splits; s0 += 4) {          // 4 splits (8 independent 16-byte loads) in flight per thread
+    float t[4][8];
+#pragma unroll
+    for (int u = 0; u < 4; ++u)
+      if (s0 + u < splits) {
+        const float4 a = __ldcg(reinterpret_cast<const float4*>(prow + (s0 + u) * split_stride));
+        const float4 b = __ldcg(reinterpret_cast<const float4*>(prow + (s0 + u) * split_stride) + 1);
+        t[u][0] = a.x; t[u][1] = a.y; t[u][2] = a.z; t[u][3] = a.w; t[u][4] = b.x; t[u][5] = b.y; t[u][6] = b.z; t[u][7] = b.w;
+      }
+#pragma unroll
+    for (int u = 0; u < 4; ++u)
+      if (s0 + u < splits) {
+#pragma unroll
+        for (int i = 0; i < 8; ++i) acc[i] += t[u][i];
+      }
+  }
+  load8(resid + row * C + c0, v);
+  load8(w + c0, g);
+  float ss = 0.f;
+#pragma unroll
+  for (int i = 0; i < 8; ++i) {
+    v[i] += __bfloat162float(__float2bfloat16_rn(acc[i]));
+    ss += v[i] * v[i];
+  }
+  store8(x_out + row * C + c0, v);
+  ss = block_sum(ss, red);
+  const float r = rsqrtf(ss / (float)C + eps);
+#pragma unroll
+  for (int i = 0; i < 8; ++i) v[i] = g[i] * (v[i] * r);
+  store8(y + row * C + c0, v);
+}
+
 // dx = dres + rstd * (w*dy - xhat * mean(w*dy*xhat)),  xhat = x*rstd
 template <typename XT>
 __global__ void rmsnorm_bwd_kernel(const XT* __restrict__ x, const float* __restrict__ w, const float* __restrict__ rstd,
@@ -481,6 +527,16 @@ extern "C" int dh_rmsnorm_fwd(const void* x, int x_dtype, const float* weight, v
   cudaStream_t s = (cudaStream_t)stream;
   if (x_dtype == 0) rmsnorm_fwd_kernel<float><<<M, C / 8, 0, s>>>((const float*)x, weight, (bf16*)y, rstd, C, eps);
   else rmsnorm_fwd_kernel<bf16><<<M, C / 8, 0, s>>>((const bf16*)x, weight, (bf16*)y, rstd, C, eps);
+  DH_CUDA(cudaGetLastError());
+  return 0;
+}
+
+extern "C" int dh_splitk_resid_rmsnorm(const float* partial, int splits, long long split_stride, const float* resid, const float* weight,
+                                       float* x_out, void* y, int M, int C, float eps, void* stream) {
+  DH_CHECK(partial && resid && weight && x_out && y && M > 0 && splits > 0, "dh_splitk_resid_rmsnorm: bad argument");
+  DH_CHECK(C % 256 == 0 && C <= 8192, "dh_splitk_resid_rmsnorm: C=%d must be a multiple of 256 and <= 8192", C);
+  DH_CHECK(split_stride >= (long long)M * C && split_stride % 4 == 0, "dh_splitk_resid_rmsnorm: bad split stride");
+  splitk_resid_rmsnorm_kernel<<<M, C / 8, 0, (cudaStream_t)stream>>>(partial, splits, split_stride, resid, weight, x_out, (bf16*)y, C, eps);
   DH_CUDA(cudaGetLastError());
   return 0;
 }

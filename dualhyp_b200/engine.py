@@ -455,9 +455,15 @@ class DecoderEngine:
         ops.embedding_fwd(tokens.contiguous(), self.wte, x)
         if pkv_all is None:
             pkv_all = self._project_prefixes(packed, "dec_pkv_all")
+        hidden = self._buf("dec_hidden", (n_seq, C), bf)
+        # The two residual GEMMs (attention proj, mlp proj; N = C gives only C / 128 tiles) run split-K over all SMs and
+        # leave fp32 partial products; the norm that follows sums them, adds the residual and normalises in one launch.
+        sk_ok = n_seq <= 128 and C % 128 == 0
+        s_proj, s_mlp = (ops.decode_split_k(C, C), ops.decode_split_k(C, I)) if sk_ok else (1, 1)
+        ws = self._buf("dec_splitk", (max(s_proj, s_mlp), n_seq, C), f32) if (s_proj > 1 or s_mlp > 1) else None
+        ops.rmsnorm_fwd(x, self.layers[0]["norm1"], n, None, s.norm_eps)
         for i, lw in enumerate(self.layers):
             pk = packed.get(i, {})
-            ops.rmsnorm_fwd(x, lw["norm1"], n, None, s.norm_eps)
             if "qkv_a" in pk:
                 a_s = self._buf("dec_as", (n_seq, LORA_PAD), bf)
                 ops.gemm(n, pk["qkv_a"], a_s)
@@ -473,15 +479,24 @@ class DecoderEngine:
                 gate = pk["gate"]
             ops.attention_decode(qkv, self.cache_k[i], self.cache_v[i], lens, y, G, qpk, prefix_kv, gate,
                                  s.adapter_prompt_length if prefix_kv is not None else 0)
+            a2 = b2 = None
             if "proj_a" in pk:
-                ap_s = self._buf("dec_aps", (n_seq, LORA_PAD), bf)
-                ops.gemm(y, pk["proj_a"], ap_s)
-                ops.gemm(y, lw["wproj"], x2, A2=ap_s, B2=pk["proj_b"], epilogue=ops.EPI_RESID_F32, aux=x)
+                a2 = self._buf("dec_aps", (n_seq, LORA_PAD), bf)
+                ops.gemm(y, pk["proj_a"], a2)
+                b2 = pk["proj_b"]
+            if s_proj > 1:
+                ops.gemm(y, lw["wproj"], ws[:s_proj], A2=a2, B2=b2, epilogue=ops.EPI_F32, split_k=s_proj)
+                ops.splitk_resid_rmsnorm(ws[:s_proj], x, lw["norm2"], x2, n, s.norm_eps)
             else:
-                ops.gemm(y, lw["wproj"], x2, epilogue=ops.EPI_RESID_F32, aux=x)
-            ops.rmsnorm_fwd(x2, lw["norm2"], n, None, s.norm_eps)
+                ops.gemm(y, lw["wproj"], x2, A2=a2, B2=b2, epilogue=ops.EPI_RESID_F32, aux=x)
+                ops.rmsnorm_fwd(x2, lw["norm2"], n, None, s.norm_eps)
             ops.gemm(n, lw["w12"], None, epilogue=ops.EPI_SWIGLU, out2=act)
-            ops.gemm(act, lw["wmlp"], x, epilogue=ops.EPI_RESID_F32, aux=x2)
-        hidden = self._buf("dec_hidden", (n_seq, C), bf)
-        ops.rmsnorm_fwd(x, self.ln_f, hidden, None, s.norm_eps)
+            last = i + 1 == len(self.layers)
+            w_next, n_next = (self.ln_f, hidden) if last else (self.layers[i + 1]["norm1"], n)
+            if s_mlp > 1:
+                ops.gemm(act, lw["wmlp"], ws[:s_mlp], epilogue=ops.EPI_F32, split_k=s_mlp)
+                ops.splitk_resid_rmsnorm(ws[:s_mlp], x2, w_next, x, n_next, s.norm_eps)
+            else:
+                ops.gemm(act, lw["wmlp"], x, epilogue=ops.EPI_RESID_F32, aux=x2)
+                ops.rmsnorm_fwd(x, w_next, n_next, None, s.norm_eps)
         return hidden

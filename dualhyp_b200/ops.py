@@ -94,8 +94,9 @@ def gemm(A: Tensor, B: Tensor, out: Optional[Tensor], *, epilogue: int = EPI_BF1
          out2: Optional[Tensor] = None, aux: Optional[Tensor] = None, alpha: float = 1.0, accumulate: bool = False,
          col_scale: Optional[Tensor] = None, col_bias: Optional[Tensor] = None, rope_cos: Optional[Tensor] = None,
          rope_sin: Optional[Tensor] = None, positions: Optional[Tensor] = None, seq_len: int = 0, q_per_kv: int = 0,
-         m_limit: Optional[Tensor] = None) -> None:
-    """D = A op(B) (+ A2 op(B2)) with a fused epilogue; see `dh_gemm` in include/dualhyp.h."""
+         m_limit: Optional[Tensor] = None, split_k: int = 0) -> None:
+    """D = A op(B) (+ A2 op(B2)) with a fused epilogue; see `dh_gemm` in include/dualhyp.h.  split_k > 1 (decode, M <= 128,
+    EPI_F32): `out` is fp32 [split_k, M, N] of partial products for `splitk_resid_rmsnorm` to sum."""
     _dev(A)
     assert A.dtype == torch.bfloat16 and B.dtype == torch.bfloat16
     a = GemmArgs()
@@ -120,7 +121,10 @@ def gemm(A: Tensor, B: Tensor, out: Optional[Tensor], *, epilogue: int = EPI_BF1
         a.a2_layout, a.b2_layout = a2_layout, b2_layout
     a.epilogue, a.accumulate, a.alpha = epilogue, int(accumulate), alpha
     a.seq_len, a.q_per_kv = seq_len, q_per_kv
-    if out is not None:
+    if split_k > 1:
+        assert out is not None and out.dim() == 3 and out.shape[0] == split_k and out.is_contiguous() and out.dtype == torch.float32
+        a.split_k, a.out, a.ldo = split_k, out.data_ptr(), out.shape[2]
+    elif out is not None:
         a.out, a.ldo = out.data_ptr(), _rowmajor(out, "out")
     if out2 is not None:
         a.out2, a.ldo2 = out2.data_ptr(), _rowmajor(out2, "out2")
@@ -142,6 +146,27 @@ def rmsnorm_fwd(x: Tensor, weight: Tensor, y: Tensor, rstd: Optional[Tensor], ep
     check(_lib.load().dh_rmsnorm_fwd(x.data_ptr(), xd, weight.data_ptr(), y.data_ptr(), _ptr(rstd), M, Cdim, eps, _stream()),
           "dh_rmsnorm_fwd")
     _count()
+
+
+@_profiled("splitk_resid_rmsnorm")
+def splitk_resid_rmsnorm(partial: Tensor, resid: Tensor, weight: Tensor, x_out: Tensor, y: Tensor, eps: float) -> None:
+    """x_out = resid + bf16(sum of the split-K slices); y = rmsnorm(x_out) * weight (bf16)."""
+    _dev(partial)
+    S, M, Cdim = partial.shape
+    assert partial.is_contiguous() and partial.dtype == torch.float32 and resid.dtype == torch.float32 and x_out.dtype == torch.float32
+    assert resid.is_contiguous() and x_out.is_contiguous() and y.is_contiguous() and y.dtype == torch.bfloat16
+    assert resid.shape == (M, Cdim) and x_out.shape == (M, Cdim) and y.shape == (M, Cdim) and weight.dtype == torch.float32
+    check(_lib.load().dh_splitk_resid_rmsnorm(partial.data_ptr(), S, M * Cdim, resid.data_ptr(), weight.data_ptr(), x_out.data_ptr(),
+                                              y.data_ptr(), M, Cdim, eps, _stream()), "dh_splitk_resid_rmsnorm")
+    _count()
+
+
+def decode_split_k(N: int, K: int) -> int:
+    """Split count of a decode GEMM whose consumer sums the slices: every SM gets one CTA (N / 128 tiles x splits <= SM count),
+    at least two 64-wide k-blocks per CTA."""
+    sms = int(_lib.load().dh_sm_count()) or 148
+    tiles = max(1, N // 128)
+    return max(1, min(sms // tiles, (K // 64) // 2, 16))
 
 
 @_profiled("rmsnorm_bwd")

@@ -65,7 +65,9 @@ typedef struct dh_gemm_args {
   float alpha;
   int32_t seq_len;                   /* DH_EPI_QKV_ROPE: row -> position = row % seq_len when positions == NULL */
   int32_t q_per_kv;                  /* DH_EPI_QKV_ROPE: q heads per kv head (group = q_per_kv + 2 slots of 64)   */
-  int32_t reserved0;
+  int32_t split_k;                   /* > 1 (needs M <= 128, K-major operands, DH_EPI_F32, no accumulate): `out` is fp32
+                                        [split_k][M][ldo]; CTA group s multiplies K range s of split_k into slice s and NO reduction
+                                        is done -- the consumer sums the slices (dh_splitk_resid_rmsnorm).  0 / 1: off. */
   void* out;  int64_t ldo;
   void* out2; int64_t ldo2;
   const void* aux; int64_t ldaux;
@@ -87,6 +89,12 @@ int dh_gemm(const dh_gemm_args* args, void* stream);
  * (may be NULL).  C % 8 == 0, C <= 8192. */
 int dh_rmsnorm_fwd(const void* x, int x_dtype, const float* weight, void* y, float* rstd, int M, int C, float eps,
                    void* stream);
+/* Decode: consumer of a split-K dh_gemm (split_k > 1).  partial f32 [splits][M][C] (slice pitch split_stride elements):
+ *   x_out f32 [M,C] = resid + bf16(sum_s partial[s])   -- the residual add of ger/model.py:185-186, slices summed in order;
+ *   y bf16 [M,C]    = rmsnorm(x_out) * weight          -- the norm that follows it (ger/rmsnorm.py:17-21).
+ * x_out may alias resid. */
+int dh_splitk_resid_rmsnorm(const float* partial, int splits, long long split_stride, const float* resid, const float* weight,
+                            float* x_out, void* y, int M, int C, float eps, void* stream);
 /* Backward of the above w.r.t. x (weights are frozen on this path).  dy bf16 [M,C].
  * dx_out f32 [M,C] = (dres ? dres : 0) + d(rmsnorm)/dx ; dx_bf16 (optional) = bf16(dx_out).
  * dres may alias dx_out. */

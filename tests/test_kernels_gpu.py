@@ -169,6 +169,34 @@ def test_gemm_skinny_decode_shapes(M):
     assert rel(qkv.cpu().view(M, G, qpk + 2, 64), want) < 6e-3, report("splitk rope", qkv.cpu().view(M, G, qpk + 2, 64), want)
 
 
+@pytest.mark.parametrize("M,S", [(1, 9), (64, 9), (64, 3), (100, 16), (128, 8)])
+def test_gemm_split_k_partials_and_fused_consumer(M, S):
+    """dh_gemm split_k: slice s holds the product over K range s (their sum is the GEMM); dh_splitk_resid_rmsnorm sums
+    the slices in order, adds the residual (bf16-rounded product, like DH_EPI_RESID_F32) and applies the next RMSNorm --
+    bit-identical to the unsplit residual GEMM followed by dh_rmsnorm_fwd is not required (other summation order), so
+    the check is against fp32 math; run-to-run it must be bit-identical."""
+    C, I = 2048, 5632
+    a, W = rnd((M, I), 321), rnd((C, I), 322, bound=1 / 64)
+    a2, b2 = rnd((M, 64), 323, bound=0.1), rnd((C, 64), 324, bound=0.1)
+    res, g = rnd((M, C), 325, dtype=torch.float32), rnd((C,), 326, dtype=torch.float32) + 1.5
+    ws = torch.full((S, M, C), float("nan"), device=DEV, dtype=torch.float32)
+    ops.gemm(a, W, ws, A2=a2, B2=b2, epilogue=ops.EPI_F32, split_k=S)
+    x1 = torch.empty((M, C), device=DEV, dtype=torch.float32)
+    n1 = torch.empty((M, C), device=DEV, dtype=torch.bfloat16)
+    ops.splitk_resid_rmsnorm(ws, res, g, x1, n1, 1e-5)
+    x2, n2 = torch.empty_like(x1), torch.empty_like(n1)
+    ops.gemm(a, W, ws, A2=a2, B2=b2, epilogue=ops.EPI_F32, split_k=S)
+    ops.splitk_resid_rmsnorm(ws, res, g, x2, n2, 1e-5)
+    torch.cuda.synchronize()
+    prod = a.float() @ W.float().t() + a2.float() @ b2.float().t()
+    assert rel(ws.sum(0), prod) < 1e-3, report("split-k slices", ws.sum(0), prod)
+    xr = res + prod.bfloat16().float()
+    nr = xr * torch.rsqrt((xr * xr).mean(-1, keepdim=True) + 1e-5) * g
+    assert rel(x1, xr) < 1e-3, report("split-k resid", x1, xr)
+    assert rel(n1, nr) < 4e-3, report("split-k norm", n1, nr)
+    assert torch.equal(x1, x2) and torch.equal(n1, n2)
+
+
 def _interleave(w1, w2):
     I = w1.shape[0]
     return torch.stack((w1.view(I // 32, 32, -1), w2.view(I // 32, 32, -1)), dim=1).reshape(2 * I, -1)
