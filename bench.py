@@ -47,7 +47,7 @@ def parse_args():
     ap.add_argument("--steps", type=int, default=10)
     ap.add_argument("--warmup", type=int, default=3)
     ap.add_argument("--impl", default="native", choices=["native", "reference"])
-    ap.add_argument("--workload", default="adapter", choices=["adapter", "lora", "decode"])
+    ap.add_argument("--workload", default="adapter", choices=["adapter", "lora", "relprompt", "decode"])
     ap.add_argument("--batch", type=int, default=0, help="prompts per GPU (default 16; lora: 64 / gpus)")
     ap.add_argument("--seq", type=int, default=SEQ_LEN)
     ap.add_argument("--no-cpu-baseline", action="store_true")
@@ -58,10 +58,18 @@ def parse_args():
     return ap.parse_args()
 
 
+def metric_name(args) -> str:
+    kind = {"adapter": "adapter fine-tune step", "lora": "LoRA r=8 fine-tune step", "relprompt": "RelPrompt fine-tune step"}.get(args.workload)
+    return METRIC if args.workload == "adapter" else f"DualHyp train tokens/s ({kind}, TinyLlama-1.1B, 5+5 N-best)"
+
+
 def workload_name(args) -> str:
     if args.workload == "decode":
         return ("DualHyp greedy generation with KV cache, TinyLlama-1.1B adapter random-init, synthetic prompts U[330,480] tokens, "
                 f"{args.new_tokens} new tokens, bf16, utterances sharded across GPUs")
+    if args.workload == "relprompt":
+        return ("RelPrompt fine-tune step: reliability predictors on synthetic audio [B,500,1280] / visual [B,250,1024] feature frames + "
+                "LoRA (r=16) TinyLlama-1.1B forward+backward over prompts with mask tokens, seq 512, bf16")
     if args.workload == "adapter":
         return "DualHyp adapter fine-tune step, TinyLlama-1.1B random-init, 5 ASR + 5 VSR synthetic hyps per prompt, seq 512, bf16"
     return "DualHyp LoRA (r=8) fine-tune step, TinyLlama-1.1B random-init, global batch 64 x seq 512, bf16, data parallel"
@@ -70,6 +78,8 @@ def workload_name(args) -> str:
 def per_gpu_batch(args, world: int) -> int:
     if args.batch > 0:
         return args.batch
+    if args.workload == "relprompt":
+        return 4                                   # B = 4 per GPU
     return PER_GPU_BATCH if args.workload == "adapter" else max(1, 64 // world)
 
 
@@ -132,16 +142,32 @@ def cpu_step_tokens_per_s(workload: str, seq: int, steps: int, warmup: int):
     from oracle import oracle as O
     cores = os.cpu_count() or 1
     torch.set_num_threads(cores)
+    rel = None
     if workload == "adapter":
         cfg = O.OracleConfig(variant="adapter")
+    elif workload == "relprompt":
+        cfg = O.OracleConfig(variant="relprompt", r=16, alpha=32, to_query=True, to_key=True, to_value=True, to_projection=True)
     else:
         cfg = O.OracleConfig(variant="lora", r=8, alpha=16, to_query=True, to_key=True, to_value=True, to_projection=True)
-    sd = synthetic.synth_state_dict(cfg, cfg.variant, 1337)
+    sd = synthetic.synth_state_dict(cfg, cfg.variant, 1337, extra_wte_rows=3 if workload == "relprompt" else 0)
     idx, labels = synthetic.synth_batch(1, seq, 32000, 1337, prompt_range=(int(seq * 0.65), int(seq * 0.93)))
+    if workload == "relprompt":
+        rel = (synthetic.synth_features(1, 500, 1280, 1337, 301), synthetic.synth_features(1, 250, 1024, 1337, 302),
+               synthetic.hash_ints((1, 25), 1337, 303, 0, 3), synthetic.hash_ints((1, 25), 1337, 304, 0, 3))
+        keys = O.trainable_keys(sd, cfg)
+
+    def one_step():
+        if rel is None:
+            O.loss_and_grads(sd, cfg, idx, labels, "train")
+            return
+        work = {k: (v.detach().clone().requires_grad_(True) if k in keys else v.detach()) for k, v in sd.items()}
+        loss = O.relprompt_loss(work, cfg, idx, labels, *rel)[0]
+        torch.autograd.grad(loss, [work[k] for k in keys])
+
     times = []
     for i in range(warmup + steps):
         t0 = time.perf_counter()
-        O.loss_and_grads(sd, cfg, idx, labels, "train")
+        one_step()
         dt = time.perf_counter() - t0
         if i >= warmup:
             times.append(dt)
@@ -296,7 +322,7 @@ def run_reference_arm(args):
         print(json.dumps(line), flush=True)
         return
     tps, ms, cores, sample = cpu_step_tokens_per_s(args.workload, args.seq, args.steps, args.warmup)
-    line = {"impl": "reference", "metric": METRIC, "value": round(tps, 2), "unit": UNIT, "n_gpus": args.gpus, "steps": args.steps,
+    line = {"impl": "reference", "metric": metric_name(args), "value": round(tps, 2), "unit": UNIT, "n_gpus": args.gpus, "steps": args.steps,
             "warmup": args.warmup, "ms_per_step": round(ms, 2), "higher_is_better": True, "scaling": "weak", "vs_baseline": None,
             "dtype": "f32", "data": "synthetic", "config": {"workload": workload_name(args), "seq_len": args.seq, "prompts_per_step": 1},
             "cpu_baseline": {"value": round(tps, 2), "unit": UNIT, "cores": cores, "kind": "port", "sample": sample},
@@ -316,6 +342,14 @@ def build_model(workload: str, device):
         model = adapter.GPT(cfg)
         model.load_state_dict(synthetic.synth_state_dict(cfg, "adapter", 1337), strict=True)
         adapter.mark_only_adapter_as_trainable(model)
+    elif workload == "relprompt":
+        from dualhyp_b200.ger import relprompt
+        cfg = relprompt.Config.from_name("tiny-llama-1.1b", r=16, alpha=32, to_query=True, to_key=True, to_value=True, to_projection=True)
+        model = relprompt.GPT(cfg)
+        model.resize_token_embeddings(3)           # <<C>> <<M>> <<N>> (finetune/relprompt.py:168)
+        model.load_state_dict(synthetic.synth_state_dict(cfg, "relprompt", 1337, extra_wte_rows=3), strict=True)
+        relprompt.mark_only_lora_as_trainable(model)
+        model.eval()                               # classifier dropout off (the kernel does not apply it)
     else:
         cfg = lora.Config.from_name("tiny-llama-1.1b", **LORA)
         model = lora.GPT(cfg)
@@ -351,12 +385,31 @@ def run_native(args):
     idx_h, labels_h = idx_h.pin_memory(), labels_h.pin_memory()
     idx_d, labels_d = idx_h.to(dev), labels_h.to(dev)
 
+    rel = None
+    if args.workload == "relprompt":
+        import torch.nn.functional as F
+        rel = dict(af=synthetic.synth_features(B, 500, 1280, 1337 + rank, 301, dev), vf=synthetic.synth_features(B, 250, 1024, 1337 + rank, 302, dev),
+                   at=synthetic.hash_ints((B, 25), 1337 + rank, 303, 0, 3).to(dev), vt=synthetic.hash_ints((B, 25), 1337 + rank, 304, 0, 3).to(dev))
+        # mask tokens inside the prompt span (ids 32000..32002), as the RelPrompt template places them
+        idx_h[:, 40:65] = 32000 + synthetic.hash_ints((B, 25), 1337 + rank, 305, 0, 3)
+        idx_h[:, 200:225] = 32000 + synthetic.hash_ints((B, 25), 1337 + rank, 306, 0, 3)
+        idx_d = idx_h.to(dev)
+
+    def mask_loss():
+        """finetune/relprompt.py:356-387: CE(audio) + CE(visual) over the chunk labels, logits trimmed to the label length."""
+        al, vl = model.audio_noise_classifier(rel["af"]), model.visual_noise_classifier(rel["vf"])
+        na, nv = min(al.size(1), rel["at"].size(1)), min(vl.size(1), rel["vt"].size(1))
+        return F.cross_entropy(al[:, :na].reshape(-1, 3), rel["at"][:, :na].reshape(-1)) + \
+            F.cross_entropy(vl[:, :nv].reshape(-1, 3), rel["vt"][:, :nv].reshape(-1))
+
     def step(idx, labels, sync=True):
         """The driver's micro-step (finetune/ger.py:278-292) with accumulation 1.  sync=False skips the gradient
         all-reduce: the instrumented roofline pass runs on rank 0 alone and must not enter a collective."""
         logits = model(idx, lm_head_chunk_size=128)
         logits[-1] = logits[-1][..., :-1, :]
         loss = chunked_cross_entropy(logits, labels[..., 1:])
+        if rel is not None:
+            loss = loss + 0.02 * mask_loss()
         loss.backward()
         if sync:
             bucket.allreduce()
@@ -404,8 +457,8 @@ def run_native(args):
     ms_e2e = timed(e2e_step, args.steps)
     e2e_value = tokens / (ms_e2e / 1e3)
 
-    line = {"metric": METRIC, "value": round(value, 1), "unit": UNIT, "n_gpus": world, "steps": args.steps, "warmup": max(args.warmup, 3),
-            "ms_per_step": round(ms_total / args.steps, 3), "higher_is_better": True, "scaling": "weak" if args.workload == "adapter" else "strong",
+    line = {"metric": metric_name(args), "value": round(value, 1), "unit": UNIT, "n_gpus": world, "steps": args.steps, "warmup": max(args.warmup, 3),
+            "ms_per_step": round(ms_total / args.steps, 3), "higher_is_better": True, "scaling": "strong" if args.workload == "lora" else "weak",
             "vs_baseline": None, "dtype": "bf16", "data": "synthetic",
             "config": {"workload": workload_name(args), "model": "TinyLlama-1.1B (random init)", "prompts_per_gpu": B, "seq_len": T,
                        "global_batch": world * B, "parallelism": f"dp{world}", "optimizer": "fused AdamW on the flat PEFT bucket",

@@ -33,6 +33,8 @@ struct GemmParams {
   const bf16* rope_sin;
   const int* positions;
   const int* m_limit;      // optional device-side row count: tiles at or beyond it are skipped
+  int splits;              // gemm_kernel: K split into `splits` ranges, range s -> output slice s (fp32 partial products)
+  long long split_stride;  // elements between output slices
   int sk_stages;           // skinny kernel: depth of the TMA ring
   int sk_partial;          // skinny kernel: gridDim.x CTAs per tile each store their K range's product to slice blockIdx.x of out
 };
@@ -202,7 +204,8 @@ gemm_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant__ CUt
   const int lane = threadIdx.x & 31;
   int tiles_m = p.tiles_m;
   if (p.m_limit) { const int t = (__ldg(p.m_limit) + BM - 1) / BM; tiles_m = t < tiles_m ? t : tiles_m; }
-  const int num_tiles = tiles_m * p.tiles_n;
+  const int real_tiles = tiles_m * p.tiles_n;
+  const int num_tiles = real_tiles * p.splits;   // virtual tiles: (output tile, K range); range s writes output slice s
   const int nkb1 = (p.K1 + BK - 1) / BK;   // a ragged K tail is zero-filled by TMA
   const int nkb = nkb1 + (p.K2 + BK - 1) / BK;
 
@@ -228,10 +231,12 @@ gemm_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant__ CUt
   if (warp == 0 && lane == 0) {
     // ===================== TMA producer =====================
     uint32_t it = 0;
-    for (int tile = blockIdx.x; tile < num_tiles; tile += gridDim.x) {
+    for (int vt = blockIdx.x; vt < num_tiles; vt += gridDim.x) {
+      const int tile = vt % real_tiles, split = vt / real_tiles;
       const int m0 = (tile % tiles_m) * BM;
       const int n0 = (tile / tiles_m) * BN;
-      for (int kb = 0; kb < nkb; ++kb, ++it) {
+      const int kb0 = (int)((long long)nkb * split / p.splits), kb1 = (int)((long long)nkb * (split + 1) / p.splits);
+      for (int kb = kb0; kb < kb1; ++kb, ++it) {
         const int s = it % STAGES;
         mbar_wait(&empty_bar[s], ((it / STAGES) & 1) ^ 1);
         uint8_t* sa = smem + s * Cfg::STAGE_BYTES;
@@ -258,12 +263,14 @@ gemm_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant__ CUt
   } else if (warp == 1) {
     // ===================== MMA issuer: the whole warp walks the loop (uniform operands), one elected lane issues =====================
     uint32_t it = 0, tcount = 0;
-    for (int tile = blockIdx.x; tile < num_tiles; tile += gridDim.x, ++tcount) {
+    for (int vt = blockIdx.x; vt < num_tiles; vt += gridDim.x, ++tcount) {
+      const int split = vt / real_tiles;
+      const int kb0 = (int)((long long)nkb * split / p.splits), kb1 = (int)((long long)nkb * (split + 1) / p.splits);
       const int acc = tcount & 1;
       mbar_wait(&tempty_bar[acc], ((tcount >> 1) & 1) ^ 1);
       tc_fence_after();
       const uint32_t d_tmem = tmem_base + acc * BN;
-      for (int kb = 0; kb < nkb; ++kb, ++it) {
+      for (int kb = kb0; kb < kb1; ++kb, ++it) {
         const int s = it % STAGES;
         mbar_wait(&full_bar[s], (it / STAGES) & 1);
         tc_fence_after();
@@ -280,10 +287,10 @@ gemm_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant__ CUt
             // 8-row atoms of 1024 B; 64-wide MN groups are 8 KB apart (LBO), 8-row atoms 1 KB apart (SBO).
             const uint64_t da = a_mn ? umma_desc_sw128(sa + k * 2048, 8192, 1024) : umma_desc_sw128(sa + k * 32, 16, 1024);
             const uint64_t db = b_mn ? umma_desc_sw128(sb + k * 2048, 8192, 1024) : umma_desc_sw128(sb + k * 32, 16, 1024);
-            tc_mma_ss(d_tmem, da, db, idesc, (kb | k) != 0);
+            tc_mma_ss(d_tmem, da, db, idesc, ((kb - kb0) | k) != 0);
           }
           tc_commit(&empty_bar[s]);   // frees the smem slot when these MMAs have drained
-          if (kb == nkb - 1) tc_commit(&tfull_bar[acc]);   // accumulator complete
+          if (kb == kb1 - 1) tc_commit(&tfull_bar[acc]);   // accumulator complete
         }
         __syncwarp();
       }
@@ -292,10 +299,13 @@ gemm_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant__ CUt
     // ===================== epilogue =====================
     const int q = warp & 3;
     uint32_t tcount = 0;
-    for (int tile = blockIdx.x; tile < num_tiles; tile += gridDim.x, ++tcount) {
+    for (int vt = blockIdx.x; vt < num_tiles; vt += gridDim.x, ++tcount) {
+      const int tile = vt % real_tiles, split = vt / real_tiles;
       const int acc = tcount & 1;
       const int m0 = (tile % tiles_m) * BM;
       const int n0 = (tile / tiles_m) * BN;
+      GemmParams ps = p;
+      if (EPI == DH_EPI_F32 && p.splits > 1) ps.out = reinterpret_cast<float*>(p.out) + (long long)split * p.split_stride;
       mbar_wait(&tfull_bar[acc], (tcount >> 1) & 1);
       tc_fence_after();
       const int row = m0 + q * 32 + lane;
@@ -309,7 +319,7 @@ gemm_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant__ CUt
         float v[64];
 #pragma unroll
         for (int j = 0; j < 32; ++j) { v[j] = __uint_as_float(r0[j]); v[j + 32] = __uint_as_float(r1[j]); }
-        if (row < p.M) epilogue_chunk<EPI>(p, row, n0 + c * 64, v);
+        if (row < p.M) epilogue_chunk<EPI>(ps, row, n0 + c * 64, v);
       }
       tc_fence_before();
       mbar_arrive(&tempty_bar[acc]);
@@ -967,6 +977,7 @@ static GemmParams make_params(const dh_gemm_args* a) {
   p.rope_sin = reinterpret_cast<const bf16*>(a->rope_sin);
   p.positions = a->positions;
   p.m_limit = a->m_limit;
+  p.splits = 1; p.split_stride = 0;
   p.sk_stages = 0; p.sk_partial = 0;
   return p;
 }
@@ -992,7 +1003,12 @@ static int launch_gemm(const dh_gemm_args* a, cudaStream_t stream) {
   GemmParams p = make_params(a);
   p.tiles_m = (a->M + BM - 1) / BM;
   p.tiles_n = a->N / BN;
-  const int tiles = p.tiles_m * p.tiles_n;
+  if (a->split_k > 1) {
+    const int nkb = (a->K1 + BK - 1) / BK + (a->K2 + BK - 1) / BK;
+    p.splits = a->split_k < nkb ? a->split_k : nkb;
+    p.split_stride = (long long)a->M * a->ldo;
+  }
+  const int tiles = p.tiles_m * p.tiles_n * p.splits;
   const int grid = tiles < sm_count() ? tiles : sm_count();
   gemm_kernel<BN, EPI><<<grid, GEMM_THREADS, Cfg::SMEM_BYTES, stream>>>(tmA, tmB, tmA2, tmB2, p);
   DH_CUDA(cudaGetLastError());
@@ -1149,7 +1165,7 @@ static int dispatch_bn(const dh_gemm_args* a, cudaStream_t stream) {
   }
   // CTA pairs for the big K-major GEMMs of the decoder; the 1-CTA kernel covers small M, MN-major operands, odd N.
   if (!g_force_single && a->a_layout == 0 && a->b_layout == 0 && (a->K2 == 0 || (a->a2_layout == 0 && a->b2_layout == 0)) &&
-      a->N % 256 == 0 && a->M >= 1024 && pair_epilogue_ok(a))
+      a->N % 256 == 0 && a->M >= 1024 && a->split_k <= 1 && pair_epilogue_ok(a))
     return launch_gemm_pair<EPI>(a, stream);
   // one token per sequence (decode): weight streaming with K split over a cluster
   if (a->M <= BM && a->N % SK_BN == 0 && a->a_layout == 0 && a->b_layout == 0 && (a->K2 == 0 || (a->a2_layout == 0 && a->b2_layout == 0)) &&
@@ -1157,8 +1173,9 @@ static int dispatch_bn(const dh_gemm_args* a, cudaStream_t stream) {
     return launch_gemm_skinny<EPI>(a, stream);
   // Tile width: 256 when it divides N and leaves enough tiles to fill the machine, else 128, else 64.
   const long long tiles_m = (a->M + BM - 1) / BM;
-  if (a->N % 256 == 0 && tiles_m * (a->N / 256) >= sm_count()) return launch_gemm<256, EPI>(a, stream);
-  if (a->N % 128 == 0 && tiles_m * (a->N / 128) >= sm_count() / 2) return launch_gemm<128, EPI>(a, stream);
+  const long long sk = a->split_k > 1 ? a->split_k : 1;
+  if (a->N % 256 == 0 && tiles_m * (a->N / 256) * sk >= sm_count()) return launch_gemm<256, EPI>(a, stream);
+  if (a->N % 128 == 0 && tiles_m * (a->N / 128) * sk >= sm_count() / 2) return launch_gemm<128, EPI>(a, stream);
   return launch_gemm<64, EPI>(a, stream);
 }
 
@@ -1176,9 +1193,7 @@ extern "C" int dh_gemm(const dh_gemm_args* a, void* stream_) {
   DH_CHECK(((uintptr_t)a->A & 15) == 0 && ((uintptr_t)a->B & 15) == 0, "dh_gemm: operands must be 16-byte aligned");
   if (a->K2 > 0) DH_CHECK(a->A2 && a->B2 && (a->lda2 % 8) == 0 && (a->ldb2 % 8) == 0, "dh_gemm: bad second source");
   if (a->split_k > 1)
-    DH_CHECK(a->M <= BM && a->N % 128 == 0 && a->a_layout == 0 && a->b_layout == 0 && (a->K2 == 0 || (a->a2_layout == 0 && a->b2_layout == 0)) &&
-                 a->epilogue == DH_EPI_F32 && !a->accumulate && !a->m_limit,
-             "dh_gemm: split_k needs M <= 128, N %% 128 == 0, K-major operands and the plain DH_EPI_F32 epilogue");
+    DH_CHECK(a->epilogue == DH_EPI_F32 && !a->accumulate && !a->m_limit, "dh_gemm: split_k needs the plain DH_EPI_F32 epilogue without m_limit");
   switch (a->epilogue) {
     case DH_EPI_BF16: return dispatch_bn<DH_EPI_BF16>(a, stream);
     case DH_EPI_F32: return dispatch_bn<DH_EPI_F32>(a, stream);

@@ -297,6 +297,21 @@ class DecoderEngine:
         ops.prefix_project_fwd(packed[-1]["prefix_all"], self.wkv_all, pkv_all, s.n_query_groups, s.qpk)
         return pkv_all
 
+    def _wgrad(self, A: Tensor, B: Tensor, rows: int, cols: int, alpha: float = 1.0) -> Tensor:
+        """fp32 [rows, cols] = alpha * A^T B for the LoRA factor gradients: both operands are [tokens, *] (MN-major), the
+        reduction runs over the TOKEN dimension (K = B*T = 8192) while the output is tiny (64 x 2048: 16-32 tiles), so K is
+        split over all SMs (dh_gemm split_k: fp32 slices) and the slices are summed."""
+        K = A.shape[0]
+        tiles = ((rows + 127) // 128) * ((cols + 63) // 64)
+        S = max(1, min(ops.sm_count() // tiles, (K // 64) // 4, 16))
+        if S == 1:
+            out = torch.empty((rows, cols), device=self.device, dtype=torch.float32)
+            ops.gemm(A, B, out, a_layout=1, b_layout=1, epilogue=ops.EPI_F32, alpha=alpha)
+            return out
+        ws = self._buf("wgrad_ws", (S, rows, cols), torch.float32)
+        ops.gemm(A, B, ws, a_layout=1, b_layout=1, epilogue=ops.EPI_F32, alpha=alpha, split_k=S)
+        return ws.sum(0)
+
     def lm_head(self, hidden: Tensor, out: Optional[Tensor] = None, m_limit: Optional[Tensor] = None) -> Tensor:
         """bf16 logits [M, V] = adapter_scale * (hidden W^T + adapter_bias)  (ger/lora.py:70-71).  m_limit (device int32):
         only the first *m_limit rows are needed (valid-row compaction of the fused loss)."""
@@ -357,10 +372,8 @@ class DecoderEngine:
             if "proj_a" in pk:
                 dap = self._buf("dap", (M, LORA_PAD), bf)
                 ops.gemm(dxb, pk["proj_b_t"], dap)
-                db = torch.empty((C, LORA_PAD), device=self.device, dtype=f32)
-                ops.gemm(dxb, a["ap_s"], db, a_layout=1, b_layout=1, epilogue=ops.EPI_F32)
-                da = torch.empty((LORA_PAD, C), device=self.device, dtype=f32)
-                ops.gemm(dap, a["y"], da, a_layout=1, b_layout=1, epilogue=ops.EPI_F32, alpha=scaling)
+                db = self._wgrad(dxb, a["ap_s"], C, LORA_PAD)
+                da = self._wgrad(dap, a["y"], LORA_PAD, C, alpha=scaling)
                 grads[p + "proj.lora_A"] = da[: s.r]
                 grads[p + "proj.lora_B"] = db[:, : s.r]
                 ops.gemm(dxb, lw["wproj_t"], dy, A2=dap, B2=pk["proj_a_t"])
@@ -382,10 +395,8 @@ class DecoderEngine:
             if "qkv_a" in pk:
                 da_s = self._buf("da_s", (M, LORA_PAD), bf)
                 ops.gemm(dqkv, pk["qkv_b_t"], da_s)
-                db = torch.empty((s.qkv_out, LORA_PAD), device=self.device, dtype=f32)
-                ops.gemm(dqkv, a["a_s"], db, a_layout=1, b_layout=1, epilogue=ops.EPI_F32)
-                da = torch.empty((LORA_PAD, C), device=self.device, dtype=f32)
-                ops.gemm(da_s, a["n1"], da, a_layout=1, b_layout=1, epilogue=ops.EPI_F32, alpha=scaling)
+                db = self._wgrad(dqkv, a["a_s"], s.qkv_out, LORA_PAD)
+                da = self._wgrad(da_s, a["n1"], LORA_PAD, C, alpha=scaling)
                 r, kv = s.r, s.kv_embd
                 grads[p + "attn.lora_A"] = da[: 3 * r]
                 grads[p + "attn.lora_B"] = torch.cat((db[:C, 0:r], db[C:C + kv, r:2 * r], db[C + kv:, 2 * r:3 * r]), dim=0)

@@ -161,6 +161,10 @@ def splitk_resid_rmsnorm(partial: Tensor, resid: Tensor, weight: Tensor, x_out: 
     _count()
 
 
+def sm_count() -> int:
+    return int(_lib.load().dh_sm_count()) or 148
+
+
 def decode_split_k(N: int, K: int) -> int:
     """Split count of a decode GEMM whose consumer sums the slices: every SM gets one CTA (N / 128 tiles x splits <= SM count),
     at least two 64-wide k-blocks per CTA."""

@@ -65,9 +65,10 @@ typedef struct dh_gemm_args {
   float alpha;
   int32_t seq_len;                   /* DH_EPI_QKV_ROPE: row -> position = row % seq_len when positions == NULL */
   int32_t q_per_kv;                  /* DH_EPI_QKV_ROPE: q heads per kv head (group = q_per_kv + 2 slots of 64)   */
-  int32_t split_k;                   /* > 1 (needs M <= 128, K-major operands, DH_EPI_F32, no accumulate): `out` is fp32
-                                        [split_k][M][ldo]; CTA group s multiplies K range s of split_k into slice s and NO reduction
-                                        is done -- the consumer sums the slices (dh_splitk_resid_rmsnorm).  0 / 1: off. */
+  int32_t split_k;                   /* > 1 (DH_EPI_F32 only, no accumulate, no m_limit): `out` is fp32 [split_k][M][ldo]; K range s of
+                                        split_k is multiplied into slice s and NO reduction is done -- the consumer sums the slices
+                                        (dh_splitk_resid_rmsnorm in the decode step; a plain sum for the LoRA wgrads whose K is the
+                                        token count).  0 / 1: off. */
   void* out;  int64_t ldo;
   void* out2; int64_t ldo2;
   const void* aux; int64_t ldaux;

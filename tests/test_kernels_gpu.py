@@ -69,6 +69,21 @@ def test_gemm_wgrad_form(M, N, K):
     assert rel(out, ref) < 1e-4, report("gemm wgrad", out, ref)
 
 
+@pytest.mark.parametrize("M,N,K,S", [(64, 2048, 8192, 4), (2560, 64, 8192, 7), (64, 256, 1000, 3), (304, 128, 4096, 16)])
+def test_gemm_wgrad_split_k(M, N, K, S):
+    """LoRA factor gradients: out[M, N] = A^T B with A [K, M], B [K, N] (K = tokens).  split_k leaves S fp32 slices whose
+    sum is the product (ragged K ranges included); the slices are deterministic."""
+    A, B = rnd((K, M), 331, bound=0.5), rnd((K, N), 332, bound=0.5)
+    ws = torch.full((S, M, N), float("nan"), device=DEV, dtype=torch.float32)
+    ops.gemm(A, B, ws, a_layout=1, b_layout=1, epilogue=ops.EPI_F32, alpha=0.5, split_k=S)
+    ws2 = torch.empty_like(ws)
+    ops.gemm(A, B, ws2, a_layout=1, b_layout=1, epilogue=ops.EPI_F32, alpha=0.5, split_k=S)
+    torch.cuda.synchronize()
+    ref = 0.5 * (A.float().t() @ B.float())
+    assert rel(ws.sum(0), ref) < 2e-3, report("wgrad split-k", ws.sum(0), ref)
+    assert torch.equal(ws, ws2)
+
+
 def test_gemm_dual_source_lora():
     """pretrained + LoRA delta folded in as a K extension (ger/lora.py:388-402)."""
     M, N, K, K2 = 512, 640, 256, 64
