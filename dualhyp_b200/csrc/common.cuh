@@ -3,6 +3,7 @@
 #pragma once
 
 #include <cuda.h>
+#include <utility>
 #include <cuda_bf16.h>
 #include <cuda_runtime.h>
 #include <stdint.h>
@@ -42,8 +43,37 @@ void set_error(const char* fmt, ...);
 int make_tensor_map(CUtensorMap* map, const void* base, CUtensorMapDataType dtype, int rank, const uint64_t* dims,
                     const uint64_t* strides_bytes, const uint32_t* box, CUtensorMapSwizzle swizzle);
 int sm_count();
+bool pdl_enabled();   // programmatic dependent launch for the training-step kernels (opt-in: DH_PDL=1)
 
 #ifdef __CUDACC__
+// ---- programmatic dependent launch (PDL) ----
+// A kernel launched through launch_pdl may start while its predecessor on the stream is still draining: its prologue
+// (barrier init, TMEM allocation, tensor-map prefetch) overlaps the predecessor's tail.  EVERY such kernel must execute
+// pdl_wait() before its first global-memory access (it returns once the predecessor grid has completed and its writes are
+// visible) -- that also keeps the chain transitive.  pdl_launch_dependents() lets the NEXT kernel's CTAs be scheduled as
+// soon as every CTA of this grid has started.
+__device__ __forceinline__ void pdl_wait() { asm volatile("griddepcontrol.wait;" ::: "memory"); }
+__device__ __forceinline__ void pdl_launch_dependents() { asm volatile("griddepcontrol.launch_dependents;" ::: "memory"); }
+
+template <typename... KArgs, typename... Args>
+inline cudaError_t launch_pdl(void (*kernel)(KArgs...), dim3 grid, dim3 block, size_t smem, cudaStream_t stream, Args&&... args) {
+  cudaLaunchConfig_t cfg = {};
+  cfg.gridDim = grid;
+  cfg.blockDim = block;
+  cfg.dynamicSmemBytes = smem;
+  cfg.stream = stream;
+  cudaLaunchAttribute attr[1];
+  attr[0].id = cudaLaunchAttributeProgrammaticStreamSerialization;
+  attr[0].val.programmaticStreamSerializationAllowed = 1;
+  cfg.attrs = attr;
+  cfg.numAttrs = 0;
+  if (pdl_enabled()) {       // not under stream capture: the decode graph keeps plain edges
+    cudaStreamCaptureStatus st = cudaStreamCaptureStatusNone;
+    if (cudaStreamIsCapturing(stream, &st) == cudaSuccess && st == cudaStreamCaptureStatusNone) cfg.numAttrs = 1;
+  }
+  return cudaLaunchKernelEx(&cfg, kernel, std::forward<Args>(args)...);
+}
+
 // ------------------------------------------------------------------------------------------------
 // device side
 // ------------------------------------------------------------------------------------------------

@@ -202,12 +202,9 @@ gemm_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant__ CUt
 
   const int warp = __shfl_sync(0xffffffffu, threadIdx.x >> 5, 0);   // shfl: a warp-uniform value for the compiler
   const int lane = threadIdx.x & 31;
-  int tiles_m = p.tiles_m;
-  if (p.m_limit) { const int t = (__ldg(p.m_limit) + BM - 1) / BM; tiles_m = t < tiles_m ? t : tiles_m; }
-  const int real_tiles = tiles_m * p.tiles_n;
-  const int num_tiles = real_tiles * p.splits;   // virtual tiles: (output tile, K range); range s writes output slice s
   const int nkb1 = (p.K1 + BK - 1) / BK;   // a ragged K tail is zero-filled by TMA
   const int nkb = nkb1 + (p.K2 + BK - 1) / BK;
+  pdl_launch_dependents();
 
   if (warp == 0 && lane == 0) {
     tma_prefetch_desc(&tmA);
@@ -227,6 +224,11 @@ gemm_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant__ CUt
   __syncthreads();
   tc_fence_after();
   const uint32_t tmem_base = __shfl_sync(0xffffffffu, *tmem_slot, 0);
+  pdl_wait();          // the prologue above overlapped the previous kernel's tail; global memory is read from here on
+  int tiles_m = p.tiles_m;
+  if (p.m_limit) { const int t = (__ldg(p.m_limit) + BM - 1) / BM; tiles_m = t < tiles_m ? t : tiles_m; }
+  const int real_tiles = tiles_m * p.tiles_n;
+  const int num_tiles = real_tiles * p.splits;   // virtual tiles: (output tile, K range); range s writes output slice s
 
   if (warp == 0 && lane == 0) {
     // ===================== TMA producer =====================
@@ -788,11 +790,9 @@ gemm_pair_kernel(const __grid_constant__ PairMaps tm, const GemmParams p) {
   const uint32_t rank = cluster_ctarank();
   const int pair = blockIdx.x >> 1;
   const int npairs = gridDim.x >> 1;
-  int tiles_m = p.tiles_m;
-  if (p.m_limit) { const int t = (__ldg(p.m_limit) + 255) / 256; tiles_m = t < tiles_m ? t : tiles_m; }
-  const int num_tiles = tiles_m * p.tiles_n;
   const int nkb1 = (p.K1 + BK - 1) / BK;
   const int nkb = nkb1 + (p.K2 + BK - 1) / BK;
+  pdl_launch_dependents();
 
   if (warp == 0 && lane == 0) {
     tma_prefetch_desc(&tm.A);
@@ -818,6 +818,10 @@ gemm_pair_kernel(const __grid_constant__ PairMaps tm, const GemmParams p) {
   cluster_sync_all();
   tc_fence_after();
   const uint32_t tmem_base = __shfl_sync(0xffffffffu, *tmem_slot, 0);
+  pdl_wait();          // the prologue above overlapped the previous kernel's tail; global memory is read from here on
+  int tiles_m = p.tiles_m;
+  if (p.m_limit) { const int t = (__ldg(p.m_limit) + 255) / 256; tiles_m = t < tiles_m ? t : tiles_m; }
+  const int num_tiles = tiles_m * p.tiles_n;
 
   if (warp == 0 && lane == 0) {
     // ===================== TMA producer (each CTA loads its own halves) =====================
@@ -1010,8 +1014,7 @@ static int launch_gemm(const dh_gemm_args* a, cudaStream_t stream) {
   }
   const int tiles = p.tiles_m * p.tiles_n * p.splits;
   const int grid = tiles < sm_count() ? tiles : sm_count();
-  gemm_kernel<BN, EPI><<<grid, GEMM_THREADS, Cfg::SMEM_BYTES, stream>>>(tmA, tmB, tmA2, tmB2, p);
-  DH_CUDA(cudaGetLastError());
+  DH_CUDA(launch_pdl(gemm_kernel<BN, EPI>, dim3(grid), dim3(GEMM_THREADS), Cfg::SMEM_BYTES, stream, tmA, tmB, tmA2, tmB2, p));
   return 0;
 }
 
@@ -1083,8 +1086,7 @@ static int launch_gemm_pair(const dh_gemm_args* a, cudaStream_t stream) {
   const int tiles = p.tiles_m * p.tiles_n;
   const int pairs = sm_count() / 2;
   const int grid = 2 * (tiles < pairs ? tiles : pairs);
-  gemm_pair_kernel<EPI><<<grid, PAIR_THREADS, Cfg::SMEM_BYTES, stream>>>(tm, p);
-  DH_CUDA(cudaGetLastError());
+  DH_CUDA(launch_pdl(gemm_pair_kernel<EPI>, dim3(grid), dim3(PAIR_THREADS), Cfg::SMEM_BYTES, stream, tm, p));
   return 0;
 }
 

@@ -59,6 +59,8 @@ __global__ void rmsnorm_fwd_kernel(const XT* __restrict__ x, const float* __rest
   const long long row = blockIdx.x;
   const int c0 = threadIdx.x * 8;
   float v[8], g[8];
+  pdl_launch_dependents();
+  pdl_wait();
   load8(x + row * C + c0, v);
   load8(w + c0, g);
   float ss = 0.f;
@@ -126,6 +128,8 @@ __global__ void rmsnorm_bwd_kernel(const XT* __restrict__ x, const float* __rest
   const long long row = blockIdx.x;
   const int c0 = threadIdx.x * 8;
   float xv[8], g[8], d[8];
+  pdl_launch_dependents();
+  pdl_wait();
   load8(x + row * C + c0, xv);
   load8(w + c0, g);
   load8(dy + row * C + c0, d);
@@ -525,9 +529,8 @@ extern "C" int dh_rmsnorm_fwd(const void* x, int x_dtype, const float* weight, v
   DH_CHECK(x && weight && y && M > 0, "dh_rmsnorm_fwd: null argument");
   DH_CHECK(C % 256 == 0 && C <= 8192, "dh_rmsnorm_fwd: C=%d must be a multiple of 256 and <= 8192", C);
   cudaStream_t s = (cudaStream_t)stream;
-  if (x_dtype == 0) rmsnorm_fwd_kernel<float><<<M, C / 8, 0, s>>>((const float*)x, weight, (bf16*)y, rstd, C, eps);
-  else rmsnorm_fwd_kernel<bf16><<<M, C / 8, 0, s>>>((const bf16*)x, weight, (bf16*)y, rstd, C, eps);
-  DH_CUDA(cudaGetLastError());
+  if (x_dtype == 0) DH_CUDA(launch_pdl(rmsnorm_fwd_kernel<float>, dim3(M), dim3(C / 8), 0, s, (const float*)x, weight, (bf16*)y, rstd, C, eps));
+  else DH_CUDA(launch_pdl(rmsnorm_fwd_kernel<bf16>, dim3(M), dim3(C / 8), 0, s, (const bf16*)x, weight, (bf16*)y, rstd, C, eps));
   return 0;
 }
 
@@ -547,10 +550,9 @@ extern "C" int dh_rmsnorm_bwd(const void* x, int x_dtype, const float* weight, c
   DH_CHECK(C % 256 == 0 && C <= 8192, "dh_rmsnorm_bwd: C=%d must be a multiple of 256 and <= 8192", C);
   cudaStream_t s = (cudaStream_t)stream;
   if (x_dtype == 0)
-    rmsnorm_bwd_kernel<float><<<M, C / 8, 0, s>>>((const float*)x, weight, rstd, (const bf16*)dy, dres, dx_out, (bf16*)dx_bf16, C);
+    DH_CUDA(launch_pdl(rmsnorm_bwd_kernel<float>, dim3(M), dim3(C / 8), 0, s, (const float*)x, weight, rstd, (const bf16*)dy, dres, dx_out, (bf16*)dx_bf16, C));
   else
-    rmsnorm_bwd_kernel<bf16><<<M, C / 8, 0, s>>>((const bf16*)x, weight, rstd, (const bf16*)dy, dres, dx_out, (bf16*)dx_bf16, C);
-  DH_CUDA(cudaGetLastError());
+    DH_CUDA(launch_pdl(rmsnorm_bwd_kernel<bf16>, dim3(M), dim3(C / 8), 0, s, (const bf16*)x, weight, rstd, (const bf16*)dy, dres, dx_out, (bf16*)dx_bf16, C));
   return 0;
 }
 

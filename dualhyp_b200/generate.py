@@ -44,6 +44,7 @@ class DecodeLoop:
         self.eos = torch.full((1,), -1, dtype=torch.int64, device=dev)
         self.eos_id: Optional[int] = None
         self.kernels_per_token = 0
+        self.trainable_sig = None
         self.graph: Optional[torch.cuda.CUDAGraph] = None
         self.cache_sig = None
 
@@ -107,15 +108,20 @@ class DecodeLoop:
         return steps
 
 
-def _decode_loop(eng, packed, n: int, max_new: int) -> DecodeLoop:
+def _decode_loop(model, eng, n: int, max_new: int) -> DecodeLoop:
     """One loop (and one captured graph) per batch size; `out_ids` has room for at least 256 new tokens so that
-    calls with different `max_new_tokens` (generate/base.py is called once per utterance) share it."""
+    calls with different `max_new_tokens` (generate/base.py is called once per utterance) share it.  The bf16 operand
+    forms of the trainable tensors are re-packed only when a tensor changed (data pointer / version counter): an
+    inference service decodes thousands of batches against the same adapter."""
+    names, tensors = model._trainables()
+    sig = tuple((t.data_ptr(), t._version) for t in tensors)
     loops = eng._bufs.setdefault("decode_loops", {})
     loop = loops.get(n)
     if loop is None or loop.max_new < max_new:
-        loop = loops[n] = DecodeLoop(eng, packed, n, max(256, max_new))
-    else:
-        loop.refresh(packed)
+        loop = loops[n] = DecodeLoop(eng, eng.pack_trainable(dict(zip(names, tensors))), n, max(256, max_new))
+    elif loop.trainable_sig != sig:
+        loop.refresh(eng.pack_trainable(dict(zip(names, tensors))))
+    loop.trainable_sig = sig
     return loop
 
 
@@ -140,8 +146,6 @@ def generate_batch(model, prompts: Sequence[Tensor], max_new_tokens: int, eos_id
     `[n, steps]` of generated ids instead (no device-to-host copy; used by bench.py's HBM-resident leg)."""
     eng = model._engine_ready()
     dev = eng.device
-    names, tensors = model._trainables()
-    packed = eng.pack_trainable(dict(zip(names, tensors)))
     n = len(prompts)
     lens = torch.tensor([int(p.numel()) for p in prompts], dtype=torch.int32)
     Tmax = int(lens.max())
@@ -150,13 +154,23 @@ def generate_batch(model, prompts: Sequence[Tensor], max_new_tokens: int, eos_id
     if all(p.is_cuda for p in prompts):
         ids = torch.nn.utils.rnn.pad_sequence(list(prompts), batch_first=True, padding_value=0)
     else:
-        ids = torch.zeros((n, Tmax), dtype=torch.int64).pin_memory()
+        prev = eng._bufs.get(("pinned_ids_event", n))
+        if prev is not None:
+            prev.synchronize()
+        stage = eng._bufs.get(("pinned_ids", n))                # pinned staging rows, allocated once per batch size
+        if stage is None or stage.shape[1] < Tmax:
+            stage = eng._bufs[("pinned_ids", n)] = torch.zeros((n, max(Tmax, model.max_seq_length)), dtype=torch.int64).pin_memory()
+        ids_h = stage[:, :Tmax]
+        ids_h.zero_()
         for i, p in enumerate(prompts):
-            ids[i, : p.numel()] = p.cpu()
-        ids = ids.to(dev, non_blocking=True)
+            ids_h[i, : p.numel()] = p.cpu()
+        ids = ids_h.to(dev, non_blocking=True)
+        copied = torch.cuda.Event()
+        copied.record()
+        eng._bufs[("pinned_ids_event", n)] = copied             # the next call waits for this copy before re-using the rows
     lens_d = lens.to(dev)
     eng.alloc_cache(n, max(model.max_seq_length, total))
-    loop = _decode_loop(eng, packed, n, max_new_tokens)
+    loop = _decode_loop(model, eng, n, max_new_tokens)
     hidden = eng.prefill(ids, loop.packed).view(n, Tmax, -1)
     last = hidden[torch.arange(n, device=dev), (lens_d - 1).long()]                    # ln_f state of each prompt's last token
     loop.reset(last, lens_d, eos_id)

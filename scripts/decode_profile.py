@@ -35,3 +35,28 @@ tot = sum(v[1] for v in agg.values()) / 4
 print(f"n={n}: sum of per-op event times {tot:.3f} ms per token step")
 for k, v in sorted(agg.items(), key=lambda kv: -kv[1][1]):
     print(f"  {k[0]:18s} {str(k[1]):38s} x{v[0] // 4:3d}  {1e3 * v[1] / v[0]:8.1f} us each  {v[1] / 4:7.3f} ms/step")
+
+# ---- prefill: per-op device time of one batched prompt pass (same prompts) ----
+eng = model._engine
+ids = torch.nn.utils.rnn.pad_sequence(prompts, batch_first=True, padding_value=0)
+with torch.inference_mode():
+    eng.prefill(ids, loop.packed)
+    torch.cuda.synchronize()
+    e0, e1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+    e0.record()
+    eng.prefill(ids, loop.packed)
+    e1.record()
+    torch.cuda.synchronize()
+    print(f"prefill of {tuple(ids.shape)}: {e0.elapsed_time(e1):.2f} ms (events around the whole pass)")
+    with ops.profile() as recs:
+        eng.prefill(ids, loop.packed)
+        torch.cuda.synchronize()
+agg = {}
+for name, meta, a, b in recs:
+    key = (name, meta[:5] if meta else None)
+    v = agg.setdefault(key, [0, 0.0])
+    v[0] += 1
+    v[1] += a.elapsed_time(b)
+print(f"sum of per-op event times {sum(v[1] for v in agg.values()):.2f} ms")
+for k, v in sorted(agg.items(), key=lambda kv: -kv[1][1])[:12]:
+    print(f"  {k[0]:18s} {str(k[1]):38s} x{v[0]:3d}  {1e3 * v[1] / v[0]:8.1f} us each  {v[1]:7.3f} ms")
