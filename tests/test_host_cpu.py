@@ -173,3 +173,50 @@ def test_relprompt_mask_token_splice_equals_text_substitution():
     via_ids = R.fill_mask_tokens(ids, a_pred, v_pred, slots[0], slots[1], first_mask_id=500)
     assert via_ids.tolist() == via_text.tolist()
     assert via_ids.numel() == ids.numel() - 2 + 5 + 3
+
+
+def test_prompt_assembly_label_masking_and_collation():
+    """SURVEY 8f row 2 (host side): the three dataset classes' placeholder substitution, the -1 label span over the
+    prompt, right-padded collation as the reference's collate_fn, and the pad-free packed layout."""
+    import os
+    from dualhyp_b200 import collate as Cc
+    if os.path.isfile("/root/reference/data/prompts.py"):           # the real templates where the checkout is mounted
+        ns = {}
+        exec(open("/root/reference/data/prompts.py").read(), ns)
+        ger, dual, relp = ns["GER_PROMPTS"], ns["DualHyp_PROMPTS"], ns["RelPrompt_PROMPTS"]
+    else:
+        ger = {"prompt_1": "revise:\n", "prompt_2": "\n\nothers:", "prompt_3": "\n\nresponse:\n"}
+        dual = {"prompt_1": "asr <<<ASR_NHYPS>>> vsr <<<VSR_NHYPS>>>", "prompt_2": "\nA:\n<<<ASR_NHYPS>>>\nV:\n<<<VSR_NHYPS>>>", "prompt_3": "\nresponse:\n"}
+        relp = {"prompt_1": "a <<<ASR_BEST_NHYPS>>> <<<ASR_NHYPS>>> m <<<ASR_MASKS>>> v <<<VSR_BEST_NHYPS>>> <<<VSR_NHYPS>>> m <<<VSR_MASKS>>>",
+                "prompt_2": "", "prompt_3": "\nresponse:\n"}
+    asr = ["the cat sat", "the cat sad", "a cat sat", "the cap sat", "the cat set"]
+    vsr = ["the bat sat", "the cat sat", "the mat sat", "the cat fat", "the cat hat"]
+    g = Cc.ger_prompt(ger, asr)
+    assert g.startswith(ger["prompt_1"] + asr[0]) and g.endswith(ger["prompt_3"]) and "\n".join(asr[1:]) in g
+    assert asr[4] not in Cc.ger_prompt(ger, asr, max_nhyps=3)
+    d = Cc.dualhyp_prompt(dual, asr, vsr)
+    assert "<<<" not in d and asr[0] in d and vsr[0] in d and "\n".join(vsr[1:]) in d and d.endswith(dual["prompt_3"])
+    r_inf = Cc.relprompt_prompt(relp, asr, vsr)
+    assert "<<<ASR_MASKS>>>" in r_inf and "<<<VSR_MASKS>>>" in r_inf and "<<<ASR_NHYPS>>>" not in r_inf
+    r_tr = Cc.relprompt_prompt(relp, asr, vsr, ["<<C>>", "<<N>>"], ["<<M>>"])
+    assert "<<C>><<N>>" in r_tr and "<<<" not in r_tr.replace("<<C>>", "").replace("<<N>>", "").replace("<<M>>", "")
+
+    enc = lambda t: [1] + [3 + (ord(c) % 200) for c in t]          # char tokenizer with a BOS id, like the llama one
+    s1 = Cc.encode_sample(enc, d, "the cat sat", "</s>")
+    s2 = Cc.encode_sample(enc, g, "a cat", "</s>")
+    n1 = s1["input_ids_no_response"].numel()
+    assert torch.equal(s1["input_ids"][:n1], s1["input_ids_no_response"])
+    assert (s1["labels"][:n1] == -1).all() and torch.equal(s1["labels"][n1:], s1["input_ids"][n1:])
+    b = Cc.collate_right_pad([s1, s2])
+    T = max(s1["input_ids"].numel(), s2["input_ids"].numel())
+    assert b["input_ids"].shape == (2, T) and b["labels"].shape == (2, T)
+    short = 1 if s2["input_ids"].numel() < s1["input_ids"].numel() else 0
+    ns_ = [s1, s2][short]["input_ids"].numel()
+    assert (b["input_ids"][short, ns_:] == 0).all() and (b["labels"][short, ns_:] == -1).all()
+    pk = Cc.pack_varlen([s1, s2])
+    assert pk["cu_seqlens"].tolist() == [0, s1["input_ids"].numel(), s1["input_ids"].numel() + s2["input_ids"].numel()]
+    assert pk["positions"][pk["cu_seqlens"][1]] == 0 and pk["targets"][pk["cu_seqlens"][1] - 1] == -1
+    # packed next-token targets == the padded batch's shifted labels on the valid positions
+    for i, s in enumerate([s1, s2]):
+        a, e = pk["cu_seqlens"][i].item(), pk["cu_seqlens"][i + 1].item()
+        assert torch.equal(pk["targets"][a:e - 1], b["labels"][i, 1:e - a])
