@@ -36,9 +36,9 @@ PER_GPU_BATCH = 16
 DECODE_METRIC = "DualHyp infer utterances/s (greedy KV-cache decode, adapter TinyLlama-1.1B, 5+5 N-best prompts, 64 new tokens)"
 DECODE_UTTS, DECODE_NEW = 64, 64
 LORA = dict(r=8, alpha=16, dropout=0.0, to_query=True, to_key=True, to_value=True, to_projection=True)
-# DRAM bytes per launch of the dominant GEMMs from one `ncu --set full` capture of this command (profiles/r01g_ncu_full_summary.txt);
+# DRAM bytes per launch of the dominant GEMMs from one `ncu --set full` capture of this command (profiles/r01u_ncu_full_summary.txt);
 # key = (M, N, K, epilogue).  Algorithmic bytes of the SwiGLU GEMM: A 33.6 MB + B 46.1 MB + h12 184.5 MB + act 92.3 MB = 356.5 MB.
-NCU_DRAM_BYTES = {(8192, 11264, 2048, 5): 372.5e6, (8192, 2048, 5632, 2): 523.8e6, (8192, 2560, 2048, 4): 58.6e6, (8192, 2048, 2048, 2): 179.8e6}
+NCU_DRAM_BYTES = {(8192, 11264, 2048, 5): 369.5e6, (8192, 2048, 5632, 2): 522.9e6, (8192, 2560, 2048, 4): 59.1e6, (8192, 2048, 2048, 2): 179.3e6}
 
 
 def parse_args():
@@ -502,7 +502,7 @@ def run_native(args):
         achieved = fl / (dms / dcount / 1e3) / 1e12
         line["roofline"] = {"bound": "tensor", "achieved": round(achieved, 1), "peak": peak_tf, "unit": "TFLOP/s",
                             "frac": round(achieved / peak_tf, 4), "traffic": NCU_DRAM_BYTES.get((M_, N_, K_ + K2_, epi)), "peak_source": peak_src,
-                            "traffic_source": "dram__bytes_read.sum + dram__bytes_write.sum per launch, ncu --set full (profiles/r01g_ncu_full_summary.txt)",
+                            "traffic_source": "dram__bytes_read.sum + dram__bytes_write.sum per launch, ncu --set full (profiles/r01u_ncu_full_summary.txt)",
                             "kernel": f"gemm_kernel<256,{gemm_epi_name(epi)}> M={M_} N={N_} K={K_}", "launches": dcount,
                             "avg_ms": round(dms / dcount, 4), "share_of_step": round(dms / total_ms, 4),
                             "all_gemms": {"tflops": round(gemm_fl / (gemm_ms / 1e3) / 1e12, 1), "share_of_step": round(gemm_ms / total_ms, 4)},
