@@ -13,6 +13,8 @@
 //   decode   : single-query attention over the KV cache (CUDA cores; HBM-bound).
 #include <math.h>
 
+#include <stdlib.h>
+
 #include "common.cuh"
 #include "../../include/dualhyp.h"
 
@@ -1421,6 +1423,220 @@ __global__ void __launch_bounds__(DEC_THREADS) attn_decode_kernel(const bf16* __
   orow[lane + 32] = __float2bfloat16_rn(o1);
 }
 
+// =================================================================================================
+// decode on tensor cores.  The CUDA-core kernel above is ISSUE-bound (ncu: 9.3 M warp instructions per launch, 128 fp32
+// FMAs per key and thread for the 8 heads that share a K / V row).  Here the 8 q heads of the group are the rows of an
+// mma.sync m16n8k16 tile (rows 8..15 unused): scores S[head, key] = Q K^T with 8 keys per MMA column block, and
+// O[head, dim] += P V with 16 keys per MMA k-step -- ~45x fewer issue slots, so the kernel is left with its K / V loads.
+//   Q K^T : the k index of an MMA is only a summation index, so A and B use the same permuted k order and every
+//           thread feeds the tensor core straight from one 16-byte load of its K row (dims 8q..8q+7 of a 32-dim block
+//           supply k-slots {2q,2q+1 | 2q+8,2q+9} of two MMAs); no shared-memory staging for K.
+//   P V   : B[k = key][n = dim] needs two KEYS of one dim per register: V rows go through a per-warp swizzled 2 KB
+//           shared tile and come back transposed with ldmatrix.trans; P (fp32 in shared memory) is packed to bf16.
+// Block = (sequence, kv group), 8 warps; warp w takes key blocks w, w + 8, ...
+// =================================================================================================
+constexpr int DM_VT_BYTES = 8 * 2 * 2048;          // per warp: two 16-key x 128-byte V tiles (double buffer)
+constexpr int DM_FIXED_BYTES = DM_VT_BYTES /* also the per-warp partial outputs afterwards */ + (DEC_MAX_QPK * HD + 2 * DEC_MAX_QPK) * 4;
+
+__device__ __forceinline__ void mma_bf16_16816(float (&d)[4], uint32_t a0, uint32_t a1, uint32_t a2, uint32_t a3, uint32_t b0, uint32_t b1) {
+  asm volatile("mma.sync.aligned.m16n8k16.row.col.f32.bf16.bf16.f32 {%0,%1,%2,%3}, {%4,%5,%6,%7}, {%8,%9}, {%0,%1,%2,%3};"
+               : "+f"(d[0]), "+f"(d[1]), "+f"(d[2]), "+f"(d[3])
+               : "r"(a0), "r"(a1), "r"(a2), "r"(a3), "r"(b0), "r"(b1));
+}
+__device__ __forceinline__ void ldmatrix_x4_trans(uint32_t (&r)[4], uint32_t smem_addr) {
+  asm volatile("ldmatrix.sync.aligned.m8n8.x4.trans.shared.b16 {%0,%1,%2,%3}, [%4];"
+               : "=r"(r[0]), "=r"(r[1]), "=r"(r[2]), "=r"(r[3]) : "r"(smem_addr));
+}
+
+__global__ void __launch_bounds__(DEC_THREADS, 2) attn_decode_mma_kernel(const bf16* __restrict__ qkv, const bf16* __restrict__ ck,
+                                                                         const bf16* __restrict__ cv, const int* __restrict__ lens, bf16* out,
+                                                                         const bf16* __restrict__ prefix_kv, const float* __restrict__ gate,
+                                                                         int max_len, int G, int qpk, int prefix_len, long long ld_qkv, float scale) {
+  extern __shared__ __align__(128) uint8_t sdm[];
+  uint8_t* vt = sdm;                                                    // [8 warps][2][16 keys][128 B], later [8][8][64] floats
+  float* spart = reinterpret_cast<float*>(sdm);
+  float* sout = reinterpret_cast<float*>(sdm + DM_VT_BYTES);            // [8][64]
+  float* sinv = sout + DEC_MAX_QPK * HD;                                // [8] 1 / sum, [8] spare
+  float* sc = sinv + 2 * DEC_MAX_QPK;                                   // [qpk][stride] scores / probabilities
+  const int stride = max_len + 20;                                      // multiple of 4 (8-byte P loads), rows 16 keys apart in banks
+  const int seq = blockIdx.x, g = blockIdx.y;
+  const int tid = threadIdx.x, warp = tid >> 5, lane = tid & 31;
+  const int r = lane >> 2, q = lane & 3;                                // MMA fragment coordinates: row / column group, k pair
+  const int H = G * qpk;
+  const int len = lens[seq];
+  const bf16* qrow = qkv + (long long)seq * ld_qkv + (long long)(g * (qpk + 2)) * HD;
+  const bf16* kg = ck + ((long long)seq * G + g) * max_len * HD;
+  const bf16* vg = cv + ((long long)seq * G + g) * max_len * HD;
+
+  // ---- scores: A = Q (head r, unscaled bf16), B = K^T, fp32 accumulate, scale applied to the result ----
+  {
+    uint4 qa[2] = {make_uint4(0, 0, 0, 0), make_uint4(0, 0, 0, 0)};
+    if (r < qpk) {
+      qa[0] = *reinterpret_cast<const uint4*>(qrow + r * HD + 8 * q);
+      qa[1] = *reinterpret_cast<const uint4*>(qrow + r * HD + 32 + 8 * q);
+    }
+    const int nblk = (len + 7) >> 3;
+    for (int b0 = warp; b0 < nblk; b0 += 64) {        // 8 key blocks (16 independent 16-byte loads) in flight per thread
+      uint4 kv[8][2];
+#pragma unroll
+      for (int u = 0; u < 8; ++u) {
+        const int key = (b0 + 8 * u) * 8 + r;
+        const bool ok = key < len;
+        const uint4* kp = reinterpret_cast<const uint4*>(kg + (long long)key * HD + 8 * q);
+        kv[u][0] = ok ? __ldg(kp) : make_uint4(0, 0, 0, 0);
+        kv[u][1] = ok ? __ldg(kp + 4) : make_uint4(0, 0, 0, 0);
+      }
+#pragma unroll
+      for (int u = 0; u < 8; ++u) {
+        const int key0 = (b0 + 8 * u) * 8;
+        if (key0 < len) {                             // warp-uniform
+          float c[4] = {0.f, 0.f, 0.f, 0.f};
+          mma_bf16_16816(c, qa[0].x, 0u, qa[0].y, 0u, kv[u][0].x, kv[u][0].y);
+          mma_bf16_16816(c, qa[0].z, 0u, qa[0].w, 0u, kv[u][0].z, kv[u][0].w);
+          mma_bf16_16816(c, qa[1].x, 0u, qa[1].y, 0u, kv[u][1].x, kv[u][1].y);
+          mma_bf16_16816(c, qa[1].z, 0u, qa[1].w, 0u, kv[u][1].z, kv[u][1].w);
+          const int k = key0 + 2 * q;
+          if (r < qpk) {
+            if (k < len) sc[r * stride + k] = c[0] * scale;
+            if (k + 1 < len) sc[r * stride + k + 1] = c[1] * scale;
+          }
+        }
+      }
+    }
+  }
+  // the first two V blocks of this warp are requested before the softmax: their latency hides behind it
+  const int nblk16 = (len + 15) >> 4;
+  auto load_block = [&](int blk, uint4 (&v)[4]) {   // this lane's four 16-byte chunks of a 16 x 128 B tile: e = lane + 32 i -> key e / 8, chunk e % 8
+#pragma unroll
+    for (int i = 0; i < 4; ++i) {
+      const int e = lane + 32 * i, key = blk * 16 + (e >> 3);
+      v[i] = (blk < nblk16 && key < len) ? __ldg(reinterpret_cast<const uint4*>(vg + (long long)key * HD) + (e & 7)) : make_uint4(0, 0, 0, 0);
+    }
+  };
+  uint4 vreg0[4], vreg1[4];
+  load_block(warp, vreg0);
+  load_block(warp + 8, vreg1);
+  // gate * softmax(q . prefix_k) prefix_v of head `warp` (its own softmax, ger/adapter.py:139-146) depends on q only: it is
+  // computed here, while the K / V requests above are in flight, instead of at the tail of the block
+  float pfx0 = 0.f, pfx1 = 0.f;
+  if (warp < qpk && prefix_len > 0) {
+    const float q0 = __bfloat162float(qrow[warp * HD + lane]) * scale, q1 = __bfloat162float(qrow[warp * HD + lane + 32]) * scale;
+    const long long koff = (long long)(g * (qpk + 2) + qpk) * HD;
+    float ps[MAX_PREFIX];
+    float pm = -INFINITY;
+#pragma unroll
+    for (int a = 0; a < MAX_PREFIX; ++a) {
+      ps[a] = -INFINITY;
+      if (a < prefix_len) {
+        const bf16* kr = prefix_kv + (long long)a * ld_qkv + koff;
+        float s2 = q0 * __bfloat162float(kr[lane]) + q1 * __bfloat162float(kr[lane + 32]);
+        ps[a] = warp_sum(s2);
+        pm = fmaxf(pm, ps[a]);
+      }
+    }
+    float psum = 0.f;
+#pragma unroll
+    for (int a = 0; a < MAX_PREFIX; ++a) {
+      ps[a] = (a < prefix_len) ? __expf(ps[a] - pm) : 0.f;
+      psum += ps[a];
+    }
+    const float gs = gate[g * qpk + warp] / psum;
+#pragma unroll
+    for (int a = 0; a < MAX_PREFIX; ++a) {
+      if (a < prefix_len) {
+        const bf16* vr = prefix_kv + (long long)a * ld_qkv + koff + HD;
+        pfx0 += gs * ps[a] * __bfloat162float(vr[lane]);
+        pfx1 += gs * ps[a] * __bfloat162float(vr[lane + 32]);
+      }
+    }
+  }
+  __syncthreads();
+  // ---- softmax: warp h owns head h; probabilities beyond len (up to the next multiple of 16) are zeroed for the P V tiles ----
+  if (warp < qpk) {
+    float* row = sc + warp * stride;
+    float mx = -INFINITY;
+    for (int k = lane; k < len; k += 32) mx = fmaxf(mx, row[k]);
+    mx = warp_max(mx);
+    float sum = 0.f;
+    for (int k = lane; k < len; k += 32) {
+      const float e = __expf(row[k] - mx);
+      row[k] = e;
+      sum += e;
+    }
+    sum = warp_sum(sum);
+    if (lane == 0) sinv[warp] = 1.f / sum;
+    if (lane < 16 && len + lane < ((len + 15) & ~15)) row[len + lane] = 0.f;
+  }
+  __syncthreads();
+  // ---- P V: 16 keys per step; V rows -> swizzled per-warp tile -> ldmatrix.trans; P packed to bf16 from shared memory ----
+  float acc[8][4];
+#pragma unroll
+  for (int nb = 0; nb < 8; ++nb)
+#pragma unroll
+    for (int j = 0; j < 4; ++j) acc[nb][j] = 0.f;
+  {
+    uint8_t* mytile = vt + warp * 4096;
+    const uint32_t mytile_s = smem_u32(mytile);
+    const int nblk = nblk16;
+    // one 16-key step out of buffer `buf` (compile-time, so the two register sets stay in registers)
+    auto step = [&](int blk, int buf, uint4 (&vr)[4]) {
+      uint8_t* tile = mytile + buf * 2048;
+#pragma unroll
+      for (int i = 0; i < 4; ++i) {
+        const int e = lane + 32 * i, key = e >> 3, c = e & 7;
+        *reinterpret_cast<uint4*>(tile + key * 128 + ((c ^ (key & 7)) << 4)) = vr[i];
+      }
+      load_block(blk + 16, vr);                        // two blocks ahead: the rows are in flight during this and the next step
+      __syncwarp();
+      // A = P[head r][16 keys]: a0 = keys 2q, 2q+1 ; a2 = keys 2q+8, 2q+9 (rows 8..15 of the tile are unused: a1 = a3 = 0)
+      uint32_t a0 = 0u, a2 = 0u;
+      if (r < qpk) {
+        const float* pr = sc + r * stride + blk * 16 + 2 * q;
+        const float2 p0 = *reinterpret_cast<const float2*>(pr), p1 = *reinterpret_cast<const float2*>(pr + 8);
+        a0 = pack_bf16x2(p0.x, p0.y);
+        a2 = pack_bf16x2(p1.x, p1.y);
+      }
+      const uint32_t tile_s = mytile_s + buf * 2048;
+      // ldmatrix x4: lane supplies the row address of matrix m = lane / 8 (keys 8 (m & 1) .. +7, dim block 2 j + (m >> 1))
+      const int m = lane >> 3, key = 8 * (m & 1) + (lane & 7);
+#pragma unroll
+      for (int j = 0; j < 4; ++j) {
+        const int c = 2 * j + (m >> 1);
+        uint32_t b[4];
+        ldmatrix_x4_trans(b, tile_s + key * 128 + ((c ^ (key & 7)) << 4));
+        mma_bf16_16816(acc[2 * j], a0, 0u, a2, 0u, b[0], b[1]);
+        mma_bf16_16816(acc[2 * j + 1], a0, 0u, a2, 0u, b[2], b[3]);
+      }
+      __syncwarp();                                    // this buffer is rewritten two steps later
+    };
+    for (int blk = warp; blk < nblk; blk += 16) {
+      step(blk, 0, vreg0);
+      if (blk + 8 < nblk) step(blk + 8, 1, vreg1);
+    }
+  }
+  __syncthreads();                                     // every warp is done with its V tiles: the region becomes the partial outputs
+  if (r < DEC_MAX_QPK) {
+#pragma unroll
+    for (int nb = 0; nb < 8; ++nb)
+      *reinterpret_cast<float2*>(spart + (warp * 8 + r) * HD + 8 * nb + 2 * q) = make_float2(acc[nb][0], acc[nb][1]);
+  }
+  __syncthreads();
+  for (int i = tid; i < DEC_MAX_QPK * HD; i += DEC_THREADS) {
+    float a = 0.f;
+#pragma unroll
+    for (int w = 0; w < 8; ++w) a += spart[w * 8 * HD + i];
+    sout[i] = a * sinv[i >> 6];
+  }
+  __syncthreads();
+  if (warp >= qpk) return;
+  // ---- warp h finishes head h: + gate * softmax(q . prefix_k) prefix_v (its own softmax, ger/adapter.py:139-146) ----
+  const int h = g * qpk + warp;
+  const float o0 = sout[warp * HD + lane] + pfx0, o1 = sout[warp * HD + lane + 32] + pfx1;
+  bf16* orow = out + (long long)seq * H * HD + h * HD;
+  orow[lane] = __float2bfloat16_rn(o0);
+  orow[lane + 32] = __float2bfloat16_rn(o1);
+}
+
 // ---------------------------------------------------------------------------------------------
 // host
 // ---------------------------------------------------------------------------------------------
@@ -1540,17 +1756,29 @@ extern "C" int dh_attention_decode(const void* qkv, const void* cache_k, const v
   DH_CHECK(qkv && cache_k && cache_v && lens && out && nseq > 0, "dh_attention_decode: bad argument");
   DH_CHECK(q_per_kv <= DEC_MAX_QPK, "dh_attention_decode: q_per_kv %d > %d", q_per_kv, DEC_MAX_QPK);
   DH_CHECK(prefix_len >= 0 && prefix_len <= MAX_PREFIX, "dh_attention_decode: prefix_len too large");
-  const size_t smem = ((size_t)DEC_FIXED_FLOATS + (size_t)q_per_kv * (max_len + 1)) * sizeof(float);
-  DH_CHECK(smem <= 200 * 1024, "dh_attention_decode: max_len %d too large for the score buffer", max_len);
-  static bool attr = false;
-  if (!attr) {
+  static int variant = -1;      // DH_DEC_CUDA_CORES=1 selects the CUDA-core kernel (A/B runs); default: mma.sync tiles
+  if (variant < 0) {
+    const char* e = getenv("DH_DEC_CUDA_CORES");
+    variant = (e && e[0] == '1') ? 0 : 1;
     DH_CUDA(cudaFuncSetAttribute(attn_decode_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, 200 * 1024));
-    attr = true;
+    DH_CUDA(cudaFuncSetAttribute(attn_decode_mma_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, 200 * 1024));
   }
   const long long ld = (long long)n_groups * (q_per_kv + 2) * HD;
-  attn_decode_kernel<<<dim3(nseq, n_groups), DEC_THREADS, smem, (cudaStream_t)stream>>>(
-      (const bf16*)qkv, (const bf16*)cache_k, (const bf16*)cache_v, lens, (bf16*)out, (const bf16*)(prefix_len > 0 ? prefix_kv : nullptr),
-      gate, max_len, n_groups, q_per_kv, prefix_kv ? prefix_len : 0, ld, 1.0f / sqrtf((float)HD));
+  const bf16* pkv = (const bf16*)(prefix_len > 0 ? prefix_kv : nullptr);
+  const int plen = prefix_kv ? prefix_len : 0;
+  const float scale = 1.0f / sqrtf((float)HD);
+  if (variant == 1) {
+    const size_t smem = (size_t)DM_FIXED_BYTES + (size_t)q_per_kv * (max_len + 20) * sizeof(float);
+    DH_CHECK(smem <= 200 * 1024, "dh_attention_decode: max_len %d too large for the score buffer", max_len);
+    DH_CHECK((((uintptr_t)qkv | (uintptr_t)cache_k | (uintptr_t)cache_v) & 15) == 0, "dh_attention_decode: operands must be 16-byte aligned");
+    attn_decode_mma_kernel<<<dim3(nseq, n_groups), DEC_THREADS, smem, (cudaStream_t)stream>>>(
+        (const bf16*)qkv, (const bf16*)cache_k, (const bf16*)cache_v, lens, (bf16*)out, pkv, gate, max_len, n_groups, q_per_kv, plen, ld, scale);
+  } else {
+    const size_t smem = ((size_t)DEC_FIXED_FLOATS + (size_t)q_per_kv * (max_len + 1)) * sizeof(float);
+    DH_CHECK(smem <= 200 * 1024, "dh_attention_decode: max_len %d too large for the score buffer", max_len);
+    attn_decode_kernel<<<dim3(nseq, n_groups), DEC_THREADS, smem, (cudaStream_t)stream>>>(
+        (const bf16*)qkv, (const bf16*)cache_k, (const bf16*)cache_v, lens, (bf16*)out, pkv, gate, max_len, n_groups, q_per_kv, plen, ld, scale);
+  }
   DH_CUDA(cudaGetLastError());
   return 0;
 }
