@@ -53,6 +53,7 @@ SIGNATURES = {
     "dh_gemm": (_I, [C.POINTER(GemmArgs), _P]),
     "dh_rmsnorm_fwd": (_I, [_P, _I, _P, _P, _P, _I, _I, _F, _P]),
     "dh_splitk_resid_rmsnorm": (_I, [_P, _I, _L, _P, _P, _P, _P, _I, _I, _F, _P]),
+    "dh_splitk_qkv_rope_cache": (_I, [_P, _I, _L, _P, _P, _P, _P, _P, _P, _P, _I, _I, _I, _I, _P]),
     "dh_rmsnorm_bwd": (_I, [_P, _I, _P, _P, _P, _P, _P, _P, _I, _I, _P]),
     "dh_embedding_fwd": (_I, [_P, _P, _I, _P, _I, _I, _I, _I, _P]),
     "dh_rope_apply": (_I, [_P, _P, _P, _P, _I, _I, _I, _I, _I, _I, _I, _I, _P]),

@@ -88,17 +88,17 @@ __global__ void splitk_resid_rmsnorm_kernel(const float* __restrict__ partial, i
 #pragma unroll
   for (int i = 0; i < 8; ++i) acc[i] = 0.f;
   const float* prow = partial + row * C + c0;
-  for (int s0 = 0; s0 < splits; s0 += 4) {          // 4 splits (8 independent 16-byte loads) in flight per thread
-    float t[4][8];
+  for (int s0 = 0; s0 < splits; s0 += 8) {          // 8 splits (16 independent 16-byte loads) in flight per thread
+    float t[8][8];
 #pragma unroll
-    for (int u = 0; u < 4; ++u)
+    for (int u = 0; u < 8; ++u)
       if (s0 + u < splits) {
         const float4 a = __ldcg(reinterpret_cast<const float4*>(prow + (s0 + u) * split_stride));
         const float4 b = __ldcg(reinterpret_cast<const float4*>(prow + (s0 + u) * split_stride) + 1);
         t[u][0] = a.x; t[u][1] = a.y; t[u][2] = a.z; t[u][3] = a.w; t[u][4] = b.x; t[u][5] = b.y; t[u][6] = b.z; t[u][7] = b.w;
       }
 #pragma unroll
-    for (int u = 0; u < 4; ++u)
+    for (int u = 0; u < 8; ++u)
       if (s0 + u < splits) {
 #pragma unroll
         for (int i = 0; i < 8; ++i) acc[i] += t[u][i];
@@ -118,6 +118,62 @@ __global__ void splitk_resid_rmsnorm_kernel(const float* __restrict__ partial, i
 #pragma unroll
   for (int i = 0; i < 8; ++i) v[i] = g[i] * (v[i] * r);
   store8(y + row * C + c0, v);
+}
+
+// Decode: consumer of the split-K QKV GEMM.  One block per token row, one thread per 8 columns of a 64-wide head slot:
+//   qkv = bf16(sum_s partial[s])  -> NeoX RoPE on the q and k slots at the row's position (the DH_EPI_QKV_ROPE math:
+//   bf16-rounded product, bf16 tables, pairs (j, j + 32)) -> bf16 qkv row, and the k / v slots also go to the KV cache at
+//   (seq[row], pos[row]) -- reduction + ger/model.py:240-246 + the cache update :248-259 in one launch.
+__global__ void splitk_qkv_rope_cache_kernel(const float* __restrict__ partial, int splits, long long split_stride, bf16* __restrict__ qkv,
+                                             bf16* ck, bf16* cv, const int* __restrict__ seq, const int* __restrict__ pos,
+                                             const bf16* __restrict__ rope_cos, const bf16* __restrict__ rope_sin, int N, int max_len,
+                                             int n_groups, int qpk) {
+  const long long row = blockIdx.x;
+  const int p = pos[row];
+  for (int t = threadIdx.x; t < N / 16; t += blockDim.x) {       // thread: columns [j, j + 8) and [j + 32, j + 40) of one head slot
+    const int slot = t >> 2, j = (t & 3) * 8;
+    const float* pr = partial + row * N + slot * 64 + j;
+    float lo[8], hi[8];
+#pragma unroll
+    for (int i = 0; i < 8; ++i) lo[i] = hi[i] = 0.f;
+    for (int s0 = 0; s0 < splits; s0 += 4) {
+      float4 a[4][4];
+#pragma unroll
+      for (int u = 0; u < 4; ++u)
+        if (s0 + u < splits) {
+          const float4* q4 = reinterpret_cast<const float4*>(pr + (s0 + u) * split_stride);
+          a[u][0] = __ldcg(q4); a[u][1] = __ldcg(q4 + 1); a[u][2] = __ldcg(q4 + 8); a[u][3] = __ldcg(q4 + 9);
+        }
+#pragma unroll
+      for (int u = 0; u < 4; ++u)
+        if (s0 + u < splits) {
+          lo[0] += a[u][0].x; lo[1] += a[u][0].y; lo[2] += a[u][0].z; lo[3] += a[u][0].w;
+          lo[4] += a[u][1].x; lo[5] += a[u][1].y; lo[6] += a[u][1].z; lo[7] += a[u][1].w;
+          hi[0] += a[u][2].x; hi[1] += a[u][2].y; hi[2] += a[u][2].z; hi[3] += a[u][2].w;
+          hi[4] += a[u][3].x; hi[5] += a[u][3].y; hi[6] += a[u][3].z; hi[7] += a[u][3].w;
+        }
+    }
+    const int in_group = slot % (qpk + 2), g = slot / (qpk + 2);
+    if (in_group <= qpk) {                                        // q heads and the k head rotate; v passes through
+      float c[8], sn[8];
+      load8(rope_cos + (long long)p * 64 + j, c);                 // table halves are identical (repeat(1, 2))
+      load8(rope_sin + (long long)p * 64 + j, sn);
+#pragma unroll
+      for (int i = 0; i < 8; ++i) {
+        const float x1 = __bfloat162float(__float2bfloat16_rn(lo[i])), x2 = __bfloat162float(__float2bfloat16_rn(hi[i]));
+        lo[i] = x1 * c[i] - x2 * sn[i];
+        hi[i] = x2 * c[i] + x1 * sn[i];
+      }
+    }
+    bf16* dst = qkv + row * N + slot * 64 + j;
+    store8(dst, lo);
+    store8(dst + 32, hi);
+    if (in_group >= qpk) {                                        // k or v slot: also into the cache
+      bf16* cd = (in_group == qpk ? ck : cv) + (((long long)seq[row] * n_groups + g) * max_len + p) * 64 + j;
+      store8(cd, lo);
+      store8(cd + 32, hi);
+    }
+  }
 }
 
 // dx = dres + rstd * (w*dy - xhat * mean(w*dy*xhat)),  xhat = x*rstd
@@ -540,6 +596,22 @@ extern "C" int dh_splitk_resid_rmsnorm(const float* partial, int splits, long lo
   DH_CHECK(C % 256 == 0 && C <= 8192, "dh_splitk_resid_rmsnorm: C=%d must be a multiple of 256 and <= 8192", C);
   DH_CHECK(split_stride >= (long long)M * C && split_stride % 4 == 0, "dh_splitk_resid_rmsnorm: bad split stride");
   splitk_resid_rmsnorm_kernel<<<M, C / 8, 0, (cudaStream_t)stream>>>(partial, splits, split_stride, resid, weight, x_out, (bf16*)y, C, eps);
+  DH_CUDA(cudaGetLastError());
+  return 0;
+}
+
+extern "C" int dh_splitk_qkv_rope_cache(const float* partial, int splits, long long split_stride, void* qkv, void* cache_k, void* cache_v,
+                                        const int32_t* seq, const int32_t* pos, const void* rope_cos, const void* rope_sin, int M, int max_len,
+                                        int n_groups, int q_per_kv, void* stream) {
+  DH_CHECK(partial && qkv && cache_k && cache_v && seq && pos && rope_cos && rope_sin && M > 0 && splits > 0,
+           "dh_splitk_qkv_rope_cache: bad argument");
+  const int N = n_groups * (q_per_kv + 2) * 64;
+  DH_CHECK(split_stride >= (long long)M * N && split_stride % 4 == 0, "dh_splitk_qkv_rope_cache: bad split stride");
+  int threads = N / 16;
+  threads = threads > 256 ? 256 : ((threads + 31) / 32) * 32;
+  splitk_qkv_rope_cache_kernel<<<M, threads, 0, (cudaStream_t)stream>>>(partial, splits, split_stride, (bf16*)qkv, (bf16*)cache_k, (bf16*)cache_v,
+                                                                       seq, pos, (const bf16*)rope_cos, (const bf16*)rope_sin, N, max_len,
+                                                                       n_groups, q_per_kv);
   DH_CUDA(cudaGetLastError());
   return 0;
 }

@@ -472,18 +472,24 @@ class DecoderEngine:
         sk_ok = n_seq <= 128 and C % 128 == 0
         s_proj, s_mlp = (ops.decode_split_k(C, C), ops.decode_split_k(C, I)) if sk_ok else (1, 1)
         ws = self._buf("dec_splitk", (max(s_proj, s_mlp), n_seq, C), f32) if (s_proj > 1 or s_mlp > 1) else None
+        s_qkv = ops.decode_split_k(s.qkv_out, C) if (n_seq <= 128 and s.qkv_out % 128 == 0) else 1
+        ws_q = self._buf("dec_splitk_qkv", (s_qkv, n_seq, s.qkv_out), f32) if s_qkv > 1 else None
         ops.rmsnorm_fwd(x, self.layers[0]["norm1"], n, None, s.norm_eps)
         for i, lw in enumerate(self.layers):
             pk = packed.get(i, {})
+            a2q = b2q = None
             if "qkv_a" in pk:
-                a_s = self._buf("dec_as", (n_seq, LORA_PAD), bf)
-                ops.gemm(n, pk["qkv_a"], a_s)
-                ops.gemm(n, lw["wqkv"], qkv, A2=a_s, B2=pk["qkv_b"], epilogue=ops.EPI_QKV_ROPE, rope_cos=self.cos, rope_sin=self.sin,
-                         positions=positions, seq_len=1, q_per_kv=qpk)
+                a2q = self._buf("dec_as", (n_seq, LORA_PAD), bf)
+                ops.gemm(n, pk["qkv_a"], a2q)
+                b2q = pk["qkv_b"]
+            if s_qkv > 1:
+                # split-K partial products; one consumer sums them, applies RoPE and writes the qkv row and the KV cache
+                ops.gemm(n, lw["wqkv"], ws_q, A2=a2q, B2=b2q, epilogue=ops.EPI_F32, split_k=s_qkv)
+                ops.splitk_qkv_rope_cache(ws_q, qkv, self.cache_k[i], self.cache_v[i], seq_ids, positions, self.cos, self.sin, G, qpk)
             else:
-                ops.gemm(n, lw["wqkv"], qkv, epilogue=ops.EPI_QKV_ROPE, rope_cos=self.cos, rope_sin=self.sin, positions=positions,
-                         seq_len=1, q_per_kv=qpk)
-            ops.kv_cache_write(qkv, self.cache_k[i], self.cache_v[i], seq_ids, positions, G, qpk)
+                ops.gemm(n, lw["wqkv"], qkv, A2=a2q, B2=b2q, epilogue=ops.EPI_QKV_ROPE, rope_cos=self.cos, rope_sin=self.sin,
+                         positions=positions, seq_len=1, q_per_kv=qpk)
+                ops.kv_cache_write(qkv, self.cache_k[i], self.cache_v[i], seq_ids, positions, G, qpk)
             prefix_kv = gate = None
             if "prefix" in pk:
                 prefix_kv = pkv_all[i - s.adapter_start_layer]

@@ -161,6 +161,21 @@ def splitk_resid_rmsnorm(partial: Tensor, resid: Tensor, weight: Tensor, x_out: 
     _count()
 
 
+@_profiled("splitk_qkv_rope_cache")
+def splitk_qkv_rope_cache(partial: Tensor, qkv: Tensor, cache_k: Tensor, cache_v: Tensor, seq: Tensor, pos: Tensor, cos: Tensor,
+                          sin: Tensor, n_groups: int, q_per_kv: int) -> None:
+    """qkv = RoPE(bf16(sum of the split-K slices)) at pos; k / v slots also into the KV cache at (seq, pos)."""
+    _dev(partial)
+    S, M, N = partial.shape
+    assert partial.is_contiguous() and partial.dtype == torch.float32 and qkv.is_contiguous() and qkv.shape == (M, N)
+    assert N == n_groups * (q_per_kv + 2) * 64 and seq.dtype == torch.int32 and pos.dtype == torch.int32 and cos.dtype == torch.bfloat16
+    assert cache_k.is_contiguous() and cache_v.is_contiguous()
+    check(_lib.load().dh_splitk_qkv_rope_cache(partial.data_ptr(), S, M * N, qkv.data_ptr(), cache_k.data_ptr(), cache_v.data_ptr(),
+                                               seq.data_ptr(), pos.data_ptr(), cos.data_ptr(), sin.data_ptr(), M, cache_k.shape[2],
+                                               n_groups, q_per_kv, _stream()), "dh_splitk_qkv_rope_cache")
+    _count()
+
+
 def sm_count() -> int:
     return int(_lib.load().dh_sm_count()) or 148
 
@@ -170,7 +185,7 @@ def decode_split_k(N: int, K: int) -> int:
     at least two 64-wide k-blocks per CTA."""
     sms = int(_lib.load().dh_sm_count()) or 148
     tiles = max(1, N // 128)
-    return max(1, min(sms // tiles, (K // 64) // 2, 16))
+    return max(1, min(sms // tiles, (K // 64) // 2, 8))
 
 
 @_profiled("rmsnorm_bwd")

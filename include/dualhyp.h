@@ -96,6 +96,12 @@ int dh_rmsnorm_fwd(const void* x, int x_dtype, const float* weight, void* y, flo
  * x_out may alias resid. */
 int dh_splitk_resid_rmsnorm(const float* partial, int splits, long long split_stride, const float* resid, const float* weight,
                             float* x_out, void* y, int M, int C, float eps, void* stream);
+/* Decode: consumer of the split-K QKV dh_gemm.  partial f32 [splits][M][N], N = n_groups*(qpk+2)*64:
+ *   qkv bf16 [M,N] = RoPE(bf16(sum_s partial[s])) on the q and k slots at pos[row] (the DH_EPI_QKV_ROPE math, ger/model.py:240-246),
+ *   and the k / v slots are also written to the KV cache at (seq[row], pos[row]) (ger/model.py:248-259) -- one launch. */
+int dh_splitk_qkv_rope_cache(const float* partial, int splits, long long split_stride, void* qkv, void* cache_k, void* cache_v,
+                             const int32_t* seq, const int32_t* pos, const void* rope_cos, const void* rope_sin, int M, int max_len,
+                             int n_groups, int q_per_kv, void* stream);
 /* Backward of the above w.r.t. x (weights are frozen on this path).  dy bf16 [M,C].
  * dx_out f32 [M,C] = (dres ? dres : 0) + d(rmsnorm)/dx ; dx_bf16 (optional) = bf16(dx_out).
  * dres may alias dx_out. */

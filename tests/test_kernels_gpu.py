@@ -212,6 +212,34 @@ def test_gemm_split_k_partials_and_fused_consumer(M, S):
     assert torch.equal(x1, x2) and torch.equal(n1, n2)
 
 
+@pytest.mark.parametrize("M,G,qpk,S", [(64, 4, 8, 7), (3, 2, 2, 2), (128, 1, 1, 4)])
+def test_splitk_qkv_rope_cache_consumer(M, G, qpk, S):
+    """Split-K QKV partial products -> dh_splitk_qkv_rope_cache must equal the fused DH_EPI_QKV_ROPE GEMM followed by
+    dh_kv_cache_write up to the summation order (checked against fp32 math at bf16 tolerance; the cache rows must be the
+    k / v slots of the produced qkv row bit for bit)."""
+    C, N, max_len = 2048, G * (qpk + 2) * 64, 96
+    x, W = rnd((M, C), 341), rnd((N, C), 342, bound=1 / 32)
+    cos, sin = O.build_rope_cache(max_len, 64)
+    cos, sin = cos.to(DEV), sin.to(DEV)
+    pos = synthetic.hash_ints((M,), 5, 343, 0, max_len).to(torch.int32).to(DEV)
+    seq = torch.arange(M, device=DEV, dtype=torch.int32)
+    ws = torch.full((S, M, N), float("nan"), device=DEV, dtype=torch.float32)
+    qkv = torch.full((M, N), float("nan"), device=DEV, dtype=torch.bfloat16)
+    ck = torch.zeros((M, G, max_len, 64), device=DEV, dtype=torch.bfloat16)
+    cv = torch.zeros_like(ck)
+    ops.gemm(x, W, ws, epilogue=ops.EPI_F32, split_k=S)
+    ops.splitk_qkv_rope_cache(ws, qkv, ck, cv, seq, pos, cos, sin, G, qpk)
+    ref = torch.empty((M, N), device=DEV, dtype=torch.bfloat16)
+    ops.gemm(x, W, ref, epilogue=ops.EPI_QKV_ROPE, rope_cos=cos, rope_sin=sin, positions=pos, seq_len=1, q_per_kv=qpk)
+    torch.cuda.synchronize()
+    assert rel(qkv, ref) < 6e-3, report("qkv consumer", qkv, ref)
+    got = qkv.view(M, G, qpk + 2, 64)
+    rows = torch.arange(M, device=DEV)
+    for g in range(G):
+        assert torch.equal(ck[rows, g, pos.long()], got[:, g, qpk]) and torch.equal(cv[rows, g, pos.long()], got[:, g, qpk + 1])
+    assert int((ck != 0).any(-1).sum()) <= M * G and int((cv != 0).any(-1).sum()) <= M * G       # nothing else was written
+
+
 def _interleave(w1, w2):
     I = w1.shape[0]
     return torch.stack((w1.view(I // 32, 32, -1), w2.view(I // 32, 32, -1)), dim=1).reshape(2 * I, -1)
