@@ -363,9 +363,29 @@ __global__ void __launch_bounds__(256) argmax_kernel(const bf16* __restrict__ lo
   const bf16* l = logits + row * ldl;
   float best = -INFINITY;
   int bi = 0x7fffffff;
-  for (int i = threadIdx.x; i < V; i += blockDim.x) {
-    float v = __bfloat162float(l[i]);
-    if (v > best) { best = v; bi = i; }   // strided scan keeps the lowest index per thread
+  if ((((uintptr_t)l) & 15) == 0 && (V & 7) == 0) {
+    // 16-byte loads (8 logits), two in flight per thread; ascending order + strict '>' keep the lowest index per thread
+    const uint4* l4 = reinterpret_cast<const uint4*>(l);
+    const int n4 = V >> 3;
+    for (int i = threadIdx.x; i < n4; i += 2 * blockDim.x) {
+      const int i2 = i + blockDim.x;
+      const uint4 a = __ldg(l4 + i);
+      const uint4 b = i2 < n4 ? __ldg(l4 + i2) : make_uint4(0xff80ff80u, 0xff80ff80u, 0xff80ff80u, 0xff80ff80u);   // -inf
+      float f[8];
+      unpack8(a, f);
+#pragma unroll
+      for (int j = 0; j < 8; ++j)
+        if (f[j] > best) { best = f[j]; bi = 8 * i + j; }
+      unpack8(b, f);
+#pragma unroll
+      for (int j = 0; j < 8; ++j)
+        if (f[j] > best) { best = f[j]; bi = 8 * i2 + j; }
+    }
+  } else {
+    for (int i = threadIdx.x; i < V; i += blockDim.x) {
+      float v = __bfloat162float(l[i]);
+      if (v > best) { best = v; bi = i; }   // strided scan keeps the lowest index per thread
+    }
   }
 #pragma unroll
   for (int o = 16; o > 0; o >>= 1) {
