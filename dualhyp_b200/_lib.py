@@ -59,6 +59,7 @@ SIGNATURES = {
     "dh_rope_apply": (_I, [_P, _P, _P, _P, _I, _I, _I, _I, _I, _I, _I, _I, _P]),
     "dh_rope_qkv_inplace": (_I, [_P, _P, _P, _P, _I, _I, _I, _I, _I, _P]),
     "dh_attention_fwd": (_I, [_P, _P, _P, _P, _P, _I, _I, _I, _I, _I, _P]),
+    "dh_attention_fwd_varlen": (_I, [_P, _P, _P, _P, _P, _P, _I, _I, _L, _I, _I, _I, _P]),
     "dh_attention_bwd_workspace": (_Z, [_I, _I, _I, _I]),
     "dh_attention_bwd": (_I, [_P, _P, _P, _P, _P, _P, _P, _P, _P, _I, _P, _P, _I, _I, _I, _I, _I, _P, _Z, _P]),
     "dh_attention_decode": (_I, [_P, _P, _P, _P, _P, _P, _P, _I, _I, _I, _I, _I, _P]),

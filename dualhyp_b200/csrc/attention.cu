@@ -88,6 +88,9 @@ struct AttnParams {
   int need_dqkv;
   const bf16* rope_cos;
   const bf16* rope_sin;
+  // forward over packed variable-length sequences (no pad rows): sequence b = rows [cu[b], cu[b + 1]); NULL = B x T
+  const int* cu_seqlens;
+  long long total_rows;
 };
 
 __device__ __forceinline__ void load_prefix_to_smem(const AttnParams& p, int g, float* sak, float* sav) {
@@ -212,11 +215,14 @@ __global__ void __launch_bounds__(FWD_THREADS, 2) attn_fwd_kernel(const __grid_c
   const int warp = __shfl_sync(0xffffffffu, threadIdx.x >> 5, 0), lane = threadIdx.x & 31;   // shfl: warp-uniform for the compiler
   TRC_DECL
   TRC(0);
-  const int nq = (p.T + ATT_BQ - 1) / ATT_BQ;
   const int h = blockIdx.y, b = blockIdx.z;
+  // one length per batch (rows b T .. b T + T), or packed sequences of their own lengths starting at cu_seqlens[b]
+  const int row_base = p.cu_seqlens ? __ldg(p.cu_seqlens + b) : b * p.T;
+  const int T_b = p.cu_seqlens ? __ldg(p.cu_seqlens + b + 1) - row_base : p.T;
+  const int nq = (T_b + ATT_BQ - 1) / ATT_BQ;
+  if ((int)blockIdx.x >= (nq + 1) / 2) return;      // the grid is sized for the longest sequence
   const int g = h / p.qpk;
   const int q_slot = g * (p.qpk + 2) + (h % p.qpk), k_slot = g * (p.qpk + 2) + p.qpk, v_slot = k_slot + 1;
-  const int row_base = b * p.T;
   const int qi_first = nq - 1 - (int)blockIdx.x, qi_second = (int)blockIdx.x;
   const int n_items = (qi_first == qi_second) ? 1 : 2;
   const bool has_prefix = p.prefix_len > 0;
@@ -469,7 +475,7 @@ __global__ void __launch_bounds__(FWD_THREADS, 2) attn_fwd_kernel(const __grid_c
       tc_fence_after();
       const float inv_l = 1.f / l;
       // TMEM loads are .sync.aligned: every lane issues them; only the global stores are predicated.
-      const bool valid = tq < p.T;
+      const bool valid = tq < T_b;
       bf16* orow = p.out + (long long)(row_base + (valid ? tq : 0)) * (p.H * HD) + h * HD + 32 * hf;
       uint32_t o[32];
       tmem_ld32(tO + lane_off + 32 * hf, o);
@@ -486,7 +492,10 @@ __global__ void __launch_bounds__(FWD_THREADS, 2) attn_fwd_kernel(const __grid_c
           u.w = pack_bf16x2(__uint_as_float(o[8 * i + 6]) * inv_l, __uint_as_float(o[8 * i + 7]) * inv_l);
           o4[i] = u;
         }
-        if (hf == 0) p.lse[((long long)b * p.H + h) * p.T + tq] = (m_ref + log2f(l)) * LN2;
+        if (hf == 0) {
+          const long long li = p.cu_seqlens ? (long long)h * p.total_rows + row_base + tq : ((long long)b * p.H + h) * p.T + tq;
+          p.lse[li] = (m_ref + log2f(l)) * LN2;
+        }
       }
       TRC(8);
     }
@@ -1679,6 +1688,33 @@ extern "C" int dh_attention_fwd(const void* qkv, void* out, float* lse, const vo
   }
   const int nq = (T + ATT_BQ - 1) / ATT_BQ;
   dim3 grid((nq + 1) / 2, p.H, B);
+  attn_fwd_kernel<<<grid, FWD_THREADS, FWD_SMEM, (cudaStream_t)stream>>>(tm, tmp, p);
+  DH_CUDA(cudaGetLastError());
+  return 0;
+}
+
+extern "C" int dh_attention_fwd_varlen(const void* qkv, void* out, float* lse, const void* prefix_kv, const float* gate,
+                                       const int32_t* cu_seqlens, int n_seq, int max_len, long long total_rows, int n_groups, int q_per_kv,
+                                       int prefix_len, void* stream) {
+  DH_CHECK(qkv && out && lse && cu_seqlens && n_seq > 0 && max_len > 0 && total_rows > 0 && n_groups > 0 && q_per_kv > 0,
+           "dh_attention_fwd_varlen: bad argument");
+  DH_CHECK(prefix_len >= 0 && prefix_len <= MAX_PREFIX, "dh_attention_fwd_varlen: prefix_len %d > %d", prefix_len, MAX_PREFIX);
+  DH_CHECK(prefix_len == 0 || (prefix_kv && gate), "dh_attention_fwd_varlen: prefix needs prefix_kv and gate");
+  AttnParams p = {};
+  fill_common(p, n_seq, max_len, n_groups, q_per_kv, prefix_kv ? prefix_len : 0);
+  p.qkv = (const bf16*)qkv; p.out = (bf16*)out; p.lse = lse;
+  p.prefix_kv = (const bf16*)prefix_kv; p.gate = gate;
+  p.cu_seqlens = cu_seqlens; p.total_rows = total_rows;
+  CUtensorMap tm, tmp;
+  if (make_head_map(&tm, qkv, p.slots, total_rows, p.ld_qkv)) return -3;
+  if (make_head_map(&tmp, p.prefix_len > 0 ? prefix_kv : qkv, p.slots, p.prefix_len > 0 ? p.prefix_len : 1, p.ld_qkv, 16)) return -3;
+  static bool attr = false;
+  if (!attr) {
+    DH_CUDA(cudaFuncSetAttribute(attn_fwd_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, FWD_SMEM));
+    attr = true;
+  }
+  const int nq = (max_len + ATT_BQ - 1) / ATT_BQ;
+  dim3 grid((nq + 1) / 2, p.H, n_seq);
   attn_fwd_kernel<<<grid, FWD_THREADS, FWD_SMEM, (cudaStream_t)stream>>>(tm, tmp, p);
   DH_CUDA(cudaGetLastError());
   return 0;

@@ -208,6 +208,19 @@ class DecoderEngine:
             self._bufs[key] = t
         return t
 
+    def _cap_buf(self, name: str, shape, dtype) -> Tensor:
+        """Grow-only flat buffer viewed as `shape`: the inference paths see a different row count for every batch (prompt
+        lengths vary), and an exact-shape cache would keep one full activation set per distinct count."""
+        numel = 1
+        for d in shape:
+            numel *= int(d)
+        key = ("cap", name, dtype)
+        t = self._bufs.get(key)
+        if t is None or t.numel() < numel:
+            cap = ((numel + (1 << 22) - 1) >> 22) << 22          # 4 Mi-element granules
+            t = self._bufs[key] = torch.empty(cap, device=self.device, dtype=dtype)
+        return t[:numel].view(shape)
+
     def release_buffers(self) -> None:
         self._bufs.clear()
         self._saved = None
@@ -215,66 +228,82 @@ class DecoderEngine:
     # ------------------------------------------------------------------------------------------
     # forward over full sequences (training / evaluation / prefill)
     # ------------------------------------------------------------------------------------------
-    def forward_hidden(self, idx: Tensor, packed: Dict[int, Dict[str, Tensor]], save: bool, write_cache: bool = False) -> Tensor:
-        """idx int64 [B, T] -> ln_f output bf16 [B*T, C].  save=True keeps what backward() needs."""
+    def forward_hidden(self, idx: Tensor, packed: Dict[int, Dict[str, Tensor]], save: bool, write_cache: bool = False,
+                       varlen: Optional[Dict] = None) -> Tensor:
+        """idx int64 [B, T] -> ln_f output bf16 [B*T, C].  save=True keeps what backward() needs.
+        varlen (inference only): idx is ONE row of packed sequences [1, M] without pad tokens; `varlen` holds cu_seqlens
+        int32 [n + 1], positions int32 [M] (RoPE position of every row inside its sequence), seq_ids int32 [M] and max_len."""
         s = self.spec
         B, T = idx.shape
-        assert T <= s.block_size, f"Cannot forward sequence of length {T}, block size is only {s.block_size}"
+        if varlen is not None:
+            assert not save and B == 1, "packed variable-length batches are a forward-only (prefill) path"
+            assert varlen["max_len"] <= s.block_size
+        else:
+            assert T <= s.block_size, f"Cannot forward sequence of length {T}, block size is only {s.block_size}"
         M, C, I, G, qpk = B * T, s.n_embd, s.intermediate_size, s.n_query_groups, s.qpk
+        vpos = varlen["positions"] if varlen is not None else None
         L = s.n_layer
         bf, f32 = torch.bfloat16, torch.float32
         idx = idx.contiguous()
         per = (lambda name, i: f"{name}{i}") if save else (lambda name, i: name)
+        _buf = self._buf if save else self._cap_buf          # training: exact shapes kept per layer; inference: grow-only
         # the residual stream alternates between two buffers unless the backward needs every stage
-        x = self._buf(per("x", 0), (M, C), f32)
+        x = _buf(per("x", 0), (M, C), f32)
         ops.embedding_fwd(idx.view(-1), self.wte, x)
-        n = self._buf("n", (M, C), bf)
-        act = self._buf("act", (M, I), bf)
+        n = _buf("n", (M, C), bf)
+        act = _buf("act", (M, I), bf)
         saved = dict(B=B, T=T, layers=[], packed=packed) if save else None
         pkv_all = self._project_prefixes(packed, "pkv_all")
         for i, lw in enumerate(self.layers):
             pk = packed.get(i, {})
-            rstd1 = self._buf(per("rstd1_", i), (M,), f32)
-            n_i = self._buf(per("n1_", i), (M, C), bf) if (save and "qkv_a" in pk) else n
+            rstd1 = _buf(per("rstd1_", i), (M,), f32)
+            n_i = _buf(per("n1_", i), (M, C), bf) if (save and "qkv_a" in pk) else n
             ops.rmsnorm_fwd(x, lw["norm1"], n_i, rstd1, s.norm_eps)
-            qkv = self._buf(per("qkv", i), (M, s.qkv_out), bf)
+            qkv = _buf(per("qkv", i), (M, s.qkv_out), bf)
             a_s = None
             if "qkv_a" in pk:
-                a_s = self._buf(per("qkv_as", i), (M, LORA_PAD), bf)
+                a_s = _buf(per("qkv_as", i), (M, LORA_PAD), bf)
                 ops.gemm(n_i, pk["qkv_a"], a_s)
                 ops.gemm(n_i, lw["wqkv"], qkv, A2=a_s, B2=pk["qkv_b"], epilogue=ops.EPI_QKV_ROPE, rope_cos=self.cos, rope_sin=self.sin,
-                         seq_len=T, q_per_kv=qpk)
+                         positions=vpos, seq_len=T, q_per_kv=qpk)
             else:
-                ops.gemm(n_i, lw["wqkv"], qkv, epilogue=ops.EPI_QKV_ROPE, rope_cos=self.cos, rope_sin=self.sin, seq_len=T, q_per_kv=qpk)
+                ops.gemm(n_i, lw["wqkv"], qkv, epilogue=ops.EPI_QKV_ROPE, rope_cos=self.cos, rope_sin=self.sin, positions=vpos,
+                         seq_len=T, q_per_kv=qpk)
             prefix_kv = gate = None
             if "prefix" in pk:
                 prefix_kv = pkv_all[i - s.adapter_start_layer]
                 gate = pk["gate"]
-            if write_cache:
+            if write_cache and varlen is not None:
+                ops.kv_cache_write(qkv, self.cache_k[i], self.cache_v[i], varlen["seq_ids"], vpos, G, qpk)
+            elif write_cache:
                 self._write_prefill_cache(i, qkv, B, T)
-            y = self._buf(per("y", i), (M, C), bf)
-            lse = self._buf(per("lse", i), (B, s.n_head, T), f32)
-            ops.attention_fwd(qkv, y, lse, B, T, G, qpk, prefix_kv, gate, s.adapter_prompt_length if prefix_kv is not None else 0)
-            xmid = self._buf(per("xmid", i), (M, C), f32)
+            y = _buf(per("y", i), (M, C), bf)
+            lse = _buf(per("lse", i), (B, s.n_head, T), f32)
+            if varlen is not None:
+                ops.attention_fwd_varlen(qkv, y, lse, varlen["cu_seqlens"], varlen["max_len"], G, qpk, prefix_kv, gate,
+                                         s.adapter_prompt_length if prefix_kv is not None else 0)
+            else:
+                ops.attention_fwd(qkv, y, lse, B, T, G, qpk, prefix_kv, gate, s.adapter_prompt_length if prefix_kv is not None else 0)
+            xmid = _buf(per("xmid", i), (M, C), f32)
             ap_s = None
             if "proj_a" in pk:
-                ap_s = self._buf(per("proj_as", i), (M, LORA_PAD), bf)
+                ap_s = _buf(per("proj_as", i), (M, LORA_PAD), bf)
                 ops.gemm(y, pk["proj_a"], ap_s)
                 ops.gemm(y, lw["wproj"], xmid, A2=ap_s, B2=pk["proj_b"], epilogue=ops.EPI_RESID_F32, aux=x)
             else:
                 ops.gemm(y, lw["wproj"], xmid, epilogue=ops.EPI_RESID_F32, aux=x)
-            rstd2 = self._buf(per("rstd2_", i), (M,), f32)
+            rstd2 = _buf(per("rstd2_", i), (M,), f32)
             ops.rmsnorm_fwd(xmid, lw["norm2"], n, rstd2, s.norm_eps)
-            h12 = self._buf(per("h12_", i), (M, 2 * I), bf) if save else None
+            h12 = _buf(per("h12_", i), (M, 2 * I), bf) if save else None
             ops.gemm(n, lw["w12"], h12, epilogue=ops.EPI_SWIGLU, out2=act)
-            x_next = self._buf(per("x", i + 1), (M, C), f32) if save else self._buf("x_alt" if (i % 2 == 0) else "x", (M, C), f32)
+            x_next = _buf(per("x", i + 1), (M, C), f32) if save else _buf("x_alt" if (i % 2 == 0) else "x", (M, C), f32)
             ops.gemm(act, lw["wmlp"], x_next, epilogue=ops.EPI_RESID_F32, aux=xmid)
             if save:
                 saved["layers"].append(dict(x=x, xmid=xmid, rstd1=rstd1, rstd2=rstd2, qkv=qkv, y=y, lse=lse, h12=h12, n1=n_i,
                                             a_s=a_s, ap_s=ap_s, prefix_kv=prefix_kv, gate=gate))
             x = x_next
-        hidden = self._buf("hidden", (M, C), bf)
-        rstd_f = self._buf("rstd_f", (M,), f32)
+        hidden = _buf("hidden", (M, C), bf)
+        rstd_f = _buf("rstd_f", (M,), f32)
         ops.rmsnorm_fwd(x, self.ln_f, hidden, rstd_f, s.norm_eps)
         if save:
             saved["x_final"], saved["rstd_f"] = x, rstd_f
@@ -435,6 +464,14 @@ class DecoderEngine:
             seq.copy_(torch.arange(B, device=self.device, dtype=torch.int32).repeat_interleave(T))
             pos.copy_(torch.arange(T, device=self.device, dtype=torch.int32).repeat(B))
         ops.kv_cache_write(qkv, self.cache_k[layer], self.cache_v[layer], seq, pos, self.spec.n_query_groups, self.spec.qpk)
+
+    def prefill_packed(self, ids: Tensor, cu_seqlens: Tensor, positions: Tensor, seq_ids: Tensor, max_len: int,
+                       packed: Dict[int, Dict[str, Tensor]]) -> Tensor:
+        """Causal forward over prompts packed into one row without pad tokens (ids int64 [M]); K/V of every token go to the
+        cache slot (seq_ids[m], positions[m]).  Returns ln_f output bf16 [M, C]."""
+        assert self.cache_k and self.cache_max_len >= max_len
+        return self.forward_hidden(ids.view(1, -1), packed, save=False, write_cache=True,
+                                   varlen=dict(cu_seqlens=cu_seqlens, positions=positions, seq_ids=seq_ids, max_len=max_len))
 
     def prefill(self, idx: Tensor, packed: Dict[int, Dict[str, Tensor]]) -> Tensor:
         """Full causal forward over right-padded prompts [B, T]; K/V of every position go to the cache."""

@@ -140,10 +140,12 @@ def generate(model, idx: Tensor, max_returned_tokens: int, *, temperature: float
 
 @torch.inference_mode()
 def generate_batch(model, prompts: Sequence[Tensor], max_new_tokens: int, eos_id: Optional[int] = None,
-                   poll_every: int = 8, use_graph: bool = True, return_device: bool = False):
+                   poll_every: int = 8, use_graph: bool = True, return_device: bool = False, packed_prefill: bool = True):
     """Greedy-decode every prompt (1-D int64 tensors, host or device).  Returns prompt + generated ids per sequence,
     cut after the first `eos_id` (inclusive) when given.  `return_device=True` returns the raw device tensor
-    `[n, steps]` of generated ids instead (no device-to-host copy; used by bench.py's HBM-resident leg)."""
+    `[n, steps]` of generated ids instead (no device-to-host copy; used by bench.py's HBM-resident leg).
+    `packed_prefill` (default): the prompts are prefilled as ONE packed row with cu_seqlens (no flops on pad tokens, SURVEY
+    8f row 2); False right-pads them to the longest prompt like the reference's collate_fn -- both give the same bits."""
     eng = model._engine_ready()
     dev = eng.device
     n = len(prompts)
@@ -151,28 +153,44 @@ def generate_batch(model, prompts: Sequence[Tensor], max_new_tokens: int, eos_id
     Tmax = int(lens.max())
     total = Tmax + max_new_tokens
     assert total - 1 <= model.max_seq_length, "prompt + new tokens exceed max_seq_length"
-    if all(p.is_cuda for p in prompts):
-        ids = torch.nn.utils.rnn.pad_sequence(list(prompts), batch_first=True, padding_value=0)
-    else:
-        prev = eng._bufs.get(("pinned_ids_event", n))
-        if prev is not None:
-            prev.synchronize()
-        stage = eng._bufs.get(("pinned_ids", n))                # pinned staging rows, allocated once per batch size
-        if stage is None or stage.shape[1] < Tmax:
-            stage = eng._bufs[("pinned_ids", n)] = torch.zeros((n, max(Tmax, model.max_seq_length)), dtype=torch.int64).pin_memory()
-        ids_h = stage[:, :Tmax]
-        ids_h.zero_()
-        for i, p in enumerate(prompts):
-            ids_h[i, : p.numel()] = p.cpu()
-        ids = ids_h.to(dev, non_blocking=True)
-        copied = torch.cuda.Event()
-        copied.record()
-        eng._bufs[("pinned_ids_event", n)] = copied             # the next call waits for this copy before re-using the rows
     lens_d = lens.to(dev)
     eng.alloc_cache(n, max(model.max_seq_length, total))
     loop = _decode_loop(model, eng, n, max_new_tokens)
-    hidden = eng.prefill(ids, loop.packed).view(n, Tmax, -1)
-    last = hidden[torch.arange(n, device=dev), (lens_d - 1).long()]                    # ln_f state of each prompt's last token
+    if packed_prefill:
+        # prompts packed into one row (no pad tokens): cu_seqlens / per-token positions / sequence ids are built on the host
+        cu = torch.zeros(n + 1, dtype=torch.int32)
+        cu[1:] = lens.cumsum(0)
+        M = int(cu[-1])
+        pos_h = torch.cat([torch.arange(int(L), dtype=torch.int32) for L in lens.tolist()])
+        seq_h = torch.repeat_interleave(torch.arange(n, dtype=torch.int32), lens.long())
+        if all(p.is_cuda for p in prompts):
+            ids = torch.cat(list(prompts))
+        else:
+            ids = torch.cat([p.cpu() for p in prompts]).pin_memory().to(dev, non_blocking=True)
+        meta = torch.cat((cu, pos_h, seq_h)).pin_memory().to(dev, non_blocking=True)       # one small H2D copy
+        cu_d, pos_d, seq_d = meta[: n + 1], meta[n + 1: n + 1 + M], meta[n + 1 + M:]
+        hidden = eng.prefill_packed(ids, cu_d, pos_d, seq_d, Tmax, loop.packed)
+        last = hidden[(cu_d[1:] - 1).long()]                                              # ln_f state of each prompt's last token
+    else:
+        if all(p.is_cuda for p in prompts):
+            ids = torch.nn.utils.rnn.pad_sequence(list(prompts), batch_first=True, padding_value=0)
+        else:
+            prev = eng._bufs.get(("pinned_ids_event", n))
+            if prev is not None:
+                prev.synchronize()
+            stage = eng._bufs.get(("pinned_ids", n))                # pinned staging rows, allocated once per batch size
+            if stage is None or stage.shape[1] < Tmax:
+                stage = eng._bufs[("pinned_ids", n)] = torch.zeros((n, max(Tmax, model.max_seq_length)), dtype=torch.int64).pin_memory()
+            ids_h = stage[:, :Tmax]
+            ids_h.zero_()
+            for i, p in enumerate(prompts):
+                ids_h[i, : p.numel()] = p.cpu()
+            ids = ids_h.to(dev, non_blocking=True)
+            copied = torch.cuda.Event()
+            copied.record()
+            eng._bufs[("pinned_ids_event", n)] = copied             # the next call waits for this copy before re-using the rows
+        hidden = eng.prefill(ids, loop.packed).view(n, Tmax, -1)
+        last = hidden[torch.arange(n, device=dev), (lens_d - 1).long()]                    # ln_f state of each prompt's last token
     loop.reset(last, lens_d, eos_id)
     steps = loop.run(max_new_tokens, use_graph, poll_every)
     if return_device:

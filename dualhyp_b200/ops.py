@@ -245,6 +245,21 @@ def attention_fwd(qkv: Tensor, out: Tensor, lse: Tensor, B: int, T: int, n_group
     _count()
 
 
+@_profiled("attention_fwd")
+def attention_fwd_varlen(qkv: Tensor, out: Tensor, lse: Tensor, cu_seqlens: Tensor, max_len: int, n_groups: int, q_per_kv: int,
+                         prefix_kv: Optional[Tensor] = None, gate: Optional[Tensor] = None, prefix_len: int = 0) -> None:
+    """Causal attention over packed sequences: rows [cu_seqlens[b], cu_seqlens[b + 1]) of qkv / out are sequence b."""
+    _dev(qkv)
+    M = qkv.shape[0]
+    assert qkv.is_contiguous() and out.is_contiguous() and lse.is_contiguous() and qkv.dtype == torch.bfloat16
+    assert cu_seqlens.dtype == torch.int32 and cu_seqlens.is_cuda and lse.numel() >= n_groups * q_per_kv * M
+    assert qkv.shape[1] == n_groups * (q_per_kv + 2) * 64 and out.shape == (M, n_groups * q_per_kv * 64)
+    check(_lib.load().dh_attention_fwd_varlen(qkv.data_ptr(), out.data_ptr(), lse.data_ptr(), _ptr(prefix_kv), _ptr(gate),
+                                              cu_seqlens.data_ptr(), cu_seqlens.numel() - 1, max_len, M, n_groups, q_per_kv, prefix_len,
+                                              _stream()), "dh_attention_fwd_varlen")
+    _count()
+
+
 def attention_bwd_workspace(B: int, T: int, n_groups: int, q_per_kv: int) -> int:
     return int(_lib.load().dh_attention_bwd_workspace(B, T, n_groups, q_per_kv))
 

@@ -130,6 +130,13 @@ int dh_rope_qkv_inplace(void* qkv, const void* cos, const void* sin, const int32
  * ------------------------------------------------------------------------------------------------- */
 int dh_attention_fwd(const void* qkv, void* out, float* lse, const void* prefix_kv, const float* gate, int B, int T,
                      int n_groups, int q_per_kv, int prefix_len, void* stream);
+/* The same forward over PACKED variable-length sequences (no pad rows; SURVEY 8f row 2: the prompts of a decode batch are
+ * 330-480 tokens of 480): sequence b = rows [cu_seqlens[b], cu_seqlens[b+1]) of qkv / out (total_rows rows), causal inside
+ * each sequence; max_len = the longest sequence (sizes the grid); lse: f32 [n_head, total_rows].  RoPE positions restart
+ * per sequence (dh_gemm `positions`). */
+int dh_attention_fwd_varlen(const void* qkv, void* out, float* lse, const void* prefix_kv, const float* gate,
+                            const int32_t* cu_seqlens, int n_seq, int max_len, long long total_rows, int n_groups, int q_per_kv,
+                            int prefix_len, void* stream);
 /* Backward.  dout bf16 [B*T, n_head*64].  dqkv bf16 (same layout as qkv; every slot is written).
  * d_prefix_kv f32 [aT, n_groups*(qpk+2)*64] and d_gate f32 [n_head] are ACCUMULATED into (caller zeroes).
  * need_dqkv = 0 computes only the prefix/gate gradients (first adapter layer). workspace: dh_attention_bwd_workspace.

@@ -521,6 +521,31 @@ def test_attention_bwd(B_, T, G, qpk, prefix, rope):
         assert rel(dpk.cpu(), pkr.grad) < 1e-2, report("dprefix", dpk.cpu(), pkr.grad)
 
 
+@pytest.mark.parametrize("lens,G,qpk,prefix", [([200, 77, 128, 1, 333], 2, 2, 10), ([480, 330, 415], 4, 8, 10), ([129], 1, 1, 0)])
+def test_attention_fwd_varlen_equals_per_sequence(lens, G, qpk, prefix):
+    """Packed variable-length forward (cu_seqlens, no pad rows) == the fixed-length kernel run on each sequence alone,
+    bit for bit (same tiles relative to the sequence start), for sequences that start at arbitrary row offsets."""
+    N, H = G * (qpk + 2) * 64, G * qpk
+    M = sum(lens)
+    qkv = rnd((M, N), 351, 2.0)
+    pk, gate = (rnd((prefix, N), 352, 2.0), rnd((H,), 353, 1.0, torch.float32)) if prefix else (None, None)
+    cu = torch.tensor([0] + list(torch.tensor(lens).cumsum(0)), dtype=torch.int32, device=DEV)
+    out = torch.full((M, H * 64), float("nan"), device=DEV, dtype=torch.bfloat16)
+    lse = torch.full((H, M), float("nan"), device=DEV)
+    ops.attention_fwd_varlen(qkv, out, lse, cu, max(lens), G, qpk, pk, gate, prefix)
+    torch.cuda.synchronize()
+    o = 0
+    for L in lens:
+        one = torch.empty((L, H * 64), device=DEV, dtype=torch.bfloat16)
+        lse1 = torch.empty((1, H, L), device=DEV)
+        ops.attention_fwd(qkv[o:o + L].contiguous(), one, lse1, 1, L, G, qpk, pk, gate, prefix)
+        torch.cuda.synchronize()
+        assert torch.equal(out[o:o + L], one), report(f"varlen seq at {o}", out[o:o + L], one)
+        assert torch.equal(lse[:, o:o + L], lse1[0])
+        o += L
+    assert not torch.isnan(out.float()).any()
+
+
 def test_attention_decode_matches_prefill():
     B_, T, G, qpk, prefix = 3, 200, 2, 4, 10
     N, H = G * (qpk + 2) * 64, G * qpk

@@ -245,6 +245,20 @@ def test_relprompt_inference_glue():
     m.reset_cache()
 
 
+def test_packed_prefill_equals_padded_prefill():
+    """generate_batch prefills the prompts as one packed row (cu_seqlens, no pad tokens) by default; right-padding them
+    like the reference's collate_fn must give the same ids (the per-row GEMM results and the per-sequence attention tiles
+    do not depend on where a sequence sits in the batch)."""
+    for variant in ("adapter", "lora"):
+        m, _ = build(variant, **({"adapter_start_layer": 1} if variant == "adapter" else {}))
+        prompts = [p.to(DEV) for p in synthetic.synth_prompts(5, 512, SEED + 7, prompt_range=(3, 150))]
+        a = generate_batch(m, prompts, 10, packed_prefill=True)
+        b = generate_batch(m, prompts, 10, packed_prefill=False)
+        c = generate_batch(m, [p.cpu() for p in prompts], 10, packed_prefill=True)        # host prompts
+        assert [x.tolist() for x in a] == [x.tolist() for x in b] == [x.tolist() for x in c]
+        m.reset_cache()
+
+
 def test_reference_generate_loop_runs_on_the_model():
     """generate/base.py's loop restated verbatim: model(x, input_pos) -> logits[0, -1] / temperature -> topk(1) ->
     where(< v) -> softmax -> multinomial, one token at a time through the KV cache.  bf16 logits can tie exactly at
