@@ -1472,6 +1472,8 @@ __global__ void __launch_bounds__(DEC_THREADS, 2) attn_decode_mma_kernel(const b
   const int tid = threadIdx.x, warp = tid >> 5, lane = tid & 31;
   const int r = lane >> 2, q = lane & 3;                                // MMA fragment coordinates: row / column group, k pair
   const int H = G * qpk;
+  pdl_launch_dependents();
+  pdl_wait();
   const int len = lens[seq];
   const bf16* qrow = qkv + (long long)seq * ld_qkv + (long long)(g * (qpk + 2)) * HD;
   const bf16* kg = ck + ((long long)seq * G + g) * max_len * HD;
@@ -1807,8 +1809,9 @@ extern "C" int dh_attention_decode(const void* qkv, const void* cache_k, const v
     const size_t smem = (size_t)DM_FIXED_BYTES + (size_t)q_per_kv * (max_len + 20) * sizeof(float);
     DH_CHECK(smem <= 200 * 1024, "dh_attention_decode: max_len %d too large for the score buffer", max_len);
     DH_CHECK((((uintptr_t)qkv | (uintptr_t)cache_k | (uintptr_t)cache_v) & 15) == 0, "dh_attention_decode: operands must be 16-byte aligned");
-    attn_decode_mma_kernel<<<dim3(nseq, n_groups), DEC_THREADS, smem, (cudaStream_t)stream>>>(
-        (const bf16*)qkv, (const bf16*)cache_k, (const bf16*)cache_v, lens, (bf16*)out, pkv, gate, max_len, n_groups, q_per_kv, plen, ld, scale);
+    DH_CUDA(launch_pdl(attn_decode_mma_kernel, dim3(nseq, n_groups), dim3(DEC_THREADS), smem, (cudaStream_t)stream, (const bf16*)qkv,
+                       (const bf16*)cache_k, (const bf16*)cache_v, (const int*)lens, (bf16*)out, pkv, (const float*)gate, max_len, n_groups, q_per_kv, plen,
+                       ld, scale));
   } else {
     const size_t smem = ((size_t)DEC_FIXED_FLOATS + (size_t)q_per_kv * (max_len + 1)) * sizeof(float);
     DH_CHECK(smem <= 200 * 1024, "dh_attention_decode: max_len %d too large for the score buffer", max_len);

@@ -43,6 +43,7 @@ void set_error(const char* fmt, ...);
 int make_tensor_map(CUtensorMap* map, const void* base, CUtensorMapDataType dtype, int rank, const uint64_t* dims,
                     const uint64_t* strides_bytes, const uint32_t* box, CUtensorMapSwizzle swizzle);
 int sm_count();
+int pdl_level();      // DH_PDL: 0 off, 1 eager launches only, 2 also while a stream is being captured
 bool pdl_enabled();   // programmatic dependent launch for the training-step kernels (opt-in: DH_PDL=1)
 
 #ifdef __CUDACC__
@@ -67,7 +68,9 @@ inline cudaError_t launch_pdl(void (*kernel)(KArgs...), dim3 grid, dim3 block, s
   attr[0].val.programmaticStreamSerializationAllowed = 1;
   cfg.attrs = attr;
   cfg.numAttrs = 0;
-  if (pdl_enabled()) {       // not under stream capture: the decode graph keeps plain edges
+  if (pdl_level() >= 2) {
+    cfg.numAttrs = 1;
+  } else if (pdl_level() == 1) {       // not under stream capture: the decode graph keeps plain edges
     cudaStreamCaptureStatus st = cudaStreamCaptureStatusNone;
     if (cudaStreamIsCapturing(stream, &st) == cudaSuccess && st == cudaStreamCaptureStatusNone) cfg.numAttrs = 1;
   }

@@ -401,10 +401,12 @@ gemm_skinny_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constan
     tmem_alloc(tmem_slot, SK_BN);
     tmem_relinquish();
   }
+  pdl_launch_dependents();
   tc_fence_before();
   __syncthreads();
   tc_fence_after();
   const uint32_t tmem_base = __shfl_sync(0xffffffffu, *tmem_slot, 0);
+  pdl_wait();          // barrier init, TMEM allocation and descriptor prefetch overlapped the previous kernel's tail
 
   if (warp == 0 && lane == 0) {
     uint32_t it = 0;
@@ -1146,13 +1148,21 @@ static int launch_gemm_skinny(const dh_gemm_args* a, cudaStream_t stream) {
   cfg.blockDim = dim3(GEMM_THREADS);
   cfg.dynamicSmemBytes = (size_t)stages * stage_bytes + 1024 + 256;
   cfg.stream = stream;
-  cudaLaunchAttribute attr[1];
+  cudaLaunchAttribute attr[2];
   attr[0].id = cudaLaunchAttributeClusterDimension;
   attr[0].val.clusterDim.x = p.sk_partial ? 1 : S;
   attr[0].val.clusterDim.y = 1;
   attr[0].val.clusterDim.z = 1;
+  attr[1].id = cudaLaunchAttributeProgrammaticStreamSerialization;
+  attr[1].val.programmaticStreamSerializationAllowed = 1;
   cfg.attrs = attr;
   cfg.numAttrs = 1;
+  if (pdl_level() >= 2) {
+    cfg.numAttrs = 2;
+  } else if (pdl_level() == 1) {
+    cudaStreamCaptureStatus st = cudaStreamCaptureStatusNone;
+    if (cudaStreamIsCapturing(stream, &st) == cudaSuccess && st == cudaStreamCaptureStatusNone) cfg.numAttrs = 2;
+  }
   DH_CUDA(cudaLaunchKernelEx(&cfg, gemm_skinny_kernel<EPI>, tmA, tmB, tmA2, tmB2, p));
   return 0;
 }

@@ -82,6 +82,8 @@ __global__ void splitk_resid_rmsnorm_kernel(const float* __restrict__ partial, i
                                             const float* __restrict__ resid, const float* __restrict__ w, float* __restrict__ x_out,
                                             bf16* __restrict__ y, int C, float eps) {
   __shared__ float red[32];
+  pdl_launch_dependents();
+  pdl_wait();
   const long long row = blockIdx.x;
   const int c0 = threadIdx.x * 8;
   float acc[8], v[8], g[8];
@@ -128,6 +130,8 @@ __global__ void splitk_qkv_rope_cache_kernel(const float* __restrict__ partial, 
                                              bf16* ck, bf16* cv, const int* __restrict__ seq, const int* __restrict__ pos,
                                              const bf16* __restrict__ rope_cos, const bf16* __restrict__ rope_sin, int N, int max_len,
                                              int n_groups, int qpk) {
+  pdl_launch_dependents();
+  pdl_wait();
   const long long row = blockIdx.x;
   const int p = pos[row];
   for (int t = threadIdx.x; t < N / 16; t += blockDim.x) {       // thread: columns [j, j + 8) and [j + 32, j + 40) of one head slot
@@ -359,6 +363,8 @@ __global__ void loss_reduce_kernel(const float* __restrict__ row_loss, const lon
 __global__ void __launch_bounds__(256) argmax_kernel(const bf16* __restrict__ logits, long long ldl, long long* __restrict__ ids, int V) {
   __shared__ float sv[8];
   __shared__ int si[8];
+  pdl_launch_dependents();
+  pdl_wait();
   const long long row = blockIdx.x;
   const bf16* l = logits + row * ldl;
   float best = -INFINITY;
@@ -615,7 +621,8 @@ extern "C" int dh_splitk_resid_rmsnorm(const float* partial, int splits, long lo
   DH_CHECK(partial && resid && weight && x_out && y && M > 0 && splits > 0, "dh_splitk_resid_rmsnorm: bad argument");
   DH_CHECK(C % 256 == 0 && C <= 8192, "dh_splitk_resid_rmsnorm: C=%d must be a multiple of 256 and <= 8192", C);
   DH_CHECK(split_stride >= (long long)M * C && split_stride % 4 == 0, "dh_splitk_resid_rmsnorm: bad split stride");
-  splitk_resid_rmsnorm_kernel<<<M, C / 8, 0, (cudaStream_t)stream>>>(partial, splits, split_stride, resid, weight, x_out, (bf16*)y, C, eps);
+  DH_CUDA(launch_pdl(splitk_resid_rmsnorm_kernel, dim3(M), dim3(C / 8), 0, (cudaStream_t)stream, partial, splits, split_stride, resid, weight, x_out,
+                     (bf16*)y, C, eps));
   DH_CUDA(cudaGetLastError());
   return 0;
 }
@@ -629,10 +636,8 @@ extern "C" int dh_splitk_qkv_rope_cache(const float* partial, int splits, long l
   DH_CHECK(split_stride >= (long long)M * N && split_stride % 4 == 0, "dh_splitk_qkv_rope_cache: bad split stride");
   int threads = N / 16;
   threads = threads > 256 ? 256 : ((threads + 31) / 32) * 32;
-  splitk_qkv_rope_cache_kernel<<<M, threads, 0, (cudaStream_t)stream>>>(partial, splits, split_stride, (bf16*)qkv, (bf16*)cache_k, (bf16*)cache_v,
-                                                                       seq, pos, (const bf16*)rope_cos, (const bf16*)rope_sin, N, max_len,
-                                                                       n_groups, q_per_kv);
-  DH_CUDA(cudaGetLastError());
+  DH_CUDA(launch_pdl(splitk_qkv_rope_cache_kernel, dim3(M), dim3(threads), 0, (cudaStream_t)stream, partial, splits, split_stride, (bf16*)qkv,
+                     (bf16*)cache_k, (bf16*)cache_v, seq, pos, (const bf16*)rope_cos, (const bf16*)rope_sin, N, max_len, n_groups, q_per_kv));
   return 0;
 }
 
@@ -712,7 +717,7 @@ extern "C" int dh_loss_reduce(const float* row_loss, const int64_t* targets, flo
 
 extern "C" int dh_argmax(const void* logits, int64_t ldl, int64_t* ids, int M, int V, void* stream) {
   DH_CHECK(logits && ids && M > 0 && V > 0, "dh_argmax: bad argument");
-  argmax_kernel<<<M, 256, 0, (cudaStream_t)stream>>>((const bf16*)logits, ldl, (long long*)ids, V);
+  DH_CUDA(launch_pdl(argmax_kernel, dim3(M), dim3(256), 0, (cudaStream_t)stream, (const bf16*)logits, ldl, (long long*)ids, V));
   DH_CUDA(cudaGetLastError());
   return 0;
 }

@@ -73,14 +73,15 @@ int make_tensor_map(CUtensorMap* map, const void* base, CUtensorMapDataType dtyp
 
 int sm_count() { return g_sm_count > 0 ? g_sm_count : 148; }
 
-bool pdl_enabled() {
+int pdl_level() {
   static int v = -1;
   if (v < 0) {
-    const char* e = getenv("DH_PDL");
-    v = (e && e[0] == '1') ? 1 : 0;      // opt-in: measured neutral on the power-capped B200 (35.8 vs 35.8 ms per step)
+    const char* e = getenv("DH_PDL");    // 1: eager launches (measured neutral on the power-capped training step, 35.8 vs 35.8 ms)
+    v = (e && e[0] >= '0' && e[0] <= '2') ? e[0] - '0' : 0;   // 2: also under stream capture (programmatic edges in the decode graph)
   }
-  return v == 1;
+  return v;
 }
+bool pdl_enabled() { return pdl_level() >= 1; }
 
 }  // namespace dh
 
