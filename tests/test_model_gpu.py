@@ -210,6 +210,36 @@ def test_graph_decode_equals_eager_and_is_reusable():
     m.reset_cache()
 
 
+def test_continuous_batching_service_equals_per_utterance_decode():
+    """serve.DecodeService: 3 cache slots serve 7 prompts with different token budgets, slots are refilled
+    as sequences stop (budget or EOS); every utterance gets the ids of decoding it on its own (generate/base.py:19-82)."""
+    from dualhyp_b200.serve import DecodeService
+    m, _ = build("adapter", adapter_start_layer=1)
+    prompts = [p.to(DEV) for p in synthetic.synth_prompts(7, 512, SEED + 5, prompt_range=(12, 80))]
+    budgets = [5, 9, 3, 12, 6, 4, 8]
+    alone = [generate_batch(m, [p], b)[0] for p, b in zip(prompts, budgets)]
+    svc = DecodeService(m, n_slots=3, max_new_tokens=12, poll_every=2)
+    got = svc.run(prompts, budgets)
+    for a, g, p, b in zip(alone, got, prompts, budgets):
+        assert g.numel() == p.numel() + b
+        assert a.tolist() == g.tolist()
+    assert svc.stats["generated"] == sum(budgets) and svc.stats["prefills"] >= 3
+    # fewer token steps than decoding [0:3], [3:6], [6:7] as three batches that each wait for their longest answer
+    assert svc.stats["token_steps"] <= 9 + 12 + 8 + 3 * 2
+    # EOS: an id the answers contain stops those sequences early (cut inclusive); the freed slot is re-used
+    eos = int(alone[3][prompts[3].numel() + 4])
+    alone_e = [generate_batch(m, [p], b, eos_id=eos)[0] for p, b in zip(prompts, budgets)]
+    svc_e = DecodeService(m, n_slots=3, max_new_tokens=12, eos_id=eos, poll_every=3)
+    got_e = svc_e.run(prompts, budgets)
+    assert [x.tolist() for x in alone_e] == [x.tolist() for x in got_e]
+    assert alone_e[3].numel() < alone[3].numel()
+    # the batch decode of the same width still works afterwards (shared per-width buffers), and so does a second run
+    again = generate_batch(m, prompts[:3], 6)
+    assert [x.tolist()[: p.numel() + 3] for x, p in zip(again, prompts[:3])] == [x.tolist()[: p.numel() + 3] for x, p in zip(alone[:3], prompts[:3])]
+    assert [x.tolist() for x in svc.run(prompts[::-1], budgets[::-1])] == [x.tolist() for x in alone[::-1]]
+    m.reset_cache()
+
+
 def test_relprompt_inference_glue():
     """inference/relprompt.py:102-173 on tensors: classifier arg-max (checked against the oracle's classifier), mask
     tokens spliced into the prompts, batched decode == the same prompts decoded one by one through generate()."""
