@@ -34,7 +34,7 @@ UNIT = "tokens/s"
 SEQ_LEN = 512
 PER_GPU_BATCH = 16
 DECODE_METRIC = "DualHyp infer utterances/s (greedy KV-cache decode, adapter TinyLlama-1.1B, 5+5 N-best prompts, 64 new tokens)"
-DECODE_UTTS, DECODE_NEW = 64, 64
+DECODE_UTTS, DECODE_NEW = 128, 64     # 128 sequences per token step: the widest the decode GEMM's one-tile M takes
 LORA = dict(r=8, alpha=16, dropout=0.0, to_query=True, to_key=True, to_value=True, to_projection=True)
 # DRAM bytes per launch of the dominant GEMMs from one `ncu --set full` capture of this command (profiles/r01u_ncu_full_summary.txt);
 # key = (M, N, K, epilogue).  Algorithmic bytes of the SwiGLU GEMM: A 33.6 MB + B 46.1 MB + h12 184.5 MB + act 92.3 MB = 356.5 MB.
