@@ -43,7 +43,7 @@ void set_error(const char* fmt, ...);
 int make_tensor_map(CUtensorMap* map, const void* base, CUtensorMapDataType dtype, int rank, const uint64_t* dims,
                     const uint64_t* strides_bytes, const uint32_t* box, CUtensorMapSwizzle swizzle);
 int sm_count();
-int pdl_level();      // DH_PDL: 0 off, 1 eager launches only, 2 also while a stream is being captured
+int pdl_level();      // DH_PDL: 0 off, 1 eager launches only, 2 (default) also while a stream is being captured
 bool pdl_enabled();   // programmatic dependent launch for the training-step kernels (opt-in: DH_PDL=1)
 
 #ifdef __CUDACC__

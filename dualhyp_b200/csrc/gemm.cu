@@ -37,6 +37,7 @@ struct GemmParams {
   long long split_stride;  // elements between output slices
   int sk_stages;           // skinny kernel: depth of the TMA ring
   int sk_partial;          // skinny kernel: gridDim.x CTAs per tile each store their K range's product to slice blockIdx.x of out
+  int b_frozen;            // skinny kernel: B (first source) is a frozen weight -- its tiles may be fetched before pdl_wait()
 };
 
 template <int BN> struct GemmCfg {
@@ -406,22 +407,36 @@ gemm_skinny_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constan
   __syncthreads();
   tc_fence_after();
   const uint32_t tmem_base = __shfl_sync(0xffffffffu, *tmem_slot, 0);
-  pdl_wait();          // barrier init, TMEM allocation and descriptor prefetch overlapped the previous kernel's tail
 
   if (warp == 0 && lane == 0) {
+    // A frozen weight does not depend on the previous kernel: its first ring of tiles is requested BEFORE pdl_wait(), so
+    // the weight stream starts while the predecessor (a consumer on a few SMs, another GEMM's tail) is still running;
+    // the activation boxes follow after the wait and complete the same stage barriers.
+    int n_pre = 0;
+    if (p.b_frozen) {
+      const int first_end = kb_end < nkb1 ? kb_end : nkb1;
+      for (int kb = kb_begin; kb < first_end && n_pre < stages; ++kb, ++n_pre) {
+        mbar_expect_tx(&full_bar[n_pre], stage_bytes);
+        tma_load_2d(smem + n_pre * stage_bytes + a_bytes, &tmB, kb * BK, n0, &full_bar[n_pre]);
+      }
+    }
+    pdl_wait();
     uint32_t it = 0;
     for (int kb = kb_begin; kb < kb_end; ++kb, ++it) {
       const int s = it % stages;
-      mbar_wait(&empty_bar[s], ((it / stages) & 1) ^ 1);
       uint8_t* sa = smem + s * stage_bytes;
       uint8_t* sb = sa + a_bytes;
-      mbar_expect_tx(&full_bar[s], stage_bytes);
       const bool second = kb >= nkb1;
       const int k0 = (second ? kb - nkb1 : kb) * BK;
+      if ((int)it >= n_pre) {
+        mbar_wait(&empty_bar[s], ((it / stages) & 1) ^ 1);
+        mbar_expect_tx(&full_bar[s], stage_bytes);
+        tma_load_2d(sb, second ? &tmB2 : &tmB, k0, n0, &full_bar[s]);
+      }
       tma_load_2d(sa, second ? &tmA2 : &tmA, k0, 0, &full_bar[s]);
-      tma_load_2d(sb, second ? &tmB2 : &tmB, k0, n0, &full_bar[s]);
     }
   } else if (warp == 1) {
+    pdl_wait();
     const uint32_t idesc = umma_idesc_bf16(BM, SK_BN, 0, 0);
     uint32_t it = 0;
     for (int kb = kb_begin; kb < kb_end; ++kb, ++it) {
@@ -440,6 +455,7 @@ gemm_skinny_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constan
       __syncwarp();
     }
   } else if (warp >= 4 && S > 1) {
+    pdl_wait();
     // park this CTA's partial rows in shared memory (the ring is idle once the last MMA has completed)
     const int q = warp & 3;
     const int r = q * 32 + lane;
@@ -465,6 +481,7 @@ gemm_skinny_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constan
     cluster_sync_any();
   }
   if (warp >= 4) {
+    pdl_wait();
     const int t = threadIdx.x - 128;
     if (S == 1) {
       const int q = warp & 3;
@@ -984,7 +1001,7 @@ static GemmParams make_params(const dh_gemm_args* a) {
   p.positions = a->positions;
   p.m_limit = a->m_limit;
   p.splits = 1; p.split_stride = 0;
-  p.sk_stages = 0; p.sk_partial = 0;
+  p.sk_stages = 0; p.sk_partial = 0; p.b_frozen = 0;
   return p;
 }
 
@@ -1092,6 +1109,8 @@ static int launch_gemm_pair(const dh_gemm_args* a, cudaStream_t stream) {
   return 0;
 }
 
+static thread_local int t_b_frozen = 0;   // DH_B_FROZEN of the call being dispatched (dh_gemm strips it from b_layout)
+
 template <int EPI>
 static int launch_gemm_skinny(const dh_gemm_args* a, cudaStream_t stream) {
   static bool attr_set = false;
@@ -1111,6 +1130,7 @@ static int launch_gemm_skinny(const dh_gemm_args* a, cudaStream_t stream) {
     tmB2 = tmB;
   }
   GemmParams p = make_params(a);
+  p.b_frozen = t_b_frozen;
   p.tiles_m = 1;
   p.tiles_n = a->N / SK_BN;
   const int tiles = p.tiles_n;
@@ -1193,10 +1213,14 @@ static int dispatch_bn(const dh_gemm_args* a, cudaStream_t stream) {
 
 }  // namespace dh
 
-extern "C" int dh_gemm(const dh_gemm_args* a, void* stream_) {
+extern "C" int dh_gemm(const dh_gemm_args* args, void* stream_) {
   using namespace dh;
   cudaStream_t stream = reinterpret_cast<cudaStream_t>(stream_);
-  DH_CHECK(a != nullptr, "dh_gemm: null args");
+  DH_CHECK(args != nullptr, "dh_gemm: null args");
+  dh_gemm_args local = *args;
+  t_b_frozen = (local.b_layout & DH_B_FROZEN) ? 1 : 0;
+  local.b_layout &= ~DH_B_FROZEN;
+  const dh_gemm_args* a = &local;
   DH_CHECK(a->M > 0 && a->N > 0 && a->K1 > 0, "dh_gemm: bad shape M=%d N=%d K1=%d", a->M, a->N, a->K1);
   DH_CHECK(a->N % 64 == 0 && a->K1 % 8 == 0 && a->K2 % 8 == 0, "dh_gemm: N %% 64, K1 %% 8, K2 %% 8 must be 0 (N=%d K1=%d K2=%d)",
            a->N, a->K1, a->K2);

@@ -346,7 +346,7 @@ class DecoderEngine:
         only the first *m_limit rows are needed (valid-row compaction of the fused loss)."""
         M = hidden.shape[0]
         logits = out if out is not None else self._buf("logits", (M, self.spec.vocab), torch.bfloat16)
-        ops.gemm(hidden, self.lm_w, logits, col_scale=self.lm_scale, col_bias=self.lm_bias, m_limit=m_limit)
+        ops.gemm(hidden, self.lm_w, logits, col_scale=self.lm_scale, col_bias=self.lm_bias, m_limit=m_limit, b_frozen=True)
         return logits
 
     # ------------------------------------------------------------------------------------------
@@ -521,11 +521,11 @@ class DecoderEngine:
                 b2q = pk["qkv_b"]
             if s_qkv > 1:
                 # split-K partial products; one consumer sums them, applies RoPE and writes the qkv row and the KV cache
-                ops.gemm(n, lw["wqkv"], ws_q, A2=a2q, B2=b2q, epilogue=ops.EPI_F32, split_k=s_qkv)
+                ops.gemm(n, lw["wqkv"], ws_q, A2=a2q, B2=b2q, epilogue=ops.EPI_F32, split_k=s_qkv, b_frozen=True)
                 ops.splitk_qkv_rope_cache(ws_q, qkv, self.cache_k[i], self.cache_v[i], seq_ids, positions, self.cos, self.sin, G, qpk)
             else:
                 ops.gemm(n, lw["wqkv"], qkv, A2=a2q, B2=b2q, epilogue=ops.EPI_QKV_ROPE, rope_cos=self.cos, rope_sin=self.sin,
-                         positions=positions, seq_len=1, q_per_kv=qpk)
+                         positions=positions, seq_len=1, q_per_kv=qpk, b_frozen=True)
                 ops.kv_cache_write(qkv, self.cache_k[i], self.cache_v[i], seq_ids, positions, G, qpk)
             prefix_kv = gate = None
             if "prefix" in pk:
@@ -539,18 +539,18 @@ class DecoderEngine:
                 ops.gemm(y, pk["proj_a"], a2)
                 b2 = pk["proj_b"]
             if s_proj > 1:
-                ops.gemm(y, lw["wproj"], ws[:s_proj], A2=a2, B2=b2, epilogue=ops.EPI_F32, split_k=s_proj)
+                ops.gemm(y, lw["wproj"], ws[:s_proj], A2=a2, B2=b2, epilogue=ops.EPI_F32, split_k=s_proj, b_frozen=True)
                 ops.splitk_resid_rmsnorm(ws[:s_proj], x, lw["norm2"], x2, n, s.norm_eps)
             else:
-                ops.gemm(y, lw["wproj"], x2, A2=a2, B2=b2, epilogue=ops.EPI_RESID_F32, aux=x)
+                ops.gemm(y, lw["wproj"], x2, A2=a2, B2=b2, epilogue=ops.EPI_RESID_F32, aux=x, b_frozen=True)
                 ops.rmsnorm_fwd(x2, lw["norm2"], n, None, s.norm_eps)
-            ops.gemm(n, lw["w12"], None, epilogue=ops.EPI_SWIGLU, out2=act)
+            ops.gemm(n, lw["w12"], None, epilogue=ops.EPI_SWIGLU, out2=act, b_frozen=True)
             last = i + 1 == len(self.layers)
             w_next, n_next = (self.ln_f, hidden) if last else (self.layers[i + 1]["norm1"], n)
             if s_mlp > 1:
-                ops.gemm(act, lw["wmlp"], ws[:s_mlp], epilogue=ops.EPI_F32, split_k=s_mlp)
+                ops.gemm(act, lw["wmlp"], ws[:s_mlp], epilogue=ops.EPI_F32, split_k=s_mlp, b_frozen=True)
                 ops.splitk_resid_rmsnorm(ws[:s_mlp], x2, w_next, x, n_next, s.norm_eps)
             else:
-                ops.gemm(act, lw["wmlp"], x, epilogue=ops.EPI_RESID_F32, aux=x2)
+                ops.gemm(act, lw["wmlp"], x, epilogue=ops.EPI_RESID_F32, aux=x2, b_frozen=True)
                 ops.rmsnorm_fwd(x, w_next, n_next, None, s.norm_eps)
         return hidden

@@ -53,6 +53,9 @@ def _profiled(name, meta_fn=None):
     return deco
 
 
+B_FROZEN = 0x100
+
+
 def _gemm_meta(A, B, out, *, epilogue=EPI_BF16, b_layout=0, a_layout=0, A2=None, **kw):
     M, K = (A.shape if a_layout == 0 else (A.shape[1], A.shape[0]))
     N = B.shape[0] if b_layout == 0 else B.shape[1]
@@ -94,7 +97,7 @@ def gemm(A: Tensor, B: Tensor, out: Optional[Tensor], *, epilogue: int = EPI_BF1
          out2: Optional[Tensor] = None, aux: Optional[Tensor] = None, alpha: float = 1.0, accumulate: bool = False,
          col_scale: Optional[Tensor] = None, col_bias: Optional[Tensor] = None, rope_cos: Optional[Tensor] = None,
          rope_sin: Optional[Tensor] = None, positions: Optional[Tensor] = None, seq_len: int = 0, q_per_kv: int = 0,
-         m_limit: Optional[Tensor] = None, split_k: int = 0) -> None:
+         m_limit: Optional[Tensor] = None, split_k: int = 0, b_frozen: bool = False) -> None:
     """D = A op(B) (+ A2 op(B2)) with a fused epilogue; see `dh_gemm` in include/dualhyp.h.  split_k > 1 (decode, M <= 128,
     EPI_F32): `out` is fp32 [split_k, M, N] of partial products for `splitk_resid_rmsnorm` to sum."""
     _dev(A)
@@ -112,7 +115,7 @@ def gemm(A: Tensor, B: Tensor, out: Optional[Tensor], *, epilogue: int = EPI_BF1
         Kb, N = B.shape
     assert K == Kb, f"K mismatch: A gives {K}, B gives {Kb}"
     a.M, a.N, a.K1, a.K2 = M, N, K, 0
-    a.a_layout, a.b_layout = a_layout, b_layout
+    a.a_layout, a.b_layout = a_layout, b_layout | (B_FROZEN if b_frozen else 0)      # DH_B_FROZEN: see include/dualhyp.h
     if A2 is not None:
         assert B2 is not None and A2.dtype == torch.bfloat16 and B2.dtype == torch.bfloat16
         a.A2, a.lda2 = A2.data_ptr(), _rowmajor(A2, "A2")

@@ -36,10 +36,15 @@ int dh_sm_count(void);
  *   D[M,N] = A[M,K1] * op(B) (+ A2[M,K2] * op(B2)),   bf16 operands, fp32 accumulation in TMEM.
  * a_layout/b_layout 0 = K-major  (A is [M,K] row-major; B is [N,K] row-major, i.e. y = x W^T with W as stored)
  *                   1 = MN-major (A is [K,M] row-major; B is [K,N] row-major)            -- dgrad / wgrad forms
+ * b_layout may carry DH_B_FROZEN: B is a frozen weight that no kernel on the stream writes.  The decode GEMM (M <= 128) then
+ * requests its first ring of weight tiles before waiting for the previous kernel (programmatic dependent launch, DH_PDL=2),
+ * so the weight stream of one GEMM overlaps the tail of the kernel before it.  Never set it for an operand produced on the stream.
  * The second source pair folds a LoRA low-rank delta into the same accumulator (K extension).
  * Constraints: N % 64 == 0, K1 % 8 == 0, K2 % 8 == 0, 16-byte aligned rows.  M is arbitrary and K may be ragged (tails
  * are zero-filled by TMA on load; tail rows are masked on store).
  * ------------------------------------------------------------------------------------------------- */
+#define DH_B_FROZEN 0x100
+
 enum dh_epilogue {
   DH_EPI_BF16 = 0,        /* out[bf16] = (acc*alpha [+col_bias]) [*col_scale]                                  */
   DH_EPI_F32 = 1,         /* out[f32]  = acc*alpha (+ out if accumulate)                                       */
