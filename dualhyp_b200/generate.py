@@ -154,7 +154,7 @@ def generate_batch(model, prompts: Sequence[Tensor], max_new_tokens: int, eos_id
     total = Tmax + max_new_tokens
     assert total - 1 <= model.max_seq_length, "prompt + new tokens exceed max_seq_length"
     lens_d = lens.to(dev)
-    eng.alloc_cache(n, max(model.max_seq_length, total))
+    eng.alloc_cache_for(n, total)
     loop = _decode_loop(model, eng, n, max_new_tokens)
     if packed_prefill:
         # prompts packed into one row (no pad tokens): cu_seqlens / per-token positions / sequence ids are built on the host

@@ -319,8 +319,8 @@ class GPT(nn.Module):
         names, tensors = self._trainables()
         packed = eng.pack_trainable(dict(zip(names, tensors)))
         B, T = idx.shape
-        if not eng.cache_k or self._cache_batch != B:
-            eng.alloc_cache(B, self.max_seq_length)
+        if not eng.cache_k or self._cache_batch != B or eng.cache_k[0].shape[0] != B or eng.cache_max_len < self.max_seq_length:
+            eng.alloc_cache(B, self.max_seq_length)      # generate_batch / DecodeService may have left a shorter cache
             self._cache_batch = B
             self.kv_caches = list(zip(eng.cache_k, eng.cache_v))
         if T > 1:

@@ -135,7 +135,7 @@ class DecodeService:
         for p, b in zip(prompts, budgets):
             if p.numel() + b - 1 > model.max_seq_length:
                 raise ValueError(f"prompt of {p.numel()} tokens + {b} new tokens exceeds max_seq_length {model.max_seq_length}")
-        eng.alloc_cache(self.n, model.max_seq_length)
+        eng.alloc_cache_for(self.n, max(p.numel() + b for p, b in zip(prompts, budgets)))
         loop = self._loop(eng)
         waiting = deque(range(len(prompts)))
         owner = [-1] * self.n                                        # request index held by each slot
