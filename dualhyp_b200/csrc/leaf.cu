@@ -74,6 +74,54 @@ __global__ void rmsnorm_fwd_kernel(const XT* __restrict__ x, const float* __rest
   if (rstd && threadIdx.x == 0) rstd[row] = r;
 }
 
+// Many rows (training step, prefill): one WARP per row, C = NCH * 256, lane l owns the 8-element chunks j * 32 + l.  All NCH
+// 32-byte loads of a lane are in flight before the first add and the row sum is five shuffles (no block barrier): the
+// one-block-per-row form above keeps a single load per thread in flight and measured 3.7 TB/s on [8192, 2048] fp32.
+template <typename XT, int NCH>
+__global__ void __launch_bounds__(256) rmsnorm_fwd_warp_kernel(const XT* __restrict__ x, const float* __restrict__ w, bf16* __restrict__ y,
+                                                               float* __restrict__ rstd, int M, float eps) {
+  constexpr int C = NCH * 256;
+  pdl_launch_dependents();
+  pdl_wait();
+  const int lane = threadIdx.x & 31;
+  const long long row = blockIdx.x * 8LL + (threadIdx.x >> 5);
+  if (row >= M) return;
+  const XT* xr = x + row * C;
+  float v[NCH][8];
+#pragma unroll
+  for (int j = 0; j < NCH; ++j) load8(xr + (j * 32 + lane) * 8, v[j]);
+  float ss = 0.f;
+#pragma unroll
+  for (int j = 0; j < NCH; ++j)
+#pragma unroll
+    for (int i = 0; i < 8; ++i) ss += v[j][i] * v[j][i];
+#pragma unroll
+  for (int o = 16; o > 0; o >>= 1) ss += __shfl_xor_sync(0xffffffffu, ss, o);
+  const float r = rsqrtf(ss / (float)C + eps);
+  bf16* yr = y + row * C;
+#pragma unroll
+  for (int j = 0; j < NCH; ++j) {
+    float g[8];
+    load8(w + (j * 32 + lane) * 8, g);
+#pragma unroll
+    for (int i = 0; i < 8; ++i) v[j][i] = g[i] * (v[j][i] * r);
+    store8(yr + (j * 32 + lane) * 8, v[j]);
+  }
+  if (rstd && lane == 0) rstd[row] = r;
+}
+
+template <typename XT>
+static cudaError_t launch_rmsnorm_fwd(const XT* x, const float* w, bf16* y, float* rstd, int M, int C, float eps, cudaStream_t s) {
+  const dim3 grid((M + 7) / 8), block(256);
+  if (M >= 512) {
+    if (C == 2048) return launch_pdl(rmsnorm_fwd_warp_kernel<XT, 8>, grid, block, 0, s, x, w, y, rstd, M, eps);
+    if (C == 1024) return launch_pdl(rmsnorm_fwd_warp_kernel<XT, 4>, grid, block, 0, s, x, w, y, rstd, M, eps);
+    if (C == 512) return launch_pdl(rmsnorm_fwd_warp_kernel<XT, 2>, grid, block, 0, s, x, w, y, rstd, M, eps);
+    if (C == 256) return launch_pdl(rmsnorm_fwd_warp_kernel<XT, 1>, grid, block, 0, s, x, w, y, rstd, M, eps);
+  }
+  return launch_pdl(rmsnorm_fwd_kernel<XT>, dim3(M), dim3(C / 8), 0, s, x, w, y, rstd, C, eps);
+}
+
 // Decode: consumer of a split-K GEMM (dh_gemm with split_k > 1 leaves `splits` fp32 partial products [splits][M][C]):
 //   x_out = resid + bf16(sum_s partial[s])      (the residual epilogue of the GEMM, ger/model.py:185-186)
 //   y     = rmsnorm(x_out) * w  in bf16         (the next norm, ger/rmsnorm.py:17-21)
@@ -611,8 +659,8 @@ extern "C" int dh_rmsnorm_fwd(const void* x, int x_dtype, const float* weight, v
   DH_CHECK(x && weight && y && M > 0, "dh_rmsnorm_fwd: null argument");
   DH_CHECK(C % 256 == 0 && C <= 8192, "dh_rmsnorm_fwd: C=%d must be a multiple of 256 and <= 8192", C);
   cudaStream_t s = (cudaStream_t)stream;
-  if (x_dtype == 0) DH_CUDA(launch_pdl(rmsnorm_fwd_kernel<float>, dim3(M), dim3(C / 8), 0, s, (const float*)x, weight, (bf16*)y, rstd, C, eps));
-  else DH_CUDA(launch_pdl(rmsnorm_fwd_kernel<bf16>, dim3(M), dim3(C / 8), 0, s, (const bf16*)x, weight, (bf16*)y, rstd, C, eps));
+  if (x_dtype == 0) DH_CUDA(launch_rmsnorm_fwd((const float*)x, weight, (bf16*)y, rstd, M, C, eps, s));
+  else DH_CUDA(launch_rmsnorm_fwd((const bf16*)x, weight, (bf16*)y, rstd, M, C, eps, s));
   return 0;
 }
 

@@ -357,6 +357,24 @@ def test_gemm_pair_kernel_rope_and_swiglu():
 # ----------------------------------------------------------------------------------------------
 # leaf ops
 # ----------------------------------------------------------------------------------------------
+@pytest.mark.parametrize("M,C,dt", [(1037, 2048, torch.float32), (520, 256, torch.bfloat16), (4096, 1024, torch.float32)])
+def test_rmsnorm_fwd_many_rows(M, C, dt):
+    """M >= 512 takes the warp-per-row kernel (ragged last block of 8 rows); same tolerance as the block-per-row one, and
+    the rstd it leaves feeds the backward."""
+    x = rnd((M, C), 36, 2.0, dt)
+    w = rnd((C,), 37, 0.5, torch.float32) + 1.0
+    y = torch.full((M, C), float("nan"), device=DEV, dtype=torch.bfloat16)
+    rstd = torch.full((M,), float("nan"), device=DEV)
+    ops.rmsnorm_fwd(x, w, y, rstd, 1e-5)
+    ref = O.rmsnorm(x.float(), w, 1e-5)
+    assert rel(y, ref) < 4e-3, report("rmsnorm", y, ref)
+    want = torch.rsqrt((x.float() ** 2).mean(-1) + 1e-5)
+    assert rel(rstd, want) < 1e-5
+    ys = torch.empty((300, C), device=DEV, dtype=torch.bfloat16)
+    ops.rmsnorm_fwd(x[:300].contiguous(), w, ys, None, 1e-5)                   # block-per-row kernel on the same rows
+    assert (ys.float() - y[:300].float()).abs().max() <= 2 ** -7 * ref[:300].abs().max()   # at most one bf16 ulp apart
+
+
 def test_rmsnorm_fwd_bwd():
     M, C = 300, 2048
     x = rnd((M, C), 30, 2.0, torch.float32)
