@@ -1444,8 +1444,12 @@ __global__ void __launch_bounds__(DEC_THREADS) attn_decode_kernel(const bf16* __
 //           shared tile and come back transposed with ldmatrix.trans; P (fp32 in shared memory) is packed to bf16.
 // Block = (sequence, kv group), 8 warps; warp w takes key blocks w, w + 8, ...
 // =================================================================================================
-constexpr int DM_VT_BYTES = 8 * 2 * 2048;          // per warp: two 16-key x 128-byte V tiles (double buffer)
-constexpr int DM_FIXED_BYTES = DM_VT_BYTES /* also the per-warp partial outputs afterwards */ + (DEC_MAX_QPK * HD + 2 * DEC_MAX_QPK) * 4;
+// DM_NVB = V tiles (16 keys x 128 B, swizzled) per warp requested ahead by cp.async: 4 (all of V up to 512 keys in flight from
+// the first instruction on) while two blocks still fit an SM, else 2 (long cache rows: the score buffer takes the room)
+constexpr int dm_vt_bytes(int nvb) { return 8 * nvb * 2048; }
+constexpr int dm_fixed_bytes(int nvb) {
+  return dm_vt_bytes(nvb) /* also the per-warp partial outputs afterwards */ + (DEC_MAX_QPK * HD + 2 * DEC_MAX_QPK) * 4 + MAX_PREFIX * 256 /* prefix k | v */;
+}
 
 __device__ __forceinline__ void mma_bf16_16816(float (&d)[4], uint32_t a0, uint32_t a1, uint32_t a2, uint32_t a3, uint32_t b0, uint32_t b1) {
   asm volatile("mma.sync.aligned.m16n8k16.row.col.f32.bf16.bf16.f32 {%0,%1,%2,%3}, {%4,%5,%6,%7}, {%8,%9}, {%0,%1,%2,%3};"
@@ -1457,6 +1461,13 @@ __device__ __forceinline__ void ldmatrix_x4_trans(uint32_t (&r)[4], uint32_t sme
                : "=r"(r[0]), "=r"(r[1]), "=r"(r[2]), "=r"(r[3]) : "r"(smem_addr));
 }
 
+__device__ __forceinline__ void cp_async_16(uint32_t dst_smem, const void* src, int src_bytes) {   // src_bytes 0: zero-fill
+  asm volatile("cp.async.cg.shared.global [%0], [%1], 16, %2;" ::"r"(dst_smem), "l"(src), "r"(src_bytes) : "memory");
+}
+__device__ __forceinline__ void cp_async_commit() { asm volatile("cp.async.commit_group;" ::: "memory"); }
+template <int N> __device__ __forceinline__ void cp_async_wait() { asm volatile("cp.async.wait_group %0;" ::"n"(N) : "memory"); }
+
+template <int DM_NVB>
 __global__ void __launch_bounds__(DEC_THREADS, 2) attn_decode_mma_kernel(const bf16* __restrict__ qkv, const bf16* __restrict__ ck,
                                                                          const bf16* __restrict__ cv, const int* __restrict__ lens, bf16* out,
                                                                          const bf16* __restrict__ prefix_kv, const float* __restrict__ gate,
@@ -1464,9 +1475,10 @@ __global__ void __launch_bounds__(DEC_THREADS, 2) attn_decode_mma_kernel(const b
   extern __shared__ __align__(128) uint8_t sdm[];
   uint8_t* vt = sdm;                                                    // [8 warps][2][16 keys][128 B], later [8][8][64] floats
   float* spart = reinterpret_cast<float*>(sdm);
-  float* sout = reinterpret_cast<float*>(sdm + DM_VT_BYTES);            // [8][64]
+  float* sout = reinterpret_cast<float*>(sdm + dm_vt_bytes(DM_NVB));    // [8][64]
   float* sinv = sout + DEC_MAX_QPK * HD;                                // [8] 1 / sum, [8] spare
-  float* sc = sinv + 2 * DEC_MAX_QPK;                                   // [qpk][stride] scores / probabilities
+  bf16* spfx = reinterpret_cast<bf16*>(sinv + 2 * DEC_MAX_QPK);         // [MAX_PREFIX][k 64 | v 64] adapter prefix rows of this group
+  float* sc = sinv + 2 * DEC_MAX_QPK + MAX_PREFIX * 64;                 // [qpk][stride] scores / probabilities
   const int stride = max_len + 20;                                      // multiple of 4 (8-byte P loads), rows 16 keys apart in banks
   const int seq = blockIdx.x, g = blockIdx.y;
   const int tid = threadIdx.x, warp = tid >> 5, lane = tid & 31;
@@ -1479,6 +1491,33 @@ __global__ void __launch_bounds__(DEC_THREADS, 2) attn_decode_mma_kernel(const b
   const bf16* kg = ck + ((long long)seq * G + g) * max_len * HD;
   const bf16* vg = cv + ((long long)seq * G + g) * max_len * HD;
 
+  // the adapter prefix rows of this group (k | v, 256 B each) ride in the first cp.async group; they are used at the tail.
+  // (Read straight from global memory they cost 2 x prefix_len dependent L2 round trips per warp: a quarter of the kernel.)
+  if (tid < prefix_len * 16) {
+    const int a = tid >> 4, c = tid & 15;
+    cp_async_16(smem_u32(spfx + a * 128 + c * 8), prefix_kv + (long long)a * ld_qkv + (long long)(g * (qpk + 2) + qpk) * HD + c * 8, 16);
+  }
+  float q0 = 0.f, q1 = 0.f, gate_h = 0.f;
+  if (warp < qpk && prefix_len > 0) {
+    q0 = __bfloat162float(qrow[warp * HD + lane]) * scale;
+    q1 = __bfloat162float(qrow[warp * HD + lane + 32]) * scale;
+    gate_h = gate[g * qpk + warp];
+  }
+  // ---- V: this warp's first DM_NVB tiles (keys 16 (warp + 8 i) .. +15) are requested NOW, by cp.async straight into the
+  // swizzled tiles, so that K and V share one memory round trip (up to 512 keys: all of V); rows at or beyond len are zero-filled
+  const int nblk16 = (len + 15) >> 4;
+  const uint32_t mytile_s = smem_u32(vt + warp * (DM_NVB * 2048));
+  auto fetch_block = [&](int blk, int buf) {
+#pragma unroll
+    for (int i = 0; i < 4; ++i) {
+      const int e = lane + 32 * i, kin = e >> 3, c = e & 7, key = blk * 16 + kin;
+      const bool ok = blk < nblk16 && key < len;
+      cp_async_16(mytile_s + buf * 2048 + kin * 128 + ((c ^ (kin & 7)) << 4), reinterpret_cast<const uint4*>(vg + (long long)(ok ? key : 0) * HD) + c, ok ? 16 : 0);
+    }
+    cp_async_commit();
+  };
+#pragma unroll
+  for (int i = 0; i < DM_NVB; ++i) fetch_block(warp + 8 * i, i);
   // ---- scores: A = Q (head r, unscaled bf16), B = K^T, fp32 accumulate, scale applied to the result ----
   {
     uint4 qa[2] = {make_uint4(0, 0, 0, 0), make_uint4(0, 0, 0, 0)};
@@ -1515,52 +1554,6 @@ __global__ void __launch_bounds__(DEC_THREADS, 2) attn_decode_mma_kernel(const b
       }
     }
   }
-  // the first two V blocks of this warp are requested before the softmax: their latency hides behind it
-  const int nblk16 = (len + 15) >> 4;
-  auto load_block = [&](int blk, uint4 (&v)[4]) {   // this lane's four 16-byte chunks of a 16 x 128 B tile: e = lane + 32 i -> key e / 8, chunk e % 8
-#pragma unroll
-    for (int i = 0; i < 4; ++i) {
-      const int e = lane + 32 * i, key = blk * 16 + (e >> 3);
-      v[i] = (blk < nblk16 && key < len) ? __ldg(reinterpret_cast<const uint4*>(vg + (long long)key * HD) + (e & 7)) : make_uint4(0, 0, 0, 0);
-    }
-  };
-  uint4 vreg0[4], vreg1[4];
-  load_block(warp, vreg0);
-  load_block(warp + 8, vreg1);
-  // gate * softmax(q . prefix_k) prefix_v of head `warp` (its own softmax, ger/adapter.py:139-146) depends on q only: it is
-  // computed here, while the K / V requests above are in flight, instead of at the tail of the block
-  float pfx0 = 0.f, pfx1 = 0.f;
-  if (warp < qpk && prefix_len > 0) {
-    const float q0 = __bfloat162float(qrow[warp * HD + lane]) * scale, q1 = __bfloat162float(qrow[warp * HD + lane + 32]) * scale;
-    const long long koff = (long long)(g * (qpk + 2) + qpk) * HD;
-    float ps[MAX_PREFIX];
-    float pm = -INFINITY;
-#pragma unroll
-    for (int a = 0; a < MAX_PREFIX; ++a) {
-      ps[a] = -INFINITY;
-      if (a < prefix_len) {
-        const bf16* kr = prefix_kv + (long long)a * ld_qkv + koff;
-        float s2 = q0 * __bfloat162float(kr[lane]) + q1 * __bfloat162float(kr[lane + 32]);
-        ps[a] = warp_sum(s2);
-        pm = fmaxf(pm, ps[a]);
-      }
-    }
-    float psum = 0.f;
-#pragma unroll
-    for (int a = 0; a < MAX_PREFIX; ++a) {
-      ps[a] = (a < prefix_len) ? __expf(ps[a] - pm) : 0.f;
-      psum += ps[a];
-    }
-    const float gs = gate[g * qpk + warp] / psum;
-#pragma unroll
-    for (int a = 0; a < MAX_PREFIX; ++a) {
-      if (a < prefix_len) {
-        const bf16* vr = prefix_kv + (long long)a * ld_qkv + koff + HD;
-        pfx0 += gs * ps[a] * __bfloat162float(vr[lane]);
-        pfx1 += gs * ps[a] * __bfloat162float(vr[lane + 32]);
-      }
-    }
-  }
   __syncthreads();
   // ---- softmax: warp h owns head h; probabilities beyond len (up to the next multiple of 16) are zeroed for the P V tiles ----
   if (warp < qpk) {
@@ -1586,18 +1579,10 @@ __global__ void __launch_bounds__(DEC_THREADS, 2) attn_decode_mma_kernel(const b
 #pragma unroll
     for (int j = 0; j < 4; ++j) acc[nb][j] = 0.f;
   {
-    uint8_t* mytile = vt + warp * 4096;
-    const uint32_t mytile_s = smem_u32(mytile);
-    const int nblk = nblk16;
-    // one 16-key step out of buffer `buf` (compile-time, so the two register sets stay in registers)
-    auto step = [&](int blk, int buf, uint4 (&vr)[4]) {
-      uint8_t* tile = mytile + buf * 2048;
-#pragma unroll
-      for (int i = 0; i < 4; ++i) {
-        const int e = lane + 32 * i, key = e >> 3, c = e & 7;
-        *reinterpret_cast<uint4*>(tile + key * 128 + ((c ^ (key & 7)) << 4)) = vr[i];
-      }
-      load_block(blk + 16, vr);                        // two blocks ahead: the rows are in flight during this and the next step
+    int it = 0;
+    for (int blk = warp; blk < nblk16; blk += 8, ++it) {
+      const int buf = it % DM_NVB;
+      cp_async_wait<DM_NVB - 1>();                     // one group per tile, DM_NVB ahead: the oldest (this tile) has landed
       __syncwarp();
       // A = P[head r][16 keys]: a0 = keys 2q, 2q+1 ; a2 = keys 2q+8, 2q+9 (rows 8..15 of the tile are unused: a1 = a3 = 0)
       uint32_t a0 = 0u, a2 = 0u;
@@ -1618,12 +1603,10 @@ __global__ void __launch_bounds__(DEC_THREADS, 2) attn_decode_mma_kernel(const b
         mma_bf16_16816(acc[2 * j], a0, 0u, a2, 0u, b[0], b[1]);
         mma_bf16_16816(acc[2 * j + 1], a0, 0u, a2, 0u, b[2], b[3]);
       }
-      __syncwarp();                                    // this buffer is rewritten two steps later
-    };
-    for (int blk = warp; blk < nblk; blk += 16) {
-      step(blk, 0, vreg0);
-      if (blk + 8 < nblk) step(blk + 8, 1, vreg1);
+      __syncwarp();                                    // every lane has read the tile: it is refilled DM_NVB tiles ahead
+      fetch_block(blk + 8 * DM_NVB, buf);
     }
+    cp_async_wait<0>();                                // trailing (zero-fill) requests must land before the tiles become `spart`
   }
   __syncthreads();                                     // every warp is done with its V tiles: the region becomes the partial outputs
   if (r < DEC_MAX_QPK) {
@@ -1641,6 +1624,33 @@ __global__ void __launch_bounds__(DEC_THREADS, 2) attn_decode_mma_kernel(const b
   __syncthreads();
   if (warp >= qpk) return;
   // ---- warp h finishes head h: + gate * softmax(q . prefix_k) prefix_v (its own softmax, ger/adapter.py:139-146) ----
+  float pfx0 = 0.f, pfx1 = 0.f;
+  if (prefix_len > 0) {
+    float ps[MAX_PREFIX];
+    float pm = -INFINITY;
+#pragma unroll
+    for (int a = 0; a < MAX_PREFIX; ++a) {
+      ps[a] = -INFINITY;
+      if (a < prefix_len) {
+        ps[a] = warp_sum(q0 * __bfloat162float(spfx[a * 128 + lane]) + q1 * __bfloat162float(spfx[a * 128 + lane + 32]));
+        pm = fmaxf(pm, ps[a]);
+      }
+    }
+    float psum = 0.f;
+#pragma unroll
+    for (int a = 0; a < MAX_PREFIX; ++a) {
+      ps[a] = (a < prefix_len) ? __expf(ps[a] - pm) : 0.f;
+      psum += ps[a];
+    }
+    const float gs = gate_h / psum;
+#pragma unroll
+    for (int a = 0; a < MAX_PREFIX; ++a) {
+      if (a < prefix_len) {
+        pfx0 += gs * ps[a] * __bfloat162float(spfx[a * 128 + 64 + lane]);
+        pfx1 += gs * ps[a] * __bfloat162float(spfx[a * 128 + 96 + lane]);
+      }
+    }
+  }
   const int h = g * qpk + warp;
   const float o0 = sout[warp * HD + lane] + pfx0, o1 = sout[warp * HD + lane + 32] + pfx1;
   bf16* orow = out + (long long)seq * H * HD + h * HD;
@@ -1799,22 +1809,25 @@ extern "C" int dh_attention_decode(const void* qkv, const void* cache_k, const v
     const char* e = getenv("DH_DEC_CUDA_CORES");
     variant = (e && e[0] == '1') ? 0 : 1;
     DH_CUDA(cudaFuncSetAttribute(attn_decode_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, 200 * 1024));
-    DH_CUDA(cudaFuncSetAttribute(attn_decode_mma_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, 200 * 1024));
+    DH_CUDA(cudaFuncSetAttribute(attn_decode_mma_kernel<2>, cudaFuncAttributeMaxDynamicSharedMemorySize, 200 * 1024));
+    DH_CUDA(cudaFuncSetAttribute(attn_decode_mma_kernel<4>, cudaFuncAttributeMaxDynamicSharedMemorySize, 200 * 1024));
   }
   const long long ld = (long long)n_groups * (q_per_kv + 2) * HD;
   const bf16* pkv = (const bf16*)(prefix_len > 0 ? prefix_kv : nullptr);
   const int plen = prefix_kv ? prefix_len : 0;
   const float scale = 1.0f / sqrtf((float)HD);
   if (variant == 1) {
-    const size_t smem = (size_t)DM_FIXED_BYTES + (size_t)q_per_kv * (max_len + 20) * sizeof(float);
+    const size_t score_bytes = (size_t)q_per_kv * (max_len + 20) * sizeof(float);
+    const bool deep = 2 * (dm_fixed_bytes(4) + score_bytes + 1024) <= 227 * 1024;      // two blocks per SM with 4 tiles per warp?
+    const size_t smem = (size_t)dm_fixed_bytes(deep ? 4 : 2) + score_bytes;
     DH_CHECK(smem <= 200 * 1024, "dh_attention_decode: max_len %d too large for the score buffer", max_len);
-    DH_CHECK((((uintptr_t)qkv | (uintptr_t)cache_k | (uintptr_t)cache_v) & 15) == 0, "dh_attention_decode: operands must be 16-byte aligned");
-    // three blocks per SM (80 registers) once 3 x (smem + 1 KB reserved) fits the SM's 228 KB and there is more than one wave of two
-    // two blocks per SM (124 registers).  Three (an 80-register build, 220 B of spills) was measured SLOWER on 512 blocks:
+    DH_CHECK((((uintptr_t)qkv | (uintptr_t)cache_k | (uintptr_t)cache_v | (uintptr_t)pkv) & 15) == 0, "dh_attention_decode: operands must be 16-byte aligned");
+    DH_CHECK(plen <= MAX_PREFIX, "dh_attention_decode: prefix_len %d > %d", plen, MAX_PREFIX);
+    // two blocks per SM (118 registers).  Three (an 80-register build, 220 B of spills) was measured SLOWER on 512 blocks:
     // 2.07 vs 1.89 ms per token step of 128 sequences.
-    DH_CUDA(launch_pdl(attn_decode_mma_kernel, dim3(nseq, n_groups), dim3(DEC_THREADS), smem, (cudaStream_t)stream, (const bf16*)qkv,
-                       (const bf16*)cache_k, (const bf16*)cache_v, (const int*)lens, (bf16*)out, pkv, (const float*)gate, max_len, n_groups, q_per_kv, plen,
-                       ld, scale));
+    DH_CUDA(launch_pdl(deep ? attn_decode_mma_kernel<4> : attn_decode_mma_kernel<2>, dim3(nseq, n_groups), dim3(DEC_THREADS), smem,
+                       (cudaStream_t)stream, (const bf16*)qkv, (const bf16*)cache_k, (const bf16*)cache_v, (const int*)lens, (bf16*)out, pkv,
+                       (const float*)gate, max_len, n_groups, q_per_kv, plen, ld, scale));
   } else {
     const size_t smem = ((size_t)DEC_FIXED_FLOATS + (size_t)q_per_kv * (max_len + 1)) * sizeof(float);
     DH_CHECK(smem <= 200 * 1024, "dh_attention_decode: max_len %d too large for the score buffer", max_len);

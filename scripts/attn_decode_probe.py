@@ -1,5 +1,5 @@
 """Decode attention alone on cold KV caches: a CUDA graph of 22 calls over 22 different caches (one per layer, as in the
-token step), events around the replay.  Usage: [DH_DEC_VARIANT=0|1] python scripts/attn_decode_probe.py [max_len]"""
+token step), events around the replay.  Usage: [DH_DEC_CUDA_CORES=1] python scripts/attn_decode_probe.py [max_len [sequences]]"""
 import os
 import sys
 
@@ -11,7 +11,8 @@ from dualhyp_b200 import ops  # noqa: E402
 
 max_len = int(sys.argv[1]) if len(sys.argv) > 1 else 2048
 dev = torch.device("cuda", 0)
-nseq, G, qpk, L = 64, 4, 8, 22
+nseq = int(sys.argv[2]) if len(sys.argv) > 2 else 64
+G, qpk, L = 4, 8, 22
 torch.manual_seed(0)
 lens = torch.randint(394, 545, (nseq,), dtype=torch.int32, device=dev)
 ck = [torch.randn(nseq, G, max_len, 64, device=dev).bfloat16() for _ in range(L)]
@@ -43,4 +44,4 @@ for _ in range(5):
     torch.cuda.synchronize()
     best = min(best, e0.elapsed_time(e1))
 mb = float(lens.sum()) * G * 64 * 2 * 2 / 1e6
-print(f"variant {os.environ.get('DH_DEC_VARIANT', '0')} max_len {max_len}: {best / L * 1e3:.2f} us per call, K+V {mb:.1f} MB -> {mb / (best / L) / 1e3:.2f} TB/s")
+print(f"{nseq} sequences, cache rows of {max_len}: {best / L * 1e3:.2f} us per call, K+V {mb:.1f} MB -> {mb / (best / L) / 1e3:.2f} TB/s")

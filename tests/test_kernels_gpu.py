@@ -587,11 +587,12 @@ def test_attention_decode_matches_prefill():
     assert rel(dec, ref) < 1e-2, report("decode attn", dec, ref)
 
 
-@pytest.mark.parametrize("nseq,G,qpk,prefix", [(5, 4, 8, 10), (3, 2, 2, 0), (2, 1, 1, 16)])
-def test_attention_decode_against_fp32(nseq, G, qpk, prefix):
-    """The decode kernel against fp32 softmax attention over the valid cache slots (lengths from 1 to several hundred,
-    not multiples of the 32-key slice width), with and without the gated prefix."""
-    H, max_len = G * qpk, 640
+@pytest.mark.parametrize("nseq,G,qpk,prefix,max_len", [(5, 4, 8, 10, 640), (3, 2, 2, 0, 640), (2, 1, 1, 16, 640), (4, 4, 8, 10, 2048)])
+def test_attention_decode_against_fp32(nseq, G, qpk, prefix, max_len):
+    """The decode kernel against fp32 softmax attention over the valid cache slots (lengths from 1 to the whole row, not
+    multiples of the 16-key tiles), with and without the gated prefix; rows of 640 slots take the 4-tiles-ahead V prefetch,
+    rows of 2048 x 8 heads the 2-tiles-ahead build (the score buffer takes the shared memory)."""
+    H = G * qpk
     N = G * (qpk + 2) * 64
     lens = synthetic.hash_ints((nseq,), 3, 401, 1, max_len + 1).to(torch.int32)
     lens[0], lens[-1] = 1, max_len
