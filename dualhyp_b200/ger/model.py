@@ -46,13 +46,15 @@ class _DecoderFn(torch.autograd.Function):
         grads = eng.backward(d_hidden.reshape(-1, d_hidden.shape[-1]).to(torch.bfloat16), ctx.step_id)
         scale = model._pending_grad_scale
         model._pending_grad_scale = None
-        out = []
-        for n in ctx.names:
-            g = grads.get(n)
-            if g is not None and scale is not None:
-                g = g * scale
-            out.append(g)
-        return (None, None, None, *out)
+        if scale is not None:
+            # the engine hands out views of a few batched buffers (all gates, all prefixes, one tensor per LoRA wgrad): scale
+            # each underlying buffer once, in place, instead of one elementwise launch per parameter
+            bases = {}
+            for g in grads.values():
+                b = g._base if g._base is not None else g
+                bases[id(b)] = b
+            torch._foreach_mul_(list(bases.values()), scale)
+        return (None, None, None, *[grads.get(n) for n in ctx.names])
 
 
 class _LMHeadFn(torch.autograd.Function):
