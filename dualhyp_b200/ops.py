@@ -3,6 +3,7 @@ current stream only; every function here enqueues hand-written sm_100a kernels a
 from __future__ import annotations
 
 import ctypes as C
+import os
 from typing import Optional
 
 import torch
@@ -188,7 +189,8 @@ def decode_split_k(N: int, K: int) -> int:
     at least two 64-wide k-blocks per CTA."""
     sms = int(_lib.load().dh_sm_count()) or 148
     tiles = max(1, N // 128)
-    return max(1, min(sms // tiles, (K // 64) // 2, 8))
+    cap = int(os.environ.get("DH_DECODE_SPLIT_MAX", "8"))          # developer knob for A/B runs
+    return max(1, min(sms // tiles, (K // 64) // 2, cap))
 
 
 @_profiled("rmsnorm_bwd")
