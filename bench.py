@@ -34,6 +34,9 @@ UNIT = "tokens/s"
 SEQ_LEN = 512
 PER_GPU_BATCH = 16
 DECODE_METRIC = "DualHyp infer utterances/s (greedy KV-cache decode, adapter TinyLlama-1.1B, 5+5 N-best prompts, 64 new tokens)"
+# dram__bytes_read.sum + dram__bytes_write.sum of one decode token step by utterances per GPU (profiles/r01zz_decode_traffic.txt;
+# ncu flushes the caches between kernels, so 0.62 GB of it are split-K partial products that stay in L2 in a graph replay)
+NCU_DECODE_DRAM_BYTES = {128: 3.99e9}
 DECODE_UTTS, DECODE_NEW = 128, 64     # 128 sequences per token step: the widest the decode GEMM's one-tile M takes
 LORA = dict(r=8, alpha=16, dropout=0.0, to_query=True, to_key=True, to_value=True, to_projection=True)
 # DRAM bytes per launch of the dominant GEMMs from one `ncu --set full` capture of this command (profiles/r01u_ncu_full_summary.txt);
@@ -300,7 +303,8 @@ def decode_line(args, r, world, utts, clocks, steps=None):
             "e2e": {"value": round(utts / (r["ms_e2e"] / 1e3), 2), "unit": "utt/s", "h2d_bytes_per_step": r["h2d"], "d2h_bytes_per_step": r["d2h"],
                     "ms_per_step": round(r["ms_e2e"] / steps, 3)},
             "gpu_launches": r["launches"], "clocks": clocks,
-            "roofline": {"bound": "hbm", "achieved": round(ach, 1), "peak": peak, "unit": "GB/s", "frac": round(ach / peak, 4), "traffic": None,
+            "roofline": {"bound": "hbm", "achieved": round(ach, 1), "peak": peak, "unit": "GB/s", "frac": round(ach / peak, 4),
+                         "traffic": NCU_DECODE_DRAM_BYTES.get(args.utts),
                          "peak_source": "measured copy bandwidth (MEASURED_PEAKS.json)" if peaks else "fallback 6.5 TB/s",
                          "kernel": "one decode token step (CUDA graph of %d kernels: lm_head, arg-max, 22 layers over the KV cache)" % r["kernels_per_token"],
                          "algorithmic_bytes_per_launch": round(r["step_bytes"]), "avg_ms": round(r["tok_ms"], 4),
