@@ -103,12 +103,12 @@ class DecodeService:
         M = int(cu[-1])
         pos_h = torch.cat([torch.arange(int(L), dtype=torch.int32) for L in lens.tolist()])
         seq_h = torch.repeat_interleave(torch.tensor(slots, dtype=torch.int32), lens.long())     # cache row = slot
+        stage = (lambda t: t.pin_memory().to(dev, non_blocking=True)) if dev.type == "cuda" else (lambda t: t)
         if all(p.is_cuda for p in prompts):
             ids = torch.cat(list(prompts))
         else:
-            ids = torch.cat([p.cpu() for p in prompts]).pin_memory().to(dev, non_blocking=True)
-        meta = torch.cat((cu, pos_h, seq_h, lens, torch.tensor(slots, dtype=torch.int32),
-                          torch.tensor(limits, dtype=torch.int32))).pin_memory().to(dev, non_blocking=True)
+            ids = stage(torch.cat([p.cpu() for p in prompts]))
+        meta = stage(torch.cat((cu, pos_h, seq_h, lens, torch.tensor(slots, dtype=torch.int32), torch.tensor(limits, dtype=torch.int32))))
         o = 0
         cu_d, o = meta[o: o + k + 1], o + k + 1
         pos_d, o = meta[o: o + M], o + M
