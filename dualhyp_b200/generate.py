@@ -156,6 +156,7 @@ def generate_batch(model, prompts: Sequence[Tensor], max_new_tokens: int, eos_id
     lens_d = lens.to(dev)
     eng.alloc_cache_for(n, total)
     loop = _decode_loop(model, eng, n, max_new_tokens)
+    stage = (lambda t: t.pin_memory().to(dev, non_blocking=True)) if dev.type == "cuda" else (lambda t: t)
     if packed_prefill:
         # prompts packed into one row (no pad tokens): cu_seqlens / per-token positions / sequence ids are built on the host
         cu = torch.zeros(n + 1, dtype=torch.int32)
@@ -166,8 +167,8 @@ def generate_batch(model, prompts: Sequence[Tensor], max_new_tokens: int, eos_id
         if all(p.is_cuda for p in prompts):
             ids = torch.cat(list(prompts))
         else:
-            ids = torch.cat([p.cpu() for p in prompts]).pin_memory().to(dev, non_blocking=True)
-        meta = torch.cat((cu, pos_h, seq_h)).pin_memory().to(dev, non_blocking=True)       # one small H2D copy
+            ids = stage(torch.cat([p.cpu() for p in prompts]))
+        meta = stage(torch.cat((cu, pos_h, seq_h)))                                        # one small H2D copy
         cu_d, pos_d, seq_d = meta[: n + 1], meta[n + 1: n + 1 + M], meta[n + 1 + M:]
         hidden = eng.prefill_packed(ids, cu_d, pos_d, seq_d, Tmax, loop.packed)
         last = hidden[(cu_d[1:] - 1).long()]                                              # ln_f state of each prompt's last token

@@ -127,3 +127,23 @@ def test_budget_and_length_checks():
     except ValueError:
         return
     raise AssertionError("a prompt that cannot fit max_seq_length was accepted")
+
+
+def test_generate_batch_host_logic_on_the_stand_in_engine(monkeypatch):
+    """generate.generate_batch on the same stand-in: packed prompt staging (cu_seqlens, per-token positions, cache rows), the
+    device-side step counter, the inclusive EOS cut and the result assembly."""
+    from dualhyp_b200.generate import generate_batch
+    monkeypatch.setattr(ops, "argmax", lambda logits, out: out.copy_(logits.float().argmax(-1)))
+    prompts = _prompts(5, 8)
+    m = _Model()
+    got = generate_batch(m, prompts, 7, use_graph=False)
+    assert [g.tolist() for g in got] == [_alone(p, 7) for p in prompts]
+    assert m._engine.prefills == [[0, 1, 2, 3, 4]]
+    eos = got[1][len(prompts[1]) + 2].item()
+    cut = generate_batch(m, prompts, 7, eos_id=eos, poll_every=2, use_graph=False)
+    for c, p in zip(cut, prompts):
+        full = _alone(p, 7)
+        gen = full[len(p):]
+        assert c.tolist() == (full if eos not in gen else full[: len(p) + gen.index(eos) + 1])
+    raw = generate_batch(m, prompts, 3, use_graph=False, return_device=True)
+    assert raw.shape == (5, 3) and raw.tolist() == [_alone(p, 3)[len(p):] for p in prompts]
