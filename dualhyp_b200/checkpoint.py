@@ -19,6 +19,20 @@ import torch
 
 Tensor = torch.Tensor
 FORMAT = "dualhyp-trainable-v1"
+# RelPrompt: `resize_token_embeddings(3)` appends randomly initialised wte rows for <<C>>/<<M>>/<<N>> (ger/relprompt.py:215-230)
+# and `mark_only_lora_as_trainable` then freezes wte (finetune/relprompt.py:168-169).  The LoRA factors are trained AGAINST those
+# rows, so a trainable-only checkpoint has to carry them: they are stored under this extra key (ignored by the reference's
+# `load_state_dict(strict=False)`), rows [padded_vocab_size:] of transformer.wte.weight.
+EXTRA_WTE_KEY = "transformer.wte.weight::extra_rows"
+
+
+def _extra_wte_rows(model: torch.nn.Module) -> Optional[Tensor]:
+    cfg = getattr(model, "config", None)
+    wte = getattr(getattr(model, "transformer", {}), "wte", None) if hasattr(model, "transformer") else None
+    if cfg is None or wte is None or getattr(cfg, "padded_vocab_size", None) is None:
+        return None
+    w = wte.weight
+    return w.detach()[cfg.padded_vocab_size:] if w.shape[0] > cfg.padded_vocab_size else None
 
 
 def default_filter(name: str, _value=None) -> bool:
@@ -47,6 +61,9 @@ def save_trainable(model: torch.nn.Module, file_path: Union[str, Path], key_filt
     sd = trainable_state(model, key_filter)
     if not sd:
         raise ValueError("no trainable tensors selected: call mark_only_*_as_trainable(model) or pass a key_filter")
+    extra_rows = _extra_wte_rows(model)
+    if extra_rows is not None:
+        sd[EXTRA_WTE_KEY] = extra_rows.to("cpu").clone()
     file_path = Path(file_path)
     file_path.parent.mkdir(parents=True, exist_ok=True)
     payload = {"model": sd, "format": FORMAT}
@@ -63,7 +80,16 @@ def load_trainable(model: torch.nn.Module, file_path: Union[str, Path], require_
     names the model does not have or shape mismatches; with require_all, also when a parameter that requires grad
     got no value from the file.  Returns the names loaded."""
     ckpt = torch.load(str(file_path), map_location="cpu", weights_only=False)
-    sd = ckpt.get("model", ckpt)
+    sd = dict(ckpt.get("model", ckpt))
+    extra_rows = sd.pop(EXTRA_WTE_KEY, None)
+    own_extra = _extra_wte_rows(model)
+    if own_extra is not None and extra_rows is None and "transformer.wte.weight" not in sd:
+        raise KeyError(f"the model has {own_extra.shape[0]} resized wte rows (resize_token_embeddings) but the checkpoint holds none: "
+                       "the LoRA factors were trained against embeddings this file does not provide")
+    if extra_rows is not None:
+        if own_extra is None or tuple(own_extra.shape) != tuple(extra_rows.shape):
+            raise ValueError(f"checkpoint carries {tuple(extra_rows.shape)} extra wte rows, the model has "
+                             f"{None if own_extra is None else tuple(own_extra.shape)}: call resize_token_embeddings first")
     own = model.state_dict()
     unknown = [k for k in sd if k not in own]
     if unknown:
@@ -77,4 +103,10 @@ def load_trainable(model: torch.nn.Module, file_path: Union[str, Path], require_
         if missing:
             raise KeyError(f"trainable parameters missing from the checkpoint: {missing[:5]}{' ...' if len(missing) > 5 else ''}")
     model.load_state_dict(sd, strict=False)
-    return list(sd)
+    loaded = list(sd)
+    if extra_rows is not None:
+        with torch.no_grad():
+            w = model.transformer.wte.weight
+            w[model.config.padded_vocab_size:].copy_(extra_rows.to(w.device, w.dtype))     # in place: bumps the version, the engine re-packs
+        loaded.append(EXTRA_WTE_KEY)
+    return loaded

@@ -172,7 +172,7 @@ class DecoderEngine:
                 d["gate"] = tr[p + "gating_factor"].detach().to(dev, torch.float32).reshape(-1).contiguous()
             if s.has_lora(i):
                 C, r = s.n_embd, s.r
-                if s.lora_qkv:
+                if s.lora_qkv and (p + "attn.lora_A") in tr:       # absent: the module was merged into W (LoRALinear.merge)
                     A, Bm = tr[p + "attn.lora_A"].detach().to(dev), tr[p + "attn.lora_B"].detach().to(dev)
                     a_pad = torch.zeros((LORA_PAD, C), device=dev, dtype=torch.bfloat16)
                     a_pad[: 3 * r] = (A.float() * scaling).to(torch.bfloat16)
@@ -183,7 +183,7 @@ class DecoderEngine:
                     b_ext[C + kv:, 2 * r:3 * r] = Bm[C + kv:].to(torch.bfloat16)    # v rows use [:, 2r:3r]
                     d["qkv_a"], d["qkv_b"] = a_pad, b_ext
                     d["qkv_a_t"], d["qkv_b_t"] = a_pad.t().contiguous(), b_ext.t().contiguous()
-                if s.lora_proj:
+                if s.lora_proj and (p + "proj.lora_A") in tr:
                     A, Bm = tr[p + "proj.lora_A"].detach().to(dev), tr[p + "proj.lora_B"].detach().to(dev)
                     a_pad = torch.zeros((LORA_PAD, C), device=dev, dtype=torch.bfloat16)
                     a_pad[:r] = (A.float() * scaling).to(torch.bfloat16)

@@ -80,7 +80,10 @@ class DecodeLoop:
     def capture(self) -> None:
         """Record one body() into a graph.  Must follow at least one eager body() of the same shape (first-use
         initialisation inside the C ABI -- function attributes, the device query -- is not capturable)."""
-        sig = tuple(t.data_ptr() for t in self.eng.cache_k)
+        # everything the captured launches bake in about the cache: row count, row length (the kernels' max_len stride) and the
+        # K and V base pointers -- the caching allocator can hand a re-allocated cache of another shape the same pointers
+        eng = self.eng
+        sig = (self.n, eng.cache_max_len, tuple(t.data_ptr() for t in eng.cache_k), tuple(t.data_ptr() for t in eng.cache_v))
         if self.graph is not None and sig == self.cache_sig:
             return
         torch.cuda.synchronize()

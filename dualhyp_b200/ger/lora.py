@@ -71,8 +71,10 @@ class LoRALinear(LoRALayer):
     def merge(self):
         """W += (B A) * scaling  (ger/lora.py:152-157); tiny host-side update of the frozen weight."""
         if self.r > 0 and not self.merged:
-            self.linear.weight.data += ((self.lora_B.data.float() @ self.lora_A.data.float()) * self.scaling).to(self.linear.weight.dtype)
-            self.merged = True
+            delta = ((self.lora_B.data.float() @ self.lora_A.data.float()) * self.scaling).to(self.linear.weight.dtype)
+            with torch.no_grad():
+                self.linear.weight.add_(delta)      # in place THROUGH the parameter: bumps its version, so the engine re-packs W
+            self.merged = True                      # the engine drops the LoRA K-extension of merged modules (GPT._trainables)
 
 
 class LoRAQKVLinear(LoRALinear):
@@ -109,7 +111,8 @@ class LoRAQKVLinear(LoRALinear):
             for i, s in enumerate(self.qkv_shapes):
                 parts.append(Bm[off:off + s] @ A[i * r:(i + 1) * r])
                 off += s
-            self.linear.weight.data += (torch.cat(parts, dim=0) * self.scaling).to(self.linear.weight.dtype)
+            with torch.no_grad():
+                self.linear.weight.add_((torch.cat(parts, dim=0) * self.scaling).to(self.linear.weight.dtype))
             self.merged = True
 
 

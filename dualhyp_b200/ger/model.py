@@ -274,8 +274,12 @@ class GPT(nn.Module):
 
     def _trainables(self) -> Tuple[Tuple[str, ...], Tuple[Tensor, ...]]:
         names, tensors = [], []
+        # a merged LoRA module computes linear(x) only (reference ger/lora.py:159-161): its factors are already inside W
+        merged = tuple(mn + ".lora_" for mn, m in self.named_modules() if getattr(m, "merged", False))
         for n, p in self.named_parameters():
             if "noise_classifier" in n:
+                continue
+            if merged and n.startswith(merged):
                 continue
             if self._trainable_filter(n):
                 names.append(n)

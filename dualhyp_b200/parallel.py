@@ -59,6 +59,10 @@ class FlatTrainables:
         self.step_count += 1
         ops.adamw_step(self.flat, self.grad, self.exp_avg, self.exp_avg_sq, lr, betas[0], betas[1], eps, weight_decay, self.step_count,
                        grad_scale)
+        # the kernel wrote the parameters through the flat buffer: tell autograd / every (data_ptr, _version) cache key
+        # (generate._decode_loop, serve.DecodeService, GPT._frozen_sig) that they changed
+        for p in self.params:
+            torch.autograd.graph.increment_version(p)
 
 
 def shard_indices(n_items: int, rank: int, world: int) -> List[int]:

@@ -143,6 +143,88 @@ def test_trainable_only_checkpoint_roundtrip(tmp_path):
     checkpoint.load_trainable(b, tmp_path / "partial.pth", require_all=False)
 
 
+def test_relprompt_checkpoint_carries_resized_wte_rows(tmp_path):
+    """resize_token_embeddings(3) appends random wte rows that mark_only_lora_as_trainable freezes (finetune/relprompt.py:168-169):
+    a trainable-only checkpoint must carry them, restore them, and refuse a file without them."""
+    from dualhyp_b200 import checkpoint
+    from dualhyp_b200.ger import relprompt
+    cfg = relprompt.Config.from_name("tiny-llama-test", r=4, alpha=8, whisper_dim=48, raven_dim=32, pool_size=5)
+    torch.manual_seed(0)
+    a = relprompt.GPT(cfg)
+    a.resize_token_embeddings(3)
+    relprompt.mark_only_lora_as_trainable(a)
+    torch.manual_seed(1)
+    b = relprompt.GPT(cfg)
+    b.resize_token_embeddings(3)
+    relprompt.mark_only_lora_as_trainable(b)
+    V = cfg.padded_vocab_size
+    with torch.no_grad():
+        b.transformer.wte.weight[:V].copy_(a.transformer.wte.weight[:V])     # the shared frozen base checkpoint
+    assert not torch.equal(a.transformer.wte.weight[V:], b.transformer.wte.weight[V:])
+    path = tmp_path / "rel.pth"
+    checkpoint.save_trainable(a, path)
+    stored = torch.load(str(path), weights_only=False)["model"]
+    assert checkpoint.EXTRA_WTE_KEY in stored and stored[checkpoint.EXTRA_WTE_KEY].shape == (3, cfg.n_embd)
+    assert any("noise_classifier" in k for k in stored) and "transformer.wte.weight" not in stored
+    v0 = b.transformer.wte.weight._version
+    loaded = checkpoint.load_trainable(b, path)
+    assert checkpoint.EXTRA_WTE_KEY in loaded and b.transformer.wte.weight._version > v0      # the engine's frozen signature sees it
+    assert torch.equal(a.transformer.wte.weight, b.transformer.wte.weight)
+    for (n, pa), (_, pb) in zip(a.named_parameters(), b.named_parameters()):
+        if pa.requires_grad:
+            assert torch.equal(pa, pb), n
+    # a file without the rows is refused by a resized model; a file with rows is refused by a model that was not resized
+    del stored[checkpoint.EXTRA_WTE_KEY]
+    torch.save({"model": stored}, str(tmp_path / "norows.pth"))
+    with pytest.raises(KeyError):
+        checkpoint.load_trainable(b, tmp_path / "norows.pth")
+    c = relprompt.GPT(cfg)
+    relprompt.mark_only_lora_as_trainable(c)
+    with pytest.raises(ValueError):
+        checkpoint.load_trainable(c, path)
+
+
+def test_merged_lora_modules_leave_the_trainable_set_and_bump_the_weight_version():
+    """after merge_lora_weights() the factors live inside W; the engine must not add them a second time
+    (GPT._trainables drops them) and must re-pack W (the in-place add bumps the parameter version the frozen signature reads)."""
+    cfg = lora.Config.from_name("tiny-llama-test", **LORA)
+    m = lora.GPT(cfg)
+    lora.mark_only_lora_as_trainable(m)
+    with torch.no_grad():
+        for n, p in m.named_parameters():
+            if "lora_B" in n:
+                p.normal_(0, 0.05)
+    names, _ = m._trainables()
+    assert len(names) == 4 * cfg.n_layer
+    w = m.transformer.h[0].attn.attn.linear.weight
+    v0, before = w._version, w.detach().clone()
+    lora.merge_lora_weights(m)
+    assert w._version > v0 and not torch.equal(before, w)
+    names2, _ = m._trainables()
+    assert names2 == ()
+    at = m.transformer.h[0].attn.attn
+    r = cfg.r
+    A, Bm = at.lora_A.float(), at.lora_B.float()
+    q = cfg.n_embd
+    kv = at.kv_embd_size
+    delta = torch.cat((Bm[:q] @ A[:r], Bm[q:q + kv] @ A[r:2 * r], Bm[q + kv:] @ A[2 * r:])) * (cfg.alpha / cfg.r)
+    assert torch.allclose(w.detach() - before, delta, atol=1e-6)
+    lora.merge_lora_weights(m)                  # idempotent
+    assert torch.allclose(w.detach() - before, delta, atol=1e-6)
+
+
+def test_flat_bucket_adamw_bumps_parameter_versions(monkeypatch):
+    """the fused AdamW writes the parameters through the flat buffer; the (data_ptr, _version) cache keys of
+    the decode loops must see it."""
+    from dualhyp_b200 import parallel
+    ps = [torch.nn.Parameter(torch.randn(4, 3)), torch.nn.Parameter(torch.randn(5))]
+    b = parallel.FlatTrainables(ps)
+    monkeypatch.setattr(parallel.ops, "adamw_step", lambda *a, **k: None)
+    v = [p._version for p in ps]
+    b.adamw_step(lr=1e-3)
+    assert all(p._version > v0 for p, v0 in zip(ps, v))
+
+
 def test_relprompt_mask_token_splice_equals_text_substitution():
     """splicing mask-token ids == the reference's text replace + re-tokenise (inference/relprompt.py:145-157)
     for a tokenizer in which every mask token is one id (what add_special_tokens + resize_token_embeddings(3) gives)."""
