@@ -56,6 +56,9 @@ def parse_args():
     ap.add_argument("--no-cpu-baseline", action="store_true")
     ap.add_argument("--no-roofline", action="store_true")
     ap.add_argument("--no-infer", action="store_true", help="skip the decode sample appended to the training line")
+    ap.add_argument("--padded", action="store_true",
+                    help="train on right-padded [B, T] batches like the reference's collate_fn (tokens/s then counts pad tokens); "
+                         "default: the same samples packed into one row without pad tokens, tokens/s counts REAL tokens")
     ap.add_argument("--utts", type=int, default=DECODE_UTTS, help="decode workload: utterances per GPU per step")
     ap.add_argument("--new-tokens", type=int, default=DECODE_NEW)
     return ap.parse_args()
@@ -386,8 +389,24 @@ def run_native(args):
     model = build_model(args.workload, dev)
     bucket = FlatTrainables(p for p in model.parameters() if p.requires_grad)
     idx_h, labels_h = synthetic.synth_batch(B, T, 32000, 1337 + rank)
+    packed_mode = not args.padded and args.workload != "relprompt"
+    pk_h = pk_d = None
+    longest = T
+    if packed_mode:
+        # the same samples without their right pad (data/av_dataset.py:258-292 pads to the longest sample of the batch):
+        # one packed row + cu_seqlens (dualhyp_b200.collate.pack_varlen), consumed by GPT.forward_packed
+        from dualhyp_b200.collate import pack_varlen
+        samples = []
+        for b in range(B):
+            n = int((labels_h[b] != -1).nonzero().max()) + 1
+            samples.append({"input_ids": idx_h[b, :n].clone(), "labels": labels_h[b, :n].clone()})
+        longest = max(int(smp["input_ids"].numel()) for smp in samples)
+        pk = pack_varlen(samples)
+        pk_h = {k: pk[k].pin_memory() for k in ("input_ids", "targets", "cu_seqlens", "positions")}
+        pk_d = {k: v.to(dev) for k, v in pk_h.items()}
     idx_h, labels_h = idx_h.pin_memory(), labels_h.pin_memory()
     idx_d, labels_d = idx_h.to(dev), labels_h.to(dev)
+    real_tokens = int(pk_h["input_ids"].numel()) if packed_mode else B * T
 
     rel = None
     if args.workload == "relprompt":
@@ -408,10 +427,15 @@ def run_native(args):
 
     def step(idx, labels, sync=True):
         """The driver's micro-step (finetune/ger.py:278-292) with accumulation 1.  sync=False skips the gradient
-        all-reduce: the instrumented roofline pass runs on rank 0 alone and must not enter a collective."""
-        logits = model(idx, lm_head_chunk_size=128)
-        logits[-1] = logits[-1][..., :-1, :]
-        loss = chunked_cross_entropy(logits, labels[..., 1:])
+        all-reduce: the instrumented roofline pass runs on rank 0 alone and must not enter a collective.
+        Packed mode: `idx` is the dict of packed tensors (input_ids, targets, cu_seqlens, positions)."""
+        if packed_mode:
+            logits = model.forward_packed(idx["input_ids"], idx["cu_seqlens"], idx["positions"], longest, lm_head_chunk_size=128)
+            loss = chunked_cross_entropy(logits, idx["targets"])
+        else:
+            logits = model(idx, lm_head_chunk_size=128)
+            logits[-1] = logits[-1][..., :-1, :]
+            loss = chunked_cross_entropy(logits, labels[..., 1:])
         if rel is not None:
             loss = loss + 0.02 * mask_loss()
         loss.backward()
@@ -439,20 +463,28 @@ def run_native(args):
             dist.all_reduce(ms, op=dist.ReduceOp.MAX)
         return float(ms)
 
+    in_d = pk_d if packed_mode else idx_d
     for _ in range(max(args.warmup, 3)):
-        step(idx_d, labels_d)
+        step(in_d, labels_d)
     sampler = ClockSampler(local) if rank == 0 else None
     l0 = ops.launches()
-    ms_total = timed(lambda: step(idx_d, labels_d), args.steps)
+    ms_total = timed(lambda: step(in_d, labels_d), args.steps)
     n_launch = ops.launches() - l0
     clocks = sampler.stop() if sampler else None
-    tokens = world * B * T * args.steps
+    tok_t = torch.tensor([float(real_tokens)], device=dev)
+    if world > 1:
+        dist.all_reduce(tok_t)                      # every rank packs its own samples: sum the real token counts
+    tokens_per_step = float(tok_t)
+    tokens = tokens_per_step * args.steps
     value = tokens / (ms_total / 1e3)
 
     # ---- end to end: pinned host inputs -> H2D -> step -> loss read back on the host, every step ----
     losses = []
 
     def e2e_step():
+        if packed_mode:
+            losses.append(step({k: v.to(dev, non_blocking=True) for k, v in pk_h.items()}, None).item())
+            return
         i_d = idx_h.to(dev, non_blocking=True)
         l_d = labels_h.to(dev, non_blocking=True)
         losses.append(step(i_d, l_d).item())
@@ -467,14 +499,25 @@ def run_native(args):
             "config": {"workload": workload_name(args), "model": "TinyLlama-1.1B (random init)", "prompts_per_gpu": B, "seq_len": T,
                        "global_batch": world * B, "parallelism": f"dp{world}", "optimizer": "fused AdamW on the flat PEFT bucket",
                        "l2": "per-step working set (~9 GB of activations + 2.2 GB weights) >> 126 MB L2; no explicit flush",
-                       "loss": round(losses[-1], 4)},
-            "e2e": {"value": round(e2e_value, 1), "unit": UNIT, "h2d_bytes_per_step": 2 * B * T * 8, "d2h_bytes_per_step": 4,
+                       "loss": round(losses[-1], 4),
+                       "tokens_counted": ("REAL tokens only: the samples are packed into one row without the right pad of the reference's "
+                                          "collate_fn (cu_seqlens attention forward + backward)" if packed_mode else
+                                          "all B x T positions of the right-padded batch (pad tokens included, as the reference computes them)"),
+                       "tokens_per_step": round(tokens_per_step), "padded_positions_per_step": world * B * longest,
+                       "padded_equivalent_tokens_per_s": round(world * B * longest * args.steps / (ms_total / 1e3), 1)},
+            "e2e": {"value": round(e2e_value, 1), "unit": UNIT,
+                    "h2d_bytes_per_step": (sum(v.numel() * v.element_size() for v in pk_h.values()) if packed_mode else 2 * B * T * 8),
+                    "d2h_bytes_per_step": 4,
                     "ms_per_step": round(ms_e2e / args.steps, 3)},
             "gpu_launches": n_launch, "clocks": clocks}
     # the vocabulary projection only runs on rows with a target (valid-row compaction): credit only those flops
-    rho = float((labels_h[..., 1:] != -1).sum()) / float(B * T)
+    rho = float((labels_h[..., 1:] != -1).sum()) / float(real_tokens)
     line["config"]["lm_head_row_fraction"] = round(rho, 4)
-    step_fl = flops.step_flops(model.config, args.workload, B, T, training=True, rho=rho)
+    if packed_mode:        # per-token flops with each sequence's own causal length, summed over the real tokens of this rank
+        lens = (pk_h["cu_seqlens"][1:] - pk_h["cu_seqlens"][:-1]).tolist()
+        step_fl = sum(flops.step_flops(model.config, args.workload, 1, int(n), training=True, rho=rho) for n in lens)
+    else:
+        step_fl = flops.step_flops(model.config, args.workload, B, T, training=True, rho=rho)
     line["step_tflops_per_gpu"] = round(step_fl / (ms_total / args.steps / 1e3) / 1e12, 1)
 
     # ---- roofline of the dominant kernel: per-launch CUDA events in a dedicated instrumented pass ----
@@ -488,7 +531,7 @@ def run_native(args):
         peak_src = "measured sustained (MEASURED_PEAKS.json)" if peaks else "fallback 1.4 PF/s sustained"
         with ops.profile() as recs:
             for _ in range(2):
-                step(idx_d, labels_d, sync=False)
+                step(in_d, labels_d, sync=False)
             torch.cuda.synchronize()
         agg, total_ms = {}, 0.0
         for name, meta, e0, e1 in recs:

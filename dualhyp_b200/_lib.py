@@ -62,6 +62,7 @@ SIGNATURES = {
     "dh_attention_fwd_varlen": (_I, [_P, _P, _P, _P, _P, _P, _I, _I, _L, _I, _I, _I, _P]),
     "dh_attention_bwd_workspace": (_Z, [_I, _I, _I, _I]),
     "dh_attention_bwd": (_I, [_P, _P, _P, _P, _P, _P, _P, _P, _P, _I, _P, _P, _I, _I, _I, _I, _I, _P, _Z, _P]),
+    "dh_attention_bwd_varlen": (_I, [_P, _P, _P, _P, _P, _P, _P, _P, _P, _I, _P, _P, _P, _I, _I, _L, _I, _I, _I, _P, _Z, _P]),
     "dh_attention_decode": (_I, [_P, _P, _P, _P, _P, _P, _P, _I, _I, _I, _I, _I, _P]),
     "dh_prefix_project_fwd": (_I, [_P, _P, _P, _I, _I, _I, _I, _I, _P]),
     "dh_prefix_project_bwd": (_I, [_P, _P, _P, _I, _I, _I, _I, _I, _P]),

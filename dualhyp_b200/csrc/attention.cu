@@ -93,6 +93,16 @@ struct AttnParams {
   long long total_rows;
 };
 
+// index of (batch/sequence b, head h, position t inside the sequence) in the lse / delta statistics: [B, H, T] for padded batches,
+// [H, total_rows] (row = row_base + t) for packed variable-length sequences
+__device__ __forceinline__ long long stat_index(const AttnParams& p, int b, int h, int row_base, int t) {
+  return p.cu_seqlens ? (long long)h * p.total_rows + row_base + t : ((long long)b * p.H + h) * p.T + t;
+}
+// the same for a flat token row m of the whole batch
+__device__ __forceinline__ long long stat_index_flat(const AttnParams& p, int h, long long m) {
+  return p.cu_seqlens ? (long long)h * p.total_rows + m : ((long long)(m / p.T) * p.H + h) * p.T + (m % p.T);
+}
+
 __device__ __forceinline__ void load_prefix_to_smem(const AttnParams& p, int g, float* sak, float* sav) {
   const int n = p.prefix_len * HD;
   const long long koff = (long long)(g * (p.qpk + 2) + p.qpk) * HD;
@@ -493,8 +503,7 @@ __global__ void __launch_bounds__(FWD_THREADS, 2) attn_fwd_kernel(const __grid_c
           o4[i] = u;
         }
         if (hf == 0) {
-          const long long li = p.cu_seqlens ? (long long)h * p.total_rows + row_base + tq : ((long long)b * p.H + h) * p.T + tq;
-          p.lse[li] = (m_ref + log2f(l)) * LN2;
+          p.lse[stat_index(p, b, h, row_base, tq)] = (m_ref + log2f(l)) * LN2;
         }
       }
       TRC(8);
@@ -612,10 +621,13 @@ __global__ void __launch_bounds__(DKV_THREADS, 1) attn_bwd_dkv_kernel(const __gr
   const int warp = __shfl_sync(0xffffffffu, threadIdx.x >> 5, 0), lane = threadIdx.x & 31;   // shfl: the compiler sees a warp-uniform value
   TRC_DECL
   TRC(0);
-  const int nq = (p.T + ATT_BQ - 1) / ATT_BQ;
   const int g = blockIdx.y, b = blockIdx.z;
+  // one length per batch (rows b T .. b T + T), or packed sequences of their own lengths starting at cu_seqlens[b]
+  const int row_base = p.cu_seqlens ? __ldg(p.cu_seqlens + b) : b * p.T;
+  const int T_b = p.cu_seqlens ? __ldg(p.cu_seqlens + b + 1) - row_base : p.T;
+  const int nq = (T_b + ATT_BQ - 1) / ATT_BQ;
+  if ((int)blockIdx.x >= (nq + 1) / 2) return;      // the grid is sized for the longest sequence
   const int k_slot = g * (p.qpk + 2) + p.qpk, v_slot = k_slot + 1;
-  const int row_base = b * p.T;
   const int j_first = nq - 1 - (int)blockIdx.x, j_second = (int)blockIdx.x;
   const int n_items = (j_first == j_second) ? 1 : 2;
 
@@ -648,12 +660,12 @@ __global__ void __launch_bounds__(DKV_THREADS, 1) attn_bwd_dkv_kernel(const __gr
         for (int i = j; i < nq; ++i, ++n) {
           const int s = n % DKV_STAGES;
           // the statistics go to registers first (independent loads, in flight across the wait for the stage)
-          const long long sbase = ((long long)b * p.H + h) * p.T;
+          const long long sbase = stat_index(p, b, h, row_base, 0);
           float lv[4], dv[4];
 #pragma unroll
           for (int k = 0; k < 4; ++k) {
             const int tq = i * ATT_BQ + lane + 32 * k;
-            const bool ok = tq < p.T;
+            const bool ok = tq < T_b;      // rows beyond the sequence (the next sequence's, or zero fill) contribute nothing
             lv[k] = ok ? __ldg(p.lse + sbase + tq) * LOG2E : INFINITY;   // +inf => p = 0 for padded query rows
             dv[k] = ok ? __ldg(p.delta + sbase + tq) : 0.f;
           }
@@ -774,7 +786,7 @@ __global__ void __launch_bounds__(DKV_THREADS, 1) attn_bwd_dkv_kernel(const __gr
       while (nacc < npds) { mbar_wait(acc_done, nacc & 1); ++nacc; }
       tc_fence_after();
       const int tk = j * ATT_BK + r;
-      const bool valid = tk < p.T;
+      const bool valid = tk < T_b;
       bf16* rowp = p.dqkv + (long long)(row_base + (valid ? tk : 0)) * p.ld_qkv;
       uint32_t lo[8], hi[8];
       tmem_ld8(tdV + lane_off + 8 * qt, lo);
@@ -822,10 +834,12 @@ __global__ void __launch_bounds__(DQ_THREADS, 1) attn_bwd_dq_kernel(const __grid
   uint32_t* tmem_slot = reinterpret_cast<uint32_t*>(sp_full + 6);
 
   const int warp = __shfl_sync(0xffffffffu, threadIdx.x >> 5, 0), lane = threadIdx.x & 31;
-  const int nq = (p.T + ATT_BQ - 1) / ATT_BQ;
   const int g = blockIdx.y, b = blockIdx.z;
+  const int row_base = p.cu_seqlens ? __ldg(p.cu_seqlens + b) : b * p.T;
+  const int T_b = p.cu_seqlens ? __ldg(p.cu_seqlens + b + 1) - row_base : p.T;
+  const int nq = (T_b + ATT_BQ - 1) / ATT_BQ;
+  if ((int)blockIdx.x >= (nq + 1) / 2) return;      // the grid is sized for the longest sequence
   const int k_slot = g * (p.qpk + 2) + p.qpk, v_slot = k_slot + 1;
-  const int row_base = b * p.T;
   const int i_first = nq - 1 - (int)blockIdx.x, i_second = (int)blockIdx.x;
   const int n_items = (i_first == i_second) ? 1 : 2;
 
@@ -928,7 +942,7 @@ __global__ void __launch_bounds__(DQ_THREADS, 1) attn_bwd_dq_kernel(const __grid
       tmem_ld8(tdQ + 64 * (hcw & 1) + lane_off + 32 + 8 * qt, hi);
       tmem_wait_ld();
       tc_fence_before();
-      if (tq < p.T) {
+      if (tq < T_b) {
         bf16* row = p.dqkv + (long long)(row_base + tq) * p.ld_qkv + (g * (p.qpk + 2) + (h - g * p.qpk)) * HD;
         if (p.prefix_len > 0) {
           float a[8], c[8];
@@ -948,10 +962,10 @@ __global__ void __launch_bounds__(DQ_THREADS, 1) attn_bwd_dq_kernel(const __grid
     for (int item = 0; item < n_items; ++item) {
       const int i = item ? i_second : i_first;
       const int tq = i * ATT_BQ + r;
-      const bool valid = tq < p.T;
+      const bool valid = tq < T_b;
       for (int hh = 0; hh < p.qpk; ++hh, ++hc) {
         const int h = g * p.qpk + hh;
-        const long long stat_idx = ((long long)b * p.H + h) * p.T + (valid ? tq : 0);
+        const long long stat_idx = stat_index(p, b, h, row_base, valid ? tq : 0);
         const float lse2 = valid ? __ldg(p.lse + stat_idx) * LOG2E : INFINITY;    // +inf => p = 0 on padded rows
         const float delta = valid ? __ldg(p.delta + stat_idx) : 0.f;
         for (int j = 0; j <= i; ++j, ++n) {
@@ -1005,7 +1019,7 @@ __global__ void __launch_bounds__(DQ_THREADS, 1) attn_bwd_dq_kernel(const __grid
 //                                            accumulated in TMEM over all row tiles of the CTA, then atomics.
 // =================================================================================================
 __global__ void __launch_bounds__(256) attn_bwd_delta_kernel(const AttnParams p) {
-  const long long M = (long long)p.B * p.T;
+  const long long M = p.cu_seqlens ? p.total_rows : (long long)p.B * p.T;
   const int sub = threadIdx.x & 7;                      // 8 lanes x 16 bytes = one head of one row
   const long long pairs = M * p.H;
   for (long long pr = (long long)blockIdx.x * 32 + (threadIdx.x >> 3); pr < pairs; pr += (long long)gridDim.x * 32) {
@@ -1020,7 +1034,7 @@ __global__ void __launch_bounds__(256) attn_bwd_delta_kernel(const AttnParams p)
     acc += __shfl_xor_sync(0xffffffffu, acc, 1);
     acc += __shfl_xor_sync(0xffffffffu, acc, 2);
     acc += __shfl_xor_sync(0xffffffffu, acc, 4);
-    if (sub == 0) p.delta[((long long)(m / p.T) * p.H + h) * p.T + (m % p.T)] = acc;
+    if (sub == 0) p.delta[stat_index_flat(p, h, m)] = acc;
   }
 }
 
@@ -1048,7 +1062,7 @@ __global__ void __launch_bounds__(PFX_THREADS, 2) attn_bwd_prefix_kernel(const _
   const int h = blockIdx.y;
   const int g = h / p.qpk;
   const int q_slot = g * (p.qpk + 2) + (h % p.qpk), k_slot = g * (p.qpk + 2) + p.qpk, v_slot = k_slot + 1;
-  const long long M = (long long)p.B * p.T;
+  const long long M = p.cu_seqlens ? p.total_rows : (long long)p.B * p.T;      // row-wise: sequence boundaries do not matter here
   const int ntiles = (int)((M + 127) / 128);
   const int my_tiles = ((int)blockIdx.x < ntiles) ? (ntiles - 1 - (int)blockIdx.x) / (int)gridDim.x + 1 : 0;
 
@@ -1163,7 +1177,7 @@ __global__ void __launch_bounds__(PFX_THREADS, 2) attn_bwd_prefix_kernel(const _
 #pragma unroll
       for (int a = 0; a < MAX_PREFIX; ++a) { pa[a] *= inv; doay += pa[a] * __uint_as_float(dv[a]); }
       if (valid) {
-        p.delta[((long long)(m / p.T) * p.H + h) * p.T + (m % p.T)] = dot_out - gate * doay;
+        p.delta[stat_index_flat(p, h, m)] = dot_out - gate * doay;
         dgate_acc += doay;
       }
       // dS_a (scaled) and gP, bf16: A operand of dQ_a (TMEM) and B operand of the dAK / dAV accumulation (smem)
@@ -1736,17 +1750,18 @@ extern "C" size_t dh_attention_bwd_workspace(int B, int T, int n_groups, int q_p
   return (size_t)B * T * n_groups * q_per_kv * sizeof(float);   // delta
 }
 
-extern "C" int dh_attention_bwd(const void* qkv, const void* out, const void* dout, const float* lse, const void* prefix_kv,
-                                const float* gate, void* dqkv, float* d_prefix_kv, float* d_gate, int need_dqkv,
-                                const void* rope_cos, const void* rope_sin, int B, int T, int n_groups, int q_per_kv,
-                                int prefix_len, void* workspace, size_t workspace_bytes, void* stream) {
-  DH_CHECK(qkv && out && dout && lse && B > 0 && T > 0, "dh_attention_bwd: bad argument");
-  DH_CHECK(prefix_len >= 0 && prefix_len <= MAX_PREFIX, "dh_attention_bwd: prefix_len %d > %d", prefix_len, MAX_PREFIX);
-  DH_CHECK(workspace && workspace_bytes >= dh_attention_bwd_workspace(B, T, n_groups, q_per_kv), "dh_attention_bwd: workspace too small");
-  DH_CHECK(!need_dqkv || dqkv, "dh_attention_bwd: dqkv is NULL");
+// shared by the padded ([B, T]) and the packed (cu_seqlens) entry points: B = number of sequences, T = the longest one
+static int attention_bwd_impl(const void* qkv, const void* out, const void* dout, const float* lse, const void* prefix_kv,
+                              const float* gate, void* dqkv, float* d_prefix_kv, float* d_gate, int need_dqkv, const void* rope_cos,
+                              const void* rope_sin, const int32_t* cu_seqlens, long long total_rows, int B, int T, int n_groups,
+                              int q_per_kv, int prefix_len, void* workspace, size_t workspace_bytes, void* stream, const char* who) {
+  DH_CHECK(qkv && out && dout && lse && B > 0 && T > 0 && total_rows > 0, "%s: bad argument", who);
+  DH_CHECK(prefix_len >= 0 && prefix_len <= MAX_PREFIX, "%s: prefix_len %d > %d", who, prefix_len, MAX_PREFIX);
+  DH_CHECK(workspace && workspace_bytes >= (size_t)total_rows * n_groups * q_per_kv * sizeof(float), "%s: workspace too small", who);
+  DH_CHECK(!need_dqkv || dqkv, "%s: dqkv is NULL", who);
   const bool has_prefix = prefix_kv && prefix_len > 0;
-  DH_CHECK(!has_prefix || (gate && d_prefix_kv && d_gate), "dh_attention_bwd: prefix needs gate, d_prefix_kv, d_gate");
-  DH_CHECK((rope_cos == nullptr) == (rope_sin == nullptr), "dh_attention_bwd: pass both rope tables or neither");
+  DH_CHECK(!has_prefix || (gate && d_prefix_kv && d_gate), "%s: prefix needs gate, d_prefix_kv, d_gate", who);
+  DH_CHECK((rope_cos == nullptr) == (rope_sin == nullptr), "%s: pass both rope tables or neither", who);
   cudaStream_t s = (cudaStream_t)stream;
   AttnParams p = {};
   fill_common(p, B, T, n_groups, q_per_kv, has_prefix ? prefix_len : 0);
@@ -1755,7 +1770,8 @@ extern "C" int dh_attention_bwd(const void* qkv, const void* out, const void* do
   p.dqkv = (bf16*)dqkv; p.delta = (float*)workspace; p.d_prefix_kv = d_prefix_kv; p.d_gate = d_gate;
   p.need_dqkv = need_dqkv;
   p.rope_cos = (const bf16*)rope_cos; p.rope_sin = (const bf16*)rope_sin;
-  const long long M = (long long)B * T;
+  p.cu_seqlens = cu_seqlens; p.total_rows = total_rows;
+  const long long M = total_rows;
   if (!has_prefix) {
     const long long pairs = M * p.H;
     long long gx = (pairs + 31) / 32;
@@ -1796,6 +1812,25 @@ extern "C" int dh_attention_bwd(const void* qkv, const void* out, const void* do
   attn_bwd_dq_kernel<<<dim3((nq + 1) / 2, n_groups, B), DQ_THREADS, DQ_SMEM, s>>>(tmQKV, tmDO, p);
   DH_CUDA(cudaGetLastError());
   return 0;
+}
+
+extern "C" int dh_attention_bwd(const void* qkv, const void* out, const void* dout, const float* lse, const void* prefix_kv,
+                                const float* gate, void* dqkv, float* d_prefix_kv, float* d_gate, int need_dqkv,
+                                const void* rope_cos, const void* rope_sin, int B, int T, int n_groups, int q_per_kv,
+                                int prefix_len, void* workspace, size_t workspace_bytes, void* stream) {
+  return attention_bwd_impl(qkv, out, dout, lse, prefix_kv, gate, dqkv, d_prefix_kv, d_gate, need_dqkv, rope_cos, rope_sin, nullptr,
+                            (long long)B * T, B, T, n_groups, q_per_kv, prefix_len, workspace, workspace_bytes, stream, "dh_attention_bwd");
+}
+
+extern "C" int dh_attention_bwd_varlen(const void* qkv, const void* out, const void* dout, const float* lse, const void* prefix_kv,
+                                       const float* gate, void* dqkv, float* d_prefix_kv, float* d_gate, int need_dqkv,
+                                       const void* rope_cos, const void* rope_sin, const int32_t* cu_seqlens, int n_seq, int max_len,
+                                       long long total_rows, int n_groups, int q_per_kv, int prefix_len, void* workspace,
+                                       size_t workspace_bytes, void* stream) {
+  DH_CHECK(cu_seqlens && n_seq > 0 && max_len > 0, "dh_attention_bwd_varlen: bad argument");
+  return attention_bwd_impl(qkv, out, dout, lse, prefix_kv, gate, dqkv, d_prefix_kv, d_gate, need_dqkv, rope_cos, rope_sin, cu_seqlens,
+                            total_rows, n_seq, max_len, n_groups, q_per_kv, prefix_len, workspace, workspace_bytes, stream,
+                            "dh_attention_bwd_varlen");
 }
 
 extern "C" int dh_attention_decode(const void* qkv, const void* cache_k, const void* cache_v, const int32_t* lens, void* out,

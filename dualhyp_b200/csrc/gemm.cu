@@ -1222,8 +1222,12 @@ extern "C" int dh_gemm(const dh_gemm_args* args, void* stream_) {
   local.b_layout &= ~DH_B_FROZEN;
   const dh_gemm_args* a = &local;
   DH_CHECK(a->M > 0 && a->N > 0 && a->K1 > 0, "dh_gemm: bad shape M=%d N=%d K1=%d", a->M, a->N, a->K1);
-  DH_CHECK(a->N % 64 == 0 && a->K1 % 8 == 0 && a->K2 % 8 == 0, "dh_gemm: N %% 64, K1 %% 8, K2 %% 8 must be 0 (N=%d K1=%d K2=%d)",
-           a->N, a->K1, a->K2);
+  // K is the row pitch of a K-major operand (16-byte aligned rows => K % 8); for MN-major operands (the wgrad forms, K = the token
+  // count of a packed batch) K only counts rows and may be anything: TMA zero-fills the rows of the last k-block
+  const bool k1_pitch = a->a_layout == 0 || a->b_layout == 0;
+  const bool k2_pitch = a->K2 > 0 && (a->a2_layout == 0 || a->b2_layout == 0);
+  DH_CHECK(a->N % 64 == 0 && (!k1_pitch || a->K1 % 8 == 0) && (!k2_pitch || a->K2 % 8 == 0),
+           "dh_gemm: N %% 64 must be 0, and K %% 8 for K-major operands (N=%d K1=%d K2=%d)", a->N, a->K1, a->K2);
   DH_CHECK(a->A && a->B && (a->out || a->epilogue == DH_EPI_SWIGLU), "dh_gemm: null operand");
   DH_CHECK((a->lda % 8) == 0 && (a->ldb % 8) == 0, "dh_gemm: leading dimensions must be multiples of 8 elements");
   DH_CHECK(((uintptr_t)a->A & 15) == 0 && ((uintptr_t)a->B & 15) == 0, "dh_gemm: operands must be 16-byte aligned");

@@ -217,7 +217,8 @@ class DecoderEngine:
         key = ("cap", name, dtype)
         t = self._bufs.get(key)
         if t is None or t.numel() < numel:
-            cap = ((numel + (1 << 22) - 1) >> 22) << 22          # 4 Mi-element granules
+            g = 22 if numel >= (1 << 20) else 12                 # 4 Mi-element granules (4 Ki for the small per-row vectors)
+            cap = ((numel + (1 << g) - 1) >> g) << g
             t = self._bufs[key] = torch.empty(cap, device=self.device, dtype=dtype)
         return t[:numel].view(shape)
 
@@ -231,12 +232,13 @@ class DecoderEngine:
     def forward_hidden(self, idx: Tensor, packed: Dict[int, Dict[str, Tensor]], save: bool, write_cache: bool = False,
                        varlen: Optional[Dict] = None) -> Tensor:
         """idx int64 [B, T] -> ln_f output bf16 [B*T, C].  save=True keeps what backward() needs.
-        varlen (inference only): idx is ONE row of packed sequences [1, M] without pad tokens; `varlen` holds cu_seqlens
-        int32 [n + 1], positions int32 [M] (RoPE position of every row inside its sequence), seq_ids int32 [M] and max_len."""
+        varlen: idx is ONE row of packed sequences [1, M] without pad tokens; `varlen` holds cu_seqlens int32 [n + 1], positions
+        int32 [M] (RoPE position of every row inside its sequence), max_len, and for the cache-writing prefill seq_ids int32 [M].
+        Training over packed rows (save=True) keeps the same activations; only the attention kernels see sequence boundaries."""
         s = self.spec
         B, T = idx.shape
         if varlen is not None:
-            assert not save and B == 1, "packed variable-length batches are a forward-only (prefill) path"
+            assert B == 1, "a packed variable-length batch is ONE row of concatenated sequences"
             assert varlen["max_len"] <= s.block_size
         else:
             assert T <= s.block_size, f"Cannot forward sequence of length {T}, block size is only {s.block_size}"
@@ -246,13 +248,13 @@ class DecoderEngine:
         bf, f32 = torch.bfloat16, torch.float32
         idx = idx.contiguous()
         per = (lambda name, i: f"{name}{i}") if save else (lambda name, i: name)
-        _buf = self._buf if save else self._cap_buf          # training: exact shapes kept per layer; inference: grow-only
+        _buf = self._cap_buf          # grow-only flat buffers viewed at the step's row count (packed batches change it every step)
         # the residual stream alternates between two buffers unless the backward needs every stage
         x = _buf(per("x", 0), (M, C), f32)
         ops.embedding_fwd(idx.view(-1), self.wte, x)
         n = _buf("n", (M, C), bf)
         act = _buf("act", (M, I), bf)
-        saved = dict(B=B, T=T, layers=[], packed=packed) if save else None
+        saved = dict(B=B, T=T, layers=[], packed=packed, varlen=varlen) if save else None
         pkv_all = self._project_prefixes(packed, "pkv_all")
         for i, lw in enumerate(self.layers):
             pk = packed.get(i, {})
@@ -345,7 +347,7 @@ class DecoderEngine:
         """bf16 logits [M, V] = adapter_scale * (hidden W^T + adapter_bias)  (ger/lora.py:70-71).  m_limit (device int32):
         only the first *m_limit rows are needed (valid-row compaction of the fused loss)."""
         M = hidden.shape[0]
-        logits = out if out is not None else self._buf("logits", (M, self.spec.vocab), torch.bfloat16)
+        logits = out if out is not None else self._cap_buf("logits", (M, self.spec.vocab), torch.bfloat16)
         ops.gemm(hidden, self.lm_w, logits, col_scale=self.lm_scale, col_bias=self.lm_bias, m_limit=m_limit, b_frozen=True)
         return logits
 
@@ -355,7 +357,7 @@ class DecoderEngine:
     def lm_head_backward(self, dlogits: Tensor, m_limit: Optional[Tensor] = None, name: str = "d_hidden") -> Tensor:
         """d(hidden) bf16 [M, C] = dlogits [M, V] @ W [V, C]   (W^T [C, V] is the K-major B operand)."""
         M = dlogits.shape[0]
-        d_hidden = self._buf(name, (M, self.spec.n_embd), torch.bfloat16)
+        d_hidden = self._cap_buf(name, (M, self.spec.n_embd), torch.bfloat16)
         if self.lm_scale is not None:
             raise NotImplementedError("training through a non-trivial adapter_scale is not supported (it is frozen at 1)")
         ops.gemm(dlogits, self.lm_w_t, d_hidden, m_limit=m_limit)
@@ -369,6 +371,7 @@ class DecoderEngine:
         if step_id is not None and step_id != sv["step_id"]:
             raise RuntimeError("the engine's saved activations belong to a later forward; call backward before the next forward")
         B, T = sv["B"], sv["T"]
+        vl = sv.get("varlen")          # packed sequences: B = 1, T = total rows
         M, C, I, G, qpk = B * T, s.n_embd, s.intermediate_size, s.n_query_groups, s.qpk
         bf, f32 = torch.bfloat16, torch.float32
         packed = sv["packed"]
@@ -376,14 +379,14 @@ class DecoderEngine:
         first = s.first_trainable_layer
         if first >= s.n_layer:
             return grads
-        dx = self._buf("dx", (M, C), f32)
-        dxb = self._buf("dxb", (M, C), bf)
+        dx = self._cap_buf("dx", (M, C), f32)
+        dxb = self._cap_buf("dxb", (M, C), bf)
         ops.rmsnorm_bwd(sv["x_final"], self.ln_f, sv["rstd_f"], d_hidden.contiguous(), None, dx, dxb)
-        dh12 = self._buf("dh12", (M, 2 * I), bf)
-        dn = self._buf("dn", (M, C), bf)
-        dy = self._buf("dy", (M, C), bf)
-        dqkv = self._buf("dqkv", (M, s.qkv_out), bf)
-        ws = self._buf("attn_ws", (ops.attention_bwd_workspace(B, T, G, qpk),), torch.uint8)
+        dh12 = self._cap_buf("dh12", (M, 2 * I), bf)
+        dn = self._cap_buf("dn", (M, C), bf)
+        dy = self._cap_buf("dy", (M, C), bf)
+        dqkv = self._cap_buf("dqkv", (M, s.qkv_out), bf)
+        ws = self._cap_buf("attn_ws", (ops.attention_bwd_workspace(B, T, G, qpk),), torch.uint8)
         scaling = (s.alpha / s.r) if s.r > 0 else 0.0
         d_pkv_all = d_gate_all = None
         if s.variant == "adapter":
@@ -399,7 +402,7 @@ class DecoderEngine:
             ops.rmsnorm_bwd(a["xmid"], lw["norm2"], a["rstd2"], dn, dx, dx, dxb)
             # ---- attention output projection ----
             if "proj_a" in pk:
-                dap = self._buf("dap", (M, LORA_PAD), bf)
+                dap = self._cap_buf("dap", (M, LORA_PAD), bf)
                 ops.gemm(dxb, pk["proj_b_t"], dap)
                 db = self._wgrad(dxb, a["ap_s"], C, LORA_PAD)
                 da = self._wgrad(dap, a["y"], LORA_PAD, C, alpha=scaling)
@@ -413,16 +416,20 @@ class DecoderEngine:
             d_pkv = d_gate = None
             if a["prefix_kv"] is not None:
                 d_pkv, d_gate = d_pkv_all[i - s.adapter_start_layer], d_gate_all[i - s.adapter_start_layer]
-            ops.attention_bwd(a["qkv"], a["y"], dy, a["lse"], dqkv if need_dqkv else None, ws, B, T, G, qpk, a["prefix_kv"], a["gate"],
-                              d_pkv, d_gate, s.adapter_prompt_length if a["prefix_kv"] is not None else 0, need_dqkv,
-                              rope_cos=self.cos, rope_sin=self.sin)
+            plen = s.adapter_prompt_length if a["prefix_kv"] is not None else 0
+            if vl is not None:
+                ops.attention_bwd_varlen(a["qkv"], a["y"], dy, a["lse"], dqkv if need_dqkv else None, ws, vl["cu_seqlens"], vl["max_len"],
+                                         G, qpk, a["prefix_kv"], a["gate"], d_pkv, d_gate, plen, need_dqkv, rope_cos=self.cos, rope_sin=self.sin)
+            else:
+                ops.attention_bwd(a["qkv"], a["y"], dy, a["lse"], dqkv if need_dqkv else None, ws, B, T, G, qpk, a["prefix_kv"], a["gate"],
+                                  d_pkv, d_gate, plen, need_dqkv, rope_cos=self.cos, rope_sin=self.sin)
             if d_pkv is not None:
                 grads[p + "gating_factor"] = d_gate.view(1, 1, s.n_head, 1)
             if not need_dqkv:
                 continue
             # ---- QKV projection ----
             if "qkv_a" in pk:
-                da_s = self._buf("da_s", (M, LORA_PAD), bf)
+                da_s = self._cap_buf("da_s", (M, LORA_PAD), bf)
                 ops.gemm(dqkv, pk["qkv_b_t"], da_s)
                 db = self._wgrad(dqkv, a["a_s"], s.qkv_out, LORA_PAD)
                 da = self._wgrad(da_s, a["n1"], LORA_PAD, C, alpha=scaling)

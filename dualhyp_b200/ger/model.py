@@ -31,19 +31,36 @@ class _DecoderFn(torch.autograd.Function):
     """idx -> ln_f hidden [B, T, C] bf16; differentiable w.r.t. the trainable PEFT tensors only."""
 
     @staticmethod
-    def forward(ctx, model: "GPT", idx: Tensor, names: Tuple[str, ...], *trainables: Tensor):
+    def forward(ctx, model: "GPT", idx: Tensor, varlen: Optional[Dict], names: Tuple[str, ...], *trainables: Tensor):
         eng = model._engine_ready()
         packed = eng.pack_trainable(dict(zip(names, trainables)))
-        hidden = eng.forward_hidden(idx, packed, save=True)
-        ctx.model, ctx.names, ctx.step_id = model, names, eng.step_id
+        ctx.model, ctx.names, ctx.unpad = model, names, None
         B, T = idx.shape
+        if varlen is not None and "row_map" in varlen:
+            # a right-padded [B, T] batch executed without its pad rows (GPT.skip_pad): gather the real tokens into one packed
+            # row, run the decoder over it, scatter the hidden states back to [B, T] (pad rows = 0; they carry no loss)
+            rows, count = varlen["row_map"], varlen["count"]
+            ids = idx.reshape(-1).index_select(0, varlen["row_map_long"]).view(1, -1)
+            hidden_p = eng.forward_hidden(ids, packed, save=True, varlen=varlen)
+            hidden = eng._cap_buf("hidden_unpacked", (B * T, hidden_p.shape[1]), torch.bfloat16)
+            ops.scatter_rows(hidden_p, rows, count, hidden)
+            ctx.unpad = (rows, count, hidden_p.shape[0])
+        else:
+            hidden = eng.forward_hidden(idx, packed, save=True, varlen=varlen)
+        ctx.step_id = eng.step_id
         return hidden.view(B, T, -1)
 
     @staticmethod
     def backward(ctx, d_hidden: Tensor):
         model = ctx.model
         eng = model._engine
-        grads = eng.backward(d_hidden.reshape(-1, d_hidden.shape[-1]).to(torch.bfloat16), ctx.step_id)
+        d2 = d_hidden.reshape(-1, d_hidden.shape[-1]).to(torch.bfloat16).contiguous()
+        if ctx.unpad is not None:
+            rows, count, Mp = ctx.unpad
+            d2p = eng._cap_buf("d_hidden_packed", (Mp, d2.shape[1]), torch.bfloat16)
+            ops.gather_rows(d2, rows, count, d2p)
+            d2 = d2p
+        grads = eng.backward(d2, ctx.step_id)
         scale = model._pending_grad_scale
         model._pending_grad_scale = None
         if scale is not None:
@@ -54,7 +71,7 @@ class _DecoderFn(torch.autograd.Function):
                 b = g._base if g._base is not None else g
                 bases[id(b)] = b
             torch._foreach_mul_(list(bases.values()), scale)
-        return (None, None, None, *[grads.get(n) for n in ctx.names])
+        return (None, None, None, None, *[grads.get(n) for n in ctx.names])
 
 
 class _LMHeadFn(torch.autograd.Function):
@@ -93,13 +110,13 @@ class _LMHeadCEFn(torch.autograd.Function):
         # they go through the vocabulary projection: ordered compaction on the device, GEMMs bounded by the device-side
         # count -- the host never learns it, there is no sync.
         count = eng._buf("ce_count", (1,), torch.int32)
-        rows = eng._buf("ce_row_idx", (M,), torch.int32)
-        tg_c = eng._buf("ce_targets_c", (M,), torch.int64)
-        h_c = eng._buf("ce_hidden_c", (M, C), torch.bfloat16)
+        rows = eng._cap_buf("ce_row_idx", (M,), torch.int32)
+        tg_c = eng._cap_buf("ce_targets_c", (M,), torch.int64)
+        h_c = eng._cap_buf("ce_hidden_c", (M, C), torch.bfloat16)
         ops.compact_targets(tg, count, rows, tg_c)
         ops.gather_rows(h2, rows, count, h_c)
         logits = eng.lm_head(h_c, m_limit=count)
-        row = eng._buf("ce_rows", (M,), torch.float32)
+        row = eng._cap_buf("ce_rows", (M,), torch.float32)
         out2 = torch.empty(2, device=h2.device, dtype=torch.float32)
         ops.cross_entropy(logits, tg_c, row, (1.0 / denom) if denom > 0 else 1.0, 2 if need_grad else 0)
         ops.loss_reduce(row, tg_c, out2)
@@ -115,7 +132,7 @@ class _LMHeadCEFn(torch.autograd.Function):
         eng = model._engine
         rows, count = ctx.compact
         d_hidden_c = eng.lm_head_backward(ctx.logits, m_limit=count, name="d_hidden_c")
-        d_hidden = eng._buf("d_hidden", tuple(d_hidden_c.shape), torch.bfloat16)
+        d_hidden = eng._cap_buf("d_hidden", tuple(d_hidden_c.shape), torch.bfloat16)
         ops.scatter_rows(d_hidden_c, rows, count, d_hidden)
         (out2,) = ctx.saved_tensors
         scale = d_loss.float() if ctx.denom > 0 else d_loss.float() / out2[1]
@@ -129,8 +146,10 @@ class LazyLogits:
     dims stays lazy (`logits[-1][..., :-1, :]`, `logits[0, -1]`); anything else materialises through the
     lm_head GEMM.  `ger.utils.chunked_cross_entropy` consumes these without ever building [B, T, V]."""
 
-    def __init__(self, model: "GPT", hidden: Tensor, base: Optional[Tensor] = None, t0: int = 0, t1: Optional[int] = None):
+    def __init__(self, model: "GPT", hidden: Tensor, base: Optional[Tensor] = None, t0: int = 0, t1: Optional[int] = None,
+                 packed_meta: Optional[Tuple[int, int]] = None):
         self.model, self.hidden = model, hidden
+        self.packed_meta = packed_meta          # (n sequences, longest) of a packed batch: the loss denominator follows it
         self.base = base if base is not None else (hidden if hidden.dim() == 3 else None)   # [B, T, C] it was cut from
         self.t0 = t0
         self.t1 = t1 if t1 is not None else (hidden.shape[1] if hidden.dim() == 3 else None)
@@ -170,8 +189,8 @@ class LazyLogits:
             if (self.base is not None and nd == 3 and lead[0] == slice(None) and isinstance(lead[1], slice)
                     and lead[1].step in (None, 1)):
                 a, b, _ = lead[1].indices(self.t1 - self.t0)
-                return LazyLogits(self.model, self.hidden[:, a:b], self.base, self.t0 + a, self.t0 + b)
-            return LazyLogits(self.model, self.hidden[lead], None)
+                return LazyLogits(self.model, self.hidden[:, a:b], self.base, self.t0 + a, self.t0 + b, packed_meta=self.packed_meta)
+            return LazyLogits(self.model, self.hidden[lead], None, packed_meta=self.packed_meta)
         return self.materialize()[item]
 
     def materialize(self) -> Tensor:
@@ -235,6 +254,9 @@ class GPT(nn.Module):
         self._frozen_sig = None
         self._pending_grad_scale: Optional[Tensor] = None
         self._cache_batch = 0
+        # opt-in: run right-padded [B, T] batches without their pad rows (packed cu_seqlens attention); logits at pad
+        # positions are then those of a zero hidden state instead of the reference's (ignored, label -1) values
+        self.skip_pad = False
 
     def _engine_spec(self) -> EngineSpec:
         c = self.config
@@ -291,14 +313,62 @@ class GPT(nn.Module):
         return tuple(names), tuple(tensors)
 
     # -- forward ---------------------------------------------------------------------------------
-    def _hidden(self, idx: Tensor) -> Tensor:
+    def _hidden(self, idx: Tensor, varlen: Optional[Dict] = None) -> Tensor:
         names, tensors = self._trainables()
+        if varlen is None and self.skip_pad and idx.size(0) > 1:
+            varlen = self._pad_free_layout(idx)
         if torch.is_grad_enabled() and any(t.requires_grad for t in tensors):
-            return _DecoderFn.apply(self, idx, names, *tensors)
+            return _DecoderFn.apply(self, idx, varlen, names, *tensors)
         eng = self._engine_ready()
         packed = eng.pack_trainable(dict(zip(names, tensors)))
         B, T = idx.shape
-        return eng.forward_hidden(idx, packed, save=False).view(B, T, -1)
+        if varlen is not None and "row_map" in varlen:
+            ids = idx.reshape(-1).index_select(0, varlen["row_map_long"]).view(1, -1)
+            hidden_p = eng.forward_hidden(ids, packed, save=False, varlen=varlen)
+            hidden = eng._cap_buf("hidden_unpacked", (B * T, hidden_p.shape[1]), torch.bfloat16)
+            ops.scatter_rows(hidden_p, varlen["row_map"], varlen["count"], hidden)
+            return hidden.view(B, T, -1)
+        return eng.forward_hidden(idx, packed, save=False, varlen=varlen).view(B, T, -1)
+
+    def _pad_free_layout(self, idx: Tensor, lengths: Optional[Tensor] = None) -> Optional[Dict]:
+        """Layout of a right-padded [B, T] batch without its pad rows.  The reference's collate pads ids with 0
+        (data/av_dataset.py:260-292) and every sample ends with the eos id, so the length of a row is the position of its last
+        non-zero id + 1 (one small device -> host read per batch, unless the caller supplies `lengths`)."""
+        B, T = idx.shape
+        if lengths is None:
+            pos = torch.arange(1, T + 1, device=idx.device, dtype=torch.int32)
+            lengths = ((idx != 0).to(torch.int32) * pos).amax(dim=1).clamp_(min=1).cpu()
+        lens = [int(x) for x in lengths.tolist()]
+        if sum(lens) == B * T:
+            return None
+        dev = idx.device
+        cu = torch.zeros(B + 1, dtype=torch.int32)
+        cu[1:] = torch.tensor(lens, dtype=torch.int32).cumsum(0)
+        Mp = int(cu[-1])
+        positions = torch.cat([torch.arange(n, dtype=torch.int32) for n in lens])
+        row_map = torch.cat([torch.arange(b * T, b * T + n, dtype=torch.int32) for b, n in enumerate(lens)])
+        meta = torch.cat((cu, positions, row_map, torch.tensor([Mp], dtype=torch.int32)))
+        meta = meta.pin_memory().to(dev, non_blocking=True) if dev.type == "cuda" else meta
+        cu_d, pos_d, map_d, cnt_d = meta[:B + 1], meta[B + 1:B + 1 + Mp], meta[B + 1 + Mp:B + 1 + 2 * Mp], meta[B + 1 + 2 * Mp:]
+        return dict(cu_seqlens=cu_d, positions=pos_d, max_len=max(lens), n_seq=B, row_map=map_d, row_map_long=map_d.long(), count=cnt_d)
+
+    def forward_packed(self, input_ids: Tensor, cu_seqlens: Tensor, positions: Tensor, max_len: int, lm_head_chunk_size: int = 0):
+        """Causal forward over sequences packed into ONE row without pad tokens (`dualhyp_b200.collate.pack_varlen`; SURVEY 8f
+        row 2): input_ids int64 [M], cu_seqlens int32 [n + 1], positions int32 [M] (position of every token inside its
+        sequence), max_len = the longest sequence.  Returns logits [1, M, V] (or the chunk list) like `forward`; for training,
+        `chunked_cross_entropy(logits, batch["targets"])` keeps the reference's train reduction: the sum over valid targets
+        divided by n * (max_len - 1), the number of positions of the right-padded batch the reference would have built
+        (ger/utils.py:442-448, quirk Q2)."""
+        n = cu_seqlens.numel() - 1
+        assert input_ids.dim() == 1 and positions.numel() == input_ids.numel() and max_len <= self.config.block_size
+        varlen = dict(cu_seqlens=cu_seqlens.to(torch.int32), positions=positions.to(torch.int32), max_len=int(max_len), n_seq=n)
+        hidden = self._hidden(input_ids.view(1, -1), varlen)
+        meta = (n, int(max_len))
+        M = input_ids.numel()
+        if lm_head_chunk_size > 0:
+            return [LazyLogits(self, hidden[:, a:a + lm_head_chunk_size], hidden, a, min(M, a + lm_head_chunk_size), packed_meta=meta)
+                    for a in range(0, M, lm_head_chunk_size)]
+        return LazyLogits(self, hidden, packed_meta=meta)
 
     def _forward_impl(self, idx: Tensor, input_pos: Optional[Tensor], lm_head_chunk_size: int):
         T = idx.size(1)

@@ -70,6 +70,13 @@ def chunked_cross_entropy(logits, targets: Tensor, chunk_size: int = 128) -> Ten
         same_base = all(l.base is not None and l.base is logits[0].base for l in logits)
         contiguous_cover = same_base and all(logits[i].t1 == logits[i + 1].t0 for i in range(len(logits) - 1))
         n_pos = sum(int(l.shape[0]) * int(l.shape[1]) if l.dim() == 3 else int(l.shape[0]) for l in logits)
+        if logits[0].packed_meta is not None:
+            # packed batch (GPT.forward_packed): the reference would have right-padded these n sequences to the longest and
+            # averaged over ALL n * (T - 1) shifted positions (quirk Q2); the targets are already shifted per sequence
+            n_seq, longest = logits[0].packed_meta
+            n_pos = n_seq * (longest - 1)
+        if contiguous_cover and targets.dim() == 1 and logits[0].base.shape[0] == 1:
+            targets = targets.unsqueeze(0)                  # packed batch: one row of concatenated sequences
         if contiguous_cover and targets.dim() == 2:
             base = logits[0].base
             Bsz, T, _ = base.shape

@@ -285,6 +285,27 @@ def attention_bwd(qkv: Tensor, out: Tensor, dout: Tensor, lse: Tensor, dqkv: Opt
     _count(3 if need_dqkv else 1)
 
 
+@_profiled("attention_bwd")
+def attention_bwd_varlen(qkv: Tensor, out: Tensor, dout: Tensor, lse: Tensor, dqkv: Optional[Tensor], workspace: Tensor,
+                         cu_seqlens: Tensor, max_len: int, n_groups: int, q_per_kv: int, prefix_kv: Optional[Tensor] = None,
+                         gate: Optional[Tensor] = None, d_prefix_kv: Optional[Tensor] = None, d_gate: Optional[Tensor] = None,
+                         prefix_len: int = 0, need_dqkv: bool = True, rope_cos: Optional[Tensor] = None,
+                         rope_sin: Optional[Tensor] = None) -> None:
+    """Backward of `attention_fwd_varlen`: rows [cu_seqlens[b], cu_seqlens[b + 1]) of qkv / out / dout / dqkv are sequence b."""
+    _dev(qkv)
+    M = qkv.shape[0]
+    assert qkv.is_contiguous() and out.is_contiguous() and dout.is_contiguous() and dout.dtype == torch.bfloat16
+    assert cu_seqlens.dtype == torch.int32 and cu_seqlens.is_cuda and lse.numel() >= n_groups * q_per_kv * M
+    if d_prefix_kv is not None:
+        assert d_prefix_kv.dtype == torch.float32 and d_prefix_kv.is_contiguous() and d_gate.dtype == torch.float32
+    check(_lib.load().dh_attention_bwd_varlen(qkv.data_ptr(), out.data_ptr(), dout.data_ptr(), lse.data_ptr(), _ptr(prefix_kv), _ptr(gate),
+                                              _ptr(dqkv), _ptr(d_prefix_kv), _ptr(d_gate), int(need_dqkv), _ptr(rope_cos), _ptr(rope_sin),
+                                              cu_seqlens.data_ptr(), cu_seqlens.numel() - 1, max_len, M, n_groups, q_per_kv, prefix_len,
+                                              workspace.data_ptr(), workspace.numel() * workspace.element_size(), _stream()),
+          "dh_attention_bwd_varlen")
+    _count(3 if need_dqkv else 1)
+
+
 @_profiled("attention_decode")
 def attention_decode(qkv: Tensor, cache_k: Tensor, cache_v: Tensor, lens: Tensor, out: Tensor, n_groups: int, q_per_kv: int,
                      prefix_kv: Optional[Tensor] = None, gate: Optional[Tensor] = None, prefix_len: int = 0) -> None:

@@ -22,7 +22,7 @@
 extern "C" {
 #endif
 
-#define DH_ABI_VERSION 2
+#define DH_ABI_VERSION 3
 
 int dh_abi_version(void);
 const char* dh_last_error(void);
@@ -40,8 +40,9 @@ int dh_sm_count(void);
  * requests its first ring of weight tiles before waiting for the previous kernel (programmatic dependent launch, DH_PDL=2),
  * so the weight stream of one GEMM overlaps the tail of the kernel before it.  Never set it for an operand produced on the stream.
  * The second source pair folds a LoRA low-rank delta into the same accumulator (K extension).
- * Constraints: N % 64 == 0, K1 % 8 == 0, K2 % 8 == 0, 16-byte aligned rows.  M is arbitrary and K may be ragged (tails
- * are zero-filled by TMA on load; tail rows are masked on store).
+ * Constraints: N % 64 == 0, 16-byte aligned rows (so K % 8 == 0 for a K-major operand and M % 8 / N % 8 for an MN-major one).
+ * M is arbitrary and K may be ragged (tails are zero-filled by TMA on load; tail rows are masked on store); with both operands
+ * MN-major (the wgrad form, K = token count of a packed batch) K is arbitrary.
  * ------------------------------------------------------------------------------------------------- */
 #define DH_B_FROZEN 0x100
 
@@ -153,6 +154,15 @@ int dh_attention_bwd(const void* qkv, const void* out, const void* dout, const f
                      const float* gate, void* dqkv, float* d_prefix_kv, float* d_gate, int need_dqkv,
                      const void* rope_cos, const void* rope_sin, int B, int T, int n_groups, int q_per_kv, int prefix_len,
                      void* workspace, size_t workspace_bytes, void* stream);
+/* The same backward over PACKED variable-length sequences (training on DualHyp prompts of 330-480 tokens without the right
+ * pad of data/av_dataset.py:258-292): sequence b = rows [cu_seqlens[b], cu_seqlens[b+1]) of qkv, out, dout and
+ * dqkv (total_rows rows), causal inside each sequence; lse as written by dh_attention_fwd_varlen (f32 [n_head, total_rows]);
+ * RoPE positions restart per sequence; workspace >= total_rows * n_head * 4 bytes.  ABI v3. */
+int dh_attention_bwd_varlen(const void* qkv, const void* out, const void* dout, const float* lse, const void* prefix_kv,
+                            const float* gate, void* dqkv, float* d_prefix_kv, float* d_gate, int need_dqkv,
+                            const void* rope_cos, const void* rope_sin, const int32_t* cu_seqlens, int n_seq, int max_len,
+                            long long total_rows, int n_groups, int q_per_kv, int prefix_len, void* workspace,
+                            size_t workspace_bytes, void* stream);
 /* Adapter prefix K/V for ALL adapter layers in one launch (ger/adapter.py:129-137, `self.attn(prefix)` of which only the k
  * and v slots are used).  prefix bf16 [L, aT, C]; wkv bf16 [L, n_groups*128, C] = the k rows (64) then the v rows (64) of
  * every group of each layer's QKV weight; prefix_kv bf16 [L, aT, n_groups*(qpk+2)*64]: only the k and v slots are written.

@@ -25,7 +25,7 @@ def test_library_exports_every_declared_symbol():
     for n in names:
         assert hasattr(lib, n), f"{n} declared in include/dualhyp.h but not exported by libdualhyp.so"
     assert sorted(_lib.SIGNATURES) == names, "ctypes binding and header disagree on the entry-point list"
-    assert _lib.load().dh_abi_version() == 2
+    assert _lib.load().dh_abi_version() == 3
 
 
 def test_gemm_args_struct_matches_header_layout():

@@ -58,7 +58,7 @@ def test_gemm_b_mn_major(M, N, K):
     assert rel(out, ref) < 4e-3, report("gemm b_mn", out, ref)
 
 
-@pytest.mark.parametrize("M,N,K", [(128, 64, 64), (64, 256, 1024), (24, 2048, 4096)])
+@pytest.mark.parametrize("M,N,K", [(128, 64, 64), (64, 256, 1024), (24, 2048, 4096), (64, 256, 571)])
 def test_gemm_wgrad_form(M, N, K):
     """wgrad form: D[M,N] = A^T B with A stored [K, M], B stored [K, N]; fp32 output, accumulate."""
     A, B = rnd((K, M), 5), rnd((K, N), 6)
@@ -69,7 +69,7 @@ def test_gemm_wgrad_form(M, N, K):
     assert rel(out, ref) < 1e-4, report("gemm wgrad", out, ref)
 
 
-@pytest.mark.parametrize("M,N,K,S", [(64, 2048, 8192, 4), (2560, 64, 8192, 7), (64, 256, 1000, 3), (304, 128, 4096, 16)])
+@pytest.mark.parametrize("M,N,K,S", [(64, 2048, 8192, 4), (2560, 64, 8192, 7), (64, 256, 1000, 3), (304, 128, 4096, 16), (64, 2048, 6659, 8)])
 def test_gemm_wgrad_split_k(M, N, K, S):
     """LoRA factor gradients: out[M, N] = A^T B with A [K, M], B [K, N] (K = tokens).  split_k leaves S fp32 slices whose
     sum is the product (ragged K ranges included); the slices are deterministic."""
@@ -562,6 +562,50 @@ def test_attention_fwd_varlen_equals_per_sequence(lens, G, qpk, prefix):
         assert torch.equal(lse[:, o:o + L], lse1[0])
         o += L
     assert not torch.isnan(out.float()).any()
+
+
+@pytest.mark.parametrize("lens,G,qpk,prefix,rope", [([200, 77, 128, 1, 333], 2, 2, 10, True), ([480, 330, 415], 4, 8, 10, True),
+                                                    ([129], 1, 1, 0, False), ([256, 100, 300], 2, 4, 0, True)])
+def test_attention_bwd_varlen_equals_per_sequence(lens, G, qpk, prefix, rope):
+    """Packed variable-length backward (cu_seqlens, no pad rows) == the fixed-length kernels run on each sequence alone:
+    dqkv bit for bit (same tiles relative to the sequence start; rows beyond a sequence -- the next sequence's rows inside
+    the last 128-row box -- must contribute nothing), prefix / gate gradients to fp32 accumulation-order tolerance."""
+    N, H = G * (qpk + 2) * 64, G * qpk
+    M = sum(lens)
+    qkv = rnd((M, N), 451, 2.0)
+    dout = rnd((M, H * 64), 454, 1.0)
+    pk, gate = (rnd((prefix, N), 452, 2.0), rnd((H,), 453, 1.0, torch.float32)) if prefix else (None, None)
+    cu = torch.tensor([0] + list(torch.tensor(lens).cumsum(0)), dtype=torch.int32, device=DEV)
+    cos, sin = (t.to(DEV) for t in O.build_rope_cache(512, 64))
+    out = torch.empty((M, H * 64), device=DEV, dtype=torch.bfloat16)
+    lse = torch.empty((H, M), device=DEV)
+    ops.attention_fwd_varlen(qkv, out, lse, cu, max(lens), G, qpk, pk, gate, prefix)
+    dqkv = torch.full((M, N), float("nan"), device=DEV, dtype=torch.bfloat16)
+    ws = torch.empty(M * H * 4, dtype=torch.uint8, device=DEV)
+    dpk = torch.zeros((prefix, N), device=DEV) if prefix else None
+    dg = torch.zeros(H, device=DEV) if prefix else None
+    ops.attention_bwd_varlen(qkv, out, dout, lse, dqkv, ws, cu, max(lens), G, qpk, pk, gate, dpk, dg, prefix,
+                             rope_cos=cos if rope else None, rope_sin=sin if rope else None)
+    torch.cuda.synchronize()
+    assert not torch.isnan(dqkv.float()).any()
+    dpk1 = torch.zeros_like(dpk) if prefix else None
+    dg1 = torch.zeros_like(dg) if prefix else None
+    o = 0
+    for L in lens:
+        q1, do1 = qkv[o:o + L].contiguous(), dout[o:o + L].contiguous()
+        out1 = torch.empty((L, H * 64), device=DEV, dtype=torch.bfloat16)
+        lse1 = torch.empty((1, H, L), device=DEV)
+        ops.attention_fwd(q1, out1, lse1, 1, L, G, qpk, pk, gate, prefix)
+        d1 = torch.full((L, N), float("nan"), device=DEV, dtype=torch.bfloat16)
+        ws1 = torch.empty(ops.attention_bwd_workspace(1, L, G, qpk), dtype=torch.uint8, device=DEV)
+        ops.attention_bwd(q1, out1, do1, lse1, d1, ws1, 1, L, G, qpk, pk, gate, dpk1, dg1, prefix,
+                          rope_cos=cos if rope else None, rope_sin=sin if rope else None)
+        torch.cuda.synchronize()
+        assert torch.equal(dqkv[o:o + L], d1), report(f"varlen bwd seq at {o}", dqkv[o:o + L], d1)
+        o += L
+    if prefix:
+        assert rel(dg, dg1) < 1e-5, report("dgate", dg, dg1)
+        assert rel(dpk, dpk1) < 1e-5, report("dprefix", dpk, dpk1)
 
 
 def test_attention_decode_matches_prefill():

@@ -300,6 +300,63 @@ def test_packed_prefill_equals_padded_prefill():
         m.reset_cache()
 
 
+def _unpad(idx, labels):
+    """Samples of a synthetic right-padded batch (the response span is the last labelled stretch of every row)."""
+    out = []
+    for b in range(idx.shape[0]):
+        n = int((labels[b] != -1).nonzero().max()) + 1
+        out.append({"input_ids": idx[b, :n].clone(), "labels": labels[b, :n].clone()})
+    return out
+
+
+def packed_train_step(m, samples):
+    """The driver's micro-step on a packed batch (collate.pack_varlen -> GPT.forward_packed -> chunked_cross_entropy)."""
+    from dualhyp_b200.collate import pack_varlen
+    pk = {k: v.to(DEV) for k, v in pack_varlen(samples).items()}
+    longest = max(int(s["input_ids"].numel()) for s in samples)
+    logits = m.forward_packed(pk["input_ids"], pk["cu_seqlens"], pk["positions"], longest, lm_head_chunk_size=128)
+    loss = chunked_cross_entropy(logits, pk["targets"])
+    loss.backward()
+    return loss
+
+
+@pytest.mark.parametrize("variant", ["adapter", "lora"])
+def test_packed_training_step_equals_padded_step(variant):
+    """the same samples as one packed row (no pad tokens, cu_seqlens attention forward AND backward) give the
+    loss and PEFT gradients of the reference's right-padded batch -- including the train reduction's denominator, the
+    B * (T - 1) positions of the padded batch (quirk Q2).  Also the opt-in `skip_pad` mode of the unchanged [B, T] call."""
+    m, _ = build(variant, **({"adapter_start_layer": 1} if variant == "adapter" else {}))
+    idx, labels = synthetic.synth_batch(5, 160, 512, SEED + 3, prompt_range=(20, 130))
+    samples = _unpad(idx, labels)
+    longest = max(int(s["input_ids"].numel()) for s in samples)
+    assert longest < 160 and min(int(s["input_ids"].numel()) for s in samples) < longest
+    idx_p, labels_p = idx[:, :longest].to(DEV), labels[:, :longest].to(DEV)       # what the reference's collate_fn builds
+    loss_pad = train_step(m, idx_p, labels_p)
+    g_pad = {n: p.grad.clone() for n, p in m.named_parameters() if p.requires_grad}
+    m.zero_grad(set_to_none=True)
+    loss_pk = packed_train_step(m, samples)
+    assert abs(float(loss_pk) - float(loss_pad)) <= 2e-6 * max(1.0, abs(float(loss_pad))), (float(loss_pk), float(loss_pad))
+    for n, p in m.named_parameters():
+        if p.requires_grad:
+            assert cos_sim(p.grad, g_pad[n]) > 0.99999, n
+            assert abs(float(p.grad.double().norm() / g_pad[n].double().norm().clamp_min(1e-30)) - 1) < 1e-3, n
+    m.zero_grad(set_to_none=True)
+    m.skip_pad = True
+    loss_sp = train_step(m, idx_p, labels_p)
+    m.skip_pad = False
+    assert abs(float(loss_sp) - float(loss_pad)) <= 2e-6 * max(1.0, abs(float(loss_pad)))
+    for n, p in m.named_parameters():
+        if p.requires_grad:
+            assert cos_sim(p.grad, g_pad[n]) > 0.99999, n
+    # validation reduction (mean over valid targets) on the packed row
+    with torch.no_grad():
+        from dualhyp_b200.collate import pack_varlen
+        pk = {k: v.to(DEV) for k, v in pack_varlen(samples).items()}
+        v_pk = chunked_cross_entropy(m.forward_packed(pk["input_ids"], pk["cu_seqlens"], pk["positions"], longest), pk["targets"], chunk_size=0)
+        v_pad = chunked_cross_entropy(m(idx_p)[..., :-1, :], labels_p[..., 1:], chunk_size=0)
+    assert abs(float(v_pk) - float(v_pad)) < 2e-3, (float(v_pk), float(v_pad))
+
+
 def test_reference_generate_loop_runs_on_the_model():
     """generate/base.py's loop restated verbatim: model(x, input_pos) -> logits[0, -1] / temperature -> topk(1) ->
     where(< v) -> softmax -> multinomial, one token at a time through the KV cache.  bf16 logits can tie exactly at
