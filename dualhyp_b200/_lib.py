@@ -42,6 +42,24 @@ class GemmArgs(C.Structure):
     ]
 
 
+class DecodeLayer(C.Structure):
+    """Mirror of `dh_decode_layer` (include/dualhyp.h)."""
+    _fields_ = [("wqkv", C.c_void_p), ("wproj", C.c_void_p), ("w12", C.c_void_p), ("wmlp", C.c_void_p),
+                ("norm2", C.c_void_p), ("norm_next", C.c_void_p), ("cache_k", C.c_void_p), ("cache_v", C.c_void_p),
+                ("prefix_kv", C.c_void_p), ("gate", C.c_void_p)]
+
+
+class DecodeDesc(C.Structure):
+    """Mirror of `dh_decode_desc` (include/dualhyp.h)."""
+    _fields_ = [("n_layer", C.c_int32), ("n_seq", C.c_int32), ("C", C.c_int32), ("I", C.c_int32), ("n_groups", C.c_int32),
+                ("q_per_kv", C.c_int32), ("max_len", C.c_int32), ("prefix_len", C.c_int32),
+                ("eps", C.c_float),
+                ("x", C.c_void_p), ("x2", C.c_void_p), ("n", C.c_void_p), ("qkv", C.c_void_p), ("y", C.c_void_p), ("act", C.c_void_p),
+                ("hidden", C.c_void_p), ("ws", C.c_void_p), ("ws_bytes", C.c_size_t),
+                ("positions", C.c_void_p), ("rope_cos", C.c_void_p), ("rope_sin", C.c_void_p),
+                ("barrier", C.c_void_p), ("layers", C.POINTER(DecodeLayer))]
+
+
 _P, _I, _F, _L, _Z = C.c_void_p, C.c_int, C.c_float, C.c_int64, C.c_size_t
 
 # name -> (restype, argtypes); every symbol include/dualhyp.h declares
@@ -64,6 +82,10 @@ SIGNATURES = {
     "dh_attention_bwd": (_I, [_P, _P, _P, _P, _P, _P, _P, _P, _P, _I, _P, _P, _I, _I, _I, _I, _I, _P, _Z, _P]),
     "dh_attention_bwd_varlen": (_I, [_P, _P, _P, _P, _P, _P, _P, _P, _P, _I, _P, _P, _P, _I, _I, _L, _I, _I, _I, _P, _Z, _P]),
     "dh_attention_decode": (_I, [_P, _P, _P, _P, _P, _P, _P, _I, _I, _I, _I, _I, _P]),
+    "dh_decode_plan_bytes": (_Z, [_I]),
+    "dh_decode_workspace_bytes": (_Z, [C.POINTER(DecodeDesc)]),
+    "dh_decode_plan_build": (_I, [C.POINTER(DecodeDesc), _P]),
+    "dh_decode_layers": (_I, [_P, _P, _P]),
     "dh_prefix_project_fwd": (_I, [_P, _P, _P, _I, _I, _I, _I, _I, _P]),
     "dh_prefix_project_bwd": (_I, [_P, _P, _P, _I, _I, _I, _I, _I, _P]),
     "dh_kv_cache_write": (_I, [_P, _P, _P, _P, _P, _I, _I, _I, _I, _P]),

@@ -495,8 +495,62 @@ class DecoderEngine:
         assert self.cache_k and self.cache_k[0].shape[0] >= idx.shape[0] and self.cache_max_len >= idx.shape[1]
         return self.forward_hidden(idx, packed, save=False, write_cache=True)
 
+    def decode_plan_supported(self, n_seq: int, packed: Dict[int, Dict[str, Tensor]]) -> bool:
+        """The persistent decode kernel covers the base and adapter decoders (a LoRA model decodes through it once merged,
+        generate/lora.py:112 merges before generating; un-merged LoRA factors take the per-GEMM path)."""
+        import os
+        s = self.spec
+        if os.environ.get("DH_DECODE_MEGA", "1") == "0" or not self.cache_k:
+            return False
+        if any(("qkv_a" in d or "proj_a" in d) for d in packed.values()):
+            return False
+        return (1 <= n_seq <= 128 and s.n_embd % 128 == 0 and s.qkv_out % 128 == 0 and (2 * s.intermediate_size) % 128 == 0
+                and s.qpk <= 8 and s.n_layer <= 64 and self.cache_max_len <= 1536)
+
+    def build_decode_plan(self, n_seq: int, positions: Tensor, packed: Dict[int, Dict[str, Tensor]], pkv_all: Optional[Tensor]):
+        """Stage table + TMA descriptors of `dh_decode_layers` for the current cache, the `dec_*` activation buffers of this
+        batch size, `positions` (a device tensor whose ADDRESS is baked in) and the packed adapter tensors."""
+        import ctypes as C
+        from . import _lib
+        s = self.spec
+        Cd, I = s.n_embd, s.intermediate_size
+        bf, f32 = torch.bfloat16, torch.float32
+        assert positions.dtype == torch.int32 and positions.is_contiguous() and positions.numel() == n_seq
+        bufs = dict(x=self._buf("dec_x", (n_seq, Cd), f32), x2=self._buf("dec_x2", (n_seq, Cd), f32), n=self._buf("dec_n", (n_seq, Cd), bf),
+                    qkv=self._buf("dec_qkv", (n_seq, s.qkv_out), bf), y=self._buf("dec_y", (n_seq, Cd), bf), act=self._buf("dec_act", (n_seq, I), bf),
+                    hidden=self._buf("dec_hidden", (n_seq, Cd), bf))
+        if "dec_barrier" not in self._bufs:
+            self._bufs["dec_barrier"] = torch.zeros(2, device=self.device, dtype=torch.int64)     # arrive counter, launch generation
+        barrier = self._bufs["dec_barrier"]
+        layers = (_lib.DecodeLayer * s.n_layer)()
+        keep = [positions, barrier, self.cos, self.sin, self.ln_f, pkv_all] + list(bufs.values())
+        for i, lw in enumerate(self.layers):
+            L, pk = layers[i], packed.get(i, {})
+            L.wqkv, L.wproj, L.w12, L.wmlp = lw["wqkv"].data_ptr(), lw["wproj"].data_ptr(), lw["w12"].data_ptr(), lw["wmlp"].data_ptr()
+            L.norm2 = lw["norm2"].data_ptr()
+            L.norm_next = (self.layers[i + 1]["norm1"] if i + 1 < s.n_layer else self.ln_f).data_ptr()
+            L.cache_k, L.cache_v = self.cache_k[i].data_ptr(), self.cache_v[i].data_ptr()
+            if "prefix" in pk:
+                L.prefix_kv, L.gate = pkv_all[i - s.adapter_start_layer].data_ptr(), pk["gate"].data_ptr()
+                keep.append(pk["gate"])
+        d = _lib.DecodeDesc()
+        d.n_layer, d.n_seq, d.C, d.I, d.n_groups, d.q_per_kv = s.n_layer, n_seq, Cd, I, s.n_query_groups, s.qpk
+        d.max_len, d.prefix_len, d.eps = self.cache_max_len, (s.adapter_prompt_length if s.variant == "adapter" else 0), s.norm_eps
+        for k, t in bufs.items():
+            setattr(d, k, t.data_ptr())
+        d.positions, d.rope_cos, d.rope_sin, d.barrier = positions.data_ptr(), self.cos.data_ptr(), self.sin.data_ptr(), barrier.data_ptr()
+        d.layers = C.cast(layers, C.POINTER(_lib.DecodeLayer))
+        d.ws, d.ws_bytes = 0, 0
+        ws_bytes = ops.decode_workspace_bytes(d)
+        ws = self._cap_buf("dec_mega_ws", (ws_bytes // 4,), f32)
+        d.ws, d.ws_bytes = ws.data_ptr(), ws.numel() * 4
+        keep += [ws, self.cache_k, self.cache_v]
+        plan = ops.DecodePlan(d, keep)
+        plan.n_seq = n_seq
+        return plan
+
     def decode_step(self, tokens: Tensor, positions: Tensor, packed: Dict[int, Dict[str, Tensor]],
-                    pkv_all: Optional[Tensor] = None) -> Tensor:
+                    pkv_all: Optional[Tensor] = None, plan=None) -> Tensor:
         """One new token per sequence: tokens int64 [n], positions int32 [n] (0-based position of that token).
         Returns ln_f output bf16 [n, C].  Allocation-free after the first call of a given n (all buffers come from
         `_buf`), so a whole step can be captured into a CUDA graph (generate.DecodeLoop); `pkv_all` = the adapter
@@ -521,6 +575,12 @@ class DecoderEngine:
         if pkv_all is None:
             pkv_all = self._project_prefixes(packed, "dec_pkv_all")
         hidden = self._buf("dec_hidden", (n_seq, C), bf)
+        if plan is not None:
+            # every layer in ONE persistent kernel (csrc/decode.cu); `plan` was built for these buffers, this cache and `positions`
+            assert plan.n_seq == n_seq
+            ops.rmsnorm_fwd(x, self.layers[0]["norm1"], n, None, s.norm_eps)
+            ops.decode_layers(plan)
+            return hidden
         # The two residual GEMMs (attention proj, mlp proj; N = C gives only C / 128 tiles) run split-K over all SMs and
         # leave fp32 partial products; the norm that follows sums them, adds the residual and normalises in one launch.
         sk_ok = n_seq <= 128 and C % 128 == 0

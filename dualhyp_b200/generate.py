@@ -47,6 +47,8 @@ class DecodeLoop:
         self.trainable_sig = None
         self.graph: Optional[torch.cuda.CUDAGraph] = None
         self.cache_sig = None
+        self.plan = None              # persistent-kernel plan of the token step (engine.build_decode_plan), tied to the cache
+        self.plan_sig = None
 
     def refresh(self, packed: Dict[int, Dict[str, Tensor]]) -> None:
         """New values of the trainable tensors into the buffers the captured graph reads."""
@@ -64,14 +66,29 @@ class DecodeLoop:
         self.eos_id = eos_id
         self.eos.fill_(-1 if eos_id is None else int(eos_id))
 
+    def _cache_signature(self):
+        # everything the captured launches / the plan bake in about the cache: row count, row length (the kernels' max_len stride)
+        # and the K and V base pointers -- the caching allocator can hand a re-allocated cache of another shape the same pointers
+        eng = self.eng
+        return (self.n, eng.cache_max_len, tuple(t.data_ptr() for t in eng.cache_k), tuple(t.data_ptr() for t in eng.cache_v))
+
+    def _ensure_plan(self) -> None:
+        eng = self.eng
+        sig = self._cache_signature()
+        if sig == self.plan_sig:
+            return
+        self.plan = eng.build_decode_plan(self.n, self.pos, self.packed, self.pkv_all) if eng.decode_plan_supported(self.n, self.packed) else None
+        self.plan_sig = sig
+
     def body(self) -> None:
         eng = self.eng
+        self._ensure_plan()
         l0 = ops.launches()
         eng.lm_head(self.last, out=self.logits)
         ops.argmax(self.logits, self.nxt)
         self.out_ids.index_copy_(1, self.step, self.nxt.unsqueeze(1))
         self.done.logical_or_(self.nxt == self.eos)
-        hidden = eng.decode_step(self.nxt, self.pos, self.packed, self.pkv_all)
+        hidden = eng.decode_step(self.nxt, self.pos, self.packed, self.pkv_all, plan=self.plan)
         assert hidden.data_ptr() == self.last.data_ptr()
         self.pos.add_(1)
         self.step.add_(1)
@@ -80,10 +97,7 @@ class DecodeLoop:
     def capture(self) -> None:
         """Record one body() into a graph.  Must follow at least one eager body() of the same shape (first-use
         initialisation inside the C ABI -- function attributes, the device query -- is not capturable)."""
-        # everything the captured launches bake in about the cache: row count, row length (the kernels' max_len stride) and the
-        # K and V base pointers -- the caching allocator can hand a re-allocated cache of another shape the same pointers
-        eng = self.eng
-        sig = (self.n, eng.cache_max_len, tuple(t.data_ptr() for t in eng.cache_k), tuple(t.data_ptr() for t in eng.cache_v))
+        sig = self._cache_signature()
         if self.graph is not None and sig == self.cache_sig:
             return
         torch.cuda.synchronize()

@@ -451,3 +451,31 @@ def scatter_rows(src: Tensor, rows: Tensor, count: Tensor, dst: Tensor) -> None:
     check(_lib.load().dh_scatter_rows(src.data_ptr(), rows.data_ptr(), count.data_ptr(), dst.data_ptr(), dst.shape[0], dst.shape[1],
                                       _stream()), "dh_scatter_rows")
     _count()
+
+
+class DecodePlan:
+    """Host + device copies of the stage table / TMA descriptors of the persistent decode kernel (`dh_decode_layers`)."""
+
+    def __init__(self, desc, keep):
+        lib = _lib.load()
+        n = int(lib.dh_decode_plan_bytes(desc.n_layer))
+        self.host = (C.c_uint8 * n)()
+        check(lib.dh_decode_plan_build(C.byref(desc), self.host), "dh_decode_plan_build")
+        blob = torch.frombuffer(self.host, dtype=torch.uint8)
+        self.dev = torch.empty(n + 64, dtype=torch.uint8, device=keep[0].device)
+        off = (-self.dev.data_ptr()) % 64                      # tensor maps need 64-byte alignment
+        self.dev_view = self.dev[off:off + n]
+        self.dev_view.copy_(blob)
+        self.keep = keep                                       # the tensors whose addresses are baked into the plan
+        self.kernels = 1
+
+
+def decode_workspace_bytes(desc) -> int:
+    return int(_lib.load().dh_decode_workspace_bytes(C.byref(desc)))
+
+
+@_profiled("decode_layers")
+def decode_layers(plan: DecodePlan) -> None:
+    """All decoder layers of one decode token step as one persistent kernel (see include/dualhyp.h)."""
+    check(_lib.load().dh_decode_layers(plan.dev_view.data_ptr(), C.addressof(plan.host), _stream()), "dh_decode_layers")
+    _count()

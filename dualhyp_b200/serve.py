@@ -39,6 +39,7 @@ class SlotLoop(DecodeLoop):
 
     def body(self) -> None:
         eng = self.eng
+        self._ensure_plan()
         l0 = ops.launches()
         eng.lm_head(self.last, out=self.logits)
         ops.argmax(self.logits, self.nxt)
@@ -46,7 +47,7 @@ class SlotLoop(DecodeLoop):
         self.cnt.add_(self.done.logical_not())                       # the token counts only for a live slot
         self.done.logical_or_(self.nxt == self.eos)
         self.done.logical_or_(self.cnt >= self.limit)
-        hidden = eng.decode_step(self.nxt, self.pos, self.packed, self.pkv_all)
+        hidden = eng.decode_step(self.nxt, self.pos, self.packed, self.pkv_all, plan=self.plan)
         assert hidden.data_ptr() == self.last.data_ptr()
         self.pos.add_(self.done.logical_not())                       # a stopped slot stays where it is
         self.kernels_per_token = ops.launches() - l0

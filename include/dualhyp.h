@@ -177,6 +177,43 @@ int dh_prefix_project_bwd(const float* d_prefix_kv, const void* wkv, float* d_pr
 int dh_attention_decode(const void* qkv, const void* cache_k, const void* cache_v, const int32_t* lens, void* out,
                         const void* prefix_kv, const float* gate, int nseq, int max_len, int n_groups, int q_per_kv,
                         int prefix_len, void* stream);
+/* ---------------------------------------------------------------------------------------------------
+ * One decode token step for ALL decoder layers as one persistent kernel (ger/model.py:163-268 per layer, driven one token at
+ * a time by generate/base.py:57-80): one CTA per SM, grid-wide barriers between the stages, the frozen weights of every GEMM
+ * streamed by a producer warp that runs ahead of the barriers (stream-K units over all SMs), split-K partial tiles summed by the
+ * stage that follows (RoPE + KV-cache write inside the attention stage, residual + RMSNorm, SwiGLU).  n_seq <= 128 sequences.
+ *   in : x f32 [n_seq, C] residual stream (the token embeddings), n bf16 [n_seq, C] = rmsnorm(x) * layer 0's norm_1 weight,
+ *        positions int32 [n_seq] (position of the token being decoded = number of cached keys before it)
+ *   out: hidden bf16 [n_seq, C] = ln_f output; x; the k / v rows of the new token in every layer's cache at (row, position)
+ * dh_decode_plan_build encodes the TMA descriptors and the stage table into a HOST blob of dh_decode_plan_bytes(n_layer) bytes;
+ * the caller copies it to device memory (64-byte aligned) and passes both copies to dh_decode_layers.  `barrier` = 16 bytes of
+ * device memory zeroed once; `ws` >= dh_decode_workspace_bytes(desc).  Cache row of sequence i is i.  ABI v3.
+ * ------------------------------------------------------------------------------------------------- */
+typedef struct dh_decode_layer {
+  const void* wqkv; const void* wproj; const void* w12; const void* wmlp;   /* bf16 [N, K] as stored; w12 = fc_1|fc_2 in 32-row blocks */
+  const float* norm2;              /* this layer's norm_2 weight */
+  const float* norm_next;          /* the next layer's norm_1 weight; ln_f weight for the last layer */
+  void* cache_k; void* cache_v;    /* bf16 [n_seq, n_groups, max_len, 64] */
+  const void* prefix_kv;           /* adapter prefix rows bf16 [prefix_len, n_groups*(qpk+2)*64] or NULL */
+  const float* gate;               /* f32 [n_head] or NULL */
+} dh_decode_layer;
+
+typedef struct dh_decode_desc {
+  int32_t n_layer, n_seq, C, I, n_groups, q_per_kv, max_len, prefix_len;
+  float eps;
+  void* x; void* x2; void* n; void* qkv; void* y; void* act; void* hidden;
+  void* ws; size_t ws_bytes;
+  const int32_t* positions;
+  const void* rope_cos; const void* rope_sin;
+  void* barrier;
+  const dh_decode_layer* layers;
+} dh_decode_desc;
+
+size_t dh_decode_plan_bytes(int n_layer);
+size_t dh_decode_workspace_bytes(const dh_decode_desc* desc);
+int dh_decode_plan_build(const dh_decode_desc* desc, void* plan_host);
+int dh_decode_layers(const void* plan_dev, const void* plan_host, void* stream);
+
 /* Scatter the k and v slots of qkv rows into the cache at (seq[m], pos[m]). */
 int dh_kv_cache_write(const void* qkv, void* cache_k, void* cache_v, const int32_t* seq, const int32_t* pos, int M,
                       int max_len, int n_groups, int q_per_kv, void* stream);

@@ -300,6 +300,49 @@ def test_packed_prefill_equals_padded_prefill():
         m.reset_cache()
 
 
+@pytest.mark.parametrize("variant,name,n,plen", [("adapter", "tiny-llama-test", 5, (3, 60)), ("adapter", "tiny-llama-test", 128, (3, 100)),
+                                                 ("lora", "tiny-llama-test", 7, (3, 60)), ("adapter", "tiny-llama-1.1b", 37, (100, 300))])
+def test_persistent_decode_kernel_matches_per_gemm_path(variant, name, n, plen):
+    """One decode token step of all layers as ONE persistent kernel (csrc/decode.cu: stream-K weight streaming over all SMs,
+    grid barriers, partial tiles summed by the stage that follows) against the per-GEMM kernel sequence it replaces: same
+    ln_f state (bf16 tolerance: the fp32 partial sums are associated differently), same new K / V rows in the cache, and
+    bit-identical results from launch to launch (the stages sum their partial tiles in a fixed order)."""
+    m, _ = build(variant, name=name, **({"adapter_start_layer": 1} if (variant == "adapter" and name == "tiny-llama-test") else {}))
+    if variant == "lora":
+        lora.merge_lora_weights(m)               # generate/lora.py:112 merges before decoding; un-merged factors take the per-GEMM path
+    vocab = m.config.padded_vocab_size
+    prompts = [p.to(DEV) for p in synthetic.synth_prompts(n, vocab, SEED + 21, prompt_range=plen)]
+    with torch.inference_mode():
+        generate_batch(m, prompts, 2, use_graph=False)                 # fills the cache rows, leaves the engine's decode buffers in place
+        eng = m._engine
+        names, tensors = m._trainables()
+        packed = eng.pack_trainable(dict(zip(names, tensors)))
+        pkv = eng._project_prefixes(packed, "dec_pkv_all")
+        assert eng.decode_plan_supported(n, packed)
+        pos = torch.tensor([int(p.numel()) + 2 for p in prompts], dtype=torch.int32, device=DEV)
+        tok = synthetic.hash_ints((n,), SEED, 77, 3, vocab).to(DEV)
+        rows = torch.arange(n, device=DEV)
+        h_old = eng.decode_step(tok, pos, packed, pkv).clone()
+        k_old = [ck[rows, :, pos.long()].clone() for ck in eng.cache_k]
+        v_old = [cv[rows, :, pos.long()].clone() for cv in eng.cache_v]
+        for ck, cv in zip(eng.cache_k, eng.cache_v):
+            ck[rows, :, pos.long()] = 0
+            cv[rows, :, pos.long()] = 0
+        plan = eng.build_decode_plan(n, pos, packed, pkv)
+        h_new = eng.decode_step(tok, pos, packed, pkv, plan=plan).clone()
+        torch.cuda.synchronize()
+        assert torch.isfinite(h_new.float()).all()
+        e = rel_err(h_new.float().cpu(), h_old.float().cpu())
+        assert e < 2e-2, f"ln_f state rel err {e:.3e}"
+        for i in range(len(eng.cache_k)):
+            ek = rel_err(eng.cache_k[i][rows, :, pos.long()].float().cpu(), k_old[i].float().cpu())
+            ev = rel_err(eng.cache_v[i][rows, :, pos.long()].float().cpu(), v_old[i].float().cpu())
+            assert ek < 2e-2 and ev < 2e-2, f"layer {i}: new K / V rows rel err {ek:.3e} / {ev:.3e}"
+        h_again = eng.decode_step(tok, pos, packed, pkv, plan=plan).clone()       # second launch: generation counter, determinism
+        assert torch.equal(h_new, h_again)
+    m.reset_cache()
+
+
 def _unpad(idx, labels):
     """Samples of a synthetic right-padded batch (the response span is the last labelled stretch of every row)."""
     out = []

@@ -20,6 +20,10 @@ class _Engine:
         self.device, self.spec, self._bufs = torch.device("cpu"), _Spec(), {}
         self.cache = None
         self.prefills = []
+        self.cache_k, self.cache_v, self.cache_max_len = [], [], ROW
+
+    def decode_plan_supported(self, n_seq, packed):
+        return False                   # the persistent decode kernel needs a GPU: the stand-in takes the per-step path
 
     def _buf(self, name, shape, dtype):
         return self._bufs.setdefault((name, tuple(shape), dtype), torch.zeros(shape, dtype=dtype))
@@ -51,7 +55,8 @@ class _Engine:
         out.scatter_(1, last[:, :1].long(), 1.0)
         return out
 
-    def decode_step(self, tokens, positions, packed, pkv_all=None):
+    def decode_step(self, tokens, positions, packed, pkv_all=None, plan=None):
+        assert plan is None
         hidden = self._buf("dec_hidden", (tokens.numel(), C), torch.bfloat16)
         for s in range(tokens.numel()):
             self.cache[s, int(positions[s])] = int(tokens[s])
