@@ -57,7 +57,7 @@ class DecodeDesc(C.Structure):
                 ("x", C.c_void_p), ("x2", C.c_void_p), ("n", C.c_void_p), ("qkv", C.c_void_p), ("y", C.c_void_p), ("act", C.c_void_p),
                 ("hidden", C.c_void_p), ("ws", C.c_void_p), ("ws_bytes", C.c_size_t),
                 ("positions", C.c_void_p), ("rope_cos", C.c_void_p), ("rope_sin", C.c_void_p),
-                ("barrier", C.c_void_p), ("layers", C.POINTER(DecodeLayer))]
+                ("barrier", C.c_void_p), ("layers", C.POINTER(DecodeLayer)), ("trace", C.c_void_p)]
 
 
 _P, _I, _F, _L, _Z = C.c_void_p, C.c_int, C.c_float, C.c_int64, C.c_size_t
@@ -82,6 +82,7 @@ SIGNATURES = {
     "dh_attention_bwd": (_I, [_P, _P, _P, _P, _P, _P, _P, _P, _P, _I, _P, _P, _I, _I, _I, _I, _I, _P, _Z, _P]),
     "dh_attention_bwd_varlen": (_I, [_P, _P, _P, _P, _P, _P, _P, _P, _P, _I, _P, _P, _P, _I, _I, _L, _I, _I, _I, _P, _Z, _P]),
     "dh_attention_decode": (_I, [_P, _P, _P, _P, _P, _P, _P, _I, _I, _I, _I, _I, _P]),
+    "dh_attention_decode_stream": (_I, [_P, _P, _P, _P, _P, _P, _P, _I, _I, _I, _I, _I, _P]),
     "dh_decode_plan_bytes": (_Z, [_I]),
     "dh_decode_workspace_bytes": (_Z, [C.POINTER(DecodeDesc)]),
     "dh_decode_plan_build": (_I, [C.POINTER(DecodeDesc), _P]),

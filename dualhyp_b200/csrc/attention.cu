@@ -1833,25 +1833,35 @@ extern "C" int dh_attention_bwd_varlen(const void* qkv, const void* out, const v
                             "dh_attention_bwd_varlen");
 }
 
+extern "C" int dh_attention_decode_stream(const void* qkv, const void* cache_k, const void* cache_v, const int32_t* lens, void* out,
+                                          const void* prefix_kv, const float* gate, int nseq, int max_len, int n_groups, int q_per_kv,
+                                          int prefix_len, void* stream);
+
 extern "C" int dh_attention_decode(const void* qkv, const void* cache_k, const void* cache_v, const int32_t* lens, void* out,
                                    const void* prefix_kv, const float* gate, int nseq, int max_len, int n_groups, int q_per_kv,
                                    int prefix_len, void* stream) {
   DH_CHECK(qkv && cache_k && cache_v && lens && out && nseq > 0, "dh_attention_decode: bad argument");
   DH_CHECK(q_per_kv <= DEC_MAX_QPK, "dh_attention_decode: q_per_kv %d > %d", q_per_kv, DEC_MAX_QPK);
   DH_CHECK(prefix_len >= 0 && prefix_len <= MAX_PREFIX, "dh_attention_decode: prefix_len too large");
-  static int variant = -1;      // DH_DEC_CUDA_CORES=1 selects the CUDA-core kernel (A/B runs); default: mma.sync tiles
+  // default: the whole-row mma.sync kernel; DH_DEC_ATTN=stream selects the streamed kernel (csrc/decode_attn.cu: TMA ring of
+  // 64-key chunks, flash-style warps; measured 1.92 vs 1.80 ms per token step of 128 sequences), DH_DEC_CUDA_CORES=1 the
+  // CUDA-core kernel (A/B runs)
+  static int variant = -1;
   if (variant < 0) {
     const char* e = getenv("DH_DEC_CUDA_CORES");
-    variant = (e && e[0] == '1') ? 0 : 1;
+    const char* a = getenv("DH_DEC_ATTN");
+    variant = (e && e[0] == '1') ? 0 : (a && a[0] == 's') ? 2 : 1;
     DH_CUDA(cudaFuncSetAttribute(attn_decode_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, 200 * 1024));
     DH_CUDA(cudaFuncSetAttribute(attn_decode_mma_kernel<2>, cudaFuncAttributeMaxDynamicSharedMemorySize, 200 * 1024));
     DH_CUDA(cudaFuncSetAttribute(attn_decode_mma_kernel<4>, cudaFuncAttributeMaxDynamicSharedMemorySize, 200 * 1024));
   }
+  if (variant == 2 && max_len % 64 == 0 && q_per_kv <= 8)
+    return dh_attention_decode_stream(qkv, cache_k, cache_v, lens, out, prefix_kv, gate, nseq, max_len, n_groups, q_per_kv, prefix_len, stream);
   const long long ld = (long long)n_groups * (q_per_kv + 2) * HD;
   const bf16* pkv = (const bf16*)(prefix_len > 0 ? prefix_kv : nullptr);
   const int plen = prefix_kv ? prefix_len : 0;
   const float scale = 1.0f / sqrtf((float)HD);
-  if (variant == 1) {
+  if (variant >= 1) {
     const size_t score_bytes = (size_t)q_per_kv * (max_len + 20) * sizeof(float);
     const bool deep = 2 * (dm_fixed_bytes(4) + score_bytes + 1024) <= 227 * 1024;      // two blocks per SM with 4 tiles per warp?
     const size_t smem = (size_t)dm_fixed_bytes(deep ? 4 : 2) + score_bytes;

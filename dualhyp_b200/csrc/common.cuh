@@ -117,10 +117,11 @@ __device__ __forceinline__ bool mbar_try_wait(uint64_t* bar, uint32_t parity) {
       : "memory");
   return ok != 0;
 }
-static __device__ __noinline__ void mbar_hang(const uint64_t* bar, uint32_t parity) {
+[[noreturn]] static __device__ __noinline__ void mbar_hang(const uint64_t* bar, uint32_t parity) {
   printf("[dualhyp] mbarrier wait timed out: block (%d,%d,%d) thread %d bar@%u parity %u\n", blockIdx.x, blockIdx.y,
          blockIdx.z, threadIdx.x, smem_u32(bar), parity);
   __trap();
+  while (true) {}
 }
 __device__ __forceinline__ void mbar_wait(uint64_t* bar, uint32_t parity) {
   if (mbar_try_wait(bar, parity)) return;

@@ -22,13 +22,18 @@
 //     cached keys (native GQA), adapter prefix with its own softmax (ger/adapter.py:116-146) -- the algorithm of
 //     attn_decode_mma_kernel (attention.cu) run as a stage of this kernel.
 //
+//   * the KV cache is STREAMED like the weights: the activation producer's ring also carries the attention stage's K / V
+//     chunks (64 keys: K 8 KB + V 8 KB per stage, 128-byte-swizzled TMA boxes of the cache rows).  Only keys written by
+//     EARLIER launches are streamed (the new token's k / v stay in shared memory), so the loads have no dependency on this
+//     step and start as soon as the QKV GEMM has freed the ring -- before the grid barrier in front of the attention.
+//
 // Warp roles (352 threads): warps 0-7 compute (barriers, partial-tile drain, consumers, attention), warp 8 weight TMA,
-// warp 9 activation TMA, warp 10 tcgen05.mma issue.
+// warp 9 activation / KV-chunk TMA, warp 10 tcgen05.mma issue.
 #include <math.h>
 #include <stdlib.h>
 #include <string.h>
 
-#include "common.cuh"
+#include "decode_attn.cuh"
 #include "../../include/dualhyp.h"
 
 namespace dh {
@@ -36,16 +41,20 @@ namespace dh {
 constexpr int DK_CWARPS = 8;
 constexpr int DK_CTHREADS = DK_CWARPS * 32;
 constexpr int DK_THREADS = (DK_CWARPS + 3) * 32;
-constexpr int DK_TILE_BYTES = 128 * 64 * 2;        // one [128 rows x 64 k] bf16 box
-constexpr int DK_W_STAGES = 8;
-constexpr int DK_A_STAGES = 2;
+constexpr int DK_TILE_BYTES = 128 * 64 * 2;        // one [128 rows x 64 k] bf16 box = one ring stage
+constexpr int DK_W_STAGES = 4;
+constexpr int DK_A_STAGES = 7;
+constexpr int DK_STG_BYTES = 32 * 1024;            // drain transpose staging (4 KB per compute warp) / attention scratch
+constexpr int DK_KV_KEYS = KVC_KEYS;               // keys per streamed K / V chunk (K 8 KB + V 8 KB = one ring stage)
 constexpr int DK_HD = 64;
 constexpr int DK_MAX_QPK = 8;
 constexpr int DK_MAX_PREFIX = 16;
 constexpr int DK_MAX_LAYERS = 64;
+constexpr int DK_TRACE_SLOTS = 24;
 
 struct DecodeLayer {
   CUtensorMap wqkv, wproj, w12, wmlp;   // [N, K] bf16 K-major, box {64 k, 128 n}
+  CUtensorMap kmap, vmap;               // KV cache as [n_seq * G * max_len, 64] bf16, box {64, DK_KV_KEYS keys}
   const float* norm2;                   // this layer's norm_2 weight
   const float* norm_next;               // the next layer's norm_1 weight (ln_f after the last layer)
   bf16* cache_k;
@@ -55,6 +64,17 @@ struct DecodeLayer {
   long long pad_[2];
 };
 static_assert(sizeof(DecodeLayer) % 64 == 0, "tensor maps inside the layer array must stay 64-byte aligned");
+// the pointer members of a DecodeLayer: the kernel keeps a copy of these per layer in shared memory (with 200+ KB of shared
+// memory per CTA the L1 is almost gone, so every read of the plan in global memory would be an L2 round trip)
+struct LayerPtrs {
+  const float* norm2;
+  const float* norm_next;
+  bf16* cache_k;
+  bf16* cache_v;
+  const bf16* prefix_kv;
+  const float* gate;
+};
+static_assert(offsetof(DecodeLayer, norm2) + sizeof(LayerPtrs) <= sizeof(DecodeLayer), "LayerPtrs mirrors the tail of DecodeLayer");
 
 struct DecodePlan {
   CUtensorMap a_n, a_y, a_act;          // activation operands [n_seq, K] bf16, box {64 k, 128 rows}
@@ -74,7 +94,8 @@ struct DecodePlan {
   const bf16* rope_cos;
   const bf16* rope_sin;
   unsigned long long* bar;              // [0] arrive counter, [1] launch generation
-  long long pad_[3];
+  long long* trace;                     // optional [2 CTAs][n_layer][9] globaltimer stamps of the compute warps (NULL: off)
+  long long pad_[2];
 };
 static_assert(sizeof(DecodePlan) % 64 == 0, "the layer array follows the plan header and must stay 64-byte aligned");
 
@@ -87,6 +108,9 @@ __device__ __forceinline__ unsigned long long ld_acquire_u64(const unsigned long
   asm volatile("ld.acquire.gpu.global.u64 %0, [%1];" : "=l"(v) : "l"(p) : "memory");
   return v;
 }
+__device__ __forceinline__ void red_release_add_u64(unsigned long long* p, unsigned long long v) {
+  asm volatile("red.release.gpu.global.add.u64 [%0], %1;" ::"l"(p), "l"(v) : "memory");
+}
 __device__ __forceinline__ int ld_volatile_shared(const int* p) {
   int v;
   asm volatile("ld.volatile.shared.s32 %0, [%1];" : "=r"(v) : "r"(smem_u32(p)) : "memory");
@@ -94,17 +118,19 @@ __device__ __forceinline__ int ld_volatile_shared(const int* p) {
 }
 __device__ __forceinline__ void fence_proxy_async_all() { asm volatile("fence.proxy.async;" ::: "memory"); }
 
-static __device__ __noinline__ void dk_hang(const char* what, int a, int b) {
+[[noreturn]] static __device__ __noinline__ void dk_hang(const char* what, int a, int b) {
   printf("[dualhyp] decode step timed out in %s (block %d, %d / %d)\n", what, blockIdx.x, a, b);
   __trap();
+  while (true) {}
 }
 
-// grid-wide barrier over the compute warps of all CTAs: every CTA arrives once on a monotonic counter
+// grid-wide barrier over the compute warps of all CTAs: every CTA arrives once on a monotonic counter.  bar.sync orders the
+// CTA's writes before thread 0's release, and thread 0's acquire before the CTA's later reads (all cross-CTA reads in this
+// kernel go to L2: ld.global.cg, TMA).
 __device__ __forceinline__ void grid_barrier(unsigned long long* bar, unsigned long long target) {
   cbar_sync();
   if (threadIdx.x == 0) {
-    __threadfence();
-    atomicAdd(bar, 1ULL);
+    red_release_add_u64(bar, 1ULL);
     if (ld_acquire_u64(bar) < target) {
       const uint64_t t0 = globaltimer_ns();
       uint32_t spins = 0;
@@ -112,74 +138,102 @@ __device__ __forceinline__ void grid_barrier(unsigned long long* bar, unsigned l
         if (((++spins) & 0xFF) == 0 && globaltimer_ns() - t0 > DH_HANG_GUARD_NS) dk_hang("grid barrier", (int)(target & 0x7fffffff), 0);
       }
     }
-    __threadfence();          // gpu-scope fence: also drops this SM's L1 lines (data other CTAs wrote since)
   }
   cbar_sync();
 }
 
 struct Phase {
-  const CUtensorMap* w;
-  const CUtensorMap* a;
   int tiles, nkb, maxseg, units;
+  int P;            // CTAs that share this GEMM: min(grid, units), so that every one of them owns at least one unit
 };
-__device__ __forceinline__ Phase get_phase(const DecodePlan* p, const DecodeLayer* L, int g) {
+// `p` = the plan header (the kernel passes its shared-memory copy)
+__device__ __forceinline__ Phase get_phase(const DecodePlan* p, int g) {
   Phase ph;
-  if (g == 0) { ph.w = &L->wqkv; ph.a = &p->a_n; ph.tiles = p->G * (p->qpk + 2) * DK_HD / 128; ph.nkb = p->C / 64; }
-  else if (g == 1) { ph.w = &L->wproj; ph.a = &p->a_y; ph.tiles = p->C / 128; ph.nkb = p->C / 64; }
-  else if (g == 2) { ph.w = &L->w12; ph.a = &p->a_n; ph.tiles = 2 * p->I / 128; ph.nkb = p->C / 64; }
-  else { ph.w = &L->wmlp; ph.a = &p->a_act; ph.tiles = p->C / 128; ph.nkb = p->I / 64; }
+  if (g == 0) { ph.tiles = p->G * (p->qpk + 2) * DK_HD / 128; ph.nkb = p->C / 64; }
+  else if (g == 1) { ph.tiles = p->C / 128; ph.nkb = p->C / 64; }
+  else if (g == 2) { ph.tiles = 2 * p->I / 128; ph.nkb = p->C / 64; }
+  else { ph.tiles = p->C / 128; ph.nkb = p->I / 64; }
   ph.maxseg = p->maxseg[g];
   ph.units = ph.tiles * ph.nkb;
+  ph.P = ph.units < p->n_ctas ? ph.units : p->n_ctas;
   return ph;
 }
+// tensor maps live in GLOBAL memory (the plan as the host wrote it): weight map of GEMM g in layer L, activation map of GEMM g
+__device__ __forceinline__ const CUtensorMap* weight_map(const DecodeLayer* L, int g) {
+  return g == 0 ? &L->wqkv : g == 1 ? &L->wproj : g == 2 ? &L->w12 : &L->wmlp;
+}
+__device__ __forceinline__ const CUtensorMap* act_map(const DecodePlan* gp, int g) {
+  return g == 1 ? &gp->a_y : g == 3 ? &gp->a_act : &gp->a_n;
+}
 // contiguous run of (tile, k-block) units of CTA c: [unit_lo(c), unit_lo(c + 1))
-__device__ __host__ __forceinline__ int unit_lo(int units, int c, int P) { return (int)((long long)units * c / P); }
+__device__ __host__ __forceinline__ int unit_lo(int units, int c, int P) { return c >= P ? units : (int)((long long)units * c / P); }
 // the CTA whose run holds unit u
 __device__ __host__ __forceinline__ int unit_owner(int units, int u, int P) { return (int)((((long long)u + 1) * P - 1) / units); }
+
+// number of partial-tile slices of `tile` (the CTAs whose runs touch it are contiguous and each owns at least one unit)
+__device__ __forceinline__ int tile_segments(const Phase& ph, int tile) {
+  return unit_owner(ph.units, (tile + 1) * ph.nkb - 1, ph.P) - unit_owner(ph.units, tile * ph.nkb, ph.P) + 1;
+}
+
+__device__ __forceinline__ void f4_add(float4& a, const float4& b) { a.x += b.x; a.y += b.y; a.z += b.z; a.w += b.w; }
+
+// Sum `nseg` partial-tile slices (16384 floats apart) at two float4 positions, slices in ascending order (deterministic); the
+// loads of NB slices are issued together so that the reduction costs one L2 round trip, not nseg.
+template <int NB = 4>
+__device__ __forceinline__ void sum_slices2(const float* base, int off_b, int nseg, float4& lo, float4& hi) {
+  lo = make_float4(0.f, 0.f, 0.f, 0.f);
+  hi = lo;
+  for (int s0 = 0; s0 < nseg; s0 += NB) {
+    float4 a[NB], b[NB];
+#pragma unroll
+    for (int i = 0; i < NB; ++i) {
+      a[i] = make_float4(0.f, 0.f, 0.f, 0.f);
+      b[i] = a[i];
+      if (s0 + i < nseg) {
+        a[i] = __ldcg(reinterpret_cast<const float4*>(base + (size_t)(s0 + i) * 128 * 128));
+        b[i] = __ldcg(reinterpret_cast<const float4*>(base + (size_t)(s0 + i) * 128 * 128 + off_b));
+      }
+    }
+#pragma unroll
+    for (int i = 0; i < NB; ++i) { f4_add(lo, a[i]); f4_add(hi, b[i]); }       // absent slices add +0
+  }
+}
 
 // ---------------------------------------------------------------------------------------------
 // attention stage (one (sequence, kv group) item; 256 compute threads)
 // ---------------------------------------------------------------------------------------------
-__device__ __forceinline__ void dk_mma_16816(float (&d)[4], uint32_t a0, uint32_t a1, uint32_t a2, uint32_t a3, uint32_t b0, uint32_t b1) {
-  asm volatile("mma.sync.aligned.m16n8k16.row.col.f32.bf16.bf16.f32 {%0,%1,%2,%3}, {%4,%5,%6,%7}, {%8,%9}, {%0,%1,%2,%3};"
-               : "+f"(d[0]), "+f"(d[1]), "+f"(d[2]), "+f"(d[3])
-               : "r"(a0), "r"(a1), "r"(a2), "r"(a3), "r"(b0), "r"(b1));
-}
-__device__ __forceinline__ void dk_ldmatrix_x4_trans(uint32_t (&r)[4], uint32_t smem_addr) {
-  asm volatile("ldmatrix.sync.aligned.m8n8.x4.trans.shared.b16 {%0,%1,%2,%3}, [%4];"
-               : "=r"(r[0]), "=r"(r[1]), "=r"(r[2]), "=r"(r[3]) : "r"(smem_addr));
-}
 __device__ __forceinline__ void dk_cp_async_16(uint32_t dst_smem, const void* src, int src_bytes) {
   asm volatile("cp.async.cg.shared.global [%0], [%1], 16, %2;" ::"r"(dst_smem), "l"(src), "r"(src_bytes) : "memory");
 }
 __device__ __forceinline__ void dk_cp_async_commit() { asm volatile("cp.async.commit_group;" ::: "memory"); }
 template <int N> __device__ __forceinline__ void dk_cp_async_wait() { asm volatile("cp.async.wait_group %0;" ::"n"(N) : "memory"); }
 
-__host__ __device__ constexpr int dk_vt_bytes(int nvb) { return 8 * nvb * 2048; }
-__host__ __device__ constexpr int dk_att_fixed_bytes(int nvb) {
-  return dk_vt_bytes(nvb) + (DK_MAX_QPK * DK_HD + 2 * DK_MAX_QPK) * 4 + DK_MAX_PREFIX * 256;
-}
+// attention scratch inside the 32 KB staging region
+struct AttScratch {
+  float part[DK_CWARPS][DK_MAX_QPK][DK_HD];     // per-warp un-normalised outputs over the warp's key chunks
+  float pm[DK_CWARPS][DK_MAX_QPK];              // per-warp running max (log2 domain)
+  float pl[DK_CWARPS][DK_MAX_QPK];              // per-warp sum of exp2
+  float sout[DK_MAX_QPK][DK_HD];                // merged, normalised output of the cached keys + the new key
+  float snew[DK_MAX_QPK];                       // the new key's score (log2 domain)
+  float knew[DK_HD], vnew[DK_HD];               // the new token's k (after RoPE) and v, bf16-rounded
+  bf16 sq[DK_MAX_QPK][DK_HD];                   // the new token's q heads of this group (after RoPE)
+  bf16 spfx[DK_MAX_PREFIX][2 * DK_HD];          // adapter prefix rows [k 64 | v 64]
+};
+static_assert(sizeof(AttScratch) <= DK_STG_BYTES, "attention scratch must fit the staging region");
 
 // Sum the QKV GEMM's partial tiles for row `seq`, columns of kv group g (qpk + 2 head slots), apply NeoX RoPE to the q and k
-// slots at the row's position (the DH_EPI_QKV_ROPE math: bf16-rounded product, bf16 tables, pairs (j, j + 32)), write the
-// bf16 qkv row segment and put the k / v slots into the KV cache at (seq, pos).  80 of the 256 threads work.
-__device__ __forceinline__ void qkv_reduce_rope_cache(const DecodePlan* p, const DecodeLayer* L, const Phase& ph, int seq, int g, int pos, int tid) {
+// slots at the row's position (the DH_EPI_QKV_ROPE math: bf16-rounded product, bf16 tables, pairs (j, j + 32)); the q heads
+// stay in shared memory, the k / v slots go to the KV cache at (seq, pos) and to shared memory.  80 of the 256 threads work.
+__device__ __forceinline__ void qkv_reduce_rope_cache(const DecodePlan* p, const LayerPtrs* L, const Phase& ph, AttScratch* sc, int seq, int g,
+                                                      int pos, int tid) {
   const int slots = p->qpk + 2;
-  const int N = p->G * slots * DK_HD;
-  const int P = p->n_ctas;
   for (int t = tid; t < slots * 8; t += DK_CTHREADS) {
     const int slot = t >> 3, j = (t & 7) * 4;
     const int col0 = (g * slots + slot) * DK_HD + j;
     const int tile = col0 >> 7, within = col0 & 127;
-    const int first = unit_owner(ph.units, tile * ph.nkb, P), last = unit_owner(ph.units, (tile + 1) * ph.nkb - 1, P);
-    float4 lo = make_float4(0.f, 0.f, 0.f, 0.f), hi = lo;
-    const float* base = p->ws + ((size_t)tile * ph.maxseg * 128 + seq) * 128 + within;
-    for (int s = 0; s <= last - first; ++s) {
-      const float4 a = __ldcg(reinterpret_cast<const float4*>(base + (size_t)s * 128 * 128));
-      const float4 b = __ldcg(reinterpret_cast<const float4*>(base + (size_t)s * 128 * 128 + 32));
-      lo.x += a.x; lo.y += a.y; lo.z += a.z; lo.w += a.w;
-      hi.x += b.x; hi.y += b.y; hi.z += b.z; hi.w += b.w;
-    }
+    const int first = unit_owner(ph.units, tile * ph.nkb, ph.P), last = unit_owner(ph.units, (tile + 1) * ph.nkb - 1, ph.P);
+    float4 lo, hi;
+    sum_slices2<4>(p->ws + ((size_t)tile * ph.maxseg * 128 + seq) * 128 + within, 32, last - first + 1, lo, hi);
     float l4[4] = {lo.x, lo.y, lo.z, lo.w}, h4[4] = {hi.x, hi.y, hi.z, hi.w};
     if (slot <= p->qpk) {
       const uint2 cu = *reinterpret_cast<const uint2*>(p->rope_cos + (long long)pos * 64 + j);   // table halves are identical (repeat(1, 2))
@@ -195,221 +249,173 @@ __device__ __forceinline__ void qkv_reduce_rope_cache(const DecodePlan* p, const
     }
     const uint2 lo2 = make_uint2(pack_bf16x2(l4[0], l4[1]), pack_bf16x2(l4[2], l4[3]));
     const uint2 hi2 = make_uint2(pack_bf16x2(h4[0], h4[1]), pack_bf16x2(h4[2], h4[3]));
-    bf16* dst = p->qkv + (long long)seq * N + col0;
-    *reinterpret_cast<uint2*>(dst) = lo2;
-    *reinterpret_cast<uint2*>(dst + 32) = hi2;
-    if (slot >= p->qpk) {
+    if (slot < p->qpk) {
+      *reinterpret_cast<uint2*>(&sc->sq[slot][j]) = lo2;
+      *reinterpret_cast<uint2*>(&sc->sq[slot][j + 32]) = hi2;
+    } else {
       bf16* cd = (slot == p->qpk ? L->cache_k : L->cache_v) + (((long long)seq * p->G + g) * p->max_len + pos) * DK_HD + j;
       *reinterpret_cast<uint2*>(cd) = lo2;
       *reinterpret_cast<uint2*>(cd + 32) = hi2;
+      float* dn = slot == p->qpk ? sc->knew : sc->vnew;
+      const float2 a0 = unpack_bf16x2(lo2.x), a1 = unpack_bf16x2(lo2.y), b0 = unpack_bf16x2(hi2.x), b1 = unpack_bf16x2(hi2.y);
+      dn[j] = a0.x; dn[j + 1] = a0.y; dn[j + 2] = a1.x; dn[j + 3] = a1.y;
+      dn[j + 32] = b0.x; dn[j + 33] = b0.y; dn[j + 34] = b1.x; dn[j + 35] = b1.y;
     }
   }
 }
 
-template <int NVB>
-__device__ __forceinline__ void attention_item(const DecodePlan* p, const DecodeLayer* L, uint8_t* sdm, int seq, int g, int len, int tid) {
+// One (sequence, kv group) item: `pos` keys of earlier steps arrive through the activation ring as chunks of 64 keys (K tile
+// at the stage base, V tile 8 KB above it; 128-byte rows, 16-byte chunks XOR-swizzled by row & 7); warp w owns chunks w,
+// w + 8, ... and keeps a flash-style running (max, sum, output) for the group's q heads (rows of m16n8k16 tiles, native GQA);
+// the warps' partial results and the new token's own key are merged in shared memory.  `ait` = ring index of the item's first
+// chunk (advanced by the number of chunks).
+__device__ __forceinline__ void attention_item(const DecodePlan* p, const LayerPtrs* L, uint8_t* aring, AttScratch* sc,
+                                               uint64_t* a_full, uint64_t* a_empty, uint32_t* slot_done, uint32_t& ait, int seq, int g, int pos,
+                                               int tid) {
   const int warp = tid >> 5, lane = tid & 31;
-  const int qpk = p->qpk, G = p->G, max_len = p->max_len;
+  const int qpk = p->qpk, G = p->G;
   const int prefix_len = L->prefix_kv ? p->prefix_len : 0;
   const float scale = p->scale;
-  const long long ld_qkv = (long long)G * (qpk + 2) * DK_HD;
-  uint8_t* vt = sdm;                                                    // [8 warps][NVB][16 keys][128 B], later [8][8][64] floats
-  float* spart = reinterpret_cast<float*>(sdm);
-  float* sout = reinterpret_cast<float*>(sdm + dk_vt_bytes(NVB));       // [8][64]
-  float* sinv = sout + DK_MAX_QPK * DK_HD;                              // [8] 1 / sum, [8] spare
-  bf16* spfx = reinterpret_cast<bf16*>(sinv + 2 * DK_MAX_QPK);          // [MAX_PREFIX][k 64 | v 64]
-  float* sc = sinv + 2 * DK_MAX_QPK + DK_MAX_PREFIX * 64;               // [qpk][stride] scores / probabilities
-  const int stride = max_len + 20;
+  const float sl2 = scale * 1.4426950408889634f;
   const int r = lane >> 2, q = lane & 3;
-  const int H = G * qpk;
-  const bf16* qrow = p->qkv + (long long)seq * ld_qkv + (long long)(g * (qpk + 2)) * DK_HD;
-  const bf16* kg = L->cache_k + ((long long)seq * G + g) * max_len * DK_HD;
-  const bf16* vg = L->cache_v + ((long long)seq * G + g) * max_len * DK_HD;
+  const long long ld_qkv = (long long)G * (qpk + 2) * DK_HD;
 
+  qkv_reduce_rope_cache(p, L, get_phase(p, 0), sc, seq, g, pos, tid);
   if (tid < prefix_len * 16) {
     const int a = tid >> 4, c = tid & 15;
-    dk_cp_async_16(smem_u32(spfx + a * 128 + c * 8), L->prefix_kv + (long long)a * ld_qkv + (long long)(g * (qpk + 2) + qpk) * DK_HD + c * 8, 16);
+    dk_cp_async_16(smem_u32(&sc->spfx[a][c * 8]), L->prefix_kv + (long long)a * ld_qkv + (long long)(g * (qpk + 2) + qpk) * DK_HD + c * 8, 16);
   }
-  float q0 = 0.f, q1 = 0.f, gate_h = 0.f;
-  if (warp < qpk && prefix_len > 0) {
-    q0 = __bfloat162float(qrow[warp * DK_HD + lane]) * scale;
-    q1 = __bfloat162float(qrow[warp * DK_HD + lane + 32]) * scale;
-    gate_h = L->gate[g * qpk + warp];
+  dk_cp_async_commit();
+  cbar_sync();                                  // sq / knew / vnew visible
+
+  // q fragments (A operand rows = heads; rows >= qpk are zero)
+  uint32_t qa[4][2];
+#pragma unroll
+  for (int ks = 0; ks < 4; ++ks) {
+    qa[ks][0] = r < qpk ? *reinterpret_cast<const uint32_t*>(&sc->sq[r][16 * ks + 2 * q]) : 0u;
+    qa[ks][1] = r < qpk ? *reinterpret_cast<const uint32_t*>(&sc->sq[r][16 * ks + 8 + 2 * q]) : 0u;
   }
-  const int nblk16 = (len + 15) >> 4;
-  const uint32_t mytile_s = smem_u32(vt + warp * (NVB * 2048));
-  auto fetch_block = [&](int blk, int buf) {
-#pragma unroll
-    for (int i = 0; i < 4; ++i) {
-      const int e = lane + 32 * i, kin = e >> 3, c = e & 7, key = blk * 16 + kin;
-      const bool ok = blk < nblk16 && key < len;
-      dk_cp_async_16(mytile_s + buf * 2048 + kin * 128 + ((c ^ (kin & 7)) << 4), reinterpret_cast<const uint4*>(vg + (long long)(ok ? key : 0) * DK_HD) + c, ok ? 16 : 0);
-    }
-    dk_cp_async_commit();
-  };
-#pragma unroll
-  for (int i = 0; i < NVB; ++i) fetch_block(warp + 8 * i, i);
-  // ---- scores ----
-  {
-    uint4 qa[2] = {make_uint4(0, 0, 0, 0), make_uint4(0, 0, 0, 0)};
-    if (r < qpk) {
-      qa[0] = __ldcg(reinterpret_cast<const uint4*>(qrow + r * DK_HD + 8 * q));
-      qa[1] = __ldcg(reinterpret_cast<const uint4*>(qrow + r * DK_HD + 32 + 8 * q));
-    }
-    const int nblk = (len + 7) >> 3;
-    for (int b0 = warp; b0 < nblk; b0 += 64) {
-      uint4 kv[8][2];
-#pragma unroll
-      for (int u = 0; u < 8; ++u) {
-        const int key = (b0 + 8 * u) * 8 + r;
-        const bool ok = key < len;
-        const uint4* kp = reinterpret_cast<const uint4*>(kg + (long long)key * DK_HD + 8 * q);
-        kv[u][0] = ok ? __ldcg(kp) : make_uint4(0, 0, 0, 0);
-        kv[u][1] = ok ? __ldcg(kp + 4) : make_uint4(0, 0, 0, 0);
-      }
-#pragma unroll
-      for (int u = 0; u < 8; ++u) {
-        const int key0 = (b0 + 8 * u) * 8;
-        if (key0 < len) {
-          float c[4] = {0.f, 0.f, 0.f, 0.f};
-          dk_mma_16816(c, qa[0].x, 0u, qa[0].y, 0u, kv[u][0].x, kv[u][0].y);
-          dk_mma_16816(c, qa[0].z, 0u, qa[0].w, 0u, kv[u][0].z, kv[u][0].w);
-          dk_mma_16816(c, qa[1].x, 0u, qa[1].y, 0u, kv[u][1].x, kv[u][1].y);
-          dk_mma_16816(c, qa[1].z, 0u, qa[1].w, 0u, kv[u][1].z, kv[u][1].w);
-          const int k = key0 + 2 * q;
-          if (r < qpk) {
-            if (k < len) sc[r * stride + k] = c[0] * scale;
-            if (k + 1 < len) sc[r * stride + k + 1] = c[1] * scale;
-          }
+  KvcState st;
+  st.init();
+  const int nch = (pos + DK_KV_KEYS - 1) / DK_KV_KEYS;
+  for (int c = warp; c < nch; c += DK_CWARPS) {
+    const uint32_t it = ait + c;
+    const int s = it % DK_A_STAGES;
+    // A parity wait may look at most ONE phase ahead.  Chunk c shares its stage with chunk c - A_STAGES, which ANOTHER warp
+    // consumes: wait for that warp's release through a monotonic per-stage counter (it cannot alias the way a parity does)
+    // -- after it the phase in flight on a_full[s] is this chunk's.
+    if (c >= DK_A_STAGES) {
+      const uint32_t want = it - DK_A_STAGES + 1;
+      if ((uint32_t)ld_volatile_shared(reinterpret_cast<const int*>(slot_done + s)) < want) {
+        const uint64_t t0 = globaltimer_ns();
+        uint32_t spins = 0;
+        while ((uint32_t)ld_volatile_shared(reinterpret_cast<const int*>(slot_done + s)) < want) {
+          if (((++spins) & 0x3FF) == 0 && globaltimer_ns() - t0 > DH_HANG_GUARD_NS) dk_hang("kv stage hand-over", (int)want, s);
         }
       }
     }
+    mbar_wait(&a_full[s], (it / DK_A_STAGES) & 1);
+    kvc_chunk_step(st, qa, smem_u32(aring + s * DK_TILE_BYTES), c * DK_KV_KEYS, pos, sl2, lane);
+    __syncwarp();
+    if (lane == 0) {
+      asm volatile("st.volatile.shared.u32 [%0], %1;" ::"r"(smem_u32(slot_done + s)), "r"(it + 1) : "memory");
+      mbar_arrive(&a_empty[s]);                        // the stage may be refilled
+    }
   }
-  cbar_sync();
+  ait += nch;
+  st.l += __shfl_xor_sync(0xffffffffu, st.l, 1);
+  st.l += __shfl_xor_sync(0xffffffffu, st.l, 2);
+#pragma unroll
+  for (int dt = 0; dt < 8; ++dt) *reinterpret_cast<float2*>(&sc->part[warp][r][8 * dt + 2 * q]) = make_float2(st.acc[dt][0], st.acc[dt][1]);
+  if (q == 0) { sc->pm[warp][r] = st.m; sc->pl[warp][r] = st.l; }
+  // the new token's own key: score per head (warp = head)
+  float q0 = 0.f, q1 = 0.f, gate_h = 0.f;
   if (warp < qpk) {
-    float* row = sc + warp * stride;
-    float mx = -INFINITY;
-    for (int k = lane; k < len; k += 32) mx = fmaxf(mx, row[k]);
-    mx = warp_max(mx);
-    float sum = 0.f;
-    for (int k = lane; k < len; k += 32) {
-      const float e = __expf(row[k] - mx);
-      row[k] = e;
-      sum += e;
-    }
-    sum = warp_sum(sum);
-    if (lane == 0) sinv[warp] = 1.f / sum;
-    if (lane < 16 && len + lane < ((len + 15) & ~15)) row[len + lane] = 0.f;
+    q0 = __bfloat162float(sc->sq[warp][lane]);
+    q1 = __bfloat162float(sc->sq[warp][lane + 32]);
+    const float d = warp_sum(q0 * sc->knew[lane] + q1 * sc->knew[lane + 32]);
+    if (lane == 0) sc->snew[warp] = d * sl2;
+    q0 *= scale;
+    q1 *= scale;
+    if (prefix_len > 0) gate_h = L->gate[g * qpk + warp];
   }
+  dk_cp_async_wait<0>();
   cbar_sync();
-  float acc[8][4];
-#pragma unroll
-  for (int nb = 0; nb < 8; ++nb)
-#pragma unroll
-    for (int j = 0; j < 4; ++j) acc[nb][j] = 0.f;
-  {
-    int it = 0;
-    for (int blk = warp; blk < nblk16; blk += 8, ++it) {
-      const int buf = it % NVB;
-      dk_cp_async_wait<NVB - 1>();
-      __syncwarp();
-      uint32_t a0 = 0u, a2 = 0u;
-      if (r < qpk) {
-        const float* pr = sc + r * stride + blk * 16 + 2 * q;
-        const float2 p0 = *reinterpret_cast<const float2*>(pr), p1 = *reinterpret_cast<const float2*>(pr + 8);
-        a0 = pack_bf16x2(p0.x, p0.y);
-        a2 = pack_bf16x2(p1.x, p1.y);
-      }
-      const uint32_t tile_s = mytile_s + buf * 2048;
-      const int m = lane >> 3, key = 8 * (m & 1) + (lane & 7);
-#pragma unroll
-      for (int j = 0; j < 4; ++j) {
-        const int c = 2 * j + (m >> 1);
-        uint32_t b[4];
-        dk_ldmatrix_x4_trans(b, tile_s + key * 128 + ((c ^ (key & 7)) << 4));
-        dk_mma_16816(acc[2 * j], a0, 0u, a2, 0u, b[0], b[1]);
-        dk_mma_16816(acc[2 * j + 1], a0, 0u, a2, 0u, b[2], b[3]);
-      }
-      __syncwarp();
-      fetch_block(blk + 8 * NVB, buf);
-    }
-    dk_cp_async_wait<0>();
-  }
-  cbar_sync();
-  if (r < DK_MAX_QPK) {
-#pragma unroll
-    for (int nb = 0; nb < 8; ++nb)
-      *reinterpret_cast<float2*>(spart + (warp * 8 + r) * DK_HD + 8 * nb + 2 * q) = make_float2(acc[nb][0], acc[nb][1]);
-  }
-  cbar_sync();
+  // ---- merge the warps' partial results and the new key ----
   for (int i = tid; i < DK_MAX_QPK * DK_HD; i += DK_CTHREADS) {
-    float a = 0.f;
+    const int h = i >> 6, d = i & 63;
+    if (h < qpk) {
+      const float sn = sc->snew[h];
+      float M = sn;
 #pragma unroll
-    for (int w = 0; w < 8; ++w) a += spart[w * 8 * DK_HD + i];
-    sout[i] = a * sinv[i >> 6];
+      for (int w = 0; w < DK_CWARPS; ++w) M = fmaxf(M, sc->pm[w][h]);
+      const float en = exp2f(sn - M);
+      float num = en * sc->vnew[d], den = en;
+#pragma unroll
+      for (int w = 0; w < DK_CWARPS; ++w) {
+        const float e = exp2f(sc->pm[w][h] - M);
+        num += e * sc->part[w][h][d];
+        den += e * sc->pl[w][h];
+      }
+      sc->sout[h][d] = num / den;
+    }
   }
   cbar_sync();
   if (warp < qpk) {
     float pfx0 = 0.f, pfx1 = 0.f;
     if (prefix_len > 0) {
       float ps[DK_MAX_PREFIX];
-      float pm = -INFINITY;
+      float pmx = -INFINITY;
 #pragma unroll
       for (int a = 0; a < DK_MAX_PREFIX; ++a) {
         ps[a] = -INFINITY;
         if (a < prefix_len) {
-          ps[a] = warp_sum(q0 * __bfloat162float(spfx[a * 128 + lane]) + q1 * __bfloat162float(spfx[a * 128 + lane + 32]));
-          pm = fmaxf(pm, ps[a]);
+          ps[a] = warp_sum(q0 * __bfloat162float(sc->spfx[a][lane]) + q1 * __bfloat162float(sc->spfx[a][lane + 32]));
+          pmx = fmaxf(pmx, ps[a]);
         }
       }
       float psum = 0.f;
 #pragma unroll
       for (int a = 0; a < DK_MAX_PREFIX; ++a) {
-        ps[a] = (a < prefix_len) ? __expf(ps[a] - pm) : 0.f;
+        ps[a] = (a < prefix_len) ? __expf(ps[a] - pmx) : 0.f;
         psum += ps[a];
       }
       const float gs = gate_h / psum;
 #pragma unroll
       for (int a = 0; a < DK_MAX_PREFIX; ++a) {
         if (a < prefix_len) {
-          pfx0 += gs * ps[a] * __bfloat162float(spfx[a * 128 + 64 + lane]);
-          pfx1 += gs * ps[a] * __bfloat162float(spfx[a * 128 + 96 + lane]);
+          pfx0 += gs * ps[a] * __bfloat162float(sc->spfx[a][64 + lane]);
+          pfx1 += gs * ps[a] * __bfloat162float(sc->spfx[a][96 + lane]);
         }
       }
     }
     const int h = g * qpk + warp;
-    const float o0 = sout[warp * DK_HD + lane] + pfx0, o1 = sout[warp * DK_HD + lane + 32] + pfx1;
-    bf16* orow = p->y + (long long)seq * H * DK_HD + h * DK_HD;
+    const float o0 = sc->sout[warp][lane] + pfx0, o1 = sc->sout[warp][lane + 32] + pfx1;
+    bf16* orow = p->y + (long long)seq * (G * qpk) * DK_HD + h * DK_HD;
     orow[lane] = __float2bfloat16_rn(o0);
     orow[lane + 32] = __float2bfloat16_rn(o1);
   }
-  cbar_sync();      // the shared-memory region is re-used by the next item
+  cbar_sync();      // the scratch is re-used by the next item
 }
 
 // ---------------------------------------------------------------------------------------------
 // consumer stages
 // ---------------------------------------------------------------------------------------------
-// row `row`: x_out = resid + bf16(sum of the GEMM's partial tiles), y = rmsnorm(x_out) * w  (256 threads, C <= 8192)
-__device__ __forceinline__ void resid_norm_row(const DecodePlan* p, const Phase& ph, int row, const float* resid, float* x_out, bf16* y,
+// row `row`: x_out = resid + bf16(sum of the GEMM's partial tiles), y = rmsnorm(x_out) * w  (256 threads, C <= 4096)
+__device__ __forceinline__ void resid_norm_row(const DecodePlan* p, int gemm, int row, const float* resid, float* x_out, bf16* y,
                                                const float* w, float* red, int tid) {
-  const int C = p->C, P = p->n_ctas;
-  float v[4][8];
+  const Phase ph = get_phase(p, gemm);
+  const int C = p->C;
+  float v[2][8];
   float ss = 0.f;
 #pragma unroll
-  for (int rep = 0; rep < 4; ++rep) {
+  for (int rep = 0; rep < 2; ++rep) {
     const int c0 = rep * 2048 + tid * 8;
     if (c0 < C) {
       const int tile = c0 >> 7, within = c0 & 127;
-      const int first = unit_owner(ph.units, tile * ph.nkb, P), last = unit_owner(ph.units, (tile + 1) * ph.nkb - 1, P);
-      const float* base = p->ws + ((size_t)tile * ph.maxseg * 128 + row) * 128 + within;
-      float acc[8];
-#pragma unroll
-      for (int i = 0; i < 8; ++i) acc[i] = 0.f;
-      for (int s = 0; s <= last - first; ++s) {
-        const float4 a = __ldcg(reinterpret_cast<const float4*>(base + (size_t)s * 128 * 128));
-        const float4 b = __ldcg(reinterpret_cast<const float4*>(base + (size_t)s * 128 * 128 + 4));
-        acc[0] += a.x; acc[1] += a.y; acc[2] += a.z; acc[3] += a.w; acc[4] += b.x; acc[5] += b.y; acc[6] += b.z; acc[7] += b.w;
-      }
+      float4 s0, s1;
+      sum_slices2(p->ws + ((size_t)tile * ph.maxseg * 128 + row) * 128 + within, 4, tile_segments(ph, tile), s0, s1);
+      const float acc[8] = {s0.x, s0.y, s0.z, s0.w, s1.x, s1.y, s1.z, s1.w};
       const float4 r0 = __ldcg(reinterpret_cast<const float4*>(resid + (size_t)row * C + c0));
       const float4 r1 = __ldcg(reinterpret_cast<const float4*>(resid + (size_t)row * C + c0 + 4));
       const float rr[8] = {r0.x, r0.y, r0.z, r0.w, r1.x, r1.y, r1.z, r1.w};
@@ -418,8 +424,8 @@ __device__ __forceinline__ void resid_norm_row(const DecodePlan* p, const Phase&
         v[rep][i] = rr[i] + bf16_round(acc[i]);
         ss += v[rep][i] * v[rep][i];
       }
-      *reinterpret_cast<float4*>(x_out + (size_t)row * C + c0) = make_float4(v[rep][0], v[rep][1], v[rep][2], v[rep][3]);
-      *reinterpret_cast<float4*>(x_out + (size_t)row * C + c0 + 4) = make_float4(v[rep][4], v[rep][5], v[rep][6], v[rep][7]);
+      __stcg(reinterpret_cast<float4*>(x_out + (size_t)row * C + c0), make_float4(v[rep][0], v[rep][1], v[rep][2], v[rep][3]));
+      __stcg(reinterpret_cast<float4*>(x_out + (size_t)row * C + c0 + 4), make_float4(v[rep][4], v[rep][5], v[rep][6], v[rep][7]));
     }
   }
   ss = warp_sum(ss);
@@ -431,7 +437,7 @@ __device__ __forceinline__ void resid_norm_row(const DecodePlan* p, const Phase&
   for (int i = 0; i < DK_CWARPS; ++i) tot += red[i];
   const float rs = rsqrtf(tot / (float)C + p->eps);
 #pragma unroll
-  for (int rep = 0; rep < 4; ++rep) {
+  for (int rep = 0; rep < 2; ++rep) {
     const int c0 = rep * 2048 + tid * 8;
     if (c0 < C) {
       const float4 g0 = *reinterpret_cast<const float4*>(w + c0), g1 = *reinterpret_cast<const float4*>(w + c0 + 4);
@@ -445,46 +451,55 @@ __device__ __forceinline__ void resid_norm_row(const DecodePlan* p, const Phase&
 }
 
 // act[row, 64 t + 32 b' ...] = silu(h1) * h2 over the fc_1|fc_2 GEMM's partial tiles; columns are [fc_1 x32 | fc_2 x32] blocks
-__device__ __forceinline__ void swiglu_stage(const DecodePlan* p, const Phase& ph, int tid) {
+__device__ __forceinline__ void swiglu_stage(const DecodePlan* p, int tid) {
+  const Phase ph = get_phase(p, 2);
   const int P = p->n_ctas, I = p->I;
   const int per_row = ph.tiles * 2 * 8;                 // (tile, 64-column block, 4-column group)
   const int total = p->n_seq * per_row;
-  for (int e = blockIdx.x * DK_CTHREADS + tid; e < total; e += P * DK_CTHREADS) {
-    const int row = e / per_row, rem = e % per_row;
-    const int tile = rem >> 4, blk = (rem >> 3) & 1, j = (rem & 7) * 4;
-    const int first = unit_owner(ph.units, tile * ph.nkb, P), last = unit_owner(ph.units, (tile + 1) * ph.nkb - 1, P);
-    const float* base = p->ws + ((size_t)tile * ph.maxseg * 128 + row) * 128 + blk * 64 + j;
-    float4 h1 = make_float4(0.f, 0.f, 0.f, 0.f), h2 = h1;
-    for (int s = 0; s <= last - first; ++s) {
-      const float4 a = __ldcg(reinterpret_cast<const float4*>(base + (size_t)s * 128 * 128));
-      const float4 b = __ldcg(reinterpret_cast<const float4*>(base + (size_t)s * 128 * 128 + 32));
-      h1.x += a.x; h1.y += a.y; h1.z += a.z; h1.w += a.w;
-      h2.x += b.x; h2.y += b.y; h2.z += b.z; h2.w += b.w;
-    }
-    const float a1[4] = {h1.x, h1.y, h1.z, h1.w}, a2[4] = {h2.x, h2.y, h2.z, h2.w};
-    float o[4];
+  const int stride = P * DK_CTHREADS;
+  for (int e0 = blockIdx.x * DK_CTHREADS + tid; e0 < total; e0 += 2 * stride) {
+    float4 h1[2], h2[2];
+    int rows[2], cols[2];
 #pragma unroll
-    for (int i = 0; i < 4; ++i) {
-      const float u = bf16_round(a1[i]), g = bf16_round(a2[i]);
-      o[i] = (u / (1.f + __expf(-u))) * g;
+    for (int k = 0; k < 2; ++k) {                       // two elements in flight per thread
+      const int e = e0 + k * stride;
+      rows[k] = -1;
+      if (e < total) {
+        const int row = e / per_row, rem = e % per_row;
+        const int tile = rem >> 4, blk = (rem >> 3) & 1, j = (rem & 7) * 4;
+        rows[k] = row;
+        cols[k] = tile * 64 + blk * 32 + j;
+        sum_slices2(p->ws + ((size_t)tile * ph.maxseg * 128 + row) * 128 + blk * 64 + j, 32, tile_segments(ph, tile), h1[k], h2[k]);
+      }
     }
-    *reinterpret_cast<uint2*>(p->act + (size_t)row * I + tile * 64 + blk * 32 + j) = make_uint2(pack_bf16x2(o[0], o[1]), pack_bf16x2(o[2], o[3]));
+#pragma unroll
+    for (int k = 0; k < 2; ++k) {
+      if (rows[k] >= 0) {
+        const float a1[4] = {h1[k].x, h1[k].y, h1[k].z, h1[k].w}, a2[4] = {h2[k].x, h2[k].y, h2[k].z, h2[k].w};
+        float o[4];
+#pragma unroll
+        for (int i = 0; i < 4; ++i) {
+          const float u = bf16_round(a1[i]), g = bf16_round(a2[i]);
+          o[i] = (u / (1.f + __expf(-u))) * g;
+        }
+        *reinterpret_cast<uint2*>(p->act + (size_t)rows[k] * I + cols[k]) = make_uint2(pack_bf16x2(o[0], o[1]), pack_bf16x2(o[2], o[3]));
+      }
+    }
   }
 }
 
 // ---------------------------------------------------------------------------------------------
 // the kernel
 // ---------------------------------------------------------------------------------------------
-template <int NVB>
+template <bool TRACE>
 __global__ void __launch_bounds__(DK_THREADS, 1) decode_layers_kernel(const DecodePlan* __restrict__ plan) {
   extern __shared__ uint8_t smem_raw[];
   uint8_t* smem = reinterpret_cast<uint8_t*>((reinterpret_cast<uintptr_t>(smem_raw) + 1023) & ~uintptr_t(1023));
-  uint8_t* wring = smem;                                          // [W_STAGES][16 KB]
-  uint8_t* aring = smem + DK_W_STAGES * DK_TILE_BYTES;            // [A_STAGES][16 KB]; the attention stage re-uses this region and beyond
-  const DecodePlan* p = plan;
-  const int att_bytes = dk_att_fixed_bytes(NVB) + p->qpk * (p->max_len + 20) * 4;
-  const int region = att_bytes > DK_A_STAGES * DK_TILE_BYTES ? att_bytes : DK_A_STAGES * DK_TILE_BYTES;
-  uint64_t* bars = reinterpret_cast<uint64_t*>(aring + ((region + 127) & ~127));
+  uint8_t* wring = smem;                                          // [W_STAGES][16 KB] weight tiles
+  uint8_t* aring = smem + DK_W_STAGES * DK_TILE_BYTES;            // [A_STAGES][16 KB] activation boxes / K+V chunks
+  uint8_t* stg = aring + DK_A_STAGES * DK_TILE_BYTES;             // 32 KB: drain transpose staging / attention scratch
+  const DecodePlan* gp = plan;                                    // global copy: the tensor maps TMA reads
+  uint64_t* bars = reinterpret_cast<uint64_t*>(stg + DK_STG_BYTES);
   uint64_t* w_full = bars;                        // [W_STAGES]
   uint64_t* w_empty = bars + DK_W_STAGES;         // [W_STAGES]
   uint64_t* a_full = bars + 2 * DK_W_STAGES;      // [A_STAGES]
@@ -494,18 +509,30 @@ __global__ void __launch_bounds__(DK_THREADS, 1) decode_layers_kernel(const Deco
   uint32_t* tmem_slot = reinterpret_cast<uint32_t*>(tempty + 2);
   int* phase_go = reinterpret_cast<int*>(tmem_slot + 1);
   float* red = reinterpret_cast<float*>(tmem_slot + 4);           // [8]
+  uint32_t* slot_done = reinterpret_cast<uint32_t*>(red + 8);     // [A_STAGES] ring index + 1 of the last K/V chunk released per stage
+  // shared-memory copies of the plan header and of every layer's pointers (see LayerPtrs)
+  DecodePlan* sp = reinterpret_cast<DecodePlan*>(reinterpret_cast<uint8_t*>(bars) + 512);
+  LayerPtrs* slp = reinterpret_cast<LayerPtrs*>(sp + 1);
+  const DecodeLayer* layers = reinterpret_cast<const DecodeLayer*>(gp + 1);
+  {
+    const int n_layer_g = gp->n_layer;
+    for (int i = threadIdx.x; i < (int)(sizeof(DecodePlan) / 16); i += DK_THREADS)
+      reinterpret_cast<uint4*>(sp)[i] = reinterpret_cast<const uint4*>(gp)[i];
+    for (int i = threadIdx.x; i < n_layer_g * 6; i += DK_THREADS)
+      reinterpret_cast<uint64_t*>(slp)[i] = *reinterpret_cast<const uint64_t*>(reinterpret_cast<const uint8_t*>(layers + i / 6) + offsetof(DecodeLayer, norm2) + (i % 6) * 8);
+  }
+  const DecodePlan* p = sp;
 
   const int warp = __shfl_sync(0xffffffffu, threadIdx.x >> 5, 0);
   const int lane = threadIdx.x & 31;
-  const int cta = blockIdx.x, P = p->n_ctas;
-  const int n_layer = p->n_layer;
-  const DecodeLayer* layers = reinterpret_cast<const DecodeLayer*>(p + 1);
+  const int cta = blockIdx.x;
 
   if (threadIdx.x == 0) {
     for (int i = 0; i < DK_W_STAGES; ++i) { mbar_init(&w_full[i], 1); mbar_init(&w_empty[i], 1); }
     for (int i = 0; i < DK_A_STAGES; ++i) { mbar_init(&a_full[i], 1); mbar_init(&a_empty[i], 1); }
     for (int i = 0; i < 2; ++i) { mbar_init(&tfull[i], 1); mbar_init(&tempty[i], DK_CWARPS); }
     *phase_go = 0;
+    for (int i = 0; i < DK_A_STAGES; ++i) slot_done[i] = 0;
     fence_barrier_init();
   }
   if (warp == DK_CWARPS + 2) { tmem_alloc(tmem_slot, 256); tmem_relinquish(); }
@@ -513,6 +540,13 @@ __global__ void __launch_bounds__(DK_THREADS, 1) decode_layers_kernel(const Deco
   __syncthreads();
   tc_fence_after();
   const uint32_t tmem_base = __shfl_sync(0xffffffffu, *tmem_slot, 0);
+  const int P = p->n_ctas;
+  const int n_layer = p->n_layer;
+  const int n_items = p->n_seq * p->G;
+
+  // K/V chunks this CTA streams per layer (its attention items are the same in every layer)
+  int my_chunks = 0;
+  for (int item = cta; item < n_items; item += P) my_chunks += (__ldg(p->positions + item / p->G) + DK_KV_KEYS - 1) / DK_KV_KEYS;
 
   if (warp == DK_CWARPS) {
     // ===================== weight producer: never waits for a grid barrier =====================
@@ -520,40 +554,59 @@ __global__ void __launch_bounds__(DK_THREADS, 1) decode_layers_kernel(const Deco
       uint32_t it = 0;
       for (int l = 0; l < n_layer; ++l) {
         for (int g = 0; g < 4; ++g) {
-          const Phase ph = get_phase(p, layers + l, g);
-          const int u0 = unit_lo(ph.units, cta, P), u1 = unit_lo(ph.units, cta + 1, P);
+          const Phase ph = get_phase(p, g);
+          const CUtensorMap* wmap = weight_map(layers + l, g);
+          const int u0 = unit_lo(ph.units, cta, ph.P), u1 = unit_lo(ph.units, cta + 1, ph.P);
           for (int u = u0; u < u1; ++u, ++it) {
             const int s = it % DK_W_STAGES;
             mbar_wait(&w_empty[s], ((it / DK_W_STAGES) & 1) ^ 1);
             mbar_expect_tx(&w_full[s], DK_TILE_BYTES);
-            tma_load_2d(wring + s * DK_TILE_BYTES, ph.w, (u % ph.nkb) * 64, (u / ph.nkb) * 128, &w_full[s]);
+            tma_load_2d(wring + s * DK_TILE_BYTES, wmap, (u % ph.nkb) * 64, (u / ph.nkb) * 128, &w_full[s]);
           }
         }
       }
     }
   } else if (warp == DK_CWARPS + 1) {
-    // ===================== activation producer: a stage's A boxes once its input exists =====================
+    // ===================== activation producer: a stage's A boxes once its input exists; K/V chunks as soon as the ring is free ==========
     if (lane == 0) {
       uint32_t it = 0;
       for (int l = 0; l < n_layer; ++l) {
+        const DecodeLayer* L = layers + l;
         for (int g = 0; g < 4; ++g) {
-          const Phase ph = get_phase(p, layers + l, g);
-          const int u0 = unit_lo(ph.units, cta, P), u1 = unit_lo(ph.units, cta + 1, P);
-          if (u0 == u1) continue;
-          const int need = l * 4 + g + 1;
-          if (ld_volatile_shared(phase_go) < need) {
-            const uint64_t t0 = globaltimer_ns();
-            uint32_t spins = 0;
-            while (ld_volatile_shared(phase_go) < need) {
-              if (((++spins) & 0x3FF) == 0 && globaltimer_ns() - t0 > DH_HANG_GUARD_NS) dk_hang("activation producer", need, 0);
+          const Phase ph = get_phase(p, g);
+          const CUtensorMap* amap = act_map(gp, g);
+          const int u0 = unit_lo(ph.units, cta, ph.P), u1 = unit_lo(ph.units, cta + 1, ph.P);
+          if (u0 < u1) {
+            const int need = l * 4 + g + 1;
+            if (ld_volatile_shared(phase_go) < need) {
+              const uint64_t t0 = globaltimer_ns();
+              uint32_t spins = 0;
+              while (ld_volatile_shared(phase_go) < need) {
+                if (((++spins) & 0x3FF) == 0 && globaltimer_ns() - t0 > DH_HANG_GUARD_NS) dk_hang("activation producer", need, 0);
+              }
+            }
+            fence_proxy_async_all();        // the activations were written through the generic proxy by other SMs
+            for (int u = u0; u < u1; ++u, ++it) {
+              const int s = it % DK_A_STAGES;
+              mbar_wait(&a_empty[s], ((it / DK_A_STAGES) & 1) ^ 1);
+              mbar_expect_tx(&a_full[s], DK_TILE_BYTES);
+              tma_load_2d(aring + s * DK_TILE_BYTES, amap, (u % ph.nkb) * 64, 0, &a_full[s]);
             }
           }
-          fence_proxy_async_all();        // the activations were written through the generic proxy by other SMs
-          for (int u = u0; u < u1; ++u, ++it) {
-            const int s = it % DK_A_STAGES;
-            mbar_wait(&a_empty[s], ((it / DK_A_STAGES) & 1) ^ 1);
-            mbar_expect_tx(&a_full[s], DK_TILE_BYTES);
-            tma_load_2d(aring + s * DK_TILE_BYTES, ph.a, (u % ph.nkb) * 64, 0, &a_full[s]);
+          if (g == 0) {
+            // the cached keys of this CTA's attention items (written by earlier launches: no dependency on this step)
+            for (int item = cta; item < n_items; item += P) {
+              const int seq = item / p->G, kg = item % p->G;
+              const int pos = __ldg(p->positions + seq);
+              const int row0 = (seq * p->G + kg) * p->max_len;
+              for (int c = 0; c * DK_KV_KEYS < pos; ++c, ++it) {
+                const int s = it % DK_A_STAGES;
+                mbar_wait(&a_empty[s], ((it / DK_A_STAGES) & 1) ^ 1);
+                mbar_expect_tx(&a_full[s], DK_TILE_BYTES);
+                tma_load_2d(aring + s * DK_TILE_BYTES, &L->kmap, 0, row0 + c * DK_KV_KEYS, &a_full[s]);
+                tma_load_2d(aring + s * DK_TILE_BYTES + DK_KV_KEYS * 128, &L->vmap, 0, row0 + c * DK_KV_KEYS, &a_full[s]);
+              }
+            }
           }
         }
       }
@@ -561,12 +614,25 @@ __global__ void __launch_bounds__(DK_THREADS, 1) decode_layers_kernel(const Deco
   } else if (warp == DK_CWARPS + 2) {
     // ===================== MMA issuer (whole warp walks the loop, one elected lane issues) =====================
     constexpr uint32_t idesc = umma_idesc_bf16(128, 128, 0, 0);
-    uint32_t it = 0, seg = 0;
+    uint32_t wit = 0, ait = 0, seg = 0;
     for (int l = 0; l < n_layer; ++l) {
       for (int g = 0; g < 4; ++g) {
-        const Phase ph = get_phase(p, layers + l, g);
-        const int u0 = unit_lo(ph.units, cta, P), u1 = unit_lo(ph.units, cta + 1, P);
-        for (int u = u0; u < u1; ++u, ++it) {
+        const Phase ph = get_phase(p, g);
+        const int u0 = unit_lo(ph.units, cta, ph.P), u1 = unit_lo(ph.units, cta + 1, ph.P);
+        if (u0 < u1) {
+          // A parity wait may look at most ONE phase ahead, and the attention stage's K/V chunks cycle through the same ring
+          // slots between the QKV and the proj GEMM: do not touch a_full before the compute warps have opened this stage
+          // (by then every earlier use of the ring has completed).
+          const int need = l * 4 + g + 1;
+          if (ld_volatile_shared(phase_go) < need) {
+            const uint64_t t0 = globaltimer_ns();
+            uint32_t spins = 0;
+            while (ld_volatile_shared(phase_go) < need) {
+              if (((++spins) & 0x3FF) == 0 && globaltimer_ns() - t0 > DH_HANG_GUARD_NS) dk_hang("mma issuer", need, 0);
+            }
+          }
+        }
+        for (int u = u0; u < u1; ++u, ++wit, ++ait) {
           const int kb = u % ph.nkb;
           const bool first = (u == u0) || kb == 0, last = (u == u1 - 1) || kb == ph.nkb - 1;
           const int acc = seg & 1;
@@ -574,9 +640,9 @@ __global__ void __launch_bounds__(DK_THREADS, 1) decode_layers_kernel(const Deco
             mbar_wait(&tempty[acc], ((seg >> 1) & 1) ^ 1);
             tc_fence_after();
           }
-          const int ws = it % DK_W_STAGES, as = it % DK_A_STAGES;
-          mbar_wait(&w_full[ws], (it / DK_W_STAGES) & 1);
-          mbar_wait(&a_full[as], (it / DK_A_STAGES) & 1);
+          const int ws = wit % DK_W_STAGES, as = ait % DK_A_STAGES;
+          mbar_wait(&w_full[ws], (wit / DK_W_STAGES) & 1);
+          mbar_wait(&a_full[as], (ait / DK_A_STAGES) & 1);
           tc_fence_after();
           const uint32_t sa = smem_u32(aring + as * DK_TILE_BYTES), sb = smem_u32(wring + ws * DK_TILE_BYTES);
           const uint32_t d_tmem = tmem_base + acc * 128;
@@ -591,6 +657,7 @@ __global__ void __launch_bounds__(DK_THREADS, 1) decode_layers_kernel(const Deco
           __syncwarp();
           if (last) ++seg;
         }
+        if (g == 0) ait += my_chunks;          // the attention stage's K/V chunks pass through the same ring
       }
     }
   } else {
@@ -600,15 +667,20 @@ __global__ void __launch_bounds__(DK_THREADS, 1) decode_layers_kernel(const Deco
     const unsigned long long gen = ld_acquire_u64(bar + 1);
     const unsigned long long nb_per_launch = (unsigned long long)n_layer * 8 - 1;     // layer 0 has no barrier in front of its QKV GEMM
     unsigned long long bcount = gen * nb_per_launch;                 // barriers completed before this launch
-    uint32_t seg = 0;
+    uint32_t seg = 0, ait = 0;
     const int q4 = warp & 3, half = warp >> 2;
+    long long t_first_full = 0;
+    AttScratch* sc = reinterpret_cast<AttScratch*>(stg);
+    float* stgw = reinterpret_cast<float*>(stg) + warp * 1024;       // this warp's [32][32] transpose tile
 
-    // drain this CTA's partial tiles of one GEMM stage: TMEM -> fp32 slices in the workspace
+    // drain this CTA's partial tiles of one GEMM stage: TMEM -> (shared-memory transpose) -> fp32 slices in the workspace, so
+    // that every store instruction of a warp writes 128 contiguous bytes of one row
     auto drain = [&](const Phase& ph, int stage_index) {
       if (tid == 0) {
         asm volatile("st.volatile.shared.s32 [%0], %1;" ::"r"(smem_u32(phase_go)), "r"(stage_index + 1) : "memory");
       }
-      const int u0 = unit_lo(ph.units, cta, P), u1 = unit_lo(ph.units, cta + 1, P);
+      const int u0 = unit_lo(ph.units, cta, ph.P), u1 = unit_lo(ph.units, cta + 1, ph.P);
+      ait += u1 - u0;
       int u = u0;
       while (u < u1) {
         const int tile = u / ph.nkb;
@@ -616,59 +688,95 @@ __global__ void __launch_bounds__(DK_THREADS, 1) decode_layers_kernel(const Deco
         const int acc = seg & 1;
         mbar_wait(&tfull[acc], (seg >> 1) & 1);
         tc_fence_after();
-        uint32_t r0[32], r1[32];
-        const uint32_t taddr = tmem_base + ((uint32_t)(q4 * 32) << 16) + acc * 128 + half * 64;
-        tmem_ld32(taddr, r0);
-        tmem_ld32(taddr + 32, r1);
-        tmem_wait_ld();
-        tc_fence_before();
-        __syncwarp();
-        if (lane == 0) mbar_arrive(&tempty[acc]);
-        const int row = q4 * 32 + lane;
-        if (row < p->n_seq) {
-          const int sidx = cta - unit_owner(ph.units, tile * ph.nkb, P);
-          float4* dst = reinterpret_cast<float4*>(p->ws + (((size_t)tile * ph.maxseg + sidx) * 128 + row) * 128 + half * 64);
+        if (TRACE && u == u0 && tid == 0) t_first_full = (long long)globaltimer_ns();
+        const int sidx = cta - unit_owner(ph.units, tile * ph.nkb, ph.P);
+        float* dst = p->ws + (((size_t)tile * ph.maxseg + sidx) * 128 + q4 * 32) * 128 + half * 64 + lane;
+        const int nrow = p->n_seq - q4 * 32;                       // valid rows of this warp's 32-row block
 #pragma unroll
-          for (int i = 0; i < 8; ++i) {
-            dst[i] = make_float4(__uint_as_float(r0[4 * i]), __uint_as_float(r0[4 * i + 1]), __uint_as_float(r0[4 * i + 2]), __uint_as_float(r0[4 * i + 3]));
-            dst[8 + i] = make_float4(__uint_as_float(r1[4 * i]), __uint_as_float(r1[4 * i + 1]), __uint_as_float(r1[4 * i + 2]), __uint_as_float(r1[4 * i + 3]));
+        for (int h2 = 0; h2 < 2; ++h2) {
+          uint32_t rg[32];
+          tmem_ld32(tmem_base + ((uint32_t)(q4 * 32) << 16) + acc * 128 + half * 64 + h2 * 32, rg);
+          tmem_wait_ld();
+          if (h2 == 1) {
+            tc_fence_before();
+            __syncwarp();
+            if (lane == 0) mbar_arrive(&tempty[acc]);              // the accumulator may be overwritten
           }
+#pragma unroll
+          for (int i = 0; i < 32; ++i) stgw[lane * 32 + (i ^ lane)] = __uint_as_float(rg[i]);
+          __syncwarp();
+#pragma unroll 8
+          for (int rr = 0; rr < 32; ++rr) {
+            if (rr < nrow) __stcg(dst + (size_t)rr * 128 + h2 * 32, stgw[rr * 32 + (lane ^ rr)]);
+          }
+          __syncwarp();
         }
         ++seg;
         u = end;
       }
     };
 
+    // developer trace (DH_DECODE_TRACE=1): [3 CTAs][n_layer][24] stage stamps, then [8 barriers][P][2] arrive / release of layer 5
+    long long* trace = TRACE ? p->trace : nullptr;
+    long long* tr_bar = trace ? trace + (size_t)3 * n_layer * DK_TRACE_SLOTS : nullptr;
+    if (trace && !(cta == 0 || cta == P / 2 || cta == P - 1)) trace = nullptr;
+    if (trace) trace += (size_t)(cta == 0 ? 0 : cta == P - 1 ? 2 : 1) * n_layer * DK_TRACE_SLOTS;
+    auto stamp = [&](int l, int i) {
+      if (TRACE && trace && tid == 0) trace[l * DK_TRACE_SLOTS + i] = (long long)globaltimer_ns();
+    };
+    auto gbar = [&](int l, int b) {
+      const bool rec = TRACE && tr_bar && tid == 0 && l == (n_layer > 5 ? 5 : n_layer - 1);
+      if (rec) tr_bar[((size_t)b * P + cta) * 2] = (long long)globaltimer_ns();
+      grid_barrier(bar, (++bcount) * P);
+      if (rec) tr_bar[((size_t)b * P + cta) * 2 + 1] = (long long)globaltimer_ns();
+    };
     for (int l = 0; l < n_layer; ++l) {
-      const DecodeLayer* L = layers + l;
-      const Phase g0 = get_phase(p, L, 0), g1 = get_phase(p, L, 1), g2 = get_phase(p, L, 2), g3 = get_phase(p, L, 3);
+      const LayerPtrs* L = slp + l;
+      stamp(l, 0);
       // ---- QKV GEMM (input: n) ----
-      if (l > 0) grid_barrier(bar, (++bcount) * P);      // layer 0's input was written before the launch
-      drain(g0, l * 4 + 0);
-      grid_barrier(bar, (++bcount) * P);
+      if (l > 0) gbar(l, 0);      // layer 0's input was written before the launch
+      stamp(l, 1);
+      drain(get_phase(p, 0), l * 4 + 0);
+      if (TRACE && trace && tid == 0) trace[l * DK_TRACE_SLOTS + 2] = t_first_full;
+      stamp(l, 3);
+      gbar(l, 1);
+      stamp(l, 4);
       // ---- attention over the KV cache: items (sequence, kv group) ----
-      for (int item = cta; item < p->n_seq * p->G; item += P) {
+      for (int item = cta; item < n_items; item += P) {
         const int seq = item / p->G, g = item % p->G;
-        const int pos = __ldcg(p->positions + seq);
-        qkv_reduce_rope_cache(p, L, g0, seq, g, pos, tid);
-        __threadfence_block();
-        cbar_sync();
-        attention_item<NVB>(p, L, aring, seq, g, pos + 1, tid);
+        attention_item(p, L, aring, sc, a_full, a_empty, slot_done, ait, seq, g, __ldg(p->positions + seq), tid);
+        if (item == cta) stamp(l, 5);
       }
-      grid_barrier(bar, (++bcount) * P);
+      stamp(l, 6);
+      gbar(l, 2);
+      stamp(l, 7);
       // ---- attention output projection ----
-      drain(g1, l * 4 + 1);
-      grid_barrier(bar, (++bcount) * P);
-      if (cta < p->n_seq) resid_norm_row(p, g1, cta, p->x, p->x2, p->n, L->norm2, red, tid);
-      grid_barrier(bar, (++bcount) * P);
+      drain(get_phase(p, 1), l * 4 + 1);
+      if (TRACE && trace && tid == 0) trace[l * DK_TRACE_SLOTS + 8] = t_first_full;
+      stamp(l, 9);
+      gbar(l, 3);
+      stamp(l, 10);
+      if (cta < p->n_seq) resid_norm_row(p, 1, cta, p->x, p->x2, p->n, L->norm2, red, tid);
+      stamp(l, 11);
+      gbar(l, 4);
+      stamp(l, 12);
       // ---- MLP ----
-      drain(g2, l * 4 + 2);
-      grid_barrier(bar, (++bcount) * P);
-      swiglu_stage(p, g2, tid);
-      grid_barrier(bar, (++bcount) * P);
-      drain(g3, l * 4 + 3);
-      grid_barrier(bar, (++bcount) * P);
-      if (cta < p->n_seq) resid_norm_row(p, g3, cta, p->x2, p->x, l + 1 == n_layer ? p->hidden : p->n, L->norm_next, red, tid);
+      drain(get_phase(p, 2), l * 4 + 2);
+      if (TRACE && trace && tid == 0) trace[l * DK_TRACE_SLOTS + 13] = t_first_full;
+      stamp(l, 14);
+      gbar(l, 5);
+      stamp(l, 15);
+      swiglu_stage(p, tid);
+      stamp(l, 16);
+      gbar(l, 6);
+      stamp(l, 17);
+      drain(get_phase(p, 3), l * 4 + 3);
+      if (TRACE && trace && tid == 0) trace[l * DK_TRACE_SLOTS + 18] = t_first_full;
+      stamp(l, 19);
+      gbar(l, 7);
+      stamp(l, 20);
+      if (cta < p->n_seq) resid_norm_row(p, 3, cta, p->x2, p->x, l + 1 == n_layer ? p->hidden : p->n, L->norm_next, red, tid);
+      stamp(l, 21);
     }
     if (cta == 0 && tid == 0) {
       __threadfence();
@@ -684,10 +792,8 @@ __global__ void __launch_bounds__(DK_THREADS, 1) decode_layers_kernel(const Deco
   }
 }
 
-static size_t decode_smem_bytes(int nvb, int qpk, int max_len) {
-  const int att = dk_att_fixed_bytes(nvb) + qpk * (max_len + 20) * 4;
-  const int region = att > DK_A_STAGES * DK_TILE_BYTES ? att : DK_A_STAGES * DK_TILE_BYTES;
-  return (size_t)DK_W_STAGES * DK_TILE_BYTES + ((region + 127) & ~127) + 512 + 1024;
+static size_t decode_smem_bytes() {
+  return (size_t)(DK_W_STAGES + DK_A_STAGES) * DK_TILE_BYTES + DK_STG_BYTES + 512 + sizeof(DecodePlan) + DK_MAX_LAYERS * sizeof(LayerPtrs) + 1024;
 }
 
 static int make_kmajor_map(CUtensorMap* map, const void* base, long long ld, long long rows, long long k) {
@@ -711,9 +817,10 @@ extern "C" size_t dh_decode_workspace_bytes(const dh_decode_desc* d) {
   size_t best = 0;
   for (int g = 0; g < 4; ++g) {
     const int units = tiles[g] * nkb[g];
+    const int Pg = units < P ? units : P;
     int maxseg = 1;
     for (int t = 0; t < tiles[g]; ++t) {
-      const int c = unit_owner(units, (t + 1) * nkb[g] - 1, P) - unit_owner(units, t * nkb[g], P) + 1;
+      const int c = unit_owner(units, (t + 1) * nkb[g] - 1, Pg) - unit_owner(units, t * nkb[g], Pg) + 1;
       if (c > maxseg) maxseg = c;
     }
     const size_t b = (size_t)tiles[g] * maxseg * 128 * 128 * sizeof(float);
@@ -726,7 +833,7 @@ extern "C" int dh_decode_plan_build(const dh_decode_desc* d, void* plan_host) {
   DH_CHECK(d && plan_host && d->layers, "dh_decode_plan_build: null argument");
   DH_CHECK(d->n_layer > 0 && d->n_layer <= DK_MAX_LAYERS, "dh_decode_plan_build: n_layer %d out of range", d->n_layer);
   DH_CHECK(d->n_seq > 0 && d->n_seq <= 128, "dh_decode_plan_build: n_seq %d must be in [1, 128]", d->n_seq);
-  DH_CHECK(d->C % 128 == 0 && d->C <= 8192 && d->I % 64 == 0 && (2 * d->I) % 128 == 0, "dh_decode_plan_build: C %% 128, I %% 64 (C=%d I=%d)", d->C, d->I);
+  DH_CHECK(d->C % 128 == 0 && d->C <= 4096 && d->I % 64 == 0 && (2 * d->I) % 128 == 0, "dh_decode_plan_build: C %% 128, I %% 64 (C=%d I=%d)", d->C, d->I);
   DH_CHECK(d->q_per_kv >= 1 && d->q_per_kv <= DK_MAX_QPK && (d->n_groups * (d->q_per_kv + 2) * 64) % 128 == 0,
            "dh_decode_plan_build: q_per_kv %d / n_groups %d not supported", d->q_per_kv, d->n_groups);
   DH_CHECK(d->prefix_len >= 0 && d->prefix_len <= DK_MAX_PREFIX, "dh_decode_plan_build: prefix_len %d", d->prefix_len);
@@ -734,9 +841,9 @@ extern "C" int dh_decode_plan_build(const dh_decode_desc* d, void* plan_host) {
            "dh_decode_plan_build: null buffer");
   const int P = sm_count();
   DH_CHECK(P > 0, "dh_decode_plan_build: call dh_init first");
-  int nvb = 4;
-  if (decode_smem_bytes(4, d->q_per_kv, d->max_len) > 227 * 1024) nvb = 2;
-  DH_CHECK(decode_smem_bytes(nvb, d->q_per_kv, d->max_len) <= 227 * 1024, "dh_decode_plan_build: max_len %d too long for the score buffer", d->max_len);
+  DH_CHECK(d->max_len > 0 && d->max_len % DK_KV_KEYS == 0, "dh_decode_plan_build: max_len %d must be a multiple of %d (K/V chunks)", d->max_len, DK_KV_KEYS);
+  static_assert((DK_W_STAGES + DK_A_STAGES) * DK_TILE_BYTES + DK_STG_BYTES + 512 + sizeof(DecodePlan) + DK_MAX_LAYERS * sizeof(LayerPtrs) + 1024 <= 227 * 1024,
+                "shared memory budget");
   DH_CHECK(d->ws_bytes >= dh_decode_workspace_bytes(d), "dh_decode_plan_build: workspace too small");
   DecodePlan* p = reinterpret_cast<DecodePlan*>(plan_host);
   memset(p, 0, dh_decode_plan_bytes(d->n_layer));
@@ -746,19 +853,21 @@ extern "C" int dh_decode_plan_build(const dh_decode_desc* d, void* plan_host) {
   if (make_kmajor_map(&p->a_act, d->act, d->I, d->n_seq, d->I)) return -3;
   p->n_layer = d->n_layer; p->n_seq = d->n_seq; p->C = d->C; p->I = d->I; p->G = d->n_groups; p->qpk = d->q_per_kv;
   p->max_len = d->max_len; p->prefix_len = d->prefix_len;
-  p->n_ctas = P; p->nvb = nvb;
+  p->n_ctas = P; p->nvb = 0;
   p->eps = d->eps; p->scale = 1.0f / sqrtf((float)DK_HD);
   p->x = (float*)d->x; p->x2 = (float*)d->x2; p->n = (bf16*)d->n; p->qkv = (bf16*)d->qkv; p->y = (bf16*)d->y; p->act = (bf16*)d->act;
   p->hidden = (bf16*)d->hidden; p->ws = (float*)d->ws; p->positions = d->positions;
   p->rope_cos = (const bf16*)d->rope_cos; p->rope_sin = (const bf16*)d->rope_sin;
   p->bar = (unsigned long long*)d->barrier;
+  p->trace = (long long*)d->trace;
   const int tiles[4] = {qkv_out / 128, d->C / 128, 2 * d->I / 128, d->C / 128};
   const int nkb[4] = {d->C / 64, d->C / 64, d->C / 64, d->I / 64};
   for (int g = 0; g < 4; ++g) {
     const int units = tiles[g] * nkb[g];
+    const int Pg = units < P ? units : P;
     int maxseg = 1;
     for (int t = 0; t < tiles[g]; ++t) {
-      const int c = unit_owner(units, (t + 1) * nkb[g] - 1, P) - unit_owner(units, t * nkb[g], P) + 1;
+      const int c = unit_owner(units, (t + 1) * nkb[g] - 1, Pg) - unit_owner(units, t * nkb[g], Pg) + 1;
       if (c > maxseg) maxseg = c;
     }
     p->maxseg[g] = maxseg;
@@ -771,6 +880,8 @@ extern "C" int dh_decode_plan_build(const dh_decode_desc* d, void* plan_host) {
     if (make_kmajor_map(&L[l].wproj, s->wproj, d->C, d->C, d->C)) return -3;
     if (make_kmajor_map(&L[l].w12, s->w12, d->C, 2 * d->I, d->C)) return -3;
     if (make_kmajor_map(&L[l].wmlp, s->wmlp, d->I, d->C, d->I)) return -3;
+    if (make_kv_cache_map(&L[l].kmap, s->cache_k, (long long)d->n_seq * d->n_groups * d->max_len)) return -3;
+    if (make_kv_cache_map(&L[l].vmap, s->cache_v, (long long)d->n_seq * d->n_groups * d->max_len)) return -3;
     L[l].norm2 = s->norm2; L[l].norm_next = s->norm_next;
     L[l].cache_k = (bf16*)s->cache_k; L[l].cache_v = (bf16*)s->cache_v;
     L[l].prefix_kv = (const bf16*)(d->prefix_len > 0 ? s->prefix_kv : nullptr);
@@ -783,12 +894,12 @@ extern "C" int dh_decode_plan_build(const dh_decode_desc* d, void* plan_host) {
 extern "C" int dh_decode_layers(const void* plan_dev, const void* plan_host, void* stream) {
   DH_CHECK(plan_dev && plan_host, "dh_decode_layers: null plan");
   const DecodePlan* h = reinterpret_cast<const DecodePlan*>(plan_host);
-  const size_t smem = decode_smem_bytes(h->nvb, h->qpk, h->max_len);
+  const size_t smem = decode_smem_bytes();
   static bool attr = false;
   static int coop = -1;
   if (!attr) {
-    DH_CUDA(cudaFuncSetAttribute(decode_layers_kernel<2>, cudaFuncAttributeMaxDynamicSharedMemorySize, 227 * 1024));
-    DH_CUDA(cudaFuncSetAttribute(decode_layers_kernel<4>, cudaFuncAttributeMaxDynamicSharedMemorySize, 227 * 1024));
+    DH_CUDA(cudaFuncSetAttribute(decode_layers_kernel<false>, cudaFuncAttributeMaxDynamicSharedMemorySize, 227 * 1024));
+    DH_CUDA(cudaFuncSetAttribute(decode_layers_kernel<true>, cudaFuncAttributeMaxDynamicSharedMemorySize, 227 * 1024));
     const char* e = getenv("DH_DECODE_COOP");
     coop = (e && e[0] == '0') ? 0 : 1;
     attr = true;
@@ -804,7 +915,7 @@ extern "C" int dh_decode_layers(const void* plan_dev, const void* plan_host, voi
   cfg.attrs = at;
   cfg.numAttrs = coop ? 1 : 0;
   const DecodePlan* pd = reinterpret_cast<const DecodePlan*>(plan_dev);
-  if (h->nvb == 4) DH_CUDA(cudaLaunchKernelEx(&cfg, decode_layers_kernel<4>, pd));
-  else DH_CUDA(cudaLaunchKernelEx(&cfg, decode_layers_kernel<2>, pd));
+  if (h->trace) DH_CUDA(cudaLaunchKernelEx(&cfg, decode_layers_kernel<true>, pd));
+  else DH_CUDA(cudaLaunchKernelEx(&cfg, decode_layers_kernel<false>, pd));
   return 0;
 }

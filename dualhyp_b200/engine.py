@@ -496,21 +496,24 @@ class DecoderEngine:
         return self.forward_hidden(idx, packed, save=False, write_cache=True)
 
     def decode_plan_supported(self, n_seq: int, packed: Dict[int, Dict[str, Tensor]]) -> bool:
-        """The persistent decode kernel covers the base and adapter decoders (a LoRA model decodes through it once merged,
-        generate/lora.py:112 merges before generating; un-merged LoRA factors take the per-GEMM path)."""
+        """The persistent decode kernel (csrc/decode.cu) covers the base and adapter decoders (a LoRA model decodes through it once
+        merged, generate/lora.py:112 merges before generating; un-merged LoRA factors take the per-GEMM path).  OPT-IN
+        (DH_DECODE_MEGA=1): measured on B200 it is slower than the per-GEMM graph (2.39 vs 1.80 ms per token step of 128 sequences,
+        profiles/r02_decode_mega_trace.txt: 8 grid barriers per layer cost 28 us of waiting)."""
         import os
         s = self.spec
-        if os.environ.get("DH_DECODE_MEGA", "1") == "0" or not self.cache_k:
+        if os.environ.get("DH_DECODE_MEGA", "0") != "1" or not self.cache_k:
             return False
         if any(("qkv_a" in d or "proj_a" in d) for d in packed.values()):
             return False
         return (1 <= n_seq <= 128 and s.n_embd % 128 == 0 and s.qkv_out % 128 == 0 and (2 * s.intermediate_size) % 128 == 0
-                and s.qpk <= 8 and s.n_layer <= 64 and self.cache_max_len <= 1536)
+                and s.qpk <= 8 and s.n_layer <= 64 and self.cache_max_len % 64 == 0)
 
     def build_decode_plan(self, n_seq: int, positions: Tensor, packed: Dict[int, Dict[str, Tensor]], pkv_all: Optional[Tensor]):
         """Stage table + TMA descriptors of `dh_decode_layers` for the current cache, the `dec_*` activation buffers of this
         batch size, `positions` (a device tensor whose ADDRESS is baked in) and the packed adapter tensors."""
         import ctypes as C
+        import os
         from . import _lib
         s = self.spec
         Cd, I = s.n_embd, s.intermediate_size
@@ -541,6 +544,10 @@ class DecoderEngine:
         d.positions, d.rope_cos, d.rope_sin, d.barrier = positions.data_ptr(), self.cos.data_ptr(), self.sin.data_ptr(), barrier.data_ptr()
         d.layers = C.cast(layers, C.POINTER(_lib.DecodeLayer))
         d.ws, d.ws_bytes = 0, 0
+        if os.environ.get("DH_DECODE_TRACE", "0") == "1":            # developer knob: per-stage globaltimer stamps (scripts/decode_mega_trace.py)
+            tr = self._bufs["dec_trace"] = torch.zeros(3 * s.n_layer * 24 + 8 * ops.sm_count() * 2, device=self.device, dtype=torch.int64)
+            d.trace = tr.data_ptr()
+            keep.append(tr)
         ws_bytes = ops.decode_workspace_bytes(d)
         ws = self._cap_buf("dec_mega_ws", (ws_bytes // 4,), f32)
         d.ws, d.ws_bytes = ws.data_ptr(), ws.numel() * 4

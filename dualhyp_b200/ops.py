@@ -308,13 +308,15 @@ def attention_bwd_varlen(qkv: Tensor, out: Tensor, dout: Tensor, lse: Tensor, dq
 
 @_profiled("attention_decode")
 def attention_decode(qkv: Tensor, cache_k: Tensor, cache_v: Tensor, lens: Tensor, out: Tensor, n_groups: int, q_per_kv: int,
-                     prefix_kv: Optional[Tensor] = None, gate: Optional[Tensor] = None, prefix_len: int = 0) -> None:
+                     prefix_kv: Optional[Tensor] = None, gate: Optional[Tensor] = None, prefix_len: int = 0, stream_kv: bool = False) -> None:
+    """`stream_kv=True` calls the streamed kernel (csrc/decode_attn.cu) directly; the default entry picks its kernel itself."""
     _dev(qkv)
     nseq, max_len = cache_k.shape[0], cache_k.shape[2]
     assert cache_k.is_contiguous() and cache_v.is_contiguous() and lens.dtype == torch.int32 and qkv.is_contiguous()
-    check(_lib.load().dh_attention_decode(qkv.data_ptr(), cache_k.data_ptr(), cache_v.data_ptr(), lens.data_ptr(), out.data_ptr(),
-                                          _ptr(prefix_kv), _ptr(gate), nseq, max_len, n_groups, q_per_kv, prefix_len, _stream()),
-          "dh_attention_decode")
+    lib = _lib.load()
+    fn, name = (lib.dh_attention_decode_stream, "dh_attention_decode_stream") if stream_kv else (lib.dh_attention_decode, "dh_attention_decode")
+    check(fn(qkv.data_ptr(), cache_k.data_ptr(), cache_v.data_ptr(), lens.data_ptr(), out.data_ptr(),
+             _ptr(prefix_kv), _ptr(gate), nseq, max_len, n_groups, q_per_kv, prefix_len, _stream()), name)
     _count()
 
 

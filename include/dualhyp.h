@@ -177,6 +177,11 @@ int dh_prefix_project_bwd(const float* d_prefix_kv, const void* wkv, float* d_pr
 int dh_attention_decode(const void* qkv, const void* cache_k, const void* cache_v, const int32_t* lens, void* out,
                         const void* prefix_kv, const float* gate, int nseq, int max_len, int n_groups, int q_per_kv,
                         int prefix_len, void* stream);
+/* The kernel dh_attention_decode uses when max_len is a multiple of 64 (csrc/decode_attn.cu): the cached K / V rows of one
+ * (sequence, kv group) stream through a TMA ring as 64-key chunks, flash-style running softmax per warp, same arguments. */
+int dh_attention_decode_stream(const void* qkv, const void* cache_k, const void* cache_v, const int32_t* lens, void* out,
+                               const void* prefix_kv, const float* gate, int nseq, int max_len, int n_groups, int q_per_kv,
+                               int prefix_len, void* stream);
 /* ---------------------------------------------------------------------------------------------------
  * One decode token step for ALL decoder layers as one persistent kernel (ger/model.py:163-268 per layer, driven one token at
  * a time by generate/base.py:57-80): one CTA per SM, grid-wide barriers between the stages, the frozen weights of every GEMM
@@ -207,6 +212,7 @@ typedef struct dh_decode_desc {
   const void* rope_cos; const void* rope_sin;
   void* barrier;
   const dh_decode_layer* layers;
+  void* trace;                     /* developer trace, int64 [3 * n_layer * 24 + 8 * n_sm * 2] globaltimer stamps (NULL: off); see scripts/decode_mega_trace.py */
 } dh_decode_desc;
 
 size_t dh_decode_plan_bytes(int n_layer);

@@ -631,11 +631,13 @@ def test_attention_decode_matches_prefill():
     assert rel(dec, ref) < 1e-2, report("decode attn", dec, ref)
 
 
+@pytest.mark.parametrize("stream_kv", [False, True])
 @pytest.mark.parametrize("nseq,G,qpk,prefix,max_len", [(5, 4, 8, 10, 640), (3, 2, 2, 0, 640), (2, 1, 1, 16, 640), (4, 4, 8, 10, 2048)])
-def test_attention_decode_against_fp32(nseq, G, qpk, prefix, max_len):
+def test_attention_decode_against_fp32(nseq, G, qpk, prefix, max_len, stream_kv):
     """The decode kernel against fp32 softmax attention over the valid cache slots (lengths from 1 to the whole row, not
     multiples of the 16-key tiles), with and without the gated prefix; rows of 640 slots take the 4-tiles-ahead V prefetch,
-    rows of 2048 x 8 heads the 2-tiles-ahead build (the score buffer takes the shared memory)."""
+    rows of 2048 x 8 heads the 2-tiles-ahead build (the score buffer takes the shared memory).  `stream_kv`: the same cases
+    through the streamed kernel (dh_attention_decode_stream: TMA ring of 64-key chunks, up to 32 chunks per row here)."""
     H = G * qpk
     N = G * (qpk + 2) * 64
     lens = synthetic.hash_ints((nseq,), 3, 401, 1, max_len + 1).to(torch.int32)
@@ -645,7 +647,7 @@ def test_attention_decode_against_fp32(nseq, G, qpk, prefix, max_len):
     pk = rnd((max(prefix, 1), N), 405, 2.0)
     gate = rnd((H,), 406, 1.0, torch.float32)
     out = torch.full((nseq, H * 64), float("nan"), device=DEV, dtype=torch.bfloat16)
-    ops.attention_decode(row, ck, cv, lens.to(DEV), out, G, qpk, pk if prefix else None, gate if prefix else None, prefix)
+    ops.attention_decode(row, ck, cv, lens.to(DEV), out, G, qpk, pk if prefix else None, gate if prefix else None, prefix, stream_kv=stream_kv)
     torch.cuda.synchronize()
     r = row.float().view(nseq, G, qpk + 2, 64)
     ref = torch.zeros((nseq, G, qpk, 64), device=DEV)

@@ -302,11 +302,13 @@ def test_packed_prefill_equals_padded_prefill():
 
 @pytest.mark.parametrize("variant,name,n,plen", [("adapter", "tiny-llama-test", 5, (3, 60)), ("adapter", "tiny-llama-test", 128, (3, 100)),
                                                  ("lora", "tiny-llama-test", 7, (3, 60)), ("adapter", "tiny-llama-1.1b", 37, (100, 300))])
-def test_persistent_decode_kernel_matches_per_gemm_path(variant, name, n, plen):
-    """One decode token step of all layers as ONE persistent kernel (csrc/decode.cu: stream-K weight streaming over all SMs,
+def test_persistent_decode_kernel_matches_per_gemm_path(variant, name, n, plen, monkeypatch):
+    """(The persistent kernel is opt-in, DH_DECODE_MEGA=1: measured slower than the per-GEMM graph)
+    One decode token step of all layers as ONE persistent kernel (csrc/decode.cu: stream-K weight streaming over all SMs,
     grid barriers, partial tiles summed by the stage that follows) against the per-GEMM kernel sequence it replaces: same
     ln_f state (bf16 tolerance: the fp32 partial sums are associated differently), same new K / V rows in the cache, and
     bit-identical results from launch to launch (the stages sum their partial tiles in a fixed order)."""
+    monkeypatch.setenv("DH_DECODE_MEGA", "1")
     m, _ = build(variant, name=name, **({"adapter_start_layer": 1} if (variant == "adapter" and name == "tiny-llama-test") else {}))
     if variant == "lora":
         lora.merge_lora_weights(m)               # generate/lora.py:112 merges before decoding; un-merged factors take the per-GEMM path
