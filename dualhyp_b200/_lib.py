@@ -99,6 +99,9 @@ SIGNATURES = {
     "dh_relpred_fwd": (_I, [_P] * 11 + [_I, _I, _I, _I, _P]),
     "dh_relpred_bwd": (_I, [_P] * 15 + [_I, _I, _I, _I, _P]),
     "dh_cast_f32_to_bf16": (_I, [_P, _L, _P, _L, _L, _L, _P]),
+    "dh_relpred_head_fwd": (_I, [_P, _P, _P, _P, _P, _I, _I, _I, _P]),
+    "dh_relpred_head_bwd": (_I, [_P, _P, _P, _P, _P, _P, _P, _I, _I, _I, _P]),
+    "dh_dropout_bf16": (_I, [_P, _P, _L, _F, C.c_uint64, C.c_uint64, _I, _P]),
     "dh_adamw_step": (_I, [_P, _P, _P, _P, _L, _F, _F, _F, _F, _F, _I, _F, _P]),
 }
 

@@ -467,6 +467,43 @@ __global__ void cast_f32_bf16_kernel(const float* __restrict__ src, long long ld
   }
 }
 
+// Philox4x32-10 (Salmon et al., SC'11): counter-based, so the mask of element block i is a pure function of (seed, offset, i) --
+// the backward regenerates it instead of saving it.
+__device__ __forceinline__ uint4 philox4x32_10(uint4 ctr, uint2 key) {
+#pragma unroll
+  for (int r = 0; r < 10; ++r) {
+    const uint32_t hi0 = __umulhi(0xD2511F53u, ctr.x), lo0 = 0xD2511F53u * ctr.x;
+    const uint32_t hi1 = __umulhi(0xCD9E8D57u, ctr.z), lo1 = 0xCD9E8D57u * ctr.z;
+    ctr = make_uint4(hi1 ^ ctr.y ^ key.x, lo1, hi0 ^ ctr.w ^ key.y, lo0);
+    key.x += 0x9E3779B9u;
+    key.y += 0xBB67AE85u;
+  }
+  return ctr;
+}
+
+// nn.Dropout(p) on a bf16 tensor (ger/lora.py:94-98,165: the LoRA branch sees dropout(x)): out = keep ? x / (1 - p) : 0, one
+// Philox call per 8 elements (eight 16-bit uniforms; keep when u16 >= p * 65536).  ADD = true: out += the masked, scaled x (the
+// gradient of the LoRA branch flowing back into x through the same mask).
+template <bool ADD>
+__global__ void dropout_bf16_kernel(const bf16* __restrict__ x, bf16* __restrict__ out, long long n8, uint32_t thresh, float inv_keep,
+                                    uint2 key, uint2 offset) {
+  for (long long i = blockIdx.x * (long long)blockDim.x + threadIdx.x; i < n8; i += (long long)gridDim.x * blockDim.x) {
+    const uint4 rnd = philox4x32_10(make_uint4((uint32_t)i, (uint32_t)(i >> 32), offset.x, offset.y), key);
+    const uint32_t w[4] = {rnd.x, rnd.y, rnd.z, rnd.w};
+    float v[8];
+    unpack8(*reinterpret_cast<const uint4*>(x + i * 8), v);
+    float o[8];
+    if (ADD) unpack8(*reinterpret_cast<const uint4*>(out + i * 8), o);
+#pragma unroll
+    for (int j = 0; j < 8; ++j) {
+      const uint32_t u = (w[j >> 1] >> (16 * (j & 1))) & 0xFFFFu;
+      const float m = u >= thresh ? v[j] * inv_keep : 0.f;
+      o[j] = ADD ? o[j] + m : m;
+    }
+    *reinterpret_cast<uint4*>(out + i * 8) = pack8(o);
+  }
+}
+
 // torch.optim.AdamW (decoupled weight decay, bias-corrected), one flat bucket
 __global__ void adamw_kernel(float* p, const float* __restrict__ g, float* m, float* v, long long n, float lr, float b1, float b2,
                              float eps, float wd, float bc1, float bc2_sqrt, float gscale) {
@@ -773,6 +810,19 @@ extern "C" int dh_argmax(const void* logits, int64_t ldl, int64_t* ids, int M, i
 extern "C" int dh_cast_f32_to_bf16(const float* src, int64_t lds, void* dst, int64_t ldd, int64_t rows, int64_t cols, void* stream) {
   DH_CHECK(src && dst && rows > 0 && cols > 0 && cols % 8 == 0 && lds % 4 == 0 && ldd % 8 == 0, "dh_cast_f32_to_bf16: bad argument");
   cast_f32_bf16_kernel<<<grid_for(rows * cols / 8, 256), 256, 0, (cudaStream_t)stream>>>(src, lds, (bf16*)dst, ldd, rows, cols);
+  DH_CUDA(cudaGetLastError());
+  return 0;
+}
+
+extern "C" int dh_dropout_bf16(const void* x, void* out, int64_t n, float p, uint64_t seed, uint64_t offset, int accumulate, void* stream) {
+  DH_CHECK(x && out && n > 0 && n % 8 == 0, "dh_dropout_bf16: n must be a positive multiple of 8");
+  DH_CHECK(p >= 0.f && p < 1.f, "dh_dropout_bf16: p = %f not in [0, 1)", (double)p);
+  DH_CHECK((((uintptr_t)x | (uintptr_t)out) & 15) == 0, "dh_dropout_bf16: operands must be 16-byte aligned");
+  const uint32_t thresh = (uint32_t)lrintf(p * 65536.f);
+  const float inv_keep = 65536.f / (float)(65536u - thresh);         // the keep probability the 16-bit threshold really gives
+  const uint2 key = make_uint2((uint32_t)seed, (uint32_t)(seed >> 32)), off = make_uint2((uint32_t)offset, (uint32_t)(offset >> 32));
+  if (accumulate) dropout_bf16_kernel<true><<<grid_for(n / 8, 256), 256, 0, (cudaStream_t)stream>>>((const bf16*)x, (bf16*)out, n / 8, thresh, inv_keep, key, off);
+  else dropout_bf16_kernel<false><<<grid_for(n / 8, 256), 256, 0, (cudaStream_t)stream>>>((const bf16*)x, (bf16*)out, n / 8, thresh, inv_keep, key, off);
   DH_CUDA(cudaGetLastError());
   return 0;
 }

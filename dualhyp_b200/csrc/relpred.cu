@@ -217,3 +217,28 @@ extern "C" int dh_relpred_bwd(const float* x, const float* w1, const float* w2, 
   DH_CUDA(cudaGetLastError());
   return 0;
 }
+
+// The pooling + classifier tail of the head on its own (the tensor-core path runs the two convolutions as bf16 GEMMs through
+// dh_gemm -- rows of three consecutive frames are the K-major A operand, no im2col kernel -- and only needs the tail here).
+extern "C" int dh_relpred_head_fwd(const float* h2, const float* wc, const float* bc, float* pooled, float* logits, int B, int T, int pool,
+                                   void* stream) {
+  DH_CHECK(h2 && wc && bc && pooled && logits && B > 0 && T > 0 && pool > 0, "dh_relpred_head_fwd: bad argument");
+  cudaStream_t s = (cudaStream_t)stream;
+  const int n_out = (T + pool - 1) / pool;
+  pool_fwd_kernel<<<(B * n_out * HID + 255) / 256, 256, 0, s>>>(h2, pooled, B, T, pool, n_out);
+  classifier_fwd_kernel<<<(B * n_out * 3 * 32 + 255) / 256, 256, 0, s>>>(pooled, wc, bc, logits, B * n_out);
+  DH_CUDA(cudaGetLastError());
+  return 0;
+}
+
+// d_logits -> dz2 = d(conv2 pre-activation) f32 [B, T, 256] (through the average pool and the ReLU of h2); dwc / dbc ACCUMULATED.
+extern "C" int dh_relpred_head_bwd(const float* h2, const float* pooled, const float* d_logits, const float* wc, float* dz2, float* dwc,
+                                   float* dbc, int B, int T, int pool, void* stream) {
+  DH_CHECK(h2 && pooled && d_logits && wc && dz2 && dwc && dbc && B > 0 && T > 0 && pool > 0, "dh_relpred_head_bwd: bad argument");
+  cudaStream_t s = (cudaStream_t)stream;
+  const int n_out = (T + pool - 1) / pool;
+  classifier_bwd_kernel<<<(3 * HID + 3 + 255) / 256, 256, 0, s>>>(pooled, d_logits, dwc, dbc, B * n_out);
+  pool_bwd_kernel<<<(int)(((long long)B * T * HID + 255) / 256), 256, 0, s>>>(h2, d_logits, wc, dz2, B, T, pool, n_out);
+  DH_CUDA(cudaGetLastError());
+  return 0;
+}

@@ -44,6 +44,7 @@ class EngineSpec:
     lora_qkv: bool = False
     lora_proj: bool = False
     lora_start_layer: int = 0
+    lora_dropout: float = 0.0          # nn.Dropout(p) on the input of every LoRA branch in training (ger/lora.py:94-98,165)
     adapter_prompt_length: int = 0
     adapter_start_layer: int = 0
 
@@ -159,18 +160,75 @@ class DecoderEngine:
             self.lm_scale = self.lm_bias = None
         self.lm_w_t = self.lm_w.t().contiguous() if s.first_trainable_layer < s.n_layer else None
 
+    def _persistent(self, name: str, shape, dtype) -> Tensor:
+        """Zero-initialised buffer that lives as long as the engine (created outside inference mode, so that both the training
+        step and `generate` may update it in place)."""
+        key = ("persistent", name, tuple(shape), dtype)
+        t = self._bufs.get(key)
+        if t is None:
+            with torch.inference_mode(False):
+                t = torch.zeros(shape, device=self.device, dtype=dtype)
+            self._bufs[key] = t
+        return t
+
+    def _pack_lora_batched(self, tr: Dict[str, Tensor], packed: Dict[int, Dict[str, Tensor]]) -> bool:
+        """The bf16 operand forms of ALL LoRA layers in ~17 launches (per-layer packing costs ~20 ATen launches per layer, 440 of
+        the 1179 launches of a LoRA step: profiles/r02_lora_launch_summary_before.txt).  The forms live in persistent buffers
+        [L, ...] whose zero padding is written once; a layer's entry in `packed` is a view of its slice.  Returns False when a
+        LoRA module is absent from `tr` (merged into W): the caller then packs layer by layer."""
+        s = self.spec
+        lay = [i for i in range(s.n_layer) if s.has_lora(i)]
+        if not lay:
+            return True
+        L, C, r, kv = len(lay), s.n_embd, s.r, s.kv_embd
+        scaling = s.alpha / s.r
+        pre = "transformer.h.{}.attn.{}"
+        bf = torch.bfloat16
+
+        def stack(fmt):
+            return torch.stack([tr[fmt.format(i)].detach() for i in lay]).to(self.device)
+
+        for kind, on, n_a, out_rows in (("attn", s.lora_qkv, 3 * r, s.qkv_out), ("proj", s.lora_proj, r, C)):
+            if not on:
+                continue
+            fa, fb = pre.format("{}", kind + ".lora_A"), pre.format("{}", kind + ".lora_B")
+            if any(fa.format(i) not in tr or fb.format(i) not in tr for i in lay):
+                return False
+            key = "qkv" if kind == "attn" else "proj"
+            a_pad = self._persistent(key + "_a_all", (L, LORA_PAD, C), bf)
+            a_pad_t = self._persistent(key + "_a_t_all", (L, C, LORA_PAD), bf)
+            b_ext = self._persistent(key + "_b_all", (L, out_rows, LORA_PAD), bf)
+            b_ext_t = self._persistent(key + "_b_t_all", (L, LORA_PAD, out_rows), bf)
+            A, Bm = stack(fa), stack(fb)                                   # [L, n_a, C] / [L, out_rows, r] fp32
+            a_pad[:, :n_a].copy_(A.float() * scaling)
+            if kind == "attn":                                              # quirk Q3: q rows use after_A[:, 0:r], k rows [r:2r], v rows [2r:3r]
+                b_ext[:, :C, 0:r].copy_(Bm[:, :C])
+                b_ext[:, C:C + kv, r:2 * r].copy_(Bm[:, C:C + kv])
+                b_ext[:, C + kv:, 2 * r:3 * r].copy_(Bm[:, C + kv:])
+            else:
+                b_ext[:, :, :r].copy_(Bm)
+            a_pad_t.copy_(a_pad.transpose(1, 2))
+            b_ext_t.copy_(b_ext.transpose(1, 2))
+            for j, i in enumerate(lay):
+                d = packed.setdefault(i, {})
+                d[key + "_a"], d[key + "_b"], d[key + "_a_t"], d[key + "_b_t"] = a_pad[j], b_ext[j], a_pad_t[j], b_ext_t[j]
+        return True
+
     def pack_trainable(self, tr: Dict[str, Tensor]) -> Dict[int, Dict[str, Tensor]]:
         """Per-step bf16 forms of the small trainable tensors (reference-keyed, fp32 masters)."""
         s, dev = self.spec, self.device
         packed: Dict[int, Dict[str, Tensor]] = {}
         scaling = (s.alpha / s.r) if s.r > 0 else 0.0
+        lora_done = s.variant == "lora" and s.r > 0 and self._pack_lora_batched(tr, packed)
+        if s.variant == "lora" and s.r > 0 and not lora_done:
+            packed.clear()
         for i in range(s.n_layer):
             p = f"transformer.h.{i}.attn."
             d: Dict[str, Tensor] = {}
             if s.has_adapter(i):
                 d["prefix"] = tr[p + "adapter_wte.weight"].detach().to(dev, torch.bfloat16).contiguous()
                 d["gate"] = tr[p + "gating_factor"].detach().to(dev, torch.float32).reshape(-1).contiguous()
-            if s.has_lora(i):
+            if s.has_lora(i) and not lora_done:
                 C, r = s.n_embd, s.r
                 if s.lora_qkv and (p + "attn.lora_A") in tr:       # absent: the module was merged into W (LoRALinear.merge)
                     A, Bm = tr[p + "attn.lora_A"].detach().to(dev), tr[p + "attn.lora_B"].detach().to(dev)
@@ -192,7 +250,7 @@ class DecoderEngine:
                     d["proj_a"], d["proj_b"] = a_pad, b_ext
                     d["proj_a_t"], d["proj_b_t"] = a_pad.t().contiguous(), b_ext.t().contiguous()
             if d:
-                packed[i] = d
+                packed.setdefault(i, {}).update(d)
         if s.variant == "adapter" and s.adapter_start_layer < s.n_layer:
             packed[-1] = {"prefix_all": torch.stack([packed[i]["prefix"] for i in range(s.adapter_start_layer, s.n_layer)]).contiguous()}
         return packed
@@ -229,8 +287,8 @@ class DecoderEngine:
     # ------------------------------------------------------------------------------------------
     # forward over full sequences (training / evaluation / prefill)
     # ------------------------------------------------------------------------------------------
-    def forward_hidden(self, idx: Tensor, packed: Dict[int, Dict[str, Tensor]], save: bool, write_cache: bool = False,
-                       varlen: Optional[Dict] = None) -> Tensor:
+    def forward_hidden(self, idx: Tensor, packed: Dict[int, Dict[str, Tensor]], save: bool = False, write_cache: bool = False,
+                       varlen: Optional[Dict] = None, dropout_seed: Optional[int] = None) -> Tensor:
         """idx int64 [B, T] -> ln_f output bf16 [B*T, C].  save=True keeps what backward() needs.
         varlen: idx is ONE row of packed sequences [1, M] without pad tokens; `varlen` holds cu_seqlens int32 [n + 1], positions
         int32 [M] (RoPE position of every row inside its sequence), max_len, and for the cache-writing prefill seq_ids int32 [M].
@@ -254,7 +312,10 @@ class DecoderEngine:
         ops.embedding_fwd(idx.view(-1), self.wte, x)
         n = _buf("n", (M, C), bf)
         act = _buf("act", (M, I), bf)
-        saved = dict(B=B, T=T, layers=[], packed=packed, varlen=varlen) if save else None
+        # LoRA dropout (training only): the LoRA branch multiplies dropout(x), the frozen path the plain x (ger/lora.py:159-166).
+        # The mask is Philox(seed, offset = 2 * layer [+ 1 for proj]); backward() regenerates it from the same pair.
+        use_do = save and dropout_seed is not None and s.variant == "lora" and s.lora_dropout > 0
+        saved = dict(B=B, T=T, layers=[], packed=packed, varlen=varlen, dropout_seed=dropout_seed if use_do else None) if save else None
         pkv_all = self._project_prefixes(packed, "pkv_all")
         for i, lw in enumerate(self.layers):
             pk = packed.get(i, {})
@@ -265,7 +326,11 @@ class DecoderEngine:
             a_s = None
             if "qkv_a" in pk:
                 a_s = _buf(per("qkv_as", i), (M, LORA_PAD), bf)
-                ops.gemm(n_i, pk["qkv_a"], a_s)
+                src = n_i
+                if use_do:
+                    src = _buf("lora_do", (M, C), bf)
+                    ops.dropout_bf16(n_i, src, s.lora_dropout, dropout_seed, 2 * i)
+                ops.gemm(src, pk["qkv_a"], a_s)
                 ops.gemm(n_i, lw["wqkv"], qkv, A2=a_s, B2=pk["qkv_b"], epilogue=ops.EPI_QKV_ROPE, rope_cos=self.cos, rope_sin=self.sin,
                          positions=vpos, seq_len=T, q_per_kv=qpk)
             else:
@@ -290,7 +355,11 @@ class DecoderEngine:
             ap_s = None
             if "proj_a" in pk:
                 ap_s = _buf(per("proj_as", i), (M, LORA_PAD), bf)
-                ops.gemm(y, pk["proj_a"], ap_s)
+                src = y
+                if use_do:
+                    src = _buf("lora_do", (M, C), bf)
+                    ops.dropout_bf16(y, src, s.lora_dropout, dropout_seed, 2 * i + 1)
+                ops.gemm(src, pk["proj_a"], ap_s)
                 ops.gemm(y, lw["wproj"], xmid, A2=ap_s, B2=pk["proj_b"], epilogue=ops.EPI_RESID_F32, aux=x)
             else:
                 ops.gemm(y, lw["wproj"], xmid, epilogue=ops.EPI_RESID_F32, aux=x)
@@ -328,20 +397,18 @@ class DecoderEngine:
         ops.prefix_project_fwd(packed[-1]["prefix_all"], self.wkv_all, pkv_all, s.n_query_groups, s.qpk)
         return pkv_all
 
-    def _wgrad(self, A: Tensor, B: Tensor, rows: int, cols: int, alpha: float = 1.0) -> Tensor:
-        """fp32 [rows, cols] = alpha * A^T B for the LoRA factor gradients: both operands are [tokens, *] (MN-major), the
-        reduction runs over the TOKEN dimension (K = B*T = 8192) while the output is tiny (64 x 2048: 16-32 tiles), so K is
-        split over all SMs (dh_gemm split_k: fp32 slices) and the slices are summed."""
-        K = A.shape[0]
+    def _wgrad_plan(self, rows: int, cols: int, K: int) -> int:
+        """Split-K factor of a LoRA factor gradient (see _wgrad)."""
         tiles = ((rows + 127) // 128) * ((cols + 63) // 64)
-        S = max(1, min(ops.sm_count() // tiles, (K // 64) // 4, 16))
+        return max(1, min(ops.sm_count() // tiles, (K // 64) // 4, 16))
+
+    def _wgrad_into(self, A: Tensor, B: Tensor, ws: Tensor, alpha: float = 1.0) -> None:
+        """ws [S, rows, cols] fp32 = the S split-K slices of alpha * A^T B (the caller sums them, for all layers at once)."""
+        S = ws.shape[0]
         if S == 1:
-            out = torch.empty((rows, cols), device=self.device, dtype=torch.float32)
-            ops.gemm(A, B, out, a_layout=1, b_layout=1, epilogue=ops.EPI_F32, alpha=alpha)
-            return out
-        ws = self._buf("wgrad_ws", (S, rows, cols), torch.float32)
-        ops.gemm(A, B, ws, a_layout=1, b_layout=1, epilogue=ops.EPI_F32, alpha=alpha, split_k=S)
-        return ws.sum(0)
+            ops.gemm(A, B, ws[0], a_layout=1, b_layout=1, epilogue=ops.EPI_F32, alpha=alpha)
+        else:
+            ops.gemm(A, B, ws, a_layout=1, b_layout=1, epilogue=ops.EPI_F32, alpha=alpha, split_k=S)
 
     def lm_head(self, hidden: Tensor, out: Optional[Tensor] = None, m_limit: Optional[Tensor] = None) -> Tensor:
         """bf16 logits [M, V] = adapter_scale * (hidden W^T + adapter_bias)  (ger/lora.py:70-71).  m_limit (device int32):
@@ -375,6 +442,7 @@ class DecoderEngine:
         M, C, I, G, qpk = B * T, s.n_embd, s.intermediate_size, s.n_query_groups, s.qpk
         bf, f32 = torch.bfloat16, torch.float32
         packed = sv["packed"]
+        do_seed = sv.get("dropout_seed")
         grads: Dict[str, Tensor] = {}
         first = s.first_trainable_layer
         if first >= s.n_layer:
@@ -393,6 +461,15 @@ class DecoderEngine:
             La = s.n_layer - s.adapter_start_layer
             d_pkv_all = torch.zeros((La, s.adapter_prompt_length, s.qkv_out), device=self.device, dtype=f32)
             d_gate_all = torch.zeros((La, s.n_head), device=self.device, dtype=f32)
+        # LoRA factor gradients: every layer's split-K slices go to ONE workspace per kind, summed for all layers at the end
+        # (4 reductions + 3 slice copies per step instead of ~12 ATen launches per layer)
+        lora_lay = [i for i in range(first, s.n_layer) if s.has_lora(i)] if s.variant == "lora" else []
+        lora_pos = {i: j for j, i in enumerate(lora_lay)}
+        lws: Dict[str, Tensor] = {}
+        if lora_lay:
+            Ll = len(lora_lay)
+            for key, rows, cols in (("qkv_dB", s.qkv_out, LORA_PAD), ("qkv_dA", LORA_PAD, C), ("proj_dB", C, LORA_PAD), ("proj_dA", LORA_PAD, C)):
+                lws[key] = self._cap_buf("lora_ws_" + key, (Ll, self._wgrad_plan(rows, cols, M), rows, cols), f32)
         for i in range(s.n_layer - 1, first - 1, -1):
             lw, a, pk = self.layers[i], sv["layers"][i], packed.get(i, {})
             p = f"transformer.h.{i}.attn."
@@ -404,11 +481,19 @@ class DecoderEngine:
             if "proj_a" in pk:
                 dap = self._cap_buf("dap", (M, LORA_PAD), bf)
                 ops.gemm(dxb, pk["proj_b_t"], dap)
-                db = self._wgrad(dxb, a["ap_s"], C, LORA_PAD)
-                da = self._wgrad(dap, a["y"], LORA_PAD, C, alpha=scaling)
-                grads[p + "proj.lora_A"] = da[: s.r]
-                grads[p + "proj.lora_B"] = db[:, : s.r]
-                ops.gemm(dxb, lw["wproj_t"], dy, A2=dap, B2=pk["proj_a_t"])
+                self._wgrad_into(dxb, a["ap_s"], lws["proj_dB"][lora_pos[i]])
+                if do_seed is None:
+                    self._wgrad_into(dap, a["y"], lws["proj_dA"][lora_pos[i]], alpha=scaling)
+                    ops.gemm(dxb, lw["wproj_t"], dy, A2=dap, B2=pk["proj_a_t"])
+                else:
+                    # the LoRA branch saw dropout(y): its factor gradient multiplies the regenerated dropout(y), and its share of
+                    # d(y) passes through the same mask, so it cannot ride the dgrad's K-extension
+                    xd, tmp = self._cap_buf("lora_do", (M, C), bf), self._cap_buf("lora_do_g", (M, C), bf)
+                    ops.dropout_bf16(a["y"], xd, s.lora_dropout, do_seed, 2 * i + 1)
+                    self._wgrad_into(dap, xd, lws["proj_dA"][lora_pos[i]], alpha=scaling)
+                    ops.gemm(dxb, lw["wproj_t"], dy)
+                    ops.gemm(dap, pk["proj_a_t"], tmp)
+                    ops.dropout_bf16(tmp, dy, s.lora_dropout, do_seed, 2 * i + 1, accumulate=True)
             else:
                 ops.gemm(dxb, lw["wproj_t"], dy)
             # ---- attention ----
@@ -431,17 +516,44 @@ class DecoderEngine:
             if "qkv_a" in pk:
                 da_s = self._cap_buf("da_s", (M, LORA_PAD), bf)
                 ops.gemm(dqkv, pk["qkv_b_t"], da_s)
-                db = self._wgrad(dqkv, a["a_s"], s.qkv_out, LORA_PAD)
-                da = self._wgrad(da_s, a["n1"], LORA_PAD, C, alpha=scaling)
-                r, kv = s.r, s.kv_embd
-                grads[p + "attn.lora_A"] = da[: 3 * r]
-                grads[p + "attn.lora_B"] = torch.cat((db[:C, 0:r], db[C:C + kv, r:2 * r], db[C + kv:, 2 * r:3 * r]), dim=0)
-                if i > first:
-                    ops.gemm(dqkv, lw["wqkv_t"], dn, A2=da_s, B2=pk["qkv_a_t"])
+                self._wgrad_into(dqkv, a["a_s"], lws["qkv_dB"][lora_pos[i]])
+                if do_seed is None:
+                    self._wgrad_into(da_s, a["n1"], lws["qkv_dA"][lora_pos[i]], alpha=scaling)
+                    if i > first:
+                        ops.gemm(dqkv, lw["wqkv_t"], dn, A2=da_s, B2=pk["qkv_a_t"])
+                else:
+                    xd, tmp = self._cap_buf("lora_do", (M, C), bf), self._cap_buf("lora_do_g", (M, C), bf)
+                    ops.dropout_bf16(a["n1"], xd, s.lora_dropout, do_seed, 2 * i)
+                    self._wgrad_into(da_s, xd, lws["qkv_dA"][lora_pos[i]], alpha=scaling)
+                    if i > first:
+                        ops.gemm(dqkv, lw["wqkv_t"], dn)
+                        ops.gemm(da_s, pk["qkv_a_t"], tmp)
+                        ops.dropout_bf16(tmp, dn, s.lora_dropout, do_seed, 2 * i, accumulate=True)
             elif i > first:
                 ops.gemm(dqkv, lw["wqkv_t"], dn)
             if i > first:
                 ops.rmsnorm_bwd(a["x"], lw["norm1"], a["rstd1"], dn, dx, dx, dxb)
+        if lora_lay:
+            r, kv = s.r, s.kv_embd
+            pre = "transformer.h.{}.attn."
+            if s.lora_qkv and any("qkv_a" in packed.get(i, {}) for i in lora_lay):
+                dA = lws["qkv_dA"].sum(1)                                           # [L, 64, C]
+                dBf = lws["qkv_dB"].sum(1)                                          # [L, qkv_out, 64]
+                dB = torch.empty((len(lora_lay), s.qkv_out, r), device=self.device, dtype=f32)
+                dB[:, :C].copy_(dBf[:, :C, 0:r])                                    # quirk Q3 scatter, inverted
+                dB[:, C:C + kv].copy_(dBf[:, C:C + kv, r:2 * r])
+                dB[:, C + kv:].copy_(dBf[:, C + kv:, 2 * r:3 * r])
+                for j, i in enumerate(lora_lay):
+                    if "qkv_a" in packed.get(i, {}):
+                        grads[pre.format(i) + "attn.lora_A"] = dA[j, : 3 * r]
+                        grads[pre.format(i) + "attn.lora_B"] = dB[j]
+            if s.lora_proj and any("proj_a" in packed.get(i, {}) for i in lora_lay):
+                dA = lws["proj_dA"].sum(1)
+                dB = lws["proj_dB"].sum(1)
+                for j, i in enumerate(lora_lay):
+                    if "proj_a" in packed.get(i, {}):
+                        grads[pre.format(i) + "proj.lora_A"] = dA[j, :r]
+                        grads[pre.format(i) + "proj.lora_B"] = dB[j, :, :r]
         if d_pkv_all is not None:      # d(adapter_wte) of all layers in one launch: d(prefix k/v) through the k / v weight rows
             d_wte_all = torch.empty((d_pkv_all.shape[0], s.adapter_prompt_length, C), device=self.device, dtype=f32)
             ops.prefix_project_bwd(d_pkv_all, self.wkv_all, d_wte_all, G, qpk)

@@ -185,13 +185,11 @@ class GPT(BaseModel):
         qkv_flags = (c.to_query, c.to_key, c.to_value)
         if c.r > 0 and any(qkv_flags) and not all(qkv_flags):
             raise NotImplementedError("the B200 LoRA-QKV path implements the all-enabled case the DualHyp scripts use (q, k, v together)")
-        if c.dropout > 0 and self.training:
-            import warnings
-            warnings.warn("LoRA dropout is not applied by the B200 engine yet (parity runs use dropout=0)")
         return EngineSpec(n_layer=c.n_layer, n_head=c.n_head, n_query_groups=c.n_query_groups, n_embd=c.n_embd,
                           intermediate_size=c.intermediate_size, vocab=c.padded_vocab_size, block_size=c.block_size,
                           norm_eps=c.norm_eps, variant="lora", r=c.r, alpha=float(c.alpha), lora_qkv=all(qkv_flags) and c.r > 0,
-                          lora_proj=bool(c.to_projection) and c.r > 0, lora_start_layer=c.lora_start_layer)
+                          lora_proj=bool(c.to_projection) and c.r > 0, lora_start_layer=c.lora_start_layer,
+                          lora_dropout=float(c.dropout))
 
     def _trainable_filter(self, name: str) -> bool:
         return "lora_" in name

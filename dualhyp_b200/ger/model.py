@@ -41,12 +41,12 @@ class _DecoderFn(torch.autograd.Function):
             # row, run the decoder over it, scatter the hidden states back to [B, T] (pad rows = 0; they carry no loss)
             rows, count = varlen["row_map"], varlen["count"]
             ids = idx.reshape(-1).index_select(0, varlen["row_map_long"]).view(1, -1)
-            hidden_p = eng.forward_hidden(ids, packed, save=True, varlen=varlen)
+            hidden_p = eng.forward_hidden(ids, packed, save=True, varlen=varlen, dropout_seed=model._dropout_seed())
             hidden = eng._cap_buf("hidden_unpacked", (B * T, hidden_p.shape[1]), torch.bfloat16)
             ops.scatter_rows(hidden_p, rows, count, hidden)
             ctx.unpad = (rows, count, hidden_p.shape[0])
         else:
-            hidden = eng.forward_hidden(idx, packed, save=True, varlen=varlen)
+            hidden = eng.forward_hidden(idx, packed, save=True, varlen=varlen, dropout_seed=model._dropout_seed())
         ctx.step_id = eng.step_id
         return hidden.view(B, T, -1)
 
@@ -267,6 +267,14 @@ class GPT(nn.Module):
     def _trainable_filter(self, name: str) -> bool:
         """Names the engine can produce gradients for."""
         return False
+
+    def _dropout_seed(self) -> Optional[int]:
+        """Seed of this forward's LoRA dropout masks, drawn from torch's CPU generator (so `torch.manual_seed` / Fabric's
+        `seed_everything` make a run repeatable, finetune/ger.py:105); None in eval mode or when the model has no dropout."""
+        p = float(getattr(self.config, "dropout", 0.0) or 0.0)
+        if not self.training or p <= 0.0:
+            return None
+        return int(torch.randint(0, 2 ** 62, (1,), dtype=torch.int64).item())
 
     def _frozen_items(self):
         return [(n, p) for n, p in self.named_parameters() if not self._trainable_filter(n) and "noise_classifier" not in n]

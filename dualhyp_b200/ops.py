@@ -38,10 +38,39 @@ class profile:
         return False
 
 
+_region_depth = 0
+
+
+class region:
+    """`with ops.region("relpred_fwd"):` -- a composite op (several C-ABI launches plus tensor glue) shows up in `profile()` as ONE
+    record timed around the whole block; the ops launched inside are not recorded a second time."""
+
+    def __init__(self, name: str):
+        self.name, self.e0 = name, None
+
+    def __enter__(self):
+        global _region_depth
+        if _prof is not None and _region_depth == 0:
+            self.e0 = torch.cuda.Event(enable_timing=True)
+            self.e0.record()
+        _region_depth += 1
+        return self
+
+    def __exit__(self, *exc):
+        global _region_depth
+        _region_depth -= 1
+        if self.e0 is not None and _prof is not None:
+            e1 = torch.cuda.Event(enable_timing=True)
+            e1.record()
+            _prof.append((self.name, None, self.e0, e1))
+        self.e0 = None
+        return False
+
+
 def _profiled(name, meta_fn=None):
     def deco(fn):
         def wrapper(*args, **kwargs):
-            if _prof is None:
+            if _prof is None or _region_depth > 0:
                 return fn(*args, **kwargs)
             e0, e1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
             e0.record()
@@ -376,6 +405,7 @@ def adamw_step(param: Tensor, grad: Tensor, exp_avg: Tensor, exp_avg_sq: Tensor,
     _count()
 
 
+@_profiled("relpred_fwd")
 def relpred_fwd(x: Tensor, w1, b1, w2, b2, wc, bc, h1: Tensor, h2: Tensor, pooled: Tensor, logits: Tensor, pool: int) -> None:
     _dev(x)
     B, T, Cd = x.shape
@@ -387,6 +417,7 @@ def relpred_fwd(x: Tensor, w1, b1, w2, b2, wc, bc, h1: Tensor, h2: Tensor, poole
     _count(4)
 
 
+@_profiled("relpred_bwd")
 def relpred_bwd(x, w1, w2, wc, h1, h2, pooled, d_logits, dw1, db1, dw2, db2, dwc, dbc, scratch, pool: int) -> None:
     _dev(x)
     B, T, Cd = x.shape
@@ -452,6 +483,35 @@ def scatter_rows(src: Tensor, rows: Tensor, count: Tensor, dst: Tensor) -> None:
     assert src.dtype == torch.bfloat16 and dst.dtype == torch.bfloat16 and src.is_contiguous() and dst.is_contiguous()
     check(_lib.load().dh_scatter_rows(src.data_ptr(), rows.data_ptr(), count.data_ptr(), dst.data_ptr(), dst.shape[0], dst.shape[1],
                                       _stream()), "dh_scatter_rows")
+    _count()
+
+
+def relpred_head_fwd(h2: Tensor, wc: Tensor, bc: Tensor, pooled: Tensor, logits: Tensor, pool: int) -> None:
+    """AvgPool1d(pool, ceil_mode) + Linear(256 -> 3) over h2 f32 [B, T, 256] (ger/relprompt.py:143-146)."""
+    _dev(h2)
+    B, T, H = h2.shape
+    assert H == 256 and all(t.dtype == torch.float32 and t.is_contiguous() for t in (h2, wc, bc, pooled, logits))
+    check(_lib.load().dh_relpred_head_fwd(h2.data_ptr(), wc.data_ptr(), bc.data_ptr(), pooled.data_ptr(), logits.data_ptr(), B, T, pool, _stream()),
+          "dh_relpred_head_fwd")
+    _count(2)
+
+
+def relpred_head_bwd(h2: Tensor, pooled: Tensor, d_logits: Tensor, wc: Tensor, dz2: Tensor, dwc: Tensor, dbc: Tensor, pool: int) -> None:
+    _dev(h2)
+    B, T, H = h2.shape
+    assert H == 256 and all(t.dtype == torch.float32 and t.is_contiguous() for t in (h2, pooled, d_logits, wc, dz2, dwc, dbc))
+    check(_lib.load().dh_relpred_head_bwd(h2.data_ptr(), pooled.data_ptr(), d_logits.data_ptr(), wc.data_ptr(), dz2.data_ptr(), dwc.data_ptr(),
+                                          dbc.data_ptr(), B, T, pool, _stream()), "dh_relpred_head_bwd")
+    _count(2)
+
+
+@_profiled("dropout")
+def dropout_bf16(x: Tensor, out: Tensor, p: float, seed: int, offset: int, accumulate: bool = False) -> None:
+    """out (+)= dropout(x, p) with the Philox mask of (seed, offset); see include/dualhyp.h."""
+    _dev(x)
+    assert x.dtype == torch.bfloat16 and out.dtype == torch.bfloat16 and x.is_contiguous() and out.is_contiguous() and x.numel() == out.numel()
+    check(_lib.load().dh_dropout_bf16(x.data_ptr(), out.data_ptr(), x.numel(), float(p), int(seed) & (2 ** 64 - 1), int(offset), int(accumulate), _stream()),
+          "dh_dropout_bf16")
     _count()
 
 

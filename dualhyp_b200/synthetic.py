@@ -60,10 +60,12 @@ def hash_ints(shape, seed: int, stream: int, lo: int, hi: int, device="cpu") -> 
 
 
 _SQRT3 = math.sqrt(3.0)
+PEAKY_MIX = 0.12
+PEAKY_A, PEAKY_B = 7919, 104729          # the `peaky` head permutation v -> (A v + B) mod V (A odd and not a multiple of 5: a bijection for V = 2^a 5^b ...)
 
 
 def synth_state_dict(cfg, variant: str, seed: int = 1337, device="cpu", lora_b_std: float = 0.02,
-                     gate_std: float = 0.5, dtype=torch.float32, extra_wte_rows: int = 0) -> Dict[str, Tensor]:
+                     gate_std: float = 0.5, dtype=torch.float32, extra_wte_rows: int = 0, peaky: bool = False) -> Dict[str, Tensor]:
     """A full state dict with the reference's key names for `variant` in
     {"base", "lora", "adapter", "relprompt"}.  `cfg` needs n_layer, n_head, n_query_groups, head_size,
     n_embd, intermediate_size, padded_vocab_size and the PEFT fields of the variant.
@@ -71,7 +73,13 @@ def synth_state_dict(cfg, variant: str, seed: int = 1337, device="cpu", lora_b_s
     Distributions follow PyTorch's defaults in spirit (what `empty_init=False` yields in the reference,
     finetune/ger.py:115): Linear ~ U(+-1/sqrt(fan_in)), Embedding unit variance, norms = 1; then, so the
     PEFT paths are live rather than zero-initialised: lora_B ~ U with std `lora_b_std`, gating_factor
-    ~ U with std `gate_std`."""
+    ~ U with std `gate_std`.
+
+    `peaky`: a random-init decoder has near-uniform logits, so greedy ids flip on bf16 noise.  With peaky=True the output head is
+    tied to a PERMUTATION of the embedding (lm_head row v = wte row (PEAKY_A * v + PEAKY_B) mod V, scaled by 1 / sqrt(C)): the
+    residual stream is dominated by the current token's embedding, so the arg-max is the permutation's pre-image of that token
+    with a top-1 / top-2 margin far above bf16 noise, and a greedy decode walks a non-trivial, fully determined id sequence
+    through every layer, the KV cache and the adapter / LoRA paths ("make logits peaky")."""
     sd: Dict[str, Tensor] = {}
     C, I, V = cfg.n_embd, cfg.intermediate_size, cfg.padded_vocab_size
     qkv_out = (cfg.n_head + 2 * cfg.n_query_groups) * cfg.head_size
@@ -118,6 +126,13 @@ def synth_state_dict(cfg, variant: str, seed: int = 1337, device="cpu", lora_b_s
         sd["lm_head.adapter_scale"] = torch.ones(V, device=device, dtype=dtype)
     else:
         sd["lm_head.weight"] = linear(V, C)
+    if peaky:
+        perm = (PEAKY_A * torch.arange(V, device=device, dtype=torch.int64) + PEAKY_B) % V
+        key = "lm_head.linear.weight" if lora_keys else "lm_head.weight"
+        head = sd["transformer.wte.weight"][:V].index_select(0, perm) / math.sqrt(C)
+        # a blend with the random head keeps the other logits (and the layers' contribution to them) alive: the margin stays
+        # ~10x the bf16 noise of the logit scale instead of ~90x
+        sd[key] = (PEAKY_MIX * head + (1.0 - PEAKY_MIX) * sd[key]).contiguous()
     if variant == "relprompt":
         for name, dim in (("audio_noise_classifier", cfg.whisper_dim), ("visual_noise_classifier", cfg.raven_dim)):
             q = name + "."

@@ -255,6 +255,15 @@ int dh_argmax(const void* logits, int64_t ldl, int64_t* ids, int M, int V, void*
 int dh_relpred_fwd(const float* x, const float* w1, const float* b1, const float* w2, const float* b2,
                    const float* wc, const float* bc, float* h1, float* h2, float* pooled, float* logits, int B, int T,
                    int C, int pool, void* stream);
+/* The tail of the head alone: AvgPool1d(pool, ceil_mode) + Linear(256->3) over h2 = relu(conv2) f32 [B, T, 256], and its backward
+ * (dz2 f32 [B, T, 256] = gradient of conv2's pre-activation; dwc / dbc ACCUMULATED).  The default (tensor-core) path of
+ * `NoiseMaskClassifier` runs the two convolutions as bf16 GEMMs through dh_gemm -- a row of three consecutive frames is the
+ * K-major A operand -- and calls these for the rest; dh_relpred_fwd / dh_relpred_bwd below stay as the fp32 path
+ * (DH_RELPRED=fp32, the arithmetic of the reference on CPU). */
+int dh_relpred_head_fwd(const float* h2, const float* wc, const float* bc, float* pooled, float* logits, int B, int T, int pool,
+                        void* stream);
+int dh_relpred_head_bwd(const float* h2, const float* pooled, const float* d_logits, const float* wc, float* dz2, float* dwc,
+                        float* dbc, int B, int T, int pool, void* stream);
 /* d_logits f32 [B, n_out, 3] -> gradients of all six parameter tensors (ACCUMULATED; caller zeroes). */
 int dh_relpred_bwd(const float* x, const float* w1, const float* w2, const float* wc, const float* h1, const float* h2,
                    const float* pooled, const float* d_logits, float* dw1, float* db1, float* dw2, float* db2,
@@ -265,6 +274,12 @@ int dh_relpred_bwd(const float* x, const float* w1, const float* w2, const float
  * ------------------------------------------------------------------------------------------------- */
 /* dst bf16 [rows, cols] = src f32 [rows, cols] (ld in elements) */
 int dh_cast_f32_to_bf16(const float* src, int64_t lds, void* dst, int64_t ldd, int64_t rows, int64_t cols, void* stream);
+/* nn.Dropout(p) on a bf16 tensor of n elements (the input of the LoRA branch, ger/lora.py:94-98,165; finetune/ger.py:401 trains with
+ * p = 0.05): out = keep ? x / (1 - p) : 0.  The mask is Philox4x32-10 of (seed, offset, element index / 8): the same (seed, offset)
+ * regenerates it, so the backward recomputes dropout(x) for the factor gradients instead of saving it.  accumulate != 0: out += the
+ * masked, scaled x (the LoRA branch's gradient flowing back into x through the mask).  The keep probability is quantised to
+ * 1 - round(p * 65536) / 65536. */
+int dh_dropout_bf16(const void* x, void* out, int64_t n, float p, uint64_t seed, uint64_t offset, int accumulate, void* stream);
 /* fused AdamW over one flat fp32 bucket (torch.optim.AdamW semantics, finetune/ger.py:132) */
 int dh_adamw_step(float* param, const float* grad, float* exp_avg, float* exp_avg_sq, int64_t n, float lr, float beta1,
                   float beta2, float eps, float weight_decay, int step, float grad_scale, void* stream);

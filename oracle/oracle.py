@@ -97,16 +97,28 @@ def apply_rope(x: Tensor, cos: Tensor, sin: Tensor) -> Tensor:
     return ((x * cos) + (rotated * sin)).type_as(x)
 
 
-def lora_linear(x: Tensor, W: Tensor, A: Optional[Tensor], B: Optional[Tensor], scaling: float) -> Tensor:
-    """ger/lora.py:159-166 (dropout = identity: parity runs use p=0 / eval)."""
+# nn.Dropout on the LoRA branch input (ger/lora.py:94-98,165,373): the reference draws the mask from torch's generator.  To compare
+# the CUDA path (Philox masks) with this restatement on the SAME mask, a test may install the multiplicative masks here:
+# {(layer, "attn" | "proj"): tensor broadcastable to the branch input, already scaled by 1 / (1 - p)}.  None = identity (p = 0 / eval).
+LORA_DROPOUT_MASKS: Optional[Dict[Tuple[int, str], Tensor]] = None
+
+
+def _dropped(x: Tensor, layer: Optional[int], which: str) -> Tensor:
+    if LORA_DROPOUT_MASKS is None or layer is None or (layer, which) not in LORA_DROPOUT_MASKS:
+        return x
+    return x * LORA_DROPOUT_MASKS[(layer, which)].view_as(x)
+
+
+def lora_linear(x: Tensor, W: Tensor, A: Optional[Tensor], B: Optional[Tensor], scaling: float, layer: Optional[int] = None) -> Tensor:
+    """ger/lora.py:159-166: pretrained(x) + (dropout(x) @ A^T @ B^T) * scaling."""
     pre = F.linear(x, W)
     if A is None:
         return pre
-    return pre + (x @ A.transpose(0, 1) @ B.transpose(0, 1)) * scaling
+    return pre + (_dropped(x, layer, "proj") @ A.transpose(0, 1) @ B.transpose(0, 1)) * scaling
 
 
 def lora_qkv_linear(x: Tensor, W: Tensor, A: Optional[Tensor], B: Optional[Tensor], scaling: float,
-                    cfg: OracleConfig) -> Tensor:
+                    cfg: OracleConfig, layer: Optional[int] = None) -> Tensor:
     """ger/lora.py:367-402 with all of q,k,v enabled and n_head != n_query_groups (the split path of
     `conv1d`, :343-347).  The delta columns are laid out [q | k | v] contiguously (qkv_shapes,
     :228-234) and are added as-is onto the *group-interleaved* pretrained output (quirk Q3)."""
@@ -114,7 +126,7 @@ def lora_qkv_linear(x: Tensor, W: Tensor, A: Optional[Tensor], B: Optional[Tenso
     if A is None:
         return pre
     r = A.size(0) // 3
-    after_A = F.linear(x, A)                                   # (..., 3r)
+    after_A = F.linear(_dropped(x, layer, "attn"), A)          # (..., 3r); ger/lora.py:373 `self.lora_dropout(x)`
     kv = cfg.n_embd // cfg.q_per_kv                            # kv_embd_size, ger/lora.py:226
     shapes = (cfg.n_embd, kv, kv)
     parts = []
@@ -200,7 +212,7 @@ def attention(x: Tensor, sd: StateDict, i: int, cfg: OracleConfig, cos: Tensor, 
     scaling = cfg.alpha / cfg.r if cfg.r > 0 else 0.0
     if use_lora and (cfg.to_query or cfg.to_key or cfg.to_value):
         assert cfg.to_query and cfg.to_key and cfg.to_value, "oracle restates the all-enabled path only"
-        qkv = lora_qkv_linear(x, Wqkv, sd[p + "attn.lora_A"], sd[p + "attn.lora_B"], scaling, cfg)
+        qkv = lora_qkv_linear(x, Wqkv, sd[p + "attn.lora_A"], sd[p + "attn.lora_B"], scaling, cfg, layer=i)
     else:
         qkv = F.linear(x, Wqkv)
     q, k, v = split_qkv(qkv, cfg)
@@ -218,7 +230,7 @@ def attention(x: Tensor, sd: StateDict, i: int, cfg: OracleConfig, cos: Tensor, 
     y = y.reshape(B, T, C)
     Wp = _w(sd, p + "proj", lk)
     if use_lora and cfg.to_projection:
-        y = lora_linear(y, Wp, sd[p + "proj.lora_A"], sd[p + "proj.lora_B"], scaling)
+        y = lora_linear(y, Wp, sd[p + "proj.lora_A"], sd[p + "proj.lora_B"], scaling, layer=i)
     else:
         y = F.linear(y, Wp)
     return y, kv_cache
@@ -365,11 +377,14 @@ def generate_greedy(sd: StateDict, cfg: OracleConfig, prompt: Tensor, max_return
 # RelPrompt reliability predictors
 # --------------------------------------------------------------------------------------------
 
-def noise_mask_classifier(x: Tensor, sd: StateDict, prefix: str, pool_size: int) -> Tensor:
-    """ger/relprompt.py:126-147 (dropout = identity).  x (B, T, C) -> logits (B, ceil(T/pool), 3).
+def noise_mask_classifier(x: Tensor, sd: StateDict, prefix: str, pool_size: int, dropout_mask: Optional[Tensor] = None) -> Tensor:
+    """ger/relprompt.py:126-147.  x (B, T, C) -> logits (B, ceil(T/pool), 3).  `dropout_mask` (B, T, 256), already scaled by
+    1 / (1 - p): the nn.Dropout between the convolutions (:141) with a mask supplied by the test; None = identity (eval).
     AvgPool1d(ceil_mode=True): the last, partial window averages over its valid frames only."""
     h = x.transpose(1, 2)
     h = F.relu(F.conv1d(h, sd[prefix + "conv1.weight"], sd[prefix + "conv1.bias"], padding=1))
+    if dropout_mask is not None:
+        h = h * dropout_mask.transpose(1, 2)
     h = F.relu(F.conv1d(h, sd[prefix + "conv2.weight"], sd[prefix + "conv2.bias"], padding=1))
     B, C, T = h.shape
     n_out = -(-T // pool_size)

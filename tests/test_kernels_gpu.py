@@ -751,3 +751,37 @@ def test_valid_row_compaction_and_bounded_gemm():
     ops.gemm(h_c, w, out, m_limit=count)
     torch.cuda.synchronize()
     assert int(count) == 0
+
+
+@pytest.mark.parametrize("p", [0.05, 0.5])
+def test_dropout_bf16_statistics_and_determinism(p):
+    """dh_dropout_bf16 (the LoRA branch's nn.Dropout, ger/lora.py:94-98,165): keep rate within 5 sigma of 1 - p, kept values =
+    x / (1 - p) exactly (p quantised to 16 bits), the mean is preserved, the same (seed, offset) regenerates the mask bit for
+    bit, another offset or seed gives an independent one, and `accumulate` adds the masked tensor onto the output."""
+    n = 1 << 22
+    x = torch.ones(n, device=DEV, dtype=torch.bfloat16)
+    a, b, c, d = (torch.empty_like(x) for _ in range(4))
+    ops.dropout_bf16(x, a, p, 1234, 7)
+    ops.dropout_bf16(x, b, p, 1234, 7)
+    ops.dropout_bf16(x, c, p, 1234, 8)
+    ops.dropout_bf16(x, d, p, 99, 7)
+    torch.cuda.synchronize()
+    assert torch.equal(a, b)
+    keep = float((a != 0).float().mean())
+    sigma = (p * (1 - p) / n) ** 0.5
+    assert abs(keep - (1 - p)) < 5 * sigma + 1e-4, (keep, 1 - p)
+    q = round(p * 65536) / 65536
+    kept = a[a != 0].float()
+    assert float((kept - 1 / (1 - q)).abs().max()) < 2 ** -7 / (1 - q)          # one bf16 rounding of 1 / (1 - p)
+    assert abs(float(a.float().mean()) - 1.0) < 5 * sigma / (1 - p) + 4e-3
+    for other in (c, d):                                                        # independent masks: joint keep rate = (1 - p)^2
+        both = float(((a != 0) & (other != 0)).float().mean())
+        assert abs(both - (1 - p) ** 2) < 6 * sigma + 1e-3, both
+    y = rnd((4096, 512), 901, 2.0)
+    base = rnd((4096, 512), 902, 2.0)
+    m = torch.empty_like(y)
+    ops.dropout_bf16(y, m, p, 5, 3)
+    acc = base.clone()
+    ops.dropout_bf16(y, acc, p, 5, 3, accumulate=True)
+    torch.cuda.synchronize()
+    assert rel(acc, base.float() + m.float()) < 4e-3

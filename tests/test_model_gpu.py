@@ -90,15 +90,21 @@ def test_tiny_against_reference_golden(variant):
     check_grads(m, {k[5:]: t(g[k]) for k in g if k.startswith("grad.")}, 0.995, variant)
 
 
-def test_tiny_relprompt_against_reference_golden():
+def test_tiny_relprompt_against_reference_golden(monkeypatch):
     g = load_golden("tiny_relprompt.npz")
     m, _ = build("relprompt", whisper_dim=48, raven_dim=32, pool_size=5)
     m.eval()
     B = g["idx"].shape[0]
     af = synthetic.synth_features(B, 103, 48, SEED, 301, DEV)
     vf = synthetic.synth_features(B, 52, 32, SEED, 302, DEV)
+    # the fp32 CUDA-core head reproduces the reference's fp32 logits to 1e-4; the default tensor-core head (bf16 operands, what the
+    # rest of this test trains through) to bf16 tolerance
+    monkeypatch.setenv("DH_RELPRED", "fp32")
     al, vl = m.audio_noise_classifier(af), m.visual_noise_classifier(vf)
     assert rel_err(al.detach().cpu(), t(g["audio_logits"])) < 1e-4 and rel_err(vl.detach().cpu(), t(g["visual_logits"])) < 1e-4
+    monkeypatch.delenv("DH_RELPRED")
+    al, vl = m.audio_noise_classifier(af), m.visual_noise_classifier(vf)
+    assert rel_err(al.detach().cpu(), t(g["audio_logits"])) < 1.5e-2 and rel_err(vl.detach().cpu(), t(g["visual_logits"])) < 1.5e-2
     at, vt = t(g["audio_targets"]).to(DEV), t(g["visual_targets"]).to(DEV)
     # finetune/relprompt.py:360-387 (trim to the common length), through this package's CE kernel
     na, nv = min(al.size(1), at.size(1)), min(vl.size(1), vt.size(1))
@@ -111,7 +117,7 @@ def test_tiny_relprompt_against_reference_golden():
     llm = chunked_cross_entropy(logits, labels[..., 1:])
     loss = llm + 0.02 * ml
     loss.backward()
-    assert abs(float(ml) - float(g["mask_loss"])) < 1e-3
+    assert abs(float(ml) - float(g["mask_loss"])) < 1e-2
     assert abs(float(llm) - float(g["llm_loss"])) < 5e-3
     ref = {}
     for k in g:
@@ -267,8 +273,8 @@ def test_relprompt_inference_glue():
     assert [p.numel() for p in a_pred] == [10, 8, 5] and [p.numel() for p in v_pred] == [10, 8, 5]
     for b in range(Bn):
         ra, rv = ref_a[b, : a_pred[b].numel()], ref_v[b, : v_pred[b].numel()]
-        clear_a = (ra.topk(2).values[:, 0] - ra.topk(2).values[:, 1]) > 1e-3
-        clear_v = (rv.topk(2).values[:, 0] - rv.topk(2).values[:, 1]) > 1e-3
+        clear_a = (ra.topk(2).values[:, 0] - ra.topk(2).values[:, 1]) > 2e-2 * ra.abs().max()      # bf16 head: skip near-ties
+        clear_v = (rv.topk(2).values[:, 0] - rv.topk(2).values[:, 1]) > 2e-2 * rv.abs().max()
         assert torch.equal(a_pred[b].cpu()[clear_a], ra.argmax(-1)[clear_a])
         assert torch.equal(v_pred[b].cpu()[clear_v], rv.argmax(-1)[clear_v])
     prompts = [p.to(DEV) for p in synthetic.synth_prompts(Bn, 500, SEED + 5, prompt_range=(24, 40))]
@@ -476,3 +482,197 @@ def test_full_tinyllama_greedy_decode_against_oracle():
             clear += 1
     assert clear >= 4, f"only {clear} decode positions agreed with the oracle"
     m.reset_cache()
+
+
+def test_lora_dropout_matches_oracle_on_the_same_masks():
+    """LoRA dropout in training (ger/lora.py:94-98,165,373; finetune/ger.py:401 trains with p = 0.05).  The engine draws Philox
+    masks from (seed, 2 * layer [+ 1]); the test reads the same masks back through dh_dropout_bf16 on a tensor of ones, installs
+    them in the oracle (oracle.LORA_DROPOUT_MASKS) and compares loss and LoRA gradients; the same torch seed repeats the step
+    bit for bit, another seed changes it, eval() ignores dropout."""
+    from dualhyp_b200 import ops
+    p_drop = 0.25
+    m, sd = build("lora", dropout=p_drop)
+    cfg = tiny_cfg("lora")
+    B, T, C = 3, 48, cfg.n_embd
+    idx, labels = synthetic.synth_batch(B, T, 512, SEED + 5, prompt_range=(20, 40))
+    idx_d, labels_d = idx.to(DEV), labels.to(DEV)
+    m.train()
+    torch.manual_seed(777)
+    seed = int(torch.randint(0, 2 ** 62, (1,), dtype=torch.int64).item())       # what GPT._dropout_seed() will draw next
+    torch.manual_seed(777)
+    loss = train_step(m, idx_d, labels_d)
+    g1 = {n: p.grad.clone() for n, p in m.named_parameters() if p.grad is not None}
+    ones = torch.ones((B * T, C), device=DEV, dtype=torch.bfloat16)
+    masks = {}
+    for i in range(cfg.n_layer):
+        for off, which in ((0, "attn"), (1, "proj")):
+            mk = torch.empty_like(ones)
+            ops.dropout_bf16(ones, mk, p_drop, seed, 2 * i + off)
+            masks[(i, which)] = mk.float().cpu().view(B, T, C)
+    assert 0.6 < float((masks[(0, "attn")] != 0).float().mean()) < 0.9
+    O.LORA_DROPOUT_MASKS = masks
+    try:
+        ref_loss, ref_grads = O.loss_and_grads(sd, cfg, idx, labels, "train")
+    finally:
+        O.LORA_DROPOUT_MASKS = None
+    assert abs(float(loss) - float(ref_loss)) < max(2e-2 * 0.25, 5e-3 * float(ref_loss)), (float(loss), float(ref_loss))
+    check_grads(m, ref_grads, 0.995, "lora dropout")
+    ref0, _ = O.loss_and_grads(sd, cfg, idx, labels, "train")                    # the masks matter: p = 0 gives another loss
+    assert abs(float(ref0) - float(ref_loss)) > 1e-4
+    m.zero_grad(set_to_none=True)
+    torch.manual_seed(777)
+    loss2 = train_step(m, idx_d, labels_d)
+    assert float(loss2) == float(loss)
+    for n, p in m.named_parameters():
+        if p.grad is not None:
+            assert torch.equal(p.grad, g1[n]), n
+    m.zero_grad(set_to_none=True)
+    torch.manual_seed(778)
+    assert float(train_step(m, idx_d, labels_d)) != float(loss)
+    m.eval()
+    m.zero_grad(set_to_none=True)
+    le = train_step(m, idx_d, labels_d)
+    assert abs(float(le) - float(ref0)) < max(2e-2 * 0.25, 5e-3 * float(ref0))
+
+
+@pytest.mark.parametrize("variant", ["adapter", "lora"])
+def test_full_tinyllama_greedy_64_tokens_identical_to_oracle(variant):
+    """TinyLlama-1.1B shapes, ALL 64 greedy ids of every sequence identical to the fp32 CPU oracle's `generate_greedy`
+    (generate/base.py:19-82 restated).  A random-init decoder has near-tied logits, so the fixture is the `peaky` one of
+    dualhyp_b200.synthetic (head tied to a permutation of the embedding, blended with the random head): the test first checks that
+    the ORACLE's top-1 / top-2 margin is at least 10 % of the logit scale at every step -- several times the bf16 noise -- and then
+    demands exact equality.  Adapter: prefix attention + gates in every layer; LoRA: the un-merged factors ride the decode
+    GEMMs' K-extension.  Batched decode over the CUDA graph, prompts of different lengths."""
+    if variant == "adapter":
+        cfg_m = adapter.Config.from_name("tiny-llama-1.1b")
+        m = adapter.GPT(cfg_m)
+    else:
+        cfg_m = lora.Config.from_name("tiny-llama-1.1b", **LORA)
+        m = lora.GPT(cfg_m)
+    sd = synthetic.synth_state_dict(cfg_m, variant, SEED, peaky=True)
+    m.load_state_dict(sd, strict=True)
+    m = m.to(DEV)
+    cfg = full_cfg(variant)
+    prompts = synthetic.synth_prompts(2, 32000, SEED + 9, prompt_range=(150, 210))
+    n_new = 64
+    outs = generate_batch(m, [p.to(DEV) for p in prompts], n_new)
+    for p, o in zip(prompts, outs):
+        ref, step_logits = O.generate_greedy(sd, cfg, p, p.numel() + n_new, return_logits=True)
+        for i, lg in enumerate(step_logits):
+            top2 = lg.float().topk(2).values
+            assert float(top2[0] - top2[1]) >= 0.1 * float(lg.float().abs().max()), f"fixture not peaky at step {i}"
+        assert o.tolist() == ref.tolist()
+        assert len(set(o[p.numel():].tolist())) >= 16, "the decode should walk distinct ids, not repeat one"
+    m.reset_cache()
+
+
+@pytest.mark.parametrize("variant", ["adapter", "lora"])
+def test_bench_shape_step_against_golden(variant):
+    """The fine-tune step at bench.py's shapes (adapter 16 x 512 = the CTA-pair GEMMs' persistent schedule over 32 x N/256 tiles,
+    the fused loss's valid-row compaction at ~3 % of the rows; LoRA 8 x 512) against the fp32 CPU oracle's loss and PEFT
+    gradients, computed once on the build box (oracle/make_golden_bench_shape.py -> tests/golden/bench_shape_*.npz).  Then the
+    same samples packed into one row without their pad tokens (what bench.py times) must give the same loss and gradients."""
+    from oracle.make_golden_bench_shape import bench_batch, model_config
+    g = load_golden(f"bench_shape_{variant}.npz")
+    cfg_m = model_config(variant)
+    m = (adapter.GPT if variant == "adapter" else lora.GPT)(cfg_m)
+    sd = synthetic.synth_state_dict(cfg_m, variant, SEED)
+    m.load_state_dict(sd, strict=True)
+    (adapter.mark_only_adapter_as_trainable if variant == "adapter" else lora.mark_only_lora_as_trainable)(m)
+    m = m.to(DEV)
+    idx, labels = bench_batch(variant)
+    assert list(idx.shape) == g["shape"].tolist() and int(idx.sum()) == int(g["ids_checksum"]) and int(labels.sum()) == int(g["labels_checksum"])
+    loss = train_step(m, idx.to(DEV), labels.to(DEV))
+    ref_loss = float(g["loss_train"])
+    assert abs(float(loss) - ref_loss) < max(2e-2 * ref_loss, 5e-3), (float(loss), ref_loss)
+    got = {n: p.grad.detach().clone() for n, p in m.named_parameters() if p.requires_grad}
+    n_full = 0
+    for key in g:
+        if key.startswith("norm/"):
+            name = key[5:]
+            nr = float(got[name].double().norm().cpu()) / max(float(g[key]), 1e-30)
+            assert abs(nr - 1) <= 5e-2, f"{variant}: grad {name} norm ratio {nr:.4f}"
+        elif key.startswith("grad/"):
+            name = key[5:]
+            c = cos_sim(got[name], t(g[key]))
+            assert c >= MIN_COS_BENCH[variant], f"{variant}: grad {name} cosine {c:.5f}"
+            n_full += 1
+    assert n_full >= 6
+    # the packed form of the same batch (no pad rows): same loss, same gradients up to bf16 re-association
+    m.zero_grad(set_to_none=True)
+    samples = _unpad(idx, labels)
+    loss_p = packed_train_step(m, samples)
+    # the train reduction divides by B * (T - 1) of the PADDED batch (quirk Q2, ger/utils.py:442-448); the packed call states the
+    # collate's T = the longest sample, the golden batch is padded to 512
+    longest = max(int(s_["input_ids"].numel()) for s_ in samples)
+    scale = (longest - 1) / (idx.shape[1] - 1)
+    assert abs(float(loss_p) * scale - float(loss)) < 2e-3 * max(1.0, abs(float(loss))), (float(loss_p), scale, float(loss))
+    for name, p in m.named_parameters():
+        if p.requires_grad:
+            assert cos_sim(p.grad, got[name]) >= 0.999, name
+
+
+MIN_COS_BENCH = {"adapter": 0.999, "lora": 0.999}
+
+
+@pytest.mark.parametrize("B,T,C,pool", [(4, 500, 1280, 20), (4, 250, 1024, 10), (3, 103, 96, 10)])
+def test_reliability_head_tensor_core_path_at_cfg4_shapes(B, T, C, pool):
+    """`NoiseMaskClassifier` (ger/relprompt.py:126-147) at the shapes RelPrompt really runs (whisper_dim 1280 x 500 frames pooled
+    by 20, raven_dim 1024 x 250 frames pooled by 10, ger/relprompt.py:212-213; 25 mask targets each) plus a ragged toy shape,
+    on the default tensor-core path: logits and the gradients of all six parameter tensors against the fp32 CPU oracle.
+    Tolerance: bf16 operands with fp32 accumulation over K = 3 C up to 3840 -- logits 1.5e-2 relative (Frobenius), gradients
+    cosine >= 0.995 and norm within 5 % (see grads_close); the fp32 CUDA-core path (DH_RELPRED=fp32) is held to 1e-4 by
+    tests/test_kernels_gpu.py::test_relpred_fwd_bwd.
+    Then training mode: the Dropout(0.1) between the convolutions (:141) on the mask the kernel drew, read back through
+    dh_dropout_bf16 on ones and replayed by the oracle."""
+    from dualhyp_b200 import ops
+    head = relprompt.NoiseMaskClassifier(C, pool_size=pool).to(DEV)
+    p = "h."
+    sd = {p + n: synthetic.hash_uniform(tuple(t.shape), 5, 80 + i, 1.0 / (3 * t.shape[1]) ** 0.5 if t.dim() == 3 else 0.06, DEV, bf16_exact=False)
+          for i, (n, t) in enumerate(head.named_parameters())}
+    with torch.no_grad():
+        for n, t in head.named_parameters():
+            t.copy_(sd[p + n])
+    x = synthetic.synth_features(B, T, C, 3, 70, DEV)
+    n_out = -(-T // pool)
+    dl = synthetic.hash_uniform((B, n_out, 3), 11, 71, 1.0, DEV)
+
+    def run(mask):
+        work = {k: v.cpu().clone().requires_grad_(True) for k, v in sd.items()}
+        ref = O.noise_mask_classifier(x.cpu(), work, p, pool, dropout_mask=mask)
+        ref.backward(dl.cpu())
+        return ref.detach(), {k: v.grad for k, v in work.items()}
+
+    head.eval()
+    logits = head(x)
+    logits.backward(dl)
+    ref, ref_g = run(None)
+    assert tuple(logits.shape) == (B, n_out, 3)
+    assert rel_err(logits.detach().cpu(), ref) < 1.5e-2, rel_err(logits.detach().cpu(), ref)
+    def grads_close(ref_grads, what):
+        # ReLU makes the gradient discontinuous in the pre-activations: a bf16-operand pre-activation within ~1 % of zero lands on
+        # the other side for ~1 % of the elements, each a full-size error -- so the bound is the cosine / norm pair the decoder's
+        # gradient checks use, not a Frobenius 1e-2 (measured here: 2-5 % Frobenius, growing from conv2.bias back to conv1.weight)
+        for n, t_ in head.named_parameters():
+            c = cos_sim(t_.grad, ref_grads[p + n])
+            nr = float(t_.grad.double().norm().cpu() / ref_grads[p + n].double().norm().clamp_min(1e-30))
+            assert c >= 0.995 and abs(nr - 1) <= 5e-2, f"{what}: grad {n} cosine {c:.5f} norm ratio {nr:.4f}"
+
+    grads_close(ref_g, "eval")
+    # ---- training mode: dropout between the convolutions ----
+    head.train()
+    head.zero_grad(set_to_none=True)
+    torch.manual_seed(4242)
+    seed = int(torch.randint(0, 2 ** 62, (1,), dtype=torch.int64).item())
+    torch.manual_seed(4242)
+    logits_t = head(x)
+    logits_t.backward(dl)
+    ones = torch.ones((B * T, 256), device=DEV, dtype=torch.bfloat16)
+    mk = torch.empty_like(ones)
+    ops.dropout_bf16(ones, mk, head.dropout.p, seed, 0)
+    mask = mk.float().cpu().view(B, T, 256)
+    assert 0.85 < float((mask != 0).float().mean()) < 0.95
+    ref_t, ref_gt = run(mask)
+    assert rel_err(ref_t, ref) > 1e-3                       # the mask matters
+    assert rel_err(logits_t.detach().cpu(), ref_t) < 1.5e-2
+    grads_close(ref_gt, "train")
