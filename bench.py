@@ -34,14 +34,24 @@ UNIT = "tokens/s"
 SEQ_LEN = 512
 PER_GPU_BATCH = 16
 DECODE_METRIC = "DualHyp infer utterances/s (greedy KV-cache decode, adapter TinyLlama-1.1B, 5+5 N-best prompts, 64 new tokens)"
-# dram__bytes_read.sum + dram__bytes_write.sum of one decode token step by utterances per GPU (profiles/r01zz_decode_traffic.txt;
-# ncu flushes the caches between kernels, so 0.62 GB of it are split-K partial products that stay in L2 in a graph replay)
-NCU_DECODE_DRAM_BYTES = {128: 3.99e9}
 DECODE_UTTS, DECODE_NEW = 128, 64     # 128 sequences per token step: the widest the decode GEMM's one-tile M takes
-LORA = dict(r=8, alpha=16, dropout=0.0, to_query=True, to_key=True, to_value=True, to_projection=True)
-# DRAM bytes per launch of the dominant GEMMs from one `ncu --set full` capture of this command (profiles/r01u_ncu_full_summary.txt);
-# key = (M, N, K, epilogue).  Algorithmic bytes of the SwiGLU GEMM: A 33.6 MB + B 46.1 MB + h12 184.5 MB + act 92.3 MB = 356.5 MB.
-NCU_DRAM_BYTES = {(8192, 11264, 2048, 5): 369.5e6, (8192, 2048, 5632, 2): 522.9e6, (8192, 2560, 2048, 4): 59.1e6, (8192, 2048, 2048, 2): 179.3e6}
+# LoRA as the shipped scripts train it (finetune/ger.py:397-407): r = 8, alpha = 16, dropout 0.05 on the LoRA branch, q/k/v/proj
+LORA = dict(r=8, alpha=16, dropout=0.05, to_query=True, to_key=True, to_value=True, to_projection=True)
+
+
+
+def measured_traffic():
+    """profiles/traffic.json (scripts/capture_traffic.py: ncu --set full of a build) -- valid only for the libdualhyp.so it was captured
+    from; returns ({} , why) otherwise."""
+    import hashlib
+    try:
+        t = json.load(open(os.path.join(ROOT, "profiles", "traffic.json")))
+        sha = hashlib.sha256(open(os.path.join(ROOT, "dualhyp_b200", "libdualhyp.so"), "rb").read()).hexdigest()[:16]
+    except Exception as e:  # noqa: BLE001
+        return {}, f"no capture ({type(e).__name__})"
+    if t.get("so_sha16") != sha:
+        return {}, f"profiles/traffic.json was captured from build {t.get('so_sha16')}, this run uses {sha}: not reported"
+    return t, f"{t.get('source')}, build {sha}"
 
 
 def parse_args():
@@ -59,6 +69,8 @@ def parse_args():
     ap.add_argument("--padded", action="store_true",
                     help="train on right-padded [B, T] batches like the reference's collate_fn (tokens/s then counts pad tokens); "
                          "default: the same samples packed into one row without pad tokens, tokens/s counts REAL tokens")
+    ap.add_argument("--lora-dropout", type=float, default=LORA["dropout"], help="LoRA branch dropout of the lora / relprompt workloads (reference default 0.05)")
+    ap.add_argument("--no-lora-sample", action="store_true", help="skip the LoRA (configs[2]) sample appended to the default training line")
     ap.add_argument("--utts", type=int, default=DECODE_UTTS, help="decode workload: utterances per GPU per step")
     ap.add_argument("--new-tokens", type=int, default=DECODE_NEW)
     return ap.parse_args()
@@ -329,7 +341,8 @@ def decode_line(args, r, world, utts, clocks, steps=None):
                     "ms_per_step": round(r["ms_e2e"] / steps, 3)},
             "gpu_launches": r["launches"], "clocks": clocks,
             "roofline": {"bound": "hbm", "achieved": round(ach, 1), "peak": peak, "unit": "GB/s", "frac": round(ach / peak, 4),
-                         "traffic": NCU_DECODE_DRAM_BYTES.get(args.utts),
+                         "traffic": (measured_traffic()[0].get("decode", {}).get(str(args.utts), {}) or {}).get("dram_bytes_per_token_step"),
+                         "traffic_source": measured_traffic()[1],
                          "peak_source": "measured copy bandwidth (MEASURED_PEAKS.json)" if peaks else "fallback 6.5 TB/s",
                          "kernel": "one decode token step (CUDA graph of %d kernels: lm_head, arg-max, 22 layers over the KV cache)" % r["kernels_per_token"],
                          "algorithmic_bytes_per_launch": round(r["step_bytes"]), "avg_ms": round(r["tok_ms"], 4),
@@ -362,7 +375,7 @@ def run_reference_arm(args):
 # ------------------------------------------------------------------------------------------------
 # native arm
 # ------------------------------------------------------------------------------------------------
-def build_model(workload: str, device):
+def build_model(workload: str, device, lora_dropout: float = LORA["dropout"]):
     import torch
     from dualhyp_b200 import synthetic
     from dualhyp_b200.ger import adapter, lora
@@ -373,18 +386,66 @@ def build_model(workload: str, device):
         adapter.mark_only_adapter_as_trainable(model)
     elif workload == "relprompt":
         from dualhyp_b200.ger import relprompt
-        cfg = relprompt.Config.from_name("tiny-llama-1.1b", r=16, alpha=32, to_query=True, to_key=True, to_value=True, to_projection=True)
+        cfg = relprompt.Config.from_name("tiny-llama-1.1b", r=16, alpha=32, dropout=lora_dropout, to_query=True, to_key=True, to_value=True,
+                                         to_projection=True)
         model = relprompt.GPT(cfg)
         model.resize_token_embeddings(3)           # <<C>> <<M>> <<N>> (finetune/relprompt.py:168)
         model.load_state_dict(synthetic.synth_state_dict(cfg, "relprompt", 1337, extra_wte_rows=3), strict=True)
         relprompt.mark_only_lora_as_trainable(model)
-        model.eval()                               # classifier dropout off (the kernel does not apply it)
+        model.train()                              # LoRA dropout and the classifiers' Dropout(0.1) are live, as in finetune/relprompt.py
     else:
-        cfg = lora.Config.from_name("tiny-llama-1.1b", **LORA)
+        cfg = lora.Config.from_name("tiny-llama-1.1b", **{**LORA, "dropout": lora_dropout})
         model = lora.GPT(cfg)
         model.load_state_dict(synthetic.synth_state_dict(cfg, "lora", 1337), strict=True)
         lora.mark_only_lora_as_trainable(model)
     return model.to(device)
+
+
+def lora_sample(args, dev, world: int, rank: int, timed, steps: int = 5, warmup: int = 3):
+    """BASELINE.json configs[2] next to the headline line: the LoRA r = 8 fine-tune step, GLOBAL batch 64 x seq 512 split over the
+    ranks (strong scaling: 64 / N prompts per GPU), packed rows, LoRA dropout 0.05, one flat-bucket all-reduce + fused AdamW."""
+    import torch
+    import torch.distributed as dist
+    from dualhyp_b200 import flops, synthetic
+    from dualhyp_b200.collate import pack_varlen
+    from dualhyp_b200.ger.utils import chunked_cross_entropy
+    from dualhyp_b200.parallel import FlatTrainables
+    B = max(1, 64 // world)
+    model = build_model("lora", dev, args.lora_dropout)
+    model.train()
+    bucket = FlatTrainables(p for p in model.parameters() if p.requires_grad)
+    idx_h, labels_h = synthetic.synth_batch(B, SEQ_LEN, 32000, 4337 + rank)
+    samples = []
+    for b in range(B):
+        n = int((labels_h[b] != -1).nonzero().max()) + 1
+        samples.append({"input_ids": idx_h[b, :n].clone(), "labels": labels_h[b, :n].clone()})
+    longest = max(int(smp["input_ids"].numel()) for smp in samples)
+    pk = {k: v.to(dev) for k, v in pack_varlen(samples).items()}
+
+    def step():
+        logits = model.forward_packed(pk["input_ids"], pk["cu_seqlens"], pk["positions"], longest, lm_head_chunk_size=128)
+        loss = chunked_cross_entropy(logits, pk["targets"])
+        loss.backward()
+        bucket.allreduce()
+        bucket.adamw_step(lr=1e-4, weight_decay=0.01, grad_scale=1.0 / world)
+        bucket.zero_grad()
+        return loss
+
+    for _ in range(warmup):
+        step()
+    ms = timed(step, steps)
+    tok = torch.tensor([float(pk["input_ids"].numel())], device=dev)
+    if world > 1:
+        dist.all_reduce(tok)
+    lens = (pk["cu_seqlens"][1:] - pk["cu_seqlens"][:-1]).tolist()
+    rho = float((pk["targets"] != -1).sum()) / float(pk["input_ids"].numel())
+    fl = sum(flops.step_flops(model.config, "lora", 1, int(n), training=True, rho=rho) for n in lens)
+    out = {"metric": "DualHyp train tokens/s (LoRA r=8 fine-tune step, TinyLlama-1.1B, 5+5 N-best)", "value": round(float(tok) * steps / (ms / 1e3), 1),
+           "unit": UNIT, "ms_per_step": round(ms / steps, 3), "steps": steps, "scaling": "strong", "global_batch": B * world, "prompts_per_gpu": B,
+           "tokens_per_step": round(float(tok)), "lora_dropout": args.lora_dropout, "step_tflops_per_gpu": round(fl / (ms / steps / 1e3) / 1e12, 1)}
+    del model, bucket
+    torch.cuda.empty_cache()
+    return out
 
 
 def gemm_epi_name(e: int) -> str:
@@ -408,7 +469,8 @@ def run_native(args):
     if world > 1:
         dist.init_process_group("nccl", device_id=dev)
     B, T = per_gpu_batch(args, world), args.seq
-    model = build_model(args.workload, dev)
+    model = build_model(args.workload, dev, args.lora_dropout)
+    model.train()
     bucket = FlatTrainables(p for p in model.parameters() if p.requires_grad)
     idx_h, labels_h = synthetic.synth_batch(B, T, 32000, 1337 + rank)
     packed_mode = not args.padded and args.workload != "relprompt"
@@ -447,6 +509,8 @@ def run_native(args):
         return F.cross_entropy(al[:, :na].reshape(-1, 3), rel["at"][:, :na].reshape(-1)) + \
             F.cross_entropy(vl[:, :nv].reshape(-1, 3), rel["vt"][:, :nv].reshape(-1))
 
+    ar_events = None
+
     def step(idx, labels, sync=True):
         """The driver's micro-step (finetune/ger.py:278-292) with accumulation 1.  sync=False skips the gradient
         all-reduce: the instrumented roofline pass runs on rank 0 alone and must not enter a collective.
@@ -462,7 +526,14 @@ def run_native(args):
             loss = loss + 0.02 * mask_loss()
         loss.backward()
         if sync:
-            bucket.allreduce()
+            if world > 1 and ar_events is not None:      # exposed time of the gradient exchange (collective + the wait for the slowest rank)
+                ea, eb = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+                ea.record()
+                bucket.allreduce()
+                eb.record()
+                ar_events.append((ea, eb))
+            else:
+                bucket.allreduce()
         bucket.adamw_step(lr=1e-4, weight_decay=0.01, grad_scale=1.0 / world)
         bucket.zero_grad()
         return loss
@@ -490,8 +561,15 @@ def run_native(args):
         step(in_d, labels_d)
     sampler = ClockSampler(local) if rank == 0 else None
     l0 = ops.launches()
+    ar_events = [] if world > 1 else None
     ms_total = timed(lambda: step(in_d, labels_d), args.steps)
     n_launch = ops.launches() - l0
+    ar_ms = None
+    if ar_events:
+        ar_t = torch.tensor([sum(a.elapsed_time(b) for a, b in ar_events) / len(ar_events)], device=dev)
+        dist.all_reduce(ar_t, op=dist.ReduceOp.MAX)
+        ar_ms = float(ar_t)
+    ar_events = None
     clocks = sampler.stop() if sampler else None
     tok_t = torch.tensor([float(real_tokens)], device=dev)
     if world > 1:
@@ -532,6 +610,11 @@ def run_native(args):
                     "d2h_bytes_per_step": 4,
                     "ms_per_step": round(ms_e2e / args.steps, 3)},
             "gpu_launches": n_launch, "clocks": clocks}
+    if ar_ms is not None:
+        line["grad_allreduce"] = {"exposed_ms_per_step": round(ar_ms, 3), "bytes": int(bucket.numel * 4),
+                                  "note": "CUDA events around the one flat-bucket ncclAllReduce on the compute stream, max over ranks: the collective plus "
+                                          "the wait for the slowest rank's backward; every gradient materialises at the end of the backward (batched "
+                                          "prefix / LoRA reductions), so there is nothing left to overlap it with"}
     # the vocabulary projection only runs on rows with a target (valid-row compaction): credit only those flops
     rho = float((labels_h[..., 1:] != -1).sum()) / float(real_tokens)
     line["config"]["lm_head_row_fraction"] = round(rho, 4)
@@ -569,10 +652,18 @@ def run_native(args):
         M_, N_, K_, K2_, epi, al, bl = dmeta
         fl = 2.0 * M_ * N_ * (K_ + K2_)
         achieved = fl / (dms / dcount / 1e3) / 1e12
+        # the launch behind this shape: CTA-pair kernel for K-major operands, N % 256 == 0, M >= 1024 (csrc/gemm.cu dispatch_bn)
+        kname = f"gemm_pair_kernel<{epi}>" if (al == 0 and bl == 0 and N_ % 256 == 0 and M_ >= 1024) else f"gemm_kernel<*,{epi}>"
+        tr, traffic_src = measured_traffic()
+        ent = tr.get("train", {}).get(kname)
+        traffic = ent["dram_bytes_per_launch"] if ent else None
+        # A + B read once; SwiGLU writes h12 (M x N) and act (M x N/2); the others write M x N (bf16) or read + write fp32 M x N
+        alg_bytes = 2 * M_ * (K_ + K2_) + 2 * N_ * (K_ + K2_) + (2 * M_ * N_ + M_ * N_ if gemm_epi_name(epi) == "swiglu" else 2 * M_ * N_)
         line["roofline"] = {"bound": "tensor", "achieved": round(achieved, 1), "peak": peak_tf, "unit": "TFLOP/s",
-                            "frac": round(achieved / peak_tf, 4), "traffic": NCU_DRAM_BYTES.get((M_, N_, K_ + K2_, epi)), "peak_source": peak_src,
-                            "traffic_source": "dram__bytes_read.sum + dram__bytes_write.sum per launch, ncu --set full (profiles/r01u_ncu_full_summary.txt)",
-                            "kernel": f"gemm_kernel<256,{gemm_epi_name(epi)}> M={M_} N={N_} K={K_}", "launches": dcount,
+                            "frac": round(achieved / peak_tf, 4), "traffic": traffic, "peak_source": peak_src,
+                            "traffic_source": traffic_src,
+                            "algorithmic_bytes": alg_bytes,
+                            "kernel": f"{kname} ({gemm_epi_name(epi)} epilogue) M={M_} N={N_} K={K_ + K2_}", "launches": dcount,
                             "avg_ms": round(dms / dcount, 4), "share_of_step": round(dms / total_ms, 4),
                             "all_gemms": {"tflops": round(gemm_fl / (gemm_ms / 1e3) / 1e12, 1), "share_of_step": round(gemm_ms / total_ms, 4)},
                             "by_op_ms_per_step": {n: round(sum(v[1] for k, v in agg.items() if k[0] == n) / 2, 3)
@@ -590,6 +681,11 @@ def run_native(args):
             d = decode_line(args, r, world, world * args.utts * 2, None, steps=2)
             line["infer"] = {"metric": DECODE_METRIC, "value": d["value"], "unit": "utt/s", "e2e": d["e2e"], "ms_per_batch": d["ms_per_step"],
                              "utterances_per_gpu": args.utts, "new_tokens": args.new_tokens, "roofline": d["roofline"]}
+    if args.workload == "adapter" and not args.no_lora_sample:
+        model._engine.release_buffers()
+        ls = lora_sample(args, dev, world, rank, timed)
+        if rank == 0:
+            line["lora"] = ls
     if rank == 0 and world == 1 and not args.no_cpu_baseline:
         tps, ms, cores, sample = cpu_step_tokens_per_s(args.workload, T, 4, 1)      # ~7 s of CPU work (1 warm-up + 4 timed steps)
         line["cpu_baseline"] = {"value": round(tps, 2), "unit": UNIT, "cores": cores, "kind": "port", "sample": sample}

@@ -313,12 +313,13 @@ class DecoderEngine:
         n = _buf("n", (M, C), bf)
         act = _buf("act", (M, I), bf)
         # LoRA dropout (training only): the LoRA branch multiplies dropout(x), the frozen path the plain x (ger/lora.py:159-166).
-        # The mask is Philox(seed, offset = 2 * layer [+ 1 for proj]); backward() regenerates it from the same pair.
+        # The mask is Philox(seed, offset = 2 * layer [+ 1 for proj]); backward() regenerates it from the same pair for d(x).
         use_do = save and dropout_seed is not None and s.variant == "lora" and s.lora_dropout > 0
         saved = dict(B=B, T=T, layers=[], packed=packed, varlen=varlen, dropout_seed=dropout_seed if use_do else None) if save else None
         pkv_all = self._project_prefixes(packed, "pkv_all")
         for i, lw in enumerate(self.layers):
             pk = packed.get(i, {})
+            nd_i = yd_i = None
             rstd1 = _buf(per("rstd1_", i), (M,), f32)
             n_i = _buf(per("n1_", i), (M, C), bf) if (save and "qkv_a" in pk) else n
             ops.rmsnorm_fwd(x, lw["norm1"], n_i, rstd1, s.norm_eps)
@@ -327,8 +328,8 @@ class DecoderEngine:
             if "qkv_a" in pk:
                 a_s = _buf(per("qkv_as", i), (M, LORA_PAD), bf)
                 src = n_i
-                if use_do:
-                    src = _buf("lora_do", (M, C), bf)
+                if use_do:       # dropout(n) is kept for the factor gradient (27 MB per layer at 6.6 k tokens; regenerating it costs a pass)
+                    src = nd_i = _buf(per("lora_do_qkv", i), (M, C), bf)
                     ops.dropout_bf16(n_i, src, s.lora_dropout, dropout_seed, 2 * i)
                 ops.gemm(src, pk["qkv_a"], a_s)
                 ops.gemm(n_i, lw["wqkv"], qkv, A2=a_s, B2=pk["qkv_b"], epilogue=ops.EPI_QKV_ROPE, rope_cos=self.cos, rope_sin=self.sin,
@@ -357,7 +358,7 @@ class DecoderEngine:
                 ap_s = _buf(per("proj_as", i), (M, LORA_PAD), bf)
                 src = y
                 if use_do:
-                    src = _buf("lora_do", (M, C), bf)
+                    src = yd_i = _buf(per("lora_do_proj", i), (M, C), bf)
                     ops.dropout_bf16(y, src, s.lora_dropout, dropout_seed, 2 * i + 1)
                 ops.gemm(src, pk["proj_a"], ap_s)
                 ops.gemm(y, lw["wproj"], xmid, A2=ap_s, B2=pk["proj_b"], epilogue=ops.EPI_RESID_F32, aux=x)
@@ -371,7 +372,7 @@ class DecoderEngine:
             ops.gemm(act, lw["wmlp"], x_next, epilogue=ops.EPI_RESID_F32, aux=xmid)
             if save:
                 saved["layers"].append(dict(x=x, xmid=xmid, rstd1=rstd1, rstd2=rstd2, qkv=qkv, y=y, lse=lse, h12=h12, n1=n_i,
-                                            a_s=a_s, ap_s=ap_s, prefix_kv=prefix_kv, gate=gate))
+                                            a_s=a_s, ap_s=ap_s, prefix_kv=prefix_kv, gate=gate, n1_do=nd_i, y_do=yd_i))
             x = x_next
         hidden = _buf("hidden", (M, C), bf)
         rstd_f = _buf("rstd_f", (M,), f32)
@@ -486,11 +487,10 @@ class DecoderEngine:
                     self._wgrad_into(dap, a["y"], lws["proj_dA"][lora_pos[i]], alpha=scaling)
                     ops.gemm(dxb, lw["wproj_t"], dy, A2=dap, B2=pk["proj_a_t"])
                 else:
-                    # the LoRA branch saw dropout(y): its factor gradient multiplies the regenerated dropout(y), and its share of
-                    # d(y) passes through the same mask, so it cannot ride the dgrad's K-extension
-                    xd, tmp = self._cap_buf("lora_do", (M, C), bf), self._cap_buf("lora_do_g", (M, C), bf)
-                    ops.dropout_bf16(a["y"], xd, s.lora_dropout, do_seed, 2 * i + 1)
-                    self._wgrad_into(dap, xd, lws["proj_dA"][lora_pos[i]], alpha=scaling)
+                    # the LoRA branch saw dropout(y): its factor gradient multiplies the saved dropout(y), and its share of d(y) passes
+                    # through the same mask (regenerated from (seed, offset)), so it cannot ride the dgrad's K-extension
+                    tmp = self._cap_buf("lora_do_g", (M, C), bf)
+                    self._wgrad_into(dap, a["y_do"], lws["proj_dA"][lora_pos[i]], alpha=scaling)
                     ops.gemm(dxb, lw["wproj_t"], dy)
                     ops.gemm(dap, pk["proj_a_t"], tmp)
                     ops.dropout_bf16(tmp, dy, s.lora_dropout, do_seed, 2 * i + 1, accumulate=True)
@@ -522,9 +522,8 @@ class DecoderEngine:
                     if i > first:
                         ops.gemm(dqkv, lw["wqkv_t"], dn, A2=da_s, B2=pk["qkv_a_t"])
                 else:
-                    xd, tmp = self._cap_buf("lora_do", (M, C), bf), self._cap_buf("lora_do_g", (M, C), bf)
-                    ops.dropout_bf16(a["n1"], xd, s.lora_dropout, do_seed, 2 * i)
-                    self._wgrad_into(da_s, xd, lws["qkv_dA"][lora_pos[i]], alpha=scaling)
+                    tmp = self._cap_buf("lora_do_g", (M, C), bf)
+                    self._wgrad_into(da_s, a["n1_do"], lws["qkv_dA"][lora_pos[i]], alpha=scaling)
                     if i > first:
                         ops.gemm(dqkv, lw["wqkv_t"], dn)
                         ops.gemm(da_s, pk["qkv_a_t"], tmp)

@@ -454,7 +454,7 @@ def test_full_tinyllama_step_against_oracle(variant, B, T):
     torch.set_num_threads(max(1, torch.get_num_threads()))
     ref_loss, ref_grads = O.loss_and_grads(sd, cfg, idx, labels, "train")
     assert abs(float(loss) - float(ref_loss)) < max(2e-2 * float(ref_loss), 5e-3), (float(loss), float(ref_loss))
-    check_grads(m, ref_grads, 0.999 if variant == "lora" else 0.99, variant)
+    check_grads(m, ref_grads, 0.999, variant)
 
 
 def test_full_tinyllama_greedy_decode_against_oracle():
