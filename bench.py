@@ -34,7 +34,7 @@ UNIT = "tokens/s"
 SEQ_LEN = 512
 PER_GPU_BATCH = 16
 DECODE_METRIC = "DualHyp infer utterances/s (greedy KV-cache decode, adapter TinyLlama-1.1B, 5+5 N-best prompts, 64 new tokens)"
-DECODE_UTTS, DECODE_NEW = 128, 64     # 128 sequences per token step: the widest the decode GEMM's one-tile M takes
+DECODE_UTTS, DECODE_NEW = 256, 64     # 256 sequences per token step: two 128-row activation boxes stream each weight tile once
 # LoRA as the shipped scripts train it (finetune/ger.py:397-407): r = 8, alpha = 16, dropout 0.05 on the LoRA branch, q/k/v/proj
 LORA = dict(r=8, alpha=16, dropout=0.05, to_query=True, to_key=True, to_value=True, to_projection=True)
 
@@ -66,6 +66,7 @@ def parse_args():
     ap.add_argument("--no-cpu-baseline", action="store_true")
     ap.add_argument("--no-roofline", action="store_true")
     ap.add_argument("--no-infer", action="store_true", help="skip the decode sample appended to the training line")
+    ap.add_argument("--no-e2e", action="store_true", help="profiling runs only (scripts/profile_step.sh): skip the end-to-end leg, `e2e` is then null")
     ap.add_argument("--padded", action="store_true",
                     help="train on right-padded [B, T] batches like the reference's collate_fn (tokens/s then counts pad tokens); "
                          "default: the same samples packed into one row without pad tokens, tokens/s counts REAL tokens")
@@ -588,9 +589,13 @@ def run_native(args):
         i_d = idx_h.to(dev, non_blocking=True)
         l_d = labels_h.to(dev, non_blocking=True)
         losses.append(step(i_d, l_d).item())
-    for _ in range(2):
-        e2e_step()
-    ms_e2e = timed(e2e_step, args.steps)
+    if args.no_e2e:
+        losses.append(float(step(in_d, labels_d)))
+        ms_e2e = float("nan")
+    else:
+        for _ in range(2):
+            e2e_step()
+        ms_e2e = timed(e2e_step, args.steps)
     e2e_value = tokens / (ms_e2e / 1e3)
 
     line = {"metric": metric_name(args), "value": round(value, 1), "unit": UNIT, "n_gpus": world, "steps": args.steps, "warmup": max(args.warmup, 3),
@@ -605,7 +610,7 @@ def run_native(args):
                                           "all B x T positions of the right-padded batch (pad tokens included, as the reference computes them)"),
                        "tokens_per_step": round(tokens_per_step), "padded_positions_per_step": world * B * longest,
                        "padded_equivalent_tokens_per_s": round(world * B * longest * args.steps / (ms_total / 1e3), 1)},
-            "e2e": {"value": round(e2e_value, 1), "unit": UNIT,
+            "e2e": None if args.no_e2e else {"value": round(e2e_value, 1), "unit": UNIT,
                     "h2d_bytes_per_step": (sum(v.numel() * v.element_size() for v in pk_h.values()) if packed_mode else 2 * B * T * 8),
                     "d2h_bytes_per_step": 4,
                     "ms_per_step": round(ms_e2e / args.steps, 3)},

@@ -1790,7 +1790,9 @@ static int attention_bwd_impl(const void* qkv, const void* out, const void* dout
       pattr = true;
     }
     const int ntiles = (int)((M + 127) / 128);
-    int gx = (2 * sm_count() + p.H - 1) / p.H;
+    // two CTAs per SM and ONE wave: rounding the column count up (10 x 32 heads = 320 CTAs on 296 slots) left 24 CTAs to a second
+    // wave that cost as much as the first
+    int gx = (2 * sm_count()) / p.H;
     if (gx > ntiles) gx = ntiles;
     if (gx < 1) gx = 1;
     attn_bwd_prefix_kernel<<<dim3(gx, p.H), PFX_THREADS, PFX_SMEM, s>>>(tQ, tDO, tO, tP, p);

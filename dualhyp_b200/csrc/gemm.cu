@@ -344,6 +344,7 @@ gemm_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant__ CUt
 // parks its fp32 partial tile in its own shared memory, and after one cluster barrier the tile's (row, 64-column)
 // units are dealt round-robin to the S CTAs, each summing the S partials over DISTRIBUTED SHARED MEMORY in rank
 // order (deterministic) and running the fused epilogue.  No global workspace, no atomics.
+// 128 < M <= 256: two activation boxes per stage and two TMEM accumulators, the weight tile is streamed once for both.
 // M <= 64 loads only a 64-row A box: the accumulator rows 64..127 are then garbage computed from whatever the
 // B tile behind it holds (MMA rows are independent) and are never read, so a stage is 8 KB of A + 16 KB of W.
 // Roles as gemm_kernel: warp 0 TMA, warp 1 MMA, warp 2 TMEM, warps 4-7 epilogue.
@@ -370,7 +371,9 @@ gemm_skinny_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constan
                    const __grid_constant__ CUtensorMap tmA2, const __grid_constant__ CUtensorMap tmB2, const GemmParams p) {
   extern __shared__ uint8_t smem_raw[];
   uint8_t* smem = reinterpret_cast<uint8_t*>((reinterpret_cast<uintptr_t>(smem_raw) + 1023) & ~uintptr_t(1023));
-  const int a_bytes = p.M <= 64 ? 64 * BK * 2 : BM * BK * 2;
+  const int MB = p.M > BM ? 2 : 1;                       // row blocks: up to 256 activation rows stream the same weight tile
+  const int a_box_bytes = p.M <= 64 ? 64 * BK * 2 : BM * BK * 2;
+  const int a_bytes = a_box_bytes * MB;
   const int stage_bytes = a_bytes + SK_B_BYTES;
   const int stages = p.sk_stages;
   uint64_t* bars = reinterpret_cast<uint64_t*>(smem + stages * stage_bytes);
@@ -399,7 +402,7 @@ gemm_skinny_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constan
     fence_barrier_init();
   }
   if (warp == 2) {
-    tmem_alloc(tmem_slot, SK_BN);
+    tmem_alloc(tmem_slot, 2 * SK_BN);                    // one accumulator per row block
     tmem_relinquish();
   }
   pdl_launch_dependents();
@@ -434,6 +437,7 @@ gemm_skinny_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constan
         tma_load_2d(sb, second ? &tmB2 : &tmB, k0, n0, &full_bar[s]);
       }
       tma_load_2d(sa, second ? &tmA2 : &tmA, k0, 0, &full_bar[s]);
+      if (MB == 2) tma_load_2d(sa + a_box_bytes, second ? &tmA2 : &tmA, k0, BM, &full_bar[s]);
     }
   } else if (warp == 1) {
     pdl_wait();
@@ -446,9 +450,12 @@ gemm_skinny_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constan
       const uint32_t sa = smem_u32(smem + s * stage_bytes);
       const uint32_t sb = sa + a_bytes;
       if (elect_one()) {
+        for (int rb = 0; rb < MB; ++rb) {
 #pragma unroll
-        for (int k = 0; k < BK / 16; ++k)
-          tc_mma_ss(tmem_base, umma_desc_sw128(sa + k * 32, 16, 1024), umma_desc_sw128(sb + k * 32, 16, 1024), idesc, (it | k) != 0);
+          for (int k = 0; k < BK / 16; ++k)
+            tc_mma_ss(tmem_base + rb * SK_BN, umma_desc_sw128(sa + rb * a_box_bytes + k * 32, 16, 1024), umma_desc_sw128(sb + k * 32, 16, 1024),
+                      idesc, (it | k) != 0);
+        }
         tc_commit(&empty_bar[s]);
         if (kb == kb_end - 1) tc_commit(tfull_bar);
       }
@@ -458,20 +465,22 @@ gemm_skinny_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constan
     pdl_wait();
     // park this CTA's partial rows in shared memory (the ring is idle once the last MMA has completed)
     const int q = warp & 3;
-    const int r = q * 32 + lane;
     mbar_wait(tfull_bar, 0);
     tc_fence_after();
-    float* prow = reinterpret_cast<float*>(smem) + (size_t)r * SK_PAD;
+    for (int rb = 0; rb < MB; ++rb) {
+      const int r = rb * BM + q * 32 + lane;
+      float* prow = reinterpret_cast<float*>(smem) + (size_t)r * SK_PAD;
 #pragma unroll 1
-    for (int c = 0; c < SK_BN / 32; ++c) {
-      uint32_t r0[32];
-      tmem_ld32(tmem_base + ((uint32_t)(q * 32) << 16) + c * 32, r0);
-      tmem_wait_ld();
-      if (r < p.M) {
+      for (int c = 0; c < SK_BN / 32; ++c) {
+        uint32_t r0[32];
+        tmem_ld32(tmem_base + ((uint32_t)(q * 32) << 16) + rb * SK_BN + c * 32, r0);
+        tmem_wait_ld();
+        if (r < p.M) {
 #pragma unroll
-        for (int i = 0; i < 8; ++i)
-          *reinterpret_cast<float4*>(prow + c * 32 + 4 * i) =
-              make_float4(__uint_as_float(r0[4 * i]), __uint_as_float(r0[4 * i + 1]), __uint_as_float(r0[4 * i + 2]), __uint_as_float(r0[4 * i + 3]));
+          for (int i = 0; i < 8; ++i)
+            *reinterpret_cast<float4*>(prow + c * 32 + 4 * i) =
+                make_float4(__uint_as_float(r0[4 * i]), __uint_as_float(r0[4 * i + 1]), __uint_as_float(r0[4 * i + 2]), __uint_as_float(r0[4 * i + 3]));
+        }
       }
     }
   }
@@ -485,13 +494,14 @@ gemm_skinny_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constan
     const int t = threadIdx.x - 128;
     if (S == 1) {
       const int q = warp & 3;
-      const int row = q * 32 + lane;
       mbar_wait(tfull_bar, 0);
       tc_fence_after();
 #pragma unroll 1
-      for (int c = 0; c < SK_BN / 64; ++c) {
+      for (int cc = 0; cc < MB * (SK_BN / 64); ++cc) {
+        const int rb = cc / (SK_BN / 64), c = cc % (SK_BN / 64);
+        const int row = rb * BM + q * 32 + lane;
         uint32_t r0[32], r1[32];
-        const uint32_t taddr = tmem_base + ((uint32_t)(q * 32) << 16) + c * 64;
+        const uint32_t taddr = tmem_base + ((uint32_t)(q * 32) << 16) + rb * SK_BN + c * 64;
         tmem_ld32(taddr, r0);
         tmem_ld32(taddr + 32, r1);
         tmem_wait_ld();
@@ -549,7 +559,7 @@ gemm_skinny_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constan
   if (S > 1) cluster_sync_any();       // nobody leaves while a peer may still read its partial tile
   if (warp == 2) {
     tc_fence_after();
-    tmem_dealloc(tmem_base, SK_BN);
+    tmem_dealloc(tmem_base, 2 * SK_BN);
   }
 }
 
@@ -1141,7 +1151,7 @@ static int launch_gemm_skinny(const dh_gemm_args* a, cudaStream_t stream) {
   // (two per GPC would need 16 free SMs in every GPC), which doubles the time -- hence the cap of 4.
   int S = 1;
   while (S < 4 && tiles * (2 * S) <= sm_count() && nkb / (2 * S) >= 2) S *= 2;
-  const int stage_bytes = box_m * BK * 2 + SK_B_BYTES;
+  const int stage_bytes = box_m * BK * 2 * (a->M > BM ? 2 : 1) + SK_B_BYTES;      // two activation boxes per stage for 128 < M <= 256
   int stages = SK_RING_BYTES / stage_bytes;
   if (stages > SK_MAX_STAGES) stages = SK_MAX_STAGES;
   const int per_cta = (nkb + S - 1) / S;
@@ -1200,7 +1210,7 @@ static int dispatch_bn(const dh_gemm_args* a, cudaStream_t stream) {
       a->N % 256 == 0 && a->M >= 1024 && a->split_k <= 1 && pair_epilogue_ok(a))
     return launch_gemm_pair<EPI>(a, stream);
   // one token per sequence (decode): weight streaming with K split over a cluster
-  if (a->M <= BM && a->N % SK_BN == 0 && a->a_layout == 0 && a->b_layout == 0 && (a->K2 == 0 || (a->a2_layout == 0 && a->b2_layout == 0)) &&
+  if (a->M <= 2 * BM && a->N % SK_BN == 0 && a->a_layout == 0 && a->b_layout == 0 && (a->K2 == 0 || (a->a2_layout == 0 && a->b2_layout == 0)) &&
       !a->m_limit && EPI != DH_EPI_SWIGLU_BWD && (EPI != DH_EPI_F32 || !a->accumulate))
     return launch_gemm_skinny<EPI>(a, stream);
   // Tile width: 256 when it divides N and leaves enough tiles to fill the machine, else 128, else 64.

@@ -701,10 +701,10 @@ class DecoderEngine:
             return hidden
         # The two residual GEMMs (attention proj, mlp proj; N = C gives only C / 128 tiles) run split-K over all SMs and
         # leave fp32 partial products; the norm that follows sums them, adds the residual and normalises in one launch.
-        sk_ok = n_seq <= 128 and C % 128 == 0
+        sk_ok = n_seq <= 256 and C % 128 == 0
         s_proj, s_mlp = (ops.decode_split_k(C, C), ops.decode_split_k(C, I)) if sk_ok else (1, 1)
         ws = self._buf("dec_splitk", (max(s_proj, s_mlp), n_seq, C), f32) if (s_proj > 1 or s_mlp > 1) else None
-        s_qkv = ops.decode_split_k(s.qkv_out, C) if (n_seq <= 128 and s.qkv_out % 128 == 0) else 1
+        s_qkv = ops.decode_split_k(s.qkv_out, C) if (n_seq <= 256 and s.qkv_out % 128 == 0) else 1
         ws_q = self._buf("dec_splitk_qkv", (s_qkv, n_seq, s.qkv_out), f32) if s_qkv > 1 else None
         ops.rmsnorm_fwd(x, self.layers[0]["norm1"], n, None, s.norm_eps)
         for i, lw in enumerate(self.layers):

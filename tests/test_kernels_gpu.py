@@ -133,9 +133,10 @@ def test_gemm_qkv_rope_epilogue():
     assert rel(gv, v[:, ::qpk]) < 6e-3, report("v", gv, v[:, ::qpk])
 
 
-@pytest.mark.parametrize("M", [1, 5, 64, 100, 128])
+@pytest.mark.parametrize("M", [1, 5, 64, 100, 128, 129, 200, 256])
 def test_gemm_skinny_decode_shapes(M):
-    """M <= 128 (decode: one token per sequence) takes the cluster split-K weight-streaming kernel: every epilogue the decode
+    """M <= 256 (decode: one token per sequence; above 128 rows a stage carries two activation boxes and the weight tile feeds two
+    TMEM accumulators) takes the cluster split-K weight-streaming kernel: every epilogue the decode
     step uses, at the TinyLlama shapes (split counts 1, 2, 8, 9, with and without the LoRA second source), is checked
     against fp32 math and must be bit-identical run to run (partials are summed in split order, not arrival order)."""
     C, I, G, qpk = 2048, 5632, 4, 8
@@ -184,7 +185,7 @@ def test_gemm_skinny_decode_shapes(M):
     assert rel(qkv.cpu().view(M, G, qpk + 2, 64), want) < 6e-3, report("splitk rope", qkv.cpu().view(M, G, qpk + 2, 64), want)
 
 
-@pytest.mark.parametrize("M,S", [(1, 9), (64, 9), (64, 3), (100, 16), (128, 8)])
+@pytest.mark.parametrize("M,S", [(1, 9), (64, 9), (64, 3), (100, 16), (128, 8), (200, 9), (256, 8)])
 def test_gemm_split_k_partials_and_fused_consumer(M, S):
     """dh_gemm split_k: slice s holds the product over K range s (their sum is the GEMM); dh_splitk_resid_rmsnorm sums
     the slices in order, adds the residual (bf16-rounded product, like DH_EPI_RESID_F32) and applies the next RMSNorm --
@@ -212,7 +213,7 @@ def test_gemm_split_k_partials_and_fused_consumer(M, S):
     assert torch.equal(x1, x2) and torch.equal(n1, n2)
 
 
-@pytest.mark.parametrize("M,G,qpk,S", [(64, 4, 8, 7), (3, 2, 2, 2), (128, 1, 1, 4)])
+@pytest.mark.parametrize("M,G,qpk,S", [(64, 4, 8, 7), (3, 2, 2, 2), (128, 1, 1, 4), (250, 4, 8, 7)])
 def test_splitk_qkv_rope_cache_consumer(M, G, qpk, S):
     """Split-K QKV partial products -> dh_splitk_qkv_rope_cache must equal the fused DH_EPI_QKV_ROPE GEMM followed by
     dh_kv_cache_write up to the summation order (checked against fp32 math at bf16 tolerance; the cache rows must be the

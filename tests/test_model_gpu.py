@@ -216,13 +216,14 @@ def test_graph_decode_equals_eager_and_is_reusable():
     m.reset_cache()
 
 
-def test_wide_batch_decode_equals_single():
-    """100 sequences per token step (the 128-row activation box of the decode GEMM, 100 x G attention blocks): every
-    sequence decodes to the ids it gets alone -- bench.py decodes 128 utterances per GPU and step."""
+@pytest.mark.parametrize("n", [100, 200])
+def test_wide_batch_decode_equals_single(n):
+    """100 / 200 sequences per token step (one / two 128-row activation boxes of the decode GEMM, n x G attention blocks): every
+    sequence decodes to the ids it gets alone -- bench.py decodes 256 utterances per GPU and step."""
     m, _ = build("adapter", adapter_start_layer=1)
-    prompts = [p.to(DEV) for p in synthetic.synth_prompts(100, 512, SEED + 9, prompt_range=(8, 70))]
+    prompts = [p.to(DEV) for p in synthetic.synth_prompts(n, 512, SEED + 9, prompt_range=(8, 70))]
     wide = generate_batch(m, prompts, 10)
-    for i in (0, 1, 37, 63, 64, 65, 98, 99):
+    for i in (0, 1, 37, 63, 64, 65, 98, n - 1, n - 2, n // 2 + 29):
         assert wide[i].tolist() == generate_batch(m, [prompts[i]], 10)[0].tolist(), i
     m.reset_cache()
 
