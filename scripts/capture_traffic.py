@@ -9,7 +9,7 @@ On the GPU box (one GPU; each only after the plain command exited 0):
         python scripts/decode_traffic.py 128
 Here:
     ncu -i gpurun_out/tr_gemm.ncu-rep --page raw --csv > gpurun_out/tr_gemm_raw.csv
-    python scripts/capture_traffic.py gpurun_out/tr_gemm_raw.csv [gpurun_out/tr_decode.csv]"""
+    python scripts/capture_traffic.py gpurun_out/tr_gemm_raw.csv [gpurun_out/tr_decode.csv [utterances]]"""
 import csv
 import hashlib
 import json
@@ -26,15 +26,33 @@ def so_hash() -> str:
 
 def main():
     out = {"so_sha16": so_hash(), "source": "ncu --set full, dram__bytes_read.sum + dram__bytes_write.sum per launch (scripts/capture_traffic.py)"}
-    rows = list(csv.DictReader(l for l in open(sys.argv[1]) if not l.startswith("==")))
-    rows = [r for r in rows if r.get("ID", "").strip().isdigit()]
+    allrows = list(csv.DictReader(l for l in open(sys.argv[1]) if not l.startswith("==")))
+    units = allrows[0]                       # the raw page's second line holds the unit of every column
+    mult = {"byte": 1.0, "kbyte": 1e3, "mbyte": 1e6, "gbyte": 1e9}
+    rows = [r for r in allrows if r.get("ID", "").strip().isdigit()]
     by = {}
     for r in rows:
-        name = re.sub(r"\(.*", "", r["Kernel Name"]).replace("void dh::", "")
-        rd, wr = float(r["dram__bytes_read.sum"].replace(",", "")), float(r["dram__bytes_write.sum"].replace(",", ""))
-        unit = 1.0
-        by.setdefault(name, []).append((rd + wr) * unit)
-    out["train"] = {k: {"launches": len(v), "dram_bytes_per_launch": round(sum(v) / len(v)), "min": round(min(v)), "max": round(max(v))} for k, v in by.items()}
+        name = re.sub(r"\(.*", "", r["Kernel Name"]).replace("void dh::", "").replace("void ", "").replace("dh::", "")
+        tot = 0.0
+        for col in ("dram__bytes_read.sum", "dram__bytes_write.sum"):
+            tot += float(r[col].replace(",", "")) * mult[units[col].strip().lower()]
+        by.setdefault(name, []).append((tot, float(r["gpu__time_duration.sum"].replace(",", ""))))
+    # one kernel name covers several GEMM shapes (the epilogue is the template argument): split launches of a name by duration class
+    split = {}
+    for name, v in by.items():
+        v.sort(key=lambda x: x[1])
+        groups = []
+        for b, t in v:
+            if groups and t < 1.25 * groups[-1][-1][1]:
+                groups[-1].append((b, t))
+            else:
+                groups.append([(b, t)])
+        for gi, g in enumerate(groups):
+            split[name if len(groups) == 1 else f"{name}#{gi}"] = g
+    by = {k: [b for b, _ in g] for k, g in split.items()}
+    dur = {k: sum(t for _, t in g) / len(g) for k, g in split.items()}
+    out["train"] = {k: {"launches": len(v), "dram_bytes_per_launch": round(sum(v) / len(v)), "min": round(min(v)), "max": round(max(v)),
+                        "ncu_duration_us": round(dur[k], 1)} for k, v in by.items()}
     if len(sys.argv) > 2:
         tot = 0.0
         steps = 0
@@ -45,7 +63,7 @@ def main():
                 tot += v * {"byte": 1, "kbyte": 1e3, "mbyte": 1e6, "gbyte": 1e9}.get(u, 1)
             if "argmax" in r.get("Kernel Name", "") and r.get("Metric Name", "") == "dram__bytes_read.sum":
                 steps += 1
-        out["decode"] = {"128": {"token_steps": steps, "dram_bytes_per_token_step": round(tot / max(steps, 1))}}
+        out["decode"] = {(sys.argv[3] if len(sys.argv) > 3 else "256"): {"token_steps": steps, "dram_bytes_per_token_step": round(tot / max(steps, 1))}}
     path = os.path.join(ROOT, "profiles", "traffic.json")
     json.dump(out, open(path, "w"), indent=1)
     print(json.dumps(out, indent=1))
