@@ -38,7 +38,23 @@ struct GemmParams {
   int sk_stages;           // skinny kernel: depth of the TMA ring
   int sk_partial;          // skinny kernel: gridDim.x CTAs per tile each store their K range's product to slice blockIdx.x of out
   int b_frozen;            // skinny kernel: B (first source) is a frozen weight -- its tiles may be fetched before pdl_wait()
+  int band_m;              // pair kernel: M-tiles per band of the tile order (see pair_tile_coords)
 };
+
+// Tile order of the persistent CTA-pair kernel.  Tiles are walked band by band: a band is `band_m` consecutive 256-row M-tiles
+// crossed with ALL N-tiles, M fastest inside the band.  The 74 pairs running at one time then share a few weight tiles, and
+// the band's A rows (band_m x 256 x K x 2 bytes, sized by the launcher to a fraction of the 126 MB L2) stay L2-resident while
+// the band sweeps N -- A and W are each read from HBM about once.  With band_m >= tiles_m (every training shape of the bench:
+// A is 27 MB) this is the plain M-fastest order.  Without bands a prefill GEMM over 100 k rows re-streamed its 500 MB A operand
+// once per N-tile: 22 GB of DRAM traffic per launch, 1105 TF/s.
+__device__ __forceinline__ void pair_tile_coords(int tile, int tiles_m, int tiles_n, int band_m, int& tm, int& tn) {
+  const int per_band = band_m * tiles_n;
+  const int b = tile / per_band, r = tile - b * per_band;
+  const int m_first = b * band_m;
+  const int rows = tiles_m - m_first < band_m ? tiles_m - m_first : band_m;     // the last band may be short
+  tn = r / rows;
+  tm = m_first + (r - tn * rows);
+}
 
 template <int BN> struct GemmCfg {
   static constexpr int A_BYTES = BM * BK * 2;
@@ -856,8 +872,10 @@ gemm_pair_kernel(const __grid_constant__ PairMaps tm, const GemmParams p) {
     // ===================== TMA producer (each CTA loads its own halves) =====================
     uint32_t it = 0;
     for (int tile = pair; tile < num_tiles; tile += npairs) {
-      const int m0 = (tile % tiles_m) * 256 + (int)rank * 128;
-      const int n0 = (tile / tiles_m) * BN + (int)rank * 128;
+      int tm_, tn_;
+      pair_tile_coords(tile, tiles_m, p.tiles_n, p.band_m, tm_, tn_);
+      const int m0 = tm_ * 256 + (int)rank * 128;
+      const int n0 = tn_ * BN + (int)rank * 128;
       for (int kb = 0; kb < nkb; ++kb, ++it) {
         const int s = it % STAGES;
         mbar_wait(&empty_bar[s], ((it / STAGES) & 1) ^ 1);
@@ -908,8 +926,16 @@ gemm_pair_kernel(const __grid_constant__ PairMaps tm, const GemmParams p) {
     const int my_tiles = pair < num_tiles ? (num_tiles - pair + npairs - 1) / npairs : 0;
     const int n_units = my_tiles * UPW;
     // unit u of this warp = column slice 2 * (u % UPW) + half of this pair's (u / UPW)-th tile
-    auto unit_row0 = [&](int u) { return ((pair + (u / UPW) * npairs) % tiles_m) * 256 + (int)rank * 128 + q * 32; };
-    auto unit_col0 = [&](int u) { return ((pair + (u / UPW) * npairs) / tiles_m) * BN + (2 * (u % UPW) + half) * UC; };
+    auto unit_row0 = [&](int u) {
+      int tm_, tn_;
+      pair_tile_coords(pair + (u / UPW) * npairs, tiles_m, p.tiles_n, p.band_m, tm_, tn_);
+      return tm_ * 256 + (int)rank * 128 + q * 32;
+    };
+    auto unit_col0 = [&](int u) {
+      int tm_, tn_;
+      pair_tile_coords(pair + (u / UPW) * npairs, tiles_m, p.tiles_n, p.band_m, tm_, tn_);
+      return tn_ * BN + (2 * (u % UPW) + half) * UC;
+    };
     if (loads && lane == 0 && n_units > 0) epi_issue_load<EPI>(&tm.aux, ebuf, &lbar[0], unit_row0(0), unit_col0(0));
     RopeRegs rope;
     for (int u = 0; u < n_units; ++u) {
@@ -1112,6 +1138,18 @@ static int launch_gemm_pair(const dh_gemm_args* a, cudaStream_t stream) {
   GemmParams p = make_params(a);
   p.tiles_m = (a->M + 255) / 256;
   p.tiles_n = a->N / Cfg::BN;
+  {
+    // band height: the band's A rows (both sources) within ~20 MB of L2, at least one wave of pairs wide when N is narrow
+    static long long budget = -1;
+    if (budget < 0) { const char* e = getenv("DH_GEMM_BAND_MB"); budget = (e ? atoll(e) : 20) << 20; }   // measured: 16-28 MB best (prefill 246 -> 196 ms)
+    const long long a_tile_bytes = 256LL * (a->K1 + a->K2) * 2;
+    long long band = budget / a_tile_bytes;
+    const long long wave_m = (sm_count() / 2 + p.tiles_n - 1) / p.tiles_n;      // M-tiles one wave of pairs spans when it covers all N-tiles
+    if (band < wave_m) band = wave_m;
+    if (band < 1) band = 1;
+    p.band_m = band >= p.tiles_m ? p.tiles_m : (int)band;
+    if (a->m_limit) p.band_m = p.tiles_m;       // the device-side row bound changes tiles_m: keep the plain order there
+  }
   const int tiles = p.tiles_m * p.tiles_n;
   const int pairs = sm_count() / 2;
   const int grid = 2 * (tiles < pairs ? tiles : pairs);
