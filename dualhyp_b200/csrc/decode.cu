@@ -480,7 +480,9 @@ __device__ __forceinline__ void swiglu_stage(const DecodePlan* p, int tid) {
 #pragma unroll
         for (int i = 0; i < 4; ++i) {
           const float u = bf16_round(a1[i]), g = bf16_round(a2[i]);
-          o[i] = (u / (1.f + __expf(-u))) * g;
+          float th;
+      asm("tanh.approx.f32 %0, %1;" : "=f"(th) : "f"(0.5f * u));        // sigmoid(u) = 0.5 + 0.5 tanh(u / 2), as the GEMM epilogues
+      o[i] = u * fmaf(0.5f, th, 0.5f) * g;
         }
         *reinterpret_cast<uint2*>(p->act + (size_t)rows[k] * I + cols[k]) = make_uint2(pack_bf16x2(o[0], o[1]), pack_bf16x2(o[2], o[3]));
       }

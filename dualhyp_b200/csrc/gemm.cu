@@ -101,6 +101,15 @@ __device__ __forceinline__ uint4 pack_bf16x8(const float (&f)[8]) {
   return u;
 }
 
+// sigmoid(x) = 0.5 + 0.5 tanh(x / 2): ONE special-function op (MUFU.TANH) instead of the two of 1 / (1 + exp(-x)) (EX2 + RCP).  The
+// SwiGLU-backward epilogue needs a sigmoid for every accumulator element: 64 K MUFU ops per CTA and tile at 16 per clock were as
+// long as the K = 2048 main loop (4096 clocks); tanh.approx is accurate to ~2^-11, the outputs are rounded to bf16 (2^-9).
+__device__ __forceinline__ float fast_sigmoid(float x) {
+  float t;
+  asm("tanh.approx.f32 %0, %1;" : "=f"(t) : "f"(0.5f * x));
+  return fmaf(0.5f, t, 0.5f);
+}
+
 template <int EPI>
 __device__ __forceinline__ void epilogue_chunk(const GemmParams& p, int row, int col0, float (&v)[64]) {
   if constexpr (EPI == DH_EPI_BF16) {
@@ -168,7 +177,7 @@ __device__ __forceinline__ void epilogue_chunk(const GemmParams& p, int row, int
 #pragma unroll
     for (int j = 0; j < 32; ++j) {
       float h1 = bf16_round(v[j]), h2 = bf16_round(v[j + 32]);
-      a[j] = (h1 / (1.f + __expf(-h1))) * h2;
+      a[j] = h1 * fast_sigmoid(h1) * h2;
     }
 #pragma unroll
     for (int i = 0; i < 4; ++i) {
@@ -189,7 +198,7 @@ __device__ __forceinline__ void epilogue_chunk(const GemmParams& p, int row, int
 #pragma unroll
       for (int j = 0; j < 32; ++j) {
         float da = bf16_round(v[32 * g + j]);
-        float sig = 1.f / (1.f + __expf(-h1[j]));
+        float sig = fast_sigmoid(h1[j]);
         float silu = h1[j] * sig;
         d[j] = da * h2[j] * (sig * (1.f + h1[j] * (1.f - sig)));
         d[j + 32] = da * silu;
@@ -627,11 +636,6 @@ __device__ __forceinline__ void bf16_round2(float& a, float& b) {
   const uint32_t u = pack_bf16x2(a, b);
   a = __uint_as_float(u << 16);
   b = __uint_as_float(u & 0xffff0000u);
-}
-__device__ __forceinline__ float fast_sigmoid(float x) {
-  float r;
-  asm("rcp.approx.ftz.f32 %0, %1;" : "=f"(r) : "f"(1.f + __expf(-x)));
-  return r;
 }
 
 // accumulator columns per epilogue unit: every unit moves 4 KB boxes
