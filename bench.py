@@ -660,8 +660,11 @@ def run_native(args):
         # the launch behind this shape: CTA-pair kernel for K-major operands, N % 256 == 0, M >= 1024 (csrc/gemm.cu dispatch_bn)
         kname = f"gemm_pair_kernel<{epi}>" if (al == 0 and bl == 0 and N_ % 256 == 0 and M_ >= 1024) else f"gemm_kernel<*,{epi}>"
         tr, traffic_src = measured_traffic()
-        ent = tr.get("train", {}).get(kname)
+        cfg_ok = tr.get("train_config") == {"workload": args.workload, "prompts_per_gpu": B, "packed": bool(packed_mode)}
+        ent = tr.get("train", {}).get(kname) if cfg_ok else None
         traffic = ent["dram_bytes_per_launch"] if ent else None
+        if tr and not cfg_ok:
+            traffic_src = f"no capture for this workload (profiles/traffic.json holds {tr.get('train_config')})"
         # A + B read once; SwiGLU writes h12 (M x N) and act (M x N/2); the others write M x N (bf16) or read + write fp32 M x N
         alg_bytes = 2 * M_ * (K_ + K2_) + 2 * N_ * (K_ + K2_) + (2 * M_ * N_ + M_ * N_ if gemm_epi_name(epi) == "swiglu" else 2 * M_ * N_)
         line["roofline"] = {"bound": "tensor", "achieved": round(achieved, 1), "peak": peak_tf, "unit": "TFLOP/s",

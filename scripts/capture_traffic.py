@@ -51,6 +51,9 @@ def main():
             split[name if len(groups) == 1 else f"{name}#{gi}"] = g
     by = {k: [b for b, _ in g] for k, g in split.items()}
     dur = {k: sum(t for _, t in g) / len(g) for k, g in split.items()}
+    # the capture command of scripts/profile_step.sh: bench.py's default adapter step (16 packed prompts); bench.py reports these
+    # bytes only for that workload
+    out["train_config"] = {"workload": "adapter", "prompts_per_gpu": 16, "packed": True}
     out["train"] = {k: {"launches": len(v), "dram_bytes_per_launch": round(sum(v) / len(v)), "min": round(min(v)), "max": round(max(v)),
                         "ncu_duration_us": round(dur[k], 1)} for k, v in by.items()}
     if len(sys.argv) > 2:
