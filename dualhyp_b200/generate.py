@@ -49,6 +49,7 @@ class DecodeLoop:
         self.cache_sig = None
         self.plan = None              # persistent-kernel plan of the token step (engine.build_decode_plan), tied to the cache
         self.plan_sig = None
+        self.sample = None            # (temperature, top_k) of generate/base.py:62-70 when it is not the top-1 setting; None = arg-max
 
     def refresh(self, packed: Dict[int, Dict[str, Tensor]]) -> None:
         """New values of the trainable tensors into the buffers the captured graph reads."""
@@ -85,7 +86,16 @@ class DecodeLoop:
         self._ensure_plan()
         l0 = ops.launches()
         eng.lm_head(self.last, out=self.logits)
-        ops.argmax(self.logits, self.nxt)
+        if self.sample is None:
+            ops.argmax(self.logits, self.nxt)
+        else:
+            # generate/base.py:62-70 for every sequence: temperature, keep the top_k logits, softmax, multinomial
+            temperature, top_k = self.sample
+            lg = self.logits.float() / temperature
+            if top_k is not None:
+                v, _ = torch.topk(lg, min(int(top_k), lg.size(-1)))
+                lg = torch.where(lg < v[:, [-1]], torch.full_like(lg, float("-inf")), lg)
+            self.nxt.copy_(torch.multinomial(torch.softmax(lg, dim=-1), num_samples=1).squeeze(1))
         self.out_ids.index_copy_(1, self.step, self.nxt.unsqueeze(1))
         self.done.logical_or_(self.nxt == self.eos)
         hidden = eng.decode_step(self.nxt, self.pos, self.packed, self.pkv_all, plan=self.plan)
@@ -149,20 +159,26 @@ def generate(model, idx: Tensor, max_returned_tokens: int, *, temperature: float
     assert max_returned_tokens > T
     if model.max_seq_length < max_returned_tokens - 1:
         raise NotImplementedError(f"max_seq_length {model.max_seq_length} needs to be >= {max_returned_tokens - 1}")
-    if top_k is not None and top_k != 1:
-        raise NotImplementedError("the DualHyp inference drivers decode with top_k=1 (inference/ger.py:78); sampling is not on this path")
-    out = generate_batch(model, [idx], max_returned_tokens - T, eos_id=eos_id)[0]
-    return out
+    if top_k == 1:
+        # the DualHyp inference drivers' setting (inference/ger.py:78): one candidate survives the top-k cut, i.e. arg-max
+        return generate_batch(model, [idx], max_returned_tokens - T, eos_id=eos_id)[0]
+    if temperature <= 0:
+        raise ValueError("temperature must be positive")
+    # generate/base.py:62-70 proper: temperature + top-k (None = whole vocabulary) + multinomial, on the device with torch's CUDA
+    # generator (so the draws differ from the reference's CPU stream); eager token loop, no graph
+    return generate_batch(model, [idx], max_returned_tokens - T, eos_id=eos_id, use_graph=False, sample=(float(temperature), top_k))[0]
 
 
 @torch.inference_mode()
 def generate_batch(model, prompts: Sequence[Tensor], max_new_tokens: int, eos_id: Optional[int] = None,
-                   poll_every: int = 8, use_graph: bool = True, return_device: bool = False, packed_prefill: bool = True):
+                   poll_every: int = 8, use_graph: bool = True, return_device: bool = False, packed_prefill: bool = True,
+                   sample: Optional[tuple] = None):
     """Greedy-decode every prompt (1-D int64 tensors, host or device).  Returns prompt + generated ids per sequence,
     cut after the first `eos_id` (inclusive) when given.  `return_device=True` returns the raw device tensor
     `[n, steps]` of generated ids instead (no device-to-host copy; used by bench.py's HBM-resident leg).
     `packed_prefill` (default): the prompts are prefilled as ONE packed row with cu_seqlens (no flops on pad tokens, SURVEY
-    8f row 2); False right-pads them to the longest prompt like the reference's collate_fn -- both give the same bits."""
+    8f row 2); False right-pads them to the longest prompt like the reference's collate_fn -- both give the same bits.
+    `sample = (temperature, top_k)`: draw every token like generate/base.py:62-70 instead of taking the arg-max (eager loop)."""
     eng = model._engine_ready()
     dev = eng.device
     n = len(prompts)
@@ -210,7 +226,11 @@ def generate_batch(model, prompts: Sequence[Tensor], max_new_tokens: int, eos_id
         hidden = eng.prefill(ids, loop.packed).view(n, Tmax, -1)
         last = hidden[torch.arange(n, device=dev), (lens_d - 1).long()]                    # ln_f state of each prompt's last token
     loop.reset(last, lens_d, eos_id)
-    steps = loop.run(max_new_tokens, use_graph, poll_every)
+    loop.sample = sample
+    try:
+        steps = loop.run(max_new_tokens, use_graph and sample is None, poll_every)
+    finally:
+        loop.sample = None
     if return_device:
         return loop.out_ids[:, :steps]
     out_ids = loop.out_ids[:, :steps].cpu()

@@ -677,3 +677,31 @@ def test_reliability_head_tensor_core_path_at_cfg4_shapes(B, T, C, pool):
     assert rel_err(ref_t, ref) > 1e-3                       # the mask matters
     assert rel_err(logits_t.detach().cpu(), ref_t) < 1.5e-2
     grads_close(ref_gt, "train")
+
+
+def test_generate_temperature_top_k_sampling():
+    """generate/base.py:62-70 beyond the drivers' top_k = 1: temperature + top-k + multinomial.  (a) every sampled id lies inside the
+    top-k set of the model's own logits for that position (recomputed without the cache; 3 extra ranks of slack for bf16 near-ties),
+    (b) a fixed torch seed repeats the draw, another seed changes it, (c) temperature -> 0 over the whole vocabulary picks a maximum of every row."""
+    m, _ = build("adapter", adapter_start_layer=1)
+    prompt = synthetic.synth_prompts(1, 512, SEED + 3, prompt_range=(20, 40))[0].to(DEV)
+    n_new, k = 12, 4
+    torch.manual_seed(11)
+    a = generate(m, prompt, prompt.numel() + n_new, temperature=0.8, top_k=k)
+    torch.manual_seed(11)
+    b = generate(m, prompt, prompt.numel() + n_new, temperature=0.8, top_k=k)
+    torch.manual_seed(12)
+    c = generate(m, prompt, prompt.numel() + n_new, temperature=0.8, top_k=k)
+    assert a.tolist() == b.tolist() and a.tolist() != c.tolist()
+    assert a[: prompt.numel()].tolist() == prompt.tolist() and a.numel() == prompt.numel() + n_new
+    with torch.no_grad():
+        full = m(a[:-1].view(1, -1).to(DEV))[0, prompt.numel() - 1:].float().cpu()
+    for i in range(n_new):
+        assert int(a[prompt.numel() + i]) in full[i].topk(k + 3).indices.tolist(), f"token {i} outside the top-{k} set"
+    cold = generate(m, prompt, prompt.numel() + n_new, temperature=1e-4, top_k=None)
+    with torch.no_grad():
+        full_c = m(cold[:-1].view(1, -1).to(DEV))[0, prompt.numel() - 1:].float().cpu()
+    for i in range(n_new):                              # every cold draw is an arg-max of its own row, up to bf16 ties
+        row = full_c[i]
+        assert float(row[int(cold[prompt.numel() + i])]) >= float(row.max()) - 0.03 * float(row.abs().max()), f"cold token {i} is not a maximum"
+    m.reset_cache()
