@@ -83,6 +83,7 @@ SIGNATURES = {
     "dh_attention_bwd_varlen": (_I, [_P, _P, _P, _P, _P, _P, _P, _P, _P, _I, _P, _P, _P, _I, _I, _L, _I, _I, _I, _P, _Z, _P]),
     "dh_attention_decode": (_I, [_P, _P, _P, _P, _P, _P, _P, _I, _I, _I, _I, _I, _P]),
     "dh_attention_decode_stream": (_I, [_P, _P, _P, _P, _P, _P, _P, _I, _I, _I, _I, _I, _P]),
+    "dh_attention_decode_rows": (_I, [_P, _P, _P, _P, _P, _P, _P, _I, _I, _I, _I, _I, _P]),
     "dh_decode_plan_bytes": (_Z, [_I]),
     "dh_decode_workspace_bytes": (_Z, [C.POINTER(DecodeDesc)]),
     "dh_decode_plan_build": (_I, [C.POINTER(DecodeDesc), _P]),

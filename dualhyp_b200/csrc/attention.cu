@@ -1839,25 +1839,26 @@ extern "C" int dh_attention_decode_stream(const void* qkv, const void* cache_k, 
                                           const void* prefix_kv, const float* gate, int nseq, int max_len, int n_groups, int q_per_kv,
                                           int prefix_len, void* stream);
 
-extern "C" int dh_attention_decode(const void* qkv, const void* cache_k, const void* cache_v, const int32_t* lens, void* out,
-                                   const void* prefix_kv, const float* gate, int nseq, int max_len, int n_groups, int q_per_kv,
-                                   int prefix_len, void* stream) {
+static int attention_decode_impl(int forced, const void* qkv, const void* cache_k, const void* cache_v, const int32_t* lens, void* out,
+                                 const void* prefix_kv, const float* gate, int nseq, int max_len, int n_groups, int q_per_kv,
+                                 int prefix_len, void* stream) {
   DH_CHECK(qkv && cache_k && cache_v && lens && out && nseq > 0, "dh_attention_decode: bad argument");
   DH_CHECK(q_per_kv <= DEC_MAX_QPK, "dh_attention_decode: q_per_kv %d > %d", q_per_kv, DEC_MAX_QPK);
   DH_CHECK(prefix_len >= 0 && prefix_len <= MAX_PREFIX, "dh_attention_decode: prefix_len too large");
-  // default: the whole-row mma.sync kernel; DH_DEC_ATTN=stream selects the streamed kernel (csrc/decode_attn.cu: TMA ring of
-  // 64-key chunks, flash-style warps; measured 1.92 vs 1.80 ms per token step of 128 sequences), DH_DEC_CUDA_CORES=1 the
-  // CUDA-core kernel (A/B runs)
-  static int variant = -1;
-  if (variant < 0) {
+  // default: the streamed kernel (csrc/decode_attn.cu: TMA ring of 32-key chunks, eight flash-style warps, two blocks per SM; measured
+  // 2.55 vs 2.63 ms per token step at 256 sequences, 1.65 vs 1.72 ms at 128); DH_DEC_ATTN=mma selects the whole-row mma.sync kernel
+  // (also taken when the cache rows are not a multiple of 32 keys), DH_DEC_CUDA_CORES=1 the CUDA-core kernel (A/B runs)
+  static int env_variant = -1;
+  if (env_variant < 0) {
     const char* e = getenv("DH_DEC_CUDA_CORES");
     const char* a = getenv("DH_DEC_ATTN");
-    variant = (e && e[0] == '1') ? 0 : (a && a[0] == 's') ? 2 : 1;
+    env_variant = (e && e[0] == '1') ? 0 : (a && a[0] == 'm') ? 1 : 2;
     DH_CUDA(cudaFuncSetAttribute(attn_decode_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, 200 * 1024));
     DH_CUDA(cudaFuncSetAttribute(attn_decode_mma_kernel<2>, cudaFuncAttributeMaxDynamicSharedMemorySize, 200 * 1024));
     DH_CUDA(cudaFuncSetAttribute(attn_decode_mma_kernel<4>, cudaFuncAttributeMaxDynamicSharedMemorySize, 200 * 1024));
   }
-  if (variant == 2 && max_len % 64 == 0 && q_per_kv <= 8)
+  const int variant = forced >= 0 ? forced : env_variant;
+  if (variant == 2 && max_len % 32 == 0 && q_per_kv <= 8)
     return dh_attention_decode_stream(qkv, cache_k, cache_v, lens, out, prefix_kv, gate, nseq, max_len, n_groups, q_per_kv, prefix_len, stream);
   const long long ld = (long long)n_groups * (q_per_kv + 2) * HD;
   const bf16* pkv = (const bf16*)(prefix_len > 0 ? prefix_kv : nullptr);
@@ -1883,4 +1884,17 @@ extern "C" int dh_attention_decode(const void* qkv, const void* cache_k, const v
   }
   DH_CUDA(cudaGetLastError());
   return 0;
+}
+
+extern "C" int dh_attention_decode(const void* qkv, const void* cache_k, const void* cache_v, const int32_t* lens, void* out,
+                                   const void* prefix_kv, const float* gate, int nseq, int max_len, int n_groups, int q_per_kv,
+                                   int prefix_len, void* stream) {
+  return attention_decode_impl(-1, qkv, cache_k, cache_v, lens, out, prefix_kv, gate, nseq, max_len, n_groups, q_per_kv, prefix_len, stream);
+}
+
+// the whole-row mma.sync kernel, whatever DH_DEC_ATTN says (tests and A/B runs)
+extern "C" int dh_attention_decode_rows(const void* qkv, const void* cache_k, const void* cache_v, const int32_t* lens, void* out,
+                                        const void* prefix_kv, const float* gate, int nseq, int max_len, int n_groups, int q_per_kv,
+                                        int prefix_len, void* stream) {
+  return attention_decode_impl(1, qkv, cache_k, cache_v, lens, out, prefix_kv, gate, nseq, max_len, n_groups, q_per_kv, prefix_len, stream);
 }

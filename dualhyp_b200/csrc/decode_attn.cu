@@ -1,9 +1,9 @@
 // Stand-alone streamed decode attention (the default behind dh_attention_decode): block = (sequence, kv group).  A producer
-// warp streams the cached K / V rows of the item as 64-key chunks through a 3-stage TMA ring (the chunks that hold only keys of
-// earlier token steps are requested BEFORE griddepcontrol.wait, so they overlap the tail of the QKV kernel); three compute warps
-// take the chunks round-robin (warp w always reads ring stage w), each keeping a flash-style running state for the group's q heads on mma.sync tiles
+// warp streams the cached K / V rows of the item as 32-key chunks through an 8-stage TMA ring (the chunks that hold only keys of
+// earlier token steps are requested BEFORE griddepcontrol.wait, so they overlap the tail of the QKV kernel); eight compute warps
+// take the 32-key chunks round-robin (warp w always reads ring stage w), each keeping a flash-style running state for the group's q heads on mma.sync tiles
 // (decode_attn.cuh), and merge in shared memory; the adapter prefix keeps its own softmax and gate (ger/adapter.py:116-146).
-// 64 KB of shared memory and 128 threads per block: three blocks per SM, i.e. nine 16 KB chunks in flight per SM.
+// 86 KB of shared memory and 288 threads per block: two blocks per SM, i.e. sixteen compute warps and 128 KB of chunks in flight per SM.
 #include <math.h>
 #include <stdlib.h>
 
@@ -12,10 +12,14 @@
 
 namespace dh {
 
-constexpr int DS_CWARPS = 3;            // == DS_STAGES: every ring stage is consumed by ONE warp (see the chunk loop)
+constexpr int DS_CWARPS = 8;            // == DS_STAGES: every ring stage is consumed by ONE warp (see the chunk loop)
 constexpr int DS_CTHREADS = DS_CWARPS * 32;
 constexpr int DS_THREADS = DS_CTHREADS + 32;
-constexpr int DS_STAGES = 3;
+constexpr int DS_STAGES = 8;
+constexpr int DS_KEYS = 32;             // keys per chunk: K 4 KB + V 4 KB per stage.  A warp's chunk is one long dependent chain (ldmatrix ->
+                                        // mma -> softmax -> mma, ~5 us per 64 keys), so latency is hidden by warps, not by deeper chunks: the first
+                                        // build (3 warps x 64 keys, 3 blocks per SM = 9 compute warps per SM) measured 48 us per layer at 256 sequences
+constexpr int DS_STAGE_BYTES = 2 * DS_KEYS * 128;
 constexpr int DS_MAX_QPK = 8;
 constexpr int DS_MAX_PREFIX = 16;
 
@@ -27,7 +31,7 @@ struct DsScratch {
   bf16 spfx[DS_MAX_PREFIX][128];
   uint64_t full[DS_STAGES], empty[DS_STAGES];
 };
-constexpr int DS_SMEM = DS_STAGES * KVC_BYTES + (int)sizeof(DsScratch) + 1024;
+constexpr int DS_SMEM = DS_STAGES * DS_STAGE_BYTES + (int)sizeof(DsScratch) + 1024;
 
 __device__ __forceinline__ void ds_cbar() { asm volatile("bar.sync 1, %0;" ::"n"(DS_CTHREADS) : "memory"); }
 __device__ __forceinline__ void ds_cp_async_16(uint32_t dst_smem, const void* src) {
@@ -36,13 +40,13 @@ __device__ __forceinline__ void ds_cp_async_16(uint32_t dst_smem, const void* sr
 
 static_assert(DS_CWARPS == DS_STAGES, "one consumer warp per ring stage");
 
-__global__ void __launch_bounds__(DS_THREADS, 3)
+__global__ void __launch_bounds__(DS_THREADS, 2)
 attn_decode_stream_kernel(const __grid_constant__ CUtensorMap kmap, const __grid_constant__ CUtensorMap vmap, const bf16* __restrict__ qkv,
                           const int* __restrict__ lens, bf16* __restrict__ out, const bf16* __restrict__ prefix_kv,
                           const float* __restrict__ gate, int max_len, int G, int qpk, int prefix_len, long long ld_qkv, float scale) {
   extern __shared__ uint8_t smem_raw[];
   uint8_t* ring = reinterpret_cast<uint8_t*>((reinterpret_cast<uintptr_t>(smem_raw) + 1023) & ~uintptr_t(1023));
-  DsScratch* sc = reinterpret_cast<DsScratch*>(ring + DS_STAGES * KVC_BYTES);
+  DsScratch* sc = reinterpret_cast<DsScratch*>(ring + DS_STAGES * DS_STAGE_BYTES);
   const int tid = threadIdx.x, warp = tid >> 5, lane = tid & 31;
   const int seq = blockIdx.x, g = blockIdx.y;
   if (tid == 0) {
@@ -52,7 +56,7 @@ attn_decode_stream_kernel(const __grid_constant__ CUtensorMap kmap, const __grid
   __syncthreads();
   pdl_launch_dependents();
   const int len = __ldg(lens + seq);             // written before the previous kernel started (the chain of pdl_wait is transitive)
-  const int nch = (len + KVC_KEYS - 1) / KVC_KEYS;
+  const int nch = (len + DS_KEYS - 1) / DS_KEYS;
   const int row0 = (seq * G + g) * max_len;
 
   if (warp == DS_CWARPS) {
@@ -63,9 +67,9 @@ attn_decode_stream_kernel(const __grid_constant__ CUtensorMap kmap, const __grid
         if (c == nch - 1 && !waited) { pdl_wait(); waited = true; }     // only the last chunk holds the key the previous kernel wrote
         const int s = c % DS_STAGES;
         mbar_wait(&sc->empty[s], ((c / DS_STAGES) & 1) ^ 1);
-        mbar_expect_tx(&sc->full[s], KVC_BYTES);
-        tma_load_2d(ring + s * KVC_BYTES, &kmap, 0, row0 + c * KVC_KEYS, &sc->full[s]);
-        tma_load_2d(ring + s * KVC_BYTES + KVC_KEYS * 128, &vmap, 0, row0 + c * KVC_KEYS, &sc->full[s]);
+        mbar_expect_tx(&sc->full[s], DS_STAGE_BYTES);
+        tma_load_2d(ring + s * DS_STAGE_BYTES, &kmap, 0, row0 + c * DS_KEYS, &sc->full[s]);
+        tma_load_2d(ring + s * DS_STAGE_BYTES + DS_KEYS * 128, &vmap, 0, row0 + c * DS_KEYS, &sc->full[s]);
       }
       if (!waited) pdl_wait();
     }
@@ -95,7 +99,7 @@ attn_decode_stream_kernel(const __grid_constant__ CUtensorMap kmap, const __grid
     // stage s == warp: a parity wait may look at most one phase ahead, and with one consumer per stage the warp's own program
     // order guarantees that (chunk c - STAGES was this warp's previous chunk)
     mbar_wait(&sc->full[s], (c / DS_STAGES) & 1);
-    kvc_chunk_step(st, qa, smem_u32(ring + s * KVC_BYTES), c * KVC_KEYS, len, sl2, lane);
+    kvc_chunk_step<DS_KEYS>(st, qa, smem_u32(ring + s * DS_STAGE_BYTES), c * DS_KEYS, len, sl2, lane);
     __syncwarp();
     if (lane == 0) mbar_arrive(&sc->empty[s]);
   }
@@ -170,7 +174,7 @@ extern "C" int dh_attention_decode_stream(const void* qkv, const void* cache_k, 
   DH_CHECK(qkv && cache_k && cache_v && lens && out && nseq > 0, "dh_attention_decode_stream: bad argument");
   DH_CHECK(q_per_kv >= 1 && q_per_kv <= DS_MAX_QPK, "dh_attention_decode_stream: q_per_kv %d not in [1, %d]", q_per_kv, DS_MAX_QPK);
   DH_CHECK(prefix_len >= 0 && prefix_len <= DS_MAX_PREFIX, "dh_attention_decode_stream: prefix_len %d > %d", prefix_len, DS_MAX_PREFIX);
-  DH_CHECK(max_len > 0 && max_len % KVC_KEYS == 0, "dh_attention_decode_stream: max_len %d must be a multiple of %d", max_len, KVC_KEYS);
+  DH_CHECK(max_len > 0 && max_len % DS_KEYS == 0, "dh_attention_decode_stream: max_len %d must be a multiple of %d", max_len, DS_KEYS);
   DH_CHECK((((uintptr_t)qkv | (uintptr_t)cache_k | (uintptr_t)cache_v | (uintptr_t)prefix_kv) & 15) == 0,
            "dh_attention_decode_stream: operands must be 16-byte aligned");
   static bool attr = false;
@@ -180,7 +184,7 @@ extern "C" int dh_attention_decode_stream(const void* qkv, const void* cache_k, 
   }
   CUtensorMap kmap, vmap;
   const long long rows = (long long)nseq * n_groups * max_len;
-  if (make_kv_cache_map(&kmap, cache_k, rows) || make_kv_cache_map(&vmap, cache_v, rows)) return -3;
+  if (make_kv_cache_map(&kmap, cache_k, rows, DS_KEYS) || make_kv_cache_map(&vmap, cache_v, rows, DS_KEYS)) return -3;
   const long long ld = (long long)n_groups * (q_per_kv + 2) * 64;
   const bf16* pkv = (const bf16*)(prefix_len > 0 ? prefix_kv : nullptr);
   const int plen = pkv ? prefix_len : 0;

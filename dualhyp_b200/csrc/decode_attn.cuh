@@ -9,7 +9,7 @@
 
 namespace dh {
 
-constexpr int KVC_KEYS = 64;                      // keys per chunk
+constexpr int KVC_KEYS = 64;                      // keys per chunk of the persistent kernel (csrc/decode.cu)
 constexpr int KVC_BYTES = 2 * KVC_KEYS * 128;     // K tile + V tile = one 16 KB ring stage
 
 __device__ __forceinline__ void kvc_mma_16816(float (&d)[4], uint32_t a0, uint32_t a1, uint32_t a2, uint32_t a3, uint32_t b0, uint32_t b1) {
@@ -42,12 +42,14 @@ struct KvcState {
 
 // qa[ks] = the A fragments of the q rows for d = 16 ks .. 16 ks + 15 ({a0, a2}; a1 = a3 = 0 are the idle rows).
 // key0 = index of the chunk's first key, n_valid = keys [0, n_valid) exist, sl2 = softmax scale * log2(e).
+template <int KEYS = KVC_KEYS>
 __device__ __forceinline__ void kvc_chunk_step(KvcState& st, const uint32_t (&qa)[4][2], uint32_t kbase, int key0, int n_valid, float sl2, int lane) {
-  const uint32_t vbase = kbase + KVC_KEYS * 128;
+  static_assert(KEYS % 32 == 0, "a chunk is a whole number of 32-key halves");
+  const uint32_t vbase = kbase + KEYS * 128;
   const int q = lane & 3, lr = lane & 7, lm = lane >> 3;
-  // two halves of 32 keys, each an online-softmax step of its own (keeps the score fragments at 16 registers)
+  // halves of 32 keys, each an online-softmax step of its own (keeps the score fragments at 16 registers)
 #pragma unroll
-  for (int hf = 0; hf < 2; ++hf) {
+  for (int hf = 0; hf < KEYS / 32; ++hf) {
     if (key0 + 32 * hf >= n_valid) break;               // warp-uniform: no valid key in this half
     float sc4[4][4];
 #pragma unroll
@@ -107,10 +109,10 @@ __device__ __forceinline__ void kvc_chunk_step(KvcState& st, const uint32_t (&qa
 }
 
 // KV cache [rows = n_seq * n_groups * max_len, 64] bf16 as rows of 128 bytes; box = 64 keys, 128-byte swizzle
-inline int make_kv_cache_map(CUtensorMap* map, const void* base, long long rows) {
+inline int make_kv_cache_map(CUtensorMap* map, const void* base, long long rows, int box_keys = KVC_KEYS) {
   uint64_t dims[2] = {64, (uint64_t)rows};
   uint64_t strides[1] = {128};
-  uint32_t box[2] = {64, (uint32_t)KVC_KEYS};
+  uint32_t box[2] = {64, (uint32_t)box_keys};
   return make_tensor_map(map, base, CU_TENSOR_MAP_DATA_TYPE_BFLOAT16, 2, dims, strides, box, CU_TENSOR_MAP_SWIZZLE_128B);
 }
 

@@ -337,13 +337,15 @@ def attention_bwd_varlen(qkv: Tensor, out: Tensor, dout: Tensor, lse: Tensor, dq
 
 @_profiled("attention_decode")
 def attention_decode(qkv: Tensor, cache_k: Tensor, cache_v: Tensor, lens: Tensor, out: Tensor, n_groups: int, q_per_kv: int,
-                     prefix_kv: Optional[Tensor] = None, gate: Optional[Tensor] = None, prefix_len: int = 0, stream_kv: bool = False) -> None:
-    """`stream_kv=True` calls the streamed kernel (csrc/decode_attn.cu) directly; the default entry picks its kernel itself."""
+                     prefix_kv: Optional[Tensor] = None, gate: Optional[Tensor] = None, prefix_len: int = 0, stream_kv: Optional[bool] = None) -> None:
+    """`stream_kv=True` calls the streamed kernel (csrc/decode_attn.cu) directly, False the whole-row mma.sync kernel; None (default):
+    `dh_attention_decode` picks (the streamed one for row lengths that are a multiple of 32 keys)."""
     _dev(qkv)
     nseq, max_len = cache_k.shape[0], cache_k.shape[2]
     assert cache_k.is_contiguous() and cache_v.is_contiguous() and lens.dtype == torch.int32 and qkv.is_contiguous()
     lib = _lib.load()
-    fn, name = (lib.dh_attention_decode_stream, "dh_attention_decode_stream") if stream_kv else (lib.dh_attention_decode, "dh_attention_decode")
+    fn, name = ((lib.dh_attention_decode, "dh_attention_decode") if stream_kv is None else
+                (lib.dh_attention_decode_stream, "dh_attention_decode_stream") if stream_kv else (lib.dh_attention_decode_rows, "dh_attention_decode_rows"))
     check(fn(qkv.data_ptr(), cache_k.data_ptr(), cache_v.data_ptr(), lens.data_ptr(), out.data_ptr(),
              _ptr(prefix_kv), _ptr(gate), nseq, max_len, n_groups, q_per_kv, prefix_len, _stream()), name)
     _count()

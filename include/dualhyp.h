@@ -177,11 +177,16 @@ int dh_prefix_project_bwd(const float* d_prefix_kv, const void* wkv, float* d_pr
 int dh_attention_decode(const void* qkv, const void* cache_k, const void* cache_v, const int32_t* lens, void* out,
                         const void* prefix_kv, const float* gate, int nseq, int max_len, int n_groups, int q_per_kv,
                         int prefix_len, void* stream);
-/* The kernel dh_attention_decode uses when max_len is a multiple of 64 (csrc/decode_attn.cu): the cached K / V rows of one
- * (sequence, kv group) stream through a TMA ring as 64-key chunks, flash-style running softmax per warp, same arguments. */
+/* The kernel dh_attention_decode uses by default when max_len is a multiple of 32 (csrc/decode_attn.cu): the cached K / V rows of
+ * one (sequence, kv group) stream through a TMA ring as 32-key chunks, flash-style running softmax per warp, same arguments.
+ * dh_attention_decode_rows is the other one, explicitly: whole-row scores in shared memory on mma.sync tiles (what
+ * DH_DEC_ATTN=mma selects, and the fallback for other row lengths). */
 int dh_attention_decode_stream(const void* qkv, const void* cache_k, const void* cache_v, const int32_t* lens, void* out,
                                const void* prefix_kv, const float* gate, int nseq, int max_len, int n_groups, int q_per_kv,
                                int prefix_len, void* stream);
+int dh_attention_decode_rows(const void* qkv, const void* cache_k, const void* cache_v, const int32_t* lens, void* out,
+                             const void* prefix_kv, const float* gate, int nseq, int max_len, int n_groups, int q_per_kv,
+                             int prefix_len, void* stream);
 /* ---------------------------------------------------------------------------------------------------
  * One decode token step for ALL decoder layers as one persistent kernel (ger/model.py:163-268 per layer, driven one token at
  * a time by generate/base.py:57-80): one CTA per SM, grid-wide barriers between the stages, the frozen weights of every GEMM
