@@ -39,6 +39,7 @@ class GemmArgs(C.Structure):
         ("rope_cos", C.c_void_p), ("rope_sin", C.c_void_p),
         ("positions", C.c_void_p),
         ("m_limit", C.c_void_p),
+        ("workspace", C.c_void_p), ("workspace_bytes", C.c_size_t),
     ]
 
 
@@ -69,6 +70,7 @@ SIGNATURES = {
     "dh_init": (_I, [_I]),
     "dh_sm_count": (_I, []),
     "dh_gemm": (_I, [C.POINTER(GemmArgs), _P]),
+    "dh_gemm_streamk_workspace_bytes": (_Z, [_I, _I, _I]),
     "dh_rmsnorm_fwd": (_I, [_P, _I, _P, _P, _P, _I, _I, _F, _P]),
     "dh_splitk_resid_rmsnorm": (_I, [_P, _I, _L, _P, _P, _P, _P, _I, _I, _F, _P]),
     "dh_splitk_qkv_rope_cache": (_I, [_P, _I, _L, _P, _P, _P, _P, _P, _P, _P, _I, _I, _I, _I, _P]),

@@ -589,6 +589,219 @@ gemm_skinny_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constan
 }
 
 // ------------------------------------------------------------------------------------------------
+// Stream-K decode GEMM (M <= 256, dh_gemm_args.workspace given): for GEMMs whose N / 128 tiles do not fill the machine and whose
+// epilogue is tile-local (SwiGLU: 88 tiles on 148 SMs left 60 SMs idle and took 33 us at 256 rows).  The (128-column tile,
+// 64-wide k-block) units are dealt out contiguously over ALL SMs, so every SM streams the same number of weight bytes; a CTA's
+// run touches one or two tiles, and each (CTA, tile) segment leaves an fp32 partial tile in the workspace (TMEM -> a shared-memory
+// transpose -> 128-byte row stores), then bumps the tile's arrival counter.  The CTA whose arrival completes a tile sums the
+// tile's slices in CTA order (deterministic whoever arrives last) and runs the fused epilogue.  Nobody ever WAITS for another
+// CTA, so there is no residency requirement and no deadlock to reason about; the counters are reset by the finisher.
+// Roles as gemm_skinny_kernel: warp 0 TMA, warp 1 MMA, warp 2 TMEM, warps 4-7 drain / finish.
+// ------------------------------------------------------------------------------------------------
+constexpr int SKK_STG_BYTES = 4 * 32 * 32 * 4;      // one [32][32] fp32 transpose tile per epilogue warp
+
+__host__ __device__ __forceinline__ int skk_unit_lo(int units, int c, int P) { return (int)((long long)units * c / P); }
+__host__ __device__ __forceinline__ int skk_unit_owner(int units, int u, int P) { return (int)((((long long)u + 1) * P - 1) / units); }
+
+template <int EPI>
+__global__ void __launch_bounds__(GEMM_THREADS, 1)
+gemm_streamk_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant__ CUtensorMap tmB, const GemmParams p,
+                    float* __restrict__ ws, unsigned int* __restrict__ counters, int maxseg) {
+  extern __shared__ uint8_t smem_raw[];
+  uint8_t* smem = reinterpret_cast<uint8_t*>((reinterpret_cast<uintptr_t>(smem_raw) + 1023) & ~uintptr_t(1023));
+  const int MB = p.M > BM ? 2 : 1;
+  const int a_box_bytes = p.M <= 64 ? 64 * BK * 2 : BM * BK * 2;
+  const int a_bytes = a_box_bytes * MB;
+  const int stage_bytes = a_bytes + SK_B_BYTES;
+  const int stages = p.sk_stages;
+  float* stg = reinterpret_cast<float*>(smem + stages * stage_bytes);
+  uint64_t* bars = reinterpret_cast<uint64_t*>(smem + stages * stage_bytes + SKK_STG_BYTES);
+  uint64_t* full_bar = bars;                       // [stages]
+  uint64_t* empty_bar = bars + SK_MAX_STAGES;      // [stages]
+  uint64_t* tfull_bar = bars + 2 * SK_MAX_STAGES;  // [2]
+  uint64_t* tempty_bar = tfull_bar + 2;            // [2]
+  uint32_t* tmem_slot = reinterpret_cast<uint32_t*>(tempty_bar + 2);
+  int* last_flag = reinterpret_cast<int*>(tmem_slot + 1);
+
+  const int warp = __shfl_sync(0xffffffffu, threadIdx.x >> 5, 0);
+  const int lane = threadIdx.x & 31;
+  const int cta = blockIdx.x;
+  const int nkb = p.K1 / BK;
+  const int units = p.tiles_n * nkb;
+  const int P = units < (int)gridDim.x ? units : (int)gridDim.x;   // CTAs that share the work: each owns at least one unit (the rest idle)
+  const int u0 = cta < P ? skk_unit_lo(units, cta, P) : units, u1 = cta < P ? skk_unit_lo(units, cta + 1, P) : units;
+  const int acc_cols = MB * SK_BN;                 // TMEM columns of one accumulator buffer
+
+  if (warp == 0 && lane == 0) { tma_prefetch_desc(&tmA); tma_prefetch_desc(&tmB); }
+  if (warp == 1 && lane == 0) {
+    for (int i = 0; i < stages; ++i) { mbar_init(&full_bar[i], 1); mbar_init(&empty_bar[i], 1); }
+    for (int i = 0; i < 2; ++i) { mbar_init(&tfull_bar[i], 1); mbar_init(&tempty_bar[i], 4); }
+    fence_barrier_init();
+  }
+  if (warp == 2) { tmem_alloc(tmem_slot, 4 * SK_BN); tmem_relinquish(); }
+  pdl_launch_dependents();
+  tc_fence_before();
+  __syncthreads();
+  tc_fence_after();
+  const uint32_t tmem_base = __shfl_sync(0xffffffffu, *tmem_slot, 0);
+
+  if (warp == 0 && lane == 0) {
+    // frozen weights do not depend on the previous kernel: the first ring of tiles is requested before pdl_wait()
+    int n_pre = 0;
+    if (p.b_frozen) {
+      for (int u = u0; u < u1 && n_pre < stages; ++u, ++n_pre) {
+        mbar_expect_tx(&full_bar[n_pre], stage_bytes);
+        tma_load_2d(smem + n_pre * stage_bytes + a_bytes, &tmB, (u % nkb) * BK, (u / nkb) * SK_BN, &full_bar[n_pre]);
+      }
+    }
+    pdl_wait();
+    uint32_t it = 0;
+    for (int u = u0; u < u1; ++u, ++it) {
+      const int s = it % stages;
+      uint8_t* sa = smem + s * stage_bytes;
+      const int k0 = (u % nkb) * BK;
+      if ((int)it >= n_pre) {
+        mbar_wait(&empty_bar[s], ((it / stages) & 1) ^ 1);
+        mbar_expect_tx(&full_bar[s], stage_bytes);
+        tma_load_2d(sa + a_bytes, &tmB, k0, (u / nkb) * SK_BN, &full_bar[s]);
+      }
+      tma_load_2d(sa, &tmA, k0, 0, &full_bar[s]);
+      if (MB == 2) tma_load_2d(sa + a_box_bytes, &tmA, k0, BM, &full_bar[s]);
+    }
+  } else if (warp == 1) {
+    pdl_wait();
+    const uint32_t idesc = umma_idesc_bf16(BM, SK_BN, 0, 0);
+    uint32_t it = 0, seg = 0;
+    for (int u = u0; u < u1; ++u, ++it) {
+      const int kb = u % nkb;
+      const bool first = (u == u0) || kb == 0, last = (u == u1 - 1) || kb == nkb - 1;
+      const int buf = seg & 1;
+      if (first) {
+        mbar_wait(&tempty_bar[buf], ((seg >> 1) & 1) ^ 1);
+        tc_fence_after();
+      }
+      const int s = it % stages;
+      mbar_wait(&full_bar[s], (it / stages) & 1);
+      tc_fence_after();
+      const uint32_t sa = smem_u32(smem + s * stage_bytes);
+      const uint32_t sb = sa + a_bytes;
+      if (elect_one()) {
+        for (int rb = 0; rb < MB; ++rb) {
+#pragma unroll
+          for (int k = 0; k < BK / 16; ++k)
+            tc_mma_ss(tmem_base + buf * acc_cols + rb * SK_BN, umma_desc_sw128(sa + rb * a_box_bytes + k * 32, 16, 1024),
+                      umma_desc_sw128(sb + k * 32, 16, 1024), idesc, (!first) || k != 0);
+        }
+        tc_commit(&empty_bar[s]);
+        if (last) tc_commit(&tfull_bar[buf]);
+      }
+      __syncwarp();
+      if (last) ++seg;
+    }
+  } else if (warp >= 4) {
+    pdl_wait();
+    const int q = warp & 3, t = threadIdx.x - 128;
+    float* stgw = stg + q * 1024;
+    const size_t slice = (size_t)MB * BM * SK_BN;           // floats per partial-tile slice
+    uint32_t seg = 0;
+    int u = u0;
+    while (u < u1) {
+      const int tile = u / nkb;
+      const int end = (tile + 1) * nkb < u1 ? (tile + 1) * nkb : u1;
+      const int buf = seg & 1;
+      const int first_owner = skk_unit_owner(units, tile * nkb, P), nseg = skk_unit_owner(units, (tile + 1) * nkb - 1, P) - first_owner + 1;
+      const int n0 = tile * SK_BN;
+      mbar_wait(&tfull_bar[buf], (seg >> 1) & 1);
+      tc_fence_after();
+      if (nseg == 1) {
+        // the whole tile was this CTA's: epilogue straight from TMEM
+        for (int cc = 0; cc < MB * (SK_BN / 64); ++cc) {
+          const int rb = cc / (SK_BN / 64), c = cc % (SK_BN / 64);
+          const int row = rb * BM + q * 32 + lane;
+          uint32_t r0[32], r1[32];
+          const uint32_t taddr = tmem_base + ((uint32_t)(q * 32) << 16) + buf * acc_cols + rb * SK_BN + c * 64;
+          tmem_ld32(taddr, r0);
+          tmem_ld32(taddr + 32, r1);
+          tmem_wait_ld();
+          float v[64];
+#pragma unroll
+          for (int j = 0; j < 32; ++j) { v[j] = __uint_as_float(r0[j]); v[j + 32] = __uint_as_float(r1[j]); }
+          if (row < p.M) epilogue_chunk<EPI>(p, row, n0 + c * 64, v);
+        }
+        tc_fence_before();
+        __syncwarp();
+        if (lane == 0) mbar_arrive(&tempty_bar[buf]);
+      } else {
+        // ---- park this segment's partial tile: TMEM -> transpose -> rows of 128 contiguous bytes ----
+        float* mine = ws + ((size_t)tile * maxseg + (cta - first_owner)) * slice;
+        for (int rb = 0; rb < MB; ++rb) {
+          const int nrow = p.M - rb * BM - q * 32;              // valid rows of this warp's 32-row block
+          for (int g = 0; g < SK_BN / 32; ++g) {
+            uint32_t rg[32];
+            tmem_ld32(tmem_base + ((uint32_t)(q * 32) << 16) + buf * acc_cols + rb * SK_BN + g * 32, rg);
+            tmem_wait_ld();
+#pragma unroll
+            for (int i = 0; i < 32; ++i) stgw[lane * 32 + (i ^ lane)] = __uint_as_float(rg[i]);
+            __syncwarp();
+            float* dst = mine + ((size_t)rb * BM + q * 32) * SK_BN + g * 32 + lane;
+#pragma unroll 8
+            for (int rr = 0; rr < 32; ++rr)
+              if (rr < nrow) __stcg(dst + (size_t)rr * SK_BN, stgw[rr * 32 + (lane ^ rr)]);
+            __syncwarp();
+          }
+        }
+        tc_fence_before();
+        __syncwarp();
+        if (lane == 0) mbar_arrive(&tempty_bar[buf]);
+        // ---- arrival; the CTA that completes the tile finishes it ----
+        __threadfence();
+        asm volatile("bar.sync 1, 128;" ::: "memory");
+        if (t == 0) {
+          const unsigned int old = atomicAdd(counters + tile, 1u);
+          const int fin = old == (unsigned int)(nseg - 1);
+          if (fin) counters[tile] = 0;                          // every segment has arrived: ready for the next launch
+          *last_flag = fin;
+        }
+        asm volatile("bar.sync 1, 128;" ::: "memory");
+        const bool fin = *reinterpret_cast<volatile int*>(last_flag) != 0;
+        asm volatile("bar.sync 1, 128;" ::: "memory");            // last_flag is rewritten by the next segment
+        if (fin) {
+          __threadfence();
+          const float* base = ws + (size_t)tile * maxseg * slice;
+          for (int cc = 0; cc < MB * (SK_BN / 64); ++cc) {
+            const int rb = cc / (SK_BN / 64), c = cc % (SK_BN / 64);
+            const int row = rb * BM + q * 32 + lane;
+            if (row < p.M) {
+              // thread = row: 16 independent 16-byte loads per slice in flight, the slices summed in CTA order (deterministic)
+              const float* src = base + (size_t)row * SK_BN + c * 64;
+              float v[64];
+#pragma unroll
+              for (int i = 0; i < 64; ++i) v[i] = 0.f;
+              for (int s2 = 0; s2 < nseg; ++s2) {
+                float4 x[16];
+#pragma unroll
+                for (int i = 0; i < 16; ++i) x[i] = __ldcg(reinterpret_cast<const float4*>(src + (size_t)s2 * slice) + i);
+#pragma unroll
+                for (int i = 0; i < 16; ++i) { v[4 * i] += x[i].x; v[4 * i + 1] += x[i].y; v[4 * i + 2] += x[i].z; v[4 * i + 3] += x[i].w; }
+              }
+              epilogue_chunk<EPI>(p, row, n0 + c * 64, v);
+            }
+          }
+        }
+      }
+      ++seg;
+      u = end;
+    }
+  }
+  tc_fence_before();
+  __syncthreads();
+  if (warp == 2) {
+    tc_fence_after();
+    tmem_dealloc(tmem_base, 4 * SK_BN);
+  }
+}
+
+// ------------------------------------------------------------------------------------------------
 // Epilogue of the CTA-pair kernel: all global traffic is TMA.  An epilogue warp owns 32 accumulator rows (TMEM
 // lanes; thread = row) and works in units of 64 accumulator columns.  Per unit it has an 8 KB shared-memory
 // tile pair laid out exactly as the tensor maps' boxes (128-byte rows, 128B swizzle => row-per-lane accesses
@@ -1239,6 +1452,53 @@ static int launch_gemm_skinny(const dh_gemm_args* a, cudaStream_t stream) {
   return 0;
 }
 
+// workspace of the stream-K decode GEMM: [arrival counters, one per tile, padded to 256 B][tiles][maxseg][row blocks * 128][128] fp32
+static size_t streamk_layout(int M, int N, int K, int* maxseg_out) {
+  const int tiles = N / SK_BN, nkb = K / BK, units = tiles * nkb;
+  int P = sm_count() > 0 ? sm_count() : 148;
+  if (units < P) P = units;
+  int maxseg = 1;
+  for (int t = 0; t < tiles; ++t) {
+    const int c = skk_unit_owner(units, (t + 1) * nkb - 1, P) - skk_unit_owner(units, t * nkb, P) + 1;
+    if (c > maxseg) maxseg = c;
+  }
+  if (maxseg_out) *maxseg_out = maxseg;
+  const size_t counters = ((size_t)tiles * sizeof(unsigned int) + 255) & ~(size_t)255;
+  return counters + (size_t)tiles * maxseg * (M > BM ? 2 : 1) * BM * SK_BN * sizeof(float);
+}
+
+template <int EPI>
+static int launch_gemm_streamk(const dh_gemm_args* a, cudaStream_t stream) {
+  const int box_m = a->M <= 64 ? 64 : BM;
+  const int stage_bytes = box_m * BK * 2 * (a->M > BM ? 2 : 1) + SK_B_BYTES;
+  int stages = SK_RING_BYTES / stage_bytes;
+  if (stages > SK_MAX_STAGES) stages = SK_MAX_STAGES;
+  const size_t smem = (size_t)stages * stage_bytes + SKK_STG_BYTES + 1024 + 256;
+  static bool attr_set = false;
+  if (!attr_set) {
+    DH_CUDA(cudaFuncSetAttribute(gemm_streamk_kernel<EPI>, cudaFuncAttributeMaxDynamicSharedMemorySize, 227 * 1024));
+    attr_set = true;
+  }
+  DH_CHECK(smem <= 227 * 1024, "dh_gemm (stream-K): shared memory %zu", smem);
+  int maxseg = 1;
+  const size_t need = streamk_layout(a->M, a->N, a->K1, &maxseg);
+  DH_CHECK(a->workspace_bytes >= need, "dh_gemm (stream-K): workspace of %zu bytes given, %zu needed (dh_gemm_streamk_workspace_bytes)",
+           (size_t)a->workspace_bytes, need);
+  CUtensorMap tmA, tmB;
+  if (make_operand_map(&tmA, a->A, a->lda, a->M, a->K1, 0, box_m)) return -3;
+  if (make_operand_map(&tmB, a->B, a->ldb, a->N, a->K1, 0, SK_BN)) return -3;
+  GemmParams p = make_params(a);
+  p.b_frozen = t_b_frozen;
+  p.tiles_m = 1;
+  p.tiles_n = a->N / SK_BN;
+  p.sk_stages = stages;
+  const int tiles = p.tiles_n;
+  unsigned int* counters = reinterpret_cast<unsigned int*>(a->workspace);
+  float* ws = reinterpret_cast<float*>(reinterpret_cast<uint8_t*>(a->workspace) + (((size_t)tiles * sizeof(unsigned int) + 255) & ~(size_t)255));
+  DH_CUDA(launch_pdl(gemm_streamk_kernel<EPI>, dim3(sm_count()), dim3(GEMM_THREADS), smem, stream, tmA, tmB, p, ws, counters, maxseg));
+  return 0;
+}
+
 static int g_force_single = -1;   // DH_GEMM_SINGLE=1 forces the 1-CTA kernel (A/B testing)
 
 template <int EPI>
@@ -1251,6 +1511,12 @@ static int dispatch_bn(const dh_gemm_args* a, cudaStream_t stream) {
   if (!g_force_single && a->a_layout == 0 && a->b_layout == 0 && (a->K2 == 0 || (a->a2_layout == 0 && a->b2_layout == 0)) &&
       a->N % 256 == 0 && a->M >= 1024 && a->split_k <= 1 && pair_epilogue_ok(a))
     return launch_gemm_pair<EPI>(a, stream);
+  // decode GEMM with a tile-local epilogue and too few tiles for the machine: stream-K over all SMs (the caller lends a workspace)
+  if constexpr (EPI == DH_EPI_SWIGLU) {
+    if (a->workspace && a->M <= 2 * BM && a->N % SK_BN == 0 && a->K1 % BK == 0 && a->K2 == 0 && a->a_layout == 0 && a->b_layout == 0 &&
+        !a->m_limit && a->N / SK_BN < sm_count())
+      return launch_gemm_streamk<EPI>(a, stream);
+  }
   // one token per sequence (decode): weight streaming with K split over a cluster
   if (a->M <= 2 * BM && a->N % SK_BN == 0 && a->a_layout == 0 && a->b_layout == 0 && (a->K2 == 0 || (a->a2_layout == 0 && a->b2_layout == 0)) &&
       !a->m_limit && EPI != DH_EPI_SWIGLU_BWD && (EPI != DH_EPI_F32 || !a->accumulate))
@@ -1264,6 +1530,11 @@ static int dispatch_bn(const dh_gemm_args* a, cudaStream_t stream) {
 }
 
 }  // namespace dh
+
+extern "C" size_t dh_gemm_streamk_workspace_bytes(int M, int N, int K) {
+  if (M <= 0 || N <= 0 || K <= 0 || N % dh::SK_BN || K % dh::BK) return 0;
+  return dh::streamk_layout(M, N, K, nullptr);
+}
 
 extern "C" int dh_gemm(const dh_gemm_args* args, void* stream_) {
   using namespace dh;

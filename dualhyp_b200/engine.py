@@ -17,6 +17,7 @@ the K-major B operand of its dgrad), so that both directions run on the CTA-pair
 from __future__ import annotations
 
 import math
+import os
 from dataclasses import dataclass
 from typing import Dict, List, Optional
 
@@ -706,6 +707,19 @@ class DecoderEngine:
         ws = self._buf("dec_splitk", (max(s_proj, s_mlp), n_seq, C), f32) if (s_proj > 1 or s_mlp > 1) else None
         s_qkv = ops.decode_split_k(s.qkv_out, C) if (n_seq <= 256 and s.qkv_out % 128 == 0) else 1
         ws_q = self._buf("dec_splitk_qkv", (s_qkv, n_seq, s.qkv_out), f32) if s_qkv > 1 else None
+        # fc_1|fc_2 (2 I / 128 = 88 tiles on 148 SMs) as stream-K over all SMs, the CTA that completes a tile applying SwiGLU
+        # (csrc/gemm.cu gemm_streamk_kernel; the workspace of partial tiles + arrival counters is zeroed once and belongs to this GEMM
+        # shape).  OPT-IN (DH_DECODE_STREAMK=1): measured SLOWER at every batch -- token step 1.41 vs 1.16 ms at 16 sequences, 1.58 vs 1.27
+        # at 48, 2.18 vs 1.64 at 128, 3.48 vs 2.54 at 256: an fp32 partial tile is twice the bytes of the weight tile it came from, and
+        # parking + re-reading it through L2 costs more than the 60 idle SMs of the 88-tile grid.
+        ws12 = None
+        if os.environ.get("DH_DECODE_STREAMK", "0") == "1" and n_seq <= 256 and (2 * I) % 128 == 0 and C % 64 == 0:
+            nb = ops.gemm_streamk_workspace_bytes(n_seq, 2 * I, C)
+            key = ("persistent", "dec_streamk_ws12", n_seq)
+            ws12 = self._bufs.get(key)
+            if ws12 is None or ws12.numel() < nb:
+                with torch.inference_mode(False):
+                    ws12 = self._bufs[key] = torch.zeros(nb, device=self.device, dtype=torch.uint8)
         ops.rmsnorm_fwd(x, self.layers[0]["norm1"], n, None, s.norm_eps)
         for i, lw in enumerate(self.layers):
             pk = packed.get(i, {})
@@ -739,7 +753,7 @@ class DecoderEngine:
             else:
                 ops.gemm(y, lw["wproj"], x2, A2=a2, B2=b2, epilogue=ops.EPI_RESID_F32, aux=x, b_frozen=True)
                 ops.rmsnorm_fwd(x2, lw["norm2"], n, None, s.norm_eps)
-            ops.gemm(n, lw["w12"], None, epilogue=ops.EPI_SWIGLU, out2=act, b_frozen=True)
+            ops.gemm(n, lw["w12"], None, epilogue=ops.EPI_SWIGLU, out2=act, b_frozen=True, workspace=ws12)
             last = i + 1 == len(self.layers)
             w_next, n_next = (self.ln_f, hidden) if last else (self.layers[i + 1]["norm1"], n)
             if s_mlp > 1:

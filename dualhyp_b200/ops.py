@@ -127,7 +127,7 @@ def gemm(A: Tensor, B: Tensor, out: Optional[Tensor], *, epilogue: int = EPI_BF1
          out2: Optional[Tensor] = None, aux: Optional[Tensor] = None, alpha: float = 1.0, accumulate: bool = False,
          col_scale: Optional[Tensor] = None, col_bias: Optional[Tensor] = None, rope_cos: Optional[Tensor] = None,
          rope_sin: Optional[Tensor] = None, positions: Optional[Tensor] = None, seq_len: int = 0, q_per_kv: int = 0,
-         m_limit: Optional[Tensor] = None, split_k: int = 0, b_frozen: bool = False) -> None:
+         m_limit: Optional[Tensor] = None, split_k: int = 0, b_frozen: bool = False, workspace: Optional[Tensor] = None) -> None:
     """D = A op(B) (+ A2 op(B2)) with a fused epilogue; see `dh_gemm` in include/dualhyp.h.  split_k > 1 (decode, M <= 128,
     EPI_F32): `out` is fp32 [split_k, M, N] of partial products for `splitk_resid_rmsnorm` to sum."""
     _dev(A)
@@ -166,6 +166,8 @@ def gemm(A: Tensor, B: Tensor, out: Optional[Tensor], *, epilogue: int = EPI_BF1
     a.col_scale, a.col_bias = _ptr(col_scale), _ptr(col_bias)
     a.rope_cos, a.rope_sin, a.positions = _ptr(rope_cos), _ptr(rope_sin), _ptr(positions)
     a.m_limit = _ptr(m_limit)
+    if workspace is not None:          # stream-K decode GEMM (see dh_gemm_args.workspace): zeroed once by the owner, one per GEMM shape
+        a.workspace, a.workspace_bytes = workspace.data_ptr(), workspace.numel() * workspace.element_size()
     check(_lib.load().dh_gemm(C.byref(a), _stream()), "dh_gemm")
     _count()
 
@@ -515,6 +517,10 @@ def dropout_bf16(x: Tensor, out: Tensor, p: float, seed: int, offset: int, accum
     check(_lib.load().dh_dropout_bf16(x.data_ptr(), out.data_ptr(), x.numel(), float(p), int(seed) & (2 ** 64 - 1), int(offset), int(accumulate), _stream()),
           "dh_dropout_bf16")
     _count()
+
+
+def gemm_streamk_workspace_bytes(M: int, N: int, K: int) -> int:
+    return int(_lib.load().dh_gemm_streamk_workspace_bytes(int(M), int(N), int(K)))
 
 
 class DecodePlan:

@@ -22,7 +22,7 @@
 extern "C" {
 #endif
 
-#define DH_ABI_VERSION 3
+#define DH_ABI_VERSION 4
 
 int dh_abi_version(void);
 const char* dh_last_error(void);
@@ -85,9 +85,15 @@ typedef struct dh_gemm_args {
   const int32_t* positions;          /* optional [M] */
   const int32_t* m_limit;            /* optional device int: only rows [0, *m_limit) are needed; whole tiles beyond are skipped
                                         (rows of a partly needed tile are still computed).  ABI v2. */
+  void* workspace;                   /* optional, ABI v4: device memory the call may use, ZEROED once by the owner and only ever passed to
+                                        calls of the same (M-class, N, K).  With it a decode GEMM (M <= 256) whose epilogue is tile-local
+                                        (DH_EPI_SWIGLU) and whose N / 128 tiles do not fill the SMs runs stream-K over ALL SMs: partial
+                                        tiles + per-tile arrival counters live here, the CTA completing a tile runs the epilogue. */
+  size_t workspace_bytes;            /* >= dh_gemm_streamk_workspace_bytes(M, N, K1) */
 } dh_gemm_args;
 
 int dh_gemm(const dh_gemm_args* args, void* stream);
+size_t dh_gemm_streamk_workspace_bytes(int M, int N, int K);
 
 /* ---------------------------------------------------------------------------------------------------
  * Bandwidth-bound leaf ops

@@ -25,12 +25,12 @@ def test_library_exports_every_declared_symbol():
     for n in names:
         assert hasattr(lib, n), f"{n} declared in include/dualhyp.h but not exported by libdualhyp.so"
     assert sorted(_lib.SIGNATURES) == names, "ctypes binding and header disagree on the entry-point list"
-    assert _lib.load().dh_abi_version() == 3
+    assert _lib.load().dh_abi_version() == 4
 
 
 def test_gemm_args_struct_matches_header_layout():
     # 4 pointer/int64 pairs, 14 int32/float scalars, 3 pointer/int64 pairs, 6 pointers (ABI v2 added m_limit)
-    assert ctypes.sizeof(_lib.GemmArgs) == 4 * 16 + 14 * 4 + 3 * 16 + 6 * 8
+    assert ctypes.sizeof(_lib.GemmArgs) == 4 * 16 + 14 * 4 + 3 * 16 + 8 * 8          # ABI v4: + workspace, workspace_bytes
 
 
 @pytest.mark.skipif(torch.cuda.is_available(), reason="checks the no-GPU failure mode")

@@ -786,3 +786,33 @@ def test_dropout_bf16_statistics_and_determinism(p):
     ops.dropout_bf16(y, acc, p, 5, 3, accumulate=True)
     torch.cuda.synchronize()
     assert rel(acc, base.float() + m.float()) < 4e-3
+
+
+@pytest.mark.parametrize("M,I,C", [(1, 5632, 2048), (100, 5632, 2048), (128, 5632, 2048), (200, 5632, 2048), (256, 5632, 2048), (37, 512, 2048),
+                                   (256, 704, 2048), (5, 512, 256), (130, 128, 128)])
+def test_gemm_streamk_swiglu_decode(M, I, C):
+    """dh_gemm with a workspace (ABI v4): the decode fc_1|fc_2 GEMM as stream-K over all SMs, partial tiles in the workspace, the
+    CTA that completes a tile sums its slices in CTA order and applies SwiGLU.  Against fp32 math at bf16 tolerance and against the
+    cluster split-K kernel (same math, other summation order); three launches on the same workspace must agree bit for bit (the
+    arrival counters reset themselves, the slice sum does not depend on who arrives last).  The last two shapes have fewer units than
+    SMs (some CTAs idle)."""
+    x = rnd((M, C), 701)
+    W1, W2 = rnd((I, C), 702, bound=1 / 32), rnd((I, C), 703, bound=1 / 32)
+    W12 = _interleave(W1, W2).contiguous()
+    nb = ops.gemm_streamk_workspace_bytes(M, 2 * I, C)
+    assert nb > 0
+    ws = torch.zeros(nb, device=DEV, dtype=torch.uint8)
+    outs = []
+    for _ in range(3):
+        act = torch.full((M, I), float("nan"), device=DEV, dtype=torch.bfloat16)
+        ops.gemm(x, W12, None, epilogue=ops.EPI_SWIGLU, out2=act, workspace=ws)
+        outs.append(act)
+    plain = torch.full((M, I), float("nan"), device=DEV, dtype=torch.bfloat16)
+    ops.gemm(x, W12, None, epilogue=ops.EPI_SWIGLU, out2=plain)
+    torch.cuda.synchronize()
+    ref = F.silu(x.float() @ W1.float().t()) * (x.float() @ W2.float().t())
+    assert rel(outs[0], ref) < 8e-3, report("stream-K swiglu", outs[0], ref)
+    assert rel(outs[0], plain) < 8e-3
+    assert torch.equal(outs[0], outs[1]) and torch.equal(outs[0], outs[2])
+    n_tiles = 2 * I // 128
+    assert int(ws[: 4 * n_tiles].view(torch.int32).abs().sum()) == 0          # every tile's counter is back at zero
