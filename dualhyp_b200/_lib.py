@@ -71,6 +71,7 @@ SIGNATURES = {
     "dh_sm_count": (_I, []),
     "dh_gemm": (_I, [C.POINTER(GemmArgs), _P]),
     "dh_gemm_streamk_workspace_bytes": (_Z, [_I, _I, _I]),
+    "dh_gemm_swiglu_streamk_noalloc": (_I, [C.POINTER(GemmArgs), _P]),
     "dh_rmsnorm_fwd": (_I, [_P, _I, _P, _P, _P, _I, _I, _F, _P]),
     "dh_splitk_resid_rmsnorm": (_I, [_P, _I, _L, _P, _P, _P, _P, _I, _I, _F, _P]),
     "dh_splitk_qkv_rope_cache": (_I, [_P, _I, _L, _P, _P, _P, _P, _P, _P, _P, _I, _I, _I, _I, _P]),

@@ -1581,3 +1581,60 @@ extern "C" int dh_gemm(const dh_gemm_args* args, void* stream_) {
   }
   return -1;
 }
+
+// ------------------------------------------------------------------------------------------------
+// dh_gemm_swiglu_streamk_noalloc: the stream-K SwiGLU decode GEMM for callers that may not allocate (no counterpart in the
+// reference).  The partial tiles and arrival counters live in a file-scope device
+// array that every GPU loading the library holds until exit.  In HOST code the array's name is only a stand-in for the symbol:
+// the device address comes from cudaGetSymbolAddress, looked up once per device with that device current.
+// ------------------------------------------------------------------------------------------------
+static __device__ __align__(256) unsigned char g_noalloc_scratch[DH_NOALLOC_SCRATCH_BYTES];
+
+namespace dh {
+constexpr int NOALLOC_MAX_DEVICES = 64;
+static void* g_noalloc_ptr[NOALLOC_MAX_DEVICES];   // device address of g_noalloc_scratch on each device (0 = not looked up yet)
+
+static int noalloc_scratch(void** out) {
+  int dev = -1;
+  DH_CUDA(cudaGetDevice(&dev));
+  DH_CHECK(dev >= 0 && dev < NOALLOC_MAX_DEVICES, "dh_gemm_swiglu_streamk_noalloc: device ordinal %d out of range", dev);
+  void* p = __atomic_load_n(&g_noalloc_ptr[dev], __ATOMIC_ACQUIRE);
+  if (!p) {
+    DH_CUDA(cudaGetSymbolAddress(&p, g_noalloc_scratch));   // same answer from every thread: a benign race
+    DH_CHECK(p != nullptr && ((uintptr_t)p & 255) == 0, "dh_gemm_swiglu_streamk_noalloc: bad scratch address %p", p);
+    __atomic_store_n(&g_noalloc_ptr[dev], p, __ATOMIC_RELEASE);
+  }
+  *out = p;
+  return 0;
+}
+}  // namespace dh
+
+extern "C" int dh_gemm_swiglu_streamk_noalloc(const dh_gemm_args* args, void* stream_) {
+  using namespace dh;
+  cudaStream_t stream = reinterpret_cast<cudaStream_t>(stream_);
+  DH_CHECK(args != nullptr, "dh_gemm_swiglu_streamk_noalloc: null args");
+  dh_gemm_args local = *args;
+  const int b_layout = local.b_layout & ~DH_B_FROZEN;
+  DH_CHECK(local.epilogue == DH_EPI_SWIGLU, "dh_gemm_swiglu_streamk_noalloc: epilogue %d, only DH_EPI_SWIGLU has a stream-K kernel", local.epilogue);
+  DH_CHECK(local.M > 0 && local.M <= 2 * BM && local.N > 0 && local.N % SK_BN == 0 && local.K1 > 0 && local.K1 % BK == 0,
+           "dh_gemm_swiglu_streamk_noalloc: shape M=%d N=%d K1=%d (needs M <= %d, N %% %d == 0, K1 %% %d == 0)", local.M, local.N,
+           local.K1, 2 * BM, SK_BN, BK);
+  DH_CHECK(local.K2 == 0 && local.a_layout == 0 && b_layout == 0 && !local.m_limit,
+           "dh_gemm_swiglu_streamk_noalloc: K-major operands, no second source, no m_limit");
+  DH_CHECK(local.N / SK_BN < sm_count(), "dh_gemm_swiglu_streamk_noalloc: N=%d already fills the %d SMs with whole tiles; use dh_gemm",
+           local.N, sm_count());
+  const size_t need = streamk_layout(local.M, local.N, local.K1, nullptr);
+  DH_CHECK(need <= DH_NOALLOC_SCRATCH_BYTES,
+           "dh_gemm_swiglu_streamk_noalloc: M=%d N=%d K1=%d needs %zu bytes of scratch, the static array holds %zu "
+           "(DH_NOALLOC_SCRATCH_BYTES); use dh_gemm with a workspace of your own",
+           local.M, local.N, local.K1, need, (size_t)DH_NOALLOC_SCRATCH_BYTES);
+  void* scratch = nullptr;
+  if (noalloc_scratch(&scratch)) return -1;
+  // the array keeps the last call's contents: the partial tiles are fully rewritten before they are read, the arrival counters
+  // must start at zero (an aborted launch, or a call of another shape, may have left them anywhere)
+  const size_t counter_bytes = ((size_t)(local.N / SK_BN) * sizeof(unsigned int) + 255) & ~(size_t)255;
+  DH_CUDA(cudaMemsetAsync(scratch, 0, counter_bytes, stream));
+  local.workspace = scratch;
+  local.workspace_bytes = DH_NOALLOC_SCRATCH_BYTES;
+  return dh_gemm(&local, stream_);
+}

@@ -95,6 +95,19 @@ typedef struct dh_gemm_args {
 int dh_gemm(const dh_gemm_args* args, void* stream);
 size_t dh_gemm_streamk_workspace_bytes(int M, int N, int K);
 
+/* No counterpart in the reference: added for callers that may not allocate (code under CUDA
+ * graph capture, tight serving loops, harnesses that forbid cudaMalloc).  The stream-K DH_EPI_SWIGLU decode GEMM of dh_gemm
+ * (args->workspace given) with the partial tiles and arrival counters in a static device array of DH_NOALLOC_SCRATCH_BYTES that
+ * every GPU loading the library holds until exit; args->workspace / workspace_bytes are ignored.  The call makes no cudaMalloc,
+ * cudaFree or allocating library call.  Accepted: epilogue DH_EPI_SWIGLU, M <= 256, N % 128 == 0, K1 % 64 == 0, K2 == 0, K-major
+ * operands, no m_limit, N / 128 < SM count, and dh_gemm_streamk_workspace_bytes(M, N, K1) <= DH_NOALLOC_SCRATCH_BYTES (TinyLlama's
+ * fc_1|fc_2 at 256 rows needs 33.0 MiB); anything else returns an error that dh_last_error() explains -- it never falls back.
+ * The arrival counters are cleared on the stream before every launch.  ALL calls on a device share the one array: calls that
+ * may overlap on the GPU (two streams, two threads) race; serialise them.  The first call on a device looks the array's address
+ * up (cudaGetSymbolAddress); make it outside stream capture. */
+#define DH_NOALLOC_SCRATCH_BYTES ((size_t)36 << 20)
+int dh_gemm_swiglu_streamk_noalloc(const dh_gemm_args* args, void* stream);
+
 /* ---------------------------------------------------------------------------------------------------
  * Bandwidth-bound leaf ops
  * ------------------------------------------------------------------------------------------------- */
