@@ -633,12 +633,14 @@ def test_attention_decode_matches_prefill():
 
 
 @pytest.mark.parametrize("stream_kv", [False, True])
-@pytest.mark.parametrize("nseq,G,qpk,prefix,max_len", [(5, 4, 8, 10, 640), (3, 2, 2, 0, 640), (2, 1, 1, 16, 640), (4, 4, 8, 10, 2048)])
+@pytest.mark.parametrize("nseq,G,qpk,prefix,max_len", [(5, 4, 8, 10, 640), (3, 2, 2, 0, 640), (2, 1, 1, 16, 640), (4, 4, 8, 10, 2048),
+                                                     (200, 4, 8, 10, 640), (301, 2, 4, 0, 320)])
 def test_attention_decode_against_fp32(nseq, G, qpk, prefix, max_len, stream_kv):
     """The decode kernel against fp32 softmax attention over the valid cache slots (lengths from 1 to the whole row, not
     multiples of the 16-key tiles), with and without the gated prefix; rows of 640 slots take the 4-tiles-ahead V prefetch,
     rows of 2048 x 8 heads the 2-tiles-ahead build (the score buffer takes the shared memory).  `stream_kv`: the same cases
-    through the streamed kernel (dh_attention_decode_stream: TMA ring of 64-key chunks, up to 32 chunks per row here)."""
+    through the streamed kernel (dh_attention_decode_stream: TMA ring of 32-key chunks; with 200 / 301 sequences every resident
+    block walks two to three (sequence, kv group) items as one chunk stream)."""
     H = G * qpk
     N = G * (qpk + 2) * 64
     lens = synthetic.hash_ints((nseq,), 3, 401, 1, max_len + 1).to(torch.int32)
