@@ -112,7 +112,6 @@ attn_decode_stream_kernel(const __grid_constant__ CUtensorMap kmap, const __grid
     return;
   }
   // ===================== compute warps =====================
-  pdl_wait();
   const int r = lane >> 2, q = lane & 3;
   const float sl2 = scale * 1.4426950408889634f;
   const int H = G * qpk;
@@ -132,6 +131,9 @@ attn_decode_stream_kernel(const __grid_constant__ CUtensorMap kmap, const __grid
   }
   asm volatile("cp.async.commit_group;" ::: "memory");
   const float gate_r = (prefix_len > 0 && r < qpk) ? __ldg(gate + g * qpk + r) : 0.f;
+  // everything above reads what was written before the token step began (the projected prefix, the gate): it runs under the tail of
+  // the previous kernel; q is that kernel's output
+  pdl_wait();
   uint32_t qa[4][2], qn[4][2];
   auto load_q = [&](uint32_t (&dst)[4][2], int seq) {
     const bf16* qrow = qkv + (long long)seq * ld_qkv + qoff;

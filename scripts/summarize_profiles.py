@@ -37,7 +37,8 @@ out.append(f"shares: GEMM kernels {100 * sum(v[1] for k, v in agg.items() if 'ge
 open(P("r02_launch_summary.txt"), "w").write("\n".join(out) + "\n")
 
 # ---- 2. ncu --set full raw pages ----
-for rep in ("gemm", "attn"):
+REPS = ["gemm", "attn"] + (["dattn"] if os.path.exists(G("dattn.ncu-rep")) else [])      # dattn: the decode attention kernel (256 sequences)
+for rep in REPS:
     with open(G(f"{rep}_raw.csv"), "w") as f:
         subprocess.run(["ncu", "-i", G(f"{rep}.ncu-rep"), "--page", "raw", "--csv"], stdout=f, stderr=subprocess.DEVNULL, check=True)
 cols = ["Grid Size", "gpu__time_duration.sum", "dram__bytes_read.sum", "dram__bytes_write.sum", "sm__throughput.avg.pct_of_peak_sustained_elapsed",
@@ -46,7 +47,9 @@ cols = ["Grid Size", "gpu__time_duration.sum", "dram__bytes_read.sum", "dram__by
 out = [f"ncu --set full --clock-control none, build {sha}, one adapter fine-tune step of 16 packed prompts",
        "columns: kernel, grid, duration us, DRAM read MB, DRAM write MB, SM throughput %, tensor pipe active % (sm__pipe_tensor_cycles_active), warps active %, "
        "regs/thread, warp instructions, issue-active %, L2 sector hit rate %", ""]
-for rep in ("gemm", "attn"):
+for rep in REPS:
+    if rep == "dattn":
+        out.append("decode attention (scripts/decode_traffic.py 256: eager token step, 256 sequences of 346..496 cached keys):")
     r = list(csv.reader(open(G(f"{rep}_raw.csv"))))
     ix = {h: i for i, h in enumerate(r[0])}
     units = r[1]
