@@ -196,8 +196,11 @@ int dh_prefix_project_bwd(const float* d_prefix_kv, const void* wkv, float* d_pr
 int dh_attention_decode(const void* qkv, const void* cache_k, const void* cache_v, const int32_t* lens, void* out,
                         const void* prefix_kv, const float* gate, int nseq, int max_len, int n_groups, int q_per_kv,
                         int prefix_len, void* stream);
-/* The kernel dh_attention_decode uses by default when max_len is a multiple of 32 (csrc/decode_attn.cu): the cached K / V rows of
- * one (sequence, kv group) stream through a TMA ring as 32-key chunks, flash-style running softmax per warp, same arguments.
+/* The kernel dh_attention_decode uses by default when max_len is a multiple of 32 (csrc/decode_attn.cu): one persistent block per
+ * SM walks its share of the (sequence, kv group) items, their cached K / V rows stream through a TMA ring as 32-key chunks,
+ * flash-style running softmax per warp, same arguments; prefix_len <= 32.  lens, prefix_kv and gate are read before
+ * griddepcontrol.wait: they must not be the output of a kernel that signals programmatic launch completion early (none of this
+ * library's producers of them does; a kernel launched without that attribute never does).
  * dh_attention_decode_rows is the other one, explicitly: whole-row scores in shared memory on mma.sync tiles (what
  * DH_DEC_ATTN=mma selects, and the fallback for other row lengths). */
 int dh_attention_decode_stream(const void* qkv, const void* cache_k, const void* cache_v, const int32_t* lens, void* out,
