@@ -8,7 +8,7 @@
  *
  * Conventions: plain pointers and sizes only; every pointer is a DEVICE pointer unless stated; the library
  * never allocates or frees caller-visible memory and keeps no mutable global state except a per-device
- * TMA-descriptor cache and the last-error string; all work is enqueued on `stream` (a cudaStream_t) and is
+ * TMA-descriptor cache, the last-error string and the static scratch array of dh_gemm_swiglu_streamk_noalloc; all work is enqueued on `stream` (a cudaStream_t) and is
  * stream-ordered; functions return 0 on success, negative on error (dh_last_error() tells why).
  * bf16 = 2-byte bfloat16.  Row-major everywhere; `ld*` are leading dimensions in ELEMENTS.
  */

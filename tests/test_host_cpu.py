@@ -302,3 +302,93 @@ def test_prompt_assembly_label_masking_and_collation():
     for i, s in enumerate([s1, s2]):
         a, e = pk["cu_seqlens"][i].item(), pk["cu_seqlens"][i + 1].item()
         assert torch.equal(pk["targets"][a:e - 1], b["labels"][i, 1:e - a])
+
+
+class _CharTokenizer:
+    """Stand-in for the llama tokenizer: BOS id 1, one id per character."""
+    eos_token = "</s>"
+
+    def encode(self, text):
+        return [1] + [3 + (ord(c) % 200) for c in text]
+
+
+def _write_nbest_json(path, n_uids=3, variants=2):
+    import json
+    recs = []
+    for u in range(n_uids):
+        for v in range(variants):
+            recs.append({"Uid": f"utt{u}", "Caption": f"the true words {u}",
+                         "nhyps_asr": {"hyps": [f"asr{u}.{v} best"] + [f"asr{u}.{v} other {k}" for k in range(4)]},
+                         "nhyps_vsr": {"hyps": [f"vsr{u}.{v} best"] + [f"vsr{u}.{v} other {k}" for k in range(4)]}})
+    with open(path, "w") as f:
+        json.dump(recs, f)
+    return recs
+
+
+def test_av_dataset_shim_exports_the_names_the_drivers_import(tmp_path):
+    """SURVEY 8(b) shims / 8f row 2: `from data.av_dataset import AVDataset, DualHypothesesAVDataset, DualHypothesesAlignAVDataset,
+    DualHypothesesAlign2AVDataset` (finetune/ger.py:36) resolves after install_as_data(); the classes take the keyword arguments the
+    driver passes (finetune/ger.py:149-160), index the JSON by Uid, build the reference's prompt text and mask the prompt span."""
+    import random
+    import sys
+    from dualhyp_b200 import av_dataset as A
+    A.install_as_data()
+    from data.av_dataset import AVDataset, DualHypothesesAVDataset, DualHypothesesAlignAVDataset, DualHypothesesAlign2AVDataset
+    assert sys.modules["data.av_dataset"] is A
+    path = str(tmp_path / "train.json")
+    recs = _write_nbest_json(path)
+    tok = _CharTokenizer()
+    driver_kwargs = dict(nhyps_key="nhyps_asr", max_input_length=-1, max_nhyps=3, tokenizer=tok, audio_corruption_enabled=False,
+                         visual_corruption_enabled=False, apply_chat_template=False)
+
+    ger = AVDataset(split="train", json_path=path, prompts_format="GER", random_sample_nhyps=False, **driver_kwargs)
+    assert len(ger) == 3 and ger.idx2uid == ["utt0", "utt1", "utt2"]
+    random.seed(5)
+    item = ger[1]
+    rec = next(r for r in recs if r["Uid"] == "utt1" and item["input"].find(r["nhyps_asr"]["hyps"][0]) >= 0)
+    h = rec["nhyps_asr"]["hyps"]
+    expect = A.GER_PROMPTS["prompt_1"] + h[0] + A.GER_PROMPTS["prompt_2"] + "\n" + "\n".join(h[1:3]) + A.GER_PROMPTS["prompt_3"]
+    assert item["input"] == expect + rec["Caption"] + "</s>" and item["uid"] == "utt1" and item["ground_truth"] == rec["Caption"]
+    n = item["input_ids_no_response"].numel()
+    assert item["input_ids_no_response"].tolist() == tok.encode(expect)
+    assert (item["labels"][:n] == -1).all() and torch.equal(item["labels"][n:], item["input_ids"][n:])
+    assert item["audio"] is None and item["video"] is None
+
+    dual = DualHypothesesAVDataset(split="train", json_path=path, prompts_format="DualHyp", random_sample_nhyps=False, **driver_kwargs)
+    seen_mixed = False
+    for s in range(20):                                               # independent draws: ASR and VSR lists of different records do occur
+        random.seed(s)
+        t = dual[0]["input"]
+        seen_mixed |= ("asr0.0" in t and "vsr0.1" in t) or ("asr0.1" in t and "vsr0.0" in t)
+        assert "<<<" not in t and t.endswith("the true words 0</s>")
+    assert seen_mixed
+
+    al = DualHypothesesAlignAVDataset(split="train", json_path=path, prompts_format="DualAlign", **driver_kwargs)
+    al2 = DualHypothesesAlign2AVDataset(split="train", json_path=path, prompts_format="DualAlign2", **driver_kwargs)
+    for s in range(20):                                               # aligned: both lists always from the same record
+        random.seed(s)
+        t = al[2]["input"]
+        assert ("asr2.0" in t) != ("asr2.1" in t) and ("asr2.0" in t) == ("vsr2.0" in t)
+        t2 = al2[2]["input"]
+        v = "0" if "asr2.0" in t2 else "1"
+        assert f"asr2.{v} other 0\nasr2.{v} other 1" in t2 and f"vsr2.{v} other 0\nvsr2.{v} other 1" in t2       # n-best order kept
+    short = DualHypothesesAlignAVDataset(split="val", json_path=path, **{**driver_kwargs, "max_input_length": 40})
+    assert short[0]["input_ids"].numel() == 40 and short[0]["labels"].numel() == 40
+
+    batch = al.collate_fn([al[0], al[1], al[2]], pack=True)
+    assert batch["input_ids"].shape == batch["labels"].shape and batch["input_ids"].shape[0] == 3 and len(batch["uid"]) == 3
+    assert batch["packed"]["cu_seqlens"].numel() == 4 and batch["packed"]["input_ids"].numel() == int(batch["packed"]["cu_seqlens"][-1])
+    assert al.get_max_seq_length()[0] >= 40
+    with pytest.raises(ValueError):
+        AVDataset(split="train", json_path=path, prompts_format="NoSuchFormat", tokenizer=tok)
+    both = AVDataset(split="train", json_path=[path, str(tmp_path / "x_pretrain.json")], tokenizer=tok) if _write_nbest_json(str(tmp_path / "x_pretrain.json"), 2, 1) else None
+    assert len(both) == 5 and "utt0_pretrain" in both.uid2sample
+
+
+@pytest.mark.skipif(not __import__("os").path.isfile("/root/reference/data/prompts.py"), reason="reference checkout not mounted")
+def test_av_dataset_shim_templates_equal_the_live_reference():
+    from dualhyp_b200 import av_dataset as A
+    ns = {}
+    exec(open("/root/reference/data/prompts.py").read(), ns)
+    assert A.GER_PROMPTS == ns["GER_PROMPTS"] and A.DUALHYP_PROMPTS == ns["DualHyp_PROMPTS"]
+    assert A.get_prompts_format("GER") == ns["get_prompts_format"]("GER") and A.get_prompts_format("DualHyp") == ns["get_prompts_format"]("DualHyp")
