@@ -41,17 +41,18 @@ LORA = dict(r=8, alpha=16, dropout=0.05, to_query=True, to_key=True, to_value=Tr
 
 
 def measured_traffic():
-    """profiles/traffic.json (scripts/capture_traffic.py: ncu --set full of a build) -- valid only for the libdualhyp.so it was captured
-    from; returns ({} , why) otherwise."""
-    import hashlib
+    """profiles/traffic.json (scripts/capture_traffic.py: ncu --set full of a build) -- valid only for the kernel sources it was
+    captured from (`_lib.source_id()`: comment- and space-insensitive hash of csrc/ + the header; the library file is not hashed,
+    nvcc does not reproduce it byte for byte); returns ({} , why) otherwise."""
     try:
+        from dualhyp_b200 import _lib as _l
         t = json.load(open(os.path.join(ROOT, "profiles", "traffic.json")))
-        sha = hashlib.sha256(open(os.path.join(ROOT, "dualhyp_b200", "libdualhyp.so"), "rb").read()).hexdigest()[:16]
+        sha = _l.source_id()
     except Exception as e:  # noqa: BLE001
         return {}, f"no capture ({type(e).__name__})"
-    if t.get("so_sha16") != sha:
-        return {}, f"profiles/traffic.json was captured from build {t.get('so_sha16')}, this run uses {sha}: not reported"
-    return t, f"{t.get('source')}, build {sha}"
+    if t.get("src_sha16") != sha:
+        return {}, f"profiles/traffic.json was captured from sources {t.get('src_sha16')}, this run uses {sha}: not reported"
+    return t, f"{t.get('source')}, kernel sources {sha}"
 
 
 def parse_args():

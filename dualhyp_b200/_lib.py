@@ -147,3 +147,24 @@ def init(device: int = 0) -> None:
         return
     check(load().dh_init(device), "dh_init")
     _initialised_device = device
+
+
+def source_id() -> str:
+    """Identity of the device code for evidence files (profiles/traffic.json): sha256 over the kernel sources with comments and
+    white space removed.  The library file itself is not hashed: nvcc does not write byte-identical files from identical sources, and
+    build() recompiles on every fresh checkout."""
+    import glob
+    import hashlib
+    import re
+    root = os.path.dirname(_HERE)
+    files = sorted(glob.glob(os.path.join(_HERE, "csrc", "*.cu")) + glob.glob(os.path.join(_HERE, "csrc", "*.cuh"))) + \
+        [os.path.join(_HERE, "csrc", "Makefile"), os.path.join(root, "include", "dualhyp.h")]
+    h = hashlib.sha256()
+    for f in files:
+        text = open(f, "r", encoding="utf-8", errors="replace").read()
+        if not f.endswith("Makefile"):
+            text = re.sub(r"/\*.*?\*/", "", text, flags=re.S)
+            text = re.sub(r"//[^\n]*", "", text)
+        h.update(os.path.basename(f).encode())
+        h.update(re.sub(r"\s+", "", text).encode())
+    return h.hexdigest()[:16]

@@ -21,11 +21,13 @@ ROOT = os.path.dirname(os.path.dirname(os.path.abspath(__file__)))
 
 
 def so_hash() -> str:
-    return hashlib.sha256(open(os.path.join(ROOT, "dualhyp_b200", "libdualhyp.so"), "rb").read()).hexdigest()[:16]
+    sys.path.insert(0, ROOT)
+    from dualhyp_b200 import _lib
+    return _lib.source_id()
 
 
 def main():
-    out = {"so_sha16": so_hash(), "source": "ncu --set full, dram__bytes_read.sum + dram__bytes_write.sum per launch (scripts/capture_traffic.py)"}
+    out = {"src_sha16": so_hash(), "source": "ncu --set full, dram__bytes_read.sum + dram__bytes_write.sum per launch (scripts/capture_traffic.py)"}
     allrows = list(csv.DictReader(l for l in open(sys.argv[1]) if not l.startswith("==")))
     units = allrows[0]                       # the raw page's second line holds the unit of every column
     mult = {"byte": 1.0, "kbyte": 1e3, "mbyte": 1e6, "gbyte": 1e9}

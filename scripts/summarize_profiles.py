@@ -14,7 +14,9 @@ ROOT = os.path.dirname(os.path.dirname(os.path.abspath(__file__)))
 tag = sys.argv[1]
 G = lambda name: os.path.join(ROOT, "gpurun_out", f"{tag}_{name}")  # noqa: E731
 P = lambda name: os.path.join(ROOT, "profiles", name)  # noqa: E731
-sha = hashlib.sha256(open(os.path.join(ROOT, "dualhyp_b200", "libdualhyp.so"), "rb").read()).hexdigest()[:16]
+sys.path.insert(0, ROOT)
+from dualhyp_b200 import _lib  # noqa: E402
+sha = _lib.source_id()          # comment- and space-insensitive hash of the kernel sources (the .so is not reproducible byte for byte)
 
 # ---- 1. launch list of one adapter step ----
 rows = [(x["Kernel Name"], float(x["Metric Value"])) for x in csv.DictReader(l for l in open(G("launches.csv")) if not l.startswith("=="))]
@@ -27,7 +29,7 @@ for n, v in step:
     d[1] += v
 tot = sum(v[1] for v in agg.values())
 out = [f"ncu --metrics gpu__time_duration.sum --clock-control none launch list of ONE adapter fine-tune step (bench.py --steps 1 --warmup 3, 16 packed prompts), "
-       f"build {sha}", f"{len(step)} launches, {tot / 1e3:.1f} us sum of kernel durations (cold-cache, serialised: compare SHARES with bench.py's by_op_ms_per_step)"]
+       f"sources {sha}", f"{len(step)} launches, {tot / 1e3:.1f} us sum of kernel durations (cold-cache, serialised: compare SHARES with bench.py's by_op_ms_per_step)"]
 for k, v in sorted(agg.items(), key=lambda kv: -kv[1][1]):
     out.append(f"{k:72s} x{v[0]:5d} {v[1] / v[0] / 1e3:8.2f} us {v[1] / 1e3:9.1f} us/step {100 * v[1] / tot:5.1f}%")
 dh = sum(v[1] for k, v in agg.items() if "dh::" in k)
@@ -44,7 +46,7 @@ for rep in REPS:
 cols = ["Grid Size", "gpu__time_duration.sum", "dram__bytes_read.sum", "dram__bytes_write.sum", "sm__throughput.avg.pct_of_peak_sustained_elapsed",
         "sm__pipe_tensor_cycles_active.avg.pct_of_peak_sustained_active", "sm__warps_active.avg.pct_of_peak_sustained_active",
         "launch__registers_per_thread", "smsp__inst_executed.sum"]
-out = [f"ncu --set full --clock-control none, build {sha}, one adapter fine-tune step of 16 packed prompts",
+out = [f"ncu --set full --clock-control none, sources {sha}, one adapter fine-tune step of 16 packed prompts",
        "columns: kernel, grid, duration us, DRAM read MB, DRAM write MB, SM throughput %, tensor pipe active % (sm__pipe_tensor_cycles_active), warps active %, "
        "regs/thread, warp instructions, issue-active %, L2 sector hit rate %", ""]
 for rep in REPS:
@@ -79,7 +81,7 @@ for (_, n, g), d in per.items():
     a[2] += d.get("dram__bytes_read.sum", 0) + d.get("dram__bytes_write.sum", 0)
 tt, tb = sum(a[1] for a in agg.values()), sum(a[2] for a in agg.values())
 out = [f"ncu launch list (gpu__time_duration.sum, dram__bytes_read.sum + dram__bytes_write.sum; --clock-control none) of TWO eager decode token steps, 256 sequences, "
-       f"build {sha} (scripts/decode_traffic.py 256)",
+       f"sources {sha} (scripts/decode_traffic.py 256)",
        f"{sum(a[0] for a in agg.values()) // 2} kernels per token step, {tt / 2:.0f} us sum of kernel durations per step (cold-cache, serialised), "
        f"{tb / 2 / 1e9:.2f} GB of DRAM traffic per step",
        f"{'kernel':44s} {'grid':>14s} {'x/step':>6s} {'us each':>8s} {'us/step':>8s} {'MB each':>8s} {'GB/s':>7s}"]
