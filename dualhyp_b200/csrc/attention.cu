@@ -1845,8 +1845,8 @@ static int attention_decode_impl(int forced, const void* qkv, const void* cache_
   DH_CHECK(qkv && cache_k && cache_v && lens && out && nseq > 0, "dh_attention_decode: bad argument");
   DH_CHECK(q_per_kv <= DEC_MAX_QPK, "dh_attention_decode: q_per_kv %d > %d", q_per_kv, DEC_MAX_QPK);
   DH_CHECK(prefix_len >= 0 && prefix_len <= MAX_PREFIX, "dh_attention_decode: prefix_len too large");
-  // default: the streamed kernel (csrc/decode_attn.cu: TMA ring of 32-key chunks, eight flash-style warps, two blocks per SM; measured
-  // 2.55 vs 2.63 ms per token step at 256 sequences, 1.65 vs 1.72 ms at 128); DH_DEC_ATTN=mma selects the whole-row mma.sync kernel
+  // default: the streamed kernel (csrc/decode_attn.cu: one persistent block of 15 flash-style warps + a TMA producer per SM, K / V as a
+  // stream of 32-key chunks; measured 2.32 vs 2.63 ms per token step at 256 sequences, 1.56 vs 1.72 ms at 128); DH_DEC_ATTN=mma selects the whole-row mma.sync kernel
   // (also taken when the cache rows are not a multiple of 32 keys), DH_DEC_CUDA_CORES=1 the CUDA-core kernel (A/B runs)
   static int env_variant = -1;
   if (env_variant < 0) {
