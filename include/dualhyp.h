@@ -200,7 +200,8 @@ int dh_attention_decode(const void* qkv, const void* cache_k, const void* cache_
  * SM walks its share of the (sequence, kv group) items, their cached K / V rows stream through a TMA ring as 32-key chunks,
  * flash-style running softmax per warp, same arguments; prefix_len <= 32.  lens, prefix_kv and gate are read before
  * griddepcontrol.wait: they must not be the output of a kernel that signals programmatic launch completion early (none of this
- * library's producers of them does; a kernel launched without that attribute never does).
+ * library's producers of them does; a kernel launched without that attribute never does).  Cache slots at or beyond lens[i]
+ * may hold any FINITE values (their softmax weight is an exact zero, and 0 * NaN is not): allocate the cache zeroed.
  * dh_attention_decode_rows is the other one, explicitly: whole-row scores in shared memory on mma.sync tiles (what
  * DH_DEC_ATTN=mma selects, and the fallback for other row lengths). */
 int dh_attention_decode_stream(const void* qkv, const void* cache_k, const void* cache_v, const int32_t* lens, void* out,
