@@ -517,7 +517,44 @@ gemm_skinny_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constan
   if (warp >= 4) {
     pdl_wait();
     const int t = threadIdx.x - 128;
-    if (S == 1) {
+    if (S == 1 && EPI == DH_EPI_F32 && p.sk_partial) {
+      // Slice `split` of the [KS][M][ldo] partial products.  A thread holds a ROW of the accumulator (tcgen05.ld 32x32b), so storing
+      // from registers makes every store instruction touch 32 rows = 32 cache lines, 16 bytes each: 2048 line requests per warp
+      // for a 256 x 128 tile.  The idle ring transposes instead (padded 32 x 36 tile per warp, conflict-free both ways): a store
+      // instruction then writes 4 rows x 128 contiguous bytes.
+      const int q = warp & 3;
+      mbar_wait(tfull_bar, 0);
+      tc_fence_after();
+      float* outp = reinterpret_cast<float*>(p.out) + (long long)split * p.M * p.ldo + n0;
+      const uint32_t stg = smem_u32(smem) + (uint32_t)q * (32 * 36 * 4);
+      const int rsub = lane >> 3, cq = lane & 7;
+#pragma unroll 1
+      for (int rb = 0; rb < MB; ++rb) {
+        const int row0 = rb * BM + q * 32;
+        const int nrow = p.M - row0;                           // valid rows of this warp's 32-row block (may be <= 0)
+#pragma unroll 1
+        for (int g = 0; g < SK_BN / 32; ++g) {
+          uint32_t rg[32];
+          tmem_ld32(tmem_base + ((uint32_t)(q * 32) << 16) + rb * SK_BN + g * 32, rg);
+          tmem_wait_ld();
+#pragma unroll
+          for (int i = 0; i < 8; ++i)
+            asm volatile("st.shared.v4.f32 [%0], {%1, %2, %3, %4};" ::"r"(stg + lane * 144 + i * 16), "f"(__uint_as_float(rg[4 * i]) * p.alpha),
+                         "f"(__uint_as_float(rg[4 * i + 1]) * p.alpha), "f"(__uint_as_float(rg[4 * i + 2]) * p.alpha),
+                         "f"(__uint_as_float(rg[4 * i + 3]) * p.alpha)
+                         : "memory");
+          __syncwarp();
+#pragma unroll
+          for (int k = 0; k < 8; ++k) {
+            const int rr = 4 * k + rsub;
+            float4 v4;
+            asm volatile("ld.shared.v4.f32 {%0, %1, %2, %3}, [%4];" : "=f"(v4.x), "=f"(v4.y), "=f"(v4.z), "=f"(v4.w) : "r"(stg + rr * 144 + cq * 16));
+            if (rr < nrow) *reinterpret_cast<float4*>(outp + (long long)(row0 + rr) * p.ldo + g * 32 + cq * 4) = v4;
+          }
+          __syncwarp();
+        }
+      }
+    } else if (S == 1) {
       const int q = warp & 3;
       mbar_wait(tfull_bar, 0);
       tc_fence_after();
